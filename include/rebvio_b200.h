@@ -1,0 +1,241 @@
+/*
+ * rebvio_b200.h — C ABI of the B200-native (sm_100a) REBVIO hot path.
+ *
+ * Drop-in boundary for the reference's C++ class API (baumlin/rebvio). The reference has no FFI layer; the
+ * seam is the set of member functions that Rebvio's two worker loops call (rebvio/src/rebvio.cpp:70,142,165,
+ * 169,172,177,223,232,245,256,259). Each entry point below names the member function it replaces. The C++
+ * adapter classes in rebvio_b200/cpp/rebvio_b200/ carry the reference signatures and forward here.
+ *
+ * Conventions
+ *   - plain C: opaque handles, POD structs, caller-owned host buffers, int status returns (0 = RBV_OK).
+ *   - no exceptions / STL / torch types cross this boundary. All device memory is owned by the context.
+ *   - a context holds B independent "lanes" (one lane = one image sequence). Every call processes all B
+ *     lanes in one set of kernel launches; per-lane scalars are passed as arrays of length B (lane-major).
+ *     B = 1 is the reference's single-stream shape.
+ *   - host pointers may be pageable or pinned; calls are asynchronous on the context's CUDA stream unless
+ *     they return data to the host, in which case they synchronise that stream before returning.
+ *   - there is NO CPU fallback: if no sm_100 device / kernel image is usable, rbv_create fails with
+ *     RBV_ERR_CUDA and rbv_last_error() says why.
+ */
+#ifndef REBVIO_B200_H_
+#define REBVIO_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RBV_OK 0
+#define RBV_ERR_ARG 1      /* bad argument (null handle, lane count mismatch, size out of range) */
+#define RBV_ERR_CUDA 2     /* CUDA runtime / driver error, no device, wrong architecture          */
+#define RBV_ERR_STATE 3    /* call order violated (e.g. tracker stage before a distance field)   */
+
+/* reduction mode for the tracker's J^T J / J^T F sums (core.cpp:130-139,244-245)                     */
+#define RBV_REDUCE_FAST 0     /* warp-shuffle tree, FP64 accumulate, fixed order (deterministic)        */
+#define RBV_REDUCE_ORDERED 1  /* per-accumulator serial float32 adds in keyline order == CPU bits        */
+
+/* ---- POD mirrors of the reference's structs ------------------------------------------------------- */
+
+/* rebvio::Camera public fields read by the hot path (camera.hpp:61-72) */
+typedef struct rbv_camera {
+  float fm, cx, cy;
+  int rows, cols;
+} rbv_camera;
+
+/* rebvio::EdgeDetectorConfig (edge_detector.hpp:19-32); plane_fit_size=2 and num_bins=100 are constexpr there */
+typedef struct rbv_detector_cfg {
+  int keylines_ref;        /* 12000 */
+  int keylines_max;        /* 16000 */
+  float pos_neg_threshold; /* 0.4 */
+  float dog_threshold;     /* 0.095259868922420 */
+  float threshold;         /* 0.01 */
+  float gain;              /* 5e-7 */
+  float max_threshold;     /* 0.5 */
+  float min_threshold;     /* 0.005 */
+} rbv_detector_cfg;
+
+/* rebvio::EdgeMapConfig (edge_map.hpp:19-26) */
+typedef struct rbv_map_cfg {
+  float pixel_uncertainty_match;  /* 2.0 */
+  float match_threshold_norm;     /* 1.0 */
+  float match_threshold_angle;    /* 45.0 */
+  float regularization_threshold; /* 0.5 */
+} rbv_map_cfg;
+
+/* rebvio::CoreConfig (core.hpp:82-95) */
+typedef struct rbv_core_cfg {
+  float search_range;                        /* 40 */
+  float reweight_distance;                   /* 2 */
+  float match_treshold;                      /* 0.5 (spelling as in the reference) */
+  unsigned int min_match_threshold;          /* 0 */
+  unsigned int iterations;                   /* 5 */
+  unsigned int global_min_matches_threshold; /* 500 */
+  float pixel_uncertainty;                   /* 1 */
+  float quantile_cutoff;                     /* 0.9 */
+  int quantile_num_bins;                     /* 100 */
+  float reshape_q_abs;                       /* 1e-4 */
+} rbv_core_cfg;
+
+/* rebvio::types::KeyLine (types/keyline.hpp:24-60), 84 bytes, same field order */
+typedef struct rbv_keyline {
+  float pos[2];
+  float pos_img[2];
+  float match_pos_img[2];
+  float gradient[2];
+  float match_gradient[2];
+  float gradient_norm;
+  float match_gradient_norm;
+  float rho;
+  float sigma_rho;
+  int id;
+  int id_prev;
+  int id_next;
+  int match_id;
+  int match_id_forward;
+  int match_id_keyframe;
+  unsigned int matches;
+} rbv_keyline;
+
+void rbv_default_camera(rbv_camera* cam);             /* camera.hpp:26-37 (EuRoC cam0, 752x480) */
+void rbv_default_detector_cfg(rbv_detector_cfg* cfg); /* edge_detector.hpp:19-32 */
+void rbv_default_map_cfg(rbv_map_cfg* cfg);           /* edge_map.hpp:19-26 */
+void rbv_default_core_cfg(rbv_core_cfg* cfg);         /* core.hpp:82-95 */
+
+/* ---- handles ---------------------------------------------------------------------------------------- */
+
+typedef struct rbv_ctx rbv_ctx; /* EdgeDetector + Core for B lanes: scale-space scratch, id mask, distance field */
+typedef struct rbv_map rbv_map; /* B EdgeMaps (one per lane): keyline SoA + pixel->id mask, device resident    */
+
+/* replaces EdgeDetector::EdgeDetector (edge_detector.cpp:17-26) + Core::Core (core.cpp:18-25) for `lanes`
+ * sequences on CUDA device `device`. Pre-computes the box widths / divisor tables (scale_space.cpp:14-41,
+ * 130-171) and the 3x25 plane-fit pseudo inverse (edge_detector.cpp:55-68). */
+int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map_cfg* map,
+               const rbv_core_cfg* core, int device, int lanes, rbv_ctx** out);
+void rbv_destroy(rbv_ctx* ctx);
+const char* rbv_last_error(void);
+int rbv_sync(rbv_ctx* ctx);
+int rbv_set_reduce_mode(rbv_ctx* ctx, int mode); /* RBV_REDUCE_FAST (default) | RBV_REDUCE_ORDERED */
+int rbv_lanes(const rbv_ctx* ctx);
+/* run every subsequent call on the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)
+ * instead of the context's own; lets a host framework time the work with its own events. */
+int rbv_set_stream(rbv_ctx* ctx, void* cuda_stream);
+/* number of kernels this context has launched since rbv_create (bench.py's gpu_launches) */
+unsigned long long rbv_launch_count(const rbv_ctx* ctx);
+
+/* allocate / free a B-lane map (replaces std::make_shared<EdgeMap>, edge_detector.cpp:50). */
+int rbv_map_create(rbv_ctx* ctx, rbv_map** out);
+void rbv_map_release(rbv_ctx* ctx, rbv_map* map);
+
+/* ---- front end -------------------------------------------------------------------------------------- */
+
+/* replaces EdgeDetector::detect → buildEdgeMap + joinEdges + tuneThreshold (edge_detector.cpp:30-186) for B
+ * frames. `images`: B pointers to host float32 frames (row pitch `pitch_bytes`), values 0..765 as produced by
+ * Rebvio::imageCallback (rebvio.cpp:43-45). `threshold[B]` is the (already servoed) config_->threshold of each
+ * lane (edge_detector.cpp:33-36 stays on the host: rbv_servo_threshold). Outputs (host, length B, optional):
+ * keyline counts and the auto threshold written to map->threshold(). The call copies H2D, launches, and
+ * returns after the counts are back on the host. */
+int rbv_detect(rbv_ctx* ctx, rbv_map* map, const float* const* images, size_t pitch_bytes,
+               const uint64_t* ts_us, const float* threshold, int* n_keylines, float* auto_threshold);
+
+/* same, frames already resident in device memory (lane-major contiguous [B][rows][cols] float32). */
+int rbv_detect_device(rbv_ctx* ctx, rbv_map* map, const float* d_images, const uint64_t* ts_us,
+                      const float* threshold, int* n_keylines, float* auto_threshold);
+
+/* host scalar servo of edge_detector.cpp:33-36: returns the new config_->threshold. */
+float rbv_servo_threshold(const rbv_detector_cfg* cfg, float threshold, int last_keyline_count);
+
+/* ---- tracker ---------------------------------------------------------------------------------------- */
+
+/* Core::buildDistanceField (core.cpp:33-37, core.hpp:37-59) from `map`; ctx remembers `map` as the
+ * distance-field map used by rbv_ext_rot_vel / rbv_update_inverse_depth (core.hpp:39,63,78). */
+int rbv_build_distance_field(rbv_ctx* ctx, rbv_map* map);
+
+/* EdgeMap::rotateKeylines (edge_map.cpp:58-71); R: B row-major 3x3. */
+int rbv_rotate_keylines(rbv_ctx* ctx, rbv_map* map, const float* R9);
+
+/* EdgeMap::estimateQuantile (edge_map.cpp:39-56) */
+int rbv_estimate_quantile(rbv_ctx* ctx, rbv_map* map, float percentile, int num_bins, float* out);
+
+/* Core::tryVel (core.cpp:78-148): one energy/Jacobian evaluation at vel[B][3] with sigma_rho cut
+ * sigma_rho_min[B]. Residuals live on the device with the map (reset with rbv_reset_residuals).
+ * Outputs per lane: JtJ[9], JtF[3], score. */
+int rbv_reset_residuals(rbv_ctx* ctx, rbv_map* map);
+int rbv_try_vel(rbv_ctx* ctx, rbv_map* map, const float* vel3, const float* sigma_rho_min, float* JtJ9,
+                float* JtF3, float* score);
+
+/* Core::minimizeVel (core.cpp:150-189): quantile + (1+iterations) tryVel + 3x3 LM steps, all on device.
+ * vel3 in/out [B][3], Rvel9 out [B][9], score out [B]. Any output pointer may be NULL (stays on device
+ * for the following stages). */
+int rbv_minimize_vel(rbv_ctx* ctx, rbv_map* old_map, float* vel3, float* Rvel9, float* score);
+
+/* EdgeMap::forwardMatch (edge_map.cpp:73-99): old → new; n_matches[B] optional. */
+int rbv_forward_match(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, int* n_matches);
+
+/* Core::extRotVel (core.cpp:191-261) on the distance-field map. Wx36/X6 per lane, ok[B] = 1/0. */
+int rbv_ext_rot_vel(rbv_ctx* ctx, rbv_map* new_map, const float* vel3, float* Wx36, float* X6, int* ok);
+
+/* EdgeMap::directedMatch + searchMatch (edge_map.cpp:101-218): new searches in old. */
+int rbv_directed_match(rbv_ctx* ctx, rbv_map* new_map, rbv_map* old_map, const float* vel3,
+                       const float* Rvel9, const float* Rback9, float max_radius, int* kf_matches,
+                       int* n_matches);
+
+/* EdgeMap::regularize1Iter (edge_map.cpp:220-259) */
+int rbv_regularize(rbv_ctx* ctx, rbv_map* map, int* n_regularized);
+
+/* Core::updateInverseDepth (core.cpp:417-456) on the distance-field map */
+int rbv_update_inverse_depth(rbv_ctx* ctx, const float* vel3);
+
+/* ---- fused per-frame graphs (CUDA-graph captured; what Rebvio::stateEstimationProcess calls in order) --- */
+
+/* G1 = buildDistanceField(new) ; rotateKeylines(old, R) ; minimizeVel(old) ; forwardMatch(old,new) ;
+ *      extRotVel(new)   (rebvio.cpp:142,165,169,172,177). One launch of a captured graph + one D2H.
+ * in : R9[B][9]      out: vel3[B][3] (Vg), Rvel9[B][9] (P_Vg), Wx36, X6, ok[B]                         */
+int rbv_track_g1(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const float* R9, float* vel3,
+                 float* Rvel9, float* Wx36, float* X6, int* ok);
+
+/* G2 = rotateKeylines(old, R0) ; directedMatch(new, old, V, P_V, Rgva) ; regularize1Iter(new) ;
+ *      updateInverseDepth(V)   (rebvio.cpp:223/232,245,256,259). `min_matches`: lanes whose directed-match
+ * count is below it skip regularise + Kalman exactly as rebvio.cpp:247-260 does.                        */
+int rbv_track_g2(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const float* R0_9, const float* V3,
+                 const float* PV9, const float* Rgva9, float max_radius, int min_matches, int* n_matches,
+                 int* kf_matches);
+
+/* ---- host mirror (EdgeMap::keylines(), operator[], mask(), size(), threshold(); edge_map.hpp:40-75) ---- */
+
+int rbv_map_size(rbv_ctx* ctx, rbv_map* map, int* n_keylines /*[B]*/);
+int rbv_map_threshold(rbv_ctx* ctx, rbv_map* map, float* threshold /*[B]*/);
+int rbv_map_set_threshold(rbv_ctx* ctx, rbv_map* map, const float* threshold /*[B]*/);
+/* AoS download of one lane: keylines (84 B each, capacity `cap`), detection pixel index per keyline
+ * (= key of EdgeMap::mask()), returns count in *n. */
+int rbv_map_download(rbv_ctx* ctx, rbv_map* map, int lane, rbv_keyline* keylines, uint32_t* pixel_idx,
+                     int cap, int* n);
+/* AoS upload of one lane (teacher forcing / callers that mutate keylines()). pixel_idx may be NULL to keep
+ * the mask untouched. */
+int rbv_map_upload(rbv_ctx* ctx, rbv_map* map, int lane, const rbv_keyline* keylines,
+                   const uint32_t* pixel_idx, int n);
+
+/* ---- debug taps used by the parity tests ---------------------------------------------------------------- */
+/* which: 0 = scale0, 1 = scale1, 2 = DoG, 3 = squared gradient magnitude; out: rows*cols float32 */
+int rbv_debug_read_image(rbv_ctx* ctx, int lane, int which, float* out);
+/* id mask of EdgeDetector (keylines_mask_, edge_detector.hpp:86) for the last detect: rows*cols int32 */
+int rbv_debug_read_mask(rbv_ctx* ctx, rbv_map* map, int lane, int* out);
+/* distance field: id and distance per pixel (core.hpp:15-18); distance is only defined where id >= 0 */
+int rbv_debug_read_field(rbv_ctx* ctx, int lane, int* id, int* distance);
+int rbv_debug_read_residuals(rbv_ctx* ctx, rbv_map* map, int lane, float* out, int cap);
+/* one box pass (createIntegralImage + average, scale_space.cpp:48-128) of width index `pass` of scale
+ * `scale` applied to a host image; for the first-kernel parity test. */
+int rbv_debug_box_pass(rbv_ctx* ctx, int scale, int pass, const float* in, float* out);
+/* the 3x25 plane-fit pseudo inverse and box widths the context computed */
+int rbv_debug_read_setup(rbv_ctx* ctx, float* pinv75, int* widths6);
+/* LM trace of the last rbv_minimize_vel: per tryVel call t=0..iterations: vel[3], JtJ[9], JtF[3], score
+ * (16 floats each); out capacity (iterations+1)*16 floats per lane. */
+int rbv_debug_read_lm_trace(rbv_ctx* ctx, int lane, float* out, int cap_floats);
+/* mean number of mask probes per keyline in the last directed match (P-bar of the byte model) */
+int rbv_debug_read_probe_count(rbv_ctx* ctx, int lane, unsigned long long* probes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REBVIO_B200_H_ */

@@ -1,0 +1,567 @@
+// ref_harness.cpp — C API over the UNMODIFIED reference (baumlin/rebvio) compiled from /root/reference.
+//
+// TEST INFRASTRUCTURE: parity checker and timed CPU baseline only. Built by oracle/Makefile into
+// oracle/_ref/librebvio_ref.so (git-ignored). Nothing in the product path links or loads it; only tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may.
+//
+// No reference source is copied: this file only *calls* the reference classes. The one piece restated here
+// is the body of Rebvio::stateEstimationProcess (rebvio/src/rebvio.cpp:119-292) as a single-threaded,
+// deterministic driver (the real one is two racing threads with a fixed camera), and the
+// LM loop of Core::minimizeVel (core.cpp:150-189) as a *tracing* variant whose result the tests assert to be
+// bit-identical to the real Core::minimizeVel.
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <iostream>
+#include <limits>
+#include <memory>
+#include <queue>
+#include <sstream>
+#include <vector>
+#include <chrono>
+
+// reach private members of the reference classes for taps (scale images, id mask, distance field) without
+// touching the reference sources. Access specifiers do not change layout or mangling with GCC.
+#define private public
+#define protected public
+#include "rebvio/camera.hpp"
+#include "rebvio/core.hpp"
+#include "rebvio/edge_detector.hpp"
+#include "rebvio/edge_map.hpp"
+#include "rebvio/sab_estimator.hpp"
+#include "rebvio/scale_space.hpp"
+#include "rebvio/types/imu.hpp"
+#include "rebvio/types/odometry.hpp"
+#include <TooN/Cholesky.h>
+#include <TooN/so3.h>
+#undef private
+#undef protected
+
+#include "../include/rebvio_b200.h"
+
+using namespace rebvio;
+using types::Float;
+
+static_assert(sizeof(types::KeyLine) == sizeof(rbv_keyline), "KeyLine layout drifted from rbv_keyline");
+
+namespace {
+
+struct RefCtx {
+  Camera::SharedPtr cam;
+  EdgeDetectorConfig::SharedPtr det_cfg;
+  CoreConfig::SharedPtr core_cfg;
+  std::unique_ptr<EdgeDetector> detector;
+  std::unique_ptr<Core> core;
+  std::unique_ptr<ScaleSpace> scale_space;  // separate instance for image taps
+  std::vector<EdgeMap::SharedPtr> maps;
+
+  // ---- deterministic pipeline state (locals/members of Rebvio, rebvio.cpp:95-115, rebvio.hpp:92-101)
+  types::ImuStateConfig imu_cfg;
+  types::ImuState imu_state;
+  std::unique_ptr<SABEstimator::State> sab_state;
+  std::queue<types::Imu> imu_buffer;
+  std::queue<EdgeMap::SharedPtr> edge_map_buffer;
+  unsigned int num_frames = 0;
+  bool run = true;
+  Float K = 1.0;
+  types::Vector3f V = TooN::Zeros, W = TooN::Zeros, Pos = TooN::Zeros;
+  types::Matrix3f R = TooN::Identity, R_global = TooN::Identity, Rgva = TooN::Identity;
+  Float P_Kp = 5e-6;
+  types::Matrix3f P_V, P_W;
+  int num_gyro_init = 0;
+  types::Vector3f gyro_init = TooN::Zeros, g_init = TooN::Zeros;
+  double t_detect = 0, t_track = 0;  // accumulated seconds (cpu baseline)
+  double t_stage[12] = {0};
+};
+
+inline void to_m3(const float* in, types::Matrix3f& m) {
+  for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) m(r, c) = in[r * 3 + c];
+}
+inline void from_m3(const types::Matrix3f& m, float* out) {
+  for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) out[r * 3 + c] = m(r, c);
+}
+inline double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // namespace
+
+extern "C" {
+
+void* ref_create(const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_core_cfg* core) {
+  RefCtx* c = new RefCtx;
+  c->cam = std::make_shared<Camera>();
+  c->cam->fm_ = cam->fm; c->cam->fx_ = cam->fm; c->cam->fy_ = cam->fm;
+  c->cam->cx_ = cam->cx; c->cam->cy_ = cam->cy;
+  c->cam->rows_ = cam->rows; c->cam->cols_ = cam->cols;
+  c->det_cfg = std::make_shared<EdgeDetectorConfig>();
+  c->det_cfg->keylines_ref = det->keylines_ref;
+  c->det_cfg->keylines_max = det->keylines_max;
+  c->det_cfg->pos_neg_threshold = det->pos_neg_threshold;
+  c->det_cfg->dog_threshold = det->dog_threshold;
+  c->det_cfg->threshold = det->threshold;
+  c->det_cfg->gain = det->gain;
+  c->det_cfg->max_threshold = det->max_threshold;
+  c->det_cfg->min_threshold = det->min_threshold;
+  c->core_cfg = std::make_shared<CoreConfig>();
+  c->core_cfg->search_range = core->search_range;
+  c->core_cfg->reweight_distance = core->reweight_distance;
+  c->core_cfg->match_treshold = core->match_treshold;
+  c->core_cfg->min_match_threshold = core->min_match_threshold;
+  c->core_cfg->iterations = core->iterations;
+  c->core_cfg->global_min_matches_threshold = core->global_min_matches_threshold;
+  c->core_cfg->pixel_uncertainty = core->pixel_uncertainty;
+  c->core_cfg->quantile_cutoff = core->quantile_cutoff;
+  c->core_cfg->quantile_num_bins = core->quantile_num_bins;
+  c->core_cfg->reshape_q_abs = core->reshape_q_abs;
+  c->detector.reset(new EdgeDetector(c->cam, c->det_cfg));
+  c->core.reset(new Core(c->cam, c->core_cfg));
+  c->scale_space.reset(new ScaleSpace(c->cam));
+  c->sab_state.reset(new SABEstimator::State(c->imu_cfg));
+  c->P_V = TooN::Identity * std::numeric_limits<Float>::max();
+  c->P_W = TooN::Identity * 1e-10;
+  return c;
+}
+
+void ref_destroy(void* h) { delete static_cast<RefCtx*>(h); }
+
+// default-constructed reference structs → PODs, so the product's rbv_default_* can be checked against them
+void ref_defaults(rbv_camera* cam, rbv_detector_cfg* det, rbv_map_cfg* map, rbv_core_cfg* core) {
+  Camera c; EdgeDetectorConfig d; EdgeMapConfig m; CoreConfig k;
+  *cam = rbv_camera{c.fm_, c.cx_, c.cy_, int(c.rows_), int(c.cols_)};
+  *det = rbv_detector_cfg{d.keylines_ref, d.keylines_max, d.pos_neg_threshold, d.dog_threshold, d.threshold,
+                          d.gain, d.max_threshold, d.min_threshold};
+  *map = rbv_map_cfg{m.pixel_uncertainty_match, m.match_threshold_norm, m.match_threshold_angle,
+                     m.regularization_threshold};
+  *core = rbv_core_cfg{k.search_range, k.reweight_distance, k.match_treshold, k.min_match_threshold,
+                       k.iterations, k.global_min_matches_threshold, k.pixel_uncertainty, k.quantile_cutoff,
+                       k.quantile_num_bins, k.reshape_q_abs};
+}
+
+void ref_camera_extrinsics(float* Rc2i9, float* tc2i3) {
+  Camera c;
+  from_m3(c.getRc2i(), Rc2i9);
+  for (int i = 0; i < 3; ++i) tc2i3[i] = c.getTc2i()[i];
+}
+
+// ---- scale space taps -------------------------------------------------------------------------------
+// FastGaussian setup (scale_space.cpp:14-41): widths[6] = 3 per scale, sigma_true[2]
+void ref_scale_setup(void* h, int* widths6, float* sigma_true2) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  for (int s = 0; s < 2; ++s) {
+    for (int i = 0; i < 3; ++i) widths6[s * 3 + i] = c->scale_space->filter_[s].widths_[i];
+    sigma_true2[s] = c->scale_space->filter_[s].sigma_true_;
+  }
+}
+void ref_divisors(void* h, int scale, int pass, float* out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  cv::Mat& d = c->scale_space->filter_[scale].divisors_[pass];
+  std::memcpy(out, d.data, sizeof(float) * d.rows * d.cols);
+}
+// one createIntegralImage (scale_space.cpp:48-67)
+void ref_integral(void* h, const float* in, float* out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  cv::Mat m(c->cam->rows_, c->cam->cols_, CV_32FC1, const_cast<float*>(in));
+  cv::Mat ii = c->scale_space->filter_[0].createIntegralImage(m);
+  std::memcpy(out, ii.data, sizeof(float) * ii.rows * ii.cols);
+}
+// one box pass = createIntegralImage + average with width index `pass` of scale `scale`
+void ref_box_pass(void* h, int scale, int pass, const float* in, float* out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  FastGaussian& f = c->scale_space->filter_[scale];
+  cv::Mat m(c->cam->rows_, c->cam->cols_, CV_32FC1, const_cast<float*>(in));
+  cv::Mat ii = f.createIntegralImage(m);
+  cv::Mat av = f.average(ii, f.widths_[pass], f.divisors_[pass]);
+  std::memcpy(out, av.data, sizeof(float) * av.rows * av.cols);
+}
+// ScaleSpace::build (scale_space.cpp:203-208); any output may be null
+void ref_scale_space(void* h, const float* img, float* s0, float* s1, float* dog, float* mag) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  cv::Mat m(c->cam->rows_, c->cam->cols_, CV_32FC1, const_cast<float*>(img));
+  c->scale_space->build(m);
+  size_t nb = sizeof(float) * c->cam->rows_ * c->cam->cols_;
+  if (s0) std::memcpy(s0, c->scale_space->scale_[0].data, nb);
+  if (s1) std::memcpy(s1, c->scale_space->scale_[1].data, nb);
+  if (dog) std::memcpy(dog, c->scale_space->dog_.data, nb);
+  if (mag) std::memcpy(mag, c->scale_space->gradient_mag_.data, nb);
+}
+
+// ---- front end ---------------------------------------------------------------------------------------
+float ref_get_threshold(void* h) { return static_cast<RefCtx*>(h)->det_cfg->threshold; }
+void ref_set_threshold(void* h, float t) { static_cast<RefCtx*>(h)->det_cfg->threshold = t; }
+void ref_set_last_count(void* h, int n) { static_cast<RefCtx*>(h)->detector->keylines_count_ = n; }
+
+// EdgeDetector::detect (edge_detector.cpp:30-43) → map handle
+int ref_detect(void* h, const float* img, uint64_t ts_us) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Image im;
+  im.ts_us = ts_us;
+  im.data = cv::Mat(c->cam->rows_, c->cam->cols_, CV_32FC1, const_cast<float*>(img));
+  double t0 = now_s();
+  EdgeMap::SharedPtr map = c->detector->detect(im);
+  c->t_detect += now_s() - t0;
+  c->maps.push_back(map);
+  return int(c->maps.size()) - 1;
+}
+void ref_detector_mask(void* h, int* out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  std::memcpy(out, c->detector->keylines_mask_.data, sizeof(int) * c->cam->rows_ * c->cam->cols_);
+}
+void ref_map_free(void* h, int m) { static_cast<RefCtx*>(h)->maps[m].reset(); }
+int ref_map_new(void* h, uint64_t ts_us) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  c->maps.push_back(std::make_shared<EdgeMap>(c->cam, c->det_cfg->keylines_max, ts_us));
+  return int(c->maps.size()) - 1;
+}
+int ref_map_size(void* h, int m) { return static_cast<RefCtx*>(h)->maps[m]->size(); }
+float ref_map_threshold(void* h, int m) { return static_cast<RefCtx*>(h)->maps[m]->threshold(); }
+void ref_map_set_threshold(void* h, int m, float t) { static_cast<RefCtx*>(h)->maps[m]->threshold(t); }
+void ref_map_get(void* h, int m, rbv_keyline* out) {
+  EdgeMap& map = *static_cast<RefCtx*>(h)->maps[m];
+  if (map.size()) std::memcpy(out, map.keylines().data(), sizeof(rbv_keyline) * map.size());
+}
+// overwrite (or resize) the keyline vector; pixel_idx (optional) rebuilds the pixel->id lookup (EdgeMap::mask())
+void ref_map_set(void* h, int m, const rbv_keyline* in, const uint32_t* pixel_idx, int n) {
+  EdgeMap& map = *static_cast<RefCtx*>(h)->maps[m];
+  std::vector<types::KeyLine>& v = map.keylines();
+  if (int(v.size()) != n) {
+    types::Point2Df p = TooN::Zeros; types::Vector2f g = TooN::Zeros;
+    v.assign(n, types::KeyLine(p, g, TooN::makeVector(0.0f, 0.0f)));
+  }
+  if (n) std::memcpy(static_cast<void*>(v.data()), in, sizeof(rbv_keyline) * n);
+  if (pixel_idx) {
+    map.mask().clear();
+    for (int i = 0; i < n; ++i) map.mask().emplace(pixel_idx[i], i);
+  }
+}
+// pixel->id lookup as pairs (sorted by id): out_pixel[id]
+void ref_map_pixels(void* h, int m, uint32_t* out_pixel) {
+  EdgeMap& map = *static_cast<RefCtx*>(h)->maps[m];
+  for (auto& kv : map.mask()) out_pixel[kv.second] = kv.first;
+}
+int ref_map_mask_size(void* h, int m) { return int(static_cast<RefCtx*>(h)->maps[m]->mask().size()); }
+
+// ---- tracker stages ------------------------------------------------------------------------------------
+void ref_build_distance_field(void* h, int m) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  c->core->buildDistanceField(c->maps[m]);
+}
+void ref_field(void* h, int* id, int* dist) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  int n = c->cam->rows_ * c->cam->cols_;
+  for (int i = 0; i < n; ++i) { id[i] = c->core->distance_field_[i].id; dist[i] = c->core->distance_field_[i].distance; }
+}
+void ref_rotate(void* h, int m, const float* R9) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Matrix3f R; to_m3(R9, R);
+  c->maps[m]->rotateKeylines(R);
+}
+float ref_quantile(void* h, int m, float pct, int bins) { return static_cast<RefCtx*>(h)->maps[m]->estimateQuantile(pct, bins); }
+
+float ref_try_vel(void* h, int m, const float* vel3, float sigma_rho_min, float* residuals, float* JtJ9, float* JtF3) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Matrix3f JtJ; types::Vector3f JtF; types::Vector3f vel = TooN::makeVector(vel3[0], vel3[1], vel3[2]);
+  Float s = c->core->tryVel(c->maps[m], JtJ, JtF, vel, sigma_rho_min, residuals);
+  from_m3(JtJ, JtJ9);
+  for (int i = 0; i < 3; ++i) JtF3[i] = JtF[i];
+  return s;
+}
+float ref_minimize_vel(void* h, int m, float* vel3, float* Rvel9) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Vector3f vel = TooN::makeVector(vel3[0], vel3[1], vel3[2]);
+  types::Matrix3f Rvel;
+  Float s = c->core->minimizeVel(c->maps[m], vel, Rvel);
+  for (int i = 0; i < 3; ++i) vel3[i] = vel[i];
+  from_m3(Rvel, Rvel9);
+  return s;
+}
+// tracing LM loop: same statements as Core::minimizeVel (core.cpp:150-189) but records every tryVel call:
+// trace[(iter)*16 + {0..2 vel, 3..11 JtJ, 12..14 JtF, 15 score}], iter = 0..iterations. Also returns the final
+// residual vector (optional). Tests assert vel/Rvel/score == ref_minimize_vel bitwise.
+float ref_minimize_vel_trace(void* h, int m, float* vel3, float* Rvel9, float* trace, float* residuals_out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  EdgeMap::SharedPtr map = c->maps[m];
+  types::Vector3f vel = TooN::makeVector(vel3[0], vel3[1], vel3[2]);
+  Float sigma_rho_min = map->estimateQuantile(c->core_cfg->quantile_cutoff, c->core_cfg->quantile_num_bins);
+  types::Matrix3f JtJ, ApI, JtJnew; types::Vector3f JtF, JtFnew, hh, Vnew;
+  std::vector<Float> residuals(std::max(1, map->size()), 0.0f);
+  auto rec = [&](int it, const types::Vector3f& v, const types::Matrix3f& A, const types::Vector3f& b, Float s) {
+    float* t = trace + it * 16;
+    for (int i = 0; i < 3; ++i) t[i] = v[i];
+    from_m3(A, t + 3);
+    for (int i = 0; i < 3; ++i) t[12 + i] = b[i];
+    t[15] = s;
+  };
+  Float F = c->core->tryVel(map, JtJ, JtF, vel, sigma_rho_min, residuals.data());
+  rec(0, vel, JtJ, JtF, F);
+  Float v = 2.0, tau = 1e-3, u = tau * TooN::max_element(JtJ).first, gain;
+  for (unsigned iter = 0; iter < c->core_cfg->iterations; ++iter) {
+    ApI = JtJ + TooN::Identity * u;
+    hh = types::invert(ApI) * (-JtF);
+    Vnew = vel + hh;
+    Float Fnew = c->core->tryVel(map, JtJnew, JtFnew, Vnew, sigma_rho_min, residuals.data());
+    rec(iter + 1, Vnew, JtJnew, JtFnew, Fnew);
+    gain = (F - Fnew) / (0.5 * hh * (u * hh - JtF));
+    if (gain > 0.0) {
+      F = Fnew; vel = Vnew; JtJ = JtJnew; JtF = JtFnew;
+      u *= std::max(0.33, 1.0 - ((2.0 * gain - 1.0) * (2.0 * gain - 1.0) * (2.0 * gain - 1.0)));
+      v = 2.0;
+    } else { u *= v; v *= 2.0; }
+  }
+  types::Matrix3f Rvel = types::invert(JtJ);
+  for (int i = 0; i < 3; ++i) vel3[i] = vel[i];
+  from_m3(Rvel, Rvel9);
+  if (residuals_out) std::memcpy(residuals_out, residuals.data(), sizeof(float) * map->size());
+  return F;
+}
+int ref_forward_match(void* h, int old_m, int new_m) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  return c->maps[old_m]->forwardMatch(c->maps[new_m]);
+}
+int ref_ext_rot_vel(void* h, int new_m, const float* vel3, float* Wx36, float* X6) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Matrix6f Wx = TooN::Zeros; types::Vector6f X = TooN::Zeros;
+  bool ok = c->core->extRotVel(c->maps[new_m], TooN::makeVector(vel3[0], vel3[1], vel3[2]), Wx, X);
+  for (int r = 0; r < 6; ++r) { X6[r] = X[r]; for (int k = 0; k < 6; ++k) Wx36[r * 6 + k] = Wx(r, k); }
+  return ok ? 1 : 0;
+}
+int ref_directed_match(void* h, int new_m, int old_m, const float* vel3, const float* Rvel9, const float* Rback9,
+                       float max_radius, int* kf_matches) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Matrix3f Rvel, Rback; to_m3(Rvel9, Rvel); to_m3(Rback9, Rback);
+  int kf = 0;
+  int n = c->maps[new_m]->directedMatch(c->maps[old_m], TooN::makeVector(vel3[0], vel3[1], vel3[2]), Rvel, Rback, kf, max_radius);
+  if (kf_matches) *kf_matches = kf;
+  return n;
+}
+int ref_regularize(void* h, int m) { return static_cast<RefCtx*>(h)->maps[m]->regularize1Iter(); }
+void ref_update_inverse_depth(void* h, const float* vel3) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Vector3f v = TooN::makeVector(vel3[0], vel3[1], vel3[2]);
+  c->core->updateInverseDepth(v);
+}
+
+// ---- deterministic single-threaded pipeline ------------------------------------------------------------
+// Rebvio::imuCallback (rebvio.cpp:50-54)
+void ref_pipeline_imu(void* h, uint64_t ts, const float* gyro3, const float* acc3) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  types::Imu s;
+  s.ts = ts;
+  s.gyro = TooN::makeVector(gyro3[0], gyro3[1], gyro3[2]);
+  s.acc = TooN::makeVector(acc3[0], acc3[1], acc3[2]);
+  c->imu_buffer.push(s);
+}
+
+struct ref_frame_out {
+  uint64_t ts_us;
+  float orientation[3], position[3];
+  float V[3], Vg[3], Xv[6], Xgv[6], Xgva[6];
+  float P_Vg[9], P_V[9], R[9], Rgva[9], R0[9], W_Xv[36];
+  float score, K, frame_dt;
+  int n_new, n_old, fwd_matches, klm_num, kf_matches, reg_num, ok, estimated, stopped;
+  int old_map, new_map;
+};
+
+// One image: Rebvio::dataAcquisitionProcess body (rebvio.cpp:63-84), then — if two maps are queued — one
+// iteration of Rebvio::stateEstimationProcess (rebvio.cpp:121-289). IMU samples with ts <= image ts are
+// integrated BEFORE the estimation step (fixes the publication race described in SURVEY.md §5).
+// `img` must already be float32 x3 and undistorted (rebvio.cpp:43-45 is upstream of the hot path).
+int ref_pipeline_frame(void* h, const float* img, uint64_t ts_us, ref_frame_out* out) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  Camera& camera = *c->cam;
+  std::memset(out, 0, sizeof(*out));
+  out->ts_us = ts_us;
+  out->old_map = out->new_map = -1;
+  if (!c->run) { out->stopped = 1; return 0; }
+
+  int mi = ref_detect(h, img, ts_us);
+  EdgeMap::SharedPtr edge_map = c->maps[mi];
+  c->edge_map_buffer.push(edge_map);
+  while (!c->imu_buffer.empty()) {
+    if (c->imu_buffer.front().ts <= ts_us) {
+      edge_map->imu().add(c->imu_buffer.front(), camera.getRc2i());
+      c->imu_buffer.pop();
+    } else break;
+  }
+  out->n_new = edge_map->size();
+  out->new_map = mi;
+  if (c->edge_map_buffer.size() < 2) return 0;
+
+  double t0 = now_s();
+  EdgeMap::SharedPtr old_edge_map = c->edge_map_buffer.front();
+  c->edge_map_buffer.pop();
+  EdgeMap::SharedPtr new_edge_map = c->edge_map_buffer.front();
+  out->old_map = mi - 1;
+  out->n_old = old_edge_map->size();
+  out->estimated = 1;
+
+  types::ImuState& imu_state_ = c->imu_state;
+  SABEstimator::State& sab_state_ = *c->sab_state;
+  types::ImuStateConfig& icfg = c->imu_cfg;
+  types::Matrix3f& R = c->R; types::Matrix3f& Rgva = c->Rgva; types::Matrix3f& R_global = c->R_global;
+  types::Vector3f& V = c->V; types::Vector3f& W = c->W; types::Vector3f& Pos = c->Pos;
+  types::Matrix3f& P_V = c->P_V; types::Matrix3f& P_W = c->P_W;
+  Float& K = c->K; Float& P_Kp = c->P_Kp;
+
+  int klm_num = 0, num_kf_back_m = 0;
+  P_V = TooN::Identity * std::numeric_limits<Float>::max();
+  P_W = TooN::Identity * std::numeric_limits<Float>::max();
+  R = TooN::Identity;
+
+  double ts0 = now_s();
+  c->core->buildDistanceField(new_edge_map);
+  c->t_stage[0] += now_s() - ts0;
+
+  const types::IntegratedImu& imu = new_edge_map->imu().get(camera.getRc2i(), camera.getTc2i());
+  if (!imu_state_.initialized && c->num_frames > 0) {
+    if (icfg.init_bias > 0) {
+      c->gyro_init += imu.gyro() * imu.dt_s();
+      c->g_init -= imu.cacc();
+      if (++c->num_gyro_init > icfg.init_bias_frame_num) {
+        imu_state_.Bg = c->gyro_init / c->num_gyro_init;
+        imu_state_.W_Bg = types::invert(imu_state_.RGBias * 1e2);
+        sab_state_.X.slice<1, 3>() = c->g_init / c->num_gyro_init;
+        imu_state_.initialized = true;
+      }
+    } else {
+      imu_state_.initialized = true;
+      imu_state_.Bg = icfg.init_bias_guess * imu.dt_s();
+    }
+  }
+
+  R = imu.R();
+  R.T() = TooN::SO3<Float>(imu_state_.Bg) * R.T();
+  ts0 = now_s();
+  old_edge_map->rotateKeylines(R.T());
+  c->t_stage[1] += now_s() - ts0;
+
+  imu_state_.Vg = TooN::Zeros;
+  ts0 = now_s();
+  out->score = c->core->minimizeVel(old_edge_map, imu_state_.Vg, imu_state_.P_Vg);
+  c->t_stage[2] += now_s() - ts0;
+  ts0 = now_s();
+  out->fwd_matches = old_edge_map->forwardMatch(new_edge_map);
+  c->t_stage[3] += now_s() - ts0;
+
+  types::Vector6f Xv = TooN::Zeros; types::Matrix6f W_Xv = TooN::Zeros;
+  ts0 = now_s();
+  out->ok = c->core->extRotVel(new_edge_map, imu_state_.Vg, W_Xv, Xv) ? 1 : 0;
+  c->t_stage[4] += now_s() - ts0;
+  types::Vector6f Xgv = Xv; types::Matrix6f W_Xgv = W_Xv;
+
+  Float frame_dt = Float(new_edge_map->ts_us() - old_edge_map->ts_us()) / 1000000.0;
+
+  imu_state_.RGBias = TooN::Identity * icfg.gyro_bias_std_dev * icfg.gyro_bias_std_dev * frame_dt * frame_dt;
+  imu_state_.RGyro = TooN::Identity * icfg.gyro_std_dev * icfg.gyro_std_dev * frame_dt * frame_dt;
+  imu_state_.Bg += c->core->gyroBiasCorrection(Xgv, W_Xgv, imu_state_.W_Bg, imu_state_.RGyro, imu_state_.RGBias);
+  imu_state_.dVgv = Xgv.slice<0, 3>();
+  imu_state_.dWgv = Xgv.slice<3, 3>();
+
+  Rgva = R;
+  TooN::SO3<Float> R0(imu_state_.dWgv);
+  R.T() = R0.get_matrix() * R.T();
+  imu_state_.Vgv = R0 * imu_state_.Vg + imu_state_.dVgv;
+  V = imu_state_.Vgv;
+  types::Matrix6f R_Xgv = TooN::Cholesky<6, Float>(W_Xgv).get_inverse();
+  P_V = R_Xgv.slice<0, 0, 3, 3>();
+  P_W = R_Xgv.slice<3, 3, 3, 3>();
+
+  c->core->estimateLs4Acceleration(-imu_state_.Vgv / frame_dt, imu_state_.Av, R, frame_dt);
+  c->core->estimateMeanAcceleration(new_edge_map->imu().cacc(), imu_state_.As, R);
+
+  types::Vector6f Xgva = Xgv;
+  sab_state_.Rv = P_V / (frame_dt * frame_dt * frame_dt * frame_dt);
+  sab_state_.Qrot = P_W;
+  sab_state_.QKp = P_Kp;
+  types::Matrix3f R0used = R0.get_matrix();
+  ts0 = now_s();
+  if (c->num_frames > 4 + (unsigned)icfg.init_bias_frame_num) {
+    K = c->core->estimateBias(imu_state_.As, imu_state_.Av, 1.0, R, sab_state_.X, sab_state_.P, sab_state_.Qg,
+                              sab_state_.Qrot, sab_state_.Qbias, sab_state_.QKp, sab_state_.Rg, sab_state_.Rs,
+                              sab_state_.Rv, sab_state_.g_est, sab_state_.b_est, W_Xgv, Xgva, icfg.g_norm);
+    imu_state_.dVgva = Xgva.slice<0, 3>();
+    imu_state_.dWgva = Xgva.slice<3, 3>();
+    TooN::SO3<Float> R0gva(imu_state_.dWgva);
+    Rgva.T() = R0gva.get_matrix() * Rgva.T();
+    imu_state_.Vgva = R0gva * imu_state_.Vg + imu_state_.dVgva;
+    V = imu_state_.Vgva;
+    R0used = R0gva.get_matrix();
+    old_edge_map->rotateKeylines(R0gva.get_matrix());
+  } else {
+    imu_state_.dVgva = imu_state_.dVgv;
+    imu_state_.dWgva = imu_state_.dWgv;
+    Rgva = R;
+    imu_state_.Vgva = imu_state_.Vgv;
+    V = imu_state_.Vgva;
+    old_edge_map->rotateKeylines(R0.get_matrix());
+  }
+  c->t_stage[5] += now_s() - ts0;
+
+  for (int i = 0; i < 3; ++i) { out->Vg[i] = imu_state_.Vg[i]; out->V[i] = V[i]; }
+  for (int i = 0; i < 6; ++i) { out->Xv[i] = Xv[i]; out->Xgv[i] = Xgv[i]; out->Xgva[i] = Xgva[i]; }
+  from_m3(imu_state_.P_Vg, out->P_Vg); from_m3(P_V, out->P_V); from_m3(R, out->R); from_m3(Rgva, out->Rgva);
+  from_m3(R0used, out->R0);
+  for (int r = 0; r < 6; ++r) for (int k = 0; k < 6; ++k) out->W_Xv[r * 6 + k] = W_Xv(r, k);
+  out->frame_dt = frame_dt;
+
+  if (TooN::isnan(V) || TooN::isnan(W)) {
+    P_V = TooN::Identity * std::numeric_limits<Float>::max();
+    V = TooN::Zeros;
+    P_Kp = std::numeric_limits<Float>::max();
+    c->run = false;
+    out->stopped = 1;
+  } else {
+    ts0 = now_s();
+    klm_num = new_edge_map->directedMatch(old_edge_map, V, P_V, Rgva, num_kf_back_m, c->core_cfg->search_range);
+    c->t_stage[6] += now_s() - ts0;
+    if (klm_num < (int)c->core_cfg->global_min_matches_threshold) {
+      P_V = TooN::Identity * std::numeric_limits<Float>::max();
+      V = TooN::Zeros;
+      P_Kp = std::numeric_limits<Float>::max();
+      c->run = false;
+      out->stopped = 2;
+    } else {
+      ts0 = now_s();
+      out->reg_num = new_edge_map->regularize1Iter();
+      c->t_stage[7] += now_s() - ts0;
+      ts0 = now_s();
+      c->core->updateInverseDepth(V);
+      c->t_stage[8] += now_s() - ts0;
+    }
+  }
+  out->klm_num = klm_num;
+  out->kf_matches = num_kf_back_m;
+
+  if (c->num_frames > 4 + (unsigned)icfg.init_bias_frame_num) {
+    imu_state_.u_est = Rgva.T() * imu_state_.u_est;
+    imu_state_.u_est = imu_state_.u_est - (imu_state_.u_est * sab_state_.g_est) / (sab_state_.g_est * sab_state_.g_est) * sab_state_.g_est;
+    TooN::normalize(imu_state_.u_est);
+    types::Matrix3f R1 = TooN::SO3<Float>(sab_state_.g_est, TooN::makeVector(0.0f, 1.0f, 0.0f)).get_matrix();
+    types::Matrix3f R2 = TooN::SO3<Float>(R1 * imu_state_.u_est, TooN::makeVector(1.0f, 0.0f, 0.0f)).get_matrix();
+    R_global = R2 * R1;
+    Pos += -R_global * imu_state_.Vgva * K;
+  }
+  types::Vector3f ori = TooN::SO3<Float>(R_global).ln();
+  for (int i = 0; i < 3; ++i) { out->orientation[i] = ori[i]; out->position[i] = Pos[i]; }
+  out->K = K;
+  ++c->num_frames;
+  c->t_track += now_s() - t0;
+  return 1;
+}
+
+// seconds spent in detect / tracker since creation, and per tracker stage:
+// [0] distance field [1] rotate#1 [2] minimizeVel [3] forwardMatch [4] extRotVel [5] fusion+rotate#2
+// [6] directedMatch [7] regularize [8] Kalman
+void ref_timers(void* h, double* detect_s, double* track_s, double* stage9) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  *detect_s = c->t_detect; *track_s = c->t_track;
+  if (stage9) for (int i = 0; i < 9; ++i) stage9[i] = c->t_stage[i];
+}
+void ref_timers_reset(void* h) {
+  RefCtx* c = static_cast<RefCtx*>(h);
+  c->t_detect = c->t_track = 0;
+  for (double& t : c->t_stage) t = 0;
+}
+size_t ref_frame_out_size(void) { return sizeof(ref_frame_out); }
+
+}  // extern "C"

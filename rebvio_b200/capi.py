@@ -1,0 +1,137 @@
+"""ctypes binding of include/rebvio_b200.h. Loads rebvio_b200/librebvio_b200.so and fails loudly if it is missing
+(build with `python -c "import __graft_entry__ as g; g.build()"` or `make -C rebvio_b200/csrc`)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librebvio_b200.so")
+
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+
+
+class Camera(C.Structure):
+    _fields_ = [("fm", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("rows", C.c_int), ("cols", C.c_int)]
+
+
+class DetectorCfg(C.Structure):
+    _fields_ = [("keylines_ref", C.c_int), ("keylines_max", C.c_int), ("pos_neg_threshold", C.c_float),
+                ("dog_threshold", C.c_float), ("threshold", C.c_float), ("gain", C.c_float),
+                ("max_threshold", C.c_float), ("min_threshold", C.c_float)]
+
+
+class MapCfg(C.Structure):
+    _fields_ = [("pixel_uncertainty_match", C.c_float), ("match_threshold_norm", C.c_float),
+                ("match_threshold_angle", C.c_float), ("regularization_threshold", C.c_float)]
+
+
+class CoreCfg(C.Structure):
+    _fields_ = [("search_range", C.c_float), ("reweight_distance", C.c_float), ("match_treshold", C.c_float),
+                ("min_match_threshold", C.c_uint), ("iterations", C.c_uint),
+                ("global_min_matches_threshold", C.c_uint), ("pixel_uncertainty", C.c_float),
+                ("quantile_cutoff", C.c_float), ("quantile_num_bins", C.c_int), ("reshape_q_abs", C.c_float)]
+
+
+KEYLINE_DTYPE = np.dtype([
+    ("pos", np.float32, 2), ("pos_img", np.float32, 2), ("match_pos_img", np.float32, 2),
+    ("gradient", np.float32, 2), ("match_gradient", np.float32, 2), ("gradient_norm", np.float32),
+    ("match_gradient_norm", np.float32), ("rho", np.float32), ("sigma_rho", np.float32),
+    ("id", np.int32), ("id_prev", np.int32), ("id_next", np.int32), ("match_id", np.int32),
+    ("match_id_forward", np.int32), ("match_id_keyframe", np.int32), ("matches", np.uint32)])
+assert KEYLINE_DTYPE.itemsize == 84
+
+RBV_OK, RBV_ERR_ARG, RBV_ERR_CUDA, RBV_ERR_STATE = 0, 1, 2, 3
+REDUCE_FAST, REDUCE_ORDERED = 0, 1
+
+vp = C.c_void_p
+_SIG = {
+    "rbv_default_camera": (None, [C.POINTER(Camera)]),
+    "rbv_default_detector_cfg": (None, [C.POINTER(DetectorCfg)]),
+    "rbv_default_map_cfg": (None, [C.POINTER(MapCfg)]),
+    "rbv_default_core_cfg": (None, [C.POINTER(CoreCfg)]),
+    "rbv_create": (C.c_int, [C.POINTER(Camera), C.POINTER(DetectorCfg), C.POINTER(MapCfg), C.POINTER(CoreCfg), C.c_int,
+                            C.c_int, C.POINTER(vp)]),
+    "rbv_destroy": (None, [vp]),
+    "rbv_last_error": (C.c_char_p, []),
+    "rbv_sync": (C.c_int, [vp]),
+    "rbv_set_reduce_mode": (C.c_int, [vp, C.c_int]),
+    "rbv_lanes": (C.c_int, [vp]),
+    "rbv_set_stream": (C.c_int, [vp, vp]),
+    "rbv_launch_count": (C.c_ulonglong, [vp]),
+    "rbv_map_create": (C.c_int, [vp, C.POINTER(vp)]),
+    "rbv_map_release": (None, [vp, vp]),
+    "rbv_detect": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),
+    "rbv_detect_device": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+    "rbv_servo_threshold": (C.c_float, [C.POINTER(DetectorCfg), C.c_float, C.c_int]),
+    "rbv_build_distance_field": (C.c_int, [vp, vp]),
+    "rbv_rotate_keylines": (C.c_int, [vp, vp, vp]),
+    "rbv_estimate_quantile": (C.c_int, [vp, vp, C.c_float, C.c_int, vp]),
+    "rbv_reset_residuals": (C.c_int, [vp, vp]),
+    "rbv_try_vel": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+    "rbv_minimize_vel": (C.c_int, [vp, vp, vp, vp, vp]),
+    "rbv_forward_match": (C.c_int, [vp, vp, vp, vp]),
+    "rbv_ext_rot_vel": (C.c_int, [vp, vp, vp, vp, vp, vp]),
+    "rbv_directed_match": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_float, vp, vp]),
+    "rbv_regularize": (C.c_int, [vp, vp, vp]),
+    "rbv_update_inverse_depth": (C.c_int, [vp, vp]),
+    "rbv_track_g1": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "rbv_track_g2": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]),
+    "rbv_map_size": (C.c_int, [vp, vp, vp]),
+    "rbv_map_threshold": (C.c_int, [vp, vp, vp]),
+    "rbv_map_set_threshold": (C.c_int, [vp, vp, vp]),
+    "rbv_map_download": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_int, vp]),
+    "rbv_map_upload": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_int]),
+    "rbv_debug_read_image": (C.c_int, [vp, C.c_int, C.c_int, vp]),
+    "rbv_debug_read_mask": (C.c_int, [vp, vp, C.c_int, vp]),
+    "rbv_debug_read_field": (C.c_int, [vp, C.c_int, vp, vp]),
+    "rbv_debug_read_residuals": (C.c_int, [vp, vp, C.c_int, vp, C.c_int]),
+    "rbv_debug_box_pass": (C.c_int, [vp, C.c_int, C.c_int, vp, vp]),
+    "rbv_debug_read_setup": (C.c_int, [vp, vp, vp]),
+    "rbv_debug_read_lm_trace": (C.c_int, [vp, C.c_int, vp, C.c_int]),
+    "rbv_debug_read_probe_count": (C.c_int, [vp, C.c_int, vp]),
+}
+
+EXPORTS = sorted(_SIG)
+_lib = None
+
+
+def load():
+    """dlopen the CUDA library; raises if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build the CUDA extension first (__graft_entry__.build()); "
+                               "rebvio_b200 has no CPU fallback")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIG.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+class RbvError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != RBV_OK:
+        raise RbvError(f"rbv error {rc}: {load().rbv_last_error().decode(errors='replace')}")
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data_as(vp)
+
+
+def defaults():
+    L = load()
+    cam, det, mp, core = Camera(), DetectorCfg(), MapCfg(), CoreCfg()
+    L.rbv_default_camera(C.byref(cam)); L.rbv_default_detector_cfg(C.byref(det))
+    L.rbv_default_map_cfg(C.byref(mp)); L.rbv_default_core_cfg(C.byref(core))
+    return cam, det, mp, core

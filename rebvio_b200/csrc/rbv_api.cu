@@ -1,0 +1,767 @@
+// rbv_api.cu — C ABI of the B200-native REBVIO hot path (see include/rebvio_b200.h for the reference member function
+// each entry point replaces). Host-side setup mirrors FastGaussian::FastGaussian (scale_space.cpp:14-35) and the
+// plane-fit pseudo inverse (edge_detector.cpp:55-68). No CPU fallback: without a usable sm_100 device rbv_create fails.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "rbv_internal.cuh"
+
+static thread_local char g_err[512] = "";
+void rbv_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* rbv_last_error(void) { return g_err; }
+
+// ---- defaults (camera.hpp:26-37, edge_detector.hpp:19-32, edge_map.hpp:19-26, core.hpp:82-95) ----
+extern "C" void rbv_default_camera(rbv_camera* cam) {
+  const float fx = 458.654f, fy = 457.296f;
+  cam->fm = (float)(0.5 * (double)(fx + fy));
+  cam->cx = 367.215f;
+  cam->cy = 248.375f;
+  cam->rows = 480;
+  cam->cols = 752;
+}
+extern "C" void rbv_default_detector_cfg(rbv_detector_cfg* c) {
+  c->keylines_ref = 12000; c->keylines_max = 16000; c->pos_neg_threshold = 0.4f; c->dog_threshold = 0.095259868922420f;
+  c->threshold = 0.01f; c->gain = 5e-7f; c->max_threshold = 0.5f; c->min_threshold = 0.005f;
+}
+extern "C" void rbv_default_map_cfg(rbv_map_cfg* c) {
+  c->pixel_uncertainty_match = 2.0f; c->match_threshold_norm = 1.0f; c->match_threshold_angle = 45.0f; c->regularization_threshold = 0.5f;
+}
+extern "C" void rbv_default_core_cfg(rbv_core_cfg* c) {
+  c->search_range = 40.0f; c->reweight_distance = 2.0f; c->match_treshold = 0.5f; c->min_match_threshold = 0; c->iterations = 5;
+  c->global_min_matches_threshold = 500; c->pixel_uncertainty = 1.0f; c->quantile_cutoff = 0.9f; c->quantile_num_bins = 100;
+  c->reshape_q_abs = 1e-4f;
+}
+
+// edge_detector.cpp:33-36
+extern "C" float rbv_servo_threshold(const rbv_detector_cfg* cfg, float threshold, int last_keyline_count) {
+  if (cfg->gain > 0) {
+    threshold -= cfg->gain * (float)(cfg->keylines_ref - last_keyline_count);
+    threshold = (threshold > cfg->max_threshold) ? cfg->max_threshold : ((threshold < cfg->min_threshold) ? cfg->min_threshold : threshold);
+  }
+  return threshold;
+}
+
+// Kovesi box widths, scale_space.cpp:20-35
+static void kovesi_widths(float sigma, int n, int* widths, float* sigma_true) {
+  const float w_ideal = (float)sqrt(12.0 * sigma * sigma / (float)(n + 1));
+  int wl = (int)w_ideal;
+  if ((wl / 2) * 2 == wl) --wl;
+  const int m = (int)roundf(((float)(3 * n + 4 * n * wl + n * wl * wl) - 12 * sigma * sigma) / (float)(4 + 4 * wl));
+  for (int i = 0; i < n; ++i) widths[i] = (i < m) ? wl : wl + 2;
+  *sigma_true = (float)sqrt((m * wl * wl + (n - m) * (wl + 2.0) * (wl + 2.0) - n) / 12.0);
+}
+
+// 3x25 pseudo inverse of the 5x5 plane-fit design matrix, edge_detector.cpp:55-68
+static void plane_fit_pinv(float* pinv75) {
+  float phi[25][3], ptp[9], ipt[9];
+  int k = 0;
+  for (int r = -2; r <= 2; ++r)
+    for (int q = -2; q <= 2; ++q, ++k) { phi[k][0] = (float)q; phi[k][1] = (float)r; phi[k][2] = 1.0f; }
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b) {
+      float acc = 0.0f;
+      for (k = 0; k < 25; ++k) acc += phi[k][a] * phi[k][b];
+      ptp[a * 3 + b] = acc;
+    }
+  rbv_inv3(ptp, ipt);
+  for (int a = 0; a < 3; ++a)
+    for (k = 0; k < 25; ++k) {
+      float acc = 0.0f;
+      for (int b = 0; b < 3; ++b) acc += ipt[a * 3 + b] * phi[k][b];
+      pinv75[a * 25 + k] = acc;
+    }
+}
+
+#define STAGE_SLOTS 16
+struct Stage {  // ring of pinned staging slots for per-call lane inputs
+  float* host[STAGE_SLOTS];
+  cudaEvent_t ev[STAGE_SLOTS];
+  int next;
+};
+static Stage* stage_of(rbv_ctx* c) { return reinterpret_cast<Stage*>(c->h_in); }
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, n * sizeof(T)); }
+
+extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map_cfg* map, const rbv_core_cfg* core,
+                          int device, int lanes, rbv_ctx** out) {
+  if (!cam || !det || !map || !core || !out || lanes < 1 || lanes > 1024) { rbv_set_error("rbv_create: bad argument"); return RBV_ERR_ARG; }
+  if (cam->rows < 32 || cam->cols < 32 || cam->rows > 65535 || det->keylines_max < 1 || det->keylines_max >= (1 << 24)) {
+    rbv_set_error("rbv_create: image size / keylines_max out of range"); return RBV_ERR_ARG;
+  }
+  if (core->iterations > RBV_MAX_LM_ITERS || core->search_range < 1 || core->search_range > 127 || core->quantile_num_bins < 1 ||
+      core->quantile_num_bins > RBV_MAX_QBINS) { rbv_set_error("rbv_create: core config out of range"); return RBV_ERR_ARG; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { rbv_set_error("rbv_create: no CUDA device (there is no CPU fallback)"); return RBV_ERR_CUDA; }
+  if (device < 0 || device >= ndev) { rbv_set_error("rbv_create: device %d out of range (%d devices)", device, ndev); return RBV_ERR_ARG; }
+  cudaDeviceProp prop;
+  RBV_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) { rbv_set_error("rbv_create: device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor); return RBV_ERR_CUDA; }
+  RBV_CUDA(cudaSetDevice(device));
+  rbv_ctx* c = new rbv_ctx();
+  memset(c, 0, sizeof(*c));
+  c->cam = *cam; c->det = *det; c->mapc = *map; c->core = *core;
+  c->device = device;
+  c->reduce_mode = RBV_REDUCE_FAST;
+  float st[2];
+  kovesi_widths(3.56359f, 3, c->widths[0], &st[0]);                       // scale_space.cpp:186
+  kovesi_widths((float)(st[0] * 1.2599), 3, c->widths[1], &st[1]);
+  for (int s = 0; s < 2; ++s) for (int p = 0; p < 3; ++p) if (c->widths[s][p] > 15) { rbv_set_error("box width > 15"); delete c; return RBV_ERR_ARG; }
+  DevParams& P = c->P;
+  P.fm = cam->fm; P.cx = cam->cx; P.cy = cam->cy; P.rows = cam->rows; P.cols = cam->cols; P.npix = cam->rows * cam->cols;
+  P.keylines_max = det->keylines_max;
+  P.kmax = (det->keylines_max + 31) & ~31;
+  P.lanes = lanes;
+  P.pn_threshold = (float)((2.0 * 2 + 1.0) * (2.0 * 2 + 1.0)) * det->pos_neg_threshold;   // edge_detector.cpp:69
+  P.dog_threshold = det->dog_threshold;
+  P.pixel_uncertainty_match = map->pixel_uncertainty_match; P.match_threshold_norm = map->match_threshold_norm;
+  P.cang_min_edge = (float)cos(map->match_threshold_angle * M_PI / 180.0);                // edge_map.cpp:104
+  P.regularization_threshold = map->regularization_threshold;
+  P.search_range = core->search_range; P.reweight_distance = core->reweight_distance; P.match_treshold = core->match_treshold;
+  P.pixel_uncertainty = core->pixel_uncertainty; P.quantile_cutoff = core->quantile_cutoff; P.reshape_q_abs = core->reshape_q_abs;
+  P.quantile_num_bins = core->quantile_num_bins; P.iterations = (int)core->iterations;
+  P.field_r0 = (int)-core->search_range;                                                   // core.hpp:49: for(int r = -search_range_; r < search_range_; ++r)
+  P.field_nr = 0;
+  for (int r = P.field_r0; r < core->search_range; ++r) ++P.field_nr;
+  P.min_matches = 0;  // std::min(min_match_threshold, frame_count_) with frame_count_ never incremented (core.cpp:22,91)
+  plane_fit_pinv(P.pinv);
+  const size_t N = (size_t)P.npix, B = (size_t)lanes, K = (size_t)P.kmax;
+  RBV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->own_stream = true;
+  const int wpr = (P.cols + 31) / 32;
+  RBV_CUDA(dalloc(&c->img, B * N));
+  RBV_CUDA(dalloc(&c->rowsum, 2 * B * N));
+  RBV_CUDA(dalloc(&c->bufA, 2 * B * N));
+  RBV_CUDA(dalloc(&c->bufB, 2 * B * N));
+  RBV_CUDA(dalloc(&c->flags, B * P.rows * wpr));
+  RBV_CUDA(dalloc(&c->rowcount, B * P.rows));
+  RBV_CUDA(dalloc(&c->rowoffset, B * P.rows));
+  RBV_CUDA(dalloc(&c->thr_dev, B));
+  RBV_CUDA(dalloc(&c->field, B * N));
+  RBV_CUDA(dalloc(&c->prod, 10 * B * K));
+  RBV_CUDA(dalloc(&c->fiabs, B * K));
+  RBV_CUDA(dalloc(&c->fwd_head, B * K));
+  RBV_CUDA(dalloc(&c->fwd_next, B * K));
+  RBV_CUDA(dalloc(&c->reg_r, B * K));
+  RBV_CUDA(dalloc(&c->reg_s, B * K));
+  RBV_CUDA(dalloc(&c->lm, B));
+  RBV_CUDA(dalloc(&c->lane_in, B * IN_STRIDE));
+  RBV_CUDA(dalloc(&c->lane_out, B * OUT_STRIDE));
+  RBV_CUDA(dalloc(&c->lane_cnt, B * CNT_STRIDE));
+  RBV_CUDA(dalloc(&c->probes, B));
+  RBV_CUDA(cudaMemset(c->lm, 0, sizeof(LMState) * B));
+  RBV_CUDA(cudaMemset(c->lane_in, 0, sizeof(float) * B * IN_STRIDE));
+  RBV_CUDA(cudaMemset(c->lane_out, 0, sizeof(float) * B * OUT_STRIDE));
+  RBV_CUDA(cudaMemset(c->lane_cnt, 0, sizeof(int) * B * CNT_STRIDE));
+  RBV_CUDA(cudaMemset(c->probes, 0, sizeof(unsigned long long) * B));
+  RBV_CUDA(cudaMemset(c->field, 0xFF, sizeof(unsigned) * B * N));
+  Stage* stg = new Stage();
+  for (int i = 0; i < STAGE_SLOTS; ++i) {
+    RBV_CUDA(cudaMallocHost((void**)&stg->host[i], sizeof(float) * B * IN_STRIDE));
+    RBV_CUDA(cudaEventCreateWithFlags(&stg->ev[i], cudaEventDisableTiming));
+  }
+  stg->next = 0;
+  c->h_in = reinterpret_cast<float*>(stg);
+  RBV_CUDA(cudaMallocHost((void**)&c->h_out, sizeof(float) * B * OUT_STRIDE));
+  RBV_CUDA(cudaMallocHost((void**)&c->h_cnt, sizeof(int) * B * (CNT_STRIDE + 2)));
+  RBV_CUDA(cudaMallocHost((void**)&c->h_lm, sizeof(LMState) * B));
+  RBV_CUDA(cudaMallocHost((void**)&c->h_img, sizeof(float) * B * N));
+  *out = c;
+  return RBV_OK;
+}
+
+extern "C" void rbv_destroy(rbv_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  void* dev[] = {c->img, c->rowsum, c->bufA, c->bufB, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->field, c->prod, c->fiabs,
+                 c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes};
+  for (void* p : dev) cudaFree(p);
+  Stage* stg = stage_of(c);
+  if (stg) {
+    for (int i = 0; i < STAGE_SLOTS; ++i) { cudaFreeHost(stg->host[i]); cudaEventDestroy(stg->ev[i]); }
+    delete stg;
+  }
+  cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm); cudaFreeHost(c->h_img);
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+extern "C" int rbv_sync(rbv_ctx* c) {
+  if (!c) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  return RBV_OK;
+}
+extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
+  if (!c || (mode != RBV_REDUCE_FAST && mode != RBV_REDUCE_ORDERED)) return RBV_ERR_ARG;
+  c->reduce_mode = mode;
+  return RBV_OK;
+}
+extern "C" int rbv_lanes(const rbv_ctx* c) { return c ? c->P.lanes : 0; }
+extern "C" int rbv_set_stream(rbv_ctx* c, void* cuda_stream) {
+  if (!c) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+  c->stream = (cudaStream_t)cuda_stream;
+  return RBV_OK;
+}
+extern "C" unsigned long long rbv_launch_count(const rbv_ctx* c) { return c ? c->launches : 0ull; }
+
+// ---- maps ----
+extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
+  if (!c || !out) return RBV_ERR_ARG;
+  RBV_CUDA(cudaSetDevice(c->device));
+  const size_t B = c->P.lanes, K = c->P.kmax, N = c->P.npix;
+  rbv_map* m = new rbv_map();
+  memset(m, 0, sizeof(*m));
+  // 5 float2 + 4 float + 5 int + 2 unsigned + 1 float (residual) per keyline, + mask + count + threshold
+  const size_t per_kl = 5 * 8 + 4 * 4 + 5 * 4 + 2 * 4 + 4;
+  m->slab_bytes = B * K * per_kl + B * N * 4 + B * 8 + 32 * 256;   // + slack for the 256-byte alignment of each array
+  RBV_CUDA(cudaMalloc(&m->slab, m->slab_bytes));
+  char* p = (char*)m->slab;
+  auto take = [&](size_t bytes) { char* r = p; p += (bytes + 255) & ~(size_t)255; return r; };
+  m->k.pos = (float2*)take(B * K * 8); m->k.pos_img = (float2*)take(B * K * 8); m->k.match_pos_img = (float2*)take(B * K * 8);
+  m->k.grad = (float2*)take(B * K * 8); m->k.match_grad = (float2*)take(B * K * 8);
+  m->k.gnorm = (float*)take(B * K * 4); m->k.match_gnorm = (float*)take(B * K * 4); m->k.rho = (float*)take(B * K * 4);
+  m->k.srho = (float*)take(B * K * 4);
+  m->k.id_prev = (int*)take(B * K * 4); m->k.id_next = (int*)take(B * K * 4); m->k.match_id = (int*)take(B * K * 4);
+  m->k.match_fwd = (int*)take(B * K * 4); m->k.match_kf = (int*)take(B * K * 4);
+  m->k.matches = (unsigned*)take(B * K * 4); m->k.pixel = (unsigned*)take(B * K * 4); m->k.residual = (float*)take(B * K * 4);
+  m->mask = (int*)take(B * N * 4);
+  m->count = (int*)take(B * 4);
+  m->threshold = (float*)take(B * 4);
+  RBV_CUDA(cudaMemsetAsync(m->slab, 0, m->slab_bytes, c->stream));
+  RBV_CUDA(cudaMemsetAsync(m->mask, 0xFF, B * N * 4, c->stream));
+  std::vector<float> thr(B, -1.0f);                                       // edge_map.cpp:17
+  RBV_CUDA(cudaMemcpyAsync(m->threshold, thr.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  m->ts_us = (uint64_t*)calloc(B, sizeof(uint64_t));
+  *out = m;
+  return RBV_OK;
+}
+
+extern "C" void rbv_map_release(rbv_ctx* c, rbv_map* m) {
+  if (!m) return;
+  if (c) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); if (c->field_map == m) c->field_map = nullptr; }
+  cudaFree(m->slab);
+  free(m->ts_us);
+  delete m;
+}
+
+// ---- per-call lane inputs: fill a pinned slot, async copy to lane_in ----
+static float* stage_begin(rbv_ctx* c, int* slot) {
+  Stage* s = stage_of(c);
+  *slot = s->next;
+  s->next = (s->next + 1) % STAGE_SLOTS;
+  cudaEventSynchronize(s->ev[*slot]);
+  memset(s->host[*slot], 0, sizeof(float) * (size_t)c->P.lanes * IN_STRIDE);
+  return s->host[*slot];
+}
+static int stage_commit(rbv_ctx* c, int slot) {
+  Stage* s = stage_of(c);
+  RBV_CUDA(cudaMemcpyAsync(c->lane_in, s->host[slot], sizeof(float) * (size_t)c->P.lanes * IN_STRIDE, cudaMemcpyHostToDevice, c->stream));
+  RBV_CUDA(cudaEventRecord(s->ev[slot], c->stream));
+  return RBV_OK;
+}
+static void put(float* h, int lane, int slot, const float* src, int n) {
+  if (src) memcpy(h + (size_t)lane * IN_STRIDE + slot, src + (size_t)lane * n, sizeof(float) * n);
+}
+static int fetch_out(rbv_ctx* c) {
+  RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * (size_t)c->P.lanes * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  return RBV_OK;
+}
+static int fetch_cnt(rbv_ctx* c) {
+  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, c->lane_cnt, sizeof(int) * (size_t)c->P.lanes * CNT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  return RBV_OK;
+}
+#define CHECK_CTX(c) do { if (!(c)) { rbv_set_error("null context"); return RBV_ERR_ARG; } RBV_CUDA(cudaSetDevice((c)->device)); } while (0)
+#define TRY(x) do { int rc_ = (x); if (rc_ != RBV_OK) return rc_; } while (0)
+
+// ---- front end ----
+extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images, const uint64_t* ts_us, const float* threshold,
+                                 int* n_keylines, float* auto_threshold) {
+  CHECK_CTX(c);
+  if (!map || !d_images || !threshold) { rbv_set_error("rbv_detect: null argument"); return RBV_ERR_ARG; }
+  const int B = c->P.lanes;
+  int slot;
+  float* h = stage_begin(c, &slot);   // reuse a staging slot for the B thresholds
+  memcpy(h, threshold, sizeof(float) * B);
+  Stage* s = stage_of(c);
+  RBV_CUDA(cudaMemcpyAsync(c->thr_dev, h, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
+  RBV_CUDA(cudaEventRecord(s->ev[slot], c->stream));
+  if (ts_us) memcpy(map->ts_us, ts_us, sizeof(uint64_t) * B);
+  TRY(fe_scale_space(c, d_images));
+  TRY(fe_detect(c, map));
+  if (n_keylines || auto_threshold) {
+    int* hc = c->h_cnt;
+    float* ht = reinterpret_cast<float*>(c->h_cnt + B);
+    RBV_CUDA(cudaMemcpyAsync(hc, map->count, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaMemcpyAsync(ht, map->threshold, sizeof(float) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaStreamSynchronize(c->stream));
+    if (n_keylines) memcpy(n_keylines, hc, sizeof(int) * B);
+    if (auto_threshold) memcpy(auto_threshold, ht, sizeof(float) * B);
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_detect(rbv_ctx* c, rbv_map* map, const float* const* images, size_t pitch_bytes, const uint64_t* ts_us,
+                          const float* threshold, int* n_keylines, float* auto_threshold) {
+  CHECK_CTX(c);
+  if (!images) { rbv_set_error("rbv_detect: null images"); return RBV_ERR_ARG; }
+  const size_t N = c->P.npix, row_bytes = sizeof(float) * c->P.cols;
+  if (pitch_bytes == 0) pitch_bytes = row_bytes;
+  if (pitch_bytes < row_bytes) { rbv_set_error("rbv_detect: pitch smaller than a row"); return RBV_ERR_ARG; }
+  for (int b = 0; b < c->P.lanes; ++b) {
+    if (!images[b]) { rbv_set_error("rbv_detect: null image for lane %d", b); return RBV_ERR_ARG; }
+    RBV_CUDA(cudaMemcpy2DAsync(c->img + (size_t)b * N, row_bytes, images[b], pitch_bytes, row_bytes, c->P.rows, cudaMemcpyHostToDevice, c->stream));
+  }
+  return rbv_detect_device(c, map, c->img, ts_us, threshold, n_keylines, auto_threshold);
+}
+
+// ---- tracker stages ----
+extern "C" int rbv_build_distance_field(rbv_ctx* c, rbv_map* map) {
+  CHECK_CTX(c);
+  if (!map) return RBV_ERR_ARG;
+  return tr_build_field(c, map);
+}
+
+extern "C" int rbv_rotate_keylines(rbv_ctx* c, rbv_map* map, const float* R9) {
+  CHECK_CTX(c);
+  if (!map || !R9) return RBV_ERR_ARG;
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R9, 9);
+  TRY(stage_commit(c, slot));
+  return tr_rotate(c, map);
+}
+
+extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile, int num_bins, float* out) {
+  CHECK_CTX(c);
+  if (!map) return RBV_ERR_ARG;
+  TRY(tr_quantile(c, map, percentile, num_bins, 0));
+  if (out) {
+    TRY(fetch_out(c));
+    for (int b = 0; b < c->P.lanes; ++b) out[b] = c->h_out[(size_t)b * OUT_STRIDE + OUT_Q];
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_reset_residuals(rbv_ctx* c, rbv_map* map) {
+  CHECK_CTX(c);
+  if (!map) return RBV_ERR_ARG;
+  RBV_CUDA(cudaMemsetAsync(map->k.residual, 0, sizeof(float) * (size_t)c->P.lanes * c->P.kmax, c->stream));   // core.cpp:158
+  return RBV_OK;
+}
+
+extern "C" int rbv_try_vel(rbv_ctx* c, rbv_map* map, const float* vel3, const float* sigma_rho_min, float* JtJ9, float* JtF3, float* score) {
+  CHECK_CTX(c);
+  if (!map || !vel3 || !sigma_rho_min) return RBV_ERR_ARG;
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) { put(h, b, IN_VEL, vel3, 3); put(h, b, IN_SRMIN, sigma_rho_min, 1); }
+  TRY(stage_commit(c, slot));
+  TRY(tr_try_vel(c, map, -1));
+  if (JtJ9 || JtF3 || score) {
+    TRY(fetch_out(c));
+    for (int b = 0; b < c->P.lanes; ++b) {
+      const float* o = c->h_out + (size_t)b * OUT_STRIDE;
+      if (JtJ9) memcpy(JtJ9 + b * 9, o + OUT_JTJ, 36);
+      if (JtF3) memcpy(JtF3 + b * 3, o + OUT_JTF, 12);
+      if (score) score[b] = o[OUT_SCORE];
+    }
+  }
+  return RBV_OK;
+}
+
+__global__ void k_lm_init(LMState* lm, const float* lane_in, int lanes) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= lanes) return;
+  for (int i = 0; i < 3; ++i) lm[b].vel[i] = lane_in[(size_t)b * IN_STRIDE + IN_VEL + i];
+}
+
+// enqueue Core::minimizeVel (core.cpp:150-189) on the stream: quantile, residual reset, (1 + iterations) tryVel + LM steps
+static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map) {
+  TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, 1));
+  RBV_CUDA(cudaMemsetAsync(old_map->k.residual, 0, sizeof(float) * (size_t)c->P.lanes * c->P.kmax, c->stream));
+  k_lm_init<<<(c->P.lanes + 63) / 64, 64, 0, c->stream>>>(c->lm, c->lane_in, c->P.lanes);
+  ++c->launches;
+  for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
+  return RBV_OK;
+}
+static int fetch_lm(rbv_ctx* c, float* vel3, float* Rvel9, float* score) {
+  RBV_CUDA(cudaMemcpyAsync(c->h_lm, c->lm, sizeof(LMState) * (size_t)c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  const LMState* L = reinterpret_cast<const LMState*>(c->h_lm);
+  for (int b = 0; b < c->P.lanes; ++b) {
+    if (vel3) memcpy(vel3 + b * 3, L[b].vel, 12);
+    if (Rvel9) memcpy(Rvel9 + b * 9, L[b].Rvel, 36);
+    if (score) score[b] = L[b].F;
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_minimize_vel(rbv_ctx* c, rbv_map* old_map, float* vel3, float* Rvel9, float* score) {
+  CHECK_CTX(c);
+  if (!old_map || !vel3) return RBV_ERR_ARG;
+  if (!c->field_map) { rbv_set_error("minimizeVel before buildDistanceField"); return RBV_ERR_STATE; }
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_VEL, vel3, 3);
+  TRY(stage_commit(c, slot));
+  TRY(enqueue_minimize(c, old_map));
+  return fetch_lm(c, vel3, Rvel9, score);
+}
+
+extern "C" int rbv_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, int* n_matches) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map) return RBV_ERR_ARG;
+  TRY(tr_forward_match(c, old_map, new_map));
+  if (n_matches) {
+    TRY(fetch_cnt(c));
+    for (int b = 0; b < c->P.lanes; ++b) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_FWD];
+  }
+  return RBV_OK;
+}
+
+static void copy_extrot_out(rbv_ctx* c, float* Wx36, float* X6, int* ok) {
+  for (int b = 0; b < c->P.lanes; ++b) {
+    const float* o = c->h_out + (size_t)b * OUT_STRIDE;
+    if (Wx36) memcpy(Wx36 + b * 36, o + OUT_WX, 144);
+    if (X6) memcpy(X6 + b * 6, o + OUT_X, 24);
+    if (ok) ok[b] = o[OUT_OK] != 0.0f;
+  }
+}
+
+extern "C" int rbv_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, const float* vel3, float* Wx36, float* X6, int* ok) {
+  CHECK_CTX(c);
+  if (!new_map || !vel3) return RBV_ERR_ARG;
+  if (c->field_map != new_map) { rbv_set_error("extRotVel: map is not the distance-field map (core.cpp:195)"); return RBV_ERR_STATE; }
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_VEL, vel3, 3);
+  TRY(stage_commit(c, slot));
+  TRY(tr_ext_rot_vel(c, new_map, 0));
+  TRY(fetch_out(c));
+  copy_extrot_out(c, Wx36, X6, ok);
+  return RBV_OK;
+}
+
+static void put_directed(rbv_ctx* c, float* h, const float* vel3, const float* Rvel9, const float* Rback9, float max_radius) {
+  for (int b = 0; b < c->P.lanes; ++b) {
+    put(h, b, IN_VEL, vel3, 3); put(h, b, IN_RVEL, Rvel9, 9); put(h, b, IN_RBACK, Rback9, 9);
+    h[(size_t)b * IN_STRIDE + IN_MAXRADIUS] = max_radius;
+  }
+}
+
+extern "C" int rbv_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map, const float* vel3, const float* Rvel9,
+                                  const float* Rback9, float max_radius, int* kf_matches, int* n_matches) {
+  CHECK_CTX(c);
+  if (!new_map || !old_map || !vel3 || !Rvel9 || !Rback9) return RBV_ERR_ARG;
+  int slot;
+  float* h = stage_begin(c, &slot);
+  put_directed(c, h, vel3, Rvel9, Rback9, max_radius);
+  TRY(stage_commit(c, slot));
+  TRY(tr_directed_match(c, new_map, old_map));
+  if (kf_matches || n_matches) {
+    TRY(fetch_cnt(c));
+    for (int b = 0; b < c->P.lanes; ++b) {
+      if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
+      if (kf_matches) kf_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_KF];
+    }
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_regularize(rbv_ctx* c, rbv_map* map, int* n_regularized) {
+  CHECK_CTX(c);
+  if (!map) return RBV_ERR_ARG;
+  TRY(tr_regularize(c, map));
+  if (n_regularized) {
+    TRY(fetch_cnt(c));
+    for (int b = 0; b < c->P.lanes; ++b) n_regularized[b] = c->h_cnt[b * CNT_STRIDE + CNT_REG];
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_update_inverse_depth(rbv_ctx* c, const float* vel3) {
+  CHECK_CTX(c);
+  if (!vel3) return RBV_ERR_ARG;
+  if (!c->field_map) { rbv_set_error("updateInverseDepth before buildDistanceField"); return RBV_ERR_STATE; }
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_VEL, vel3, 3);
+  TRY(stage_commit(c, slot));
+  return tr_kalman(c, c->field_map);
+}
+
+// ---- fused per-frame sequences (rebvio.cpp:142-177 and :223-259) ----
+extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R9, float* vel3, float* Rvel9, float* Wx36,
+                            float* X6, int* ok) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map || !R9) return RBV_ERR_ARG;
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R9, 9);   // IN_VEL stays 0: imu_state_.Vg = Zeros (rebvio.cpp:168)
+  TRY(stage_commit(c, slot));
+  TRY(tr_build_field(c, new_map));
+  TRY(tr_rotate(c, old_map));
+  TRY(enqueue_minimize(c, old_map));
+  TRY(tr_forward_match(c, old_map, new_map));
+  TRY(tr_ext_rot_vel(c, new_map, 1));
+  RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * (size_t)c->P.lanes * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  TRY(fetch_lm(c, vel3, Rvel9, nullptr));
+  copy_extrot_out(c, Wx36, X6, ok);
+  return RBV_OK;
+}
+
+__global__ void k_gate_min_matches(int* count_backup, int* count, const int* lane_cnt, int min_matches, int lanes, int restore) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= lanes) return;
+  if (!restore) {
+    count_backup[b] = count[b];
+    if (lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) count[b] = 0;   // lanes below the floor skip regularise + Kalman
+  } else {
+    count[b] = count_backup[b];
+  }
+}
+
+extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R0_9, const float* V3, const float* PV9,
+                            const float* Rgva9, float max_radius, int min_matches, int* n_matches, int* kf_matches) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map || !R0_9 || !V3 || !PV9 || !Rgva9) return RBV_ERR_ARG;
+  if (c->field_map != new_map) { rbv_set_error("track_g2: new_map is not the distance-field map"); return RBV_ERR_STATE; }
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R0_9, 9);
+  put_directed(c, h, V3, PV9, Rgva9, max_radius);
+  TRY(stage_commit(c, slot));
+  TRY(tr_rotate(c, old_map));
+  TRY(tr_directed_match(c, new_map, old_map));
+  int* backup = c->rowcount;  // scratch ints, free between detects
+  const int nb = (c->P.lanes + 63) / 64;
+  k_gate_min_matches<<<nb, 64, 0, c->stream>>>(backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 0);
+  TRY(tr_regularize(c, new_map));
+  TRY(tr_kalman(c, new_map));
+  k_gate_min_matches<<<nb, 64, 0, c->stream>>>(backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 1);
+  c->launches += 2;
+  TRY(fetch_cnt(c));
+  for (int b = 0; b < c->P.lanes; ++b) {
+    if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
+    if (kf_matches) kf_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_KF];
+  }
+  return RBV_OK;
+}
+
+// ---- host mirror (EdgeMap::keylines(), mask(), size(), threshold(); edge_map.hpp:40-75) ----
+extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
+  CHECK_CTX(c);
+  if (!m || !n) return RBV_ERR_ARG;
+  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->count, sizeof(int) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  memcpy(n, c->h_cnt, sizeof(int) * c->P.lanes);
+  return RBV_OK;
+}
+extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
+  CHECK_CTX(c);
+  if (!m || !t) return RBV_ERR_ARG;
+  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->threshold, sizeof(float) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  memcpy(t, c->h_cnt, sizeof(float) * c->P.lanes);
+  return RBV_OK;
+}
+extern "C" int rbv_map_set_threshold(rbv_ctx* c, rbv_map* m, const float* t) {
+  CHECK_CTX(c);
+  if (!m || !t) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(m->threshold, t, sizeof(float) * c->P.lanes, cudaMemcpyHostToDevice));
+  return RBV_OK;
+}
+
+template <typename T>
+static cudaError_t pull(std::vector<T>& h, const T* d, size_t lane, size_t K, int n) {
+  h.resize(n > 0 ? n : 1);
+  return cudaMemcpy(h.data(), d + lane * K, sizeof(T) * (size_t)n, cudaMemcpyDeviceToHost);
+}
+template <typename T>
+static cudaError_t push(const std::vector<T>& h, T* d, size_t lane, size_t K, int n) {
+  return cudaMemcpy(d + lane * K, h.data(), sizeof(T) * (size_t)n, cudaMemcpyHostToDevice);
+}
+
+extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* kl, uint32_t* pixel_idx, int cap, int* n_out) {
+  CHECK_CTX(c);
+  if (!m || lane < 0 || lane >= c->P.lanes || !n_out) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  int n = 0;
+  RBV_CUDA(cudaMemcpy(&n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
+  *n_out = n;
+  if (n > cap) { rbv_set_error("rbv_map_download: capacity %d < %d keylines", cap, n); return RBV_ERR_ARG; }
+  if (n == 0) return RBV_OK;
+  const size_t K = c->P.kmax, L = lane;
+  std::vector<float2> pos, pi, mpi, g, mg;
+  std::vector<float> gn, mgn, rho, sr;
+  std::vector<int> ip, in, mi, mf, mk;
+  std::vector<unsigned> mt, px;
+  RBV_CUDA(pull(pos, m->k.pos, L, K, n)); RBV_CUDA(pull(pi, m->k.pos_img, L, K, n)); RBV_CUDA(pull(mpi, m->k.match_pos_img, L, K, n));
+  RBV_CUDA(pull(g, m->k.grad, L, K, n)); RBV_CUDA(pull(mg, m->k.match_grad, L, K, n));
+  RBV_CUDA(pull(gn, m->k.gnorm, L, K, n)); RBV_CUDA(pull(mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(pull(rho, m->k.rho, L, K, n));
+  RBV_CUDA(pull(sr, m->k.srho, L, K, n));
+  RBV_CUDA(pull(ip, m->k.id_prev, L, K, n)); RBV_CUDA(pull(in, m->k.id_next, L, K, n)); RBV_CUDA(pull(mi, m->k.match_id, L, K, n));
+  RBV_CUDA(pull(mf, m->k.match_fwd, L, K, n)); RBV_CUDA(pull(mk, m->k.match_kf, L, K, n));
+  RBV_CUDA(pull(mt, m->k.matches, L, K, n)); RBV_CUDA(pull(px, m->k.pixel, L, K, n));
+  for (int i = 0; i < n; ++i) {
+    if (kl) {
+      rbv_keyline& k = kl[i];
+      k.pos[0] = pos[i].x; k.pos[1] = pos[i].y; k.pos_img[0] = pi[i].x; k.pos_img[1] = pi[i].y;
+      k.match_pos_img[0] = mpi[i].x; k.match_pos_img[1] = mpi[i].y; k.gradient[0] = g[i].x; k.gradient[1] = g[i].y;
+      k.match_gradient[0] = mg[i].x; k.match_gradient[1] = mg[i].y; k.gradient_norm = gn[i]; k.match_gradient_norm = mgn[i];
+      k.rho = rho[i]; k.sigma_rho = sr[i];
+      k.id = -1;  // KeyLine::id is never assigned by the reference (keyline.hpp:52)
+      k.id_prev = ip[i]; k.id_next = in[i]; k.match_id = mi[i]; k.match_id_forward = mf[i]; k.match_id_keyframe = mk[i];
+      k.matches = mt[i];
+    }
+    if (pixel_idx) pixel_idx[i] = px[i];
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keyline* kl, const uint32_t* pixel_idx, int n) {
+  CHECK_CTX(c);
+  if (!m || lane < 0 || lane >= c->P.lanes || n < 0 || n > c->P.keylines_max || (n && !kl)) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  const size_t K = c->P.kmax, L = lane, N = c->P.npix;
+  std::vector<float2> pos(n), pi(n), mpi(n), g(n), mg(n);
+  std::vector<float> gn(n), mgn(n), rho(n), sr(n);
+  std::vector<int> ip(n), in(n), mi(n), mf(n), mk(n);
+  std::vector<unsigned> mt(n);
+  for (int i = 0; i < n; ++i) {
+    const rbv_keyline& k = kl[i];
+    pos[i] = make_float2(k.pos[0], k.pos[1]); pi[i] = make_float2(k.pos_img[0], k.pos_img[1]);
+    mpi[i] = make_float2(k.match_pos_img[0], k.match_pos_img[1]); g[i] = make_float2(k.gradient[0], k.gradient[1]);
+    mg[i] = make_float2(k.match_gradient[0], k.match_gradient[1]); gn[i] = k.gradient_norm; mgn[i] = k.match_gradient_norm;
+    rho[i] = k.rho; sr[i] = k.sigma_rho; ip[i] = k.id_prev; in[i] = k.id_next; mi[i] = k.match_id; mf[i] = k.match_id_forward;
+    mk[i] = k.match_id_keyframe; mt[i] = k.matches;
+  }
+  if (n) {
+    RBV_CUDA(push(pos, m->k.pos, L, K, n)); RBV_CUDA(push(pi, m->k.pos_img, L, K, n)); RBV_CUDA(push(mpi, m->k.match_pos_img, L, K, n));
+    RBV_CUDA(push(g, m->k.grad, L, K, n)); RBV_CUDA(push(mg, m->k.match_grad, L, K, n));
+    RBV_CUDA(push(gn, m->k.gnorm, L, K, n)); RBV_CUDA(push(mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(push(rho, m->k.rho, L, K, n));
+    RBV_CUDA(push(sr, m->k.srho, L, K, n));
+    RBV_CUDA(push(ip, m->k.id_prev, L, K, n)); RBV_CUDA(push(in, m->k.id_next, L, K, n)); RBV_CUDA(push(mi, m->k.match_id, L, K, n));
+    RBV_CUDA(push(mf, m->k.match_fwd, L, K, n)); RBV_CUDA(push(mk, m->k.match_kf, L, K, n)); RBV_CUDA(push(mt, m->k.matches, L, K, n));
+  }
+  RBV_CUDA(cudaMemcpy(m->count + lane, &n, sizeof(int), cudaMemcpyHostToDevice));
+  if (pixel_idx) {
+    std::vector<int> mask(N, -1);
+    std::vector<unsigned> px(n > 0 ? n : 1);
+    for (int i = 0; i < n; ++i) {
+      if (pixel_idx[i] >= N) { rbv_set_error("rbv_map_upload: pixel index out of range"); return RBV_ERR_ARG; }
+      px[i] = pixel_idx[i];
+      if (mask[pixel_idx[i]] < 0) mask[pixel_idx[i]] = i;   // unordered_map::emplace keeps the first
+    }
+    RBV_CUDA(cudaMemcpy(m->mask + L * N, mask.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
+    if (n) RBV_CUDA(push(px, m->k.pixel, L, K, n));
+  }
+  return RBV_OK;
+}
+
+// ---- debug taps ----
+extern "C" int rbv_debug_read_image(rbv_ctx* c, int lane, int which, float* out) {
+  CHECK_CTX(c);
+  if (lane < 0 || lane >= c->P.lanes || which < 0 || which > 3 || !out) return RBV_ERR_ARG;
+  const size_t N = c->P.npix;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  if (which < 2) {
+    RBV_CUDA(cudaMemcpy(out, c->bufA + ((size_t)lane * 2 + which) * N, sizeof(float) * N, cudaMemcpyDeviceToHost));
+    return RBV_OK;
+  }
+  float* tmp = c->rowsum;  // scratch
+  TRY(fe_dog_mag_debug(c, lane, which, tmp));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(out, tmp, sizeof(float) * N, cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_mask(rbv_ctx* c, rbv_map* m, int lane, int* out) {
+  CHECK_CTX(c);
+  if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(out, m->mask + (size_t)lane * c->P.npix, sizeof(int) * (size_t)c->P.npix, cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_field(rbv_ctx* c, int lane, int* id, int* distance) {
+  CHECK_CTX(c);
+  if (lane < 0 || lane >= c->P.lanes) return RBV_ERR_ARG;
+  const size_t N = c->P.npix;
+  std::vector<unsigned> f(N);
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(f.data(), c->field + (size_t)lane * N, sizeof(unsigned) * N, cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < N; ++i) {
+    const bool empty = f[i] == RBV_FIELD_EMPTY;
+    if (id) id[i] = empty ? -1 : (int)(0xFFFFFFu - (f[i] & 0xFFFFFFu));
+    if (distance) distance[i] = empty ? -1 : (int)(f[i] >> 24);
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_residuals(rbv_ctx* c, rbv_map* m, int lane, float* out, int cap) {
+  CHECK_CTX(c);
+  if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  int n = 0;
+  RBV_CUDA(cudaMemcpy(&n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
+  if (n > cap) n = cap;
+  if (n) RBV_CUDA(cudaMemcpy(out, m->k.residual + (size_t)lane * c->P.kmax, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_box_pass(rbv_ctx* c, int scale, int pass, const float* in, float* out) {
+  CHECK_CTX(c);
+  if (scale < 0 || scale > 1 || pass < 0 || pass > 2 || !in || !out) return RBV_ERR_ARG;
+  const size_t N = c->P.npix;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(c->img, in, sizeof(float) * N, cudaMemcpyHostToDevice));
+  TRY(fe_box_pass_debug(c, scale, pass, c->img, c->bufB));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(out, c->bufB, sizeof(float) * N, cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_setup(rbv_ctx* c, float* pinv75, int* widths6) {
+  if (!c) return RBV_ERR_ARG;
+  if (pinv75) memcpy(pinv75, c->P.pinv, sizeof(float) * 75);
+  if (widths6) for (int s = 0; s < 2; ++s) for (int p = 0; p < 3; ++p) widths6[s * 3 + p] = c->widths[s][p];
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_lm_trace(rbv_ctx* c, int lane, float* out, int cap_floats) {
+  CHECK_CTX(c);
+  if (lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  LMState L;
+  RBV_CUDA(cudaMemcpy(&L, c->lm + lane, sizeof(LMState), cudaMemcpyDeviceToHost));
+  int n = (c->P.iterations + 1) * 16;
+  if (n > cap_floats) n = cap_floats;
+  memcpy(out, L.trace, sizeof(float) * n);
+  return RBV_OK;
+}
+
+extern "C" int rbv_debug_read_probe_count(rbv_ctx* c, int lane, unsigned long long* probes) {
+  CHECK_CTX(c);
+  if (lane < 0 || lane >= c->P.lanes || !probes) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  RBV_CUDA(cudaMemcpy(probes, c->probes + lane, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}

@@ -1,0 +1,455 @@
+// rbv_frontend.cu — edge front end on sm_100a: box-cascade scale space, DoG / gradient tests, sub-pixel plane fit,
+// ordered keyline compaction, neighbour linking, auto threshold.
+//
+// Replaces (reference paths relative to the reference root):
+//   FastGaussian::createIntegralImage + average   rebvio/src/scale_space.cpp:48-128   -> k_rowscan + k_colbox
+//   ScaleSpace::calculateDoG / GradientMagnitude   rebvio/src/scale_space.cpp:210-233  -> fused into k_detect_flags
+//   EdgeDetector::buildEdgeMap                      rebvio/src/edge_detector.cpp:45-123 -> k_detect_flags/k_detect_scan/k_detect_emit
+//   EdgeDetector::joinEdges / nextKeylineIdx        rebvio/src/edge_detector.cpp:125-165 -> k_join
+//   EdgeDetector::tuneThreshold                     rebvio/src/edge_detector.cpp:167-186 -> k_tune
+//
+// Bit-exactness: the integral images are sequential float32 prefix sums (row pass then column pass); a parallel scan
+// rounds differently, so every row / column chain is walked in order by one thread and parallelism comes from the
+// (lanes x rows) resp. (lanes x columns) independent chains. Compiled with -fmad=false.
+#include "rbv_internal.cuh"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Row pass: out[r][c] = out[r][c-1] + in[r][c]   (scale_space.cpp:50-57)
+// One warp owns 32 rows; 32x32 tiles go through shared memory so that global loads/stores are 128-byte coalesced
+// row segments while each lane walks its own row. The next tile is prefetched into registers while the current one
+// is scanned.
+__global__ void __launch_bounds__(32) k_rowscan(const float* __restrict__ in, float* __restrict__ out, int rows, int cols,
+                                                size_t in_plane_stride, size_t out_plane_stride) {
+  __shared__ float tile[32][33];
+  const int lane = threadIdx.x;
+  const int r0 = blockIdx.x * 32;
+  const float* src = in + (size_t)blockIdx.y * in_plane_stride;
+  float* dst = out + (size_t)blockIdx.y * out_plane_stride;
+  const int nr = min(32, rows - r0);
+  float nxt[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) nxt[i] = (i < nr && lane < cols) ? src[(size_t)(r0 + i) * cols + lane] : 0.0f;
+  float carry = 0.0f;
+  for (int c0 = 0; c0 < cols; c0 += 32) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) tile[i][lane] = nxt[i];
+    __syncwarp();
+    const int cn = c0 + 32;
+    if (cn < cols) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) nxt[i] = (i < nr && cn + lane < cols) ? src[(size_t)(r0 + i) * cols + cn + lane] : 0.0f;
+    }
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = tile[lane][j];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      carry = (c0 + j == 0) ? v[j] : carry + v[j];
+      v[j] = carry;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) tile[lane][j] = v[j];
+    __syncwarp();
+    if (c0 + lane < cols) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i < nr) dst[(size_t)(r0 + i) * cols + c0 + lane] = tile[i][lane];
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Column pass fused with the box average (scale_space.cpp:59-65 + 69-128).
+// Thread t of a block walks integral-image column (c0 - h - 1 + t) top to bottom: ii[r][c] = ii[r-1][c] + rowsum[r][c].
+// The last 32 rows of ii live in a shared-memory ring; after every chunk of CH rows the block emits the output rows whose
+// lower tap row is now available. The full integral image never goes to HBM.
+//   A = ii[min(r+h,R-1)][min(c+h,C-1)]  B = ii[.][c-h-1]  Cc = ii[r-h-1][.]  D = ii[r-h-1][c-h-1]
+//   value = ((A-B)-Cc)+D, bottom rows ((A-Cc)-B)+D (scale_space.cpp:99 vs :119,:124), missing taps dropped,
+//   times float(1.0/double(window area)) (precomputeDivisors, :130-171; the interior constant `a` (:72) is the same number).
+#define CB_TPB 128
+#define CB_CH 16
+#define CB_RING 32
+__global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ rowsum, float* __restrict__ out, int rows, int cols,
+                                                   size_t in_plane_stride, size_t out_plane_stride, int nz, int d0, int d1) {
+  __shared__ float ring[CB_RING][CB_TPB];
+  __shared__ float inv_area[16][16];
+  const int t = threadIdx.x;
+  const int z = blockIdx.y % nz;
+  const int d = z ? d1 : d0;
+  const int h = d / 2;
+  const int W = CB_TPB - (2 * h + 1);
+  const int c0 = blockIdx.x * W;
+  const int col = c0 - h - 1 + t;                 // integral-image column scanned by this thread
+  const bool scan_ok = col >= 0 && col < cols;
+  const int oc = c0 + t;                          // output column of this thread (t < W)
+  const bool out_ok = t < W && oc < cols;
+  const float* src = rowsum + (size_t)blockIdx.y * in_plane_stride;
+  float* dst = out + (size_t)blockIdx.y * out_plane_stride;
+  for (int i = t; i < 256; i += CB_TPB) {
+    int a = i / 16, b = i % 16;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;
+  }
+  const int chi = min(oc + h, cols - 1);
+  const int clo = oc - h - 1;
+  const int jhi = chi - (c0 - h - 1);             // ring column of the right tap
+  const int jlo = t;                              // ring column of the left tap (clo - (c0-h-1) == t)
+  const int ncol = chi - max(clo, -1);
+  float run = 0.0f;
+  float nxt[CB_CH];
+#pragma unroll
+  for (int i = 0; i < CB_CH; ++i) nxt[i] = (scan_ok && i < rows) ? src[(size_t)i * cols + col] : 0.0f;
+  int onext = 0;
+  for (int k0 = 0; k0 < rows; k0 += CB_CH) {
+    const int k1 = min(k0 + CB_CH, rows);
+    float cur[CB_CH];
+#pragma unroll
+    for (int i = 0; i < CB_CH; ++i) cur[i] = nxt[i];
+    if (k1 < rows) {
+#pragma unroll
+      for (int i = 0; i < CB_CH; ++i) nxt[i] = (scan_ok && k1 + i < rows) ? src[(size_t)(k1 + i) * cols + col] : 0.0f;
+    }
+#pragma unroll
+    for (int i = 0; i < CB_CH; ++i) {
+      if (k0 + i < rows) {
+        run = (k0 + i == 0) ? cur[i] : run + cur[i];
+        ring[(k0 + i) & (CB_RING - 1)][t] = run;
+      }
+    }
+    __syncthreads();
+    const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - h;   // last output row whose taps are all in the ring
+    if (out_ok) {
+      for (int ro = onext; ro <= olast; ++ro) {
+        const int rhi = min(ro + h, rows - 1), rlo = ro - h - 1;
+        const bool bottom = ro + h >= rows;
+        const float* hi = ring[rhi & (CB_RING - 1)];
+        float v;
+        if (rlo < 0) {
+          v = (clo < 0) ? hi[jhi] : hi[jhi] - hi[jlo];
+        } else {
+          const float* lo = ring[rlo & (CB_RING - 1)];
+          if (clo < 0) v = hi[jhi] - lo[jhi];
+          else if (bottom) v = ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo];
+          else v = ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo];
+        }
+        const int nrow = rhi - max(rlo, -1);
+        dst[(size_t)ro * cols + oc] = v * inv_area[nrow][ncol];
+      }
+    }
+    onext = max(onext, olast + 1);
+    __syncthreads();
+  }
+}
+
+// ScaleSpace::build (scale_space.cpp:203-208): 3 box passes per scale, both scales from the same input.
+// Buffers are [lane][scale][N]; result: scale s of lane b = bufA[(b*2+s)*N].
+int fe_scale_space(rbv_ctx* c, const float* d_img) {
+  const int rows = c->P.rows, cols = c->P.cols, B = c->P.lanes;
+  const size_t N = (size_t)c->P.npix;
+  // pass 0: one row prefix per lane, two column/box passes (d = widths[0][0], widths[1][0])
+  {
+    dim3 g1((rows + 31) / 32, B);
+    k_rowscan<<<g1, 32, 0, c->stream>>>(d_img, c->rowsum, rows, cols, N, N);
+    ++c->launches;
+    for (int z = 0; z < 2; ++z) {
+      const int d = c->widths[z][0];
+      const int W = CB_TPB - (2 * (d / 2) + 1);
+      dim3 g2((cols + W - 1) / W, B);
+      k_colbox<<<g2, CB_TPB, 0, c->stream>>>(c->rowsum, c->bufA + (size_t)z * N, rows, cols, N, 2 * N, 1, d, d);
+      ++c->launches;
+    }
+  }
+  float* src = c->bufA;
+  float* dst = c->bufB;
+  for (int p = 1; p < 3; ++p) {
+    dim3 g1((rows + 31) / 32, 2 * B);
+    k_rowscan<<<g1, 32, 0, c->stream>>>(src, c->rowsum, rows, cols, N, N);
+    ++c->launches;
+    const int d0 = c->widths[0][p], d1 = c->widths[1][p];
+    const int hmax = (d0 > d1 ? d0 : d1) / 2;
+    const int W = CB_TPB - (2 * hmax + 1);
+    dim3 g2((cols + W - 1) / W, 2 * B);
+    k_colbox<<<g2, CB_TPB, 0, c->stream>>>(c->rowsum, dst, rows, cols, N, N, 2, d0, d1);
+    ++c->launches;
+    float* t = src; src = dst; dst = t;
+  }
+  // after passes 1 and 2 the result is back in bufA
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// debug: one box pass (createIntegralImage + average) on lane 0, plane 0 of the scratch buffers
+int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {
+  const int rows = c->P.rows, cols = c->P.cols;
+  const size_t N = (size_t)c->P.npix;
+  k_rowscan<<<dim3((rows + 31) / 32, 1), 32, 0, c->stream>>>(d_in, c->rowsum, rows, cols, N, N);
+  const int d = c->widths[scale][pass];
+  const int W = CB_TPB - (2 * (d / 2) + 1);
+  k_colbox<<<dim3((cols + W - 1) / W, 1), CB_TPB, 0, c->stream>>>(c->rowsum, d_out, rows, cols, N, N, 1, d, d);
+  c->launches += 2;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Per-pixel keyline test (edge_detector.cpp:83-107). y[25] = DoG window in row-major order (dr outer, dc inner).
+struct FitResult {
+  float th0, th1, xs, ys;
+};
+__device__ __forceinline__ bool rbv_fit_plane(const float* y, const DevParams& P, float gradient_threshold_squared, FitResult& o) {
+  int pn = 0;
+#pragma unroll
+  for (int k = 0; k < 25; ++k) pn = (y[k] > 0.0f) ? pn + 1 : pn - 1;                   // :92
+  if (fabs((double)pn) > (double)P.pn_threshold) return false;                         // :96
+  float th[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {                                                        // :98 sequential dot from 0
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) acc += P.pinv[a * 25 + k] * y[k];
+    th[a] = acc;
+  }
+  const float n2 = th[0] * th[0] + th[1] * th[1];
+  const float tmp = th[2] / n2;                                                        // :99
+  const float xs = -th[0] * tmp, ys = -th[1] * tmp;
+  if (fabsf(xs) > 0.5f || fabsf(ys) > 0.5f) return false;                              // :103
+  if (n2 < gradient_threshold_squared) return false;                                   // :107
+  o.th0 = th[0]; o.th1 = th[1]; o.xs = xs; o.ys = ys;
+  return true;
+}
+
+// Pass 1: flags. Block = 8 warps, tile = 8 rows x 32 columns (one flag word per warp); DoG = s1 - s0 is formed in shared
+// memory (never written to HBM), the squared gradient magnitude comes from the s0 tile. Also resets the id mask.
+#define DT_ROWS 8
+__global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ scales, const float* __restrict__ thr_dev,
+                                                      unsigned* __restrict__ flags, int* __restrict__ rowcount, int* __restrict__ mask,
+                                                      const __grid_constant__ DevParams P, int wpr) {
+  __shared__ float s0t[DT_ROWS + 4][36];
+  __shared__ float dogt[DT_ROWS + 4][36];
+  const int b = blockIdx.z;
+  const int rows = P.rows, cols = P.cols;
+  const size_t N = (size_t)P.npix;
+  const float* s0 = scales + (size_t)(b * 2) * N;
+  const float* s1 = s0 + N;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * DT_ROWS;
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  for (int i = tid; i < (DT_ROWS + 4) * 36; i += 256) {
+    const int tr = i / 36, tc = i % 36;
+    const int r = r0 - 2 + tr, q = c0 - 2 + tc;
+    float a = 0.0f, d = 0.0f;
+    if (r >= 0 && r < rows && q >= 0 && q < cols) {
+      a = s0[(size_t)r * cols + q];
+      d = s1[(size_t)r * cols + q] - a;                                                // calculateDoG, scale_space.cpp:216
+    }
+    s0t[tr][tc] = a;
+    dogt[tr][tc] = d;
+  }
+  __syncthreads();
+  const int r = r0 + threadIdx.y, q = c0 + threadIdx.x;
+  bool cand = false;
+  if (r < rows && q < cols) mask[(size_t)b * N + (size_t)r * cols + q] = -1;
+  if (r >= 2 && r < rows - 2 && q >= 2 && q < cols - 2) {
+    const float thr = thr_dev[b];
+    const float tm = thr * 765.0f;
+    const float mag_threshold = tm * tm;                                               // edge_detector.cpp:71
+    const float tg = tm * P.dog_threshold;
+    const float gts = tg * tg;                                                         // :70
+    const int tr = threadIdx.y + 2, tc = threadIdx.x + 2;
+    const float dx = s0t[tr][tc + 1] - s0t[tr][tc - 1];
+    const float dy = s0t[tr + 1][tc] - s0t[tr - 1][tc];
+    const float mag = dx * dx + dy * dy;                                               // scale_space.cpp:228-230
+    if (!(mag < mag_threshold)) {                                                      // :83
+      float y[25];
+#pragma unroll
+      for (int dr = 0; dr < 5; ++dr)
+#pragma unroll
+        for (int dc = 0; dc < 5; ++dc) y[dr * 5 + dc] = dogt[tr - 2 + dr][tc - 2 + dc];
+      FitResult fr;
+      cand = rbv_fit_plane(y, P, gts, fr);
+    }
+  }
+  const unsigned word = __ballot_sync(0xFFFFFFFFu, cand);
+  if (threadIdx.x == 0 && r < rows) {
+    flags[((size_t)b * rows + r) * wpr + blockIdx.x] = word;
+    if (word) atomicAdd(&rowcount[b * rows + r], __popc(word));
+  }
+}
+
+// Pass 2: exclusive prefix of the per-row counts -> first keyline id of every row; count = min(total, keylines_max)
+__global__ void __launch_bounds__(1024) k_detect_scan(const int* __restrict__ rowcount, int* __restrict__ rowoffset, int* __restrict__ count,
+                                                      int rows, int kmax) {
+  __shared__ int part[1024];
+  const int b = blockIdx.x, t = threadIdx.x;
+  const int per = (rows + 1023) / 1024;
+  const int lo = t * per, hi = min(lo + per, rows);
+  int s = 0;
+  for (int r = lo; r < hi; ++r) s += rowcount[b * rows + r];
+  part[t] = s;
+  __syncthreads();
+  // Hillis-Steele inclusive scan over 1024 partials
+  for (int off = 1; off < 1024; off <<= 1) {
+    int v = (t >= off) ? part[t - off] : 0;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  int run = part[t] - s;
+  for (int r = lo; r < hi; ++r) {
+    rowoffset[b * rows + r] = run;
+    run += rowcount[b * rows + r];
+  }
+  if (t == 1023) count[b] = min(part[1023], kmax);
+}
+
+// Pass 3: emit keylines in row-major id order (edge_detector.cpp:109-119, KeyLine ctor types/keyline.hpp:42-59).
+// One warp per image row: lane l owns flag word l (+32 per round); ids = row offset + prefix popcount.
+__global__ void __launch_bounds__(32) k_detect_emit(const float* __restrict__ scales, const float* __restrict__ thr_dev,
+                                                    const unsigned* __restrict__ flags, const int* __restrict__ rowoffset, KeylineSoA K,
+                                                    int* __restrict__ mask, const __grid_constant__ DevParams P, int wpr) {
+  const int b = blockIdx.y, r = blockIdx.x + 2, lane = threadIdx.x;
+  const int rows = P.rows, cols = P.cols, kmax = P.kmax;
+  const size_t N = (size_t)P.npix;
+  int base = rowoffset[b * rows + r];
+  if (base >= P.keylines_max) return;
+  const float* s0 = scales + (size_t)(b * 2) * N;
+  const float* s1 = s0 + N;
+  const float thr = thr_dev[b];
+  const float tg = thr * 765.0f * P.dog_threshold;
+  const float gts = tg * tg;
+  for (int w0 = 0; w0 < wpr; w0 += 32) {
+    const int w = w0 + lane;
+    unsigned word = (w < wpr) ? flags[((size_t)b * rows + r) * wpr + w] : 0u;
+    const int cnt = __popc(word);
+    int inc = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      int v = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+      if (lane >= off) inc += v;
+    }
+    int id = base + inc - cnt;
+    base += __shfl_sync(0xFFFFFFFFu, inc, 31);
+    while (word) {
+      const int bit = __ffs(word) - 1;
+      word &= word - 1;
+      if (id < P.keylines_max) {
+        const int q = w * 32 + bit;
+        float y[25];
+#pragma unroll
+        for (int dr = 0; dr < 5; ++dr)
+#pragma unroll
+          for (int dc = 0; dc < 5; ++dc) {
+            const size_t o = (size_t)(r - 2 + dr) * cols + (q - 2 + dc);
+            y[dr * 5 + dc] = s1[o] - s0[o];
+          }
+        FitResult fr;
+        rbv_fit_plane(y, P, gts, fr);  // same arithmetic as pass 1 -> true by construction
+        const float px = (float)q + fr.xs, py = (float)r + fr.ys;                      // :109
+        const size_t o = (size_t)b * kmax + id;
+        K.pos[o] = make_float2(px, py);
+        const float2 pi = make_float2(px - P.cx, py - P.cy);                            // :110
+        K.pos_img[o] = pi;
+        K.match_pos_img[o] = pi;
+        K.grad[o] = make_float2(fr.th0, fr.th1);
+        K.match_grad[o] = make_float2(0.0f, 0.0f);
+        K.gnorm[o] = sqrtf(fr.th0 * fr.th0 + fr.th1 * fr.th1);
+        K.match_gnorm[o] = 0.0f;
+        K.rho[o] = RBV_RHO_INIT;
+        K.srho[o] = RBV_RHO_MAX;
+        K.id_prev[o] = -1; K.id_next[o] = -1; K.match_id[o] = -1; K.match_fwd[o] = -1; K.match_kf[o] = -1;
+        K.matches[o] = 0u;
+        const unsigned pix = (unsigned)(r * cols + q);
+        K.pixel[o] = pix;
+        K.residual[o] = 0.0f;
+        mask[(size_t)b * N + pix] = id;                                                 // :111-112
+      }
+      ++id;
+    }
+  }
+}
+
+// joinEdges + nextKeylineIdx (edge_detector.cpp:125-165). id_prev: the sequential loop lets the largest idx win -> atomicMax.
+__global__ void k_join(KeylineSoA K, const int* __restrict__ count, const int* __restrict__ mask, const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * P.kmax + idx;
+  const float2 p = K.pos[o], g = K.grad[o];
+  const int x = rbv_d2i((double)p.x + 0.5), y = rbv_d2i((double)p.y + 0.5);             // :128-129
+  const float tx = -g.y, ty = g.x;
+  const int sx = (ty > 0.0f) ? ((tx > 0.0f) ? 1 : -1) : ((tx < 0.0f) ? -1 : 1);
+  const int sy = (ty > 0.0f) ? 1 : -1;
+  const int* m = mask + (size_t)b * P.npix;
+  int hit = m[y * P.cols + x + sx];
+  if (hit < 0) hit = m[(y + sy) * P.cols + x];
+  if (hit < 0) hit = m[(y + sy) * P.cols + x + sx];
+  if (hit < 0) return;
+  atomicMax(&K.id_prev[(size_t)b * P.kmax + hit], idx);                                // :133
+  K.id_next[o] = hit;                                                                  // :134
+}
+
+// tuneThreshold (edge_detector.cpp:167-186). The histogram scan at :183 always runs to i == num_bins (bin 0 holds the
+// maximum, so bins 1.. can never reach keylines_max), hence threshold = max - float(100*(max-min))/100.
+__global__ void __launch_bounds__(1024) k_tune(KeylineSoA K, const int* __restrict__ count, float* __restrict__ threshold, int kmax) {
+  __shared__ float smx[32], smn[32];
+  const int b = blockIdx.x, n = count[b], t = threadIdx.x;
+  float mx = -INFINITY, mn = INFINITY;
+  for (int i = t; i < n; i += 1024) {
+    const float g = K.gnorm[(size_t)b * kmax + i];
+    mx = fmaxf(mx, g);
+    mn = fminf(mn, g);
+  }
+#pragma unroll
+  for (int off = 16; off; off >>= 1) {
+    mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
+    mn = fminf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, off));
+  }
+  if ((t & 31) == 0) { smx[t >> 5] = mx; smn[t >> 5] = mn; }
+  __syncthreads();
+  if (t == 0) {
+    for (int i = 1; i < 32; ++i) { mx = fmaxf(mx, smx[i]); mn = fminf(mn, smn[i]); }
+    if (n < 1) {
+      threshold[b] = -1.0f;  // reference: undefined behaviour on an empty map; the map keeps its initial -1
+    } else {
+      const float span = (float)RBV_TUNE_BINS * (mx - mn);                             // i*(max_dog-min_dog), i == num_bins
+      threshold[b] = mx - span / (float)RBV_TUNE_BINS;                                 // :184
+    }
+  }
+}
+
+// EdgeDetector::buildEdgeMap + joinEdges + tuneThreshold on the scale space already in bufA
+int fe_detect(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  const int B = P.lanes, rows = P.rows, cols = P.cols;
+  const int wpr = (cols + 31) / 32;
+  RBV_CUDA(cudaMemsetAsync(c->rowcount, 0, sizeof(int) * (size_t)B * rows, c->stream));
+  dim3 g1(wpr, (rows + DT_ROWS - 1) / DT_ROWS, B);
+  k_detect_flags<<<g1, dim3(32, DT_ROWS), 0, c->stream>>>(c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, P, wpr);
+  k_detect_scan<<<B, 1024, 0, c->stream>>>(c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
+  k_detect_emit<<<dim3(rows - 4, B), 32, 0, c->stream>>>(c->bufA, c->thr_dev, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+  k_join<<<dim3((P.kmax + 255) / 256, B), 256, 0, c->stream>>>(map->k, map->count, map->mask, P);
+  k_tune<<<B, 1024, 0, c->stream>>>(map->k, map->count, map->threshold, P.kmax);
+  c->launches += 5;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// debug taps: DoG (which = 2) / squared gradient magnitude (which = 3) of one lane, recomputed from the scales
+__global__ void k_dog_mag(const float* __restrict__ s0, const float* __restrict__ s1, float* __restrict__ out, int rows, int cols, int which) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (q >= cols) return;
+  const size_t o = (size_t)r * cols + q;
+  if (which == 2) { out[o] = s1[o] - s0[o]; return; }
+  float v = 0.0f;
+  if (r >= 1 && r < rows - 1 && q >= 1 && q < cols - 1) {
+    const float dx = s0[o + 1] - s0[o - 1], dy = s0[o + cols] - s0[o - cols];
+    v = dx * dx + dy * dy;
+  }
+  out[o] = v;
+}
+int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out) {
+  const size_t N = (size_t)c->P.npix;
+  const float* s0 = c->bufA + (size_t)(lane * 2) * N;
+  k_dog_mag<<<dim3((c->P.cols + 127) / 128, c->P.rows), 128, 0, c->stream>>>(s0, s0 + N, d_out, c->P.rows, c->P.cols, which);
+  ++c->launches;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}

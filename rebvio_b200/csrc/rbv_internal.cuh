@@ -1,0 +1,220 @@
+// rbv_internal.cuh — shared declarations of the B200-native REBVIO hot path (sm_100a).
+//
+// Layout in HBM (all arrays lane-major, B = lanes = independent image sequences processed per launch):
+//   images      float  [B][rows][cols]        input frame, scale-space ping/pong buffers, row-prefix scratch
+//   id mask     int32  [B][rows*cols]         per map: pixel -> keyline id (-1 none)  (EdgeMap::mask(), edge_map.hpp:130)
+//   field       uint32 [B][rows*cols]         packed distance field (|r| << 24 | 0xFFFFFF - id), 0xFFFFFFFF = empty
+//   keylines    SoA    [field][B][kmax]       float2 for the 2-vectors, float / int32 / uint32 scalars
+// Everything is float32 evaluated in the reference's order; the translation units are compiled with -fmad=false so no
+// multiply-add is ever contracted (the reference parity build is -ffp-contract=off).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rebvio_b200.h"
+
+#define RBV_RHO_MAX 20.0f   // types/keyline.hpp:19
+#define RBV_RHO_MIN 1e-3f   // types/keyline.hpp:20
+#define RBV_RHO_INIT 1.0f   // types/keyline.hpp:21
+#define RBV_FIELD_EMPTY 0xFFFFFFFFu
+#define RBV_TUNE_BINS 100
+#define RBV_MAX_QBINS 1024
+#define RBV_MAX_LM_ITERS 15
+
+// ---- keyline SoA of one B-lane map (device pointers, each [B][kmax]) ----
+struct KeylineSoA {
+  float2* pos;            // KeyLine::pos
+  float2* pos_img;        // KeyLine::pos_img
+  float2* match_pos_img;  // KeyLine::match_pos_img
+  float2* grad;           // KeyLine::gradient
+  float2* match_grad;     // KeyLine::match_gradient
+  float* gnorm;           // gradient_norm
+  float* match_gnorm;     // match_gradient_norm
+  float* rho;
+  float* srho;            // sigma_rho
+  int* id_prev;
+  int* id_next;
+  int* match_id;
+  int* match_fwd;         // match_id_forward
+  int* match_kf;          // match_id_keyframe
+  unsigned* matches;
+  unsigned* pixel;        // detection pixel (key of EdgeMap::mask())
+  float* residual;        // Core::minimizeVel's residuals[] (core.cpp:158), kept with the map
+};
+
+struct rbv_map {
+  KeylineSoA k;
+  int* mask;         // [B][npix]
+  int* count;        // [B]
+  float* threshold;  // [B]  EdgeMap::threshold_
+  uint64_t* ts_us;   // host copy only
+  void* slab;        // one allocation backing everything above
+  size_t slab_bytes;
+};
+
+// Levenberg-Marquardt state of Core::minimizeVel, one per lane, device resident
+struct LMState {
+  float vel[3];
+  float F;
+  float JtJ[9];
+  float JtF[3];
+  float u, v;
+  float vnew[3];
+  float h[3];
+  float sigma_rho_min;
+  float Rvel[9];
+  float trace[(RBV_MAX_LM_ITERS + 1) * 16];
+};
+
+struct DevParams {  // constant per context
+  float fm, cx, cy;
+  int rows, cols, npix, kmax, lanes;
+  // detector
+  float pn_threshold;
+  float dog_threshold;
+  int keylines_max;
+  // map cfg
+  float pixel_uncertainty_match, match_threshold_norm, cang_min_edge, regularization_threshold;
+  // core cfg
+  float search_range, reweight_distance, match_treshold, pixel_uncertainty, quantile_cutoff, reshape_q_abs;
+  int quantile_num_bins, iterations, field_r0, field_nr;
+  unsigned min_matches;
+  float pinv[75];
+};
+
+struct rbv_ctx {
+  DevParams P;
+  rbv_camera cam;
+  rbv_detector_cfg det;
+  rbv_map_cfg mapc;
+  rbv_core_cfg core;
+  int device;
+  int reduce_mode;
+  cudaStream_t stream;
+  bool own_stream;
+  int widths[2][3];
+  // images
+  float* img;       // [B][N]
+  float* rowsum;    // [2][B][N] row-prefix scratch per scale
+  float* bufA;      // [2][B][N]
+  float* bufB;      // [2][B][N]
+  // detect scratch
+  unsigned* flags;  // [B][rows][wpr] bit flags
+  int* rowcount;    // [B][rows]
+  int* rowoffset;   // [B][rows]
+  float* thr_dev;   // [B] servoed thresholds of this detect
+  // tracker scratch
+  unsigned* field;  // [B][N]
+  rbv_map* field_map;
+  float* prod;      // [10][B][kmax] tryVel per-keyline addends / [7][B][kmax] extRotVel rows (shared)
+  float* fiabs;     // [B][kmax]
+  int* fwd_head;    // [B][kmax]
+  int* fwd_next;    // [B][kmax]
+  float* reg_r;     // [B][kmax]
+  float* reg_s;     // [B][kmax]
+  LMState* lm;      // [B]
+  float* lane_in;   // [B][64] per-call lane inputs (R, vel, Rvel, Rback ...)
+  float* lane_out;  // [B][64] per-call lane outputs
+  int* lane_cnt;    // [B][8] counters (matches, kf, regularised ...)
+  unsigned long long* probes;  // [B]
+  // pinned host staging
+  float* h_in;
+  float* h_out;
+  int* h_cnt;
+  float* h_lm;
+  float* h_img;     // pinned staging for rbv_detect host frames [B][N]
+  unsigned long long launches;  // kernels launched since creation
+};
+
+// lane_in slots
+enum { IN_R = 0, IN_VEL = 9, IN_RVEL = 12, IN_RBACK = 21, IN_SRMIN = 30, IN_MAXRADIUS = 31, IN_STRIDE = 64 };
+// lane_out slots
+enum { OUT_JTJ = 0, OUT_JTF = 9, OUT_SCORE = 12, OUT_WX = 16, OUT_X = 52, OUT_OK = 58, OUT_Q = 59, OUT_STRIDE = 64 };
+// lane_cnt slots
+enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
+
+void rbv_set_error(const char* fmt, ...);
+#define RBV_CUDA(call)                                                                        \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      rbv_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));    \
+      return RBV_ERR_CUDA;                                                                    \
+    }                                                                                         \
+  } while (0)
+
+// ---- launchers (host functions defined in the .cu files) ----
+int fe_scale_space(rbv_ctx* c, const float* d_img);
+int fe_detect(rbv_ctx* c, rbv_map* map);
+int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out);
+int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out);
+
+int tr_build_field(rbv_ctx* c, rbv_map* map);
+int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
+int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);
+int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call);     // lm_call: -1 = single evaluation (vel, srmin in lane_in), t >= 0 = LM call t
+int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map);
+int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm);
+int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map);
+int tr_regularize(rbv_ctx* c, rbv_map* map);
+int tr_kalman(rbv_ctx* c, rbv_map* map);                   // vel in lane_in[IN_VEL]
+
+// ---- device helpers -------------------------------------------------------------------------------------
+// 3x3 determinant by Gaussian elimination with partial pivoting (TooN determinant.h:91-146)
+__host__ __device__ inline float rbv_det3(const float* in) {
+  float A[3][3];
+  for (int i = 0; i < 9; ++i) A[i / 3][i % 3] = in[i];
+  float det = 1.0f;
+  for (int i = 0; i < 3; ++i) {
+    int arg = i;
+    float best = fabsf(A[i][i]);
+    for (int k = i + 1; k < 3; ++k) {
+      float v = fabsf(A[k][i]);
+      if (v > best) { best = v; arg = k; }
+    }
+    float pivot = A[arg][i];
+    if (arg != i) {
+      det *= -1.0f;
+      for (int j = i; j < 3; ++j) { float t = A[i][j]; A[i][j] = A[arg][j]; A[arg][j] = t; }
+    }
+    det *= A[i][i];
+    if (det == 0.0f) return 0.0f;
+    for (int u = i + 1; u < 3; ++u) {
+      float factor = A[u][i] / pivot;
+      for (int j = i + 1; j < 3; ++j) A[u][j] = A[u][j] - factor * A[i][j];
+    }
+  }
+  return det;
+}
+
+// cofactor inverse / determinant (types/definitions.hpp:40-53)
+__host__ __device__ inline void rbv_inv3(const float* m, float* out) {
+  float co[9];
+  co[0] = m[4] * m[8] - m[5] * m[7];
+  co[1] = m[2] * m[7] - m[1] * m[8];
+  co[2] = m[1] * m[5] - m[2] * m[4];
+  co[3] = m[5] * m[6] - m[3] * m[8];
+  co[4] = m[0] * m[8] - m[2] * m[6];
+  co[5] = m[2] * m[3] - m[0] * m[5];
+  co[6] = m[3] * m[7] - m[4] * m[6];
+  co[7] = m[1] * m[6] - m[0] * m[7];
+  co[8] = m[0] * m[4] - m[1] * m[3];
+  float d = rbv_det3(m);
+  for (int i = 0; i < 9; ++i) out[i] = co[i] / d;
+}
+
+#ifdef __CUDACC__
+// x86 cvttsd2si / cvttss2si semantics (out of range or NaN -> INT_MIN), which the reference's static_cast<int> compiles to
+__device__ __forceinline__ int rbv_d2i(double d) {
+  return (d != d || d >= 2147483648.0 || d <= -2147483649.0) ? (-2147483647 - 1) : __double2int_rz(d);
+}
+__device__ __forceinline__ int rbv_f2i(float f) {
+  return (f != f || f >= 2147483648.0f || f < -2147483648.0f) ? (-2147483647 - 1) : __float2int_rz(f);
+}
+// std::round(float) -> int : half away from zero (getIndex, core.hpp:66-71, edge_map.hpp:119-124)
+__device__ __forceinline__ int rbv_pixel_index(int rows, int cols, float row, float col) {
+  int r = rbv_f2i(roundf(row)), q = rbv_f2i(roundf(col));
+  if (r >= rows || r < 0 || q >= cols || q < 0) return -1;
+  return r * cols + q;
+}
+#endif

@@ -1,0 +1,862 @@
+// rbv_tracker.cu — edge tracker on sm_100a: distance field, keyline rotation, sigma_rho quantile, energy / Jacobian
+// evaluation with on-device Levenberg-Marquardt, forward match, linearised 6-DoF solve, directed match, depth
+// regularisation, per-keyline Kalman update.
+//
+// Replaces (reference paths relative to the reference root):
+//   DistanceField::build                 rebvio/include/rebvio/core.hpp:37-59      -> k_field_build (packed atomicMin)
+//   EdgeMap::rotateKeylines              rebvio/src/edge_map.cpp:58-71             -> k_rotate
+//   EdgeMap::estimateQuantile            rebvio/src/edge_map.cpp:39-56             -> k_quantile
+//   Core::tryVel/calculatefJ/testfk      rebvio/src/core.cpp:39-148                -> k_tryvel_eval + k_tryvel_reduce
+//   Core::minimizeVel                    rebvio/src/core.cpp:150-189               -> LM step at the tail of k_tryvel_reduce
+//   EdgeMap::forwardMatch                rebvio/src/edge_map.cpp:73-99             -> k_fwd_link + k_fwd_resolve
+//   Core::extRotVel                      rebvio/src/core.cpp:191-261               -> k_extrot_rows + k_extrot_reduce
+//   EdgeMap::directedMatch/searchMatch   rebvio/src/edge_map.cpp:101-218           -> k_directed
+//   EdgeMap::regularize1Iter             rebvio/src/edge_map.cpp:220-259           -> k_reg_eval + k_reg_apply
+//   Core::updateInverseDepth(ARLU)       rebvio/src/core.cpp:417-456               -> k_kalman
+//
+// Reductions (J^T J, J^T F, score): RBV_REDUCE_FAST = per-thread FP64 partials + warp-shuffle tree in a fixed order;
+// RBV_REDUCE_ORDERED = one lane per accumulator adds the float32 addends in keyline order, reproducing the CPU bits.
+#include "rbv_internal.cuh"
+
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void k_field_build(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
+                              unsigned* __restrict__ field, const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y;
+  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+  const int idx = gi / P.field_nr, ri = gi - idx * P.field_nr;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * P.kmax + idx;
+  const float gn = K.gnorm[o];
+  const float thr = threshold[b];
+  if (thr > 0.0f && gn < thr) return;                                                  // core.hpp:47
+  const int r = P.field_r0 + ri;                                                       // r = -search_range .. search_range-1
+  const float2 g = K.grad[o], p = K.pos[o];
+  const int fi = rbv_pixel_index(P.rows, P.cols, (g.y / gn) * (float)r + p.y, (g.x / gn) * (float)r + p.x);  // :50-51
+  if (fi < 0) return;
+  // sequential rule (:54-56): smallest |r| wins, ties go to the later (idx, r) -> min over (|r|, -idx)
+  const unsigned key = ((unsigned)abs(r) << 24) | (0xFFFFFFu - (unsigned)idx);
+  atomicMin(&field[(size_t)b * P.npix + fi], key);
+}
+
+int tr_build_field(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  RBV_CUDA(cudaMemsetAsync(c->field, 0xFF, sizeof(unsigned) * (size_t)P.lanes * P.npix, c->stream));
+  const long long work = (long long)P.keylines_max * P.field_nr;
+  k_field_build<<<dim3((unsigned)((work + 255) / 256), P.lanes), 256, 0, c->stream>>>(map->k, map->count, map->threshold, c->field, P);
+  ++c->launches;
+  c->field_map = map;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// rotateKeylines: R * makeVector(float, float, double) is a float x double product accumulated in double
+// (TooN make_vector.hh:26, operators.hh:200-208) and rounded to float on assignment.
+__global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in, const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const float* R = lane_in + (size_t)b * IN_STRIDE + IN_R;
+  const size_t o = (size_t)b * P.kmax + idx;
+  const float fm = P.fm;
+  float2 pi = K.pos_img[o];
+  const double v0 = (double)(pi.x / fm), v1 = (double)(pi.y / fm), v2 = 1.0;
+  float q[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    double acc = 0.0;
+    acc += (double)R[r * 3 + 0] * v0;
+    acc += (double)R[r * 3 + 1] * v1;
+    acc += (double)R[r * 3 + 2] * v2;
+    q[r] = (float)acc;
+  }
+  if (fabsf(q[2]) > 0.0f) {
+    pi.x = q[0] / q[2] * fm;
+    pi.y = q[1] / q[2] * fm;
+    K.pos_img[o] = pi;
+    K.rho[o] = K.rho[o] / q[2];
+    K.srho[o] = K.srho[o] / q[2];
+  }
+  const float2 g = K.grad[o];
+  float2 go;
+  {
+    double acc = 0.0;
+    acc += (double)R[0] * (double)g.x; acc += (double)R[1] * (double)g.y; acc += (double)R[2] * 0.0;
+    go.x = (float)acc;
+    acc = 0.0;
+    acc += (double)R[3] * (double)g.x; acc += (double)R[4] * (double)g.y; acc += (double)R[5] * 0.0;
+    go.y = (float)acc;
+  }
+  K.grad[o] = go;
+}
+
+int tr_rotate(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  k_rotate<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(map->k, map->count, c->lane_in, P);
+  ++c->launches;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __restrict__ count, float percentile, int bins, int kmax,
+                                                  LMState* lm, float* lane_out, int to_lm) {
+  __shared__ int hist[RBV_MAX_QBINS];
+  const int b = blockIdx.x, n = count[b];
+  for (int i = threadIdx.x; i < bins; i += 256) hist[i] = 0;
+  __syncthreads();
+  const float span = RBV_RHO_MAX - RBV_RHO_MIN;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    int q = rbv_f2i((float)bins * (K.srho[(size_t)b * kmax + i] - RBV_RHO_MIN) / span);   // edge_map.cpp:42
+    q = q > bins - 1 ? bins - 1 : q;
+    q = q < 0 ? 0 : q;
+    atomicAdd(&hist[q], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float out = 1e3f;
+    const float lim = percentile * (float)n;
+    for (int i = 0, a = 0; i < bins; ++i) {
+      if ((float)a > lim) { out = (float)i * span / (float)bins + RBV_RHO_MIN; break; }    // :49-50
+      a += hist[i];
+    }
+    if (to_lm) lm[b].sigma_rho_min = out;
+    lane_out[(size_t)b * OUT_STRIDE + OUT_Q] = out;
+  }
+}
+
+int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
+  if (bins < 1 || bins > RBV_MAX_QBINS) { rbv_set_error("quantile bins out of range"); return RBV_ERR_ARG; }
+  k_quantile<<<c->P.lanes, 256, 0, c->stream>>>(map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm);
+  ++c->launches;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// tryVel, per-keyline part. Addends (zero for skipped keylines: x + 0 == x exactly) go to prod[10][B][kmax]:
+//   0 score f*f | 1..6 JtJ 00,11,22,01,02,12 | 7..9 JtF 0,1,2
+// fiabs code for the residual rule: >= 0 matched (|fi|), -1 in-image but unmatched, -2 no residual write.
+__global__ void __launch_bounds__(256) k_tryvel_eval(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
+                                                     KeylineSoA Kn, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
+                                                     int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
+                                                     float* __restrict__ prod, float* __restrict__ fiabs,
+                                                     const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count_o[b]) return;
+  const size_t o = (size_t)b * P.kmax + idx;
+  const size_t ps = (size_t)P.lanes * P.kmax;
+  const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+  const float sigma_rho_min = sr_ptr[(size_t)b * sr_stride];
+  float add[10];
+#pragma unroll
+  for (int a = 0; a < 10; ++a) add[a] = 0.0f;
+  float code = -2.0f;
+  int fwd = -1;
+  const float thr = thr_o[b];
+  const float gn = Ko.gnorm[o];
+  const float srho = Ko.srho[o];
+  const bool skip = (thr > 0.0f && gn < thr) || (srho > sigma_rho_min) || (Ko.matches[o] < P.min_matches);   // core.cpp:88,91
+  if (!skip) {
+    float w = 1.0f;
+    const float res = Ko.residual[o];
+    if (res > P.reweight_distance) w = P.reweight_distance / res;                        // :94
+    const float rho = Ko.rho[o];
+    const float z_p = (float)(1.0 / (double)rho + (double)v2);                           // :96
+    const float2 pi = Ko.pos_img[o];
+    bool penalty = z_p <= 0.0f;
+    float rho_p = 0.0f, px = 0.0f, py = 0.0f, pxc = 0.0f, pyc = 0.0f;
+    int x = 0, y = 0;
+    if (!penalty) {
+      rho_p = (float)(1.0 / (double)z_p);                                                // :104
+      px = rho_p * (v0 * P.fm - v2 * pi.x) + pi.x;                                       // :105
+      py = rho_p * (v1 * P.fm - v2 * pi.y) + pi.y;
+      pxc = px + P.cx; pyc = py + P.cy;
+      x = rbv_d2i((double)pxc + 0.5);                                                    // :111
+      y = rbv_d2i((double)pyc + 0.5);
+      penalty = (x < 1 || y < 1 || x >= P.cols - 1 || y >= P.rows - 1);                  // :114
+    }
+    if (penalty) {
+      const float f = (float)((1.0 / (double)srho) * (double)P.search_range * (double)w);   // :99 / :115
+      add[0] = f * f;
+    } else {
+      float dfx = 0.0f, dfy = 0.0f, f;
+      bool matched = false;
+      const unsigned cell = field[(size_t)b * P.npix + (size_t)y * P.cols + x];
+      if (cell != RBV_FIELD_EMPTY) {
+        const int tid = (int)(0xFFFFFFu - (cell & 0xFFFFFFu));
+        const size_t to = (size_t)b * P.kmax + tid;
+        const float2 tg = Kn.grad[to];
+        const float2 g = Ko.grad[o];
+        const float n2 = gn * gn;                                                        // testfk :40-42
+        const float dp = tg.x * g.x + tg.y * g.y;
+        if (!(fabsf(dp - n2) > P.match_treshold * n2)) {
+          matched = true;
+          const float2 tp = Kn.pos[to];
+          const float tgn = Kn.gnorm[to];
+          const float dx = pxc - tp.x, dy = pyc - tp.y;                                  // :62-63
+          const float gnx = tg.x / tgn, gny = tg.y / tgn;
+          const float fi = dx * gnx + dy * gny;                                          // :67
+          dfx = gnx / srho; dfy = gny / srho;
+          fwd = tid;                                                                     // :73
+          f = fi / srho;                                                                 // :75
+          code = fabsf(fi);                                                              // :141
+        }
+      }
+      if (!matched) { f = P.search_range / srho; code = -1.0f; }                         // :52 / :59
+      f *= w;
+      add[0] = f * f;
+      const float jx = rho_p * P.fm * dfx * w;                                           // :126-128
+      const float jy = rho_p * P.fm * dfy * w;
+      const float jz = -rho_p * (px * dfx + py * dfy) * w;
+      add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
+      add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
+      add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
+    }
+  }
+  Ko.match_fwd[o] = fwd;                                                                 // :87
+  fiabs[o] = code;
+#pragma unroll
+  for (int a = 0; a < 10; ++a) prod[a * ps + o] = add[a];
+}
+
+// block-wide sum of NV doubles per thread in a fixed order (deterministic): shuffle tree inside a warp, then the
+// first NV threads add the 32 warp partials in warp order.
+template <int NV>
+__device__ __forceinline__ void block_sum_fixed(double* acc, double* sm /*[32][NV]*/, double* result /*[NV] in smem*/) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int a = 0; a < NV; ++a) {
+    double v = acc[a];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+    if (lane == 0) sm[warp * NV + a] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < NV) {
+    double s = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += sm[w * NV + threadIdx.x];
+    result[threadIdx.x] = s;
+  }
+  __syncthreads();
+}
+
+// LM bookkeeping of Core::minimizeVel (core.cpp:159-185), executed by one thread per lane after each tryVel
+__device__ void lm_update(LMState& S, int call, int iterations, float score, const float* JtJn, const float* JtFn, const float* vel_used) {
+  float* tr = S.trace + call * 16;
+  for (int i = 0; i < 3; ++i) tr[i] = vel_used[i];
+  for (int i = 0; i < 9; ++i) tr[3 + i] = JtJn[i];
+  for (int i = 0; i < 3; ++i) tr[12 + i] = JtFn[i];
+  tr[15] = score;
+  bool need_step;
+  if (call == 0) {
+    S.F = score;
+    for (int i = 0; i < 9; ++i) S.JtJ[i] = JtJn[i];
+    for (int i = 0; i < 3; ++i) S.JtF[i] = JtFn[i];
+    S.v = 2.0f;
+    float mx = JtJn[0];
+    for (int i = 1; i < 9; ++i) if (JtJn[i] > mx) mx = JtJn[i];                          // TooN::max_element
+    S.u = 1e-3f * mx;                                                                    // :161-163
+    need_step = iterations > 0;
+  } else {
+    double den = 0.0;                                                                    // 0.5*h * (u*h - JtF), :172
+    for (int i = 0; i < 3; ++i) {
+      const float d = S.u * S.h[i] - S.JtF[i];
+      den += (0.5 * (double)S.h[i]) * (double)d;
+    }
+    const float gain = (float)((double)(S.F - score) / den);
+    if (gain > 0.0f) {                                                                   // :173-179
+      S.F = score;
+      for (int i = 0; i < 3; ++i) S.vel[i] = S.vnew[i];
+      for (int i = 0; i < 9; ++i) S.JtJ[i] = JtJn[i];
+      for (int i = 0; i < 3; ++i) S.JtF[i] = JtFn[i];
+      const double t = 2.0 * (double)gain - 1.0;
+      const double s = 1.0 - (t * t * t);
+      S.u = (float)((double)S.u * (0.33 > s ? 0.33 : s));
+      S.v = 2.0f;
+    } else {                                                                             // :180-183
+      S.u *= S.v;
+      S.v = (float)((double)S.v * 2.0);
+    }
+    need_step = call < iterations;
+  }
+  if (need_step) {
+    float ApI[9], inv[9];
+    for (int i = 0; i < 9; ++i) ApI[i] = S.JtJ[i];
+    ApI[0] = S.JtJ[0] + S.u; ApI[4] = S.JtJ[4] + S.u; ApI[8] = S.JtJ[8] + S.u;           // :167
+    rbv_inv3(ApI, inv);
+    const float g[3] = {S.JtF[0] * -1.0f, S.JtF[1] * -1.0f, S.JtF[2] * -1.0f};
+    for (int r = 0; r < 3; ++r) {                                                        // :168
+      float acc = 0.0f;
+      for (int j = 0; j < 3; ++j) acc += inv[r * 3 + j] * g[j];
+      S.h[r] = acc;
+    }
+    for (int i = 0; i < 3; ++i) S.vnew[i] = S.vel[i] + S.h[i];                           // :169
+  } else {
+    rbv_inv3(S.JtJ, S.Rvel);                                                             // :185
+  }
+}
+
+// tryVel, reduction part: one block per lane. (1) residual rule incl. the reference's carried `fi` (see DESIGN.md:
+// an in-image unmatched keyline stores |fi| of the most recent matched keyline, 0 before the first match);
+// (2) the ten sums; (3) LM step or plain output.
+__global__ void __launch_bounds__(1024) k_tryvel_reduce(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ prod,
+                                                        const float* __restrict__ fiabs, LMState* lm, float* lane_out,
+                                                        const float* __restrict__ vel_ptr, int vel_stride, int lm_call, int ordered,
+                                                        const __grid_constant__ DevParams P) {
+  __shared__ double sm[32 * 10];
+  __shared__ double result[10];
+  __shared__ float warp_val[32];
+  __shared__ int warp_has[32];
+  __shared__ float carry_val;
+  __shared__ int carry_has;
+  const int b = blockIdx.x, n = count_o[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const size_t base = (size_t)b * P.kmax;
+  const size_t ps = (size_t)P.lanes * P.kmax;
+  if (t == 0) { carry_val = 0.0f; carry_has = 0; }
+  __syncthreads();
+  // (1) "last matched |fi|" propagation in keyline order
+  for (int i0 = 0; i0 < n; i0 += 1024) {
+    const int idx = i0 + t;
+    const float code = (idx < n) ? fiabs[base + idx] : -2.0f;
+    int has = code >= 0.0f;
+    float val = has ? code : 0.0f;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int h2 = __shfl_up_sync(0xFFFFFFFFu, has, off);
+      const float v2 = __shfl_up_sync(0xFFFFFFFFu, val, off);
+      if (lane >= off && !has) { has = h2; val = v2; }
+    }
+    if (lane == 31) { warp_has[warp] = has; warp_val[warp] = val; }
+    __syncthreads();
+    if (!has) {
+      for (int w = warp - 1; w >= 0; --w)
+        if (warp_has[w]) { has = 1; val = warp_val[w]; break; }
+      if (!has && carry_has) { has = 1; val = carry_val; }
+    }
+    if (idx < n && code >= -1.5f) Ko.residual[base + idx] = has ? val : 0.0f;            // core.cpp:141
+    __syncthreads();
+    if (t == 1023) { if (has) { carry_has = 1; carry_val = val; } }
+    __syncthreads();
+  }
+  // (2) sums
+  if (ordered) {
+    if (warp == 0 && lane < 10) {   // one lane per accumulator: same instruction stream, ten independent serial chains
+      const float* p = prod + lane * ps + base;
+      float s = 0.0f;
+      int i = 0;
+      for (; i + 8 <= n; i += 8) {
+        const float4 a = *reinterpret_cast<const float4*>(p + i);
+        const float4 c = *reinterpret_cast<const float4*>(p + i + 4);
+        s += a.x; s += a.y; s += a.z; s += a.w; s += c.x; s += c.y; s += c.z; s += c.w;
+      }
+      for (; i < n; ++i) s += p[i];
+      result[lane] = (double)s;
+    }
+    __syncthreads();
+  } else {
+    double acc[10];
+#pragma unroll
+    for (int a = 0; a < 10; ++a) acc[a] = 0.0;
+    for (int i = t; i < n; i += 1024) {
+#pragma unroll
+      for (int a = 0; a < 10; ++a) acc[a] += (double)prod[a * ps + base + i];
+    }
+    block_sum_fixed<10>(acc, sm, result);
+  }
+  // (3)
+  if (t == 0) {
+    float JtJ[9], JtF[3];
+    const float score = (float)result[0];
+    JtJ[0] = (float)result[1]; JtJ[4] = (float)result[2]; JtJ[8] = (float)result[3];
+    JtJ[1] = JtJ[3] = (float)result[4]; JtJ[2] = JtJ[6] = (float)result[5]; JtJ[5] = JtJ[7] = (float)result[6];
+    JtF[0] = (float)result[7]; JtF[1] = (float)result[8]; JtF[2] = (float)result[9];
+    if (lm_call >= 0) {
+      float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
+      lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
+    }
+    float* out = lane_out + (size_t)b * OUT_STRIDE;
+    for (int i = 0; i < 9; ++i) out[OUT_JTJ + i] = JtJ[i];
+    for (int i = 0; i < 3; ++i) out[OUT_JTF + i] = JtF[i];
+    out[OUT_SCORE] = score;
+  }
+}
+
+// lm_call = -1: single evaluation at lane_in vel / sigma_rho_min; 0: first LM call at lm.vel; >= 1: at lm.vnew
+int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
+  const DevParams& P = c->P;
+  if (!c->field_map) { rbv_set_error("tryVel before buildDistanceField"); return RBV_ERR_STATE; }
+  const float* vel_ptr; int vel_stride; const float* sr_ptr; int sr_stride;
+  const int lm_floats = (int)(sizeof(LMState) / sizeof(float));
+  if (lm_call < 0) {
+    vel_ptr = c->lane_in + IN_VEL; vel_stride = IN_STRIDE; sr_ptr = c->lane_in + IN_SRMIN; sr_stride = IN_STRIDE;
+  } else {
+    const float* lmf = reinterpret_cast<const float*>(c->lm);
+    vel_ptr = lmf + (lm_call == 0 ? offsetof(LMState, vel) : offsetof(LMState, vnew)) / sizeof(float);
+    vel_stride = lm_floats;
+    sr_ptr = lmf + offsetof(LMState, sigma_rho_min) / sizeof(float);
+    sr_stride = lm_floats;
+  }
+  k_tryvel_eval<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(
+      map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
+  k_tryvel_reduce<<<P.lanes, 1024, 0, c->stream>>>(map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride,
+                                                    lm_call, c->reduce_mode == RBV_REDUCE_ORDERED, P);
+  c->launches += 2;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// forwardMatch (edge_map.cpp:73-99). The sequential loop visits old keylines in index order and lets a later one
+// overwrite the target unless the target already holds a larger rho; the count includes overwrites. Parallel form:
+// (a) every old keyline with a forward match pushes itself on a per-target list (atomicExch), (b) one thread per
+// target replays its (short) list in ascending index order with the reference's rule, so result and count are exact.
+__global__ void k_fwd_link(KeylineSoA Ko, const int* __restrict__ count_o, int* __restrict__ head, int* __restrict__ next, int kmax) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count_o[b]) return;
+  const size_t base = (size_t)b * kmax;
+  const int f = Ko.match_fwd[base + idx];
+  if (f < 0) return;
+  next[base + idx] = atomicExch(&head[base + f], idx);
+}
+
+__global__ void k_fwd_resolve(KeylineSoA Ko, KeylineSoA Kn, const int* __restrict__ count_n, const int* __restrict__ head,
+                              const int* __restrict__ next, int* __restrict__ lane_cnt, int kmax) {
+  const int b = blockIdx.y, f = blockIdx.x * blockDim.x + threadIdx.x;
+  int writes = 0;
+  if (f < count_n[b]) {
+    const size_t base = (size_t)b * kmax;
+    const int h = head[base + f];
+    if (h >= 0) {
+      int match_id = Kn.match_id[base + f];
+      float rho = Kn.rho[base + f];
+      int last = -1, winner = -1;
+      for (;;) {
+        int cur = 0x7FFFFFFF;                       // smallest list entry > last
+        for (int e = h; e >= 0; e = next[base + e])
+          if (e > last && e < cur) cur = e;
+        if (cur == 0x7FFFFFFF) break;
+        last = cur;
+        const float krho = Ko.rho[base + cur];
+        if (match_id >= 0 && rho > krho) continue;                                       // :83
+        rho = krho; match_id = cur; winner = cur;
+        ++writes;
+      }
+      if (winner >= 0) {                                                                 // :86-93
+        const size_t w = base + winner, o = base + f;
+        Kn.rho[o] = rho;
+        Kn.srho[o] = Ko.srho[w];
+        Kn.matches[o] = Ko.matches[w] + 1u;
+        Kn.match_id[o] = winner;
+        Kn.match_pos_img[o] = Ko.pos_img[w];
+        Kn.match_grad[o] = Ko.grad[w];
+        Kn.match_gnorm[o] = Ko.gnorm[w];
+        Kn.match_kf[o] = Ko.match_kf[w];
+      }
+    }
+  }
+  // count: warp-aggregated integer atomics (order independent)
+#pragma unroll
+  for (int off = 16; off; off >>= 1) writes += __shfl_down_sync(0xFFFFFFFFu, writes, off);
+  if ((threadIdx.x & 31) == 0 && writes) atomicAdd(&lane_cnt[b * CNT_STRIDE + CNT_FWD], writes);
+}
+
+__global__ void k_zero_cnt(int* lane_cnt, int slot, unsigned long long* probes) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  lane_cnt[b * CNT_STRIDE + slot] = 0;
+  if (slot == CNT_DIR) { lane_cnt[b * CNT_STRIDE + CNT_KF] = 0; if (probes) probes[b] = 0ull; }
+}
+
+int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
+  const DevParams& P = c->P;
+  RBV_CUDA(cudaMemsetAsync(c->fwd_head, 0xFF, sizeof(int) * (size_t)P.lanes * P.kmax, c->stream));
+  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_FWD, nullptr);
+  dim3 g((P.keylines_max + 255) / 256, P.lanes);
+  k_fwd_link<<<g, 256, 0, c->stream>>>(old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax);
+  k_fwd_resolve<<<g, 256, 0, c->stream>>>(old_map->k, new_map->k, new_map->count, c->fwd_head, c->fwd_next, c->lane_cnt, P.kmax);
+  c->launches += 3;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// extRotVel rows (core.cpp:202-236): Phi_j (6) and Y_j after the division by s_y*weight; zeros for unmatched keylines.
+__global__ void __launch_bounds__(256) k_extrot_rows(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr,
+                                                     int vel_stride, float* __restrict__ rowsout, const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * P.kmax + idx;
+  const size_t ps = (size_t)P.lanes * P.kmax;
+  float phi[7];
+#pragma unroll
+  for (int a = 0; a < 7; ++a) phi[a] = 0.0f;
+  if (K.match_id[o] >= 0) {
+    const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+    const float fm = P.fm;
+    const float2 g = K.grad[o];
+    const float gn = K.gnorm[o];
+    const float ux = g.x / gn, uy = g.y / gn;                                            // :207-208
+    const float rho_t = (float)(1.0 / (1.0 / (double)K.rho[o] + (double)v2));            // :210
+    const float2 m = K.match_pos_img[o];
+    const float qtx = m.x + rho_t * (v0 * fm - v2 * m.x);                                // :211-212
+    const float qty = m.y + rho_t * (v1 * fm - v2 * m.y);
+    const float2 q = K.pos_img[o];
+    phi[0] = ux * rho_t * fm;                                                            // :217-222
+    phi[1] = uy * rho_t * fm;
+    phi[2] = ux * (-rho_t * q.x) + uy * (-rho_t * q.y);
+    phi[3] = -ux * q.x * q.y / fm - uy * (fm + q.y * q.y / fm);
+    phi[4] = uy * q.x * q.y / fm + ux * (fm + q.x * q.x / fm);
+    phi[5] = -ux * q.y + uy * q.x;
+    float y = ux * (q.x - qtx) + uy * (q.y - qty);                                       // :224
+    const float dqvel = ux * (v0 * fm - v2 * m.x) + uy * (v1 * fm - v2 * m.y);           // :226
+    const float sr = K.srho[o];
+    const float sy = sqrtf(sr * sr * dqvel * dqvel + P.pixel_uncertainty * P.pixel_uncertainty);   // :227
+    float w = 1.0f;
+    if (fabsf(y) > P.reweight_distance) w = fabsf(y) / P.reweight_distance;              // :230
+    const float dv = sy * w;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) phi[a] /= dv;                                            // :232
+    y /= dv;                                                                             // :233
+    phi[6] = y;
+  }
+#pragma unroll
+  for (int a = 0; a < 7; ++a) rowsout[a * ps + o] = phi[a];
+}
+
+// symmetric 6x6 pseudo-inverse solve standing in for TooN::SVD<6,6,float>(JtJ).backsub(JtF) (core.cpp:247-248 ->
+// LAPACK sgesvd_, un-vendored): cyclic Jacobi eigen-decomposition in FP64, inverse zeroed when s_i*1e9 <= s_max
+// (TooN SVD.h:37,266-274). Same statement order as oracle/rebvio_oracle.c:orc_solve6.
+__device__ void rbv_solve6(const float* A36, const float* b6, float* x6) {
+  double A[6][6], V[6][6];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { A[i][j] = 0.5 * ((double)A36[i * 6 + j] + (double)A36[j * 6 + i]); V[i][j] = (i == j) ? 1.0 : 0.0; }
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    double off = 0.0;
+    for (int p = 0; p < 6; ++p) for (int q = p + 1; q < 6; ++q) off += A[p][q] * A[p][q];
+    if (off == 0.0) break;
+    for (int p = 0; p < 6; ++p)
+      for (int q = p + 1; q < 6; ++q) {
+        if (A[p][q] == 0.0) continue;
+        const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
+        for (int k = 0; k < 6; ++k) { const double akp = A[k][p], akq = A[k][q]; A[k][p] = cs * akp - sn * akq; A[k][q] = sn * akp + cs * akq; }
+        for (int k = 0; k < 6; ++k) { const double apk = A[p][k], aqk = A[q][k]; A[p][k] = cs * apk - sn * aqk; A[q][k] = sn * apk + cs * aqk; }
+        for (int k = 0; k < 6; ++k) { const double vkp = V[k][p], vkq = V[k][q]; V[k][p] = cs * vkp - sn * vkq; V[k][q] = sn * vkp + cs * vkq; }
+      }
+  }
+  double smax = 0.0;
+  for (int i = 0; i < 6; ++i) if (fabs(A[i][i]) > smax) smax = fabs(A[i][i]);
+  double x[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < 6; ++i) {
+    const double s = fabs(A[i][i]);
+    if (s * 1e9 <= smax) continue;
+    double proj = 0.0;
+    for (int k = 0; k < 6; ++k) proj += V[k][i] * (double)b6[k];
+    proj /= A[i][i];
+    for (int k = 0; k < 6; ++k) x[k] += V[k][i] * proj;
+  }
+  for (int k = 0; k < 6; ++k) x6[k] = (float)x[k];
+}
+
+// 27 accumulators: 21 upper-triangle entries of Phi^T Phi in (a,b) a<=b row-major order, then 6 of Phi^T Y.
+__constant__ signed char c_pair_a[27] = {0,0,0,0,0,0, 1,1,1,1,1, 2,2,2,2, 3,3,3, 4,4, 5, 0,1,2,3,4,5};
+__constant__ signed char c_pair_b[27] = {0,1,2,3,4,5, 1,2,3,4,5, 2,3,4,5, 3,4,5, 4,5, 5, 6,6,6,6,6,6};
+
+__global__ void __launch_bounds__(512) k_extrot_reduce(const int* __restrict__ count, const float* __restrict__ rowsin, float* lane_out,
+                                                        int ordered, const __grid_constant__ DevParams P) {
+  __shared__ double sm[32 * 27];
+  __shared__ double result[27];
+  const int b = blockIdx.x, n = count[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const size_t base = (size_t)b * P.kmax;
+  const size_t ps = (size_t)P.lanes * P.kmax;
+  if (ordered) {
+    if (warp == 0 && lane < 27) {                                                        // sequential dot, operators.hh:200-208
+      const float* pa = rowsin + c_pair_a[lane] * ps + base;
+      const float* pb = rowsin + c_pair_b[lane] * ps + base;
+      float s = 0.0f;
+      int i = 0;
+      for (; i + 4 <= n; i += 4) {
+        const float4 x = *reinterpret_cast<const float4*>(pa + i);
+        const float4 y = *reinterpret_cast<const float4*>(pb + i);
+        s += x.x * y.x; s += x.y * y.y; s += x.z * y.z; s += x.w * y.w;
+      }
+      for (; i < n; ++i) s += pa[i] * pb[i];
+      result[lane] = (double)s;
+    }
+    __syncthreads();
+  } else {
+    double acc[27];
+#pragma unroll
+    for (int a = 0; a < 27; ++a) acc[a] = 0.0;
+    for (int i = t; i < n; i += 512) {
+      float r[7];
+#pragma unroll
+      for (int a = 0; a < 7; ++a) r[a] = rowsin[a * ps + base + i];
+      int k = 0;
+#pragma unroll
+      for (int a = 0; a < 6; ++a)
+#pragma unroll
+        for (int q = a; q < 6; ++q) acc[k++] += (double)(r[a] * r[q]);
+#pragma unroll
+      for (int a = 0; a < 6; ++a) acc[21 + a] += (double)(r[a] * r[6]);
+    }
+    block_sum_fixed<27>(acc, sm, result);
+  }
+  if (t == 0) {
+    float Wx[36], JtF[6], X[6];
+    int k = 0;
+    for (int a = 0; a < 6; ++a)
+      for (int q = a; q < 6; ++q) { Wx[a * 6 + q] = (float)result[k]; Wx[q * 6 + a] = (float)result[k]; ++k; }
+    for (int a = 0; a < 6; ++a) JtF[a] = (float)result[21 + a];
+    rbv_solve6(Wx, JtF, X);
+    float* out = lane_out + (size_t)b * OUT_STRIDE;
+    int ok = 1;
+    for (int i = 0; i < 36; ++i) out[OUT_WX + i] = Wx[i];                               // _Wx = JtJ, :249
+    for (int i = 0; i < 6; ++i) { out[OUT_X + i] = X[i]; if (X[i] != X[i]) ok = 0; }    // :251-256
+    out[OUT_OK] = (float)ok;
+  }
+}
+
+int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
+  const DevParams& P = c->P;
+  const float* vel_ptr = vel_from_lm ? reinterpret_cast<const float*>(c->lm) + offsetof(LMState, vel) / sizeof(float) : c->lane_in + IN_VEL;
+  const int vel_stride = vel_from_lm ? (int)(sizeof(LMState) / sizeof(float)) : IN_STRIDE;
+  k_extrot_rows<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
+  k_extrot_reduce<<<P.lanes, 512, 0, c->stream>>>(new_map->count, c->prod, c->lane_out, c->reduce_mode == RBV_REDUCE_ORDERED, P);
+  c->launches += 2;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// directedMatch + searchMatch (edge_map.cpp:101-218): every new keyline walks its epipolar segment in the OLD map's
+// pixel->id mask. Independent per keyline (the loop only mutates the querying keyline), so one thread each.
+__global__ void __launch_bounds__(256) k_directed(KeylineSoA Kn, const int* __restrict__ count_n, KeylineSoA Ko, const int* __restrict__ mask_o,
+                                                  const float* __restrict__ lane_in, int* __restrict__ lane_cnt,
+                                                  unsigned long long* __restrict__ probes, const __grid_constant__ DevParams P) {
+  __shared__ float s_vel[3], s_Rvel[9];
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const float* in = lane_in + (size_t)b * IN_STRIDE;
+  const float* Rback = in + IN_RBACK;
+  if (threadIdx.x == 0) {                                                                // :193-194
+    const float* vel_in = in + IN_VEL;
+    const float* Rv = in + IN_RVEL;
+    float tmp[9];
+    for (int r = 0; r < 3; ++r) { float acc = 0.0f; for (int j = 0; j < 3; ++j) acc += Rback[r * 3 + j] * vel_in[j]; s_vel[r] = acc; }
+    for (int r = 0; r < 3; ++r) for (int q = 0; q < 3; ++q) { float acc = 0.0f; for (int j = 0; j < 3; ++j) acc += Rback[r * 3 + j] * Rv[j * 3 + q]; tmp[r * 3 + q] = acc; }
+    for (int r = 0; r < 3; ++r) for (int q = 0; q < 3; ++q) { float acc = 0.0f; for (int j = 0; j < 3; ++j) acc += tmp[r * 3 + j] * Rback[q * 3 + j]; s_Rvel[r * 3 + q] = acc; }
+  }
+  __syncthreads();
+  int hit = -1, nprobe = 0;
+  const size_t base = (size_t)b * P.kmax;
+  if (idx < count_n[b]) {
+    const size_t o = base + idx;
+    const float fm = P.fm, pum = P.pixel_uncertainty_match, max_radius = in[IN_MAXRADIUS];
+    const float2 pi = Kn.pos_img[o], g = Kn.grad[o];
+    const float gn = Kn.gnorm[o], k_sr = Kn.srho[o];
+    float pm[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {                                                        // :106
+      float acc = 0.0f;
+      acc += Rback[r * 3 + 0] * pi.x; acc += Rback[r * 3 + 1] * pi.y; acc += Rback[r * 3 + 2] * fm;
+      pm[r] = acc;
+    }
+    const float pmx = pm[0] * fm / pm[2], pmy = pm[1] * fm / pm[2];                      // :107-108
+    const float k_rho = Kn.rho[o] * fm / pm[2];                                          // :109
+    const float pi0x = pmx + P.cx, pi0y = pmy + P.cy;
+    float tx = -(s_vel[0] * fm - s_vel[2] * pmx), ty = -(s_vel[1] * fm - s_vel[2] * pmy);   // :114-115
+    float norm_t = sqrtf(tx * tx + ty * ty);
+    const float dr[3] = {fm, fm, -(pmx + pmy)};                                          // :118
+    float row[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) { float acc = 0.0f; for (int j = 0; j < 3; ++j) acc += dr[j] * s_Rvel[j * 3 + q]; row[q] = acc; }
+    float sigma2_t = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) sigma2_t += row[j] * dr[j];                              // :119
+    float dq_min, dq_max, dq_rho;
+    int t_steps;
+    if ((double)norm_t > 1e-6) {                                                         // :126
+      tx /= norm_t; ty /= norm_t;
+      dq_rho = norm_t * k_rho;
+      const float lo = norm_t * (k_rho - k_sr), hi = norm_t * (k_rho + k_sr);
+      dq_min = (0.0f < lo ? lo : 0.0f) - pum;                                            // std::max(0, lo), :130
+      dq_max = (hi < max_radius ? hi : max_radius) + pum;                                // std::min(max_radius, hi), :131
+      if (dq_rho > dq_max) {
+        dq_rho = (float)(0.5 * (double)(dq_max + dq_min));                               // :133
+        t_steps = rbv_d2i((double)dq_rho + 0.5);
+      } else {
+        const float a = dq_max - dq_rho, c2 = dq_rho - dq_min;
+        t_steps = rbv_f2i(a < c2 ? c2 : a);                                              // :136
+      }
+    } else {                                                                             // :138-149
+      tx = g.x; ty = g.y;
+      norm_t = gn;
+      tx /= norm_t; ty /= norm_t;
+      norm_t = 1.0f;
+      dq_min = -max_radius - pum;
+      dq_max = max_radius + pum;
+      dq_rho = 0.0f;
+      t_steps = rbv_f2i(dq_max);
+    }
+    float tn = dq_rho, tp = dq_rho + 1.0f;
+    const int* m = mask_o + (size_t)b * P.npix;
+    for (int ti = 0; ti < t_steps && hit < 0; ++ti, tp += 1.0f, tn -= 1.0f) {
+#pragma unroll
+      for (int side = 0; side < 2; ++side) {
+        if (hit >= 0) break;
+        float t;
+        if (side) { t = tp; if (t > dq_max) continue; }
+        else { t = tn; if (t < dq_min) continue; }
+        const int pix = rbv_pixel_index(P.rows, P.cols, ty * t + pi0y, tx * t + pi0x);   // :164
+        if (pix < 0) continue;
+        ++nprobe;
+        const int id = m[pix];
+        if (id < 0) continue;
+        const size_t oo = base + id;
+        const float2 og = Ko.grad[oo];
+        const float ogn = Ko.gnorm[oo];
+        const float cang = (og.x * g.x + og.y * g.y) / (ogn * gn);                       // :171
+        if (cang < P.cang_min_edge || fabs((double)(ogn / gn) - 1.0) > (double)P.match_threshold_norm) continue;   // :172
+        const float osr = Ko.srho[oo], orho = Ko.rho[oo];
+        const float v_rho_dr = (pum * pum + osr * osr * norm_t * norm_t + sigma2_t * orho * orho);   // :174
+        if ((t - norm_t * orho) * (t - norm_t * orho) > v_rho_dr) continue;              // :175
+        hit = id;
+      }
+    }
+    if (hit >= 0) {                                                                      // :202-210
+      const size_t oo = base + hit;
+      Kn.rho[o] = Ko.rho[oo];
+      Kn.srho[o] = Ko.srho[oo];
+      Kn.match_id[o] = hit;
+      Kn.matches[o] = Ko.matches[oo] + 1u;
+      Kn.match_pos_img[o] = Ko.pos_img[oo];
+      Kn.match_grad[o] = Ko.grad[oo];
+      Kn.match_gnorm[o] = Ko.gnorm[oo];
+      Kn.match_kf[o] = Ko.match_kf[oo];
+    }
+  }
+  const unsigned full = 0xFFFFFFFFu;
+  const int kf = (hit >= 0 && Ko.match_kf[base + hit] >= 0) ? 1 : 0;                     // :212
+  const unsigned mhit = __ballot_sync(full, hit >= 0), mkf = __ballot_sync(full, kf);
+#pragma unroll
+  for (int off = 16; off; off >>= 1) nprobe += __shfl_down_sync(full, nprobe, off);
+  if ((threadIdx.x & 31) == 0) {
+    if (mhit) atomicAdd(&lane_cnt[b * CNT_STRIDE + CNT_DIR], __popc(mhit));
+    if (mkf) atomicAdd(&lane_cnt[b * CNT_STRIDE + CNT_KF], __popc(mkf));
+    if (nprobe) atomicAdd(&probes[b], (unsigned long long)nprobe);
+  }
+}
+
+int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map) {
+  const DevParams& P = c->P;
+  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_DIR, c->probes);
+  k_directed<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(new_map->k, new_map->count, old_map->k, old_map->mask,
+                                                                                 c->lane_in, c->lane_cnt, c->probes, P);
+  c->launches += 2;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// regularize1Iter (edge_map.cpp:220-259): two phases like the reference (evaluate everything, then write).
+__global__ void __launch_bounds__(256) k_reg_eval(KeylineSoA K, const int* __restrict__ count, float* __restrict__ reg_r, float* __restrict__ reg_s,
+                                                  int* __restrict__ reg_set, int* __restrict__ lane_cnt, const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  int set = 0;
+  const size_t base = (size_t)b * P.kmax;
+  if (idx < count[b]) {
+    const size_t o = base + idx;
+    const int in = K.id_next[o], ip = K.id_prev[o];
+    if (in >= 0 && ip >= 0) {
+      const size_t on = base + in, op = base + ip;
+      const float rn = K.rho[on], rp = K.rho[op], sn = K.srho[on], sp = K.srho[op];
+      if (!((rn - rp) * (rn - rp) > (sn * sn + sp * sp))) {                              // :235
+        const float2 gn = K.grad[on], gp = K.grad[op];
+        float alpha = (gn.x * gp.x + gn.y * gp.y) / (K.gnorm[on] * K.gnorm[op]);         // :238
+        const float thr = P.regularization_threshold;
+        if (!(alpha < thr)) {                                                            // :239
+          alpha = (float)(((double)(alpha - thr)) / (1.0 - (double)thr));                // :241
+          alpha = (float)((double)alpha / ((double)(fabsf(rn - rp) / (sn + sp)) + 1.0)); // :242
+          const float r0 = K.rho[o], s0 = K.srho[o];
+          const float wr = (float)(1.0 / (double)(s0 * s0));                             // :243
+          const float wrn = alpha / (sn * sn);
+          const float wrp = alpha / (sp * sp);
+          reg_r[o] = (r0 * wr + rn * wrn + rp * wrp) / (wr + wrn + wrp);                 // :247-248
+          reg_s[o] = (s0 * wr + sn * wrn + sp * wrp) / (wr + wrn + wrp);
+          set = 1;
+        }
+      }
+    }
+    reg_set[o] = set;
+  }
+  const unsigned m = __ballot_sync(0xFFFFFFFFu, set);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(&lane_cnt[b * CNT_STRIDE + CNT_REG], __popc(m));
+}
+
+__global__ void k_reg_apply(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ reg_r, const float* __restrict__ reg_s,
+                            const int* __restrict__ reg_set, int kmax) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * kmax + idx;
+  if (reg_set[o]) { K.rho[o] = reg_r[o]; K.srho[o] = reg_s[o]; }                         // :252-257
+}
+
+int tr_regularize(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  dim3 g((P.keylines_max + 255) / 256, P.lanes);
+  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_REG, nullptr);
+  k_reg_eval<<<g, 256, 0, c->stream>>>(map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, P);
+  k_reg_apply<<<g, 256, 0, c->stream>>>(map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, P.kmax);
+  c->launches += 3;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// updateInverseDepth + updateInverseDepthARLU (core.cpp:417-456): scalar EKF per matched keyline of the field map
+__global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in,
+                                                const __grid_constant__ DevParams P) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * P.kmax + idx;
+  if (K.match_id[o] < 0) return;
+  const float* vel = lane_in + (size_t)b * IN_STRIDE + IN_VEL;
+  const float v0 = vel[0], v1 = vel[1], v2 = vel[2], fm = P.fm;
+  const float2 q = K.pos_img[o], q0 = K.match_pos_img[o], mg = K.match_grad[o];
+  const float mgn = K.match_gnorm[o];
+  float rho = K.rho[o], srho = K.srho[o];
+  float v_rho = srho * srho;                                                             // :429
+  const float ux = mg.x / mgn, uy = mg.y / mgn;
+  const float Y = ux * (q.x - q0.x) + uy * (q.y - q0.y);                                 // :432
+  const float H = ux * (v0 * fm - v2 * q0.x) + uy * (v1 * fm - v2 * q0.y);               // :433
+  const float rho_p = (float)(1.0 / (1.0 / (double)rho + (double)v2));                   // :434
+  float F = (float)(1.0 / (1.0 + (double)(rho * v2)));                                   // :435
+  F *= F;
+  const float qa = P.reshape_q_abs, pu = P.pixel_uncertainty;
+  const float p_p = F * v_rho * F + qa * qa;                                             // :437
+  const float e = Y - H * rho_p;
+  const float S = H * p_p * H + pu * pu;                                                 // :440
+  const float Kg = (float)((double)(p_p * H) * (1.0 / (double)S));                       // :441
+  rho = rho_p + Kg * e;                                                                  // :443
+  v_rho = (float)((1.0 - (double)(Kg * H)) * (double)p_p);                               // :444
+  srho = sqrtf(v_rho);
+  if (rho < RBV_RHO_MIN) {                                                               // :446-455
+    srho += RBV_RHO_MIN - rho;
+    rho = RBV_RHO_MIN;
+  } else if (rho > RBV_RHO_MAX) {
+    rho = RBV_RHO_MAX;
+  } else if (isnan(rho) || isnan(srho) || isinf(rho) || isinf(srho)) {
+    rho = RBV_RHO_INIT;
+    srho = RBV_RHO_MAX;
+  }
+  K.rho[o] = rho;
+  K.srho[o] = srho;
+}
+
+int tr_kalman(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  k_kalman<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(map->k, map->count, c->lane_in, P);
+  ++c->launches;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
