@@ -515,12 +515,13 @@ float orc_quantile(orc_map* m, float percentile, int num_bins) {
 
 /* Core::tryVel + calculatefJ + testfk, core.cpp:39-148.
  *
- * AS-COMPILED BEHAVIOUR KEPT: `fi` (core.cpp:122) is only assigned on the matched path of calculatefJ (:67) but
- * `_residuals[idx] = std::fabs(fi)` (:141) runs for every in-image keyline. In both reference builds the stack
- * slot keeps the value of the most recent MATCHED keyline of the same call (probe: 6084 of 6084 unmatched
- * keylines), and before the first match it holds stack garbage that is far below reweight_distance (4.6e-41
- * in the -O2 build, 0 in the -O3 build), i.e. weight 1 in the next call. The restatement carries the last matched
- * fi in index order and uses 0 before the first match; tests compare residuals from the first match onwards. */
+ * UNINITIALISED READ IN THE REFERENCE, MADE DETERMINISTIC: `fi` (core.cpp:122) is only assigned on the matched path
+ * of calculatefJ (:67) but `_residuals[idx] = std::fabs(fi)` (:141) runs for every in-image keyline. In the compiled
+ * reference the stack slot keeps the value of the most recent MATCHED keyline of the same call; before the first match
+ * of a call it holds stack garbage (observed: the previous call's last |fi|, pointer halves, LM temporaries). The
+ * restatement carries the last matched fi in index order and uses 0 before the first match of every call, which is
+ * bit-identical to the reference run with a zero-filled stack (oracle/ref_harness.cpp: scrub_stack before each direct
+ * Core::tryVel call) -- that is how tests/test_oracle_vs_ref.py pins it. */
 float orc_try_vel(orc_ctx* c, orc_map* m, const float* vel, float sigma_rho_min, float* residuals, float* JtJ9, float* JtF3) {
   const float fm = c->cam.fm, cx = c->cam.cx, cy = c->cam.cy, range = c->core.search_range, rw = c->core.reweight_distance;
   const int rows = c->cam.rows, cols = c->cam.cols;

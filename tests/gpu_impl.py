@@ -25,7 +25,7 @@ class GpuImpl:
     def _same(self, arr, what):
         arr = np.asarray(arr)
         for b in range(self.lanes):
-            assert np.array_equal(arr[b].view(np.uint8), arr[self.lane].view(np.uint8)), f"lane {b} differs in {what}"
+            assert np.ascontiguousarray(arr[b]).tobytes() == np.ascontiguousarray(arr[self.lane]).tobytes(), f"lane {b} differs in {what}"
         return arr[self.lane]
 
     # maps
