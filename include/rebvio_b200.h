@@ -124,6 +124,18 @@ int rbv_set_stream(rbv_ctx* ctx, void* cuda_stream);
 /* number of kernels this context has launched since rbv_create (bench.py's gpu_launches) */
 unsigned long long rbv_launch_count(const rbv_ctx* ctx);
 
+/* per-kernel accounting. Every device operation of this library is one of rbv_kernel_count() named kernels.
+ * rbv_profile_set: mode -1 = off (default), -2 = bracket every launch with CUDA events on the context's stream,
+ * k >= 0 = bracket only launches of kernel k (cheap enough to leave on inside a timed region).
+ * rbv_profile_read: summed event time of the bracketed launches of kernel `kid`, how many were bracketed, and how
+ * many launches of it happened since rbv_profile_reset (synchronises the stream). */
+int rbv_kernel_count(void);
+const char* rbv_kernel_name(int kid);
+int rbv_profile_set(rbv_ctx* ctx, int mode);
+int rbv_profile_reset(rbv_ctx* ctx);
+int rbv_profile_read(rbv_ctx* ctx, int kid, double* total_ms, unsigned long long* timed_launches,
+                     unsigned long long* launches);
+
 /* allocate / free a B-lane map (replaces std::make_shared<EdgeMap>, edge_detector.cpp:50). */
 int rbv_map_create(rbv_ctx* ctx, rbv_map** out);
 void rbv_map_release(rbv_ctx* ctx, rbv_map* map);

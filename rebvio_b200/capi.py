@@ -64,6 +64,11 @@ _SIG = {
     "rbv_lanes": (C.c_int, [vp]),
     "rbv_set_stream": (C.c_int, [vp, vp]),
     "rbv_launch_count": (C.c_ulonglong, [vp]),
+    "rbv_kernel_count": (C.c_int, []),
+    "rbv_kernel_name": (C.c_char_p, [C.c_int]),
+    "rbv_profile_set": (C.c_int, [vp, C.c_int]),
+    "rbv_profile_reset": (C.c_int, [vp]),
+    "rbv_profile_read": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "rbv_map_create": (C.c_int, [vp, C.POINTER(vp)]),
     "rbv_map_release": (None, [vp, vp]),
     "rbv_detect": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),

@@ -82,6 +82,95 @@ static void plane_fit_pinv(float* pinv75) {
     }
 }
 
+// ---- per-kernel launch accounting and CUDA-event timing ------------------------------------------------------
+static const char* const g_kernel_names[KID_COUNT] = {
+#define X(n) #n,
+    RBV_KERNEL_LIST(X)
+#undef X
+};
+#define PROF_PAIRS 4096
+struct ProfState {
+  cudaEvent_t ev[PROF_PAIRS][2];
+  int kid[PROF_PAIRS];
+  int used, created;
+  double ms[KID_COUNT];
+  unsigned long long n[KID_COUNT];
+};
+static void prof_drain(rbv_ctx* c) {
+  ProfState* p = static_cast<ProfState*>(c->prof);
+  if (!p || !p->used) return;
+  cudaEventSynchronize(p->ev[p->used - 1][1]);
+  for (int i = 0; i < p->used; ++i) {
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, p->ev[i][0], p->ev[i][1]) == cudaSuccess) { p->ms[p->kid[i]] += ms; ++p->n[p->kid[i]]; }
+  }
+  p->used = 0;
+}
+void rbv_prof_begin(rbv_ctx* c, int kid) {
+  ++c->launches;
+  ++c->klaunch[kid];
+  if (c->prof_mode == -1 || (c->prof_mode >= 0 && c->prof_mode != kid)) return;
+  ProfState* p = static_cast<ProfState*>(c->prof);
+  if (p->used == PROF_PAIRS) prof_drain(c);
+  if (p->used == p->created) {
+    cudaEventCreate(&p->ev[p->created][0]);
+    cudaEventCreate(&p->ev[p->created][1]);
+    ++p->created;
+  }
+  p->kid[p->used] = kid;
+  cudaEventRecord(p->ev[p->used][0], c->stream);
+}
+void rbv_prof_end(rbv_ctx* c, int kid) {
+  if (c->prof_mode == -1 || (c->prof_mode >= 0 && c->prof_mode != kid)) return;
+  ProfState* p = static_cast<ProfState*>(c->prof);
+  cudaEventRecord(p->ev[p->used][1], c->stream);
+  ++p->used;
+}
+extern "C" int rbv_kernel_count(void) { return KID_COUNT; }
+extern "C" const char* rbv_kernel_name(int kid) { return (kid >= 0 && kid < KID_COUNT) ? g_kernel_names[kid] : ""; }
+extern "C" int rbv_profile_set(rbv_ctx* c, int mode) {
+  if (!c || mode < -2 || mode >= KID_COUNT) return RBV_ERR_ARG;
+  prof_drain(c);
+  if (!c->prof) { ProfState* p = new ProfState(); memset(p, 0, sizeof(*p)); c->prof = p; }
+  c->prof_mode = mode;
+  return RBV_OK;
+}
+extern "C" int rbv_profile_reset(rbv_ctx* c) {
+  if (!c) return RBV_ERR_ARG;
+  prof_drain(c);
+  if (c->prof) { ProfState* p = static_cast<ProfState*>(c->prof); memset(p->ms, 0, sizeof(p->ms)); memset(p->n, 0, sizeof(p->n)); }
+  memset(c->klaunch, 0, sizeof(c->klaunch));
+  return RBV_OK;
+}
+extern "C" int rbv_profile_read(rbv_ctx* c, int kid, double* total_ms, unsigned long long* timed_launches, unsigned long long* launches) {
+  if (!c || kid < 0 || kid >= KID_COUNT) return RBV_ERR_ARG;
+  prof_drain(c);
+  ProfState* p = static_cast<ProfState*>(c->prof);
+  if (total_ms) *total_ms = p ? p->ms[kid] : 0.0;
+  if (timed_launches) *timed_launches = p ? p->n[kid] : 0ull;
+  if (launches) *launches = c->klaunch[kid];
+  return RBV_OK;
+}
+
+__global__ void k_fill(uint4* __restrict__ dst4, unsigned* __restrict__ tail, unsigned value, size_t n4, int ntail) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const uint4 v = make_uint4(value, value, value, value);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) dst4[i] = v;
+  if (blockIdx.x == 0 && (int)threadIdx.x < ntail) tail[threadIdx.x] = value;
+}
+int rbv_fill32(rbv_ctx* c, void* dst, unsigned value, size_t n_words) {
+  if (!n_words) return RBV_OK;
+  if (((uintptr_t)dst & 15) != 0) { rbv_set_error("rbv_fill32: unaligned destination"); return RBV_ERR_ARG; }
+  const size_t n4 = n_words / 4;
+  const int ntail = (int)(n_words - n4 * 4);
+  size_t blocks = (n4 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  RBV_LAUNCH(c, k_fill, ((unsigned)blocks), (256), 0, (uint4*)dst, (unsigned*)dst + n4 * 4, value, n4, ntail);
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
 #define STAGE_SLOTS 16
 struct Stage {  // ring of pinned staging slots for per-call lane inputs
   float* host[STAGE_SLOTS];
@@ -113,6 +202,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   c->cam = *cam; c->det = *det; c->mapc = *map; c->core = *core;
   c->device = device;
   c->reduce_mode = RBV_REDUCE_FAST;
+  c->prof_mode = -1;
   float st[2];
   kovesi_widths(3.56359f, 3, c->widths[0], &st[0]);                       // scale_space.cpp:186
   kovesi_widths((float)(st[0] * 1.2599), 3, c->widths[1], &st[1]);
@@ -191,6 +281,11 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   if (stg) {
     for (int i = 0; i < STAGE_SLOTS; ++i) { cudaFreeHost(stg->host[i]); cudaEventDestroy(stg->ev[i]); }
     delete stg;
+  }
+  if (c->prof) {
+    ProfState* p = static_cast<ProfState*>(c->prof);
+    for (int i = 0; i < p->created; ++i) { cudaEventDestroy(p->ev[i][0]); cudaEventDestroy(p->ev[i][1]); }
+    delete p;
   }
   cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm); cudaFreeHost(c->h_img);
   if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -361,8 +456,7 @@ extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile,
 extern "C" int rbv_reset_residuals(rbv_ctx* c, rbv_map* map) {
   CHECK_CTX(c);
   if (!map) return RBV_ERR_ARG;
-  RBV_CUDA(cudaMemsetAsync(map->k.residual, 0, sizeof(float) * (size_t)c->P.lanes * c->P.kmax, c->stream));   // core.cpp:158
-  return RBV_OK;
+  return rbv_fill32(c, map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax);   // core.cpp:158
 }
 
 extern "C" int rbv_try_vel(rbv_ctx* c, rbv_map* map, const float* vel3, const float* sigma_rho_min, float* JtJ9, float* JtF3, float* score) {
@@ -394,9 +488,8 @@ __global__ void k_lm_init(LMState* lm, const float* lane_in, int lanes) {
 // enqueue Core::minimizeVel (core.cpp:150-189) on the stream: quantile, residual reset, (1 + iterations) tryVel + LM steps
 static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map) {
   TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, 1));
-  RBV_CUDA(cudaMemsetAsync(old_map->k.residual, 0, sizeof(float) * (size_t)c->P.lanes * c->P.kmax, c->stream));
-  k_lm_init<<<(c->P.lanes + 63) / 64, 64, 0, c->stream>>>(c->lm, c->lane_in, c->P.lanes);
-  ++c->launches;
+  TRY(rbv_fill32(c, old_map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax));
+  RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
   for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
   return RBV_OK;
 }
@@ -551,11 +644,10 @@ extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   TRY(tr_directed_match(c, new_map, old_map));
   int* backup = c->rowcount;  // scratch ints, free between detects
   const int nb = (c->P.lanes + 63) / 64;
-  k_gate_min_matches<<<nb, 64, 0, c->stream>>>(backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 0);
+  RBV_LAUNCH(c, k_gate_min_matches, (nb), (64), 0, backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 0);
   TRY(tr_regularize(c, new_map));
   TRY(tr_kalman(c, new_map));
-  k_gate_min_matches<<<nb, 64, 0, c->stream>>>(backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 1);
-  c->launches += 2;
+  RBV_LAUNCH(c, k_gate_min_matches, (nb), (64), 0, backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 1);
   TRY(fetch_cnt(c));
   for (int b = 0; b < c->P.lanes; ++b) {
     if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];

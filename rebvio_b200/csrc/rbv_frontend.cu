@@ -149,28 +149,24 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
   // pass 0: one row prefix per lane, two column/box passes (d = widths[0][0], widths[1][0])
   {
     dim3 g1((rows + 31) / 32, B);
-    k_rowscan<<<g1, 32, 0, c->stream>>>(d_img, c->rowsum, rows, cols, N, N);
-    ++c->launches;
+    RBV_LAUNCH(c, k_rowscan, (g1), (32), 0, d_img, c->rowsum, rows, cols, N, N);
     for (int z = 0; z < 2; ++z) {
       const int d = c->widths[z][0];
       const int W = CB_TPB - (2 * (d / 2) + 1);
       dim3 g2((cols + W - 1) / W, B);
-      k_colbox<<<g2, CB_TPB, 0, c->stream>>>(c->rowsum, c->bufA + (size_t)z * N, rows, cols, N, 2 * N, 1, d, d);
-      ++c->launches;
+      RBV_LAUNCH(c, k_colbox, (g2), (CB_TPB), 0, c->rowsum, c->bufA + (size_t)z * N, rows, cols, N, 2 * N, 1, d, d);
     }
   }
   float* src = c->bufA;
   float* dst = c->bufB;
   for (int p = 1; p < 3; ++p) {
     dim3 g1((rows + 31) / 32, 2 * B);
-    k_rowscan<<<g1, 32, 0, c->stream>>>(src, c->rowsum, rows, cols, N, N);
-    ++c->launches;
+    RBV_LAUNCH(c, k_rowscan, (g1), (32), 0, src, c->rowsum, rows, cols, N, N);
     const int d0 = c->widths[0][p], d1 = c->widths[1][p];
     const int hmax = (d0 > d1 ? d0 : d1) / 2;
     const int W = CB_TPB - (2 * hmax + 1);
     dim3 g2((cols + W - 1) / W, 2 * B);
-    k_colbox<<<g2, CB_TPB, 0, c->stream>>>(c->rowsum, dst, rows, cols, N, N, 2, d0, d1);
-    ++c->launches;
+    RBV_LAUNCH(c, k_colbox, (g2), (CB_TPB), 0, c->rowsum, dst, rows, cols, N, N, 2, d0, d1);
     float* t = src; src = dst; dst = t;
   }
   // after passes 1 and 2 the result is back in bufA
@@ -182,11 +178,10 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {
   const int rows = c->P.rows, cols = c->P.cols;
   const size_t N = (size_t)c->P.npix;
-  k_rowscan<<<dim3((rows + 31) / 32, 1), 32, 0, c->stream>>>(d_in, c->rowsum, rows, cols, N, N);
+  RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 1)), (32), 0, d_in, c->rowsum, rows, cols, N, N);
   const int d = c->widths[scale][pass];
   const int W = CB_TPB - (2 * (d / 2) + 1);
-  k_colbox<<<dim3((cols + W - 1) / W, 1), CB_TPB, 0, c->stream>>>(c->rowsum, d_out, rows, cols, N, N, 1, d, d);
-  c->launches += 2;
+  RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 1)), (CB_TPB), 0, c->rowsum, d_out, rows, cols, N, N, 1, d, d);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -420,14 +415,13 @@ int fe_detect(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   const int B = P.lanes, rows = P.rows, cols = P.cols;
   const int wpr = (cols + 31) / 32;
-  RBV_CUDA(cudaMemsetAsync(c->rowcount, 0, sizeof(int) * (size_t)B * rows, c->stream));
+  { int rc = rbv_fill32(c, c->rowcount, 0u, (size_t)B * rows); if (rc != RBV_OK) return rc; }
   dim3 g1(wpr, (rows + DT_ROWS - 1) / DT_ROWS, B);
-  k_detect_flags<<<g1, dim3(32, DT_ROWS), 0, c->stream>>>(c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, P, wpr);
-  k_detect_scan<<<B, 1024, 0, c->stream>>>(c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
-  k_detect_emit<<<dim3(rows - 4, B), 32, 0, c->stream>>>(c->bufA, c->thr_dev, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
-  k_join<<<dim3((P.kmax + 255) / 256, B), 256, 0, c->stream>>>(map->k, map->count, map->mask, P);
-  k_tune<<<B, 1024, 0, c->stream>>>(map->k, map->count, map->threshold, P.kmax);
-  c->launches += 5;
+  RBV_LAUNCH(c, k_detect_flags, (g1), (dim3(32, DT_ROWS)), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, P, wpr);
+  RBV_LAUNCH(c, k_detect_scan, (B), (1024), 0, c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
+  RBV_LAUNCH(c, k_detect_emit, (dim3(rows - 4, B)), (32), 0, c->bufA, c->thr_dev, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+  RBV_LAUNCH(c, k_join, (dim3((P.kmax + 255) / 256, B)), (256), 0, map->k, map->count, map->mask, P);
+  RBV_LAUNCH(c, k_tune, (B), (1024), 0, map->k, map->count, map->threshold, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -448,8 +442,7 @@ __global__ void k_dog_mag(const float* __restrict__ s0, const float* __restrict_
 int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out) {
   const size_t N = (size_t)c->P.npix;
   const float* s0 = c->bufA + (size_t)(lane * 2) * N;
-  k_dog_mag<<<dim3((c->P.cols + 127) / 128, c->P.rows), 128, 0, c->stream>>>(s0, s0 + N, d_out, c->P.rows, c->P.cols, which);
-  ++c->launches;
+  RBV_LAUNCH(c, k_dog_mag, (dim3((c->P.cols + 127) / 128, c->P.rows)), (128), 0, s0, s0 + N, d_out, c->P.rows, c->P.cols, which);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

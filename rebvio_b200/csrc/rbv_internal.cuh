@@ -124,6 +124,9 @@ struct rbv_ctx {
   float* h_lm;
   float* h_img;     // pinned staging for rbv_detect host frames [B][N]
   unsigned long long launches;  // kernels launched since creation
+  unsigned long long klaunch[32];   // per kernel id
+  int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
+  void* prof;                       // ProfState* (rbv_api.cu)
 };
 
 // lane_in slots
@@ -132,6 +135,30 @@ enum { IN_R = 0, IN_VEL = 9, IN_RVEL = 12, IN_RBACK = 21, IN_SRMIN = 30, IN_MAXR
 enum { OUT_JTJ = 0, OUT_JTF = 9, OUT_SCORE = 12, OUT_WX = 16, OUT_X = 52, OUT_OK = 58, OUT_Q = 59, OUT_STRIDE = 64 };
 // lane_cnt slots
 enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
+
+// ---- kernel registry: every launch goes through RBV_LAUNCH so that launches are counted per kernel and can be
+// bracketed with CUDA events on the launching stream (rbv_profile_*; bench.py's roofline numbers come from there) ----
+#define RBV_KERNEL_LIST(X)                                                                                         \
+  X(k_fill) X(k_rowscan) X(k_colbox) X(k_detect_flags) X(k_detect_scan) X(k_detect_emit) X(k_join) X(k_tune)       \
+  X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
+  X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
+  X(k_kalman) X(k_lm_init) X(k_gate_min_matches)
+enum {
+#define X(n) KID_##n,
+  RBV_KERNEL_LIST(X)
+#undef X
+  KID_COUNT
+};
+void rbv_prof_begin(rbv_ctx* c, int kid);
+void rbv_prof_end(rbv_ctx* c, int kid);
+#define RBV_LAUNCH(c, kern, grid, block, smem, ...)                     \
+  do {                                                                  \
+    rbv_prof_begin((c), KID_##kern);                                    \
+    kern<<<dim3 grid, dim3 block, (smem), (c)->stream>>>(__VA_ARGS__);  \
+    rbv_prof_end((c), KID_##kern);                                      \
+  } while (0)
+// device fill of n 32-bit words (replaces cudaMemsetAsync so that every device op is one of our counted kernels)
+int rbv_fill32(rbv_ctx* c, void* dst, unsigned value, size_t n_words);
 
 void rbv_set_error(const char* fmt, ...);
 #define RBV_CUDA(call)                                                                        \

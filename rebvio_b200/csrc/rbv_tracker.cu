@@ -40,10 +40,9 @@ __global__ void k_field_build(KeylineSoA K, const int* __restrict__ count, const
 
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  RBV_CUDA(cudaMemsetAsync(c->field, 0xFF, sizeof(unsigned) * (size_t)P.lanes * P.npix, c->stream));
+  { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
   const long long work = (long long)P.keylines_max * P.field_nr;
-  k_field_build<<<dim3((unsigned)((work + 255) / 256), P.lanes), 256, 0, c->stream>>>(map->k, map->count, map->threshold, c->field, P);
-  ++c->launches;
+  RBV_LAUNCH(c, k_field_build, (dim3((unsigned)((work + 255) / 256), P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field, P);
   c->field_map = map;
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
@@ -91,8 +90,7 @@ __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const floa
 
 int tr_rotate(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  k_rotate<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(map->k, map->count, c->lane_in, P);
-  ++c->launches;
+  RBV_LAUNCH(c, k_rotate, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -126,8 +124,7 @@ __global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __res
 
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
   if (bins < 1 || bins > RBV_MAX_QBINS) { rbv_set_error("quantile bins out of range"); return RBV_ERR_ARG; }
-  k_quantile<<<c->P.lanes, 256, 0, c->stream>>>(map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm);
-  ++c->launches;
+  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (256), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -396,11 +393,8 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     sr_ptr = lmf + offsetof(LMState, sigma_rho_min) / sizeof(float);
     sr_stride = lm_floats;
   }
-  k_tryvel_eval<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(
-      map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
-  k_tryvel_reduce<<<P.lanes, 1024, 0, c->stream>>>(map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride,
-                                                    lm_call, c->reduce_mode == RBV_REDUCE_ORDERED, P);
-  c->launches += 2;
+  RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
+  RBV_LAUNCH(c, k_tryvel_reduce, (P.lanes), (1024), 0, map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, c->reduce_mode == RBV_REDUCE_ORDERED, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -468,12 +462,11 @@ __global__ void k_zero_cnt(int* lane_cnt, int slot, unsigned long long* probes) 
 
 int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
   const DevParams& P = c->P;
-  RBV_CUDA(cudaMemsetAsync(c->fwd_head, 0xFF, sizeof(int) * (size_t)P.lanes * P.kmax, c->stream));
-  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_FWD, nullptr);
+  { int rc = rbv_fill32(c, c->fwd_head, 0xFFFFFFFFu, (size_t)P.lanes * P.kmax); if (rc != RBV_OK) return rc; }
+  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_FWD, nullptr);
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
-  k_fwd_link<<<g, 256, 0, c->stream>>>(old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax);
-  k_fwd_resolve<<<g, 256, 0, c->stream>>>(old_map->k, new_map->k, new_map->count, c->fwd_head, c->fwd_next, c->lane_cnt, P.kmax);
-  c->launches += 3;
+  RBV_LAUNCH(c, k_fwd_link, (g), (256), 0, old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax);
+  RBV_LAUNCH(c, k_fwd_resolve, (g), (256), 0, old_map->k, new_map->k, new_map->count, c->fwd_head, c->fwd_next, c->lane_cnt, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -621,9 +614,8 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
   const DevParams& P = c->P;
   const float* vel_ptr = vel_from_lm ? reinterpret_cast<const float*>(c->lm) + offsetof(LMState, vel) / sizeof(float) : c->lane_in + IN_VEL;
   const int vel_stride = vel_from_lm ? (int)(sizeof(LMState) / sizeof(float)) : IN_STRIDE;
-  k_extrot_rows<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
-  k_extrot_reduce<<<P.lanes, 512, 0, c->stream>>>(new_map->count, c->prod, c->lane_out, c->reduce_mode == RBV_REDUCE_ORDERED, P);
-  c->launches += 2;
+  RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
+  RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, c->reduce_mode == RBV_REDUCE_ORDERED, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -749,10 +741,8 @@ __global__ void __launch_bounds__(256) k_directed(KeylineSoA Kn, const int* __re
 
 int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map) {
   const DevParams& P = c->P;
-  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_DIR, c->probes);
-  k_directed<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(new_map->k, new_map->count, old_map->k, old_map->mask,
-                                                                                 c->lane_in, c->lane_cnt, c->probes, P);
-  c->launches += 2;
+  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_DIR, c->probes);
+  RBV_LAUNCH(c, k_directed, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, old_map->k, old_map->mask, c->lane_in, c->lane_cnt, c->probes, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -804,10 +794,9 @@ __global__ void k_reg_apply(KeylineSoA K, const int* __restrict__ count, const f
 int tr_regularize(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
-  k_zero_cnt<<<1, P.lanes, 0, c->stream>>>(c->lane_cnt, CNT_REG, nullptr);
-  k_reg_eval<<<g, 256, 0, c->stream>>>(map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, P);
-  k_reg_apply<<<g, 256, 0, c->stream>>>(map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, P.kmax);
-  c->launches += 3;
+  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_REG, nullptr);
+  RBV_LAUNCH(c, k_reg_eval, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, P);
+  RBV_LAUNCH(c, k_reg_apply, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -855,8 +844,7 @@ __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restr
 
 int tr_kalman(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  k_kalman<<<dim3((P.keylines_max + 255) / 256, P.lanes), 256, 0, c->stream>>>(map->k, map->count, c->lane_in, P);
-  ++c->launches;
+  RBV_LAUNCH(c, k_kalman, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

@@ -96,6 +96,28 @@ class Context:
     def launch_count(self): return int(self.L.rbv_launch_count(self.h))
     def new_map(self): return Map(self)
 
+    # per-kernel accounting (rbv_profile_*)
+    def kernel_names(self):
+        return [self.L.rbv_kernel_name(i).decode() for i in range(self.L.rbv_kernel_count())]
+
+    def profile_set(self, mode):
+        """mode: -1 off, -2 all kernels, a kernel name or id = that kernel only"""
+        if isinstance(mode, str):
+            mode = self.kernel_names().index(mode)
+        check(self.L.rbv_profile_set(self.h, int(mode)))
+
+    def profile_reset(self): check(self.L.rbv_profile_reset(self.h))
+
+    def profile_read(self):
+        """-> {kernel: (total_ms of bracketed launches, bracketed launches, launches since reset)}"""
+        out = {}
+        for i, name in enumerate(self.kernel_names()):
+            ms, nt, nl = C.c_double(0), C.c_ulonglong(0), C.c_ulonglong(0)
+            check(self.L.rbv_profile_read(self.h, i, C.byref(ms), C.byref(nt), C.byref(nl)))
+            if nl.value:
+                out[name] = (ms.value, nt.value, nl.value)
+        return out
+
     def servo_threshold(self, threshold, last_count):
         return float(self.L.rbv_servo_threshold(C.byref(self.det), float(threshold), int(last_count)))
 

@@ -1,0 +1,112 @@
+"""Batched replay pipeline over the C ABI: B independent sequences ("lanes") advance one frame per `push`.
+
+Per frame it makes exactly the hot-path calls Rebvio's two worker loops make (reference rebvio/src/rebvio.cpp):
+  EdgeDetector::detect (:70)                                             -> rbv_detect / rbv_detect_device
+  buildDistanceField, rotateKeylines(R^T), minimizeVel, forwardMatch, extRotVel (:142,165,169,172,177) -> rbv_track_g1
+  [host] fusion of (Vg, P_Vg, Wx, X) into V, P_V, R0, Rgva               (:183-233; IMU filters are out of scope, see below)
+  rotateKeylines(R0), directedMatch, regularize1Iter, updateInverseDepth (:223/232,245,256,259)         -> rbv_track_g2
+The IMU/bias filters between the two halves (gyroBiasCorrection, estimateLs4Acceleration, estimateBias; core.cpp:264-414)
+are O(1) host math outside the hot path; this replay driver uses the visual-only subset of that block
+(rebvio.cpp:193-200 with the gyro prior switched off): R0 = exp(X[3:6]), V = R0 Vg + X[0:3], P_V = inv(Wx)[0:3,0:3],
+Rgva^T = R0 R^T. The relative rotation R of each frame is an input (the reference takes it from the gyro integral).
+There is no CPU fallback: everything below runs through librebvio_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi, host
+
+
+def so3_exp_batch(w):
+    """Rodrigues formula, w [B,3] float64 -> [B,3,3]"""
+    w = np.asarray(w, np.float64)
+    th = np.linalg.norm(w, axis=1)
+    K = np.zeros((len(w), 3, 3))
+    K[:, 0, 1], K[:, 0, 2], K[:, 1, 0] = -w[:, 2], w[:, 1], w[:, 2]
+    K[:, 1, 2], K[:, 2, 0], K[:, 2, 1] = -w[:, 0], -w[:, 1], w[:, 0]
+    small = th < 1e-12
+    ths = np.where(small, 1.0, th)
+    a = np.where(small, 1.0, np.sin(ths) / ths)
+    b = np.where(small, 0.0, (1 - np.cos(ths)) / ths ** 2)
+    return np.eye(3)[None] + a[:, None, None] * K + b[:, None, None] * (K @ K)
+
+
+def visual_fusion(R, Vg, Wx, X):
+    """batched host block between the two tracker halves -> float32 (R0 [B,9], V [B,3], P_V [B,9], Rgva [B,9])"""
+    B = len(X)
+    R0 = so3_exp_batch(np.asarray(X, np.float64)[:, 3:6])
+    V = np.einsum("bij,bj->bi", R0, np.asarray(Vg, np.float64)) + np.asarray(X, np.float64)[:, 0:3]
+    Wx64 = np.asarray(Wx, np.float64).reshape(B, 6, 6)
+    P = np.empty((B, 3, 3))
+    for b in range(B):
+        try:
+            P[b] = np.linalg.inv(Wx64[b])[:3, :3]
+        except np.linalg.LinAlgError:
+            P[b] = np.eye(3) * 1e10
+    Rt = R0 @ np.transpose(np.asarray(R, np.float64).reshape(B, 3, 3), (0, 2, 1))
+    Rgva = np.transpose(Rt, (0, 2, 1))
+    f = lambda a, n: np.ascontiguousarray(a, np.float32).reshape(B, n)
+    return f(R0, 9), f(V, 3), f(P, 9), f(Rgva, 9)
+
+
+class BatchedPipeline:
+    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None):
+        self.ctx = host.Context(cam, det, mapc, core, lanes=lanes, device=device, reduce_mode=reduce_mode)
+        if cuda_stream is not None:
+            self.ctx.set_stream(cuda_stream)
+        self.lanes = lanes
+        self.maps = [self.ctx.new_map(), self.ctx.new_map()]
+        self.cur = 0            # index of the map the next detect writes
+        self.have_old = False
+        self.threshold = np.full(lanes, np.float32(det.threshold), np.float32)   # config_->threshold per lane
+        self.count = np.zeros(lanes, np.int32)                                   # EdgeDetector::keylines_count_
+        self.min_matches = int(core.global_min_matches_threshold)
+        self.frames_done = 0
+        self._ptrs = (C.c_void_p * lanes)()
+
+    def close(self):
+        for m in self.maps:
+            m.release()
+        self.ctx.close()
+
+    def _servo(self):
+        L, det = self.ctx.L, self.ctx.det
+        for b in range(self.lanes):
+            self.threshold[b] = L.rbv_servo_threshold(C.byref(det), float(self.threshold[b]), int(self.count[b]))
+
+    def push(self, frames=None, R_rel=None, device_ptr=None, ts_us=None):
+        """One frame per lane. `frames`: host float32 [B,rows,cols] (0..765; pageable or pinned) — or `device_ptr`: the
+        same layout already in device memory. R_rel [B,3,3]: rotation of the camera since the previous frame.
+        Returns a dict of per-lane outputs (keyline counts always; velocities/matches once two frames are in)."""
+        ctx, B = self.ctx, self.lanes
+        self._servo()
+        new = self.maps[self.cur]
+        n = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+        ts = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if ts_us is None else ts_us, np.uint64), (B,)))
+        if device_ptr is not None:
+            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+        else:
+            base, stride = frames.ctypes.data, frames.strides[0]
+            for b in range(B):
+                self._ptrs[b] = base + b * stride
+            capi.check(ctx.L.rbv_detect(ctx.h, new.h, self._ptrs, 0, capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+        self.count = n
+        out = {"keylines": n, "auto_threshold": at}
+        if self.have_old:
+            old = self.maps[1 - self.cur]
+            R = np.ascontiguousarray(R_rel, np.float32).reshape(B, 3, 3)
+            Rt = np.ascontiguousarray(np.transpose(R, (0, 2, 1))).reshape(B, 9)
+            Vg, P_Vg, Wx, X, ok = ctx.track_g1(old, new, Rt)
+            R0, V, P_V, Rgva = visual_fusion(R, Vg, Wx, X)
+            nm, kf = ctx.track_g2(old, new, R0, V, P_V, Rgva, 40.0, self.min_matches)
+            out.update(Vg=Vg, P_Vg=P_Vg, Wx=Wx, X=X, ok=ok, V=V, matches=nm, kf_matches=kf)
+        self.have_old = True
+        self.cur = 1 - self.cur
+        self.frames_done += 1
+        return out
+
+    def newest_map(self):
+        return self.maps[1 - self.cur]

@@ -231,3 +231,73 @@ def generate(spec: SequenceSpec) -> Sequence:
         acc.append(R_C2I @ f_c + rng.normal(0, 2e-3, 3))
     return Sequence(spec, frames, ts, imu_ts, np.asarray(gyro, np.float32), np.asarray(acc, np.float32),
                     np.asarray(R_rel))
+
+
+# ---- batched renderer (torch; CPU or CUDA) for benchmark-sized workloads ------------------------------------------
+def render_batch_torch(tex, cam: CameraSpec, R_wc, p_w, planes: str, tex_scale: float, device="cpu", chunk=32):
+    """Same ray-cast as render() for a batch of poses: R_wc [M,3,3], p_w [M,3] (numpy float64) -> u8 [M,rows,cols]
+    torch tensor on `device`. Arithmetic is float64 like render(); results agree with render() to +-1 grey level
+    (tests/test_host_logic.py). Used to pre-stage bench inputs (64 sequences per GPU), never inside a timed region."""
+    import torch
+    size = tex.shape[0]
+    dev = torch.device(device)
+    f64 = torch.float64
+    t_tex = torch.as_tensor(tex, dtype=torch.float32, device=dev)
+    v, u = torch.meshgrid(torch.arange(cam.rows, dtype=f64, device=dev), torch.arange(cam.cols, dtype=f64, device=dev), indexing="ij")
+    d_c = torch.stack([(u - cam.cx) / cam.fm, (v - cam.cy) / cam.fm, torch.ones_like(u)], -1)          # [r,c,3]
+    R_all = torch.as_tensor(np.asarray(R_wc), dtype=f64, device=dev)
+    p_all = torch.as_tensor(np.asarray(p_w), dtype=f64, device=dev)
+    out = torch.empty((R_all.shape[0], cam.rows, cam.cols), dtype=torch.uint8, device=dev)
+    pl = [(torch.as_tensor(n, dtype=f64, device=dev), float(d0), torch.as_tensor(ua, dtype=f64, device=dev),
+           torch.as_tensor(va, dtype=f64, device=dev), ou, ov) for n, d0, ua, va, (ou, ov) in _planes(planes)]
+    for s0 in range(0, R_all.shape[0], chunk):
+        R, p = R_all[s0:s0 + chunk], p_all[s0:s0 + chunk]
+        d_w = torch.einsum("rck,mjk->mrcj", d_c, R)                                                     # d_c @ R^T
+        best = torch.full(d_w.shape[:3], float("inf"), dtype=f64, device=dev)
+        tu = torch.zeros_like(best)
+        tv = torch.zeros_like(best)
+        for n, d0, ua, va, ou, ov in pl:
+            denom = d_w @ n
+            s = (d0 - (p @ n))[:, None, None] / denom
+            ok = (denom > 1e-9) & (s > 0) & (s < best)
+            X = p[:, None, None, :] + s[..., None] * d_w
+            tu = torch.where(ok, (X @ ua) * tex_scale + ou * size, tu)
+            tv = torch.where(ok, (X @ va) * tex_scale + ov * size, tv)
+            best = torch.where(ok, s, best)
+        tu = torch.remainder(tu, size - 1)
+        tv = torch.remainder(tv, size - 1)
+        x0 = torch.floor(tu).long()
+        y0 = torch.floor(tv).long()
+        fx = (tu - x0).float()
+        fy = (tv - y0).float()
+        a = t_tex[y0, x0] * (1 - fx) + t_tex[y0, x0 + 1] * fx
+        b = t_tex[y0 + 1, x0] * (1 - fx) + t_tex[y0 + 1, x0 + 1] * fx
+        img = a * (1 - fy) + b * fy
+        img = torch.where(torch.isfinite(best), img, torch.full_like(img, 128.0))
+        out[s0:s0 + chunk] = torch.clamp(torch.round(img), 0, 255).to(torch.uint8)
+    return out
+
+
+def batched_sequences(spec: SequenceSpec, seeds, n_frames: int, device="cpu", n_textures: int = 4):
+    """`len(seeds)` independent sequences of `spec`'s shape (the C4 batched-replay workload of SURVEY.md 8(d)):
+    trajectory per seed; the procedural texture is one of `n_textures` (seed % n_textures) to keep set-up time bounded.
+    -> frames u8 torch [n_frames, L, rows, cols] on `device`, R_rel float32 numpy [n_frames, L, 3, 3] (identity at 0)."""
+    import torch
+    L = len(seeds)
+    tex_scale = spec.cam.fm / 2.0
+    dt = 1.0 / spec.fps
+    frames = torch.empty((n_frames, L, spec.cam.rows, spec.cam.cols), dtype=torch.uint8, device=device)
+    R_rel = np.zeros((n_frames, L, 3, 3), np.float32)
+    texs = {}
+    for i, seed in enumerate(seeds):
+        tkey = seed % n_textures
+        if tkey not in texs:
+            texs[tkey] = make_texture(9000 + tkey, n_edges=spec.n_edges, checker=spec.checker)
+        traj = Trajectory(seed)
+        R = np.stack([traj.R_wc(k * dt) for k in range(n_frames)])
+        p = np.stack([traj.pos(k * dt) for k in range(n_frames)])
+        frames[:, i] = render_batch_torch(texs[tkey], spec.cam, R, p, spec.planes, tex_scale, device=device)
+        R_rel[0, i] = np.eye(3)
+        for k in range(1, n_frames):
+            R_rel[k, i] = R[k - 1].T @ R[k]
+    return frames, R_rel

@@ -1,0 +1,96 @@
+"""CPU: the C-ABI library loads, exports every symbol include/rebvio_b200.h declares, its POD defaults equal the
+reference's, the host servo matches the oracle, and it fails loudly without a GPU (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import common
+import harness as H
+from oracle import pyref
+from rebvio_b200 import capi
+
+HEADER = os.path.join(common.ROOT, "include", "rebvio_b200.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rbv_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    names = _declared()
+    assert len(names) >= 40
+    lib = C.CDLL(capi.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/rebvio_b200.h but not exported"
+    assert sorted(capi.EXPORTS) == names, set(capi.EXPORTS) ^ set(names)
+    capi.load()
+
+
+def test_no_oracle_or_torch_in_product_library():
+    """the product .so must not link the oracle (or anything but the CUDA runtime and libc/libstdc++)"""
+    import subprocess
+    out = subprocess.run(["ldd", capi.LIB_PATH], stdout=subprocess.PIPE, text=True).stdout
+    assert "oracle" not in out and "torch" not in out and "rebvio_ref" not in out
+    for root, _, files in os.walk(os.path.join(common.ROOT, "rebvio_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                txt = open(os.path.join(root, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "librebvio_oracle" not in txt, f
+
+
+def test_defaults_equal_reference_structs():
+    cam, det, mp, core = capi.defaults()
+    rc, rd, rm, rk = pyref.default_cfgs()
+    for a, b in ((cam, rc), (det, rd), (mp, rm), (core, rk)):
+        for name, _ in a._fields_:
+            va, vb = getattr(a, name), getattr(b, name)
+            assert np.float32(va) == np.float32(vb), (name, va, vb)
+
+
+def test_servo_threshold_matches_oracle():
+    L = capi.load()
+    _, det, _, _ = capi.defaults()
+    _, rd, _, _ = pyref.default_cfgs()
+    orc = C.CDLL(os.path.join(common.ROOT, "oracle", "librebvio_oracle.so"))
+    orc.orc_servo_threshold.restype = C.c_float
+    orc.orc_servo_threshold.argtypes = [C.POINTER(pyref.DetectorCfg), C.c_float, C.c_int]
+    rng = np.random.RandomState(0)
+    for _ in range(2000):
+        thr = float(np.float32(rng.uniform(0.0, 0.6)))
+        cnt = int(rng.randint(0, 40000))
+        a = L.rbv_servo_threshold(C.byref(det), thr, cnt)
+        b = orc.orc_servo_threshold(C.byref(rd), thr, cnt)
+        assert H.bits(np.float32(a)) == H.bits(np.float32(b))
+
+
+def test_bad_arguments_are_rejected_without_touching_a_device():
+    L = capi.load()
+    cam, det, mp, core = capi.defaults()
+    h = C.c_void_p()
+    assert L.rbv_create(None, C.byref(det), C.byref(mp), C.byref(core), 0, 1, C.byref(h)) == capi.RBV_ERR_ARG
+    assert L.rbv_create(C.byref(cam), C.byref(det), C.byref(mp), C.byref(core), 0, 0, C.byref(h)) == capi.RBV_ERR_ARG
+    small = capi.Camera(100.0, 8.0, 8.0, 16, 16)
+    assert L.rbv_create(C.byref(small), C.byref(det), C.byref(mp), C.byref(core), 0, 1, C.byref(h)) == capi.RBV_ERR_ARG
+    assert L.rbv_sync(None) == capi.RBV_ERR_ARG
+    assert L.rbv_lanes(None) == 0
+    assert L.rbv_launch_count(None) == 0
+
+
+def test_create_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    L = capi.load()
+    cam, det, mp, core = capi.defaults()
+    h = C.c_void_p()
+    rc = L.rbv_create(C.byref(cam), C.byref(det), C.byref(mp), C.byref(core), 0, 1, C.byref(h))
+    assert rc == capi.RBV_ERR_CUDA and not h.value
+    assert b"no CPU fallback" in L.rbv_last_error()
+    from rebvio_b200 import host
+    with pytest.raises(capi.RbvError):
+        host.Context()

@@ -1,0 +1,222 @@
+"""GPU (B200): the CUDA path, called through the C ABI, against (a) the committed golden vectors of the unmodified
+reference, (b) the oracle on the same seeded inputs at the benchmark sizes, (c) size-independent properties.
+
+Bit-exact: keyline sets, ids, masks, distance field, match indices, and — in RBV_REDUCE_ORDERED mode — every float
+the path produces except extRotVel's X (tolerance in tests/common.py). RBV_REDUCE_FAST: indices bit-exact under
+teacher forcing, sums <= 1e-5 relative (north star tolerance)."""
+import numpy as np
+import pytest
+
+import common
+import harness as H
+from oracle import pyref
+from rebvio_b200 import capi, host, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED):
+    from gpu_impl import GpuImpl
+    cam, det, mapc, core = cfg
+    return GpuImpl(cam, det, mapc, core, lanes=lanes, lane=lane, reduce_mode=mode)
+
+
+@pytest.mark.parametrize("name", common.GOLDEN_CASES)
+def test_cuda_vs_reference_golden_teacher_forced(name):
+    frames, R_rel, meta, recs, extra = common.load_golden(name)
+    g = _gpu(common.cfgs_from_meta(meta))
+    got = H.run_stages(g, frames, R_rel, teacher=recs)
+    rep = H.report(recs, got)
+    assert H.dirty(rep) == []
+    common.assert_x_vs_ref(recs, rep)
+    assert g.ctx.launch_count() > 0
+    if extra:
+        g.detect(frames[0])
+        for which, key in enumerate(("scale/s0", "scale/s1", "scale/dog", "scale/mag")):
+            assert np.array_equal(H.bits(g.ctx.read_image(which, 1)), H.bits(extra[key])), key
+    g.close()
+
+
+@pytest.mark.parametrize("name,nf", [("C5:320x240", 4), ("C1", 3), ("C2", 4), ("C3", 3)])
+def test_cuda_vs_oracle_free_running_ordered(name, nf):
+    """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits."""
+    spec, frames, R_rel = common.sequence(name, nf)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    T = H.run_stages(orc, frames, R_rel)
+    g = _gpu(cfg)
+    G = H.run_stages(g, frames, R_rel)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    assert common.x_rel_max(rep) <= common.X_RTOL_FLOOR
+    g.close(); orc.close()
+
+
+@pytest.mark.parametrize("name,nf", [("C2", 3), ("C3", 2)])
+def test_cuda_fast_reduction_teacher_forced(name, nf):
+    """Throughput mode (FP64 shuffle-tree sums): per-stage inputs from the oracle; indices and every per-keyline output
+    stay bit-exact, the reduced sums agree to 1e-5 relative."""
+    spec, frames, R_rel = common.sequence(name, nf)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    T = H.run_stages(orc, frames, R_rel)
+    g = _gpu(cfg, mode=capi.REDUCE_FAST)
+    G = H.run_stages(g, frames, R_rel, teacher=T)
+    rep = H.report(T, G)
+    for k, stage, d in H.dirty(rep):
+        if stage == "minimize":
+            # sums differ in the last bits -> LM iterates differ by ulps; everything integer must still agree on call 0
+            assert d.get("trace_rel", 0.0) <= 1e-5 and d.get("score_rel", 0.0) <= 1e-5, (k, d)
+            assert d.get("Vg_rel", 0.0) <= 1e-4 and d.get("P_Vg_rel", 0.0) <= 1e-4, (k, d)
+        elif stage == "extrot":
+            assert d.get("Wx_rel", 0.0) <= 1e-5, (k, d)
+        else:
+            raise AssertionError((k, stage, d))
+    # single tryVel at the teacher's velocity: match indices bit-exact, sums within tolerance
+    g.close(); orc.close()
+
+
+def test_try_vel_fast_vs_ordered_indices_and_sums():
+    spec, frames, R_rel = common.sequence("C2", 3)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    a, b = orc.detect(frames[0]), orc.detect(frames[1])
+    orc.build_distance_field(b)
+    n = orc.map_size(a)
+    for mode in (capi.REDUCE_ORDERED, capi.REDUCE_FAST):
+        g = _gpu(cfg, mode=mode)
+        ga, gb = g.detect(frames[0]), g.detect(frames[1])
+        g.build_distance_field(gb)
+        res = np.zeros(n, np.float32)
+        g.ctx.resetResiduals(ga)
+        for vel in ([0, 0, 0], [0.01, -0.02, 0.005], [0.3, 0.2, -0.9], [0, 0, -1.5]):
+            so, JJo, JFo = orc.try_vel(a, np.float32(vel), 1e3, res)
+            sg, JJg, JFg = g.try_vel(ga, vel, 1e3)
+            assert np.array_equal(orc.map_get(a)["match_id_forward"], g.map_get(ga)["match_id_forward"])
+            first = H.first_match_index(orc.map_get(a))
+            assert np.array_equal(H.bits(res[first:]), H.bits(ga.residuals(1)[first:n]))
+            if mode == capi.REDUCE_ORDERED:
+                assert H.bits(np.float32(so)) == H.bits(np.float32(sg))
+                assert np.array_equal(H.bits(JJo), H.bits(JJg)) and np.array_equal(H.bits(JFo), H.bits(JFg))
+            else:
+                assert abs(sg - so) <= 1e-5 * abs(so)
+                assert H.rel_err(JJg, JJo) <= 1e-5 and H.rel_err(JFg, JFo) <= 1e-5
+        g.close()
+        # rewind the oracle's forward matches / residual state for the second mode
+        a2 = orc.detect(frames[0]); orc.map_free(a); a = a2
+    orc.close()
+
+
+@pytest.mark.parametrize("rows,cols", [(33, 47), (97, 131), (480, 752), (1080, 1920)])
+def test_box_pass_kernel_vs_oracle(rows, cols):
+    """first-kernel parity: one createIntegralImage + average pass (scale_space.cpp:48-128), ragged and full sizes"""
+    cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 200)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
+    ctx = host.Context(conv(capi.Camera, cfg[0]), conv(capi.DetectorCfg, cfg[1]), conv(capi.MapCfg, cfg[2]), conv(capi.CoreCfg, cfg[3]))
+    rng = np.random.RandomState(rows + cols)
+    img = rng.randint(0, 256, (rows, cols)).astype(np.float32) * np.float32(3.0)
+    pinv, widths = ctx.setup()
+    assert np.array_equal(H.bits(pinv), H.bits(orc.pinv()))
+    assert list(widths) == list(orc.scale_setup()[0])
+    for s in range(2):
+        for p in range(3):
+            assert np.array_equal(H.bits(ctx.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img))), (s, p)
+    ctx.close(); orc.close()
+
+
+def _shift_frames(rows, cols, n, seed):
+    """cheap edge-rich frames for the big sizes: windows of the procedural texture, shifted by a few pixels"""
+    tex = synth.make_texture(seed, size=max(2048, 1 << int(np.ceil(np.log2(max(rows, cols) + 64)))), n_edges=96)
+    out = []
+    for k in range(n):
+        out.append(np.ascontiguousarray(tex[3 * k: 3 * k + rows, 2 * k: 2 * k + cols]).round().astype(np.uint8).astype(np.float32) * np.float32(3.0))
+    return out
+
+
+@pytest.mark.parametrize("rows,cols", [(1080, 1920), (2160, 3840)])
+def test_large_frames_vs_oracle(rows, cols):
+    """kernel-sweep sizes (BASELINE.json configs[4]): detect + distance field + one LM solve, bit-exact at full size"""
+    kmax = -(-rows * cols // 22)
+    cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, int(0.75 * kmax), kmax)
+    frames = _shift_frames(rows, cols, 2, 7)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    g = _gpu(cfg, lanes=1, lane=0)
+    R = np.stack([np.eye(3)] * 2)
+    T = H.run_stages(orc, frames, R)
+    G = H.run_stages(g, frames, R)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    assert T[1]["detect"]["n"] > 20000
+    g.close(); orc.close()
+
+
+def test_lanes_are_independent():
+    """different sequences in different lanes of one context == each sequence run alone (the batched-replay shape)"""
+    spec, frames, R_rel = common.sequence("C5:320x240", 4)
+    cfg = common.cfgs_from_spec(spec)
+    conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
+    B = 3
+    ctx = host.Context(conv(capi.Camera, cfg[0]), conv(capi.DetectorCfg, cfg[1]), conv(capi.MapCfg, cfg[2]), conv(capi.CoreCfg, cfg[3]),
+                       lanes=B, reduce_mode=capi.REDUCE_ORDERED)
+    # lane b sees frames (b, b+1): three different frame pairs
+    old_imgs = np.stack([frames[b] for b in range(B)])
+    new_imgs = np.stack([frames[b + 1] for b in range(B)])
+    Rs = np.stack([np.asarray(R_rel[b + 1], np.float32).T for b in range(B)])
+    old, n_old, _ = ctx.detect(old_imgs, 0.01)
+    new, n_new, _ = ctx.detect(new_imgs, 0.01)
+    vel, Rv, Wx, X, ok = ctx.track_g1(old, new, Rs)
+    for b in range(B):
+        orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+        orc.set_threshold(0.01); orc.det.gain = 0.0
+        o = orc.map_new(); nn = orc.L.orc_detect(orc.h, np.ascontiguousarray(frames[b]), 0.01, o)
+        m = orc.map_new(); orc.L.orc_detect(orc.h, np.ascontiguousarray(frames[b + 1]), 0.01, m)
+        assert nn == n_old[b]
+        orc.build_distance_field(m)
+        orc.rotate(o, Rs[b])
+        s, v, P = orc.minimize_vel(o, [0, 0, 0])
+        orc.forward_match(o, m)
+        oko, Wxo, Xo = orc.ext_rot_vel(m, v)
+        assert np.array_equal(H.bits(v), H.bits(vel[b])) and np.array_equal(H.bits(P), H.bits(Rv[b]))
+        assert np.array_equal(H.bits(Wxo), H.bits(Wx[b]))
+        assert H.rel_err(X[b], Xo) <= common.X_RTOL_FLOOR
+        assert H.dirty([{"d": H.clean(H.compare_keylines(orc.map_get(m), new.keylines(b)[0]))}]) == []
+        assert H.dirty([{"d": H.clean(H.compare_keylines(orc.map_get(o), old.keylines(b)[0]))}]) == []
+        orc.close()
+    ctx.close()
+
+
+def test_empty_and_flat_frames():
+    """a constant frame yields no keylines (the reference would hit undefined behaviour in tuneThreshold on an empty
+    map, edge_detector.cpp:168,177; here the map keeps threshold -1) and every tracker stage is a no-op that returns."""
+    rows, cols = 120, 160
+    cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 500)
+    g = _gpu(cfg)
+    flat = np.full((rows, cols), 300.0, np.float32)
+    a = g.detect(flat); b = g.detect(flat)
+    assert g.map_size(a) == 0 and g.map_size(b) == 0 and g.map_threshold(a) == -1.0
+    assert (g.detector_mask() == -1).all()
+    g.build_distance_field(b)
+    fid, _ = g.field()
+    assert (fid == -1).all()
+    g.rotate(a, np.eye(3))
+    s, v, P = g.minimize_vel(a, [0, 0, 0])
+    assert s == 0.0
+    assert g.forward_match(a, b) == 0
+    n, kf = g.directed_match(b, a, [0, 0, 0], np.eye(3), np.eye(3))
+    assert (n, kf) == (0, 0)
+    assert g.regularize(b) == 0
+    g.update_inverse_depth([0, 0, 0])
+    g.close()
+
+
+def test_fast_mode_is_deterministic():
+    spec, frames, R_rel = common.sequence("C5:320x240", 4)
+    cfg = common.cfgs_from_spec(spec)
+    runs = []
+    for _ in range(2):
+        g = _gpu(cfg, mode=capi.REDUCE_FAST)
+        runs.append(H.run_stages(g, frames, R_rel))
+        g.close()
+    assert H.dirty(H.report(runs[0], runs[1])) == []
+    assert common.x_rel_max(H.report(runs[0], runs[1])) == 0.0

@@ -1,0 +1,99 @@
+"""CPU: the oracle against the UNMODIFIED reference compiled into oracle/_ref/librebvio_ref.so (make -C oracle ref),
+run live on seeded inputs. Skipped where the reference library is not present (it is git-ignored; it is built by
+__graft_entry__.build() wherever /root/reference exists and travels to the GPU box with the snapshot)."""
+import numpy as np
+import pytest
+
+import common
+import harness as H
+from oracle import pyref
+
+pytestmark = pytest.mark.skipif(not pyref.available(), reason="oracle/_ref/librebvio_ref.so not built")
+
+
+def _pair(rows, cols, kref=12000, kmax=16000):
+    cam, det, mapc, core = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, kref, kmax)
+    return pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+
+
+@pytest.mark.parametrize("rows,cols", [(64, 96), (97, 131), (240, 320)])
+def test_setup_divisors_integral_boxpass(rows, cols):
+    ref, orc = _pair(rows, cols)
+    wr, sr = ref.scale_setup()
+    wo, so = orc.scale_setup()
+    assert list(wr) == list(wo) == [7, 7, 7, 9, 9, 9]
+    assert np.array_equal(H.bits(sr), H.bits(so))
+    rng = np.random.RandomState(rows * 1000 + cols)
+    img = (rng.randint(0, 256, (rows, cols)).astype(np.float32) * np.float32(3.0))
+    assert np.array_equal(H.bits(ref.integral(img)), H.bits(orc.integral(img)))
+    for s in range(2):
+        for p in range(3):
+            assert np.array_equal(H.bits(ref.divisors(s, p)), H.bits(orc.divisors(s, p)))
+            assert np.array_equal(H.bits(ref.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img)))
+    for a, b in zip(ref.scale_space(img), orc.scale_space(img)):
+        assert np.array_equal(H.bits(a), H.bits(b))
+    ref.close(); orc.close()
+
+
+def test_full_chain_teacher_forced_320x240():
+    spec, frames, R_rel = common.sequence("C5:320x240", 4)
+    cam, det, mapc, core = common.cfgs_from_spec(spec)
+    ref, orc = pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+    T = H.run_stages(ref, frames, R_rel)
+    G = H.run_stages(orc, frames, R_rel, teacher=T)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    common.assert_x_vs_ref(T, rep)
+    ref.close(); orc.close()
+    # and the other way round (fresh instances: the servo state is per detector): the reference driven with the
+    # oracle's free-running state
+    ref, orc = pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+    T2 = H.run_stages(orc, frames, R_rel)
+    G2 = H.run_stages(ref, frames, R_rel, teacher=T2)
+    assert H.dirty(H.report(T2, G2)) == []
+    ref.close(); orc.close()
+
+
+def test_try_vel_nonzero_velocity_and_residual_carry():
+    """tryVel at a few velocities (incl. one that pushes keylines behind the camera / out of the image) with the
+    residual vector carried from call to call as minimizeVel does (core.cpp:158,141)."""
+    spec, frames, R_rel = common.sequence("C5:320x240", 4)
+    cam, det, mapc, core = common.cfgs_from_spec(spec)
+    ref, orc = pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+    maps = []
+    for impl in (ref, orc):
+        a = impl.detect(frames[0]); b = impl.detect(frames[1])
+        impl.build_distance_field(b)
+        maps.append(a)
+    n = ref.map_size(maps[0])
+    res_r = np.zeros(n, np.float32); res_o = np.zeros(n, np.float32)
+    for vel in ([0, 0, 0], [0.01, -0.02, 0.005], [0.3, 0.2, -0.9], [0, 0, -1.5], [-0.05, 0.05, 2.0]):
+        for srmin in (1e3, 15.0):
+            sr, JJr, JFr = ref.try_vel(maps[0], np.float32(vel), srmin, res_r)
+            so, JJo, JFo = orc.try_vel(maps[1], np.float32(vel), srmin, res_o)
+            assert H.bits(np.float32(sr)) == H.bits(np.float32(so))
+            assert np.array_equal(H.bits(JJr), H.bits(JJo)) and np.array_equal(H.bits(JFr), H.bits(JFo))
+            first = H.first_match_index(ref.map_get(maps[0]))
+            assert np.array_equal(H.bits(res_r[first:]), H.bits(res_o[first:]))
+            assert np.array_equal(ref.map_get(maps[0])["match_id_forward"], orc.map_get(maps[1])["match_id_forward"])
+    ref.close(); orc.close()
+
+
+def test_quantile_and_servo():
+    spec, frames, _ = common.sequence("C5:320x240", 4)
+    cam, det, mapc, core = common.cfgs_from_spec(spec)
+    ref, orc = pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+    mr, mo = ref.detect(frames[0]), orc.detect(frames[0])
+    kl = ref.map_get(mr)
+    rng = np.random.RandomState(3)
+    kl["sigma_rho"] = rng.uniform(0.0, 25.0, len(kl)).astype(np.float32)
+    ref.map_set(mr, kl); orc.map_set(mo, kl)
+    for pct, bins in ((0.9, 100), (0.5, 10), (0.999, 1000), (1.0, 100)):
+        assert H.bits(np.float32(ref.quantile(mr, pct, bins))) == H.bits(np.float32(orc.quantile(mo, pct, bins)))
+    # servo: drive both detectors from the same (threshold, last count) states
+    for thr, cnt in ((0.01, 0), (0.01, 16000), (0.4999, 50000), (0.0051, 0), (0.2, 12000)):
+        ref.set_threshold(thr); ref.set_last_count(cnt)
+        orc.set_threshold(thr); orc.set_last_count(cnt)
+        ref.detect(frames[1]); orc.detect(frames[1])
+        assert H.bits(np.float32(ref.get_threshold())) == H.bits(np.float32(orc.get_threshold()))
+    ref.close(); orc.close()
