@@ -230,9 +230,9 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   c->own_stream = true;
   const int wpr = (P.cols + 31) / 32;
   RBV_CUDA(dalloc(&c->img, B * N));
-  RBV_CUDA(dalloc(&c->rowsum, 2 * B * N));
+  RBV_CUDA(dalloc(&c->rowsum, 4 * B * N));   // rowsum [2][B][N] + bufB [2][B][N] contiguous (detect reuses it as float4 [B][N])
+  c->bufB = c->rowsum + 2 * B * N;
   RBV_CUDA(dalloc(&c->bufA, 2 * B * N));
-  RBV_CUDA(dalloc(&c->bufB, 2 * B * N));
   RBV_CUDA(dalloc(&c->flags, B * P.rows * wpr));
   RBV_CUDA(dalloc(&c->rowcount, B * P.rows));
   RBV_CUDA(dalloc(&c->rowoffset, B * P.rows));
@@ -249,6 +249,12 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(dalloc(&c->lane_out, B * OUT_STRIDE));
   RBV_CUDA(dalloc(&c->lane_cnt, B * CNT_STRIDE));
   RBV_CUDA(dalloc(&c->probes, B));
+  c->nblk = (P.kmax + 255) / 256;
+  RBV_CUDA(dalloc(&c->partials, B * c->nblk * 27));
+  RBV_CUDA(dalloc(&c->ticket, B));
+  RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
+  RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
+  RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->lm, 0, sizeof(LMState) * B));
   RBV_CUDA(cudaMemset(c->lane_in, 0, sizeof(float) * B * IN_STRIDE));
   RBV_CUDA(cudaMemset(c->lane_out, 0, sizeof(float) * B * OUT_STRIDE));
@@ -274,8 +280,9 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  void* dev[] = {c->img, c->rowsum, c->bufA, c->bufB, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->field, c->prod, c->fiabs,
-                 c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes};
+  void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->field, c->prod, c->fiabs,
+                 c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
+                 c->partials, c->ticket, c->blkagg};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {

@@ -69,32 +69,63 @@ __global__ void __launch_bounds__(32) k_rowscan(const float* __restrict__ in, fl
 //   times float(1.0/double(window area)) (precomputeDivisors, :130-171; the interior constant `a` (:72) is the same number).
 #define CB_TPB 128
 #define CB_CH 16
-#define CB_RING 32
-__global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ rowsum, float* __restrict__ out, int rows, int cols,
-                                                   size_t in_plane_stride, size_t out_plane_stride, int nz, int d0, int d1) {
+#define CB_RING 64   // >= 2*CB_CH + 2*hmax + 2: a chunk's writes never land on rows the previous chunk still reads -> ONE barrier per chunk
+
+// one output value (scale_space.cpp:69-128): ro = output row, h = half width, jhi / jlo = ring columns of the right / left tap
+__device__ __forceinline__ float box_value(const float (*ring)[CB_TPB], const float (*inv_area)[16], int ro, int h, int rows, int jhi,
+                                           int jlo, bool left, int ncol, float inv_mid) {
+  const int rlo = ro - h - 1;
+  if (rlo >= 0 && ro + h < rows) {                                                     // interior rows: full window height
+    const float* hi = ring[(ro + h) & (CB_RING - 1)];
+    const float* lo = ring[rlo & (CB_RING - 1)];
+    const float v = left ? ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo] : hi[jhi] - lo[jhi];   // :99 / :94
+    return v * inv_mid;
+  }
+  const int rhi = min(ro + h, rows - 1);
+  const float* hi = ring[rhi & (CB_RING - 1)];
+  float v;
+  if (rlo < 0) {
+    v = left ? hi[jhi] - hi[jlo] : hi[jhi];                                             // top rows :78-84
+  } else {
+    const float* lo = ring[rlo & (CB_RING - 1)];
+    v = left ? ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo] : hi[jhi] - lo[jhi];           // bottom rows :119,:124 / :114
+  }
+  return v * inv_area[rhi - max(rlo, -1)][ncol];
+}
+
+// dual = 1 (first pass): both scales are box-filtered from ONE column scan of the shared row-prefix image (plane =
+// blockIdx.y = lane; outputs out0 / out1 with widths d0 / d1). dual = 0: plane = blockIdx.y, width d0 or d1 by plane % nz.
+__global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ rowsum, float* __restrict__ out0, float* __restrict__ out1,
+                                                   int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
+                                                   int d1, int dual) {
   __shared__ float ring[CB_RING][CB_TPB];
   __shared__ float inv_area[16][16];
   const int t = threadIdx.x;
-  const int z = blockIdx.y % nz;
-  const int d = z ? d1 : d0;
-  const int h = d / 2;
-  const int W = CB_TPB - (2 * h + 1);
+  const int z = dual ? 0 : blockIdx.y % nz;
+  const int ha = (z ? d1 : d0) / 2;                 // half width of output A
+  const int hb = dual ? d1 / 2 : ha;                // half width of output B (dual only)
+  const int hm = max(ha, hb);
+  const int W = CB_TPB - (2 * hm + 1);
   const int c0 = blockIdx.x * W;
-  const int col = c0 - h - 1 + t;                 // integral-image column scanned by this thread
+  const int col = c0 - hm - 1 + t;                  // integral-image column scanned by this thread
   const bool scan_ok = col >= 0 && col < cols;
-  const int oc = c0 + t;                          // output column of this thread (t < W)
+  const int oc = c0 + t;                            // output column of this thread (t < W)
   const bool out_ok = t < W && oc < cols;
   const float* src = rowsum + (size_t)blockIdx.y * in_plane_stride;
-  float* dst = out + (size_t)blockIdx.y * out_plane_stride;
+  float* dstA = out0 + (size_t)blockIdx.y * out_plane_stride;
+  float* dstB = out1 + (size_t)blockIdx.y * out_plane_stride;
   for (int i = t; i < 256; i += CB_TPB) {
     int a = i / 16, b = i % 16;
-    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171 (== `a` of :72 inside)
   }
-  const int chi = min(oc + h, cols - 1);
-  const int clo = oc - h - 1;
-  const int jhi = chi - (c0 - h - 1);             // ring column of the right tap
-  const int jlo = t;                              // ring column of the left tap (clo - (c0-h-1) == t)
-  const int ncol = chi - max(clo, -1);
+  // taps of output A / B in ring coordinates (ring column j <-> image column c0 - hm - 1 + j)
+  const int chiA = min(oc + ha, cols - 1), cloA = oc - ha - 1;
+  const int jhiA = chiA - (c0 - hm - 1), jloA = t + (hm - ha), ncolA = chiA - max(cloA, -1);
+  const int chiB = min(oc + hb, cols - 1), cloB = oc - hb - 1;
+  const int jhiB = chiB - (c0 - hm - 1), jloB = t + (hm - hb), ncolB = chiB - max(cloB, -1);
+  const bool leftA = cloA >= 0, leftB = cloB >= 0;
+  const float invA = out_ok ? (float)(1.0 / (double)((float)(2 * ha + 1) * (float)ncolA)) : 0.0f;
+  const float invB = out_ok ? (float)(1.0 / (double)((float)(2 * hb + 1) * (float)ncolB)) : 0.0f;
   float run = 0.0f;
   float nxt[CB_CH];
 #pragma unroll
@@ -112,32 +143,19 @@ __global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ row
 #pragma unroll
     for (int i = 0; i < CB_CH; ++i) {
       if (k0 + i < rows) {
-        run = (k0 + i == 0) ? cur[i] : run + cur[i];
+        run = (k0 + i == 0) ? cur[i] : run + cur[i];                                   // column pass :59-65
         ring[(k0 + i) & (CB_RING - 1)][t] = run;
       }
     }
     __syncthreads();
-    const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - h;   // last output row whose taps are all in the ring
+    const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;   // last output row whose taps are all in the ring
     if (out_ok) {
       for (int ro = onext; ro <= olast; ++ro) {
-        const int rhi = min(ro + h, rows - 1), rlo = ro - h - 1;
-        const bool bottom = ro + h >= rows;
-        const float* hi = ring[rhi & (CB_RING - 1)];
-        float v;
-        if (rlo < 0) {
-          v = (clo < 0) ? hi[jhi] : hi[jhi] - hi[jlo];
-        } else {
-          const float* lo = ring[rlo & (CB_RING - 1)];
-          if (clo < 0) v = hi[jhi] - lo[jhi];
-          else if (bottom) v = ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo];
-          else v = ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo];
-        }
-        const int nrow = rhi - max(rlo, -1);
-        dst[(size_t)ro * cols + oc] = v * inv_area[nrow][ncol];
+        dstA[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, ha, rows, jhiA, jloA, leftA, ncolA, invA);
+        if (dual) dstB[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, hb, rows, jhiB, jloB, leftB, ncolB, invB);
       }
     }
     onext = max(onext, olast + 1);
-    __syncthreads();
   }
 }
 
@@ -146,27 +164,22 @@ __global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ row
 int fe_scale_space(rbv_ctx* c, const float* d_img) {
   const int rows = c->P.rows, cols = c->P.cols, B = c->P.lanes;
   const size_t N = (size_t)c->P.npix;
-  // pass 0: one row prefix per lane, two column/box passes (d = widths[0][0], widths[1][0])
+  // pass 0: one row prefix per lane, one column scan feeding both box widths (widths[0][0], widths[1][0])
   {
-    dim3 g1((rows + 31) / 32, B);
-    RBV_LAUNCH(c, k_rowscan, (g1), (32), 0, d_img, c->rowsum, rows, cols, N, N);
-    for (int z = 0; z < 2; ++z) {
-      const int d = c->widths[z][0];
-      const int W = CB_TPB - (2 * (d / 2) + 1);
-      dim3 g2((cols + W - 1) / W, B);
-      RBV_LAUNCH(c, k_colbox, (g2), (CB_TPB), 0, c->rowsum, c->bufA + (size_t)z * N, rows, cols, N, 2 * N, 1, d, d);
-    }
+    RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, B)), (32), 0, d_img, c->rowsum, rows, cols, N, N);
+    const int d0 = c->widths[0][0], d1 = c->widths[1][0];
+    const int hmax = (d0 > d1 ? d0 : d1) / 2;
+    const int W = CB_TPB - (2 * hmax + 1);
+    RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, B)), (CB_TPB), 0, c->rowsum, c->bufA, c->bufA + N, rows, cols, N, 2 * N, 1, d0, d1, 1);
   }
   float* src = c->bufA;
   float* dst = c->bufB;
   for (int p = 1; p < 3; ++p) {
-    dim3 g1((rows + 31) / 32, 2 * B);
-    RBV_LAUNCH(c, k_rowscan, (g1), (32), 0, src, c->rowsum, rows, cols, N, N);
+    RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 2 * B)), (32), 0, src, c->rowsum, rows, cols, N, N);
     const int d0 = c->widths[0][p], d1 = c->widths[1][p];
     const int hmax = (d0 > d1 ? d0 : d1) / 2;
     const int W = CB_TPB - (2 * hmax + 1);
-    dim3 g2((cols + W - 1) / W, 2 * B);
-    RBV_LAUNCH(c, k_colbox, (g2), (CB_TPB), 0, c->rowsum, dst, rows, cols, N, N, 2, d0, d1);
+    RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 2 * B)), (CB_TPB), 0, c->rowsum, dst, dst, rows, cols, N, N, 2, d0, d1, 0);
     float* t = src; src = dst; dst = t;
   }
   // after passes 1 and 2 the result is back in bufA
@@ -181,7 +194,7 @@ int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float*
   RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 1)), (32), 0, d_in, c->rowsum, rows, cols, N, N);
   const int d = c->widths[scale][pass];
   const int W = CB_TPB - (2 * (d / 2) + 1);
-  RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 1)), (CB_TPB), 0, c->rowsum, d_out, rows, cols, N, N, 1, d, d);
+  RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 1)), (CB_TPB), 0, c->rowsum, d_out, d_out, rows, cols, N, N, 1, d, d, 0);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -213,23 +226,31 @@ __device__ __forceinline__ bool rbv_fit_plane(const float* y, const DevParams& P
   return true;
 }
 
-// Pass 1: flags. Block = 8 warps, tile = 8 rows x 32 columns (one flag word per warp); DoG = s1 - s0 is formed in shared
-// memory (never written to HBM), the squared gradient magnitude comes from the s0 tile. Also resets the id mask.
-#define DT_ROWS 8
+// Pass 1: flags. Block = 256 threads, tile = 16 rows x 64 columns (+2 halo). DoG = s1 - s0 is formed in shared memory (never
+// written to HBM), the squared gradient magnitude comes from the s0 tile. Phase A: every pixel takes the cheap magnitude
+// test (:83) and the survivors are compacted into a shared-memory list; phase B: the threads work through that list
+// densely, so the 25-tap sign count and plane fit (:85-107) run without divergence. Accepted pixels set their bit in the
+// per-row flag words and park (theta0, theta1, xs, ys) in the fit buffer for the emit pass. Also resets the id mask.
+#define DT_W 64
+#define DT_H 16
+#define DT_PITCH (DT_W + 5)
 __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ scales, const float* __restrict__ thr_dev,
                                                       unsigned* __restrict__ flags, int* __restrict__ rowcount, int* __restrict__ mask,
-                                                      const __grid_constant__ DevParams P, int wpr) {
-  __shared__ float s0t[DT_ROWS + 4][36];
-  __shared__ float dogt[DT_ROWS + 4][36];
+                                                      float4* __restrict__ fit, const __grid_constant__ DevParams P, int wpr) {
+  __shared__ float s0t[DT_H + 4][DT_PITCH];
+  __shared__ float dogt[DT_H + 4][DT_PITCH];
+  __shared__ unsigned short cand[DT_W * DT_H];
+  __shared__ unsigned sflags[DT_H][2];
+  __shared__ int ncand;
   const int b = blockIdx.z;
   const int rows = P.rows, cols = P.cols;
   const size_t N = (size_t)P.npix;
   const float* s0 = scales + (size_t)(b * 2) * N;
   const float* s1 = s0 + N;
-  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * DT_ROWS;
-  const int tid = threadIdx.y * 32 + threadIdx.x;
-  for (int i = tid; i < (DT_ROWS + 4) * 36; i += 256) {
-    const int tr = i / 36, tc = i % 36;
+  const int c0 = blockIdx.x * DT_W, r0 = blockIdx.y * DT_H;
+  const int tid = threadIdx.x, lane = tid & 31;
+  for (int i = tid; i < (DT_H + 4) * (DT_W + 4); i += 256) {
+    const int tr = i / (DT_W + 4), tc = i % (DT_W + 4);
     const int r = r0 - 2 + tr, q = c0 - 2 + tc;
     float a = 0.0f, d = 0.0f;
     if (r >= 0 && r < rows && q >= 0 && q < cols) {
@@ -239,34 +260,61 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
     s0t[tr][tc] = a;
     dogt[tr][tc] = d;
   }
+  if (tid < DT_H * 2) sflags[tid >> 1][tid & 1] = 0u;
+  if (tid == 0) ncand = 0;
   __syncthreads();
-  const int r = r0 + threadIdx.y, q = c0 + threadIdx.x;
-  bool cand = false;
-  if (r < rows && q < cols) mask[(size_t)b * N + (size_t)r * cols + q] = -1;
-  if (r >= 2 && r < rows - 2 && q >= 2 && q < cols - 2) {
-    const float thr = thr_dev[b];
-    const float tm = thr * 765.0f;
-    const float mag_threshold = tm * tm;                                               // edge_detector.cpp:71
-    const float tg = tm * P.dog_threshold;
-    const float gts = tg * tg;                                                         // :70
-    const int tr = threadIdx.y + 2, tc = threadIdx.x + 2;
-    const float dx = s0t[tr][tc + 1] - s0t[tr][tc - 1];
-    const float dy = s0t[tr + 1][tc] - s0t[tr - 1][tc];
-    const float mag = dx * dx + dy * dy;                                               // scale_space.cpp:228-230
-    if (!(mag < mag_threshold)) {                                                      // :83
-      float y[25];
+  const float thr = thr_dev[b];
+  const float tm = thr * 765.0f;
+  const float mag_threshold = tm * tm;                                                 // edge_detector.cpp:71
+  const float tg = tm * P.dog_threshold;
+  const float gts = tg * tg;                                                           // :70
 #pragma unroll
-      for (int dr = 0; dr < 5; ++dr)
+  for (int i = 0; i < (DT_W * DT_H) / 256; ++i) {
+    const int p = tid + i * 256;
+    const int pr = p / DT_W, pc = p % DT_W;
+    const int r = r0 + pr, q = c0 + pc;
+    bool c = false;
+    if (r < rows && q < cols) {
+      mask[(size_t)b * N + (size_t)r * cols + q] = -1;
+      if (r >= 2 && r < rows - 2 && q >= 2 && q < cols - 2) {
+        const int tr = pr + 2, tc = pc + 2;
+        const float dx = s0t[tr][tc + 1] - s0t[tr][tc - 1];
+        const float dy = s0t[tr + 1][tc] - s0t[tr - 1][tc];
+        const float mag = dx * dx + dy * dy;                                           // scale_space.cpp:228-230
+        c = !(mag < mag_threshold);                                                    // :83
+      }
+    }
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, c);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(&ncand, __popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (c) cand[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)p;
+  }
+  __syncthreads();
+  const int nc = ncand;
+  for (int i = tid; i < nc; i += 256) {
+    const int p = cand[i];
+    const int pr = p / DT_W, pc = p % DT_W;
+    float y[25];
 #pragma unroll
-        for (int dc = 0; dc < 5; ++dc) y[dr * 5 + dc] = dogt[tr - 2 + dr][tc - 2 + dc];
-      FitResult fr;
-      cand = rbv_fit_plane(y, P, gts, fr);
+    for (int dr = 0; dr < 5; ++dr)
+#pragma unroll
+      for (int dc = 0; dc < 5; ++dc) y[dr * 5 + dc] = dogt[pr + dr][pc + dc];
+    FitResult fr;
+    if (rbv_fit_plane(y, P, gts, fr)) {
+      atomicOr(&sflags[pr][pc >> 5], 1u << (pc & 31));
+      fit[(size_t)b * N + (size_t)(r0 + pr) * cols + (c0 + pc)] = make_float4(fr.th0, fr.th1, fr.xs, fr.ys);
     }
   }
-  const unsigned word = __ballot_sync(0xFFFFFFFFu, cand);
-  if (threadIdx.x == 0 && r < rows) {
-    flags[((size_t)b * rows + r) * wpr + blockIdx.x] = word;
-    if (word) atomicAdd(&rowcount[b * rows + r], __popc(word));
+  __syncthreads();
+  if (tid < DT_H * 2) {
+    const int pr = tid >> 1, w = blockIdx.x * 2 + (tid & 1);
+    const int r = r0 + pr;
+    if (r < rows && w < wpr) flags[((size_t)b * rows + r) * wpr + w] = sflags[pr][tid & 1];
+    if ((tid & 1) == 0 && r < rows) {
+      const int cnt = __popc(sflags[pr][0]) + __popc(sflags[pr][1]);
+      if (cnt) atomicAdd(&rowcount[b * rows + r], cnt);
+    }
   }
 }
 
@@ -297,20 +345,16 @@ __global__ void __launch_bounds__(1024) k_detect_scan(const int* __restrict__ ro
 }
 
 // Pass 3: emit keylines in row-major id order (edge_detector.cpp:109-119, KeyLine ctor types/keyline.hpp:42-59).
-// One warp per image row: lane l owns flag word l (+32 per round); ids = row offset + prefix popcount.
-__global__ void __launch_bounds__(32) k_detect_emit(const float* __restrict__ scales, const float* __restrict__ thr_dev,
-                                                    const unsigned* __restrict__ flags, const int* __restrict__ rowoffset, KeylineSoA K,
-                                                    int* __restrict__ mask, const __grid_constant__ DevParams P, int wpr) {
+// One warp per image row: lane l owns flag word l (+32 per round); ids = row offset + prefix popcount. The plane-fit
+// results parked by pass 1 are read back (16 B per keyline), nothing is re-fitted.
+__global__ void __launch_bounds__(32) k_detect_emit(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
+                                                    const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
+                                                    const __grid_constant__ DevParams P, int wpr) {
   const int b = blockIdx.y, r = blockIdx.x + 2, lane = threadIdx.x;
   const int rows = P.rows, cols = P.cols, kmax = P.kmax;
   const size_t N = (size_t)P.npix;
   int base = rowoffset[b * rows + r];
   if (base >= P.keylines_max) return;
-  const float* s0 = scales + (size_t)(b * 2) * N;
-  const float* s1 = s0 + N;
-  const float thr = thr_dev[b];
-  const float tg = thr * 765.0f * P.dog_threshold;
-  const float gts = tg * tg;
   for (int w0 = 0; w0 < wpr; w0 += 32) {
     const int w = w0 + lane;
     unsigned word = (w < wpr) ? flags[((size_t)b * rows + r) * wpr + w] : 0u;
@@ -328,31 +372,22 @@ __global__ void __launch_bounds__(32) k_detect_emit(const float* __restrict__ sc
       word &= word - 1;
       if (id < P.keylines_max) {
         const int q = w * 32 + bit;
-        float y[25];
-#pragma unroll
-        for (int dr = 0; dr < 5; ++dr)
-#pragma unroll
-          for (int dc = 0; dc < 5; ++dc) {
-            const size_t o = (size_t)(r - 2 + dr) * cols + (q - 2 + dc);
-            y[dr * 5 + dc] = s1[o] - s0[o];
-          }
-        FitResult fr;
-        rbv_fit_plane(y, P, gts, fr);  // same arithmetic as pass 1 -> true by construction
-        const float px = (float)q + fr.xs, py = (float)r + fr.ys;                      // :109
+        const unsigned pix = (unsigned)(r * cols + q);
+        const float4 fr = fit[(size_t)b * N + pix];                                     // (theta0, theta1, xs, ys)
+        const float px = (float)q + fr.z, py = (float)r + fr.w;                         // :109
         const size_t o = (size_t)b * kmax + id;
         K.pos[o] = make_float2(px, py);
         const float2 pi = make_float2(px - P.cx, py - P.cy);                            // :110
         K.pos_img[o] = pi;
         K.match_pos_img[o] = pi;
-        K.grad[o] = make_float2(fr.th0, fr.th1);
+        K.grad[o] = make_float2(fr.x, fr.y);
         K.match_grad[o] = make_float2(0.0f, 0.0f);
-        K.gnorm[o] = sqrtf(fr.th0 * fr.th0 + fr.th1 * fr.th1);
+        K.gnorm[o] = sqrtf(fr.x * fr.x + fr.y * fr.y);
         K.match_gnorm[o] = 0.0f;
         K.rho[o] = RBV_RHO_INIT;
         K.srho[o] = RBV_RHO_MAX;
         K.id_prev[o] = -1; K.id_next[o] = -1; K.match_id[o] = -1; K.match_fwd[o] = -1; K.match_kf[o] = -1;
         K.matches[o] = 0u;
-        const unsigned pix = (unsigned)(r * cols + q);
         K.pixel[o] = pix;
         K.residual[o] = 0.0f;
         mask[(size_t)b * N + pix] = id;                                                 // :111-112
@@ -416,10 +451,11 @@ int fe_detect(rbv_ctx* c, rbv_map* map) {
   const int B = P.lanes, rows = P.rows, cols = P.cols;
   const int wpr = (cols + 31) / 32;
   { int rc = rbv_fill32(c, c->rowcount, 0u, (size_t)B * rows); if (rc != RBV_OK) return rc; }
-  dim3 g1(wpr, (rows + DT_ROWS - 1) / DT_ROWS, B);
-  RBV_LAUNCH(c, k_detect_flags, (g1), (dim3(32, DT_ROWS)), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, P, wpr);
+  dim3 g1((cols + DT_W - 1) / DT_W, (rows + DT_H - 1) / DT_H, B);
+  float4* fit = reinterpret_cast<float4*>(c->rowsum);   // rowsum + bufB are one contiguous 4*B*N float scratch, free after the scale space
+  RBV_LAUNCH(c, k_detect_flags, (g1), (256), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, fit, P, wpr);
   RBV_LAUNCH(c, k_detect_scan, (B), (1024), 0, c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
-  RBV_LAUNCH(c, k_detect_emit, (dim3(rows - 4, B)), (32), 0, c->bufA, c->thr_dev, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+  RBV_LAUNCH(c, k_detect_emit, (dim3(rows - 4, B)), (32), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
   RBV_LAUNCH(c, k_join, (dim3((P.kmax + 255) / 256, B)), (256), 0, map->k, map->count, map->mask, P);
   RBV_LAUNCH(c, k_tune, (B), (1024), 0, map->k, map->count, map->threshold, P.kmax);
   RBV_CUDA(cudaGetLastError());

@@ -117,6 +117,12 @@ struct rbv_ctx {
   float* lane_out;  // [B][64] per-call lane outputs
   int* lane_cnt;    // [B][8] counters (matches, kf, regularised ...)
   unsigned long long* probes;  // [B]
+  // FAST-mode reductions: per-block FP64 partials, per-lane tickets, per-block "last matched |fi|" (ping-pong)
+  double* partials;  // [B][nblk][27]
+  unsigned* ticket;  // [B]
+  float* blkagg;     // [2][B][nblk]
+  int nblk;          // blocks of 256 keylines per lane
+  int tv_parity;
   // pinned host staging
   float* h_in;
   float* h_out;
@@ -142,7 +148,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_fill) X(k_rowscan) X(k_colbox) X(k_detect_flags) X(k_detect_scan) X(k_detect_emit) X(k_join) X(k_tune)       \
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
-  X(k_kalman) X(k_lm_init) X(k_gate_min_matches)
+  X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)

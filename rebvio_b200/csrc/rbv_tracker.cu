@@ -6,10 +6,10 @@
 //   DistanceField::build                 rebvio/include/rebvio/core.hpp:37-59      -> k_field_build (packed atomicMin)
 //   EdgeMap::rotateKeylines              rebvio/src/edge_map.cpp:58-71             -> k_rotate
 //   EdgeMap::estimateQuantile            rebvio/src/edge_map.cpp:39-56             -> k_quantile
-//   Core::tryVel/calculatefJ/testfk      rebvio/src/core.cpp:39-148                -> k_tryvel_eval + k_tryvel_reduce
-//   Core::minimizeVel                    rebvio/src/core.cpp:150-189               -> LM step at the tail of k_tryvel_reduce
+//   Core::tryVel/calculatefJ/testfk      rebvio/src/core.cpp:39-148                -> k_tryvel_fast (FAST) | k_tryvel_eval + k_tryvel_reduce (ORDERED)
+//   Core::minimizeVel                    rebvio/src/core.cpp:150-189               -> LM step at the tail of k_tryvel_fast / k_tryvel_reduce
 //   EdgeMap::forwardMatch                rebvio/src/edge_map.cpp:73-99             -> k_fwd_link + k_fwd_resolve
-//   Core::extRotVel                      rebvio/src/core.cpp:191-261               -> k_extrot_rows + k_extrot_reduce
+//   Core::extRotVel                      rebvio/src/core.cpp:191-261               -> k_extrot_fast (FAST) | k_extrot_rows + k_extrot_reduce (ORDERED)
 //   EdgeMap::directedMatch/searchMatch   rebvio/src/edge_map.cpp:101-218           -> k_directed
 //   EdgeMap::regularize1Iter             rebvio/src/edge_map.cpp:220-259           -> k_reg_eval + k_reg_apply
 //   Core::updateInverseDepth(ARLU)       rebvio/src/core.cpp:417-456               -> k_kalman
@@ -19,30 +19,37 @@
 #include "rbv_internal.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void k_field_build(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
-                              unsigned* __restrict__ field, const __grid_constant__ DevParams P) {
+// One thread per keyline walks its normal line in |r| order (0, -1, 1, -2, 2, ...): the two divisions are done once per
+// keyline, neighbouring threads are neighbouring keylines (coalesced SoA reads, nearby cells), and because every thread
+// writes its nearest cells first, most far candidates are rejected by a plain load before they cost an atomic.
+__global__ void __launch_bounds__(128) k_field_build(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
+                                                     unsigned* __restrict__ field, const __grid_constant__ DevParams P) {
   const int b = blockIdx.y;
-  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
-  const int idx = gi / P.field_nr, ri = gi - idx * P.field_nr;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count[b]) return;
   const size_t o = (size_t)b * P.kmax + idx;
   const float gn = K.gnorm[o];
   const float thr = threshold[b];
   if (thr > 0.0f && gn < thr) return;                                                  // core.hpp:47
-  const int r = P.field_r0 + ri;                                                       // r = -search_range .. search_range-1
   const float2 g = K.grad[o], p = K.pos[o];
-  const int fi = rbv_pixel_index(P.rows, P.cols, (g.y / gn) * (float)r + p.y, (g.x / gn) * (float)r + p.x);  // :50-51
-  if (fi < 0) return;
-  // sequential rule (:54-56): smallest |r| wins, ties go to the later (idx, r) -> min over (|r|, -idx)
-  const unsigned key = ((unsigned)abs(r) << 24) | (0xFFFFFFu - (unsigned)idx);
-  atomicMin(&field[(size_t)b * P.npix + fi], key);
+  const float ux = g.x / gn, uy = g.y / gn;
+  unsigned* f = field + (size_t)b * P.npix;
+  const unsigned lowkey = 0xFFFFFFu - (unsigned)idx;
+  for (int j = 0; j < P.field_nr; ++j) {
+    const int r = (j & 1) ? -((j + 1) >> 1) : (j >> 1);   // bijection onto [-a, a-1] (nr = 2a) or [-a, a] (nr = 2a+1)
+    const int fi = rbv_pixel_index(P.rows, P.cols, uy * (float)r + p.y, ux * (float)r + p.x);  // :50-51
+    if (fi < 0) continue;
+    // sequential rule (:54-56): smallest |r| wins, ties go to the later (idx, r) -> min over (|r|, -idx)
+    const unsigned key = ((unsigned)abs(r) << 24) | lowkey;
+    if (__ldcg(f + fi) <= key) continue;         // cells only ever decrease: a stale read can only let a loser through to the atomic
+    atomicMin(f + fi, key);
+  }
 }
 
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
-  const long long work = (long long)P.keylines_max * P.field_nr;
-  RBV_LAUNCH(c, k_field_build, (dim3((unsigned)((work + 255) / 256), P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field, P);
+  RBV_LAUNCH(c, k_field_build, (dim3((P.keylines_max + 127) / 128, P.lanes)), (128), 0, map->k, map->count, map->threshold, c->field, P);
   c->field_map = map;
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
@@ -130,9 +137,81 @@ int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// tryVel, per-keyline part. Addends (zero for skipped keylines: x + 0 == x exactly) go to prod[10][B][kmax]:
+// tryVel, per-keyline part (core.cpp:86-141). Addends (zero for skipped keylines: x + 0 == x exactly):
 //   0 score f*f | 1..6 JtJ 00,11,22,01,02,12 | 7..9 JtF 0,1,2
-// fiabs code for the residual rule: >= 0 matched (|fi|), -1 in-image but unmatched, -2 no residual write.
+// code for the residual rule: >= 0 matched (|fi|), -1 in-image but unmatched, -2 no residual write.
+struct TryVelIn {
+  float v0, v1, v2, sigma_rho_min, thr;
+};
+__device__ __forceinline__ void tryvel_point(const KeylineSoA& Ko, const KeylineSoA& Kn, const unsigned* __restrict__ field_b,
+                                             size_t o, size_t base, float res, const TryVelIn& in, const DevParams& P,
+                                             float* add, float& code, int& fwd) {
+#pragma unroll
+  for (int a = 0; a < 10; ++a) add[a] = 0.0f;
+  code = -2.0f;
+  fwd = -1;
+  const float v0 = in.v0, v1 = in.v1, v2 = in.v2;
+  const float gn = Ko.gnorm[o];
+  const float srho = Ko.srho[o];
+  const bool skip = (in.thr > 0.0f && gn < in.thr) || (srho > in.sigma_rho_min) || (Ko.matches[o] < P.min_matches);   // core.cpp:88,91
+  if (skip) return;
+  float w = 1.0f;
+  if (res > P.reweight_distance) w = P.reweight_distance / res;                        // :94
+  const float rho = Ko.rho[o];
+  const float z_p = (float)(1.0 / (double)rho + (double)v2);                           // :96
+  const float2 pi = Ko.pos_img[o];
+  bool penalty = z_p <= 0.0f;
+  float rho_p = 0.0f, px = 0.0f, py = 0.0f, pxc = 0.0f, pyc = 0.0f;
+  int x = 0, y = 0;
+  if (!penalty) {
+    rho_p = (float)(1.0 / (double)z_p);                                                // :104
+    px = rho_p * (v0 * P.fm - v2 * pi.x) + pi.x;                                       // :105
+    py = rho_p * (v1 * P.fm - v2 * pi.y) + pi.y;
+    pxc = px + P.cx; pyc = py + P.cy;
+    x = rbv_d2i((double)pxc + 0.5);                                                    // :111
+    y = rbv_d2i((double)pyc + 0.5);
+    penalty = (x < 1 || y < 1 || x >= P.cols - 1 || y >= P.rows - 1);                  // :114
+  }
+  if (penalty) {
+    const float f = (float)((1.0 / (double)srho) * (double)P.search_range * (double)w);   // :99 / :115
+    add[0] = f * f;
+    return;
+  }
+  float dfx = 0.0f, dfy = 0.0f, f;
+  bool matched = false;
+  const unsigned cell = field_b[(size_t)y * P.cols + x];
+  if (cell != RBV_FIELD_EMPTY) {
+    const int tid = (int)(0xFFFFFFu - (cell & 0xFFFFFFu));
+    const size_t to = base + tid;
+    const float2 tg = Kn.grad[to];
+    const float2 g = Ko.grad[o];
+    const float n2 = gn * gn;                                                          // testfk :40-42
+    const float dp = tg.x * g.x + tg.y * g.y;
+    if (!(fabsf(dp - n2) > P.match_treshold * n2)) {
+      matched = true;
+      const float2 tp = Kn.pos[to];
+      const float tgn = Kn.gnorm[to];
+      const float dx = pxc - tp.x, dy = pyc - tp.y;                                    // :62-63
+      const float gnx = tg.x / tgn, gny = tg.y / tgn;
+      const float fi = dx * gnx + dy * gny;                                            // :67
+      dfx = gnx / srho; dfy = gny / srho;
+      fwd = tid;                                                                       // :73
+      f = fi / srho;                                                                   // :75
+      code = fabsf(fi);                                                                // :141
+    }
+  }
+  if (!matched) { f = P.search_range / srho; code = -1.0f; }                           // :52 / :59
+  f *= w;
+  add[0] = f * f;
+  const float jx = rho_p * P.fm * dfx * w;                                             // :126-128
+  const float jy = rho_p * P.fm * dfy * w;
+  const float jz = -rho_p * (px * dfx + py * dfy) * w;
+  add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
+  add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
+  add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
+}
+
+// ORDERED mode, phase 1: addends to prod[10][B][kmax], residual code to fiabs
 __global__ void __launch_bounds__(256) k_tryvel_eval(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
                                                      KeylineSoA Kn, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
                                                      int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
@@ -140,76 +219,15 @@ __global__ void __launch_bounds__(256) k_tryvel_eval(KeylineSoA Ko, const int* _
                                                      const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count_o[b]) return;
-  const size_t o = (size_t)b * P.kmax + idx;
+  const size_t base = (size_t)b * P.kmax, o = base + idx;
   const size_t ps = (size_t)P.lanes * P.kmax;
-  const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
-  const float sigma_rho_min = sr_ptr[(size_t)b * sr_stride];
-  float add[10];
-#pragma unroll
-  for (int a = 0; a < 10; ++a) add[a] = 0.0f;
-  float code = -2.0f;
-  int fwd = -1;
-  const float thr = thr_o[b];
-  const float gn = Ko.gnorm[o];
-  const float srho = Ko.srho[o];
-  const bool skip = (thr > 0.0f && gn < thr) || (srho > sigma_rho_min) || (Ko.matches[o] < P.min_matches);   // core.cpp:88,91
-  if (!skip) {
-    float w = 1.0f;
-    const float res = Ko.residual[o];
-    if (res > P.reweight_distance) w = P.reweight_distance / res;                        // :94
-    const float rho = Ko.rho[o];
-    const float z_p = (float)(1.0 / (double)rho + (double)v2);                           // :96
-    const float2 pi = Ko.pos_img[o];
-    bool penalty = z_p <= 0.0f;
-    float rho_p = 0.0f, px = 0.0f, py = 0.0f, pxc = 0.0f, pyc = 0.0f;
-    int x = 0, y = 0;
-    if (!penalty) {
-      rho_p = (float)(1.0 / (double)z_p);                                                // :104
-      px = rho_p * (v0 * P.fm - v2 * pi.x) + pi.x;                                       // :105
-      py = rho_p * (v1 * P.fm - v2 * pi.y) + pi.y;
-      pxc = px + P.cx; pyc = py + P.cy;
-      x = rbv_d2i((double)pxc + 0.5);                                                    // :111
-      y = rbv_d2i((double)pyc + 0.5);
-      penalty = (x < 1 || y < 1 || x >= P.cols - 1 || y >= P.rows - 1);                  // :114
-    }
-    if (penalty) {
-      const float f = (float)((1.0 / (double)srho) * (double)P.search_range * (double)w);   // :99 / :115
-      add[0] = f * f;
-    } else {
-      float dfx = 0.0f, dfy = 0.0f, f;
-      bool matched = false;
-      const unsigned cell = field[(size_t)b * P.npix + (size_t)y * P.cols + x];
-      if (cell != RBV_FIELD_EMPTY) {
-        const int tid = (int)(0xFFFFFFu - (cell & 0xFFFFFFu));
-        const size_t to = (size_t)b * P.kmax + tid;
-        const float2 tg = Kn.grad[to];
-        const float2 g = Ko.grad[o];
-        const float n2 = gn * gn;                                                        // testfk :40-42
-        const float dp = tg.x * g.x + tg.y * g.y;
-        if (!(fabsf(dp - n2) > P.match_treshold * n2)) {
-          matched = true;
-          const float2 tp = Kn.pos[to];
-          const float tgn = Kn.gnorm[to];
-          const float dx = pxc - tp.x, dy = pyc - tp.y;                                  // :62-63
-          const float gnx = tg.x / tgn, gny = tg.y / tgn;
-          const float fi = dx * gnx + dy * gny;                                          // :67
-          dfx = gnx / srho; dfy = gny / srho;
-          fwd = tid;                                                                     // :73
-          f = fi / srho;                                                                 // :75
-          code = fabsf(fi);                                                              // :141
-        }
-      }
-      if (!matched) { f = P.search_range / srho; code = -1.0f; }                         // :52 / :59
-      f *= w;
-      add[0] = f * f;
-      const float jx = rho_p * P.fm * dfx * w;                                           // :126-128
-      const float jy = rho_p * P.fm * dfy * w;
-      const float jz = -rho_p * (px * dfx + py * dfy) * w;
-      add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
-      add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
-      add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
-    }
-  }
+  TryVelIn in;
+  in.v0 = vel_ptr[(size_t)b * vel_stride]; in.v1 = vel_ptr[(size_t)b * vel_stride + 1]; in.v2 = vel_ptr[(size_t)b * vel_stride + 2];
+  in.sigma_rho_min = sr_ptr[(size_t)b * sr_stride];
+  in.thr = thr_o[b];
+  float add[10], code;
+  int fwd;
+  tryvel_point(Ko, Kn, field + (size_t)b * P.npix, o, base, Ko.residual[o], in, P, add, code, fwd);
   Ko.match_fwd[o] = fwd;                                                                 // :87
   fiabs[o] = code;
 #pragma unroll
@@ -378,6 +396,126 @@ __global__ void __launch_bounds__(1024) k_tryvel_reduce(KeylineSoA Ko, const int
   }
 }
 
+// ---- RBV_REDUCE_FAST: tryVel in ONE kernel -----------------------------------------------------------------------------
+// grid (blocks of 256 keylines, lanes). Each block evaluates its keylines, reduces the ten addends in FP64 (shuffle tree
+// + fixed warp order) into partials[lane][block][10]; the block that takes the last ticket of its lane adds the block
+// partials in block order (a fixed order -> deterministic) and runs the LM step. The reference's carried residual
+// ("an in-image unmatched keyline stores |fi| of the most recent matched keyline") is resolved inside the block; a
+// keyline with no earlier match in its block stores the marker -1 and looks back over the previous blocks' "last
+// matched |fi|" (blkagg, ping-pong per call) when the next call reads it. k_residual_resolve clears the markers after
+// the last call so the map never leaves the library with one.
+#define TV_TPB 256
+__device__ __forceinline__ float residual_lookback(const float* __restrict__ agg_lane, int blk) {
+  for (int j = blk - 1; j >= 0; --j) {
+    const float a = __ldcg(agg_lane + j);
+    if (a >= 0.0f) return a;
+  }
+  return 0.0f;
+}
+
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
+                                                        KeylineSoA Kn, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
+                                                        int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
+                                                        double* __restrict__ partials, unsigned* __restrict__ ticket,
+                                                        const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
+                                                        LMState* lm, float* lane_out, int lm_call, const __grid_constant__ DevParams P) {
+  __shared__ double sm[(TV_TPB / 32) * 10];
+  __shared__ double result[10];
+  __shared__ float warp_val[TV_TPB / 32];
+  __shared__ int warp_has[TV_TPB / 32];
+  __shared__ int s_last;
+  const int b = blockIdx.y, n = count_o[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int nact = max(1, (n + TV_TPB - 1) / TV_TPB);
+  if ((int)blockIdx.x >= nact) return;
+  const int idx = blockIdx.x * TV_TPB + t;
+  const size_t base = (size_t)b * P.kmax, o = base + idx;
+  float add[10], code = -2.0f, res = 0.0f;
+  bool was_pending = false;
+#pragma unroll
+  for (int a = 0; a < 10; ++a) add[a] = 0.0f;
+  if (idx < n) {
+    TryVelIn in;
+    in.v0 = vel_ptr[(size_t)b * vel_stride]; in.v1 = vel_ptr[(size_t)b * vel_stride + 1]; in.v2 = vel_ptr[(size_t)b * vel_stride + 2];
+    in.sigma_rho_min = sr_ptr[(size_t)b * sr_stride];
+    in.thr = thr_o[b];
+    res = Ko.residual[o];
+    if (res < 0.0f) { was_pending = true; res = residual_lookback(agg_prev + (size_t)b * nblk, blockIdx.x); }
+    int fwd;
+    tryvel_point(Ko, Kn, field + (size_t)b * P.npix, o, base, res, in, P, add, code, fwd);
+    Ko.match_fwd[o] = fwd;                                                               // core.cpp:87
+  }
+  // carried |fi| inside the block, keyline order
+  int has = code >= 0.0f;
+  float val = has ? code : 0.0f;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int h2 = __shfl_up_sync(0xFFFFFFFFu, has, off);
+    const float v2 = __shfl_up_sync(0xFFFFFFFFu, val, off);
+    if (lane >= off && !has) { has = h2; val = v2; }
+  }
+  if (lane == 31) { warp_has[warp] = has; warp_val[warp] = val; }
+  // ten sums: shuffle tree per warp
+#pragma unroll
+  for (int a = 0; a < 10; ++a) {
+    double v = (double)add[a];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+    if (lane == 0) sm[warp * 10 + a] = v;
+  }
+  __syncthreads();
+  if (!has) {
+    for (int w = warp - 1; w >= 0; --w)
+      if (warp_has[w]) { has = 1; val = warp_val[w]; break; }
+  }
+  if (idx < n) {
+    if (code >= -1.5f) Ko.residual[o] = has ? val : (blockIdx.x == 0 ? 0.0f : -1.0f);    // core.cpp:141 (-1 = look back next time)
+    else if (was_pending) Ko.residual[o] = res;                                          // no write this call: keep the resolved value
+  }
+  if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blockIdx.x] = has ? val : -1.0f;
+  if (t < 10) {
+    double s2 = 0.0;
+#pragma unroll
+    for (int w = 0; w < TV_TPB / 32; ++w) s2 += sm[w * 10 + t];
+    partials[((size_t)b * nblk + blockIdx.x) * 10 + t] = s2;
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) s_last = (atomicAdd(&ticket[b], 1u) == (unsigned)(nact - 1));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (t < 10) {
+    double s2 = 0.0;
+    for (int j = 0; j < nact; ++j) s2 += __ldcg(partials + ((size_t)b * nblk + j) * 10 + t);
+    result[t] = s2;
+  }
+  __syncthreads();
+  if (t == 0) {
+    ticket[b] = 0u;
+    float JtJ[9], JtF[3];
+    const float score = (float)result[0];
+    JtJ[0] = (float)result[1]; JtJ[4] = (float)result[2]; JtJ[8] = (float)result[3];
+    JtJ[1] = JtJ[3] = (float)result[4]; JtJ[2] = JtJ[6] = (float)result[5]; JtJ[5] = JtJ[7] = (float)result[6];
+    JtF[0] = (float)result[7]; JtF[1] = (float)result[8]; JtF[2] = (float)result[9];
+    if (lm_call >= 0) {
+      float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
+      lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
+    }
+    float* out = lane_out + (size_t)b * OUT_STRIDE;
+    for (int i = 0; i < 9; ++i) out[OUT_JTJ + i] = JtJ[i];
+    for (int i = 0; i < 3; ++i) out[OUT_JTF + i] = JtF[i];
+    out[OUT_SCORE] = score;
+  }
+}
+
+__global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
+                                                             int nblk, int kmax) {
+  const int b = blockIdx.y, idx = blockIdx.x * TV_TPB + threadIdx.x;
+  if (idx >= count_o[b]) return;
+  const size_t o = (size_t)b * kmax + idx;
+  if (Ko.residual[o] < 0.0f) Ko.residual[o] = residual_lookback(agg + (size_t)b * nblk, blockIdx.x);
+}
+
 // lm_call = -1: single evaluation at lane_in vel / sigma_rho_min; 0: first LM call at lm.vel; >= 1: at lm.vnew
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
   const DevParams& P = c->P;
@@ -393,8 +531,19 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     sr_ptr = lmf + offsetof(LMState, sigma_rho_min) / sizeof(float);
     sr_stride = lm_floats;
   }
-  RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
-  RBV_LAUNCH(c, k_tryvel_reduce, (P.lanes), (1024), 0, map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, c->reduce_mode == RBV_REDUCE_ORDERED, P);
+  if (c->reduce_mode == RBV_REDUCE_ORDERED) {
+    RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
+    RBV_LAUNCH(c, k_tryvel_reduce, (P.lanes), (1024), 0, map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, 1, P);
+  } else {
+    const int nblk = c->nblk;
+    const size_t half = (size_t)P.lanes * nblk;
+    float* agg_cur = c->blkagg + (size_t)c->tv_parity * half;
+    const float* agg_prev = c->blkagg + (size_t)(1 - c->tv_parity) * half;
+    RBV_LAUNCH(c, k_tryvel_fast, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P);
+    if (lm_call < 0 || lm_call == P.iterations)
+      RBV_LAUNCH(c, k_residual_resolve, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_cur, nblk, P.kmax);
+    c->tv_parity = 1 - c->tv_parity;
+  }
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -473,6 +622,38 @@ int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
 
 // ---------------------------------------------------------------------------------------------------------------
 // extRotVel rows (core.cpp:202-236): Phi_j (6) and Y_j after the division by s_y*weight; zeros for unmatched keylines.
+__device__ __forceinline__ void extrot_row(const KeylineSoA& K, size_t o, float v0, float v1, float v2, const DevParams& P, float* phi) {
+#pragma unroll
+  for (int a = 0; a < 7; ++a) phi[a] = 0.0f;
+  if (K.match_id[o] < 0) return;
+  const float fm = P.fm;
+  const float2 g = K.grad[o];
+  const float gn = K.gnorm[o];
+  const float ux = g.x / gn, uy = g.y / gn;                                            // :207-208
+  const float rho_t = (float)(1.0 / (1.0 / (double)K.rho[o] + (double)v2));            // :210
+  const float2 m = K.match_pos_img[o];
+  const float qtx = m.x + rho_t * (v0 * fm - v2 * m.x);                                // :211-212
+  const float qty = m.y + rho_t * (v1 * fm - v2 * m.y);
+  const float2 q = K.pos_img[o];
+  phi[0] = ux * rho_t * fm;                                                            // :217-222
+  phi[1] = uy * rho_t * fm;
+  phi[2] = ux * (-rho_t * q.x) + uy * (-rho_t * q.y);
+  phi[3] = -ux * q.x * q.y / fm - uy * (fm + q.y * q.y / fm);
+  phi[4] = uy * q.x * q.y / fm + ux * (fm + q.x * q.x / fm);
+  phi[5] = -ux * q.y + uy * q.x;
+  float y = ux * (q.x - qtx) + uy * (q.y - qty);                                       // :224
+  const float dqvel = ux * (v0 * fm - v2 * m.x) + uy * (v1 * fm - v2 * m.y);           // :226
+  const float sr = K.srho[o];
+  const float sy = sqrtf(sr * sr * dqvel * dqvel + P.pixel_uncertainty * P.pixel_uncertainty);   // :227
+  float w = 1.0f;
+  if (fabsf(y) > P.reweight_distance) w = fabsf(y) / P.reweight_distance;              // :230
+  const float dv = sy * w;
+#pragma unroll
+  for (int a = 0; a < 6; ++a) phi[a] /= dv;                                            // :232
+  y /= dv;                                                                             // :233
+  phi[6] = y;
+}
+
 __global__ void __launch_bounds__(256) k_extrot_rows(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr,
                                                      int vel_stride, float* __restrict__ rowsout, const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -480,75 +661,97 @@ __global__ void __launch_bounds__(256) k_extrot_rows(KeylineSoA K, const int* __
   const size_t o = (size_t)b * P.kmax + idx;
   const size_t ps = (size_t)P.lanes * P.kmax;
   float phi[7];
-#pragma unroll
-  for (int a = 0; a < 7; ++a) phi[a] = 0.0f;
-  if (K.match_id[o] >= 0) {
-    const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
-    const float fm = P.fm;
-    const float2 g = K.grad[o];
-    const float gn = K.gnorm[o];
-    const float ux = g.x / gn, uy = g.y / gn;                                            // :207-208
-    const float rho_t = (float)(1.0 / (1.0 / (double)K.rho[o] + (double)v2));            // :210
-    const float2 m = K.match_pos_img[o];
-    const float qtx = m.x + rho_t * (v0 * fm - v2 * m.x);                                // :211-212
-    const float qty = m.y + rho_t * (v1 * fm - v2 * m.y);
-    const float2 q = K.pos_img[o];
-    phi[0] = ux * rho_t * fm;                                                            // :217-222
-    phi[1] = uy * rho_t * fm;
-    phi[2] = ux * (-rho_t * q.x) + uy * (-rho_t * q.y);
-    phi[3] = -ux * q.x * q.y / fm - uy * (fm + q.y * q.y / fm);
-    phi[4] = uy * q.x * q.y / fm + ux * (fm + q.x * q.x / fm);
-    phi[5] = -ux * q.y + uy * q.x;
-    float y = ux * (q.x - qtx) + uy * (q.y - qty);                                       // :224
-    const float dqvel = ux * (v0 * fm - v2 * m.x) + uy * (v1 * fm - v2 * m.y);           // :226
-    const float sr = K.srho[o];
-    const float sy = sqrtf(sr * sr * dqvel * dqvel + P.pixel_uncertainty * P.pixel_uncertainty);   // :227
-    float w = 1.0f;
-    if (fabsf(y) > P.reweight_distance) w = fabsf(y) / P.reweight_distance;              // :230
-    const float dv = sy * w;
-#pragma unroll
-    for (int a = 0; a < 6; ++a) phi[a] /= dv;                                            // :232
-    y /= dv;                                                                             // :233
-    phi[6] = y;
-  }
+  extrot_row(K, o, vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2], P, phi);
 #pragma unroll
   for (int a = 0; a < 7; ++a) rowsout[a * ps + o] = phi[a];
 }
 
 // symmetric 6x6 pseudo-inverse solve standing in for TooN::SVD<6,6,float>(JtJ).backsub(JtF) (core.cpp:247-248 ->
 // LAPACK sgesvd_, un-vendored): cyclic Jacobi eigen-decomposition in FP64, inverse zeroed when s_i*1e9 <= s_max
-// (TooN SVD.h:37,266-274). Same statement order as oracle/rebvio_oracle.c:orc_solve6.
-__device__ void rbv_solve6(const float* A36, const float* b6, float* x6) {
-  double A[6][6], V[6][6];
-  for (int i = 0; i < 6; ++i)
-    for (int j = 0; j < 6; ++j) { A[i][j] = 0.5 * ((double)A36[i * 6 + j] + (double)A36[j * 6 + i]); V[i][j] = (i == j) ? 1.0 : 0.0; }
+// (TooN SVD.h:37,266-274). Same rotation order and per-element arithmetic as oracle/rebvio_oracle.c:orc_solve6, executed
+// by ONE WARP: lane k < 6 holds row k of A and of V in registers (all indices compile-time), a rotation (p,q) is a local
+// column update, a shuffle-fed update of rows p and q, and a local V column update. Sweeps stop once the off-diagonal
+// mass is below 1e-60 of the diagonal mass (FP64 converged; the oracle runs on to an exact zero, which moves X by < 1e-15).
+// Call with all 32 lanes of a warp; returns x[lane] for lane < 6.
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xFFFFFFFFu, v, src); }
+__device__ float rbv_solve6_warp(const float* A36, const float* b6) {
+  const int lane = threadIdx.x & 31;
+  const bool act = lane < 6;
+  double a[6], v[6];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    a[j] = act ? 0.5 * ((double)A36[lane * 6 + j] + (double)A36[j * 6 + lane]) : 0.0;
+    v[j] = (act && lane == j) ? 1.0 : 0.0;
+  }
   for (int sweep = 0; sweep < 60; ++sweep) {
-    double off = 0.0;
-    for (int p = 0; p < 6; ++p) for (int q = p + 1; q < 6; ++q) off += A[p][q] * A[p][q];
-    if (off == 0.0) break;
-    for (int p = 0; p < 6; ++p)
+    double off = 0.0, dia = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      if (j > lane) off += a[j] * a[j];
+      if (j == lane) dia += a[j] * a[j];
+    }
+#pragma unroll
+    for (int o2 = 4; o2; o2 >>= 1) { off += __shfl_xor_sync(0xFFFFFFFFu, off, o2); dia += __shfl_xor_sync(0xFFFFFFFFu, dia, o2); }
+    off = shfl_d(off, 0); dia = shfl_d(dia, 0);   // lanes 8..31 hold zeros: take lane 0's value so the exit is warp-uniform
+    if (off == 0.0 || off <= 1e-60 * dia) break;
+#pragma unroll
+    for (int p = 0; p < 6; ++p) {
+#pragma unroll
       for (int q = p + 1; q < 6; ++q) {
-        if (A[p][q] == 0.0) continue;
-        const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+        const double apq = shfl_d(a[q], p);
+        if (apq == 0.0) continue;
+        const double app = shfl_d(a[p], p), aqq = shfl_d(a[q], q);
+        const double theta = (aqq - app) / (2.0 * apq);
         const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
         const double cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
-        for (int k = 0; k < 6; ++k) { const double akp = A[k][p], akq = A[k][q]; A[k][p] = cs * akp - sn * akq; A[k][q] = sn * akp + cs * akq; }
-        for (int k = 0; k < 6; ++k) { const double apk = A[p][k], aqk = A[q][k]; A[p][k] = cs * apk - sn * aqk; A[q][k] = sn * apk + cs * aqk; }
-        for (int k = 0; k < 6; ++k) { const double vkp = V[k][p], vkq = V[k][q]; V[k][p] = cs * vkp - sn * vkq; V[k][q] = sn * vkp + cs * vkq; }
+        { const double akp = a[p], akq = a[q]; a[p] = cs * akp - sn * akq; a[q] = sn * akp + cs * akq; }   // columns p,q of every row
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {                                                                       // rows p,q
+          const double apk = shfl_d(a[k], p), aqk = shfl_d(a[k], q);
+          if (lane == p) a[k] = cs * apk - sn * aqk;
+          if (lane == q) a[k] = sn * apk + cs * aqk;
+        }
+        { const double vkp = v[p], vkq = v[q]; v[p] = cs * vkp - sn * vkq; v[q] = sn * vkp + cs * vkq; }
       }
+    }
   }
-  double smax = 0.0;
-  for (int i = 0; i < 6; ++i) if (fabs(A[i][i]) > smax) smax = fabs(A[i][i]);
-  double x[6] = {0, 0, 0, 0, 0, 0};
+  double d = 0.0;   // diagonal element of this lane's row
+#pragma unroll
+  for (int j = 0; j < 6; ++j) if (j == lane) d = a[j];
+  double smax = act ? fabs(d) : 0.0;
+#pragma unroll
+  for (int o2 = 4; o2; o2 >>= 1) smax = fmax(smax, __shfl_xor_sync(0xFFFFFFFFu, smax, o2));
+  smax = shfl_d(smax, 0);
+  const double bk = act ? (double)b6[lane] : 0.0;
+  double x = 0.0;
+#pragma unroll
   for (int i = 0; i < 6; ++i) {
-    const double s = fabs(A[i][i]);
-    if (s * 1e9 <= smax) continue;
+    const double aii = shfl_d(d, i);
     double proj = 0.0;
-    for (int k = 0; k < 6; ++k) proj += V[k][i] * (double)b6[k];
-    proj /= A[i][i];
-    for (int k = 0; k < 6; ++k) x[k] += V[k][i] * proj;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) proj += shfl_d(v[i] * bk, k);                            // proj += V[k][i] * b[k], k ascending
+    if (fabs(aii) * 1e9 <= smax) continue;                                               // uniform across the warp
+    proj /= aii;
+    x += v[i] * proj;
   }
-  for (int k = 0; k < 6; ++k) x6[k] = (float)x[k];
+  return (float)x;
+}
+
+// tail of extRotVel executed by warp 0 of the reducing block: result[27] (shared) -> Wx, X, ok in lane_out
+__device__ void extrot_finish_warp(const double* result, float* lane_out_b, float* s_sys /* shared, 42 floats */) {
+  const int lane = threadIdx.x & 31;
+  if (lane == 0) {
+    int k = 0;
+    for (int a = 0; a < 6; ++a)
+      for (int q = a; q < 6; ++q) { s_sys[a * 6 + q] = (float)result[k]; s_sys[q * 6 + a] = (float)result[k]; ++k; }
+    for (int a = 0; a < 6; ++a) s_sys[36 + a] = (float)result[21 + a];
+  }
+  __syncwarp();
+  const float x = rbv_solve6_warp(s_sys, s_sys + 36);
+  for (int i = lane; i < 36; i += 32) lane_out_b[OUT_WX + i] = s_sys[i];                // _Wx = JtJ, core.cpp:249
+  if (lane < 6) lane_out_b[OUT_X + lane] = x;
+  const unsigned bad = __ballot_sync(0xFFFFFFFFu, lane < 6 && x != x);                  // :251-256
+  if (lane == 0) lane_out_b[OUT_OK] = bad ? 0.0f : 1.0f;
 }
 
 // 27 accumulators: 21 upper-triangle entries of Phi^T Phi in (a,b) a<=b row-major order, then 6 of Phi^T Y.
@@ -559,6 +762,7 @@ __global__ void __launch_bounds__(512) k_extrot_reduce(const int* __restrict__ c
                                                         int ordered, const __grid_constant__ DevParams P) {
   __shared__ double sm[32 * 27];
   __shared__ double result[27];
+  __shared__ float s_sys[42];
   const int b = blockIdx.x, n = count[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const size_t base = (size_t)b * P.kmax;
   const size_t ps = (size_t)P.lanes * P.kmax;
@@ -595,27 +799,74 @@ __global__ void __launch_bounds__(512) k_extrot_reduce(const int* __restrict__ c
     }
     block_sum_fixed<27>(acc, sm, result);
   }
-  if (t == 0) {
-    float Wx[36], JtF[6], X[6];
+  if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
+}
+
+// RBV_REDUCE_FAST: rows + 27 sums + 6x6 solve in ONE kernel (same ticket scheme as k_tryvel_fast)
+__global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr,
+                                                        int vel_stride, double* __restrict__ partials, unsigned* __restrict__ ticket,
+                                                        int nblk, float* lane_out, const __grid_constant__ DevParams P) {
+  __shared__ double sm[(TV_TPB / 32) * 27];
+  __shared__ double result[27];
+  __shared__ float s_sys[42];
+  __shared__ int s_last;
+  const int b = blockIdx.y, n = count[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int nact = max(1, (n + TV_TPB - 1) / TV_TPB);
+  if ((int)blockIdx.x >= nact) return;
+  const int idx = blockIdx.x * TV_TPB + t;
+  float r[7];
+#pragma unroll
+  for (int a = 0; a < 7; ++a) r[a] = 0.0f;
+  if (idx < n)
+    extrot_row(K, (size_t)b * P.kmax + idx, vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1],
+               vel_ptr[(size_t)b * vel_stride + 2], P, r);
+  {
     int k = 0;
-    for (int a = 0; a < 6; ++a)
-      for (int q = a; q < 6; ++q) { Wx[a * 6 + q] = (float)result[k]; Wx[q * 6 + a] = (float)result[k]; ++k; }
-    for (int a = 0; a < 6; ++a) JtF[a] = (float)result[21 + a];
-    rbv_solve6(Wx, JtF, X);
-    float* out = lane_out + (size_t)b * OUT_STRIDE;
-    int ok = 1;
-    for (int i = 0; i < 36; ++i) out[OUT_WX + i] = Wx[i];                               // _Wx = JtJ, :249
-    for (int i = 0; i < 6; ++i) { out[OUT_X + i] = X[i]; if (X[i] != X[i]) ok = 0; }    // :251-256
-    out[OUT_OK] = (float)ok;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+#pragma unroll
+      for (int q = a; q < 7; ++q) {
+        const int slot = (q == 6) ? 21 + a : k++;
+        double v = (double)(r[a] * r[q]);        // float product as in the reference (operators.hh:200-208), FP64 accumulate
+#pragma unroll
+        for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+        if (lane == 0) sm[warp * 27 + slot] = v;
+      }
+    }
   }
+  __syncthreads();
+  if (t < 27) {
+    double s2 = 0.0;
+#pragma unroll
+    for (int w = 0; w < TV_TPB / 32; ++w) s2 += sm[w * 27 + t];
+    partials[((size_t)b * nblk + blockIdx.x) * 27 + t] = s2;
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) s_last = (atomicAdd(&ticket[b], 1u) == (unsigned)(nact - 1));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (t < 27) {
+    double s2 = 0.0;
+    for (int j = 0; j < nact; ++j) s2 += __ldcg(partials + ((size_t)b * nblk + j) * 27 + t);
+    result[t] = s2;
+  }
+  __syncthreads();
+  if (t == 0) ticket[b] = 0u;
+  if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
   const DevParams& P = c->P;
   const float* vel_ptr = vel_from_lm ? reinterpret_cast<const float*>(c->lm) + offsetof(LMState, vel) / sizeof(float) : c->lane_in + IN_VEL;
   const int vel_stride = vel_from_lm ? (int)(sizeof(LMState) / sizeof(float)) : IN_STRIDE;
-  RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
-  RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, c->reduce_mode == RBV_REDUCE_ORDERED, P);
+  if (c->reduce_mode == RBV_REDUCE_ORDERED) {
+    RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
+    RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
+  } else {
+    RBV_LAUNCH(c, k_extrot_fast, (dim3(c->nblk, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
+  }
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

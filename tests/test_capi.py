@@ -94,3 +94,20 @@ def test_create_fails_loudly_without_gpu():
     from rebvio_b200 import host
     with pytest.raises(capi.RbvError):
         host.Context()
+
+
+def test_cpp_adapter_compiles_and_links(tmp_path):
+    """the header-only C++ adapter (reference class API over the C ABI) builds with g++ and links the library"""
+    import shutil
+    import subprocess
+    if not shutil.which("g++"):
+        pytest.skip("no g++")
+    exe = str(tmp_path / "adapter_test")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    cmd = ["g++", "-std=c++14", "-Wall", "-I" + os.path.join(common.ROOT, "include"), "-I" + os.path.join(common.ROOT, "rebvio_b200", "cpp"),
+           os.path.join(common.ROOT, "tests", "cpp", "adapter_compile_test.cpp"), "-o", exe, "-L" + libdir, "-lrebvio_b200",
+           "-Wl,-rpath," + libdir]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    out = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
+    assert out.returncode == 0 and "adapter linked" in out.stdout

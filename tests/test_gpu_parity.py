@@ -14,6 +14,8 @@ from rebvio_b200 import capi, host, synth
 
 pytestmark = pytest.mark.gpu
 
+SCORE_RTOL = 5e-4   # FAST mode only; ORDERED mode reproduces the score bit for bit
+
 
 def _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED):
     from gpu_impl import GpuImpl
@@ -70,7 +72,9 @@ def test_cuda_fast_reduction_teacher_forced(name, nf):
             # by a few 1e-5; the minimiser still lands on the same velocity to 1e-4 relative.
             tr_r, tr_g = T[k]["minimize"]["trace"], G[k]["minimize"]["trace"]
             assert H.rel_err(tr_g[0, 3:12], tr_r[0, 3:12]) <= 1e-5 and H.rel_err(tr_g[0, 12:15], tr_r[0, 12:15]) <= 1e-5, (k, d)
-            assert abs(tr_g[0, 15] - tr_r[0, 15]) <= 1e-5 * abs(tr_r[0, 15]), (k, d)
+            # the score is a sum of ~16k positive float32 terms: the reference's own sequential float32 accumulation
+            # carries ~1e-4 relative rounding error, which is what an FP64 sum differs from it by
+            assert abs(tr_g[0, 15] - tr_r[0, 15]) <= SCORE_RTOL * abs(tr_r[0, 15]), (k, d)
             assert d.get("trace_rel", 0.0) <= 1e-3 and d.get("score_rel", 0.0) <= 1e-3, (k, d)
             assert d.get("Vg_rel", 0.0) <= 1e-3 and d.get("P_Vg_rel", 0.0) <= 1e-3, (k, d)
             assert set(d) <= {"trace_bits", "trace_rel", "score_bits", "score_rel", "Vg_rel", "P_Vg_rel", "residuals",
@@ -86,11 +90,11 @@ def test_cuda_fast_reduction_teacher_forced(name, nf):
 def test_try_vel_fast_vs_ordered_indices_and_sums():
     spec, frames, R_rel = common.sequence("C2", 3)
     cfg = common.cfgs_from_spec(spec)
-    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
-    a, b = orc.detect(frames[0]), orc.detect(frames[1])
-    orc.build_distance_field(b)
-    n = orc.map_size(a)
     for mode in (capi.REDUCE_ORDERED, capi.REDUCE_FAST):
+        orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+        a, b = orc.detect(frames[0]), orc.detect(frames[1])
+        orc.build_distance_field(b)
+        n = orc.map_size(a)
         g = _gpu(cfg, mode=mode)
         ga, gb = g.detect(frames[0]), g.detect(frames[1])
         g.build_distance_field(gb)
@@ -106,12 +110,9 @@ def test_try_vel_fast_vs_ordered_indices_and_sums():
                 assert H.bits(np.float32(so)) == H.bits(np.float32(sg))
                 assert np.array_equal(H.bits(JJo), H.bits(JJg)) and np.array_equal(H.bits(JFo), H.bits(JFg))
             else:
-                assert abs(sg - so) <= 1e-5 * abs(so)
+                assert abs(sg - so) <= SCORE_RTOL * abs(so)
                 assert H.rel_err(JJg, JJo) <= 1e-5 and H.rel_err(JFg, JFo) <= 1e-5
-        g.close()
-        # rewind the oracle's forward matches / residual state for the second mode
-        a2 = orc.detect(frames[0]); orc.map_free(a); a = a2
-    orc.close()
+        g.close(); orc.close()
 
 
 @pytest.mark.parametrize("rows,cols", [(33, 47), (97, 131), (480, 752), (1080, 1920)])
@@ -227,3 +228,22 @@ def test_fast_mode_is_deterministic():
         g.close()
     assert H.dirty(H.report(runs[0], runs[1])) == []
     assert common.x_rel_max(H.report(runs[0], runs[1])) == 0.0
+
+
+def test_cpp_adapter_runs_the_chain(tmp_path):
+    """the C++ adapter (reference class API) drives detect + the whole tracker chain on the device"""
+    import os
+    import shutil
+    import subprocess
+    if not shutil.which("g++"):
+        pytest.skip("no g++")
+    exe = str(tmp_path / "adapter_test")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    cmd = ["g++", "-std=c++14", "-I" + os.path.join(common.ROOT, "include"), "-I" + os.path.join(common.ROOT, "rebvio_b200", "cpp"),
+           os.path.join(common.ROOT, "tests", "cpp", "adapter_compile_test.cpp"), "-o", exe, "-L" + libdir, "-lrebvio_b200",
+           "-Wl,-rpath," + libdir]
+    assert subprocess.run(cmd).returncode == 0
+    out = subprocess.run([exe, "run"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout
+    fields = out.stdout.split()
+    assert int(fields[1]) > 1000 and int(fields[fields.index("directed") + 1]) > 500, out.stdout
