@@ -136,6 +136,15 @@ int rbv_profile_reset(rbv_ctx* ctx);
 int rbv_profile_read(rbv_ctx* ctx, int kid, double* total_ms, unsigned long long* timed_launches,
                      unsigned long long* launches);
 
+/* implementation choices, for tests and profiling; 0 = automatic (the default) everywhere.
+ *   RBV_TUNE_FIELD: distance field — 1 = one thread per keyline with global atomics, 2 = shared-memory row bands
+ *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel
+ *                   (one block per image plane, TMA-staged row chunks; needs cols % 4 == 0 and cols <= 832)        */
+#define RBV_TUNE_FIELD 0
+#define RBV_TUNE_BOX 1
+#define RBV_TUNE_COUNT 8
+int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
+
 /* allocate / free a B-lane map (replaces std::make_shared<EdgeMap>, edge_detector.cpp:50). */
 int rbv_map_create(rbv_ctx* ctx, rbv_map** out);
 void rbv_map_release(rbv_ctx* ctx, rbv_map* map);

@@ -48,6 +48,7 @@ assert KEYLINE_DTYPE.itemsize == 84
 
 RBV_OK, RBV_ERR_ARG, RBV_ERR_CUDA, RBV_ERR_STATE = 0, 1, 2, 3
 REDUCE_FAST, REDUCE_ORDERED = 0, 1
+TUNE_FIELD, TUNE_BOX = 0, 1   # rbv_set_tuning keys; values: 0 automatic, 1 / 2 = the two implementations (see the header)
 
 vp = C.c_void_p
 _SIG = {
@@ -61,6 +62,7 @@ _SIG = {
     "rbv_last_error": (C.c_char_p, []),
     "rbv_sync": (C.c_int, [vp]),
     "rbv_set_reduce_mode": (C.c_int, [vp, C.c_int]),
+    "rbv_set_tuning": (C.c_int, [vp, C.c_int, C.c_int]),
     "rbv_lanes": (C.c_int, [vp]),
     "rbv_set_stream": (C.c_int, [vp, vp]),
     "rbv_launch_count": (C.c_ulonglong, [vp]),

@@ -179,6 +179,15 @@ struct Stage {  // ring of pinned staging slots for per-call lane inputs
 };
 static Stage* stage_of(rbv_ctx* c) { return reinterpret_cast<Stage*>(c->h_in); }
 
+// Synchronous-looking copies IN STREAM ORDER on the context's stream. A plain cudaMemcpy from pageable memory may return
+// while the DMA is still in flight and is not ordered against a non-blocking stream, so a kernel launched right after it
+// on c->stream could read stale bytes.
+static cudaError_t copy_sync(rbv_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind) {
+  cudaError_t e = cudaMemcpyAsync(dst, src, bytes, kind, c->stream);
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(c->stream);
+}
+
 template <typename T>
 static cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, n * sizeof(T)); }
 
@@ -228,6 +237,8 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   const size_t N = (size_t)P.npix, B = (size_t)lanes, K = (size_t)P.kmax;
   RBV_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   c->own_stream = true;
+  { int rc = fe_init(c); if (rc != RBV_OK) return rc; }
+  { int rc = tr_init(c); if (rc != RBV_OK) return rc; }
   const int wpr = (P.cols + 31) / 32;
   RBV_CUDA(dalloc(&c->img, B * N));
   RBV_CUDA(dalloc(&c->rowsum, 4 * B * N));   // rowsum [2][B][N] + bufB [2][B][N] contiguous (detect reuses it as float4 [B][N])
@@ -272,6 +283,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaMallocHost((void**)&c->h_cnt, sizeof(int) * B * (CNT_STRIDE + 2)));
   RBV_CUDA(cudaMallocHost((void**)&c->h_lm, sizeof(LMState) * B));
   RBV_CUDA(cudaMallocHost((void**)&c->h_img, sizeof(float) * B * N));
+  RBV_CUDA(cudaDeviceSynchronize());   // the memsets above ran on the legacy stream; the context's stream is non-blocking
   *out = c;
   return RBV_OK;
 }
@@ -307,6 +319,11 @@ extern "C" int rbv_sync(rbv_ctx* c) {
 extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
   if (!c || (mode != RBV_REDUCE_FAST && mode != RBV_REDUCE_ORDERED)) return RBV_ERR_ARG;
   c->reduce_mode = mode;
+  return RBV_OK;
+}
+extern "C" int rbv_set_tuning(rbv_ctx* c, int key, int value) {
+  if (!c || key < 0 || key >= RBV_TUNE_COUNT || value < 0 || value > 2) return RBV_ERR_ARG;
+  c->tune[key] = value;
   return RBV_OK;
 }
 extern "C" int rbv_lanes(const rbv_ctx* c) { return c ? c->P.lanes : 0; }
@@ -684,18 +701,18 @@ extern "C" int rbv_map_set_threshold(rbv_ctx* c, rbv_map* m, const float* t) {
   CHECK_CTX(c);
   if (!m || !t) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(m->threshold, t, sizeof(float) * c->P.lanes, cudaMemcpyHostToDevice));
+  RBV_CUDA(copy_sync(c, m->threshold, t, sizeof(float) * c->P.lanes, cudaMemcpyHostToDevice));
   return RBV_OK;
 }
 
 template <typename T>
-static cudaError_t pull(std::vector<T>& h, const T* d, size_t lane, size_t K, int n) {
+static cudaError_t pull(rbv_ctx* c, std::vector<T>& h, const T* d, size_t lane, size_t K, int n) {
   h.resize(n > 0 ? n : 1);
-  return cudaMemcpy(h.data(), d + lane * K, sizeof(T) * (size_t)n, cudaMemcpyDeviceToHost);
+  return copy_sync(c, h.data(), d + lane * K, sizeof(T) * (size_t)n, cudaMemcpyDeviceToHost);
 }
 template <typename T>
-static cudaError_t push(const std::vector<T>& h, T* d, size_t lane, size_t K, int n) {
-  return cudaMemcpy(d + lane * K, h.data(), sizeof(T) * (size_t)n, cudaMemcpyHostToDevice);
+static cudaError_t push(rbv_ctx* c, const std::vector<T>& h, T* d, size_t lane, size_t K, int n) {
+  return copy_sync(c, d + lane * K, h.data(), sizeof(T) * (size_t)n, cudaMemcpyHostToDevice);
 }
 
 extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* kl, uint32_t* pixel_idx, int cap, int* n_out) {
@@ -703,7 +720,7 @@ extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* k
   if (!m || lane < 0 || lane >= c->P.lanes || !n_out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;
-  RBV_CUDA(cudaMemcpy(&n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, &n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
   *n_out = n;
   if (n > cap) { rbv_set_error("rbv_map_download: capacity %d < %d keylines", cap, n); return RBV_ERR_ARG; }
   if (n == 0) return RBV_OK;
@@ -712,13 +729,13 @@ extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* k
   std::vector<float> gn, mgn, rho, sr;
   std::vector<int> ip, in, mi, mf, mk;
   std::vector<unsigned> mt, px;
-  RBV_CUDA(pull(pos, m->k.pos, L, K, n)); RBV_CUDA(pull(pi, m->k.pos_img, L, K, n)); RBV_CUDA(pull(mpi, m->k.match_pos_img, L, K, n));
-  RBV_CUDA(pull(g, m->k.grad, L, K, n)); RBV_CUDA(pull(mg, m->k.match_grad, L, K, n));
-  RBV_CUDA(pull(gn, m->k.gnorm, L, K, n)); RBV_CUDA(pull(mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(pull(rho, m->k.rho, L, K, n));
-  RBV_CUDA(pull(sr, m->k.srho, L, K, n));
-  RBV_CUDA(pull(ip, m->k.id_prev, L, K, n)); RBV_CUDA(pull(in, m->k.id_next, L, K, n)); RBV_CUDA(pull(mi, m->k.match_id, L, K, n));
-  RBV_CUDA(pull(mf, m->k.match_fwd, L, K, n)); RBV_CUDA(pull(mk, m->k.match_kf, L, K, n));
-  RBV_CUDA(pull(mt, m->k.matches, L, K, n)); RBV_CUDA(pull(px, m->k.pixel, L, K, n));
+  RBV_CUDA(pull(c, pos, m->k.pos, L, K, n)); RBV_CUDA(pull(c, pi, m->k.pos_img, L, K, n)); RBV_CUDA(pull(c, mpi, m->k.match_pos_img, L, K, n));
+  RBV_CUDA(pull(c, g, m->k.grad, L, K, n)); RBV_CUDA(pull(c, mg, m->k.match_grad, L, K, n));
+  RBV_CUDA(pull(c, gn, m->k.gnorm, L, K, n)); RBV_CUDA(pull(c, mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(pull(c, rho, m->k.rho, L, K, n));
+  RBV_CUDA(pull(c, sr, m->k.srho, L, K, n));
+  RBV_CUDA(pull(c, ip, m->k.id_prev, L, K, n)); RBV_CUDA(pull(c, in, m->k.id_next, L, K, n)); RBV_CUDA(pull(c, mi, m->k.match_id, L, K, n));
+  RBV_CUDA(pull(c, mf, m->k.match_fwd, L, K, n)); RBV_CUDA(pull(c, mk, m->k.match_kf, L, K, n));
+  RBV_CUDA(pull(c, mt, m->k.matches, L, K, n)); RBV_CUDA(pull(c, px, m->k.pixel, L, K, n));
   for (int i = 0; i < n; ++i) {
     if (kl) {
       rbv_keyline& k = kl[i];
@@ -753,14 +770,14 @@ extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keylin
     mk[i] = k.match_id_keyframe; mt[i] = k.matches;
   }
   if (n) {
-    RBV_CUDA(push(pos, m->k.pos, L, K, n)); RBV_CUDA(push(pi, m->k.pos_img, L, K, n)); RBV_CUDA(push(mpi, m->k.match_pos_img, L, K, n));
-    RBV_CUDA(push(g, m->k.grad, L, K, n)); RBV_CUDA(push(mg, m->k.match_grad, L, K, n));
-    RBV_CUDA(push(gn, m->k.gnorm, L, K, n)); RBV_CUDA(push(mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(push(rho, m->k.rho, L, K, n));
-    RBV_CUDA(push(sr, m->k.srho, L, K, n));
-    RBV_CUDA(push(ip, m->k.id_prev, L, K, n)); RBV_CUDA(push(in, m->k.id_next, L, K, n)); RBV_CUDA(push(mi, m->k.match_id, L, K, n));
-    RBV_CUDA(push(mf, m->k.match_fwd, L, K, n)); RBV_CUDA(push(mk, m->k.match_kf, L, K, n)); RBV_CUDA(push(mt, m->k.matches, L, K, n));
+    RBV_CUDA(push(c, pos, m->k.pos, L, K, n)); RBV_CUDA(push(c, pi, m->k.pos_img, L, K, n)); RBV_CUDA(push(c, mpi, m->k.match_pos_img, L, K, n));
+    RBV_CUDA(push(c, g, m->k.grad, L, K, n)); RBV_CUDA(push(c, mg, m->k.match_grad, L, K, n));
+    RBV_CUDA(push(c, gn, m->k.gnorm, L, K, n)); RBV_CUDA(push(c, mgn, m->k.match_gnorm, L, K, n)); RBV_CUDA(push(c, rho, m->k.rho, L, K, n));
+    RBV_CUDA(push(c, sr, m->k.srho, L, K, n));
+    RBV_CUDA(push(c, ip, m->k.id_prev, L, K, n)); RBV_CUDA(push(c, in, m->k.id_next, L, K, n)); RBV_CUDA(push(c, mi, m->k.match_id, L, K, n));
+    RBV_CUDA(push(c, mf, m->k.match_fwd, L, K, n)); RBV_CUDA(push(c, mk, m->k.match_kf, L, K, n)); RBV_CUDA(push(c, mt, m->k.matches, L, K, n));
   }
-  RBV_CUDA(cudaMemcpy(m->count + lane, &n, sizeof(int), cudaMemcpyHostToDevice));
+  RBV_CUDA(copy_sync(c, m->count + lane, &n, sizeof(int), cudaMemcpyHostToDevice));
   if (pixel_idx) {
     std::vector<int> mask(N, -1);
     std::vector<unsigned> px(n > 0 ? n : 1);
@@ -769,8 +786,8 @@ extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keylin
       px[i] = pixel_idx[i];
       if (mask[pixel_idx[i]] < 0) mask[pixel_idx[i]] = i;   // unordered_map::emplace keeps the first
     }
-    RBV_CUDA(cudaMemcpy(m->mask + L * N, mask.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
-    if (n) RBV_CUDA(push(px, m->k.pixel, L, K, n));
+    RBV_CUDA(copy_sync(c, m->mask + L * N, mask.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
+    if (n) RBV_CUDA(push(c, px, m->k.pixel, L, K, n));
   }
   return RBV_OK;
 }
@@ -782,13 +799,13 @@ extern "C" int rbv_debug_read_image(rbv_ctx* c, int lane, int which, float* out)
   const size_t N = c->P.npix;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   if (which < 2) {
-    RBV_CUDA(cudaMemcpy(out, c->bufA + ((size_t)lane * 2 + which) * N, sizeof(float) * N, cudaMemcpyDeviceToHost));
+    RBV_CUDA(copy_sync(c, out, c->bufA + ((size_t)lane * 2 + which) * N, sizeof(float) * N, cudaMemcpyDeviceToHost));
     return RBV_OK;
   }
   float* tmp = c->rowsum;  // scratch
   TRY(fe_dog_mag_debug(c, lane, which, tmp));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(out, tmp, sizeof(float) * N, cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, out, tmp, sizeof(float) * N, cudaMemcpyDeviceToHost));
   return RBV_OK;
 }
 
@@ -796,7 +813,7 @@ extern "C" int rbv_debug_read_mask(rbv_ctx* c, rbv_map* m, int lane, int* out) {
   CHECK_CTX(c);
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(out, m->mask + (size_t)lane * c->P.npix, sizeof(int) * (size_t)c->P.npix, cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, out, m->mask + (size_t)lane * c->P.npix, sizeof(int) * (size_t)c->P.npix, cudaMemcpyDeviceToHost));
   return RBV_OK;
 }
 
@@ -806,7 +823,7 @@ extern "C" int rbv_debug_read_field(rbv_ctx* c, int lane, int* id, int* distance
   const size_t N = c->P.npix;
   std::vector<unsigned> f(N);
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(f.data(), c->field + (size_t)lane * N, sizeof(unsigned) * N, cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, f.data(), c->field + (size_t)lane * N, sizeof(unsigned) * N, cudaMemcpyDeviceToHost));
   for (size_t i = 0; i < N; ++i) {
     const bool empty = f[i] == RBV_FIELD_EMPTY;
     if (id) id[i] = empty ? -1 : (int)(0xFFFFFFu - (f[i] & 0xFFFFFFu));
@@ -820,9 +837,9 @@ extern "C" int rbv_debug_read_residuals(rbv_ctx* c, rbv_map* m, int lane, float*
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;
-  RBV_CUDA(cudaMemcpy(&n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, &n, m->count + lane, sizeof(int), cudaMemcpyDeviceToHost));
   if (n > cap) n = cap;
-  if (n) RBV_CUDA(cudaMemcpy(out, m->k.residual + (size_t)lane * c->P.kmax, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  if (n) RBV_CUDA(copy_sync(c, out, m->k.residual + (size_t)lane * c->P.kmax, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
   return RBV_OK;
 }
 
@@ -831,10 +848,10 @@ extern "C" int rbv_debug_box_pass(rbv_ctx* c, int scale, int pass, const float* 
   if (scale < 0 || scale > 1 || pass < 0 || pass > 2 || !in || !out) return RBV_ERR_ARG;
   const size_t N = c->P.npix;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(c->img, in, sizeof(float) * N, cudaMemcpyHostToDevice));
+  RBV_CUDA(copy_sync(c, c->img, in, sizeof(float) * N, cudaMemcpyHostToDevice));
   TRY(fe_box_pass_debug(c, scale, pass, c->img, c->bufB));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(out, c->bufB, sizeof(float) * N, cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, out, c->bufB, sizeof(float) * N, cudaMemcpyDeviceToHost));
   return RBV_OK;
 }
 
@@ -850,7 +867,7 @@ extern "C" int rbv_debug_read_lm_trace(rbv_ctx* c, int lane, float* out, int cap
   if (lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   LMState L;
-  RBV_CUDA(cudaMemcpy(&L, c->lm + lane, sizeof(LMState), cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, &L, c->lm + lane, sizeof(LMState), cudaMemcpyDeviceToHost));
   int n = (c->P.iterations + 1) * 16;
   if (n > cap_floats) n = cap_floats;
   memcpy(out, L.trace, sizeof(float) * n);
@@ -861,6 +878,6 @@ extern "C" int rbv_debug_read_probe_count(rbv_ctx* c, int lane, unsigned long lo
   CHECK_CTX(c);
   if (lane < 0 || lane >= c->P.lanes || !probes) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  RBV_CUDA(cudaMemcpy(probes, c->probes + lane, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  RBV_CUDA(copy_sync(c, probes, c->probes + lane, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return RBV_OK;
 }

@@ -159,11 +159,279 @@ __global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ row
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused box pass (createIntegralImage + average in ONE kernel, the integral image and the row prefix never reach HBM):
+// one block per image plane, so a pass moves exactly "read N + write N" floats per plane. Warp roles:
+//   warp 0 (one lane)  producer: TMA bulk copies (cp.async.bulk, one per image row) of the next BP_R-row chunk into a
+//                      double-buffered shared tile, completion on an mbarrier;
+//   warp 1             row pass: lane = row of the chunk, in-place sequential prefix along the row (scale_space.cpp:50-57);
+//   warps 2..          column pass + box: thread = image column, running column sum (:59-65) into a BP_RING-row shared ring
+//                      of the integral image, then the four-tap box (:69-128) for every row whose taps are complete.
+// full -> scanned -> empty mbarriers hand the chunk buffers round; the column warps use a named barrier for the ring.
+// Needs cols % 4 == 0 (16-byte bulk copies), 64 + cols threads <= 1024 and 2*BP_R*(cols+pad) + BP_RING*cols floats of smem.
+#define BP_R 16
+#define BP_RING 32
+#define BP_CH 8
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// wait with back-off: a spinning warp would take issue slots from the warps it is waiting for
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity, unsigned sleep_ns) {
+  const unsigned a = smem_u32(bar);
+  long long t0 = 0;
+  for (int spin = 0;; ++spin) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    if (ok) return;
+    __nanosleep(sleep_ns);
+    if ((spin & 1023) == 0) {
+      if (spin == 0) t0 = clock64();
+      else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
+    }
+  }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// one output value from a full-width ring (ring row pitch = cols; jhi / jlo are image columns)
+__device__ __forceinline__ float box_value_fw(const float* __restrict__ ring, int cols, const float (*inv_area)[16], int ro, int h, int rows,
+                                              int jhi, int jlo, bool left, int ncol, float inv_mid) {
+  const int rlo = ro - h - 1;
+  if (rlo >= 0 && ro + h < rows) {
+    const float* hi = ring + ((ro + h) & (BP_RING - 1)) * cols;
+    const float* lo = ring + (rlo & (BP_RING - 1)) * cols;
+    const float v = left ? ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo] : hi[jhi] - lo[jhi];   // :99 / :94
+    return v * inv_mid;
+  }
+  const int rhi = min(ro + h, rows - 1);
+  const float* hi = ring + (rhi & (BP_RING - 1)) * cols;
+  float v;
+  if (rlo < 0) {
+    v = left ? hi[jhi] - hi[jlo] : hi[jhi];                                             // :78-84
+  } else {
+    const float* lo = ring + (rlo & (BP_RING - 1)) * cols;
+    v = left ? ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo] : hi[jhi] - lo[jhi];           // :119,:124 / :114
+  }
+  return v * inv_area[rhi - max(rlo, -1)][ncol];
+}
+
+// BP_CH interior output rows: output i takes ring rows (hi0 + i) and (lo0 + i) (mod BP_RING), columns jhi / jlo
+__device__ __forceinline__ void bp_box8(const float* __restrict__ ring, int cols, int hi0, int lo0, int jhi, int jlo, bool left, float inv,
+                                        float* __restrict__ dst) {
+  if (left) {
+#pragma unroll
+    for (int i = 0; i < BP_CH; ++i) {
+      const float* hi = ring + ((hi0 + i) & (BP_RING - 1)) * cols;
+      const float* lo = ring + ((lo0 + i) & (BP_RING - 1)) * cols;
+      dst[i * cols] = (((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo]) * inv;                 // :99
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < BP_CH; ++i) {
+      const float* hi = ring + ((hi0 + i) & (BP_RING - 1)) * cols;
+      const float* lo = ring + ((lo0 + i) & (BP_RING - 1)) * cols;
+      dst[i * cols] = (hi[jhi] - lo[jhi]) * inv;                                         // :94
+    }
+  }
+}
+
+__device__ __forceinline__ void bp_scan4(float4& v, float& carry, bool first) {
+  v.x = first ? v.x : carry + v.x;
+  v.y = v.x + v.y;
+  v.z = v.y + v.z;
+  v.w = v.z + v.w;
+  carry = v.w;
+}
+
+__global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ in, float* __restrict__ out0, float* __restrict__ out1,
+                                                     int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
+                                                     int d1, int dual, int spitch) {
+  extern __shared__ __align__(128) float bp_smem[];
+  __shared__ float inv_area[16][16];
+  __shared__ __align__(8) unsigned long long bars[6];   // full[2], scanned[2], empty[2]
+  float* S = bp_smem;                                  // [2][BP_R][spitch]
+  float* ring = bp_smem + 2 * BP_R * spitch;           // [BP_RING][cols]
+  unsigned long long* full = bars;
+  unsigned long long* scanned = bars + 2;
+  unsigned long long* empty = bars + 4;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ncw = (int)(blockDim.x >> 5) - 2;
+  const int plane = blockIdx.x;
+  const int z = dual ? 0 : plane % nz;
+  const int ha = (z ? d1 : d0) / 2;
+  const int hb = dual ? d1 / 2 : ha;
+  const int hm = max(ha, hb);
+  const float* src = in + (size_t)plane * in_plane_stride;
+  for (int i = tid; i < 256; i += blockDim.x) {
+    const int a = i / 16, b = i % 16;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171
+  }
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(full + i, 1u); mbar_init(scanned + i, 32u); mbar_init(empty + i, (unsigned)ncw); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int nchunks = (rows + BP_R - 1) / BP_R;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int ci = 0; ci < nchunks; ++ci) {
+        const int buf = ci & 1;
+        if (ci >= 2) mbar_wait(empty + buf, (unsigned)(((ci >> 1) - 1) & 1), 200);
+        fence_proxy_async();
+        const int nr = min(BP_R, rows - ci * BP_R);
+        mbar_arrive_expect_tx(full + buf, (unsigned)(nr * cols * 4));
+        for (int j = 0; j < nr; ++j)
+          bulk_g2s(S + (size_t)(buf * BP_R + j) * spitch, src + (size_t)(ci * BP_R + j) * cols, (unsigned)(cols * 4), full + buf);
+      }
+    }
+  } else if (warp == 1) {
+    const int n4 = cols >> 2;
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci & 1;
+      mbar_wait(full + buf, (unsigned)((ci >> 1) & 1), 40);
+      if (lane < BP_R) {
+        float4* row = reinterpret_cast<float4*>(S + (size_t)(buf * BP_R + lane) * spitch);
+        float carry = 0.0f;
+        float4 a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = (i < n4) ? row[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c4 = 0; c4 < n4; c4 += 4) {
+          float4 nx[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) nx[i] = (c4 + 4 + i < n4) ? row[c4 + 4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+          bp_scan4(a[0], carry, c4 == 0);
+          bp_scan4(a[1], carry, false);
+          bp_scan4(a[2], carry, false);
+          bp_scan4(a[3], carry, false);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) if (c4 + i < n4) row[c4 + i] = a[i];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) a[i] = nx[i];
+        }
+      }
+      mbar_arrive(scanned + buf);
+    }
+  } else {
+    const int c = tid - 64;
+    const bool ok = c < cols;
+    float* dstA = out0 + (size_t)plane * out_plane_stride;
+    float* dstB = out1 + (size_t)plane * out_plane_stride;
+    const int jhiA = min(c + ha, cols - 1), jloA = c - ha - 1, ncolA = jhiA - max(jloA, -1);
+    const int jhiB = min(c + hb, cols - 1), jloB = c - hb - 1, ncolB = jhiB - max(jloB, -1);
+    const bool leftA = jloA >= 0, leftB = jloB >= 0;
+    const float invA = ok ? (float)(1.0 / (double)((float)(2 * ha + 1) * (float)ncolA)) : 0.0f;
+    const float invB = ok ? (float)(1.0 / (double)((float)(2 * hb + 1) * (float)ncolB)) : 0.0f;
+    const unsigned nbar = (unsigned)(ncw * 32);
+    float run = 0.0f;
+    int onext = 0;
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci & 1;
+      mbar_wait(scanned + buf, (unsigned)((ci >> 1) & 1), 100);
+      const int kend = min((ci + 1) * BP_R, rows);
+#pragma unroll
+      for (int sub = 0; sub < BP_R / BP_CH; ++sub) {
+        const int k0 = ci * BP_R + sub * BP_CH;
+        if (k0 >= rows) break;
+        const int k1 = min(k0 + BP_CH, rows);
+        // steady state: a full sub-chunk whose BP_CH output rows (k0 - hm ...) are interior in the row direction
+        const bool fast = k0 >= 2 * BP_CH && k0 + BP_CH < rows;
+        if (ok) {
+          const float* s = S + (size_t)(buf * BP_R + sub * BP_CH) * spitch + c;
+          if (fast) {
+            float* rg = ring + ((k0 & (BP_RING - 1)) * cols) + c;   // k0 is a multiple of BP_CH: no wrap inside the sub-chunk
+            float v[BP_CH];
+#pragma unroll
+            for (int i = 0; i < BP_CH; ++i) v[i] = s[i * spitch];
+#pragma unroll
+            for (int i = 0; i < BP_CH; ++i) { run = run + v[i]; rg[i * cols] = run; }     // column pass :59-65
+          } else {
+            float v[BP_CH];
+#pragma unroll
+            for (int i = 0; i < BP_CH; ++i) v[i] = (k0 + i < rows) ? s[(size_t)i * spitch] : 0.0f;
+#pragma unroll
+            for (int i = 0; i < BP_CH; ++i) {
+              if (k0 + i < rows) {
+                run = (k0 + i == 0) ? v[i] : run + v[i];
+                ring[((k0 + i) & (BP_RING - 1)) * cols + c] = run;
+              }
+            }
+          }
+        }
+        if (k1 == kend) {   // last read of this chunk buffer: hand it back to the producer
+          __syncwarp();
+          if (lane == 0) { fence_proxy_async(); mbar_arrive(empty + buf); }
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(nbar) : "memory");
+        const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;
+        if (ok) {
+          if (fast) {   // onext == k0 - hm here; taps: rows ro + h and ro - h - 1 of the ring, interior formula :99 / :94
+            const int ro0 = k0 - hm;
+            bp_box8(ring, cols, ro0 + ha, ro0 - ha - 1, jhiA, jloA, leftA, invA, dstA + (size_t)ro0 * cols + c);
+            if (dual) bp_box8(ring, cols, ro0 + hb, ro0 - hb - 1, jhiB, jloB, leftB, invB, dstB + (size_t)ro0 * cols + c);
+          } else {
+            for (int ro = onext; ro <= olast; ++ro) {
+              dstA[(size_t)ro * cols + c] = box_value_fw(ring, cols, inv_area, ro, ha, rows, jhiA, jloA, leftA, ncolA, invA);
+              if (dual) dstB[(size_t)ro * cols + c] = box_value_fw(ring, cols, inv_area, ro, hb, rows, jhiB, jloB, leftB, ncolB, invB);
+            }
+          }
+        }
+        onext = max(onext, olast + 1);
+      }
+    }
+  }
+}
+
+static int bp_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }   // (pitch / 4) odd: conflict-free 128-bit row accesses
+static size_t bp_smem_bytes(int cols) { return sizeof(float) * ((size_t)2 * BP_R * bp_spitch(cols) + (size_t)BP_RING * cols); }
+static bool bp_supported(const rbv_ctx* c) {
+  const int cols = c->P.cols;
+  return (cols & 3) == 0 && 64 + ((cols + 31) / 32) * 32 <= 1024 && bp_smem_bytes(cols) <= 225 * 1024;
+}
+static bool bp_use(const rbv_ctx* c, const void* src) {
+  if (!bp_supported(c) || ((uintptr_t)src & 15) != 0) return false;
+  if (c->tune[RBV_TUNE_BOX] == 1) return false;
+  if (c->tune[RBV_TUNE_BOX] == 2) return true;
+  return c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
+}
+static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
+                     int d0, int d1, int dual) {
+  const int cols = c->P.cols;
+  const int threads = 64 + ((cols + 31) / 32) * 32;
+  RBV_LAUNCH(c, k_boxpass, (planes), (threads), bp_smem_bytes(cols), in, out0, out1, c->P.rows, cols, in_stride, out_stride, nz, d0, d1,
+             dual, bp_spitch(cols));
+  return RBV_OK;
+}
+
+int fe_init(rbv_ctx* c) {
+  (void)c;   // the current device is the context's; the limit is per device and shared by every context on it
+  RBV_CUDA(cudaFuncSetAttribute(k_boxpass, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+  return RBV_OK;
+}
+
 // ScaleSpace::build (scale_space.cpp:203-208): 3 box passes per scale, both scales from the same input.
 // Buffers are [lane][scale][N]; result: scale s of lane b = bufA[(b*2+s)*N].
 int fe_scale_space(rbv_ctx* c, const float* d_img) {
   const int rows = c->P.rows, cols = c->P.cols, B = c->P.lanes;
   const size_t N = (size_t)c->P.npix;
+  if (bp_use(c, d_img)) {   // fused passes: 64 N -> 44 N bytes of traffic per frame, 3 launches instead of 6
+    bp_launch(c, d_img, c->bufA, c->bufA + N, B, N, 2 * N, 1, c->widths[0][0], c->widths[1][0], 1);
+    bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
+    bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+    RBV_CUDA(cudaGetLastError());
+    return RBV_OK;
+  }
   // pass 0: one row prefix per lane, one column scan feeding both box widths (widths[0][0], widths[1][0])
   {
     RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, B)), (32), 0, d_img, c->rowsum, rows, cols, N, N);
@@ -191,8 +459,13 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {
   const int rows = c->P.rows, cols = c->P.cols;
   const size_t N = (size_t)c->P.npix;
-  RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 1)), (32), 0, d_in, c->rowsum, rows, cols, N, N);
   const int d = c->widths[scale][pass];
+  if (c->tune[RBV_TUNE_BOX] == 2 && bp_use(c, d_in)) {
+    bp_launch(c, d_in, d_out, d_out, 1, N, N, 1, d, d, 0);
+    RBV_CUDA(cudaGetLastError());
+    return RBV_OK;
+  }
+  RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 1)), (32), 0, d_in, c->rowsum, rows, cols, N, N);
   const int W = CB_TPB - (2 * (d / 2) + 1);
   RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 1)), (CB_TPB), 0, c->rowsum, d_out, d_out, rows, cols, N, N, 1, d, d, 0);
   RBV_CUDA(cudaGetLastError());

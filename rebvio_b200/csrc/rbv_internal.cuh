@@ -130,7 +130,8 @@ struct rbv_ctx {
   float* h_lm;
   float* h_img;     // pinned staging for rbv_detect host frames [B][N]
   unsigned long long launches;  // kernels launched since creation
-  unsigned long long klaunch[32];   // per kernel id
+  unsigned long long klaunch[48];   // per kernel id
+  int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
   int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
   void* prof;                       // ProfState* (rbv_api.cu)
 };
@@ -148,7 +149,8 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_fill) X(k_rowscan) X(k_colbox) X(k_detect_flags) X(k_detect_scan) X(k_detect_emit) X(k_join) X(k_tune)       \
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
-  X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)
+  X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
+  X(k_field_band) X(k_boxpass)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
@@ -177,6 +179,8 @@ void rbv_set_error(const char* fmt, ...);
   } while (0)
 
 // ---- launchers (host functions defined in the .cu files) ----
+int fe_init(rbv_ctx* c);   // per-device kernel attributes (dynamic shared memory limits)
+int tr_init(rbv_ctx* c);
 int fe_scale_space(rbv_ctx* c, const float* d_img);
 int fe_detect(rbv_ctx* c, rbv_map* map);
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out);

@@ -46,10 +46,106 @@ __global__ void __launch_bounds__(128) k_field_build(KeylineSoA K, const int* __
   }
 }
 
+// Band form of the same rule: one block owns `band_rows` image rows of one lane's field in SHARED memory. It scans the
+// lane's keylines for those whose normal line can reach the band (|r| <= search range, so pos.y within reach + 1 rows),
+// clips each line to the r-interval that lands in the band, and resolves "min (|r|, -idx)" with shared-memory atomics;
+// the finished band is written to HBM once, coalesced (no separate reset pass, no global atomics). The result is the
+// minimum over the same candidate set as k_field_build, hence identical for any keyline order.
+#define FB_TPB 512
+__global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
+                                                       unsigned* __restrict__ field, const __grid_constant__ DevParams P, int band_rows) {
+  extern __shared__ __align__(16) unsigned fb_cell[];
+  __shared__ int s_lo, s_hi;
+  const int b = blockIdx.y, t = threadIdx.x;
+  const int rows = P.rows, cols = P.cols;
+  const int r0 = blockIdx.x * band_rows, r1 = min(r0 + band_rows, rows);
+  const int ncell = (r1 - r0) * cols;
+  const int n = count[b];
+  for (int i = t; i < ncell; i += FB_TPB) fb_cell[i] = RBV_FIELD_EMPTY;
+  if (t == 0) { s_lo = n; s_hi = 0; }
+  __syncthreads();
+  const int ra0 = P.field_r0, rb0 = P.field_r0 + P.field_nr - 1;
+  const float reach = (float)max(-ra0, rb0) + 1.0f;
+  const float ylo = (float)r0 - reach, yhi = (float)(r1 - 1) + reach;
+  const size_t base = (size_t)b * P.kmax;
+  {  // index range of the keylines that can reach the band (row-major ids make it a narrow range; any order is handled)
+    int lo = n, hi = 0;
+    for (int i = t; i < n; i += FB_TPB) {
+      const float y = K.pos[base + i].y;
+      if (y >= ylo && y <= yhi) { lo = min(lo, i); hi = max(hi, i + 1); }
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+      lo = min(lo, __shfl_xor_sync(0xFFFFFFFFu, lo, off));
+      hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, off));
+    }
+    if ((t & 31) == 0 && hi > lo) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+  }
+  __syncthreads();
+  const int lo = s_lo, hi = s_hi;
+  const float thr = threshold[b];
+  const float r0f = (float)r0, r1f = (float)r1, colsf = (float)cols;
+  for (int idx = lo + t; idx < hi; idx += FB_TPB) {
+    const size_t o = base + idx;
+    const float2 p = K.pos[o];
+    if (!(p.y >= ylo && p.y <= yhi)) continue;
+    const float gn = K.gnorm[o];
+    if (thr > 0.0f && gn < thr) continue;                                                // core.hpp:47
+    const float2 g = K.grad[o];
+    const float ux = g.x / gn, uy = g.y / gn;
+    int ra = ra0, rb = rb0;
+    if (fabsf(uy) > 1e-2f) {   // rows hit are monotone in r: clip to the r-interval that can land in [r0, r1) (+-1 margin, re-tested below)
+      const float t0 = (r0f - 0.5f - p.y) / uy, t1 = (r1f - 0.5f - p.y) / uy;
+      ra = max(ra, __float2int_rd(fminf(t0, t1)) - 1);
+      rb = min(rb, __float2int_ru(fmaxf(t0, t1)) + 1);
+    }
+    const unsigned lowkey = 0xFFFFFFu - (unsigned)idx;
+    for (int r = ra; r <= rb; ++r) {
+      const float fr = (float)r;
+      const float ry = roundf(uy * fr + p.y);                                            // core.hpp:50-51, getIndex :66-71
+      if (!(ry >= r0f && ry < r1f)) continue;
+      const float rx = roundf(ux * fr + p.x);
+      if (!(rx >= 0.0f && rx < colsf)) continue;
+      unsigned* cp = fb_cell + ((int)ry - r0) * cols + (int)rx;
+      const unsigned key = ((unsigned)abs(r) << 24) | lowkey;                            // :54-56 as min over (|r|, -idx)
+      if (*(volatile unsigned*)cp <= key) continue;
+      atomicMin(cp, key);
+    }
+  }
+  __syncthreads();
+  unsigned* dst = field + (size_t)b * P.npix + (size_t)r0 * cols;
+  if ((cols & 3) == 0) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(fb_cell);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    for (int i = t; i < ncell / 4; i += FB_TPB) d4[i] = s4[i];
+  } else {
+    for (int i = t; i < ncell; i += FB_TPB) dst[i] = fb_cell[i];
+  }
+}
+
+// rows per band: as many as fit ~100 KB (two blocks per SM); below 16 rows the keyline scan would be repeated too often
+static int field_band_rows(const rbv_ctx* c) {
+  const int by_smem = (100 * 1024) / (c->P.cols * 4);
+  return by_smem > 32 ? 32 : by_smem;
+}
+
+int tr_init(rbv_ctx* c) {
+  (void)c;   // the current device is the context's
+  RBV_CUDA(cudaFuncSetAttribute(k_field_band, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  return RBV_OK;
+}
+
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
-  RBV_LAUNCH(c, k_field_build, (dim3((P.keylines_max + 127) / 128, P.lanes)), (128), 0, map->k, map->count, map->threshold, c->field, P);
+  const int H = field_band_rows(c);
+  const bool band = c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 16);
+  if (band && H >= 1) {
+    const size_t smem = (size_t)H * P.cols * 4;
+    RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, map->k, map->count, map->threshold, c->field, P, H);
+  } else {
+    { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
+    RBV_LAUNCH(c, k_field_build, (dim3((P.keylines_max + 127) / 128, P.lanes)), (128), 0, map->k, map->count, map->threshold, c->field, P);
+  }
   c->field_map = map;
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;

@@ -84,6 +84,11 @@ class Context:
                                 C.byref(h)))
         self.h = h
         check(self.L.rbv_set_reduce_mode(self.h, reduce_mode))
+        # implementation overrides for test / profiling runs (0 = automatic): RBV_TUNE_FIELD, RBV_TUNE_BOX in the environment
+        import os
+        for key, name in ((capi.TUNE_FIELD, "RBV_TUNE_FIELD"), (capi.TUNE_BOX, "RBV_TUNE_BOX")):
+            if os.environ.get(name):
+                self.set_tuning(key, int(os.environ[name]))
 
     def close(self):
         if self.h:
@@ -91,6 +96,7 @@ class Context:
             self.h = None
 
     def set_reduce_mode(self, mode): check(self.L.rbv_set_reduce_mode(self.h, mode))
+    def set_tuning(self, key, value): check(self.L.rbv_set_tuning(self.h, int(key), int(value)))
     def set_stream(self, cuda_stream): check(self.L.rbv_set_stream(self.h, C.c_void_p(cuda_stream)))
     def sync(self): check(self.L.rbv_sync(self.h))
     def launch_count(self): return int(self.L.rbv_launch_count(self.h))
@@ -117,6 +123,10 @@ class Context:
             if nl.value:
                 out[name] = (ms.value, nt.value, nl.value)
         return out
+
+    def profile_launches(self):
+        """-> {kernel: launches since the last profile_reset (or creation)}"""
+        return {n: v[2] for n, v in self.profile_read().items()}
 
     def servo_threshold(self, threshold, last_count):
         return float(self.L.rbv_servo_threshold(C.byref(self.det), float(threshold), int(last_count)))

@@ -9,10 +9,12 @@ from rebvio_b200 import capi, host
 
 
 class GpuImpl:
-    def __init__(self, cam, det, mapc, core, lanes=1, lane=0, reduce_mode=capi.REDUCE_ORDERED, device=0):
+    def __init__(self, cam, det, mapc, core, lanes=1, lane=0, reduce_mode=capi.REDUCE_ORDERED, device=0, tune=None):
         conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
         self.ctx = host.Context(conv(capi.Camera, cam), conv(capi.DetectorCfg, det), conv(capi.MapCfg, mapc),
                                 conv(capi.CoreCfg, core), lanes=lanes, device=device, reduce_mode=reduce_mode)
+        for key, value in (tune or {}).items():
+            self.ctx.set_tuning(key, value)
         self.lanes, self.lane = lanes, lane
         self.threshold = float(np.float32(det.threshold))
         self.last_count = 0

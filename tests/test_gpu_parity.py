@@ -17,10 +17,15 @@ pytestmark = pytest.mark.gpu
 SCORE_RTOL = 5e-4   # FAST mode only; ORDERED mode reproduces the score bit for bit
 
 
-def _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED):
+def _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED, tune=None):
     from gpu_impl import GpuImpl
     cam, det, mapc, core = cfg
-    return GpuImpl(cam, det, mapc, core, lanes=lanes, lane=lane, reduce_mode=mode)
+    return GpuImpl(cam, det, mapc, core, lanes=lanes, lane=lane, reduce_mode=mode, tune=tune)
+
+
+# both implementations of the two stages that have an alternative kernel (include/rebvio_b200.h, rbv_set_tuning)
+SPLIT = {capi.TUNE_BOX: 1, capi.TUNE_FIELD: 1}
+FUSED = {capi.TUNE_BOX: 2, capi.TUNE_FIELD: 2}
 
 
 @pytest.mark.parametrize("name", common.GOLDEN_CASES)
@@ -113,6 +118,48 @@ def test_try_vel_fast_vs_ordered_indices_and_sums():
                 assert abs(sg - so) <= SCORE_RTOL * abs(so)
                 assert H.rel_err(JJg, JJo) <= 1e-5 and H.rel_err(JFg, JFo) <= 1e-5
         g.close(); orc.close()
+
+
+@pytest.mark.parametrize("name,nf,tune", [("C2", 3, FUSED), ("C2", 3, SPLIT), ("C1", 3, FUSED), ("C5:320x240", 4, FUSED),
+                                          ("C3", 2, FUSED)])
+def test_alternative_kernels_free_running(name, nf, tune):
+    """the fused box-pass kernel (TMA-staged row chunks) and the shared-memory band distance field, forced on, and the
+    split / global-atomic forms, forced on: whole chain bit-exact against the oracle either way (C3 is too wide for the
+    fused box pass and falls back, the band field still runs)"""
+    spec, frames, R_rel = common.sequence(name, nf)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    T = H.run_stages(orc, frames, R_rel)
+    g = _gpu(cfg, lanes=3, lane=2, tune=tune)
+    G = H.run_stages(g, frames, R_rel)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    names = g.ctx.profile_launches()
+    if tune is FUSED:
+        assert names.get("k_field_band", 0) > 0 and names.get("k_field_build", 0) == 0
+        if spec.cam.cols <= 832:
+            assert names.get("k_boxpass", 0) > 0 and names.get("k_colbox", 0) == 0
+    else:
+        assert names.get("k_field_build", 0) > 0 and names.get("k_colbox", 0) > 0 and names.get("k_boxpass", 0) == 0
+    g.close(); orc.close()
+
+
+@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (203, 832)])
+def test_fused_box_pass_kernel_vs_oracle(rows, cols):
+    """the fused createIntegralImage + average kernel on ragged row counts and every supported width class"""
+    cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 200)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
+    ctx = host.Context(conv(capi.Camera, cfg[0]), conv(capi.DetectorCfg, cfg[1]), conv(capi.MapCfg, cfg[2]), conv(capi.CoreCfg, cfg[3]))
+    ctx.set_tuning(capi.TUNE_BOX, 2)
+    rng = np.random.RandomState(rows * 7 + cols)
+    img = rng.randint(0, 256, (rows, cols)).astype(np.float32) * np.float32(3.0)
+    ctx.profile_reset()
+    for s in range(2):
+        for p in range(3):
+            assert np.array_equal(H.bits(ctx.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img))), (s, p)
+    assert ctx.profile_launches().get("k_boxpass", 0) == 6
+    ctx.close(); orc.close()
 
 
 @pytest.mark.parametrize("rows,cols", [(33, 47), (97, 131), (480, 752), (1080, 1920)])
