@@ -183,17 +183,17 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-// wait with back-off: a spinning warp would take issue slots from the warps it is waiting for
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity, unsigned sleep_ns) {
+// wait on a phase: try_wait with a suspend-time hint parks the warp in hardware instead of spinning (a spinning warp
+// takes issue slots from the warps it is waiting for); the loop only re-arms after the hint expires.
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
   const unsigned a = smem_u32(bar);
   long long t0 = 0;
   for (int spin = 0;; ++spin) {
     unsigned ok;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(a), "r"(parity), "r"(0x989680u) : "memory");
     if (ok) return;
-    __nanosleep(sleep_ns);
-    if ((spin & 1023) == 0) {
+    if ((spin & 255) == 0) {
       if (spin == 0) t0 = clock64();
       else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
     }
@@ -227,23 +227,62 @@ __device__ __forceinline__ float box_value_fw(const float* __restrict__ ring, in
   return v * inv_area[rhi - max(rlo, -1)][ncol];
 }
 
-// BP_CH interior output rows: output i takes ring rows (hi0 + i) and (lo0 + i) (mod BP_RING), columns jhi / jlo
-__device__ __forceinline__ void bp_box8(const float* __restrict__ ring, int cols, int hi0, int lo0, int jhi, int jlo, bool left, float inv,
-                                        float* __restrict__ dst) {
-  if (left) {
+// shared-memory accesses by 32-bit shared address: keeps the address arithmetic of the hot loops in 32-bit integer adds
+__device__ __forceinline__ float lds_f32(unsigned a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));   // volatile: ordered against the barrier / store asms, but ALU work and global stores may move across it
+  return v;
+}
+__device__ __forceinline__ float2 lds_f32x2(unsigned a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f32(unsigned a, float x) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(x) : "memory"); }
+__device__ __forceinline__ void sts_f32x2(unsigned a, float x, float y) {
+  asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+
+// taps of one output column: shared addresses of ring row 0 at the right / left tap column, divisor, left-tap flag
+struct BpTap {
+  unsigned p_hi, p_lo;
+  float inv;
+  bool left;
+};
+__device__ __forceinline__ BpTap bp_tap(unsigned ring_a, int c, int h, int cols) {
+  BpTap t;
+  const int jhi = min(c + h, cols - 1), jlo = c - h - 1;
+  t.left = jlo >= 0;
+  t.p_hi = ring_a + 4u * (unsigned)jhi;
+  t.p_lo = ring_a + 4u * (unsigned)max(jlo, 0);
+  t.inv = (float)(1.0 / (double)((float)(2 * h + 1) * (float)(jhi - max(jlo, -1))));     // interior-row divisor (:72 / :168)
+  return t;
+}
+
+// BP_CH interior output rows of two adjacent columns (t0: column c, t1: column c + 1). Output i takes ring rows
+// (ro0 + h + i) and (ro0 - h - 1 + i) mod BP_RING: ((A - B) - C) + D (:99), or A - C where there is no left tap (:94).
+template <bool MIXED>
+__device__ __forceinline__ void bp_box_rows(const BpTap& t0, const BpTap& t1, int ro0, int h, unsigned colb, float* __restrict__ dst0,
+                                            float* __restrict__ dst1, bool ok0, bool ok1, int cols) {
+  const unsigned ringb = BP_RING * colb;
+  unsigned hi_off = (unsigned)((ro0 + h) & (BP_RING - 1)) * colb;
+  unsigned lo_off = (unsigned)((ro0 - h - 1) & (BP_RING - 1)) * colb;
 #pragma unroll
-    for (int i = 0; i < BP_CH; ++i) {
-      const float* hi = ring + ((hi0 + i) & (BP_RING - 1)) * cols;
-      const float* lo = ring + ((lo0 + i) & (BP_RING - 1)) * cols;
-      dst[i * cols] = (((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo]) * inv;                 // :99
+  for (int i = 0; i < BP_CH; ++i) {
+    const float a0 = lds_f32(t0.p_hi + hi_off), b0 = lds_f32(t0.p_lo + hi_off);
+    const float c0 = lds_f32(t0.p_hi + lo_off), d0 = lds_f32(t0.p_lo + lo_off);
+    const float a1 = lds_f32(t1.p_hi + hi_off), b1 = lds_f32(t1.p_lo + hi_off);
+    const float c1 = lds_f32(t1.p_hi + lo_off), d1 = lds_f32(t1.p_lo + lo_off);
+    float v0 = ((a0 - b0) - c0) + d0, v1 = ((a1 - b1) - c1) + d1;
+    if (MIXED) {
+      if (!t0.left) v0 = a0 - c0;
+      if (!t1.left) v1 = a1 - c1;
     }
-  } else {
-#pragma unroll
-    for (int i = 0; i < BP_CH; ++i) {
-      const float* hi = ring + ((hi0 + i) & (BP_RING - 1)) * cols;
-      const float* lo = ring + ((lo0 + i) & (BP_RING - 1)) * cols;
-      dst[i * cols] = (hi[jhi] - lo[jhi]) * inv;                                         // :94
-    }
+    if (ok0) *dst0 = v0 * t0.inv;
+    if (ok1) *dst1 = v1 * t1.inv;
+    dst0 += cols; dst1 += cols;
+    hi_off += colb; if (hi_off == ringb) hi_off = 0u;
+    lo_off += colb; if (lo_off == ringb) lo_off = 0u;
   }
 }
 
@@ -255,7 +294,15 @@ __device__ __forceinline__ void bp_scan4(float4& v, float& carry, bool first) {
   carry = v.w;
 }
 
-__global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ in, float* __restrict__ out0, float* __restrict__ out1,
+#define BP_MAX_THREADS 640
+// column warps among `nwarps` warps: all but warp 0 (producer), warp 1 (row pass) and warps 5, 9, 13, ... (left idle)
+__host__ __device__ inline int bp_ncw(int nwarps) {
+  int n = 0;
+  for (int w = 2; w < nwarps; ++w) n += (w & 3) != 1;
+  return n;
+}
+
+__global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __restrict__ in, float* __restrict__ out0, float* __restrict__ out1,
                                                      int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
                                                      int d1, int dual, int spitch) {
   extern __shared__ __align__(128) float bp_smem[];
@@ -267,7 +314,9 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
   unsigned long long* scanned = bars + 2;
   unsigned long long* empty = bars + 4;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ncw = (int)(blockDim.x >> 5) - 2;
+  // warp roles: 0 producer, 1 row pass; warps 5, 9, 13, ... exit so that the row-pass warp has its scheduler (warp id % 4)
+  // to itself (its dependent add chain is the critical path); every other warp is a column warp.
+  const int ncw = bp_ncw((int)(blockDim.x >> 5));
   const int plane = blockIdx.x;
   const int z = dual ? 0 : plane % nz;
   const int ha = (z ? d1 : d0) / 2;
@@ -285,22 +334,25 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
   __syncthreads();
   const int nchunks = (rows + BP_R - 1) / BP_R;
   if (warp == 0) {
-    if (lane == 0) {
-      for (int ci = 0; ci < nchunks; ++ci) {
-        const int buf = ci & 1;
-        if (ci >= 2) mbar_wait(empty + buf, (unsigned)(((ci >> 1) - 1) & 1), 200);
-        fence_proxy_async();
-        const int nr = min(BP_R, rows - ci * BP_R);
+    // lane 0 waits for the buffer and arms the barrier; lanes 0..nr-1 then issue one row copy each (a single thread
+    // needs ~125 cycles per UBLKCP, which would put 2000 cycles of issue time on every chunk)
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci & 1;
+      const int nr = min(BP_R, rows - ci * BP_R);
+      if (lane == 0) {
+        if (ci >= 2) mbar_wait(empty + buf, (unsigned)(((ci >> 1) - 1) & 1));
+        // (the consumers fence generic -> async proxy before they arrive on `empty`)
         mbar_arrive_expect_tx(full + buf, (unsigned)(nr * cols * 4));
-        for (int j = 0; j < nr; ++j)
-          bulk_g2s(S + (size_t)(buf * BP_R + j) * spitch, src + (size_t)(ci * BP_R + j) * cols, (unsigned)(cols * 4), full + buf);
       }
+      __syncwarp();
+      if (lane < nr)
+        bulk_g2s(S + (size_t)(buf * BP_R + lane) * spitch, src + (size_t)(ci * BP_R + lane) * cols, (unsigned)(cols * 4), full + buf);
     }
   } else if (warp == 1) {
     const int n4 = cols >> 2;
     for (int ci = 0; ci < nchunks; ++ci) {
       const int buf = ci & 1;
-      mbar_wait(full + buf, (unsigned)((ci >> 1) & 1), 40);
+      mbar_wait(full + buf, (unsigned)((ci >> 1) & 1));
       if (lane < BP_R) {
         float4* row = reinterpret_cast<float4*>(S + (size_t)(buf * BP_R + lane) * spitch);
         float carry = 0.0f;
@@ -323,22 +375,34 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
       }
       mbar_arrive(scanned + buf);
     }
-  } else {
-    const int c = tid - 64;
-    const bool ok = c < cols;
+  } else if ((warp & 3) != 1) {
+    const int q = (warp - 2) - ((warp - 2) >> 2);       // column-warp index
+    // this thread owns columns c0 and c0 + 32: consecutive lanes = consecutive columns, so every shared access of the warp
+    // is unit-stride (conflict-free) and every global store a full 128-byte segment
+    const int cq[2] = {q * 64 + lane, q * 64 + 32 + lane};
+    const bool okc[2] = {cq[0] < cols, cq[1] < cols};
+    const int cc[2] = {min(cq[0], cols - 1), min(cq[1], cols - 1)};   // clamped: loads stay in range, stores are predicated
     float* dstA = out0 + (size_t)plane * out_plane_stride;
     float* dstB = out1 + (size_t)plane * out_plane_stride;
-    const int jhiA = min(c + ha, cols - 1), jloA = c - ha - 1, ncolA = jhiA - max(jloA, -1);
-    const int jhiB = min(c + hb, cols - 1), jloB = c - hb - 1, ncolB = jhiB - max(jloB, -1);
-    const bool leftA = jloA >= 0, leftB = jloB >= 0;
-    const float invA = ok ? (float)(1.0 / (double)((float)(2 * ha + 1) * (float)ncolA)) : 0.0f;
-    const float invB = ok ? (float)(1.0 / (double)((float)(2 * hb + 1) * (float)ncolB)) : 0.0f;
+    const unsigned ring_a = smem_u32(ring), S_a = smem_u32(S);
+    const unsigned colb = 4u * (unsigned)cols, spb = 4u * (unsigned)spitch;
+    const BpTap tA0 = bp_tap(ring_a, cc[0], ha, cols), tA1 = bp_tap(ring_a, cc[1], ha, cols);
+    const BpTap tB0 = bp_tap(ring_a, cc[0], hb, cols), tB1 = bp_tap(ring_a, cc[1], hb, cols);
+    const bool mixed = q == 0;                          // only the first few columns lack a left tap
+    // generic (border-row) path
+    int jhi[2][2], jlo[2][2], ncol[2][2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      jhi[0][j] = min(cc[j] + ha, cols - 1); jlo[0][j] = cc[j] - ha - 1; ncol[0][j] = jhi[0][j] - max(jlo[0][j], -1);
+      jhi[1][j] = min(cc[j] + hb, cols - 1); jlo[1][j] = cc[j] - hb - 1; ncol[1][j] = jhi[1][j] - max(jlo[1][j], -1);
+    }
     const unsigned nbar = (unsigned)(ncw * 32);
-    float run = 0.0f;
+    float run0 = 0.0f, run1 = 0.0f;
     int onext = 0;
     for (int ci = 0; ci < nchunks; ++ci) {
       const int buf = ci & 1;
-      mbar_wait(scanned + buf, (unsigned)((ci >> 1) & 1), 100);
+      if (q == 0) mbar_wait(scanned + buf, (unsigned)((ci >> 1) & 1));   // one warp watches the mbarrier,
+      asm volatile("bar.sync 1, %0;" ::"r"(nbar) : "memory");                  // the others sleep on the hardware barrier
       const int kend = min((ci + 1) * BP_R, rows);
 #pragma unroll
       for (int sub = 0; sub < BP_R / BP_CH; ++sub) {
@@ -347,24 +411,30 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
         const int k1 = min(k0 + BP_CH, rows);
         // steady state: a full sub-chunk whose BP_CH output rows (k0 - hm ...) are interior in the row direction
         const bool fast = k0 >= 2 * BP_CH && k0 + BP_CH < rows;
-        if (ok) {
-          const float* s = S + (size_t)(buf * BP_R + sub * BP_CH) * spitch + c;
+        {
+          const unsigned sa = S_a + (unsigned)((buf * BP_R + sub * BP_CH) * spitch + cc[0]) * 4u;
+          const unsigned d1 = (unsigned)(cc[1] - cc[0]) * 4u;
           if (fast) {
-            float* rg = ring + ((k0 & (BP_RING - 1)) * cols) + c;   // k0 is a multiple of BP_CH: no wrap inside the sub-chunk
-            float v[BP_CH];
+            const unsigned ra = ring_a + (unsigned)((k0 & (BP_RING - 1)) * cols + cc[0]) * 4u;   // k0 % BP_CH == 0: no wrap inside
+            float v0[BP_CH], v1[BP_CH];
 #pragma unroll
-            for (int i = 0; i < BP_CH; ++i) v[i] = s[i * spitch];
+            for (int i = 0; i < BP_CH; ++i) { v0[i] = lds_f32(sa + i * spb); v1[i] = lds_f32(sa + i * spb + d1); }
 #pragma unroll
-            for (int i = 0; i < BP_CH; ++i) { run = run + v[i]; rg[i * cols] = run; }     // column pass :59-65
+            for (int i = 0; i < BP_CH; ++i) {                                            // column pass :59-65
+              run0 = run0 + v0[i]; run1 = run1 + v1[i];
+              if (okc[0]) sts_f32(ra + i * colb, run0);
+              if (okc[1]) sts_f32(ra + i * colb + d1, run1);
+            }
           } else {
-            float v[BP_CH];
-#pragma unroll
-            for (int i = 0; i < BP_CH; ++i) v[i] = (k0 + i < rows) ? s[(size_t)i * spitch] : 0.0f;
 #pragma unroll
             for (int i = 0; i < BP_CH; ++i) {
               if (k0 + i < rows) {
-                run = (k0 + i == 0) ? v[i] : run + v[i];
-                ring[((k0 + i) & (BP_RING - 1)) * cols + c] = run;
+                const float x0 = lds_f32(sa + i * spb), x1 = lds_f32(sa + i * spb + d1);
+                run0 = (k0 + i == 0) ? x0 : run0 + x0;
+                run1 = (k0 + i == 0) ? x1 : run1 + x1;
+                const unsigned ra = ring_a + (unsigned)(((k0 + i) & (BP_RING - 1)) * cols + cc[0]) * 4u;
+                if (okc[0]) sts_f32(ra, run0);
+                if (okc[1]) sts_f32(ra + d1, run1);
               }
             }
           }
@@ -375,15 +445,26 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
         }
         asm volatile("bar.sync 1, %0;" ::"r"(nbar) : "memory");
         const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;
-        if (ok) {
-          if (fast) {   // onext == k0 - hm here; taps: rows ro + h and ro - h - 1 of the ring, interior formula :99 / :94
-            const int ro0 = k0 - hm;
-            bp_box8(ring, cols, ro0 + ha, ro0 - ha - 1, jhiA, jloA, leftA, invA, dstA + (size_t)ro0 * cols + c);
-            if (dual) bp_box8(ring, cols, ro0 + hb, ro0 - hb - 1, jhiB, jloB, leftB, invB, dstB + (size_t)ro0 * cols + c);
-          } else {
-            for (int ro = onext; ro <= olast; ++ro) {
-              dstA[(size_t)ro * cols + c] = box_value_fw(ring, cols, inv_area, ro, ha, rows, jhiA, jloA, leftA, ncolA, invA);
-              if (dual) dstB[(size_t)ro * cols + c] = box_value_fw(ring, cols, inv_area, ro, hb, rows, jhiB, jloB, leftB, ncolB, invB);
+        if (fast) {   // onext == k0 - hm here
+          const int ro0 = k0 - hm;
+          float* dA = dstA + (size_t)ro0 * cols;
+          if (mixed) bp_box_rows<true>(tA0, tA1, ro0, ha, colb, dA + cq[0], dA + cq[1], okc[0], okc[1], cols);
+          else bp_box_rows<false>(tA0, tA1, ro0, ha, colb, dA + cq[0], dA + cq[1], okc[0], okc[1], cols);
+          if (dual) {
+            float* dB = dstB + (size_t)ro0 * cols;
+            if (mixed) bp_box_rows<true>(tB0, tB1, ro0, hb, colb, dB + cq[0], dB + cq[1], okc[0], okc[1], cols);
+            else bp_box_rows<false>(tB0, tB1, ro0, hb, colb, dB + cq[0], dB + cq[1], okc[0], okc[1], cols);
+          }
+        } else {
+          for (int ro = onext; ro <= olast; ++ro) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              if (!okc[j]) continue;
+              dstA[(size_t)ro * cols + cq[j]] =
+                  box_value_fw(ring, cols, inv_area, ro, ha, rows, jhi[0][j], jlo[0][j], jlo[0][j] >= 0, ncol[0][j], j ? tA1.inv : tA0.inv);
+              if (dual)
+                dstB[(size_t)ro * cols + cq[j]] =
+                    box_value_fw(ring, cols, inv_area, ro, hb, rows, jhi[1][j], jlo[1][j], jlo[1][j] >= 0, ncol[1][j], j ? tB1.inv : tB0.inv);
             }
           }
         }
@@ -395,9 +476,15 @@ __global__ void __launch_bounds__(1024, 1) k_boxpass(const float* __restrict__ i
 
 static int bp_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }   // (pitch / 4) odd: conflict-free 128-bit row accesses
 static size_t bp_smem_bytes(int cols) { return sizeof(float) * ((size_t)2 * BP_R * bp_spitch(cols) + (size_t)BP_RING * cols); }
+static int bp_threads(int cols) {   // smallest block whose column warps cover cols at two columns per thread
+  const int need = (cols + 63) / 64;
+  int w = 3;
+  while (bp_ncw(w) < need) ++w;
+  return w * 32;
+}
 static bool bp_supported(const rbv_ctx* c) {
   const int cols = c->P.cols;
-  return (cols & 3) == 0 && 64 + ((cols + 31) / 32) * 32 <= 1024 && bp_smem_bytes(cols) <= 225 * 1024;
+  return (cols & 3) == 0 && bp_threads(cols) <= BP_MAX_THREADS && bp_smem_bytes(cols) <= 225 * 1024;
 }
 static bool bp_use(const rbv_ctx* c, const void* src) {
   if (!bp_supported(c) || ((uintptr_t)src & 15) != 0) return false;
@@ -408,7 +495,7 @@ static bool bp_use(const rbv_ctx* c, const void* src) {
 static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
                      int d0, int d1, int dual) {
   const int cols = c->P.cols;
-  const int threads = 64 + ((cols + 31) / 32) * 32;
+  const int threads = bp_threads(cols);
   RBV_LAUNCH(c, k_boxpass, (planes), (threads), bp_smem_bytes(cols), in, out0, out1, c->P.rows, cols, in_stride, out_stride, nz, d0, d1,
              dual, bp_spitch(cols));
   return RBV_OK;
