@@ -327,30 +327,35 @@ def run_b200(args):
     pipe.close()
 
     # ---- leg 2: end to end through the host-buffer API ---------------------------------------------------------
+    # uint8 camera frames in pinned host memory -> rbv_detect_u8 (upload + x3 conversion on the device, rebvio.cpp:43)
+    # -> tracker; the upload of frame k+1 is started after the front end of frame k (rbv_prefetch_frames) so that it
+    # overlaps the tracker, like the reference's acquisition thread overlaps its estimation thread.
     if not args.no_e2e:
-        h_frames = torch.empty((nf, B, spec.cam.rows, spec.cam.cols), dtype=torch.float32, pin_memory=True)
-        h_frames.copy_(d_frames)
+        h_frames = torch.empty((nf + 1, B, spec.cam.rows, spec.cam.cols), dtype=torch.uint8, pin_memory=True)
+        h_frames[:nf].copy_(frames_u8)
+        h_frames[nf].copy_(frames_u8[nf - 1])
         torch.cuda.synchronize()
         hnp = h_frames.numpy()
         pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
-        pipe.push(frames=hnp[0])
+        pipe.push(frames=hnp[0], next_frames=hnp[1])
         for k in range(1, 1 + W):
-            pipe.push(frames=hnp[k], R_rel=R_rel[k])
+            pipe.push(frames=hnp[k], R_rel=R_rel[k], next_frames=hnp[k + 1])
         barrier()
         t0 = time.perf_counter()
         for k in range(1 + W, 1 + W + K):
-            pipe.push(frames=hnp[k], R_rel=R_rel[k])
+            pipe.push(frames=hnp[k], R_rel=R_rel[k], next_frames=hnp[k + 1])
         pipe.ctx.sync()
         t1 = time.perf_counter()
         barrier()
         e2e_s = max_over_ranks(t1 - t0)
-        # bytes per step: frames + thresholds + per-lane inputs of g1/g2 (64 floats each, twice); outputs: counts,
-        # auto thresholds, LM state + 64 floats of lane outputs, match counters
+        # bytes per step: frames (1 byte per pixel) + thresholds + per-lane inputs of g1/g2 (64 floats each, twice);
+        # outputs: counts, auto thresholds, LM state + 64 floats of lane outputs, match counters
         lm_bytes = 4 * (3 + 1 + 9 + 3 + 2 + 3 + 3 + 1 + 9 + 16 * 16)
-        h2d = B * (N * 4 + 4 + 2 * 64 * 4)
+        h2d = B * (N + 4 + 2 * 64 * 4)
         d2h = B * (8 + lm_bytes + 64 * 4 + 8 * 4)
         line["e2e"] = {"value": frames_total / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                       "ms_per_step": 1e3 * e2e_s / K}
+                       "ms_per_step": 1e3 * e2e_s / K,
+                       "input": "uint8 frames in pinned host memory through rbv_detect_u8; next frame's upload overlapped (rbv_prefetch_frames)"}
         pipe.close()
         del h_frames, hnp
 

@@ -160,6 +160,20 @@ void rbv_map_release(rbv_ctx* ctx, rbv_map* map);
 int rbv_detect(rbv_ctx* ctx, rbv_map* map, const float* const* images, size_t pitch_bytes,
                const uint64_t* ts_us, const float* threshold, int* n_keylines, float* auto_threshold);
 
+/* same for 8-bit frames as the camera driver delivers them: replaces Rebvio::imageCallback's conversion
+ * `convertTo(CV_32FC1, 3.0)` (rebvio.cpp:43) + EdgeDetector::detect. The bytes are uploaded as they are (a quarter of
+ * the float traffic) and multiplied by 3.0f on the device, which is exact. Undistortion (rebvio.cpp:45, cv::undistort)
+ * is not part of this path: frames are taken as already rectified. */
+int rbv_detect_u8(rbv_ctx* ctx, rbv_map* map, const uint8_t* const* images, size_t pitch_bytes,
+                  const uint64_t* ts_us, const float* threshold, int* n_keylines, float* auto_threshold);
+
+/* start uploading the NEXT frames (B host pointers, u8 if is_u8 else float32) on the context's copy stream and return
+ * at once; the upload overlaps whatever runs on the compute stream (the tracker of the current frame — the reference
+ * overlaps acquisition and estimation with two threads, rebvio.cpp:56-117). The next rbv_detect / rbv_detect_u8 call
+ * whose images[0] equals this call's images[0] consumes the staged frames instead of copying again. Two slots. The
+ * host buffers must stay valid and unchanged until that detect call returns. */
+int rbv_prefetch_frames(rbv_ctx* ctx, const void* const* images, size_t pitch_bytes, int is_u8);
+
 /* same, frames already resident in device memory (lane-major contiguous [B][rows][cols] float32). */
 int rbv_detect_device(rbv_ctx* ctx, rbv_map* map, const float* d_images, const uint64_t* ts_us,
                       const float* threshold, int* n_keylines, float* auto_threshold);

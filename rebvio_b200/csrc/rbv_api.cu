@@ -282,7 +282,12 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaMallocHost((void**)&c->h_out, sizeof(float) * B * OUT_STRIDE));
   RBV_CUDA(cudaMallocHost((void**)&c->h_cnt, sizeof(int) * B * (CNT_STRIDE + 2)));
   RBV_CUDA(cudaMallocHost((void**)&c->h_lm, sizeof(LMState) * B));
-  RBV_CUDA(cudaMallocHost((void**)&c->h_img, sizeof(float) * B * N));
+  RBV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) {
+    RBV_CUDA(cudaMalloc(&c->raw[i], sizeof(float) * B * N));
+    RBV_CUDA(cudaEventCreateWithFlags(&c->raw_ready[i], cudaEventDisableTiming));
+    RBV_CUDA(cudaEventCreateWithFlags(&c->raw_free[i], cudaEventDisableTiming));
+  }
   RBV_CUDA(cudaDeviceSynchronize());   // the memsets above ran on the legacy stream; the context's stream is non-blocking
   *out = c;
   return RBV_OK;
@@ -306,7 +311,13 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
     for (int i = 0; i < p->created; ++i) { cudaEventDestroy(p->ev[i][0]); cudaEventDestroy(p->ev[i][1]); }
     delete p;
   }
-  cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm); cudaFreeHost(c->h_img);
+  cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm);
+  if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(c->raw[i]);
+    if (c->raw_ready[i]) cudaEventDestroy(c->raw_ready[i]);
+    if (c->raw_free[i]) cudaEventDestroy(c->raw_free[i]);
+  }
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -435,18 +446,101 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
   return RBV_OK;
 }
 
+// u8 -> float32 x 3.0 (Rebvio::imageCallback, rebvio.cpp:43: convertTo(CV_32FC1, 3.0)); exact in float32
+__global__ void k_u8_to_f32(const uint4* __restrict__ src16, float4* __restrict__ dst, const unsigned char* __restrict__ src, float* __restrict__ dstf,
+                            size_t n16, size_t n) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    const uint4 v = src16[i];
+    const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      dst[i * 4 + k] = make_float4((float)(w[k] & 0xFFu) * 3.0f, (float)((w[k] >> 8) & 0xFFu) * 3.0f, (float)((w[k] >> 16) & 0xFFu) * 3.0f,
+                                   (float)(w[k] >> 24) * 3.0f);
+  }
+  for (size_t i = n16 * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dstf[i] = (float)src[i] * 3.0f;
+}
+
+// H2D of B frames (element size esz) into a dense [B][N] device buffer on stream st: one copy when the host frames are
+// dense and back to back, else one copy per lane
+static int upload_frames(rbv_ctx* c, void* dst, const void* const* images, size_t pitch_bytes, size_t esz, cudaStream_t st) {
+  const size_t N = c->P.npix, row_bytes = esz * c->P.cols;
+  const int B = c->P.lanes;
+  if (pitch_bytes == 0) pitch_bytes = row_bytes;
+  if (pitch_bytes < row_bytes) { rbv_set_error("frame upload: pitch smaller than a row"); return RBV_ERR_ARG; }
+  bool dense = pitch_bytes == row_bytes;
+  for (int b = 0; b < B; ++b) {
+    if (!images[b]) { rbv_set_error("frame upload: null image for lane %d", b); return RBV_ERR_ARG; }
+    if ((const char*)images[b] != (const char*)images[0] + (size_t)b * N * esz) dense = false;
+  }
+  if (dense) {
+    RBV_CUDA(cudaMemcpyAsync(dst, images[0], (size_t)B * N * esz, cudaMemcpyHostToDevice, st));
+    return RBV_OK;
+  }
+  for (int b = 0; b < B; ++b) {
+    char* d = (char*)dst + (size_t)b * N * esz;
+    if (pitch_bytes == row_bytes) RBV_CUDA(cudaMemcpyAsync(d, images[b], N * esz, cudaMemcpyHostToDevice, st));
+    else RBV_CUDA(cudaMemcpy2DAsync(d, row_bytes, images[b], pitch_bytes, row_bytes, c->P.rows, cudaMemcpyHostToDevice, st));
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_prefetch_frames(rbv_ctx* c, const void* const* images, size_t pitch_bytes, int is_u8) {
+  CHECK_CTX(c);
+  if (!images) { rbv_set_error("rbv_prefetch_frames: null images"); return RBV_ERR_ARG; }
+  const int slot = c->raw_next;
+  RBV_CUDA(cudaStreamWaitEvent(c->copy_stream, c->raw_free[slot], 0));   // the front end is done with what was in this slot
+  TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, is_u8 ? 1 : 4, c->copy_stream));
+  RBV_CUDA(cudaEventRecord(c->raw_ready[slot], c->copy_stream));
+  c->raw_key[slot] = images[0];
+  c->raw_u8[slot] = is_u8 ? 1 : 0;
+  c->raw_next = 1 - slot;
+  return RBV_OK;
+}
+
+static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size_t pitch_bytes, int is_u8, const uint64_t* ts_us,
+                       const float* threshold, int* n_keylines, float* auto_threshold) {
+  if (!images || !images[0]) { rbv_set_error("rbv_detect: null images"); return RBV_ERR_ARG; }
+  int slot = -1;
+  for (int i = 0; i < 2; ++i)
+    if (c->raw_key[i] == images[0] && c->raw_u8[i] == (is_u8 ? 1 : 0)) slot = i;
+  const float* d_img;
+  if (slot >= 0) {                       // staged by rbv_prefetch_frames: wait for the copy stream, no second copy
+    RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
+    c->raw_key[slot] = nullptr;
+  } else if (is_u8) {                    // upload now, in stream order
+    slot = c->raw_next;
+    c->raw_next = 1 - slot;
+    c->raw_key[slot] = nullptr;
+    RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));   // a stale prefetch into this slot must have landed first
+    TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 1, c->stream));
+  } else {
+    TRY(upload_frames(c, c->img, images, pitch_bytes, 4, c->stream));
+  }
+  if (is_u8) {
+    const size_t n = (size_t)c->P.lanes * c->P.npix;
+    RBV_LAUNCH(c, k_u8_to_f32, (148 * 8), (256), 0, (const uint4*)c->raw[slot], (float4*)c->img, (const unsigned char*)c->raw[slot], c->img,
+               n / 16, n);
+    RBV_CUDA(cudaGetLastError());
+    d_img = c->img;
+  } else {
+    d_img = slot >= 0 ? (const float*)c->raw[slot] : c->img;
+  }
+  const int rc = rbv_detect_device(c, map, d_img, ts_us, threshold, n_keylines, auto_threshold);
+  if (slot >= 0) RBV_CUDA(cudaEventRecord(c->raw_free[slot], c->stream));
+  return rc;
+}
+
 extern "C" int rbv_detect(rbv_ctx* c, rbv_map* map, const float* const* images, size_t pitch_bytes, const uint64_t* ts_us,
                           const float* threshold, int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
-  if (!images) { rbv_set_error("rbv_detect: null images"); return RBV_ERR_ARG; }
-  const size_t N = c->P.npix, row_bytes = sizeof(float) * c->P.cols;
-  if (pitch_bytes == 0) pitch_bytes = row_bytes;
-  if (pitch_bytes < row_bytes) { rbv_set_error("rbv_detect: pitch smaller than a row"); return RBV_ERR_ARG; }
-  for (int b = 0; b < c->P.lanes; ++b) {
-    if (!images[b]) { rbv_set_error("rbv_detect: null image for lane %d", b); return RBV_ERR_ARG; }
-    RBV_CUDA(cudaMemcpy2DAsync(c->img + (size_t)b * N, row_bytes, images[b], pitch_bytes, row_bytes, c->P.rows, cudaMemcpyHostToDevice, c->stream));
-  }
-  return rbv_detect_device(c, map, c->img, ts_us, threshold, n_keylines, auto_threshold);
+  return detect_host(c, map, (const void* const*)images, pitch_bytes, 0, ts_us, threshold, n_keylines, auto_threshold);
+}
+
+extern "C" int rbv_detect_u8(rbv_ctx* c, rbv_map* map, const uint8_t* const* images, size_t pitch_bytes, const uint64_t* ts_us,
+                             const float* threshold, int* n_keylines, float* auto_threshold) {
+  CHECK_CTX(c);
+  return detect_host(c, map, (const void* const*)images, pitch_bytes, 1, ts_us, threshold, n_keylines, auto_threshold);
 }
 
 // ---- tracker stages ----

@@ -128,7 +128,15 @@ struct rbv_ctx {
   float* h_out;
   int* h_cnt;
   float* h_lm;
-  float* h_img;     // pinned staging for rbv_detect host frames [B][N]
+  // frame upload: double-buffered raw staging on a copy stream (rbv_prefetch_frames) so that the H2D of frame k+1 overlaps
+  // the tracker of frame k; u8 frames are converted (x 3.0, rebvio.cpp:43) on the device
+  cudaStream_t copy_stream;
+  void* raw[2];               // [B][N] bytes (u8) or floats (f32) as uploaded
+  cudaEvent_t raw_ready[2];   // upload of slot i finished (recorded on copy_stream)
+  cudaEvent_t raw_free[2];    // the front end has consumed slot i (recorded on stream)
+  const void* raw_key[2];     // images[0] of the prefetch that filled slot i (nullptr = empty)
+  int raw_u8[2];
+  int raw_next;
   unsigned long long launches;  // kernels launched since creation
   unsigned long long klaunch[48];   // per kernel id
   int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
@@ -150,7 +158,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
   X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
-  X(k_field_band) X(k_boxpass)
+  X(k_field_band) X(k_boxpass) X(k_u8_to_f32)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)

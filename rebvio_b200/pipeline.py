@@ -40,12 +40,15 @@ def visual_fusion(R, Vg, Wx, X):
     R0 = so3_exp_batch(np.asarray(X, np.float64)[:, 3:6])
     V = np.einsum("bij,bj->bi", R0, np.asarray(Vg, np.float64)) + np.asarray(X, np.float64)[:, 0:3]
     Wx64 = np.asarray(Wx, np.float64).reshape(B, 6, 6)
-    P = np.empty((B, 3, 3))
-    for b in range(B):
-        try:
-            P[b] = np.linalg.inv(Wx64[b])[:3, :3]
-        except np.linalg.LinAlgError:
-            P[b] = np.eye(3) * 1e10
+    try:
+        P = np.linalg.inv(Wx64)[:, :3, :3]
+    except np.linalg.LinAlgError:                      # some lane is singular: fall back to lane by lane
+        P = np.empty((B, 3, 3))
+        for b in range(B):
+            try:
+                P[b] = np.linalg.inv(Wx64[b])[:3, :3]
+            except np.linalg.LinAlgError:
+                P[b] = np.eye(3) * 1e10
     Rt = R0 @ np.transpose(np.asarray(R, np.float64).reshape(B, 3, 3), (0, 2, 1))
     Rgva = np.transpose(Rt, (0, 2, 1))
     f = lambda a, n: np.ascontiguousarray(a, np.float32).reshape(B, n)
@@ -73,13 +76,29 @@ class BatchedPipeline:
         self.ctx.close()
 
     def _servo(self):
-        L, det = self.ctx.L, self.ctx.det
-        for b in range(self.lanes):
-            self.threshold[b] = L.rbv_servo_threshold(C.byref(det), float(self.threshold[b]), int(self.count[b]))
+        """edge_detector.cpp:33-36 for every lane, in float32 like rbv_servo_threshold"""
+        det = self.ctx.det
+        if det.gain > 0:
+            t = self.threshold - np.float32(det.gain) * (np.int32(det.keylines_ref) - self.count).astype(np.float32)
+            self.threshold = np.clip(t, np.float32(det.min_threshold), np.float32(det.max_threshold)).astype(np.float32)
 
-    def push(self, frames=None, R_rel=None, device_ptr=None, ts_us=None):
-        """One frame per lane. `frames`: host float32 [B,rows,cols] (0..765; pageable or pinned) — or `device_ptr`: the
-        same layout already in device memory. R_rel [B,3,3]: rotation of the camera since the previous frame.
+    def _host_ptrs(self, frames):
+        base, stride = frames.ctypes.data, frames.strides[0]
+        ptrs = (C.c_void_p * self.lanes)()
+        for b in range(self.lanes):
+            ptrs[b] = base + b * stride
+        return ptrs
+
+    def prefetch(self, frames):
+        """start the H2D of the NEXT push's frames (uint8 or float32 [B,rows,cols]) on the copy stream; it overlaps the
+        tracker of the current frame. Pass the same array to the next push."""
+        capi.check(self.ctx.L.rbv_prefetch_frames(self.ctx.h, self._host_ptrs(frames), 0, int(frames.dtype == np.uint8)))
+
+    def push(self, frames=None, R_rel=None, device_ptr=None, ts_us=None, next_frames=None):
+        """One frame per lane. `frames`: host uint8 [B,rows,cols] as the camera delivers them (converted x3 on the device,
+        rebvio.cpp:43) or host float32 (0..765; pageable or pinned) — or `device_ptr`: float32 frames already in device
+        memory. R_rel [B,3,3]: rotation of the camera since the previous frame. `next_frames`: the frames of the NEXT
+        push; their upload is started right after this frame's front end so that it overlaps the tracker.
         Returns a dict of per-lane outputs (keyline counts always; velocities/matches once two frames are in)."""
         ctx, B = self.ctx, self.lanes
         self._servo()
@@ -89,10 +108,10 @@ class BatchedPipeline:
         if device_ptr is not None:
             capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
         else:
-            base, stride = frames.ctypes.data, frames.strides[0]
-            for b in range(B):
-                self._ptrs[b] = base + b * stride
-            capi.check(ctx.L.rbv_detect(ctx.h, new.h, self._ptrs, 0, capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+            fn = ctx.L.rbv_detect_u8 if frames.dtype == np.uint8 else ctx.L.rbv_detect
+            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+        if next_frames is not None:
+            self.prefetch(next_frames)
         self.count = n
         out = {"keylines": n, "auto_threshold": at}
         if self.have_old:

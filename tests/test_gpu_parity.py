@@ -294,3 +294,43 @@ def test_cpp_adapter_runs_the_chain(tmp_path):
     assert out.returncode == 0, out.stdout
     fields = out.stdout.split()
     assert int(fields[1]) > 1000 and int(fields[fields.index("directed") + 1]) > 500, out.stdout
+
+
+def test_u8_upload_and_prefetch_match_float_path():
+    """rbv_detect_u8 (bytes uploaded, x3 on the device; rebvio.cpp:43) and the prefetched upload (copy stream, consumed by
+    the next detect) give the same keylines and tracker outputs as float frames handed to rbv_detect"""
+    from rebvio_b200.pipeline import BatchedPipeline
+    spec = synth.config("C5:320x240", n_frames=4)
+    seq = synth.generate(spec)
+    B = 3
+    u8 = np.stack([np.stack([np.ascontiguousarray(seq.frames[(k + b) % 4]) for b in range(B)]) for k in range(4)]).astype(np.uint8)
+    f32 = u8.astype(np.float32) * np.float32(3.0)
+    R = np.stack([np.stack([seq.R_rel[min(k, 3)] for b in range(B)]) for k in range(4)])
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+    outs = []
+    for variant in ("f32", "u8", "u8_prefetch", "f32_prefetch", "u8_strided"):
+        pipe = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=capi.REDUCE_ORDERED)
+        src = f32 if variant.startswith("f32") else u8
+        if variant == "u8_strided":   # lanes not back to back in host memory: one copy per lane
+            wide = np.zeros((4, B, 2) + u8.shape[2:], np.uint8)
+            wide[:, :, 0] = u8
+            src = wide[:, :, 0]
+        rec = []
+        for k in range(4):
+            nxt = src[k + 1] if (variant.endswith("prefetch") and k + 1 < 4) else None
+            o = pipe.push(frames=src[k], R_rel=R[k] if k else None, next_frames=nxt)
+            kl = [pipe.newest_map().keylines(b)[0] for b in range(B)]
+            rec.append((o, kl))
+        outs.append(rec)
+        pipe.close()
+    ref = outs[0]
+    for rec in outs[1:]:
+        for (o, kl), (o0, kl0) in zip(rec, ref):
+            assert np.array_equal(o["keylines"], o0["keylines"])
+            for key in ("Vg", "X", "Wx", "matches"):
+                if key in o0:
+                    assert np.array_equal(H.bits(np.asarray(o[key], np.float32)), H.bits(np.asarray(o0[key], np.float32))), key
+            for a, b in zip(kl, kl0):
+                assert a.tobytes() == b.tobytes()
