@@ -249,6 +249,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(dalloc(&c->rowoffset, B * P.rows));
   RBV_CUDA(dalloc(&c->thr_dev, B));
   RBV_CUDA(dalloc(&c->field, B * N));
+  RBV_CUDA(dalloc(&c->tgt, 2 * B * K));
   RBV_CUDA(dalloc(&c->prod, 10 * B * K));
   RBV_CUDA(dalloc(&c->fiabs, B * K));
   RBV_CUDA(dalloc(&c->fwd_head, B * K));
@@ -299,7 +300,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaStreamSynchronize(c->stream);
   void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
-                 c->partials, c->ticket, c->blkagg};
+                 c->partials, c->ticket, c->blkagg, c->tgt};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {
@@ -883,6 +884,7 @@ extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keylin
     RBV_CUDA(copy_sync(c, m->mask + L * N, mask.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
     if (n) RBV_CUDA(push(c, px, m->k.pixel, L, K, n));
   }
+  if (c->field_map == m) TRY(tr_pack_targets(c, m));   // tryVel reads a packed copy of the field map's keylines
   return RBV_OK;
 }
 

@@ -623,16 +623,49 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
   const float* s1 = s0 + N;
   const int c0 = blockIdx.x * DT_W, r0 = blockIdx.y * DT_H;
   const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < (DT_H + 4) * (DT_W + 4); i += 256) {
-    const int tr = i / (DT_W + 4), tc = i % (DT_W + 4);
-    const int r = r0 - 2 + tr, q = c0 - 2 + tc;
-    float a = 0.0f, d = 0.0f;
-    if (r >= 0 && r < rows && q >= 0 && q < cols) {
-      a = s0[(size_t)r * cols + q];
-      d = s1[(size_t)r * cols + q] - a;                                                // calculateDoG, scale_space.cpp:216
+  if ((cols & 3) == 0) {
+    // aligned 16-byte loads covering columns [c0 - 4, c0 + 68): 18 float4 per tile row, all of a thread's loads in flight
+    // before the first use (the tile load is the latency-critical part of this kernel)
+    constexpr int V4 = (DT_W + 8) / 4, NV = (DT_H + 4) * V4;
+    float4 a[2], d[2];
+    int trj[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = tid + k * 256;
+      const int tr = i / V4, j = i % V4;
+      const int r = r0 - 2 + tr, q4 = c0 - 4 + 4 * j;
+      trj[k] = (i < NV) ? (tr << 8 | j) : -1;
+      a[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      d[k] = a[k];
+      if (i < NV && r >= 0 && r < rows && q4 >= 0 && q4 < cols) {
+        a[k] = *reinterpret_cast<const float4*>(s0 + (size_t)r * cols + q4);
+        d[k] = *reinterpret_cast<const float4*>(s1 + (size_t)r * cols + q4);
+      }
     }
-    s0t[tr][tc] = a;
-    dogt[tr][tc] = d;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      if (trj[k] < 0) continue;
+      const int tr = trj[k] >> 8, tc0 = 4 * (trj[k] & 255) - 2;
+      const float av[4] = {a[k].x, a[k].y, a[k].z, a[k].w};
+      const float dv[4] = {d[k].x - a[k].x, d[k].y - a[k].y, d[k].z - a[k].z, d[k].w - a[k].w};   // calculateDoG, scale_space.cpp:216
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int tc = tc0 + e;
+        if (tc >= 0 && tc < DT_W + 4) { s0t[tr][tc] = av[e]; dogt[tr][tc] = dv[e]; }
+      }
+    }
+  } else {
+    for (int i = tid; i < (DT_H + 4) * (DT_W + 4); i += 256) {
+      const int tr = i / (DT_W + 4), tc = i % (DT_W + 4);
+      const int r = r0 - 2 + tr, q = c0 - 2 + tc;
+      float a = 0.0f, d = 0.0f;
+      if (r >= 0 && r < rows && q >= 0 && q < cols) {
+        a = s0[(size_t)r * cols + q];
+        d = s1[(size_t)r * cols + q] - a;                                              // calculateDoG, scale_space.cpp:216
+      }
+      s0t[tr][tc] = a;
+      dogt[tr][tc] = d;
+    }
   }
   if (tid < DT_H * 2) sflags[tid >> 1][tid & 1] = 0u;
   if (tid == 0) ncand = 0;
@@ -740,11 +773,73 @@ __global__ void __launch_bounds__(1024) k_detect_scan(const int* __restrict__ ro
 }
 
 // Pass 3: emit keylines in row-major id order (edge_detector.cpp:109-119, KeyLine ctor types/keyline.hpp:42-59).
-// One warp per image row: lane l owns flag word l (+32 per round); ids = row offset + prefix popcount. The plane-fit
-// results parked by pass 1 are read back (16 B per keyline), nothing is re-fitted.
-__global__ void __launch_bounds__(32) k_detect_emit(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
-                                                    const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
-                                                    const __grid_constant__ DevParams P, int wpr) {
+// One warp per image row, EM_ROWS rows per block. Step 1: lane l owns flag word l (+32 per round) and lists the columns
+// of its set bits in shared memory at (prefix popcount) — the row's keylines in id order. Step 2: lane j takes list entry
+// j (+32 ...): consecutive lanes hold consecutive ids, so the plane-fit read-back (16 B per keyline, parked by pass 1)
+// is issued for 32 keylines at once and every SoA store is coalesced.
+#define EM_ROWS 4
+#define EM_MAXW 1024   // columns per row the shared list can hold (wider images take the direct path below)
+__global__ void __launch_bounds__(32 * EM_ROWS) k_detect_emit(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
+                                                              const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
+                                                              const __grid_constant__ DevParams P, int wpr) {
+  __shared__ unsigned short list[EM_ROWS][EM_MAXW];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.y, r = blockIdx.x * EM_ROWS + warp + 2;
+  const int rows = P.rows, cols = P.cols, kmax = P.kmax;
+  const size_t N = (size_t)P.npix;
+  if (r >= rows - 2) return;
+  const int base = rowoffset[b * rows + r];
+  if (base >= P.keylines_max) return;
+  int total = 0;
+  for (int w0 = 0; w0 < wpr; w0 += 32) {
+    const int w = w0 + lane;
+    unsigned word = (w < wpr) ? flags[((size_t)b * rows + r) * wpr + w] : 0u;
+    const int cnt = __popc(word);
+    int inc = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      int v = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+      if (lane >= off) inc += v;
+    }
+    int pos = total + inc - cnt;
+    total += __shfl_sync(0xFFFFFFFFu, inc, 31);
+    while (word) {
+      const int bit = __ffs(word) - 1;
+      word &= word - 1;
+      list[warp][pos++] = (unsigned short)(w * 32 + bit);
+    }
+  }
+  __syncwarp();
+  total = min(total, P.keylines_max - base);                                            // :113-119 (keylines_max cut)
+  for (int j = lane; j < total; j += 32) {
+    const int q = list[warp][j];
+    const int id = base + j;
+    const unsigned pix = (unsigned)(r * cols + q);
+    const float4 fr = fit[(size_t)b * N + pix];                                         // (theta0, theta1, xs, ys)
+    const float px = (float)q + fr.z, py = (float)r + fr.w;                             // :109
+    const size_t o = (size_t)b * kmax + id;
+    K.pos[o] = make_float2(px, py);
+    const float2 pi = make_float2(px - P.cx, py - P.cy);                                // :110
+    K.pos_img[o] = pi;
+    K.match_pos_img[o] = pi;
+    K.grad[o] = make_float2(fr.x, fr.y);
+    K.match_grad[o] = make_float2(0.0f, 0.0f);
+    K.gnorm[o] = sqrtf(fr.x * fr.x + fr.y * fr.y);
+    K.match_gnorm[o] = 0.0f;
+    K.rho[o] = RBV_RHO_INIT;
+    K.srho[o] = RBV_RHO_MAX;
+    K.id_prev[o] = -1; K.id_next[o] = -1; K.match_id[o] = -1; K.match_fwd[o] = -1; K.match_kf[o] = -1;
+    K.matches[o] = 0u;
+    K.pixel[o] = pix;
+    K.residual[o] = 0.0f;
+    mask[(size_t)b * N + pix] = id;                                                     // :111-112
+  }
+}
+
+// the same for rows wider than the shared list: lane l walks the bits of its own flag words
+__global__ void __launch_bounds__(32) k_detect_emit_wide(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
+                                                         const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
+                                                         const __grid_constant__ DevParams P, int wpr) {
   const int b = blockIdx.y, r = blockIdx.x + 2, lane = threadIdx.x;
   const int rows = P.rows, cols = P.cols, kmax = P.kmax;
   const size_t N = (size_t)P.npix;
@@ -768,11 +863,11 @@ __global__ void __launch_bounds__(32) k_detect_emit(const float4* __restrict__ f
       if (id < P.keylines_max) {
         const int q = w * 32 + bit;
         const unsigned pix = (unsigned)(r * cols + q);
-        const float4 fr = fit[(size_t)b * N + pix];                                     // (theta0, theta1, xs, ys)
-        const float px = (float)q + fr.z, py = (float)r + fr.w;                         // :109
+        const float4 fr = fit[(size_t)b * N + pix];
+        const float px = (float)q + fr.z, py = (float)r + fr.w;
         const size_t o = (size_t)b * kmax + id;
         K.pos[o] = make_float2(px, py);
-        const float2 pi = make_float2(px - P.cx, py - P.cy);                            // :110
+        const float2 pi = make_float2(px - P.cx, py - P.cy);
         K.pos_img[o] = pi;
         K.match_pos_img[o] = pi;
         K.grad[o] = make_float2(fr.x, fr.y);
@@ -785,7 +880,7 @@ __global__ void __launch_bounds__(32) k_detect_emit(const float4* __restrict__ f
         K.matches[o] = 0u;
         K.pixel[o] = pix;
         K.residual[o] = 0.0f;
-        mask[(size_t)b * N + pix] = id;                                                 // :111-112
+        mask[(size_t)b * N + pix] = id;
       }
       ++id;
     }
@@ -850,7 +945,10 @@ int fe_detect(rbv_ctx* c, rbv_map* map) {
   float4* fit = reinterpret_cast<float4*>(c->rowsum);   // rowsum + bufB are one contiguous 4*B*N float scratch, free after the scale space
   RBV_LAUNCH(c, k_detect_flags, (g1), (256), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, fit, P, wpr);
   RBV_LAUNCH(c, k_detect_scan, (B), (1024), 0, c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
-  RBV_LAUNCH(c, k_detect_emit, (dim3(rows - 4, B)), (32), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+  if (cols <= EM_MAXW)
+    RBV_LAUNCH(c, k_detect_emit, (dim3((rows - 4 + EM_ROWS - 1) / EM_ROWS, B)), (32 * EM_ROWS), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+  else
+    RBV_LAUNCH(c, k_detect_emit_wide, (dim3(rows - 4, B)), (32), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
   RBV_LAUNCH(c, k_join, (dim3((P.kmax + 255) / 256, B)), (256), 0, map->k, map->count, map->mask, P);
   RBV_LAUNCH(c, k_tune, (B), (1024), 0, map->k, map->count, map->threshold, P.kmax);
   RBV_CUDA(cudaGetLastError());

@@ -105,6 +105,7 @@ struct rbv_ctx {
   float* thr_dev;   // [B] servoed thresholds of this detect
   // tracker scratch
   unsigned* field;  // [B][N]
+  float4* tgt;      // [B][kmax][2] packed target keylines of the distance-field map (k_pack_targets)
   rbv_map* field_map;
   float* prod;      // [10][B][kmax] tryVel per-keyline addends / [7][B][kmax] extRotVel rows (shared)
   float* fiabs;     // [B][kmax]
@@ -158,7 +159,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
   X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
-  X(k_field_band) X(k_boxpass) X(k_u8_to_f32)
+  X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
@@ -195,6 +196,7 @@ int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float*
 int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out);
 
 int tr_build_field(rbv_ctx* c, rbv_map* map);
+int tr_pack_targets(rbv_ctx* c, rbv_map* map);   // refresh the packed copy after the field map's keylines were replaced
 int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call);     // lm_call: -1 = single evaluation (vel, srmin in lane_in), t >= 0 = LM call t

@@ -52,16 +52,29 @@ __global__ void __launch_bounds__(128) k_field_build(KeylineSoA K, const int* __
 // the finished band is written to HBM once, coalesced (no separate reset pass, no global atomics). The result is the
 // minimum over the same candidate set as k_field_build, hence identical for any keyline order.
 #define FB_TPB 512
+#define FB_G 8        // candidates per work item
+#define FB_MAXI 12    // work items per keyline at most (search range <= 46)
 __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
                                                        unsigned* __restrict__ field, const __grid_constant__ DevParams P, int band_rows) {
   extern __shared__ __align__(16) unsigned fb_cell[];
   __shared__ int s_lo, s_hi;
+  __shared__ float s_ux[FB_TPB], s_uy[FB_TPB], s_px[FB_TPB], s_py[FB_TPB];
+  __shared__ int s_ral[FB_TPB];                         // r-interval of the keyline: start (low 16 bits, signed) | length << 16
+  __shared__ unsigned short s_item[FB_TPB * FB_MAXI];   // work item -> keyline of the round (low 9 bits) | item of that keyline << 9
+  __shared__ int s_wsum[FB_TPB / 32];
   const int b = blockIdx.y, t = threadIdx.x;
   const int rows = P.rows, cols = P.cols;
   const int r0 = blockIdx.x * band_rows, r1 = min(r0 + band_rows, rows);
-  const int ncell = (r1 - r0) * cols;
+  const int nrows = r1 - r0;
+  const int ncell = nrows * cols;
   const int n = count[b];
-  for (int i = t; i < ncell; i += FB_TPB) fb_cell[i] = RBV_FIELD_EMPTY;
+  if ((ncell & 3) == 0) {
+    uint4* c4 = reinterpret_cast<uint4*>(fb_cell);
+    const uint4 e4 = make_uint4(RBV_FIELD_EMPTY, RBV_FIELD_EMPTY, RBV_FIELD_EMPTY, RBV_FIELD_EMPTY);
+    for (int i = t; i < ncell / 4; i += FB_TPB) c4[i] = e4;
+  } else {
+    for (int i = t; i < ncell; i += FB_TPB) fb_cell[i] = RBV_FIELD_EMPTY;
+  }
   if (t == 0) { s_lo = n; s_hi = 0; }
   __syncthreads();
   const int ra0 = P.field_r0, rb0 = P.field_r0 + P.field_nr - 1;
@@ -70,9 +83,13 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
   const size_t base = (size_t)b * P.kmax;
   {  // index range of the keylines that can reach the band (row-major ids make it a narrow range; any order is handled)
     int lo = n, hi = 0;
-    for (int i = t; i < n; i += FB_TPB) {
-      const float y = K.pos[base + i].y;
-      if (y >= ylo && y <= yhi) { lo = min(lo, i); hi = max(hi, i + 1); }
+    for (int i0 = t; i0 < n; i0 += 4 * FB_TPB) {
+      float y[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) y[u] = (i0 + u * FB_TPB < n) ? K.pos[base + i0 + u * FB_TPB].y : -1e30f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (y[u] >= ylo && y[u] <= yhi) { lo = min(lo, i0 + u * FB_TPB); hi = max(hi, i0 + u * FB_TPB + 1); }
     }
 #pragma unroll
     for (int off = 16; off; off >>= 1) {
@@ -84,35 +101,101 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
   __syncthreads();
   const int lo = s_lo, hi = s_hi;
   const float thr = threshold[b];
-  const float r0f = (float)r0, r1f = (float)r1, colsf = (float)cols;
-  for (int idx = lo + t; idx < hi; idx += FB_TPB) {
-    const size_t o = base + idx;
-    const float2 p = K.pos[o];
-    if (!(p.y >= ylo && p.y <= yhi)) continue;
-    const float gn = K.gnorm[o];
-    if (thr > 0.0f && gn < thr) continue;                                                // core.hpp:47
-    const float2 g = K.grad[o];
-    const float ux = g.x / gn, uy = g.y / gn;
-    int ra = ra0, rb = rb0;
-    if (fabsf(uy) > 1e-2f) {   // rows hit are monotone in r: clip to the r-interval that can land in [r0, r1) (+-1 margin, re-tested below)
-      const float t0 = (r0f - 0.5f - p.y) / uy, t1 = (r1f - 0.5f - p.y) / uy;
-      ra = max(ra, __float2int_rd(fminf(t0, t1)) - 1);
-      rb = min(rb, __float2int_ru(fmaxf(t0, t1)) + 1);
+  const float r0f = (float)r0, r1f = (float)r1;
+  // Rounds of FB_TPB keylines. Phase 1 (thread = keyline): unit normal and the r-interval that can land in the band.
+  // Phase 2 (thread = work item of FB_G consecutive r of one keyline): the intervals differ a lot in length (1 .. 80,
+  // by slope and by distance to the band), so they are cut into equal items and dealt out densely instead of leaving
+  // a warp waiting for its longest line.
+  const int lane = t & 31, warp = t >> 5;
+  for (int k0 = lo; k0 < hi; k0 += FB_TPB) {
+    const int idx = k0 + t;
+    int ra = 0, len = 0;
+    float ux = 0.0f, uy = 0.0f;
+    float2 p = make_float2(0.0f, 0.0f);
+    if (idx < hi) {
+      const size_t o = base + idx;
+      p = K.pos[o];
+      const float gn = K.gnorm[o];                                                       // (the three loads go out together)
+      const float2 g = K.grad[o];
+      if (p.y >= ylo && p.y <= yhi && !(thr > 0.0f && gn < thr)) {                     // core.hpp:47
+        ux = g.x / gn; uy = g.y / gn;
+        int rb = rb0;
+        ra = ra0;
+        if (fabsf(uy) > 1e-2f) {   // rows hit are monotone in r: clip to the r-interval that can land in [r0, r1) (+-1 margin, re-tested below)
+          const float t0 = (r0f - 0.5f - p.y) / uy, t1 = (r1f - 0.5f - p.y) / uy;
+          ra = max(ra, __float2int_rd(fminf(t0, t1)) - 1);
+          rb = min(rb, __float2int_ru(fmaxf(t0, t1)) + 1);
+        }
+        len = max(rb - ra + 1, 0);
+        if (!(fabsf(ux) <= 2.0f && fabsf(uy) <= 2.0f)) len = 0;   // non-finite normal: the reference's getIndex yields -1 for every r
+      }
     }
-    const unsigned lowkey = 0xFFFFFFu - (unsigned)idx;
-    for (int r = ra; r <= rb; ++r) {
-      const float fr = (float)r;
-      const float ry = roundf(uy * fr + p.y);                                            // core.hpp:50-51, getIndex :66-71
-      if (!(ry >= r0f && ry < r1f)) continue;
-      const float rx = roundf(ux * fr + p.x);
-      if (!(rx >= 0.0f && rx < colsf)) continue;
-      unsigned* cp = fb_cell + ((int)ry - r0) * cols + (int)rx;
-      const unsigned key = ((unsigned)abs(r) << 24) | lowkey;                            // :54-56 as min over (|r|, -idx)
-      if (*(volatile unsigned*)cp <= key) continue;
-      atomicMin(cp, key);
+    s_ux[t] = ux; s_uy[t] = uy; s_px[t] = p.x; s_py[t] = p.y; s_ral[t] = (ra & 0xFFFF) | (len << 16);
+    // exclusive scan of the item counts, then every keyline lists its items in the item table
+    const int items = min((len + FB_G - 1) / FB_G, FB_MAXI);
+    int inc = items;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int v = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+      if (lane >= off) inc += v;
     }
+    if (lane == 31) s_wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      int w = (lane < FB_TPB / 32) ? s_wsum[lane] : 0;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, w, off);
+        if (lane >= off) w += v;
+      }
+      if (lane < FB_TPB / 32) s_wsum[lane] = w;   // inclusive warp totals
+    }
+    __syncthreads();
+    const int first = inc - items + (warp ? s_wsum[warp - 1] : 0);
+    const int total = s_wsum[FB_TPB / 32 - 1];
+    for (int i = 0; i < items; ++i) s_item[first + i] = (unsigned short)(t | (i << 9));
+    __syncthreads();
+    for (int j = t; j < total; j += FB_TPB) {
+      const int it = s_item[j];
+      const int ks = it & 511;
+      const int ral = s_ral[ks];
+      const int kra = (int)(short)(ral & 0xFFFF);
+      const int rs = kra + (it >> 9) * FB_G;
+      const int re = kra + (ral >> 16);
+      const float kux = s_ux[ks], kuy = s_uy[ks], kpx = s_px[ks], kpy = s_py[ks];
+      const unsigned lowkey = 0xFFFFFFu - (unsigned)(k0 + ks);
+      // The FB_G candidates of the item as straight-line predicated code: FB_G independent address chains, then FB_G
+      // loads, then the (few) atomics. A loop with early `continue`s made every warp crawl through one dependent chain
+      // with a branch bubble every few instructions (measured ~12 cycles per issued instruction).
+      // getIndex (core.hpp:66-71): (int)std::round(v), half away from zero = sign(v) * trunc(|v| + 0.5). All on the FP32
+      // add pipe: the RZ add of 0.5 is what roundf() itself does, the RZ add of 2^23 leaves trunc() in the mantissa
+      // (values >= 2^23, Inf and NaN come out as huge indices and fail the range test). No FRND / F2I conversions.
+      const float fr0 = (float)rs;
+      int off[FB_G];
+      unsigned key[FB_G];
+#pragma unroll
+      for (int u = 0; u < FB_G; ++u) {
+        const int r = rs + u;
+        const float fr = fr0 + (float)u;
+        const float fy = kuy * fr + kpy;                                                  // :50
+        const float fx = kux * fr + kpx;                                                  // :51
+        const int iy = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fy), 0.5f), 8388608.0f)) - 0x4B000000;
+        const int ix = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fx), 0.5f), 8388608.0f)) - 0x4B000000;
+        const int row = (fy < 0.0f && iy != 0) ? -1 : iy;
+        const int col = (fx < 0.0f && ix != 0) ? -1 : ix;
+        const bool ok = r < re && (unsigned)(row - r0) < (unsigned)nrows && (unsigned)col < (unsigned)cols;
+        off[u] = ok ? (row - r0) * cols + col : -1;
+        key[u] = ((unsigned)abs(r) << 24) | lowkey;                                      // :54-56 as min over (|r|, -idx)
+      }
+      unsigned cur[FB_G];
+#pragma unroll
+      for (int u = 0; u < FB_G; ++u) cur[u] = off[u] >= 0 ? *(volatile unsigned*)(fb_cell + off[u]) : 0u;
+#pragma unroll
+      for (int u = 0; u < FB_G; ++u)
+        if (off[u] >= 0 && cur[u] > key[u]) atomicMin(fb_cell + off[u], key[u]);
+    }
+    __syncthreads();
   }
-  __syncthreads();
   unsigned* dst = field + (size_t)b * P.npix + (size_t)r0 * cols;
   if ((cols & 3) == 0) {
     const uint4* s4 = reinterpret_cast<const uint4*>(fb_cell);
@@ -125,8 +208,33 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
 
 // rows per band: as many as fit ~100 KB (two blocks per SM); below 16 rows the keyline scan would be repeated too often
 static int field_band_rows(const rbv_ctx* c) {
-  const int by_smem = (100 * 1024) / (c->P.cols * 4);
-  return by_smem > 32 ? 32 : by_smem;
+  const int by_smem = (90 * 1024) / (c->P.cols * 4);   // + ~23 KB of static tables: two blocks fit the 227 KB of an SM
+  int h = by_smem > 32 ? 32 : by_smem;
+  if (h >= 16) {   // prefer a row count that divides the image: no short last band
+    for (int d = h; d >= h - 4 && d >= 16; --d)
+      if (c->P.rows % d == 0) return d;
+  }
+  return h;
+}
+
+// What tryVel reads of a matched target keyline (core.cpp:39-44,62-75), packed into one 32-byte sector per keyline so
+// that the gather behind the distance-field lookup is one memory transaction; the unit gradient is divided once here
+// instead of once per keyline per LM iteration (same float division, same result).
+__global__ void k_pack_targets(KeylineSoA K, const int* __restrict__ count, float4* __restrict__ tgt, int kmax) {
+  const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count[b]) return;
+  const size_t o = (size_t)b * kmax + idx;
+  const float2 g = K.grad[o], p = K.pos[o];
+  const float gn = K.gnorm[o];
+  tgt[2 * o] = make_float4(g.x, g.y, p.x, p.y);
+  tgt[2 * o + 1] = make_float4(g.x / gn, g.y / gn, 0.0f, 0.0f);                          // core.cpp:64-65
+}
+
+int tr_pack_targets(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  RBV_LAUNCH(c, k_pack_targets, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->tgt, P.kmax);
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
 }
 
 int tr_init(rbv_ctx* c) {
@@ -138,7 +246,7 @@ int tr_init(rbv_ctx* c) {
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   const int H = field_band_rows(c);
-  const bool band = c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 16);
+  const bool band = (c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 16)) && P.field_nr <= FB_G * FB_MAXI;
   if (band && H >= 1) {
     const size_t smem = (size_t)H * P.cols * 4;
     RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, map->k, map->count, map->threshold, c->field, P, H);
@@ -146,6 +254,7 @@ int tr_build_field(rbv_ctx* c, rbv_map* map) {
     { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
     RBV_LAUNCH(c, k_field_build, (dim3((P.keylines_max + 127) / 128, P.lanes)), (128), 0, map->k, map->count, map->threshold, c->field, P);
   }
+  { int rc = tr_pack_targets(c, map); if (rc != RBV_OK) return rc; }
   c->field_map = map;
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
@@ -239,7 +348,7 @@ int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
 struct TryVelIn {
   float v0, v1, v2, sigma_rho_min, thr;
 };
-__device__ __forceinline__ void tryvel_point(const KeylineSoA& Ko, const KeylineSoA& Kn, const unsigned* __restrict__ field_b,
+__device__ __forceinline__ void tryvel_point(const KeylineSoA& Ko, const float4* __restrict__ tgt, const unsigned* __restrict__ field_b,
                                              size_t o, size_t base, float res, const TryVelIn& in, const DevParams& P,
                                              float* add, float& code, int& fwd) {
 #pragma unroll
@@ -278,17 +387,17 @@ __device__ __forceinline__ void tryvel_point(const KeylineSoA& Ko, const Keyline
   const unsigned cell = field_b[(size_t)y * P.cols + x];
   if (cell != RBV_FIELD_EMPTY) {
     const int tid = (int)(0xFFFFFFu - (cell & 0xFFFFFFu));
-    const size_t to = base + tid;
-    const float2 tg = Kn.grad[to];
+    const float4 t0 = tgt[2 * (base + tid)];                                           // (grad.x, grad.y, pos.x, pos.y) of the target
+    const float2 tg = make_float2(t0.x, t0.y);
     const float2 g = Ko.grad[o];
     const float n2 = gn * gn;                                                          // testfk :40-42
     const float dp = tg.x * g.x + tg.y * g.y;
     if (!(fabsf(dp - n2) > P.match_treshold * n2)) {
       matched = true;
-      const float2 tp = Kn.pos[to];
-      const float tgn = Kn.gnorm[to];
+      const float4 t1 = tgt[2 * (base + tid) + 1];                                     // (grad / gradient_norm, -, -): same 32-byte sector
+      const float2 tp = make_float2(t0.z, t0.w);
       const float dx = pxc - tp.x, dy = pyc - tp.y;                                    // :62-63
-      const float gnx = tg.x / tgn, gny = tg.y / tgn;
+      const float gnx = t1.x, gny = t1.y;                                              // tg / tgn, divided once when the field is built
       const float fi = dx * gnx + dy * gny;                                            // :67
       dfx = gnx / srho; dfy = gny / srho;
       fwd = tid;                                                                       // :73
@@ -309,7 +418,7 @@ __device__ __forceinline__ void tryvel_point(const KeylineSoA& Ko, const Keyline
 
 // ORDERED mode, phase 1: addends to prod[10][B][kmax], residual code to fiabs
 __global__ void __launch_bounds__(256) k_tryvel_eval(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
-                                                     KeylineSoA Kn, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
+                                                     const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
                                                      int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
                                                      float* __restrict__ prod, float* __restrict__ fiabs,
                                                      const __grid_constant__ DevParams P) {
@@ -323,7 +432,7 @@ __global__ void __launch_bounds__(256) k_tryvel_eval(KeylineSoA Ko, const int* _
   in.thr = thr_o[b];
   float add[10], code;
   int fwd;
-  tryvel_point(Ko, Kn, field + (size_t)b * P.npix, o, base, Ko.residual[o], in, P, add, code, fwd);
+  tryvel_point(Ko, tgt, field + (size_t)b * P.npix, o, base, Ko.residual[o], in, P, add, code, fwd);
   Ko.match_fwd[o] = fwd;                                                                 // :87
   fiabs[o] = code;
 #pragma unroll
@@ -510,7 +619,7 @@ __device__ __forceinline__ float residual_lookback(const float* __restrict__ agg
 }
 
 __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
-                                                        KeylineSoA Kn, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
+                                                        const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
                                                         int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
                                                         double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                         const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
@@ -537,7 +646,7 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast(KeylineSoA Ko, const int
     res = Ko.residual[o];
     if (res < 0.0f) { was_pending = true; res = residual_lookback(agg_prev + (size_t)b * nblk, blockIdx.x); }
     int fwd;
-    tryvel_point(Ko, Kn, field + (size_t)b * P.npix, o, base, res, in, P, add, code, fwd);
+    tryvel_point(Ko, tgt, field + (size_t)b * P.npix, o, base, res, in, P, add, code, fwd);
     Ko.match_fwd[o] = fwd;                                                               // core.cpp:87
   }
   // carried |fi| inside the block, keyline order
@@ -628,14 +737,14 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     sr_stride = lm_floats;
   }
   if (c->reduce_mode == RBV_REDUCE_ORDERED) {
-    RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
+    RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
     RBV_LAUNCH(c, k_tryvel_reduce, (P.lanes), (1024), 0, map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, 1, P);
   } else {
     const int nblk = c->nblk;
     const size_t half = (size_t)P.lanes * nblk;
     float* agg_cur = c->blkagg + (size_t)c->tv_parity * half;
     const float* agg_prev = c->blkagg + (size_t)(1 - c->tv_parity) * half;
-    RBV_LAUNCH(c, k_tryvel_fast, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, map->threshold, c->field_map->k, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P);
+    RBV_LAUNCH(c, k_tryvel_fast, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P);
     if (lm_call < 0 || lm_call == P.iterations)
       RBV_LAUNCH(c, k_residual_resolve, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_cur, nblk, P.kmax);
     c->tv_parity = 1 - c->tv_parity;
@@ -898,6 +1007,7 @@ __global__ void __launch_bounds__(512) k_extrot_reduce(const int* __restrict__ c
   if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
+#define ER_KPT 4
 // RBV_REDUCE_FAST: rows + 27 sums + 6x6 solve in ONE kernel (same ticket scheme as k_tryvel_fast)
 __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr,
                                                         int vel_stride, double* __restrict__ partials, unsigned* __restrict__ ticket,
@@ -907,28 +1017,36 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
   __shared__ float s_sys[42];
   __shared__ int s_last;
   const int b = blockIdx.y, n = count[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int nact = max(1, (n + TV_TPB - 1) / TV_TPB);
+  const int nact = max(1, (n + TV_TPB * ER_KPT - 1) / (TV_TPB * ER_KPT));
   if ((int)blockIdx.x >= nact) return;
-  const int idx = blockIdx.x * TV_TPB + t;
-  float r[7];
+  // ER_KPT keylines per thread: the 27 products are accumulated in FP64 registers first, so the shuffle tree (the
+  // expensive part: 27 x 5 64-bit shuffles per warp) runs once per ER_KPT x 32 keylines
+  double acc[27];
 #pragma unroll
-  for (int a = 0; a < 7; ++a) r[a] = 0.0f;
-  if (idx < n)
-    extrot_row(K, (size_t)b * P.kmax + idx, vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1],
-               vel_ptr[(size_t)b * vel_stride + 2], P, r);
-  {
+  for (int a = 0; a < 27; ++a) acc[a] = 0.0;
+  const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+#pragma unroll 1
+  for (int j = 0; j < ER_KPT; ++j) {
+    const int idx = (blockIdx.x * ER_KPT + j) * TV_TPB + t;
+    if (idx >= n) break;
+    float r[7];
+    extrot_row(K, (size_t)b * P.kmax + idx, v0, v1, v2, P, r);
     int k = 0;
 #pragma unroll
     for (int a = 0; a < 6; ++a) {
 #pragma unroll
       for (int q = a; q < 7; ++q) {
         const int slot = (q == 6) ? 21 + a : k++;
-        double v = (double)(r[a] * r[q]);        // float product as in the reference (operators.hh:200-208), FP64 accumulate
-#pragma unroll
-        for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
-        if (lane == 0) sm[warp * 27 + slot] = v;
+        acc[slot] += (double)(r[a] * r[q]);        // float product as in the reference (operators.hh:200-208), FP64 accumulate
       }
     }
+  }
+#pragma unroll
+  for (int a = 0; a < 27; ++a) {
+    double v = acc[a];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+    if (lane == 0) sm[warp * 27 + a] = v;
   }
   __syncthreads();
   if (t < 27) {
@@ -961,7 +1079,7 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
     RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
   } else {
-    RBV_LAUNCH(c, k_extrot_fast, (dim3(c->nblk, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
+    RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;

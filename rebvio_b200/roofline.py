@@ -21,11 +21,13 @@ def kernel_bytes(name, N, K, B, planes=1, P=20.0, words=0):
         "k_detect_flags": 12.0 * N,          # read both scales, write the id mask (DoG / magnitude never reach memory)
         "k_detect_scan": 0.0,
         "k_detect_emit": 84.0 * K,           # one KeyLine per keyline
+        "k_detect_emit_wide": 84.0 * K,
         "k_join": 20.0 * K,
         "k_tune": 4.0 * K,
         "k_field_build": 340.0 * K,          # 20 B keyline read + 80 candidates x 4 B
         "k_field_band": 4.0 * N + 340.0 * K,  # same + the field reset/write it absorbs (4 N)
         "k_boxpass": 8.0 * N * planes,       # one whole box pass: read N + write N per plane
+        "k_pack_targets": 52.0 * K,          # 20 B read + 32 B packed write
         "k_rotate": 48.0 * K,
         "k_quantile": 4.0 * K,
         "k_tryvel_eval": 68.0 * K,           # 36 B keyline + 4 B field + 20 B target + 8 B write
