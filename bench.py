@@ -300,7 +300,7 @@ def run_b200(args):
     probes = pipe.ctx.probe_count(0) / max(1.0, float(out["keylines"][0]))
     top_ms, top_n, top_launches = prof[top]
     # planes per launch of the box-pass kernels: pass 0 = 1 (rowscan) / 1+1 (colbox x2 launches), passes 1,2 = 2
-    planes = {"k_rowscan": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0}.get(top, 1.0)
+    planes = {"k_rowscan": 5.0 / 3.0, "k_rowscan4": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0}.get(top, 1.0)
     words = B * N if top == "k_fill" else 0
     abytes = roofline.kernel_bytes(top, N, K_mean, B, planes=planes, P=probes, words=words)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")

@@ -59,6 +59,59 @@ __global__ void __launch_bounds__(32) k_rowscan(const float* __restrict__ in, fl
   }
 }
 
+// Row pass, 16-byte version (cols % 4 == 0, 16-byte aligned planes): the same walk with a quarter of the memory
+// instructions. A warp-wide LDG.128 fetches 4 rows x 32 columns; the tile pitch of 36 floats keeps both the row-major
+// float4 stores of the load phase and the lane-per-row float4 reads of the scan phase free of bank conflicts.
+__global__ void __launch_bounds__(32) k_rowscan4(const float* __restrict__ in, float* __restrict__ out, int rows, int cols,
+                                                 size_t in_plane_stride, size_t out_plane_stride) {
+  __shared__ __align__(16) float tile[32][36];
+  const int lane = threadIdx.x;
+  const int r0 = blockIdx.x * 32;
+  const float* src = in + (size_t)blockIdx.y * in_plane_stride;
+  float* dst = out + (size_t)blockIdx.y * out_plane_stride;
+  const int nr = min(32, rows - r0);
+  const int lr = lane >> 3, lc = (lane & 7) * 4;     // this lane's row (+ 4k) and column offset inside a tile
+  float4 nxt[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    nxt[k] = (lr + 4 * k < nr && lc < cols) ? *reinterpret_cast<const float4*>(src + (size_t)(r0 + lr + 4 * k) * cols + lc)
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+  float carry = 0.0f;
+  for (int c0 = 0; c0 < cols; c0 += 32) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) *reinterpret_cast<float4*>(&tile[lr + 4 * k][lc]) = nxt[k];
+    __syncwarp();
+    const int cn = c0 + 32;
+    if (cn < cols) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        nxt[k] = (lr + 4 * k < nr && cn + lc < cols) ? *reinterpret_cast<const float4*>(src + (size_t)(r0 + lr + 4 * k) * cols + cn + lc)
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const float4*>(&tile[lane][4 * j]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[j].x = (c0 + j == 0) ? v[j].x : carry + v[j].x;                                // scale_space.cpp:50-57
+      v[j].y = v[j].x + v[j].y;
+      v[j].z = v[j].y + v[j].z;
+      v[j].w = v[j].z + v[j].w;
+      carry = v[j].w;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<float4*>(&tile[lane][4 * j]) = v[j];
+    __syncwarp();
+    if (c0 + lc < cols) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (lr + 4 * k < nr)
+          *reinterpret_cast<float4*>(dst + (size_t)(r0 + lr + 4 * k) * cols + c0 + lc) = *reinterpret_cast<const float4*>(&tile[lr + 4 * k][lc]);
+    }
+    __syncwarp();
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // Column pass fused with the box average (scale_space.cpp:59-65 + 69-128).
 // Thread t of a block walks integral-image column (c0 - h - 1 + t) top to bottom: ii[r][c] = ii[r-1][c] + rowsum[r][c].
@@ -68,8 +121,8 @@ __global__ void __launch_bounds__(32) k_rowscan(const float* __restrict__ in, fl
 //   value = ((A-B)-Cc)+D, bottom rows ((A-Cc)-B)+D (scale_space.cpp:99 vs :119,:124), missing taps dropped,
 //   times float(1.0/double(window area)) (precomputeDivisors, :130-171; the interior constant `a` (:72) is the same number).
 #define CB_TPB 128
-#define CB_CH 16
-#define CB_RING 64   // >= 2*CB_CH + 2*hmax + 2: a chunk's writes never land on rows the previous chunk still reads -> ONE barrier per chunk
+#define CB_CH 8
+#define CB_RING 32   // >= 2*CB_CH + 2*hmax + 2: a chunk's writes never land on rows the previous chunk still reads -> ONE barrier per chunk
 
 // one output value (scale_space.cpp:69-128): ro = output row, h = half width, jhi / jlo = ring columns of the right / left tap
 __device__ __forceinline__ float box_value(const float (*ring)[CB_TPB], const float (*inv_area)[16], int ro, int h, int rows, int jhi,
@@ -91,72 +144,6 @@ __device__ __forceinline__ float box_value(const float (*ring)[CB_TPB], const fl
     v = left ? ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo] : hi[jhi] - lo[jhi];           // bottom rows :119,:124 / :114
   }
   return v * inv_area[rhi - max(rlo, -1)][ncol];
-}
-
-// dual = 1 (first pass): both scales are box-filtered from ONE column scan of the shared row-prefix image (plane =
-// blockIdx.y = lane; outputs out0 / out1 with widths d0 / d1). dual = 0: plane = blockIdx.y, width d0 or d1 by plane % nz.
-__global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ rowsum, float* __restrict__ out0, float* __restrict__ out1,
-                                                   int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
-                                                   int d1, int dual) {
-  __shared__ float ring[CB_RING][CB_TPB];
-  __shared__ float inv_area[16][16];
-  const int t = threadIdx.x;
-  const int z = dual ? 0 : blockIdx.y % nz;
-  const int ha = (z ? d1 : d0) / 2;                 // half width of output A
-  const int hb = dual ? d1 / 2 : ha;                // half width of output B (dual only)
-  const int hm = max(ha, hb);
-  const int W = CB_TPB - (2 * hm + 1);
-  const int c0 = blockIdx.x * W;
-  const int col = c0 - hm - 1 + t;                  // integral-image column scanned by this thread
-  const bool scan_ok = col >= 0 && col < cols;
-  const int oc = c0 + t;                            // output column of this thread (t < W)
-  const bool out_ok = t < W && oc < cols;
-  const float* src = rowsum + (size_t)blockIdx.y * in_plane_stride;
-  float* dstA = out0 + (size_t)blockIdx.y * out_plane_stride;
-  float* dstB = out1 + (size_t)blockIdx.y * out_plane_stride;
-  for (int i = t; i < 256; i += CB_TPB) {
-    int a = i / 16, b = i % 16;
-    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171 (== `a` of :72 inside)
-  }
-  // taps of output A / B in ring coordinates (ring column j <-> image column c0 - hm - 1 + j)
-  const int chiA = min(oc + ha, cols - 1), cloA = oc - ha - 1;
-  const int jhiA = chiA - (c0 - hm - 1), jloA = t + (hm - ha), ncolA = chiA - max(cloA, -1);
-  const int chiB = min(oc + hb, cols - 1), cloB = oc - hb - 1;
-  const int jhiB = chiB - (c0 - hm - 1), jloB = t + (hm - hb), ncolB = chiB - max(cloB, -1);
-  const bool leftA = cloA >= 0, leftB = cloB >= 0;
-  const float invA = out_ok ? (float)(1.0 / (double)((float)(2 * ha + 1) * (float)ncolA)) : 0.0f;
-  const float invB = out_ok ? (float)(1.0 / (double)((float)(2 * hb + 1) * (float)ncolB)) : 0.0f;
-  float run = 0.0f;
-  float nxt[CB_CH];
-#pragma unroll
-  for (int i = 0; i < CB_CH; ++i) nxt[i] = (scan_ok && i < rows) ? src[(size_t)i * cols + col] : 0.0f;
-  int onext = 0;
-  for (int k0 = 0; k0 < rows; k0 += CB_CH) {
-    const int k1 = min(k0 + CB_CH, rows);
-    float cur[CB_CH];
-#pragma unroll
-    for (int i = 0; i < CB_CH; ++i) cur[i] = nxt[i];
-    if (k1 < rows) {
-#pragma unroll
-      for (int i = 0; i < CB_CH; ++i) nxt[i] = (scan_ok && k1 + i < rows) ? src[(size_t)(k1 + i) * cols + col] : 0.0f;
-    }
-#pragma unroll
-    for (int i = 0; i < CB_CH; ++i) {
-      if (k0 + i < rows) {
-        run = (k0 + i == 0) ? cur[i] : run + cur[i];                                   // column pass :59-65
-        ring[(k0 + i) & (CB_RING - 1)][t] = run;
-      }
-    }
-    __syncthreads();
-    const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;   // last output row whose taps are all in the ring
-    if (out_ok) {
-      for (int ro = onext; ro <= olast; ++ro) {
-        dstA[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, ha, rows, jhiA, jloA, leftA, ncolA, invA);
-        if (dual) dstB[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, hb, rows, jhiB, jloB, leftB, ncolB, invB);
-      }
-    }
-    onext = max(onext, olast + 1);
-  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -292,6 +279,130 @@ __device__ __forceinline__ void bp_scan4(float4& v, float& carry, bool first) {
   v.z = v.y + v.z;
   v.w = v.z + v.w;
   carry = v.w;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Column pass + box of the split path (few planes: single stream, or images too wide for k_boxpass).
+// dual = 1 (first pass): both scales are box-filtered from ONE column scan of the shared row-prefix image (plane =
+// blockIdx.y = lane; outputs out0 / out1 with widths d0 / d1). dual = 0: plane = blockIdx.y, width d0 or d1 by plane % nz.
+// With one warp per scheduler this kernel lives or dies by instruction latency, so the steady state is straight-line
+// code: CB_CH rows are scanned, one barrier, then CB_CH output rows whose 4 x CB_CH taps are all issued before the first
+// subtraction; the row-prefix loads run two chunks ahead.
+template <bool MIXED>
+__device__ __forceinline__ void cb_box_rows(unsigned p_hi, unsigned p_lo, bool left, float inv, int ro0, int h, float* __restrict__ dst, int cols) {
+  constexpr unsigned PITCH = CB_TPB * 4u, WRAP = CB_RING * PITCH - 1u;
+  unsigned hi_off = (unsigned)((ro0 + h) & (CB_RING - 1)) * PITCH;
+  unsigned lo_off = (unsigned)((ro0 - h - 1) & (CB_RING - 1)) * PITCH;
+  float a[CB_CH], bq[CB_CH], cq[CB_CH], dq[CB_CH];
+#pragma unroll
+  for (int i = 0; i < CB_CH; ++i) {
+    a[i] = lds_f32(p_hi + hi_off); bq[i] = lds_f32(p_lo + hi_off);
+    cq[i] = lds_f32(p_hi + lo_off); dq[i] = lds_f32(p_lo + lo_off);
+    hi_off = (hi_off + PITCH) & WRAP;
+    lo_off = (lo_off + PITCH) & WRAP;
+  }
+#pragma unroll
+  for (int i = 0; i < CB_CH; ++i) {
+    float v = ((a[i] - bq[i]) - cq[i]) + dq[i];                                          // :99
+    if (MIXED && !left) v = a[i] - cq[i];                                              // :94
+    dst[(size_t)i * cols] = v * inv;
+  }
+}
+
+__global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ rowsum, float* __restrict__ out0, float* __restrict__ out1,
+                                                   int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
+                                                   int d1, int dual) {
+  __shared__ float ring[CB_RING][CB_TPB];
+  __shared__ float inv_area[16][16];
+  const int t = threadIdx.x;
+  const int z = dual ? 0 : blockIdx.y % nz;
+  const int ha = (z ? d1 : d0) / 2;                 // half width of output A
+  const int hb = dual ? d1 / 2 : ha;                // half width of output B (dual only)
+  const int hm = max(ha, hb);
+  const int W = CB_TPB - (2 * hm + 1);
+  const int c0 = blockIdx.x * W;
+  const int col = c0 - hm - 1 + t;                  // integral-image column scanned by this thread
+  const bool scan_ok = col >= 0 && col < cols;
+  const int oc = c0 + t;                            // output column of this thread (t < W)
+  const bool out_ok = t < W && oc < cols;
+  const float* src = rowsum + (size_t)blockIdx.y * in_plane_stride + (scan_ok ? col : 0);
+  float* dstA = out0 + (size_t)blockIdx.y * out_plane_stride;
+  float* dstB = out1 + (size_t)blockIdx.y * out_plane_stride;
+  for (int i = t; i < 256; i += CB_TPB) {
+    int a = i / 16, b = i % 16;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171 (== `a` of :72 inside)
+  }
+  // taps of output A / B in ring coordinates (ring column j <-> image column c0 - hm - 1 + j)
+  const int chiA = min(oc + ha, cols - 1), cloA = oc - ha - 1;
+  const int jhiA = out_ok ? chiA - (c0 - hm - 1) : 0, jloA = t + (hm - ha), ncolA = chiA - max(cloA, -1);
+  const int chiB = min(oc + hb, cols - 1), cloB = oc - hb - 1;
+  const int jhiB = out_ok ? chiB - (c0 - hm - 1) : 0, jloB = t + (hm - hb), ncolB = chiB - max(cloB, -1);
+  const bool leftA = cloA >= 0, leftB = cloB >= 0;
+  const float invA = out_ok ? (float)(1.0 / (double)((float)(2 * ha + 1) * (float)ncolA)) : 0.0f;
+  const float invB = out_ok ? (float)(1.0 / (double)((float)(2 * hb + 1) * (float)ncolB)) : 0.0f;
+  const unsigned ring_a = smem_u32(&ring[0][0]);
+  const unsigned pA_hi = ring_a + 4u * (unsigned)jhiA, pA_lo = ring_a + 4u * (unsigned)(leftA ? jloA : 0);
+  const unsigned pB_hi = ring_a + 4u * (unsigned)jhiB, pB_lo = ring_a + 4u * (unsigned)(leftB ? jloB : 0);
+  const bool mixed = blockIdx.x == 0;               // only the first strip has columns without a left tap
+  float run = 0.0f;
+  float n0[CB_CH], n1[CB_CH];
+#pragma unroll
+  for (int i = 0; i < CB_CH; ++i) {
+    n0[i] = (scan_ok && i < rows) ? src[(size_t)i * cols] : 0.0f;
+    n1[i] = (scan_ok && CB_CH + i < rows) ? src[(size_t)(CB_CH + i) * cols] : 0.0f;
+  }
+  int onext = 0;
+  for (int k0 = 0; k0 < rows; k0 += CB_CH) {
+    const int k1 = min(k0 + CB_CH, rows);
+    float cur[CB_CH];
+#pragma unroll
+    for (int i = 0; i < CB_CH; ++i) { cur[i] = n0[i]; n0[i] = n1[i]; }
+    const int kn = k0 + 2 * CB_CH;
+    if (kn + CB_CH <= rows) {
+      if (scan_ok) {
+#pragma unroll
+        for (int i = 0; i < CB_CH; ++i) n1[i] = src[(size_t)(kn + i) * cols];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < CB_CH; ++i) n1[i] = (scan_ok && kn + i < rows) ? src[(size_t)(kn + i) * cols] : 0.0f;
+    }
+    const bool fast = k0 >= 2 * CB_CH && k0 + CB_CH < rows;
+    if (fast) {
+      const unsigned ra = ring_a + ((unsigned)(k0 & (CB_RING - 1)) * CB_TPB + (unsigned)t) * 4u;   // k0 % CB_CH == 0: no wrap inside
+#pragma unroll
+      for (int i = 0; i < CB_CH; ++i) { run = run + cur[i]; sts_f32(ra + i * CB_TPB * 4u, run); }   // column pass :59-65
+    } else {
+#pragma unroll
+      for (int i = 0; i < CB_CH; ++i) {
+        if (k0 + i < rows) {
+          run = (k0 + i == 0) ? cur[i] : run + cur[i];
+          ring[(k0 + i) & (CB_RING - 1)][t] = run;
+        }
+      }
+    }
+    __syncthreads();
+    const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;   // last output row whose taps are all in the ring
+    if (out_ok) {
+      if (fast) {   // onext == k0 - hm
+        const int ro0 = k0 - hm;
+        float* dA = dstA + (size_t)ro0 * cols + oc;
+        if (mixed) cb_box_rows<true>(pA_hi, pA_lo, leftA, invA, ro0, ha, dA, cols);
+        else cb_box_rows<false>(pA_hi, pA_lo, leftA, invA, ro0, ha, dA, cols);
+        if (dual) {
+          float* dB = dstB + (size_t)ro0 * cols + oc;
+          if (mixed) cb_box_rows<true>(pB_hi, pB_lo, leftB, invB, ro0, hb, dB, cols);
+          else cb_box_rows<false>(pB_hi, pB_lo, leftB, invB, ro0, hb, dB, cols);
+        }
+      } else {
+        for (int ro = onext; ro <= olast; ++ro) {
+          dstA[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, ha, rows, jhiA, jloA, leftA, ncolA, invA);
+          if (dual) dstB[(size_t)ro * cols + oc] = box_value(ring, inv_area, ro, hb, rows, jhiB, jloB, leftB, ncolB, invB);
+        }
+      }
+    }
+    onext = max(onext, olast + 1);
+  }
 }
 
 #define BP_MAX_THREADS 640
@@ -507,6 +618,15 @@ int fe_init(rbv_ctx* c) {
   return RBV_OK;
 }
 
+static void fe_rowscan(rbv_ctx* c, const float* in, float* out, int planes) {
+  const int rows = c->P.rows, cols = c->P.cols;
+  const size_t N = (size_t)c->P.npix;
+  if ((cols & 3) == 0 && (((uintptr_t)in | (uintptr_t)out) & 15) == 0)
+    RBV_LAUNCH(c, k_rowscan4, (dim3((rows + 31) / 32, planes)), (32), 0, in, out, rows, cols, N, N);
+  else
+    RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, planes)), (32), 0, in, out, rows, cols, N, N);
+}
+
 // ScaleSpace::build (scale_space.cpp:203-208): 3 box passes per scale, both scales from the same input.
 // Buffers are [lane][scale][N]; result: scale s of lane b = bufA[(b*2+s)*N].
 int fe_scale_space(rbv_ctx* c, const float* d_img) {
@@ -521,7 +641,7 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
   }
   // pass 0: one row prefix per lane, one column scan feeding both box widths (widths[0][0], widths[1][0])
   {
-    RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, B)), (32), 0, d_img, c->rowsum, rows, cols, N, N);
+    fe_rowscan(c, d_img, c->rowsum, B);
     const int d0 = c->widths[0][0], d1 = c->widths[1][0];
     const int hmax = (d0 > d1 ? d0 : d1) / 2;
     const int W = CB_TPB - (2 * hmax + 1);
@@ -530,7 +650,7 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
   float* src = c->bufA;
   float* dst = c->bufB;
   for (int p = 1; p < 3; ++p) {
-    RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 2 * B)), (32), 0, src, c->rowsum, rows, cols, N, N);
+    fe_rowscan(c, src, c->rowsum, 2 * B);
     const int d0 = c->widths[0][p], d1 = c->widths[1][p];
     const int hmax = (d0 > d1 ? d0 : d1) / 2;
     const int W = CB_TPB - (2 * hmax + 1);
@@ -552,7 +672,7 @@ int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float*
     RBV_CUDA(cudaGetLastError());
     return RBV_OK;
   }
-  RBV_LAUNCH(c, k_rowscan, (dim3((rows + 31) / 32, 1)), (32), 0, d_in, c->rowsum, rows, cols, N, N);
+  fe_rowscan(c, d_in, c->rowsum, 1);
   const int W = CB_TPB - (2 * (d / 2) + 1);
   RBV_LAUNCH(c, k_colbox, (dim3((cols + W - 1) / W, 1)), (CB_TPB), 0, c->rowsum, d_out, d_out, rows, cols, N, N, 1, d, d, 0);
   RBV_CUDA(cudaGetLastError());

@@ -17,6 +17,7 @@ def kernel_bytes(name, N, K, B, planes=1, P=20.0, words=0):
         # one box pass (createIntegralImage + average) must read N and write N floats per plane; it is split in two
         # kernels here, each of which reads N and writes N of its own
         "k_rowscan": 8.0 * N * planes,
+        "k_rowscan4": 8.0 * N * planes,
         "k_colbox": 8.0 * N * planes,
         "k_detect_flags": 12.0 * N,          # read both scales, write the id mask (DoG / magnitude never reach memory)
         "k_detect_scan": 0.0,
