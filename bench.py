@@ -309,6 +309,14 @@ def run_b200(args):
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
     achieved = abytes / (top_ms / max(1, top_n) * 1e-3) / 1e9
+    # DRAM traffic of the same kernel from the committed `ncu --set full` capture of this command (64 lanes, 752x480);
+    # only quoted when the run has the capture's shape
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    if os.path.exists(tpath) and B == LANES_PER_GPU and args.config == "C2":
+        tj = json.load(open(tpath))
+        if top in tj.get("bytes_per_launch", {}):
+            traffic, traffic_src = float(tj["bytes_per_launch"][top]), "profiles/r01_ncu_traffic.json (" + tj.get("source", "") + ")"
     frame_gbs = roofline.frame_bytes(N, K_mean, probes) * value / max(1, world) / 1e9
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -318,7 +326,7 @@ def run_b200(args):
                        "reduce_mode": args.reduce, "parallelism": f"replicas x{world} (no collective)",
                        "l2": f"per-step working set {B} lanes x ~14 MB >> 126 MB L2 (inputs larger than L2, no flush needed)"},
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
                          "avg_launch_ms": top_ms / max(1, top_n), "launches_timed": top_n,
                          "kernel_share_of_step": (top_ms / max(1, top_n)) * (top_launches / K) / (ms / K),
                          "frame_level": {"achieved": frame_gbs, "frac": frame_gbs / peak,
