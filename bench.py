@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-single", action="store_true", help="skip the single-stream latency leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tune", default="", help="implementation choices, e.g. '2=4,0=1' (rbv_set_tuning key=value pairs)")
     ap.add_argument("--kernel-table", default="", help="write the per-kernel CUDA-event table (one untimed step) here")
     return ap.parse_args()
 
@@ -260,6 +261,9 @@ def run_b200(args):
 
     # ---- leg 1: device-resident inputs ----------------------------------------------------------------------
     pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
+    tune = [tuple(int(x) for x in kv.split("=")) for kv in args.tune.split(",") if kv]
+    for key, val in tune:
+        pipe.ctx.set_tuning(key, val)
     ptr = lambda k: d_frames[k].data_ptr()
     pipe.push(device_ptr=ptr(0))
     # warm-up; the first warm-up step runs with every kernel bracketed by CUDA events to find the dominant kernel

@@ -629,19 +629,24 @@ static void fe_rowscan(rbv_ctx* c, const float* in, float* out, int planes) {
 
 // ScaleSpace::build (scale_space.cpp:203-208): 3 box passes per scale, both scales from the same input.
 // Buffers are [lane][scale][N]; result: scale s of lane b = bufA[(b*2+s)*N].
-int fe_scale_space(rbv_ctx* c, const float* d_img) {
+// part: 0 = everything, 1 = only the kernel that reads d_img (the one launch whose arguments change from frame to frame),
+// 2 = everything after it (captured in a CUDA graph by the caller)
+int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
   const int rows = c->P.rows, cols = c->P.cols, B = c->P.lanes;
   const size_t N = (size_t)c->P.npix;
   if (bp_use(c, d_img)) {   // fused passes: 64 N -> 44 N bytes of traffic per frame, 3 launches instead of 6
-    bp_launch(c, d_img, c->bufA, c->bufA + N, B, N, 2 * N, 1, c->widths[0][0], c->widths[1][0], 1);
-    bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
-    bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+    if (part != 2) bp_launch(c, d_img, c->bufA, c->bufA + N, B, N, 2 * N, 1, c->widths[0][0], c->widths[1][0], 1);
+    if (part != 1) {
+      bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
+      bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+    }
     RBV_CUDA(cudaGetLastError());
     return RBV_OK;
   }
   // pass 0: one row prefix per lane, one column scan feeding both box widths (widths[0][0], widths[1][0])
+  if (part != 2) fe_rowscan(c, d_img, c->rowsum, B);
+  if (part == 1) { RBV_CUDA(cudaGetLastError()); return RBV_OK; }
   {
-    fe_rowscan(c, d_img, c->rowsum, B);
     const int d0 = c->widths[0][0], d1 = c->widths[1][0];
     const int hmax = (d0 > d1 ? d0 : d1) / 2;
     const int W = CB_TPB - (2 * hmax + 1);
@@ -661,6 +666,7 @@ int fe_scale_space(rbv_ctx* c, const float* d_img) {
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
+int fe_uses_fused_box(rbv_ctx* c, const float* d_img) { return bp_use(c, d_img) ? 1 : 0; }
 
 // debug: one box pass (createIntegralImage + average) on lane 0, plane 0 of the scratch buffers
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {

@@ -143,6 +143,7 @@ struct rbv_ctx {
   int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
   int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
   void* prof;                       // ProfState* (rbv_api.cu)
+  void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed
 };
 
 // lane_in slots
@@ -159,7 +160,8 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
   X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
-  X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4)
+  X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
+  X(k_tryvel_fast2) X(k_tryvel_fast4)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
@@ -190,7 +192,8 @@ void rbv_set_error(const char* fmt, ...);
 // ---- launchers (host functions defined in the .cu files) ----
 int fe_init(rbv_ctx* c);   // per-device kernel attributes (dynamic shared memory limits)
 int tr_init(rbv_ctx* c);
-int fe_scale_space(rbv_ctx* c, const float* d_img);
+int fe_scale_space(rbv_ctx* c, const float* d_img, int part);
+int fe_uses_fused_box(rbv_ctx* c, const float* d_img);
 int fe_detect(rbv_ctx* c, rbv_map* map);
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out);
 int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out);

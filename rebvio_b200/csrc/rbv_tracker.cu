@@ -713,12 +713,246 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast(KeylineSoA Ko, const int
   }
 }
 
+// ---- the same, KPT consecutive keylines per thread ---------------------------------------------------------------------
+// k_tryvel_fast is bound by the latency of a dependent chain (keyline fields -> field cell -> target record) whose loads sit
+// behind the reference's early-outs. Here every thread owns KPT consecutive keylines (thread order = keyline order, so the
+// carried-residual rule and the fixed summation order survive), fetches all their fields with vector loads BEFORE any test,
+// then issues the KPT field-cell gathers together and the KPT target gathers together: three memory round trips per thread
+// with KPT requests in flight in each, instead of five with one. The per-keyline arithmetic is tryvel_point's, statement by
+// statement. Per-thread FP64 accumulation in keyline order, then the same shuffle tree / ticket scheme (1/KPT as many CTAs).
+template <int KPT> __device__ __forceinline__ void tv_ld(const float* __restrict__ p, float* v) {
+  if constexpr (KPT == 4) { const float4 a = *reinterpret_cast<const float4*>(p); v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; }
+  else if constexpr (KPT == 2) { const float2 a = *reinterpret_cast<const float2*>(p); v[0] = a.x; v[1] = a.y; }
+  else v[0] = *p;
+}
+template <int KPT> __device__ __forceinline__ void tv_ld(const unsigned* __restrict__ p, unsigned* v) {
+  if constexpr (KPT == 4) { const uint4 a = *reinterpret_cast<const uint4*>(p); v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; }
+  else if constexpr (KPT == 2) { const uint2 a = *reinterpret_cast<const uint2*>(p); v[0] = a.x; v[1] = a.y; }
+  else v[0] = *p;
+}
+template <int KPT> __device__ __forceinline__ void tv_ld2(const float2* __restrict__ p, float2* v) {
+  if constexpr (KPT >= 2) {
+#pragma unroll
+    for (int k = 0; k < KPT; k += 2) {
+      const float4 a = *reinterpret_cast<const float4*>(p + k);
+      v[k] = make_float2(a.x, a.y); v[k + 1] = make_float2(a.z, a.w);
+    }
+  } else v[0] = *p;
+}
+template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const T* v, int nvalid) {
+  static_assert(sizeof(T) == 4, "32-bit elements");
+  if (nvalid >= KPT) {
+    const unsigned* u = reinterpret_cast<const unsigned*>(v);
+    if constexpr (KPT == 4) *reinterpret_cast<uint4*>(p) = make_uint4(u[0], u[1], u[2], u[3]);
+    else if constexpr (KPT == 2) *reinterpret_cast<uint2*>(p) = make_uint2(u[0], u[1]);
+    else p[0] = v[0];
+  } else {
+#pragma unroll
+    for (int k = 0; k < KPT; ++k) if (k < nvalid) p[k] = v[k];
+  }
+}
+
+template <int KPT>
+__device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
+                                                         const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
+                                                         int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
+                                                         double* __restrict__ partials, unsigned* __restrict__ ticket,
+                                                         const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
+                                                         LMState* lm, float* lane_out, int lm_call, const DevParams& P) {
+  __shared__ double sm[(TV_TPB / 32) * 10];
+  __shared__ double result[10];
+  __shared__ float warp_val[TV_TPB / 32];
+  __shared__ int warp_has[TV_TPB / 32];
+  __shared__ int s_last;
+  constexpr int KPB = TV_TPB * KPT;
+  const int b = blockIdx.y, n = count_o[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int nact = max(1, (n + KPB - 1) / KPB);
+  if ((int)blockIdx.x >= nact) return;
+  const int idx0 = (blockIdx.x * TV_TPB + t) * KPT;
+  const size_t base = (size_t)b * P.kmax, o = base + idx0;
+  const int nvalid = min(KPT, n - idx0);          // <= 0: nothing of this thread is a keyline
+  double acc[10];
+#pragma unroll
+  for (int a = 0; a < 10; ++a) acc[a] = 0.0;
+  float code[KPT], res[KPT];
+#pragma unroll
+  for (int k = 0; k < KPT; ++k) { code[k] = -2.0f; res[k] = 0.0f; }
+  if (nvalid > 0) {
+    const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+    const float srmin = sr_ptr[(size_t)b * sr_stride], thr = thr_o[b];
+    const unsigned* __restrict__ field_b = field + (size_t)b * P.npix;
+    // ---- round trip 1: every field of the KPT keylines, no test in between
+    float gn[KPT], srho[KPT], rho[KPT];
+    unsigned mt[KPT];
+    float2 pi[KPT], g[KPT];
+    tv_ld<KPT>(Ko.gnorm + o, gn); tv_ld<KPT>(Ko.srho + o, srho); tv_ld<KPT>(Ko.rho + o, rho); tv_ld<KPT>(Ko.residual + o, res);
+    tv_ld<KPT>(Ko.matches + o, mt); tv_ld2<KPT>(Ko.pos_img + o, pi); tv_ld2<KPT>(Ko.grad + o, g);
+    float w[KPT], rho_p[KPT], px[KPT], py[KPT], pxc[KPT], pyc[KPT];
+    bool skip[KPT], penalty[KPT];
+    unsigned cell[KPT];
+#pragma unroll
+    for (int k = 0; k < KPT; ++k) {
+      if (res[k] < 0.0f) res[k] = residual_lookback(agg_prev + (size_t)b * nblk, blockIdx.x);
+      skip[k] = (k >= nvalid) || (thr > 0.0f && gn[k] < thr) || (srho[k] > srmin) || (mt[k] < P.min_matches);   // core.cpp:88,91
+      w[k] = 1.0f;
+      if (res[k] > P.reweight_distance) w[k] = P.reweight_distance / res[k];           // :94
+      const float z_p = (float)(1.0 / (double)rho[k] + (double)v2);                    // :96
+      penalty[k] = z_p <= 0.0f;
+      rho_p[k] = 0.0f; px[k] = py[k] = pxc[k] = pyc[k] = 0.0f;
+      int x = 0, y = 0;
+      if (!penalty[k]) {
+        rho_p[k] = (float)(1.0 / (double)z_p);                                         // :104
+        px[k] = rho_p[k] * (v0 * P.fm - v2 * pi[k].x) + pi[k].x;                       // :105
+        py[k] = rho_p[k] * (v1 * P.fm - v2 * pi[k].y) + pi[k].y;
+        pxc[k] = px[k] + P.cx; pyc[k] = py[k] + P.cy;
+        x = rbv_d2i((double)pxc[k] + 0.5);                                             // :111
+        y = rbv_d2i((double)pyc[k] + 0.5);
+        penalty[k] = (x < 1 || y < 1 || x >= P.cols - 1 || y >= P.rows - 1);           // :114
+      }
+      // ---- round trip 2: the KPT field cells
+      cell[k] = (!skip[k] && !penalty[k]) ? field_b[(size_t)y * P.cols + x] : RBV_FIELD_EMPTY;
+    }
+    // ---- round trip 3: the KPT target records (one 32-byte sector each)
+    float4 t0[KPT], t1[KPT];
+    int tid[KPT];
+#pragma unroll
+    for (int k = 0; k < KPT; ++k) {
+      tid[k] = (int)(0xFFFFFFu - (cell[k] & 0xFFFFFFu));
+      if (cell[k] != RBV_FIELD_EMPTY) { t0[k] = tgt[2 * (base + tid[k])]; t1[k] = tgt[2 * (base + tid[k]) + 1]; }
+      else { t0[k] = make_float4(0.f, 0.f, 0.f, 0.f); t1[k] = t0[k]; }
+    }
+    int fwd[KPT];
+#pragma unroll
+    for (int k = 0; k < KPT; ++k) {
+      fwd[k] = -1;
+      if (skip[k]) continue;
+      float add[10];
+      if (penalty[k]) {
+        const float f = (float)((1.0 / (double)srho[k]) * (double)P.search_range * (double)w[k]);   // :99 / :115
+        acc[0] += (double)(f * f);
+        continue;
+      }
+      float dfx = 0.0f, dfy = 0.0f, f;
+      bool matched = false;
+      if (cell[k] != RBV_FIELD_EMPTY) {
+        const float n2 = gn[k] * gn[k];                                                // testfk :40-42
+        const float dp = t0[k].x * g[k].x + t0[k].y * g[k].y;
+        if (!(fabsf(dp - n2) > P.match_treshold * n2)) {
+          matched = true;
+          const float dx = pxc[k] - t0[k].z, dy = pyc[k] - t0[k].w;                    // :62-63
+          const float gnx = t1[k].x, gny = t1[k].y;
+          const float fi = dx * gnx + dy * gny;                                        // :67
+          dfx = gnx / srho[k]; dfy = gny / srho[k];
+          fwd[k] = tid[k];                                                             // :73
+          f = fi / srho[k];                                                            // :75
+          code[k] = fabsf(fi);                                                         // :141
+        }
+      }
+      if (!matched) { f = P.search_range / srho[k]; code[k] = -1.0f; }                 // :52 / :59
+      f *= w[k];
+      add[0] = f * f;
+      const float jx = rho_p[k] * P.fm * dfx * w[k];                                   // :126-128
+      const float jy = rho_p[k] * P.fm * dfy * w[k];
+      const float jz = -rho_p[k] * (px[k] * dfx + py[k] * dfy) * w[k];
+      add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
+      add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
+      add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
+#pragma unroll
+      for (int a = 0; a < 10; ++a) acc[a] += (double)add[a];
+    }
+    tv_st<KPT, int>(Ko.match_fwd + o, fwd, nvalid);                                    // core.cpp:87
+  }
+  // carried |fi| in keyline order: thread aggregate = its last matched keyline, inclusive scan over the threads of the warp
+  int has = 0; float val = 0.0f;
+#pragma unroll
+  for (int k = 0; k < KPT; ++k) if (code[k] >= 0.0f) { has = 1; val = code[k]; }
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int h2 = __shfl_up_sync(0xFFFFFFFFu, has, off);
+    const float v2 = __shfl_up_sync(0xFFFFFFFFu, val, off);
+    if (lane >= off && !has) { has = h2; val = v2; }
+  }
+  if (lane == 31) { warp_has[warp] = has; warp_val[warp] = val; }
+  int ehas = __shfl_up_sync(0xFFFFFFFFu, has, 1);                                      // exclusive: what enters this thread
+  float eval = __shfl_up_sync(0xFFFFFFFFu, val, 1);
+  if (lane == 0) { ehas = 0; eval = 0.0f; }
+#pragma unroll
+  for (int a = 0; a < 10; ++a) {
+    double v = acc[a];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+    if (lane == 0) sm[warp * 10 + a] = v;
+  }
+  __syncthreads();
+  if (!ehas || !has) {
+    for (int w2 = warp - 1; w2 >= 0; --w2)
+      if (warp_has[w2]) {
+        if (!ehas) { ehas = 1; eval = warp_val[w2]; }
+        if (!has) { has = 1; val = warp_val[w2]; }
+        break;
+      }
+  }
+  if (nvalid > 0) {
+    float out[KPT];
+#pragma unroll
+    for (int k = 0; k < KPT; ++k) {
+      if (code[k] >= 0.0f) { ehas = 1; eval = code[k]; }
+      // core.cpp:141 (-1 = look back next time); no write this call = keep the (resolved) value that was read
+      out[k] = code[k] >= -1.5f ? (ehas ? eval : (blockIdx.x == 0 ? 0.0f : -1.0f)) : res[k];
+    }
+    tv_st<KPT, float>(Ko.residual + o, out, nvalid);
+  }
+  if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blockIdx.x] = has ? val : -1.0f;
+  if (t < 10) {
+    double s2 = 0.0;
+#pragma unroll
+    for (int w2 = 0; w2 < TV_TPB / 32; ++w2) s2 += sm[w2 * 10 + t];
+    partials[((size_t)b * nblk + blockIdx.x) * 10 + t] = s2;
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) s_last = (atomicAdd(&ticket[b], 1u) == (unsigned)(nact - 1));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (t < 10) {
+    double s2 = 0.0;
+    for (int j = 0; j < nact; ++j) s2 += __ldcg(partials + ((size_t)b * nblk + j) * 10 + t);
+    result[t] = s2;
+  }
+  __syncthreads();
+  if (t == 0) {
+    ticket[b] = 0u;
+    float JtJ[9], JtF[3];
+    const float score = (float)result[0];
+    JtJ[0] = (float)result[1]; JtJ[4] = (float)result[2]; JtJ[8] = (float)result[3];
+    JtJ[1] = JtJ[3] = (float)result[4]; JtJ[2] = JtJ[6] = (float)result[5]; JtJ[5] = JtJ[7] = (float)result[6];
+    JtF[0] = (float)result[7]; JtF[1] = (float)result[8]; JtF[2] = (float)result[9];
+    if (lm_call >= 0) {
+      float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
+      lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
+    }
+    float* outp = lane_out + (size_t)b * OUT_STRIDE;
+    for (int i = 0; i < 9; ++i) outp[OUT_JTJ + i] = JtJ[i];
+    for (int i = 0; i < 3; ++i) outp[OUT_JTF + i] = JtF[i];
+    outp[OUT_SCORE] = score;
+  }
+}
+
+#define RBV_TV_PARAMS KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,             \
+                      const unsigned* __restrict__ field, const float* __restrict__ vel_ptr, int vel_stride, const float* __restrict__ sr_ptr,    \
+                      int sr_stride, double* __restrict__ partials, unsigned* __restrict__ ticket, const float* __restrict__ agg_prev,            \
+                      float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const __grid_constant__ DevParams P
+#define RBV_TV_PASS Ko, count_o, thr_o, tgt, field, vel_ptr, vel_stride, sr_ptr, sr_stride, partials, ticket, agg_prev, agg_cur, nblk, lm, lane_out, lm_call, P
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2>(RBV_TV_PASS); }
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4>(RBV_TV_PASS); }
+
 __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
-                                                             int nblk, int kmax) {
+                                                             int nblk, int kmax, int kpb) {
   const int b = blockIdx.y, idx = blockIdx.x * TV_TPB + threadIdx.x;
   if (idx >= count_o[b]) return;
   const size_t o = (size_t)b * kmax + idx;
-  if (Ko.residual[o] < 0.0f) Ko.residual[o] = residual_lookback(agg + (size_t)b * nblk, blockIdx.x);
+  if (Ko.residual[o] < 0.0f) Ko.residual[o] = residual_lookback(agg + (size_t)b * nblk, idx / kpb);
 }
 
 // lm_call = -1: single evaluation at lane_in vel / sigma_rho_min; 0: first LM call at lm.vel; >= 1: at lm.vnew
@@ -744,9 +978,17 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     const size_t half = (size_t)P.lanes * nblk;
     float* agg_cur = c->blkagg + (size_t)c->tv_parity * half;
     const float* agg_prev = c->blkagg + (size_t)(1 - c->tv_parity) * half;
-    RBV_LAUNCH(c, k_tryvel_fast, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P);
+    // keylines per thread (RBV_TUNE_TRYVEL): 1 = k_tryvel_fast, 2 / 4 = k_tryvel_fast2 / k_tryvel_fast4 (0 = automatic: 4)
+    int kpt = c->tune[RBV_TUNE_TRYVEL] ? c->tune[RBV_TUNE_TRYVEL] : 4;
+    if (kpt == 3 || kpt > 4) kpt = 4;
+    const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
+#define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P
+    if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
+    else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
+    else { RBV_LAUNCH(c, k_tryvel_fast4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
+#undef RBV_TV_ARGS
     if (lm_call < 0 || lm_call == P.iterations)
-      RBV_LAUNCH(c, k_residual_resolve, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_cur, nblk, P.kmax);
+      RBV_LAUNCH(c, k_residual_resolve, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_cur, nblk, P.kmax, TV_TPB * kpt);
     c->tv_parity = 1 - c->tv_parity;
   }
   RBV_CUDA(cudaGetLastError());
@@ -827,19 +1069,31 @@ int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
 
 // ---------------------------------------------------------------------------------------------------------------
 // extRotVel rows (core.cpp:202-236): Phi_j (6) and Y_j after the division by s_y*weight; zeros for unmatched keylines.
-__device__ __forceinline__ void extrot_row(const KeylineSoA& K, size_t o, float v0, float v1, float v2, const DevParams& P, float* phi) {
+// what a row reads of its keyline; fetched with no test in between so that all loads of a thread are in flight together
+struct ExtRotIn {
+  int mid;
+  float2 g, m, q;
+  float gn, rho, sr;
+};
+__device__ __forceinline__ ExtRotIn extrot_load(const KeylineSoA& K, size_t o) {
+  ExtRotIn in;
+  in.mid = K.match_id[o]; in.g = K.grad[o]; in.gn = K.gnorm[o]; in.rho = K.rho[o];
+  in.m = K.match_pos_img[o]; in.q = K.pos_img[o]; in.sr = K.srho[o];
+  return in;
+}
+__device__ __forceinline__ void extrot_row_in(const ExtRotIn& in, float v0, float v1, float v2, const DevParams& P, float* phi) {
 #pragma unroll
   for (int a = 0; a < 7; ++a) phi[a] = 0.0f;
-  if (K.match_id[o] < 0) return;
+  if (in.mid < 0) return;
   const float fm = P.fm;
-  const float2 g = K.grad[o];
-  const float gn = K.gnorm[o];
+  const float2 g = in.g;
+  const float gn = in.gn;
   const float ux = g.x / gn, uy = g.y / gn;                                            // :207-208
-  const float rho_t = (float)(1.0 / (1.0 / (double)K.rho[o] + (double)v2));            // :210
-  const float2 m = K.match_pos_img[o];
+  const float rho_t = (float)(1.0 / (1.0 / (double)in.rho + (double)v2));              // :210
+  const float2 m = in.m;
   const float qtx = m.x + rho_t * (v0 * fm - v2 * m.x);                                // :211-212
   const float qty = m.y + rho_t * (v1 * fm - v2 * m.y);
-  const float2 q = K.pos_img[o];
+  const float2 q = in.q;
   phi[0] = ux * rho_t * fm;                                                            // :217-222
   phi[1] = uy * rho_t * fm;
   phi[2] = ux * (-rho_t * q.x) + uy * (-rho_t * q.y);
@@ -848,7 +1102,7 @@ __device__ __forceinline__ void extrot_row(const KeylineSoA& K, size_t o, float 
   phi[5] = -ux * q.y + uy * q.x;
   float y = ux * (q.x - qtx) + uy * (q.y - qty);                                       // :224
   const float dqvel = ux * (v0 * fm - v2 * m.x) + uy * (v1 * fm - v2 * m.y);           // :226
-  const float sr = K.srho[o];
+  const float sr = in.sr;
   const float sy = sqrtf(sr * sr * dqvel * dqvel + P.pixel_uncertainty * P.pixel_uncertainty);   // :227
   float w = 1.0f;
   if (fabsf(y) > P.reweight_distance) w = fabsf(y) / P.reweight_distance;              // :230
@@ -857,6 +1111,14 @@ __device__ __forceinline__ void extrot_row(const KeylineSoA& K, size_t o, float 
   for (int a = 0; a < 6; ++a) phi[a] /= dv;                                            // :232
   y /= dv;                                                                             // :233
   phi[6] = y;
+}
+__device__ __forceinline__ void extrot_row(const KeylineSoA& K, size_t o, float v0, float v1, float v2, const DevParams& P, float* phi) {
+  if (K.match_id[o] < 0) {
+#pragma unroll
+    for (int a = 0; a < 7; ++a) phi[a] = 0.0f;
+    return;
+  }
+  extrot_row_in(extrot_load(K, o), v0, v1, v2, P, phi);
 }
 
 __global__ void __launch_bounds__(256) k_extrot_rows(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr,
@@ -1025,12 +1287,18 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
 #pragma unroll
   for (int a = 0; a < 27; ++a) acc[a] = 0.0;
   const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
-#pragma unroll 1
-  for (int j = 0; j < ER_KPT; ++j) {
+  ExtRotIn in[ER_KPT];
+#pragma unroll
+  for (int j = 0; j < ER_KPT; ++j) {                // every load of the thread's ER_KPT keylines first (one round trip)
     const int idx = (blockIdx.x * ER_KPT + j) * TV_TPB + t;
-    if (idx >= n) break;
+    in[j].mid = -1;
+    if (idx < n) in[j] = extrot_load(K, (size_t)b * P.kmax + idx);
+  }
+#pragma unroll
+  for (int j = 0; j < ER_KPT; ++j) {
+    if (in[j].mid < 0) continue;                    // unmatched rows are all zeros: x + 0 == x
     float r[7];
-    extrot_row(K, (size_t)b * P.kmax + idx, v0, v1, v2, P, r);
+    extrot_row_in(in[j], v0, v1, v2, P, r);
     int k = 0;
 #pragma unroll
     for (int a = 0; a < 6; ++a) {

@@ -92,15 +92,17 @@ def test_cuda_fast_reduction_teacher_forced(name, nf):
     g.close(); orc.close()
 
 
-def test_try_vel_fast_vs_ordered_indices_and_sums():
+@pytest.mark.parametrize("kpt", [1, 2, 4])
+def test_try_vel_fast_vs_ordered_indices_and_sums(kpt):
+    """kpt = keylines per thread of the FAST-mode tryVel kernel (k_tryvel_fast / k_tryvel_fast2 / k_tryvel_fast4)"""
     spec, frames, R_rel = common.sequence("C2", 3)
     cfg = common.cfgs_from_spec(spec)
-    for mode in (capi.REDUCE_ORDERED, capi.REDUCE_FAST):
+    for mode in ((capi.REDUCE_ORDERED, capi.REDUCE_FAST) if kpt == 1 else (capi.REDUCE_FAST,)):
         orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
         a, b = orc.detect(frames[0]), orc.detect(frames[1])
         orc.build_distance_field(b)
         n = orc.map_size(a)
-        g = _gpu(cfg, mode=mode)
+        g = _gpu(cfg, mode=mode, tune={capi.TUNE_TRYVEL: kpt})
         ga, gb = g.detect(frames[0]), g.detect(frames[1])
         g.build_distance_field(gb)
         res = np.zeros(n, np.float32)
@@ -117,6 +119,8 @@ def test_try_vel_fast_vs_ordered_indices_and_sums():
             else:
                 assert abs(sg - so) <= SCORE_RTOL * abs(so)
                 assert H.rel_err(JJg, JJo) <= 1e-5 and H.rel_err(JFg, JFo) <= 1e-5
+        if mode == capi.REDUCE_FAST:
+            assert g.ctx.profile_launches().get({1: "k_tryvel_fast", 2: "k_tryvel_fast2", 4: "k_tryvel_fast4"}[kpt], 0) > 0
         g.close(); orc.close()
 
 
@@ -334,3 +338,35 @@ def test_u8_upload_and_prefetch_match_float_path():
                     assert np.array_equal(H.bits(np.asarray(o[key], np.float32)), H.bits(np.asarray(o0[key], np.float32))), key
             for a, b in zip(kl, kl0):
                 assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("lanes,mode", [(1, capi.REDUCE_FAST), (3, capi.REDUCE_ORDERED), (20, capi.REDUCE_FAST)])
+def test_cuda_graph_replay_equals_stream_launches(lanes, mode):
+    """RBV_TUNE_GRAPH: the captured kernel sequences of detect / track_g1 / track_g2 (replayed from frame 3 on, when both
+    map pairings have been captured) give bit-identical outputs, keylines and launch counts to plain stream launches.
+    20 lanes takes the fused box-pass path, 1 and 3 lanes the split one."""
+    from rebvio_b200.pipeline import BatchedPipeline
+    nf = 7
+    spec = synth.config("C5:320x240", n_frames=nf)
+    seq = synth.generate(spec)
+    u8 = np.stack([np.stack([np.ascontiguousarray(seq.frames[(k + b) % nf]) for b in range(lanes)]) for k in range(nf)]).astype(np.uint8)
+    R = np.stack([np.stack([seq.R_rel[k] for b in range(lanes)]) for k in range(nf)])
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+    outs = []
+    for graph in (1, 2):
+        pipe = BatchedPipeline(cam, det, mapc, core, lanes, reduce_mode=mode)
+        pipe.ctx.set_tuning(capi.TUNE_GRAPH, graph)
+        rec = []
+        for k in range(nf):
+            o = pipe.push(frames=u8[k], R_rel=R[k] if k else None)
+            rec.append((o, [pipe.newest_map().keylines(b)[0] for b in range(lanes)], pipe.ctx.launch_count(), pipe.ctx.profile_launches()))
+        outs.append(rec)
+        pipe.close()
+    for (o, kl, nl, names), (o0, kl0, nl0, names0) in zip(outs[1], outs[0]):
+        assert nl == nl0 and names == names0
+        for key in o0:
+            assert np.array_equal(H.bits(np.asarray(o[key], np.float32)), H.bits(np.asarray(o0[key], np.float32))), key
+        for a, b in zip(kl, kl0):
+            assert a.tobytes() == b.tobytes()
