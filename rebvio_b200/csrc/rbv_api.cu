@@ -455,6 +455,12 @@ void rbv_graphs_clear(rbv_ctx* c, const void* map) {
   if (!map) { delete g; c->graphs = nullptr; }
 }
 enum { GK_DETECT = 1, GK_TRACK1 = 2, GK_TRACK2 = 3 };
+// scope of a fused tracker sequence (see rbv_ctx::seq_fused)
+struct SeqFused {
+  rbv_ctx* c;
+  SeqFused(rbv_ctx* ctx, int min_matches) : c(ctx) { c->seq_fused = 1; c->seq_min_matches = min_matches; }
+  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; }
+};
 template <class Body>
 static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int flag, Body body) {
   if (c->tune[RBV_TUNE_GRAPH] == 1 || c->prof_mode != -1) return body();
@@ -681,9 +687,14 @@ __global__ void k_lm_init(LMState* lm, const float* lane_in, int lanes) {
 
 // enqueue Core::minimizeVel (core.cpp:150-189) on the stream: quantile, residual reset, (1 + iterations) tryVel + LM steps
 static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map) {
-  TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, 1));
-  TRY(rbv_fill32(c, old_map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax));
-  RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
+  // FAST mode with several keylines per thread: the quantile kernel also seeds the LM state, and call 0 of tryVel takes the
+  // residuals as zero and writes every entry, so neither k_lm_init nor the residual fill is launched
+  const bool lean = c->reduce_mode == RBV_REDUCE_FAST && c->tune[RBV_TUNE_TRYVEL] != 1;
+  TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, lean ? 2 : 1));
+  if (!lean) {
+    TRY(rbv_fill32(c, old_map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax));
+    RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
+  }
   for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
   return RBV_OK;
 }
@@ -803,6 +814,7 @@ extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R9, 9);   // IN_VEL stays 0: imu_state_.Vg = Zeros (rebvio.cpp:168)
   TRY(stage_commit(c, slot));
   TRY(run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
+    SeqFused fused(c, 0);
     TRY(tr_build_field(c, new_map));
     TRY(tr_rotate(c, old_map));
     TRY(enqueue_minimize(c, old_map));
@@ -816,17 +828,6 @@ extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   return RBV_OK;
 }
 
-__global__ void k_gate_min_matches(int* count_backup, int* count, const int* lane_cnt, int min_matches, int lanes, int restore) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= lanes) return;
-  if (!restore) {
-    count_backup[b] = count[b];
-    if (lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) count[b] = 0;   // lanes below the floor skip regularise + Kalman
-  } else {
-    count[b] = count_backup[b];
-  }
-}
-
 extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R0_9, const float* V3, const float* PV9,
                             const float* Rgva9, float max_radius, int min_matches, int* n_matches, int* kf_matches) {
   CHECK_CTX(c);
@@ -838,15 +839,11 @@ extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   put_directed(c, h, V3, PV9, Rgva9, max_radius);
   TRY(stage_commit(c, slot));
   TRY(run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
+    SeqFused fused(c, min_matches);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
     TRY(tr_rotate(c, old_map));
     TRY(tr_directed_match(c, new_map, old_map));
-    int* backup = c->rowcount;  // scratch ints, free between detects
-    const int nb = (c->P.lanes + 63) / 64;
-    RBV_LAUNCH(c, k_gate_min_matches, (nb), (64), 0, backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 0);
     TRY(tr_regularize(c, new_map));
-    TRY(tr_kalman(c, new_map));
-    RBV_LAUNCH(c, k_gate_min_matches, (nb), (64), 0, backup, new_map->count, c->lane_cnt, min_matches, c->P.lanes, 1);
-    return RBV_OK;
+    return tr_kalman(c, new_map);
   }));
   TRY(fetch_cnt(c));
   for (int b = 0; b < c->P.lanes; ++b) {

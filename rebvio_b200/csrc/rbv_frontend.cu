@@ -155,7 +155,7 @@ __device__ __forceinline__ float box_value(const float (*ring)[CB_TPB], const fl
 //   warps 2..          column pass + box: thread = image column, running column sum (:59-65) into a BP_RING-row shared ring
 //                      of the integral image, then the four-tap box (:69-128) for every row whose taps are complete.
 // full -> scanned -> empty mbarriers hand the chunk buffers round; the column warps use a named barrier for the ring.
-// Needs cols % 4 == 0 (16-byte bulk copies), 64 + cols threads <= 1024 and 2*BP_R*(cols+pad) + BP_RING*cols floats of smem.
+// Needs cols % 4 == 0 (16-byte bulk copies) and 2*BP_R*(cols+pad) + BP_RP*roundup(cols,64) floats of smem (cols <= 768).
 #define BP_R 16
 #define BP_RING 32
 #define BP_CH 8
@@ -192,24 +192,30 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// one output value from a full-width ring (ring row pitch = cols; jhi / jlo are image columns)
-__device__ __forceinline__ float box_value_fw(const float* __restrict__ ring, int cols, const float (*inv_area)[16], int ro, int h, int rows,
+// The ring of the integral image is COLUMN-major: ring[col * BP_RP + (row & 31)], rows 32..39 of a column mirror rows 0..7.
+// With the row index in the low-order position, the 8 rows of a sub-chunk are 8 consecutive words behind one base register
+// (immediate offsets, no wrap: start <= 31, start + 7 <= 38), so the steady state spends no instruction on tap addresses; the
+// odd column pitch keeps lane = column accesses conflict-free.
+#define BP_RP 41
+// one output value (border rows); jhi / jlo are image columns
+__device__ __forceinline__ float box_value_fw(const float* __restrict__ ring, const float (*inv_area)[16], int ro, int h, int rows,
                                               int jhi, int jlo, bool left, int ncol, float inv_mid) {
   const int rlo = ro - h - 1;
+  const float* chi = ring + jhi * BP_RP;
+  const float* clo = ring + max(jlo, 0) * BP_RP;
   if (rlo >= 0 && ro + h < rows) {
-    const float* hi = ring + ((ro + h) & (BP_RING - 1)) * cols;
-    const float* lo = ring + (rlo & (BP_RING - 1)) * cols;
-    const float v = left ? ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo] : hi[jhi] - lo[jhi];   // :99 / :94
+    const int rh = (ro + h) & (BP_RING - 1), rl = rlo & (BP_RING - 1);
+    const float v = left ? ((chi[rh] - clo[rh]) - chi[rl]) + clo[rl] : chi[rh] - chi[rl];   // :99 / :94
     return v * inv_mid;
   }
   const int rhi = min(ro + h, rows - 1);
-  const float* hi = ring + (rhi & (BP_RING - 1)) * cols;
+  const int rh = rhi & (BP_RING - 1);
   float v;
   if (rlo < 0) {
-    v = left ? hi[jhi] - hi[jlo] : hi[jhi];                                             // :78-84
+    v = left ? chi[rh] - clo[rh] : chi[rh];                                             // :78-84
   } else {
-    const float* lo = ring + (rlo & (BP_RING - 1)) * cols;
-    v = left ? ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo] : hi[jhi] - lo[jhi];           // :119,:124 / :114
+    const int rl = rlo & (BP_RING - 1);
+    v = left ? ((chi[rh] - chi[rl]) - clo[rh]) + clo[rl] : chi[rh] - chi[rl];           // :119,:124 / :114
   }
   return v * inv_area[rhi - max(rlo, -1)][ncol];
 }
@@ -230,7 +236,7 @@ __device__ __forceinline__ void sts_f32x2(unsigned a, float x, float y) {
   asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
 }
 
-// taps of one output column: shared addresses of ring row 0 at the right / left tap column, divisor, left-tap flag
+// taps of one output column: shared addresses of ring row 0 of the right / left tap column, divisor, left-tap flag
 struct BpTap {
   unsigned p_hi, p_lo;
   float inv;
@@ -240,36 +246,32 @@ __device__ __forceinline__ BpTap bp_tap(unsigned ring_a, int c, int h, int cols)
   BpTap t;
   const int jhi = min(c + h, cols - 1), jlo = c - h - 1;
   t.left = jlo >= 0;
-  t.p_hi = ring_a + 4u * (unsigned)jhi;
-  t.p_lo = ring_a + 4u * (unsigned)max(jlo, 0);
+  t.p_hi = ring_a + 4u * BP_RP * (unsigned)jhi;
+  t.p_lo = ring_a + 4u * BP_RP * (unsigned)max(jlo, 0);
   t.inv = (float)(1.0 / (double)((float)(2 * h + 1) * (float)(jhi - max(jlo, -1))));     // interior-row divisor (:72 / :168)
   return t;
 }
 
-// BP_CH interior output rows of two adjacent columns (t0: column c, t1: column c + 1). Output i takes ring rows
-// (ro0 + h + i) and (ro0 - h - 1 + i) mod BP_RING: ((A - B) - C) + D (:99), or A - C where there is no left tap (:94).
+// BP_CH interior output rows of two columns (t0: column c, t1: column c + 32; dst = output row ro0, column c). Output i takes
+// ring rows (ro0 + h + i) and (ro0 - h - 1 + i): ((A - B) - C) + D (:99), or A - C where there is no left tap (:94).
 template <bool MIXED>
-__device__ __forceinline__ void bp_box_rows(const BpTap& t0, const BpTap& t1, int ro0, int h, unsigned colb, float* __restrict__ dst0,
-                                            float* __restrict__ dst1, bool ok0, bool ok1, int cols) {
-  const unsigned ringb = BP_RING * colb;
-  unsigned hi_off = (unsigned)((ro0 + h) & (BP_RING - 1)) * colb;
-  unsigned lo_off = (unsigned)((ro0 - h - 1) & (BP_RING - 1)) * colb;
+__device__ __forceinline__ void bp_box_rows(const BpTap& t0, const BpTap& t1, int ro0, int h, float* __restrict__ dst, bool ok0, bool ok1,
+                                            int cols) {
+  const unsigned hs = 4u * (unsigned)((ro0 + h) & (BP_RING - 1)), ls = 4u * (unsigned)((ro0 - h - 1) & (BP_RING - 1));
+  const unsigned pa0 = t0.p_hi + hs, pb0 = t0.p_lo + hs, pc0 = t0.p_hi + ls, pd0 = t0.p_lo + ls;
+  const unsigned pa1 = t1.p_hi + hs, pb1 = t1.p_lo + hs, pc1 = t1.p_hi + ls, pd1 = t1.p_lo + ls;
 #pragma unroll
   for (int i = 0; i < BP_CH; ++i) {
-    const float a0 = lds_f32(t0.p_hi + hi_off), b0 = lds_f32(t0.p_lo + hi_off);
-    const float c0 = lds_f32(t0.p_hi + lo_off), d0 = lds_f32(t0.p_lo + lo_off);
-    const float a1 = lds_f32(t1.p_hi + hi_off), b1 = lds_f32(t1.p_lo + hi_off);
-    const float c1 = lds_f32(t1.p_hi + lo_off), d1 = lds_f32(t1.p_lo + lo_off);
+    const float a0 = lds_f32(pa0 + 4u * i), b0 = lds_f32(pb0 + 4u * i), c0 = lds_f32(pc0 + 4u * i), d0 = lds_f32(pd0 + 4u * i);
+    const float a1 = lds_f32(pa1 + 4u * i), b1 = lds_f32(pb1 + 4u * i), c1 = lds_f32(pc1 + 4u * i), d1 = lds_f32(pd1 + 4u * i);
     float v0 = ((a0 - b0) - c0) + d0, v1 = ((a1 - b1) - c1) + d1;
     if (MIXED) {
       if (!t0.left) v0 = a0 - c0;
       if (!t1.left) v1 = a1 - c1;
     }
-    if (ok0) *dst0 = v0 * t0.inv;
-    if (ok1) *dst1 = v1 * t1.inv;
-    dst0 += cols; dst1 += cols;
-    hi_off += colb; if (hi_off == ringb) hi_off = 0u;
-    lo_off += colb; if (lo_off == ringb) lo_off = 0u;
+    if (ok0) dst[0] = v0 * t0.inv;
+    if (ok1) dst[32] = v1 * t1.inv;
+    dst += cols;
   }
 }
 
@@ -420,7 +422,7 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
   __shared__ float inv_area[16][16];
   __shared__ __align__(8) unsigned long long bars[6];   // full[2], scanned[2], empty[2]
   float* S = bp_smem;                                  // [2][BP_R][spitch]
-  float* ring = bp_smem + 2 * BP_R * spitch;           // [BP_RING][cols]
+  float* ring = bp_smem + 2 * BP_R * spitch;           // [columns][BP_RP], see box_value_fw
   unsigned long long* full = bars;
   unsigned long long* scanned = bars + 2;
   unsigned long long* empty = bars + 4;
@@ -489,14 +491,18 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
   } else if ((warp & 3) != 1) {
     const int q = (warp - 2) - ((warp - 2) >> 2);       // column-warp index
     // this thread owns columns c0 and c0 + 32: consecutive lanes = consecutive columns, so every shared access of the warp
-    // is unit-stride (conflict-free) and every global store a full 128-byte segment
-    const int cq[2] = {q * 64 + lane, q * 64 + 32 + lane};
-    const bool okc[2] = {cq[0] < cols, cq[1] < cols};
-    const int cc[2] = {min(cq[0], cols - 1), min(cq[1], cols - 1)};   // clamped: loads stay in range, stores are predicated
+    // is conflict-free (row-major S: unit stride; column-major ring: stride BP_RP, odd) and every global store a full
+    // 128-byte segment. Columns >= cols (last warp) run on in-range garbage: S and the ring are padded to ncw * 64 columns,
+    // their results are never stored to global memory and no valid column taps them (jhi is clamped to cols - 1).
+    const int c0 = q * 64 + lane, c1 = c0 + 32;
+    const bool okc[2] = {c0 < cols, c1 < cols};
+    const int cc[2] = {min(c0, cols - 1), min(c1, cols - 1)};   // tap columns of the (unused) out-of-range outputs stay in range
     float* dstA = out0 + (size_t)plane * out_plane_stride;
     float* dstB = out1 + (size_t)plane * out_plane_stride;
     const unsigned ring_a = smem_u32(ring), S_a = smem_u32(S);
-    const unsigned colb = 4u * (unsigned)cols, spb = 4u * (unsigned)spitch;
+    const unsigned spb = 4u * (unsigned)spitch;
+    const unsigned rcol = ring_a + 4u * BP_RP * (unsigned)c0;        // ring column c0, row 0 (column c1: + 32 * BP_RP words)
+    constexpr unsigned RC1 = 4u * BP_RP * 32u;
     const BpTap tA0 = bp_tap(ring_a, cc[0], ha, cols), tA1 = bp_tap(ring_a, cc[1], ha, cols);
     const BpTap tB0 = bp_tap(ring_a, cc[0], hb, cols), tB1 = bp_tap(ring_a, cc[1], hb, cols);
     const bool mixed = q == 0;                          // only the first few columns lack a left tap
@@ -523,29 +529,40 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
         // steady state: a full sub-chunk whose BP_CH output rows (k0 - hm ...) are interior in the row direction
         const bool fast = k0 >= 2 * BP_CH && k0 + BP_CH < rows;
         {
-          const unsigned sa = S_a + (unsigned)((buf * BP_R + sub * BP_CH) * spitch + cc[0]) * 4u;
-          const unsigned d1 = (unsigned)(cc[1] - cc[0]) * 4u;
+          const unsigned sa = S_a + (unsigned)((buf * BP_R + sub * BP_CH) * spitch + c0) * 4u;
+          const int kr = k0 & (BP_RING - 1);                     // k0 % BP_CH == 0: no wrap inside the sub-chunk
+          const unsigned ra = rcol + 4u * (unsigned)kr;
           if (fast) {
-            const unsigned ra = ring_a + (unsigned)((k0 & (BP_RING - 1)) * cols + cc[0]) * 4u;   // k0 % BP_CH == 0: no wrap inside
             float v0[BP_CH], v1[BP_CH];
 #pragma unroll
-            for (int i = 0; i < BP_CH; ++i) { v0[i] = lds_f32(sa + i * spb); v1[i] = lds_f32(sa + i * spb + d1); }
+            for (int i = 0; i < BP_CH; ++i) { v0[i] = lds_f32(sa + i * spb); v1[i] = lds_f32(sa + i * spb + 128u); }
 #pragma unroll
             for (int i = 0; i < BP_CH; ++i) {                                            // column pass :59-65
               run0 = run0 + v0[i]; run1 = run1 + v1[i];
-              if (okc[0]) sts_f32(ra + i * colb, run0);
-              if (okc[1]) sts_f32(ra + i * colb + d1, run1);
+              v0[i] = run0; v1[i] = run1;
+              sts_f32(ra + 4u * i, run0);
+              sts_f32(ra + RC1 + 4u * i, run1);
+            }
+            if (kr == 0) {                                                               // rows 0..7 again as rows 32..39
+#pragma unroll
+              for (int i = 0; i < BP_CH; ++i) {
+                sts_f32(ra + 4u * (BP_RING + i), v0[i]);
+                sts_f32(ra + RC1 + 4u * (BP_RING + i), v1[i]);
+              }
             }
           } else {
 #pragma unroll
             for (int i = 0; i < BP_CH; ++i) {
               if (k0 + i < rows) {
-                const float x0 = lds_f32(sa + i * spb), x1 = lds_f32(sa + i * spb + d1);
+                const float x0 = lds_f32(sa + i * spb), x1 = lds_f32(sa + i * spb + 128u);
                 run0 = (k0 + i == 0) ? x0 : run0 + x0;
                 run1 = (k0 + i == 0) ? x1 : run1 + x1;
-                const unsigned ra = ring_a + (unsigned)(((k0 + i) & (BP_RING - 1)) * cols + cc[0]) * 4u;
-                if (okc[0]) sts_f32(ra, run0);
-                if (okc[1]) sts_f32(ra + d1, run1);
+                sts_f32(ra + 4u * i, run0);
+                sts_f32(ra + RC1 + 4u * i, run1);
+                if (kr == 0) {
+                  sts_f32(ra + 4u * (BP_RING + i), run0);
+                  sts_f32(ra + RC1 + 4u * (BP_RING + i), run1);
+                }
               }
             }
           }
@@ -558,24 +575,25 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
         const int olast = (k1 == rows) ? rows - 1 : k1 - 1 - hm;
         if (fast) {   // onext == k0 - hm here
           const int ro0 = k0 - hm;
-          float* dA = dstA + (size_t)ro0 * cols;
-          if (mixed) bp_box_rows<true>(tA0, tA1, ro0, ha, colb, dA + cq[0], dA + cq[1], okc[0], okc[1], cols);
-          else bp_box_rows<false>(tA0, tA1, ro0, ha, colb, dA + cq[0], dA + cq[1], okc[0], okc[1], cols);
+          float* dA = dstA + (size_t)ro0 * cols + c0;
+          if (mixed) bp_box_rows<true>(tA0, tA1, ro0, ha, dA, okc[0], okc[1], cols);
+          else bp_box_rows<false>(tA0, tA1, ro0, ha, dA, okc[0], okc[1], cols);
           if (dual) {
-            float* dB = dstB + (size_t)ro0 * cols;
-            if (mixed) bp_box_rows<true>(tB0, tB1, ro0, hb, colb, dB + cq[0], dB + cq[1], okc[0], okc[1], cols);
-            else bp_box_rows<false>(tB0, tB1, ro0, hb, colb, dB + cq[0], dB + cq[1], okc[0], okc[1], cols);
+            float* dB = dstB + (size_t)ro0 * cols + c0;
+            if (mixed) bp_box_rows<true>(tB0, tB1, ro0, hb, dB, okc[0], okc[1], cols);
+            else bp_box_rows<false>(tB0, tB1, ro0, hb, dB, okc[0], okc[1], cols);
           }
         } else {
           for (int ro = onext; ro <= olast; ++ro) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
               if (!okc[j]) continue;
-              dstA[(size_t)ro * cols + cq[j]] =
-                  box_value_fw(ring, cols, inv_area, ro, ha, rows, jhi[0][j], jlo[0][j], jlo[0][j] >= 0, ncol[0][j], j ? tA1.inv : tA0.inv);
+              const int cj = j ? c1 : c0;
+              dstA[(size_t)ro * cols + cj] =
+                  box_value_fw(ring, inv_area, ro, ha, rows, jhi[0][j], jlo[0][j], jlo[0][j] >= 0, ncol[0][j], j ? tA1.inv : tA0.inv);
               if (dual)
-                dstB[(size_t)ro * cols + cq[j]] =
-                    box_value_fw(ring, cols, inv_area, ro, hb, rows, jhi[1][j], jlo[1][j], jlo[1][j] >= 0, ncol[1][j], j ? tB1.inv : tB0.inv);
+                dstB[(size_t)ro * cols + cj] =
+                    box_value_fw(ring, inv_area, ro, hb, rows, jhi[1][j], jlo[1][j], jlo[1][j] >= 0, ncol[1][j], j ? tB1.inv : tB0.inv);
             }
           }
         }
@@ -586,12 +604,16 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
 }
 
 static int bp_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }   // (pitch / 4) odd: conflict-free 128-bit row accesses
-static size_t bp_smem_bytes(int cols) { return sizeof(float) * ((size_t)2 * BP_R * bp_spitch(cols) + (size_t)BP_RING * cols); }
 static int bp_threads(int cols) {   // smallest block whose column warps cover cols at two columns per thread
   const int need = (cols + 63) / 64;
   int w = 3;
   while (bp_ncw(w) < need) ++w;
   return w * 32;
+}
+// S: two chunk buffers [BP_R][spitch]; ring: [columns padded to 64][BP_RP] (+ 64 floats: out-of-range columns of the last
+// warp read S up to 63 floats past a row, which for the last row of buffer 1 is the start of the ring - in range either way)
+static size_t bp_smem_bytes(int cols) {
+  return sizeof(float) * ((size_t)2 * BP_R * bp_spitch(cols) + (size_t)((cols + 63) / 64 * 64) * BP_RP + 64);
 }
 static bool bp_supported(const rbv_ctx* c) {
   const int cols = c->P.cols;

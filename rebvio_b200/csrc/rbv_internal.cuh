@@ -143,6 +143,8 @@ struct rbv_ctx {
   int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
   int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
   void* prof;                       // ProfState* (rbv_api.cu)
+  int seq_fused;                    // inside rbv_track_g1/g2: k_rotate zeroes the lane counters, the stages skip k_zero_cnt
+  int seq_min_matches;              // rbv_track_g2: lanes whose directed-match count is below this skip regularise + Kalman (0 = off)
   void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed
 };
 
@@ -159,7 +161,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
   X(k_fill) X(k_rowscan) X(k_colbox) X(k_detect_flags) X(k_detect_scan) X(k_detect_emit) X(k_join) X(k_tune)       \
   X(k_dog_mag) X(k_field_build) X(k_rotate) X(k_quantile) X(k_tryvel_eval) X(k_tryvel_reduce) X(k_zero_cnt)        \
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
-  X(k_kalman) X(k_lm_init) X(k_gate_min_matches) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
+  X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4)
 enum {

@@ -263,8 +263,14 @@ int tr_build_field(rbv_ctx* c, rbv_map* map) {
 // ---------------------------------------------------------------------------------------------------------------
 // rotateKeylines: R * makeVector(float, float, double) is a float x double product accumulated in double
 // (TooN make_vector.hh:26, operators.hh:200-208) and rounded to float on assignment.
-__global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in, const __grid_constant__ DevParams P) {
+__global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in, int* zero_cnt,
+                         unsigned long long* zero_probes, const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (zero_cnt && idx == 0) {   // first kernel of a fused tracker sequence: reset the lane's match counters for the stages behind it
+    zero_cnt[b * CNT_STRIDE + CNT_FWD] = 0; zero_cnt[b * CNT_STRIDE + CNT_DIR] = 0;
+    zero_cnt[b * CNT_STRIDE + CNT_KF] = 0; zero_cnt[b * CNT_STRIDE + CNT_REG] = 0;
+    zero_probes[b] = 0ull;
+  }
   if (idx >= count[b]) return;
   const float* R = lane_in + (size_t)b * IN_STRIDE + IN_R;
   const size_t o = (size_t)b * P.kmax + idx;
@@ -302,14 +308,15 @@ __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const floa
 
 int tr_rotate(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  RBV_LAUNCH(c, k_rotate, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, P);
+  RBV_LAUNCH(c, k_rotate, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in,
+             c->seq_fused ? c->lane_cnt : nullptr, c->probes, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __restrict__ count, float percentile, int bins, int kmax,
-                                                  LMState* lm, float* lane_out, int to_lm) {
+                                                  LMState* lm, float* lane_out, int to_lm, const float* __restrict__ lane_in) {
   __shared__ int hist[RBV_MAX_QBINS];
   const int b = blockIdx.x, n = count[b];
   for (int i = threadIdx.x; i < bins; i += 256) hist[i] = 0;
@@ -329,14 +336,18 @@ __global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __res
       if ((float)a > lim) { out = (float)i * span / (float)bins + RBV_RHO_MIN; break; }    // :49-50
       a += hist[i];
     }
-    if (to_lm) lm[b].sigma_rho_min = out;
+    if (to_lm) {
+      lm[b].sigma_rho_min = out;
+      if (to_lm == 2)   // also the start velocity of Core::minimizeVel (what k_lm_init does for the stand-alone call)
+        for (int i = 0; i < 3; ++i) lm[b].vel[i] = lane_in[(size_t)b * IN_STRIDE + IN_VEL + i];
+    }
     lane_out[(size_t)b * OUT_STRIDE + OUT_Q] = out;
   }
 }
 
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
   if (bins < 1 || bins > RBV_MAX_QBINS) { rbv_set_error("quantile bins out of range"); return RBV_ERR_ARG; }
-  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (256), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm);
+  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (256), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm, c->lane_in);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -785,7 +796,8 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
     float gn[KPT], srho[KPT], rho[KPT];
     unsigned mt[KPT];
     float2 pi[KPT], g[KPT];
-    tv_ld<KPT>(Ko.gnorm + o, gn); tv_ld<KPT>(Ko.srho + o, srho); tv_ld<KPT>(Ko.rho + o, rho); tv_ld<KPT>(Ko.residual + o, res);
+    tv_ld<KPT>(Ko.gnorm + o, gn); tv_ld<KPT>(Ko.srho + o, srho); tv_ld<KPT>(Ko.rho + o, rho);
+    if (lm_call != 0) tv_ld<KPT>(Ko.residual + o, res);   // call 0 of minimizeVel starts from residuals = 0 (core.cpp:158): no fill pass, no read
     tv_ld<KPT>(Ko.matches + o, mt); tv_ld2<KPT>(Ko.pos_img + o, pi); tv_ld2<KPT>(Ko.grad + o, g);
     float w[KPT], rho_p[KPT], px[KPT], py[KPT], pxc[KPT], pyc[KPT];
     bool skip[KPT], penalty[KPT];
@@ -1059,7 +1071,7 @@ __global__ void k_zero_cnt(int* lane_cnt, int slot, unsigned long long* probes) 
 int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
   const DevParams& P = c->P;
   { int rc = rbv_fill32(c, c->fwd_head, 0xFFFFFFFFu, (size_t)P.lanes * P.kmax); if (rc != RBV_OK) return rc; }
-  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_FWD, nullptr);
+  if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_FWD, nullptr);
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
   RBV_LAUNCH(c, k_fwd_link, (g), (256), 0, old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax);
   RBV_LAUNCH(c, k_fwd_resolve, (g), (256), 0, old_map->k, new_map->k, new_map->count, c->fwd_head, c->fwd_next, c->lane_cnt, P.kmax);
@@ -1474,7 +1486,7 @@ __global__ void __launch_bounds__(256) k_directed(KeylineSoA Kn, const int* __re
 
 int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map) {
   const DevParams& P = c->P;
-  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_DIR, c->probes);
+  if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_DIR, c->probes);
   RBV_LAUNCH(c, k_directed, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, old_map->k, old_map->mask, c->lane_in, c->lane_cnt, c->probes, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
@@ -1483,8 +1495,9 @@ int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map) {
 // ---------------------------------------------------------------------------------------------------------------
 // regularize1Iter (edge_map.cpp:220-259): two phases like the reference (evaluate everything, then write).
 __global__ void __launch_bounds__(256) k_reg_eval(KeylineSoA K, const int* __restrict__ count, float* __restrict__ reg_r, float* __restrict__ reg_s,
-                                                  int* __restrict__ reg_set, int* __restrict__ lane_cnt, const __grid_constant__ DevParams P) {
+                                                  int* __restrict__ reg_set, int* lane_cnt, int min_matches, const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (min_matches > 0 && lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) return;   // rebvio.cpp:247-252: this lane stopped (whole block)
   int set = 0;
   const size_t base = (size_t)b * P.kmax;
   if (idx < count[b]) {
@@ -1517,9 +1530,10 @@ __global__ void __launch_bounds__(256) k_reg_eval(KeylineSoA K, const int* __res
 }
 
 __global__ void k_reg_apply(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ reg_r, const float* __restrict__ reg_s,
-                            const int* __restrict__ reg_set, int kmax) {
+                            const int* __restrict__ reg_set, const int* __restrict__ lane_cnt, int min_matches, int kmax) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count[b]) return;
+  if (min_matches > 0 && lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) return;
   const size_t o = (size_t)b * kmax + idx;
   if (reg_set[o]) { K.rho[o] = reg_r[o]; K.srho[o] = reg_s[o]; }                         // :252-257
 }
@@ -1527,9 +1541,9 @@ __global__ void k_reg_apply(KeylineSoA K, const int* __restrict__ count, const f
 int tr_regularize(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
-  RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_REG, nullptr);
-  RBV_LAUNCH(c, k_reg_eval, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, P);
-  RBV_LAUNCH(c, k_reg_apply, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, P.kmax);
+  if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_REG, nullptr);
+  RBV_LAUNCH(c, k_reg_eval, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, c->seq_fused ? c->seq_min_matches : 0, P);
+  RBV_LAUNCH(c, k_reg_apply, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, c->seq_fused ? c->seq_min_matches : 0, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -1537,9 +1551,10 @@ int tr_regularize(rbv_ctx* c, rbv_map* map) {
 // ---------------------------------------------------------------------------------------------------------------
 // updateInverseDepth + updateInverseDepthARLU (core.cpp:417-456): scalar EKF per matched keyline of the field map
 __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in,
-                                                const __grid_constant__ DevParams P) {
+                                                const int* __restrict__ lane_cnt, int min_matches, const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count[b]) return;
+  if (min_matches > 0 && lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) return;
   const size_t o = (size_t)b * P.kmax + idx;
   if (K.match_id[o] < 0) return;
   const float* vel = lane_in + (size_t)b * IN_STRIDE + IN_VEL;
@@ -1577,7 +1592,8 @@ __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restr
 
 int tr_kalman(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
-  RBV_LAUNCH(c, k_kalman, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, P);
+  RBV_LAUNCH(c, k_kalman, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, c->lane_cnt,
+             c->seq_fused ? c->seq_min_matches : 0, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

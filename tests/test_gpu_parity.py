@@ -141,14 +141,14 @@ def test_alternative_kernels_free_running(name, nf, tune):
     names = g.ctx.profile_launches()
     if tune is FUSED:
         assert names.get("k_field_band", 0) > 0 and names.get("k_field_build", 0) == 0
-        if spec.cam.cols <= 832:
+        if spec.cam.cols <= 768:
             assert names.get("k_boxpass", 0) > 0 and names.get("k_colbox", 0) == 0
     else:
         assert names.get("k_field_build", 0) > 0 and names.get("k_colbox", 0) > 0 and names.get("k_boxpass", 0) == 0
     g.close(); orc.close()
 
 
-@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (203, 832)])
+@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (203, 768), (35, 832)])
 def test_fused_box_pass_kernel_vs_oracle(rows, cols):
     """the fused createIntegralImage + average kernel on ragged row counts and every supported width class"""
     cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 200)
@@ -162,7 +162,8 @@ def test_fused_box_pass_kernel_vs_oracle(rows, cols):
     for s in range(2):
         for p in range(3):
             assert np.array_equal(H.bits(ctx.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img))), (s, p)
-    assert ctx.profile_launches().get("k_boxpass", 0) == 6
+    # wider than 768 columns the fused kernel's shared-memory ring does not fit and the split kernels take over
+    assert ctx.profile_launches().get("k_boxpass", 0) == (6 if cols <= 768 else 0)
     ctx.close(); orc.close()
 
 
