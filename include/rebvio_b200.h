@@ -138,8 +138,10 @@ int rbv_profile_read(rbv_ctx* ctx, int kid, double* total_ms, unsigned long long
 
 /* implementation choices, for tests and profiling; 0 = automatic (the default) everywhere.
  *   RBV_TUNE_FIELD: distance field — 1 = one thread per keyline with global atomics, 2 = shared-memory row bands
- *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel
+ *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel,
+ *                   3 = the shared-memory-resident pair for few planes (k_rowscan_lat + k_colbox_lat)
  *   RBV_TUNE_TRYVEL: keylines per thread of the FAST-mode tryVel kernel — 1, 2 or 4
+ *   RBV_TUNE_FIELD_ROWS: image rows per band of the shared-memory distance field (0 = automatic)
  *   RBV_TUNE_GRAPH: 1 = every kernel launched on the stream, 2 (default) = the kernel sequences of rbv_detect*, rbv_track_g1 and
  *                   rbv_track_g2 are captured once per (map pair) as CUDA graphs and replayed with one launch each
  *                   (one block per image plane, TMA-staged row chunks; needs cols % 4 == 0 and cols <= 832)        */
@@ -147,6 +149,7 @@ int rbv_profile_read(rbv_ctx* ctx, int kid, double* total_ms, unsigned long long
 #define RBV_TUNE_BOX 1
 #define RBV_TUNE_TRYVEL 2
 #define RBV_TUNE_GRAPH 3
+#define RBV_TUNE_FIELD_ROWS 4
 #define RBV_TUNE_COUNT 8
 int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
 

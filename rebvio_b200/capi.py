@@ -48,7 +48,7 @@ assert KEYLINE_DTYPE.itemsize == 84
 
 RBV_OK, RBV_ERR_ARG, RBV_ERR_CUDA, RBV_ERR_STATE = 0, 1, 2, 3
 REDUCE_FAST, REDUCE_ORDERED = 0, 1
-TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH = 0, 1, 2, 3   # rbv_set_tuning keys (0 = automatic; see the header for the values)
+TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH, TUNE_FIELD_ROWS = 0, 1, 2, 3, 4   # rbv_set_tuning keys (0 = automatic; see the header for the values)
 
 vp = C.c_void_p
 _SIG = {

@@ -338,7 +338,7 @@ extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
   return RBV_OK;
 }
 extern "C" int rbv_set_tuning(rbv_ctx* c, int key, int value) {
-  if (!c || key < 0 || key >= RBV_TUNE_COUNT || value < 0 || value > 8) return RBV_ERR_ARG;
+  if (!c || key < 0 || key >= RBV_TUNE_COUNT || value < 0 || value > 64) return RBV_ERR_ARG;
   rbv_graphs_clear(c, nullptr);
   c->tune[key] = value;
   return RBV_OK;

@@ -407,6 +407,155 @@ __global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ row
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Latency-optimised box pass for FEW planes (single stream). With one or two planes the split kernels above are bound by
+// global-load latency: a warp fetches one 32-column tile per round trip, 24 round trips per row block (k_rowscan4 22 us,
+// k_colbox 41 us per launch at 752x480) although the dependent add chains themselves are only 752 resp. 480 adds long
+// (~1.5 us). Here a block brings its WHOLE working set into shared memory with one round trip - 32 full rows by TMA bulk
+// copies (row pass), a 32-column strip of all rows by 4-byte cp.async (column pass) - then walks the chains out of shared
+// memory, and every thread of the block shares the load, box and store work. Same arithmetic, statement by statement.
+#define RL_R 32
+#define RL_TPB 256
+__global__ void __launch_bounds__(RL_TPB) k_rowscan_lat(const float* __restrict__ in, float* __restrict__ out, int rows, int cols,
+                                                        size_t in_plane_stride, size_t out_plane_stride, int spitch) {
+  extern __shared__ __align__(128) float rl_smem[];   // [RL_R][spitch], (spitch / 4) odd: conflict-free 128-bit row walks
+  __shared__ __align__(8) unsigned long long rl_bar;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r0 = blockIdx.x * RL_R, nr = min(RL_R, rows - r0);
+  const float* src = in + (size_t)blockIdx.y * in_plane_stride + (size_t)r0 * cols;
+  float* dst = out + (size_t)blockIdx.y * out_plane_stride + (size_t)r0 * cols;
+  const int n4 = cols >> 2;
+  if (tid == 0) {
+    mbar_init(&rl_bar, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 0) {
+    if (lane == 0) mbar_arrive_expect_tx(&rl_bar, (unsigned)(nr * cols * 4));
+    __syncwarp();
+    if (lane < nr) bulk_g2s(rl_smem + (size_t)lane * spitch, src + (size_t)lane * cols, (unsigned)(cols * 4), &rl_bar);
+    mbar_wait(&rl_bar, 0u);
+    if (lane < nr) {                                                                     // scale_space.cpp:50-57, lane = row
+      float4* row = reinterpret_cast<float4*>(rl_smem + (size_t)lane * spitch);
+      float carry = 0.0f;
+      float4 a[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = (i < n4) ? row[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int c4 = 0; c4 < n4; c4 += 4) {
+        float4 nx[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) nx[i] = (c4 + 4 + i < n4) ? row[c4 + 4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        bp_scan4(a[0], carry, c4 == 0);
+        bp_scan4(a[1], carry, false);
+        bp_scan4(a[2], carry, false);
+        bp_scan4(a[3], carry, false);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (c4 + i < n4) row[c4 + i] = a[i];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = nx[i];
+      }
+    }
+  }
+  __syncthreads();
+  for (int r = warp; r < nr; r += RL_TPB / 32) {
+    const float4* srow = reinterpret_cast<const float4*>(rl_smem + (size_t)r * spitch);
+    float4* drow = reinterpret_cast<float4*>(dst + (size_t)r * cols);
+    for (int c4 = lane; c4 < n4; c4 += 32) drow[c4] = srow[c4];
+  }
+}
+
+// one output value from a linear [rows][tw] tile of the integral image (same regions and association orders as box_value)
+__device__ __forceinline__ float box_value_lin(const float* __restrict__ tile, int tw, const float (*inv_area)[16], int ro, int h, int rows,
+                                               int jhi, int jlo, bool left, int ncol, float inv_mid) {
+  const int rlo = ro - h - 1;
+  if (rlo >= 0 && ro + h < rows) {
+    const float* hi = tile + (ro + h) * tw;
+    const float* lo = tile + rlo * tw;
+    const float v = left ? ((hi[jhi] - hi[jlo]) - lo[jhi]) + lo[jlo] : hi[jhi] - lo[jhi];   // :99 / :94
+    return v * inv_mid;
+  }
+  const int rhi = min(ro + h, rows - 1);
+  const float* hi = tile + rhi * tw;
+  float v;
+  if (rlo < 0) {
+    v = left ? hi[jhi] - hi[jlo] : hi[jhi];                                             // :78-84
+  } else {
+    const float* lo = tile + rlo * tw;
+    v = left ? ((hi[jhi] - lo[jhi]) - hi[jlo]) + lo[jlo] : hi[jhi] - lo[jhi];           // :119,:124 / :114
+  }
+  return v * inv_area[rhi - max(rlo, -1)][ncol];
+}
+
+#define CL_W 32
+#define CL_TPB 256
+__global__ void __launch_bounds__(CL_TPB) k_colbox_lat(const float* __restrict__ rowsum, float* __restrict__ out0, float* __restrict__ out1,
+                                                       int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
+                                                       int d1, int dual, int hmax) {
+  extern __shared__ __align__(16) float cl_tile[];   // [rows][tw]: image columns c0 - hmax - 1 .. c0 + CL_W - 1 + hmax
+  __shared__ float inv_area[16][16];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int plane = blockIdx.y;
+  const int z = dual ? 0 : plane % nz;
+  const int ha = (z ? d1 : d0) / 2;
+  const int hb = dual ? d1 / 2 : ha;
+  const int tw = CL_W + 2 * hmax + 1;                 // odd: lane = column accesses are conflict-free
+  const int c0 = blockIdx.x * CL_W, cbase = c0 - hmax - 1;
+  const float* src = rowsum + (size_t)plane * in_plane_stride;
+  for (int i = tid; i < 256; i += CL_TPB) {
+    const int a = i / 16, b = i % 16;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171
+  }
+  {  // the whole strip in one round trip: 4-byte cp.async straight into shared memory, all of a thread's copies in flight
+    const int total = rows * tw, q = CL_TPB / tw, rem = CL_TPB % tw;
+    int r = tid / tw, j = tid % tw;
+    const unsigned tile_a = smem_u32(cl_tile);
+    for (int i = tid; i < total; i += CL_TPB) {
+      const int col = cbase + j;
+      if (col >= 0 && col < cols)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(tile_a + 4u * (unsigned)(r * tw + j)), "l"(src + (size_t)r * cols + col) : "memory");
+      r += q; j += rem;
+      if (j >= tw) { j -= tw; ++r; }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid < tw) {                                      // column pass :59-65, thread = column of the strip
+    const int col = cbase + tid;
+    if (col >= 0 && col < cols) {
+      float* p = cl_tile + tid;
+      float run = p[0];
+      int r = 1;
+      for (; r + 8 <= rows; r += 8) {
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = p[(r + i) * tw];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { run = run + v[i]; p[(r + i) * tw] = run; }
+      }
+      for (; r < rows; ++r) { run = run + p[r * tw]; p[r * tw] = run; }
+    }
+  }
+  __syncthreads();
+  const int col = c0 + lane;
+  if (col >= cols) return;
+  int jhi[2], jlo[2], ncol[2];
+  float inv_mid[2];
+  const int hh[2] = {ha, hb};
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    const int chi = min(col + hh[w], cols - 1), clo = col - hh[w] - 1;
+    jhi[w] = chi - cbase; jlo[w] = max(clo, 0) - cbase; ncol[w] = chi - max(clo, -1);
+    inv_mid[w] = (float)(1.0 / (double)((float)(2 * hh[w] + 1) * (float)ncol[w]));     // interior-row divisor (:72 / :168)
+  }
+  const bool leftA = col - ha - 1 >= 0, leftB = col - hb - 1 >= 0;
+  float* dA = out0 + (size_t)plane * out_plane_stride + col;
+  float* dB = out1 + (size_t)plane * out_plane_stride + col;
+  for (int ro = warp; ro < rows; ro += CL_TPB / 32) {
+    dA[(size_t)ro * cols] = box_value_lin(cl_tile, tw, inv_area, ro, ha, rows, jhi[0], jlo[0], leftA, ncol[0], inv_mid[0]);
+    if (dual) dB[(size_t)ro * cols] = box_value_lin(cl_tile, tw, inv_area, ro, hb, rows, jhi[1], jlo[1], leftB, ncol[1], inv_mid[1]);
+  }
+}
+
 #define BP_MAX_THREADS 640
 // column warps among `nwarps` warps: all but warp 0 (producer), warp 1 (row pass) and warps 5, 9, 13, ... (left idle)
 __host__ __device__ inline int bp_ncw(int nwarps) {
@@ -621,7 +770,7 @@ static bool bp_supported(const rbv_ctx* c) {
 }
 static bool bp_use(const rbv_ctx* c, const void* src) {
   if (!bp_supported(c) || ((uintptr_t)src & 15) != 0) return false;
-  if (c->tune[RBV_TUNE_BOX] == 1) return false;
+  if (c->tune[RBV_TUNE_BOX] == 1 || c->tune[RBV_TUNE_BOX] == 3) return false;
   if (c->tune[RBV_TUNE_BOX] == 2) return true;
   return c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
 }
@@ -634,9 +783,39 @@ static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int 
   return RBV_OK;
 }
 
+// ---- latency-optimised pair (k_rowscan_lat / k_colbox_lat) ----
+static int lat_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }
+static int lat_hmax(const rbv_ctx* c) {
+  int m = 0;
+  for (int s2 = 0; s2 < 2; ++s2)
+    for (int p = 0; p < 3; ++p) m = c->widths[s2][p] / 2 > m ? c->widths[s2][p] / 2 : m;
+  return m;
+}
+static size_t lat_row_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)RL_R * lat_spitch(c->P.cols); }
+static size_t lat_col_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)c->P.rows * (CL_W + 2 * lat_hmax(c) + 1); }
+static bool lat_use(const rbv_ctx* c, const void* src) {
+  const bool fits = (c->P.cols & 3) == 0 && lat_row_smem(c) <= 200 * 1024 && lat_col_smem(c) <= 200 * 1024 && lat_hmax(c) <= 7 &&
+                    ((uintptr_t)src & 15) == 0;
+  if (!fits || c->tune[RBV_TUNE_BOX] == 1 || c->tune[RBV_TUNE_BOX] == 2) return false;
+  if (c->tune[RBV_TUNE_BOX] == 3) return true;
+  return true;   // automatic: the fused kernel was already chosen above for many lanes; this beats the split pair otherwise
+}
+static void lat_rowscan(rbv_ctx* c, const float* in, float* out, int planes) {
+  const size_t N = (size_t)c->P.npix;
+  RBV_LAUNCH(c, k_rowscan_lat, (dim3((c->P.rows + RL_R - 1) / RL_R, planes)), (RL_TPB), lat_row_smem(c), in, out, c->P.rows, c->P.cols, N, N,
+             lat_spitch(c->P.cols));
+}
+static void lat_colbox(rbv_ctx* c, const float* rowsum, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
+                       int d0, int d1, int dual) {
+  RBV_LAUNCH(c, k_colbox_lat, (dim3((c->P.cols + CL_W - 1) / CL_W, planes)), (CL_TPB), lat_col_smem(c), rowsum, out0, out1, c->P.rows,
+             c->P.cols, in_stride, out_stride, nz, d0, d1, dual, lat_hmax(c));
+}
+
 int fe_init(rbv_ctx* c) {
   (void)c;   // the current device is the context's; the limit is per device and shared by every context on it
   RBV_CUDA(cudaFuncSetAttribute(k_boxpass, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+  RBV_CUDA(cudaFuncSetAttribute(k_rowscan_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  RBV_CUDA(cudaFuncSetAttribute(k_colbox_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   return RBV_OK;
 }
 
@@ -661,6 +840,20 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
     if (part != 1) {
       bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
       bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+    }
+    RBV_CUDA(cudaGetLastError());
+    return RBV_OK;
+  }
+  if (lat_use(c, d_img)) {   // few planes: whole-working-set-in-shared-memory kernels (one load round trip per block)
+    if (part != 2) lat_rowscan(c, d_img, c->rowsum, B);
+    if (part == 1) { RBV_CUDA(cudaGetLastError()); return RBV_OK; }
+    lat_colbox(c, c->rowsum, c->bufA, c->bufA + N, B, N, 2 * N, 1, c->widths[0][0], c->widths[1][0], 1);
+    float* src = c->bufA;
+    float* dst = c->bufB;
+    for (int p = 1; p < 3; ++p) {
+      lat_rowscan(c, src, c->rowsum, 2 * B);
+      lat_colbox(c, c->rowsum, dst, dst, 2 * B, N, N, 2, c->widths[0][p], c->widths[1][p], 0);
+      float* t = src; src = dst; dst = t;
     }
     RBV_CUDA(cudaGetLastError());
     return RBV_OK;
@@ -697,6 +890,12 @@ int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float*
   const int d = c->widths[scale][pass];
   if (c->tune[RBV_TUNE_BOX] == 2 && bp_use(c, d_in)) {
     bp_launch(c, d_in, d_out, d_out, 1, N, N, 1, d, d, 0);
+    RBV_CUDA(cudaGetLastError());
+    return RBV_OK;
+  }
+  if (c->tune[RBV_TUNE_BOX] == 3 && lat_use(c, d_in)) {
+    lat_rowscan(c, d_in, c->rowsum, 1);
+    lat_colbox(c, c->rowsum, d_out, d_out, 1, N, N, 1, d, d, 0);
     RBV_CUDA(cudaGetLastError());
     return RBV_OK;
   }

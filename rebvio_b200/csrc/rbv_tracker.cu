@@ -210,10 +210,14 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
 static int field_band_rows(const rbv_ctx* c) {
   const int by_smem = (90 * 1024) / (c->P.cols * 4);   // + ~23 KB of static tables: two blocks fit the 227 KB of an SM
   int h = by_smem > 32 ? 32 : by_smem;
+  if (c->tune[RBV_TUNE_FIELD_ROWS] > 0) return c->tune[RBV_TUNE_FIELD_ROWS] < h ? c->tune[RBV_TUNE_FIELD_ROWS] : h;
   if (h >= 16) {   // prefer a row count that divides the image: no short last band
     for (int d = h; d >= h - 4 && d >= 16; --d)
-      if (c->P.rows % d == 0) return d;
+      if (c->P.rows % d == 0) { h = d; break; }
   }
+  // few lanes: the grid (bands x lanes) should still cover the 148 SMs; lower bands repeat the keyline scan more often but
+  // a single stream is bound by the longest block, not by total work
+  while (h > 8 && ((c->P.rows + h - 1) / h) * c->P.lanes < 148) h = (h + 1) / 2;
   return h;
 }
 
@@ -246,7 +250,7 @@ int tr_init(rbv_ctx* c) {
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   const int H = field_band_rows(c);
-  const bool band = (c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 16)) && P.field_nr <= FB_G * FB_MAXI;
+  const bool band = (c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 8)) && P.field_nr <= FB_G * FB_MAXI;
   if (band && H >= 1) {
     const size_t smem = (size_t)H * P.cols * 4;
     RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, map->k, map->count, map->threshold, c->field, P, H);
@@ -315,14 +319,14 @@ int tr_rotate(rbv_ctx* c, rbv_map* map) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __restrict__ count, float percentile, int bins, int kmax,
+__global__ void __launch_bounds__(1024) k_quantile(KeylineSoA K, const int* __restrict__ count, float percentile, int bins, int kmax,
                                                   LMState* lm, float* lane_out, int to_lm, const float* __restrict__ lane_in) {
   __shared__ int hist[RBV_MAX_QBINS];
   const int b = blockIdx.x, n = count[b];
-  for (int i = threadIdx.x; i < bins; i += 256) hist[i] = 0;
+  for (int i = threadIdx.x; i < bins; i += blockDim.x) hist[i] = 0;
   __syncthreads();
   const float span = RBV_RHO_MAX - RBV_RHO_MIN;
-  for (int i = threadIdx.x; i < n; i += 256) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
     int q = rbv_f2i((float)bins * (K.srho[(size_t)b * kmax + i] - RBV_RHO_MIN) / span);   // edge_map.cpp:42
     q = q > bins - 1 ? bins - 1 : q;
     q = q < 0 ? 0 : q;
@@ -347,7 +351,7 @@ __global__ void __launch_bounds__(256) k_quantile(KeylineSoA K, const int* __res
 
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
   if (bins < 1 || bins > RBV_MAX_QBINS) { rbv_set_error("quantile bins out of range"); return RBV_ERR_ARG; }
-  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (256), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm, c->lane_in);
+  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (1024), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm, c->lane_in);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

@@ -19,6 +19,8 @@ def kernel_bytes(name, N, K, B, planes=1, P=20.0, words=0):
         "k_rowscan": 8.0 * N * planes,
         "k_rowscan4": 8.0 * N * planes,
         "k_colbox": 8.0 * N * planes,
+        "k_rowscan_lat": 8.0 * N * planes,
+        "k_colbox_lat": 8.0 * N * planes,
         "k_detect_flags": 12.0 * N,          # read both scales, write the id mask (DoG / magnitude never reach memory)
         "k_detect_scan": 0.0,
         "k_detect_emit": 84.0 * K,           # one KeyLine per keyline

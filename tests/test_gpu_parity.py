@@ -26,6 +26,7 @@ def _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED, tune=None):
 # both implementations of the two stages that have an alternative kernel (include/rebvio_b200.h, rbv_set_tuning)
 SPLIT = {capi.TUNE_BOX: 1, capi.TUNE_FIELD: 1}
 FUSED = {capi.TUNE_BOX: 2, capi.TUNE_FIELD: 2}
+LAT = {capi.TUNE_BOX: 3, capi.TUNE_FIELD: 2}
 
 
 @pytest.mark.parametrize("name", common.GOLDEN_CASES)
@@ -125,7 +126,7 @@ def test_try_vel_fast_vs_ordered_indices_and_sums(kpt):
 
 
 @pytest.mark.parametrize("name,nf,tune", [("C2", 3, FUSED), ("C2", 3, SPLIT), ("C1", 3, FUSED), ("C5:320x240", 4, FUSED),
-                                          ("C3", 2, FUSED)])
+                                          ("C3", 2, FUSED), ("C2", 3, LAT), ("C3", 2, LAT)])
 def test_alternative_kernels_free_running(name, nf, tune):
     """the fused box-pass kernel (TMA-staged row chunks) and the shared-memory band distance field, forced on, and the
     split / global-atomic forms, forced on: whole chain bit-exact against the oracle either way (C3 is too wide for the
@@ -139,7 +140,9 @@ def test_alternative_kernels_free_running(name, nf, tune):
     rep = H.report(T, G)
     assert H.dirty(rep) == []
     names = g.ctx.profile_launches()
-    if tune is FUSED:
+    if tune is LAT:
+        assert names.get("k_colbox_lat", 0) > 0 and names.get("k_colbox", 0) == 0 and names.get("k_boxpass", 0) == 0
+    elif tune is FUSED:
         assert names.get("k_field_band", 0) > 0 and names.get("k_field_build", 0) == 0
         if spec.cam.cols <= 768:
             assert names.get("k_boxpass", 0) > 0 and names.get("k_colbox", 0) == 0
@@ -182,6 +185,24 @@ def test_box_pass_kernel_vs_oracle(rows, cols):
     for s in range(2):
         for p in range(3):
             assert np.array_equal(H.bits(ctx.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img))), (s, p)
+    ctx.close(); orc.close()
+
+
+@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (35, 832), (720, 1280)])
+def test_latency_box_pass_kernels_vs_oracle(rows, cols):
+    """k_rowscan_lat + k_colbox_lat (the shared-memory-resident box pass used with few lanes), ragged and full sizes"""
+    cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 200)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
+    ctx = host.Context(conv(capi.Camera, cfg[0]), conv(capi.DetectorCfg, cfg[1]), conv(capi.MapCfg, cfg[2]), conv(capi.CoreCfg, cfg[3]))
+    ctx.set_tuning(capi.TUNE_BOX, 3)
+    rng = np.random.RandomState(rows * 5 + cols)
+    img = rng.randint(0, 256, (rows, cols)).astype(np.float32) * np.float32(3.0)
+    ctx.profile_reset()
+    for s in range(2):
+        for p in range(3):
+            assert np.array_equal(H.bits(ctx.box_pass(s, p, img)), H.bits(orc.box_pass(s, p, img))), (s, p)
+    assert ctx.profile_launches().get("k_colbox_lat", 0) == 6 and ctx.profile_launches().get("k_rowscan_lat", 0) == 6
     ctx.close(); orc.close()
 
 
