@@ -245,6 +245,23 @@ int rbv_track_g2(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const float* 
                  const float* PV9, const float* Rgva9, float max_radius, int min_matches, int* n_matches,
                  int* kf_matches);
 
+/* Host block between the two halves, visual-only subset of rebvio.cpp:183-233 (gyro prior and IMU filters switched off;
+ * those stay in the reference's own host code): R0 = exp(X[3:6]) (rebvio.cpp:194-196),
+ * V = R0 Vg + X[0:3], P_V = inv(Wx)[0:3][0:3] (rebvio.cpp:198-200), Rgva = (R0 R^T)^T. Pure host arithmetic in double,
+ * no device access; all arrays [lanes][...]. A singular Wx gives P_V = 1e10 I.                                        */
+int rbv_visual_fusion(int lanes, const float* R9, const float* Vg3, const float* Wx36, const float* X6, float* R0_9,
+                      float* V3, float* PV9, float* Rgva9);
+
+/* One tracker frame in one call: rbv_track_g1, rbv_visual_fusion, rbv_track_g2 (what a replay driver without IMU
+ * filters does per frame). R9 = rotation of the camera since the previous frame, [lanes][9] row-major (the call
+ * rotates the old map by its transpose, rebvio.cpp:165). Outputs (any may be NULL): Vg3, PVg9 (minimizeVel),
+ * Wx36, X6, ok (extRotVel), V3 (fused velocity), n_matches / kf_matches (directedMatch), n_keylines_new /
+ * auto_threshold_new (size and tuned threshold of new_map, so that rbv_detect* can be called without outputs and the
+ * frame needs no device synchronisation of its own for them).                                                      */
+int rbv_track(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const float* R9, float max_radius, int min_matches,
+              float* Vg3, float* PVg9, float* Wx36, float* X6, int* ok, float* V3, int* n_matches, int* kf_matches,
+              int* n_keylines_new, float* auto_threshold_new);
+
 /* ---- host mirror (EdgeMap::keylines(), operator[], mask(), size(), threshold(); edge_map.hpp:40-75) ---- */
 
 int rbv_map_size(rbv_ctx* ctx, rbv_map* map, int* n_keylines /*[B]*/);

@@ -458,8 +458,8 @@ enum { GK_DETECT = 1, GK_TRACK1 = 2, GK_TRACK2 = 3 };
 // scope of a fused tracker sequence (see rbv_ctx::seq_fused)
 struct SeqFused {
   rbv_ctx* c;
-  SeqFused(rbv_ctx* ctx, int min_matches) : c(ctx) { c->seq_fused = 1; c->seq_min_matches = min_matches; }
-  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; }
+  SeqFused(rbv_ctx* ctx, int min_matches, rbv_map* new_map = nullptr) : c(ctx) { c->seq_fused = 1; c->seq_min_matches = min_matches; c->seq_new = new_map; }
+  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; c->seq_new = nullptr; }
 };
 template <class Body>
 static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int flag, Body body) {
@@ -839,7 +839,7 @@ extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   put_directed(c, h, V3, PV9, Rgva9, max_radius);
   TRY(stage_commit(c, slot));
   TRY(run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
-    SeqFused fused(c, min_matches);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
+    SeqFused fused(c, min_matches, new_map);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
     TRY(tr_rotate(c, old_map));
     TRY(tr_directed_match(c, new_map, old_map));
     TRY(tr_regularize(c, new_map));
@@ -849,6 +849,105 @@ extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   for (int b = 0; b < c->P.lanes; ++b) {
     if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
     if (kf_matches) kf_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_KF];
+  }
+  return RBV_OK;
+}
+
+// ---- host block between the halves + whole-frame call ----
+static void so3_exp_d(const double w[3], double R[9]) {   // Rodrigues; TooN::SO3::exp equivalent to double rounding
+  const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = sqrt(th2);
+  double a, b;
+  if (th < 1e-12) { a = 1.0; b = 0.0; }
+  else { a = sin(th) / th; b = (1.0 - cos(th)) / th2; }
+  const double K[9] = {0.0, -w[2], w[1], w[2], 0.0, -w[0], -w[1], w[0], 0.0};
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      double kk = 0.0;
+      for (int k = 0; k < 3; ++k) kk += K[i * 3 + k] * K[k * 3 + j];
+      R[i * 3 + j] = (i == j ? 1.0 : 0.0) + a * K[i * 3 + j] + b * kk;
+    }
+}
+static bool inv6_d(const double* A, double* inv) {   // Gauss-Jordan with partial pivoting
+  double M[6][12];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { M[i][j] = A[i * 6 + j]; M[i][6 + j] = i == j ? 1.0 : 0.0; }
+  for (int c2 = 0; c2 < 6; ++c2) {
+    int piv = c2;
+    for (int r = c2 + 1; r < 6; ++r) if (fabs(M[r][c2]) > fabs(M[piv][c2])) piv = r;
+    if (!(fabs(M[piv][c2]) > 0.0) || !isfinite(M[piv][c2])) return false;
+    if (piv != c2) for (int j = 0; j < 12; ++j) { const double t = M[c2][j]; M[c2][j] = M[piv][j]; M[piv][j] = t; }
+    const double d = 1.0 / M[c2][c2];
+    for (int j = 0; j < 12; ++j) M[c2][j] *= d;
+    for (int r = 0; r < 6; ++r) {
+      if (r == c2) continue;
+      const double f = M[r][c2];
+      if (f != 0.0) for (int j = 0; j < 12; ++j) M[r][j] -= f * M[c2][j];
+    }
+  }
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) inv[i * 6 + j] = M[i][6 + j];
+  return true;
+}
+extern "C" int rbv_visual_fusion(int lanes, const float* R9, const float* Vg3, const float* Wx36, const float* X6, float* R0_9, float* V3,
+                                 float* PV9, float* Rgva9) {
+  if (lanes < 1 || !R9 || !Vg3 || !Wx36 || !X6 || !R0_9 || !V3 || !PV9 || !Rgva9) { rbv_set_error("rbv_visual_fusion: null argument"); return RBV_ERR_ARG; }
+  for (int b = 0; b < lanes; ++b) {
+    const float* X = X6 + b * 6;
+    const double w[3] = {X[3], X[4], X[5]};
+    double R0[9], A[36], Ai[36];
+    so3_exp_d(w, R0);
+    for (int i = 0; i < 3; ++i) {
+      double v = 0.0;
+      for (int k = 0; k < 3; ++k) v += R0[i * 3 + k] * (double)Vg3[b * 3 + k];
+      V3[b * 3 + i] = (float)(v + (double)X[i]);
+    }
+    for (int i = 0; i < 36; ++i) A[i] = Wx36[b * 36 + i];
+    const bool ok = inv6_d(A, Ai);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) PV9[b * 9 + i * 3 + j] = ok ? (float)Ai[i * 6 + j] : (i == j ? 1e10f : 0.0f);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        double t = 0.0;   // (R0 R^T)[j][i] -> Rgva[i][j]
+        for (int k = 0; k < 3; ++k) t += R0[j * 3 + k] * (double)R9[b * 9 + i * 3 + k];
+        Rgva9[b * 9 + i * 3 + j] = (float)t;
+        R0_9[b * 9 + i * 3 + j] = (float)R0[i * 3 + j];
+      }
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_track(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R9, float max_radius, int min_matches, float* Vg3,
+                         float* PVg9, float* Wx36, float* X6, int* ok, float* V3, int* n_matches, int* kf_matches, int* n_keylines_new,
+                         float* auto_threshold_new) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map || !R9) return RBV_ERR_ARG;
+  const int B = c->P.lanes;
+  std::vector<float> buf((size_t)B * (9 + 3 + 9 + 36 + 6 + 9 + 3 + 9 + 9));
+  float* Rt = buf.data();
+  float* vg = Rt + (size_t)B * 9;
+  float* pvg = vg + (size_t)B * 3;
+  float* wx = pvg + (size_t)B * 9;
+  float* x = wx + (size_t)B * 36;
+  float* r0 = x + (size_t)B * 6;
+  float* v = r0 + (size_t)B * 9;
+  float* pv = v + (size_t)B * 3;
+  float* rg = pv + (size_t)B * 9;
+  std::vector<int> okv((size_t)B);
+  for (int b = 0; b < B; ++b)
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) Rt[b * 9 + i * 3 + j] = R9[b * 9 + j * 3 + i];           // old->rotateKeylines(R.T()), rebvio.cpp:165
+  TRY(rbv_track_g1(c, old_map, new_map, Rt, vg, pvg, wx, x, okv.data()));
+  TRY(rbv_visual_fusion(B, R9, vg, wx, x, r0, v, pv, rg));
+  TRY(rbv_track_g2(c, old_map, new_map, r0, v, pv, rg, max_radius, min_matches, n_matches, kf_matches));
+  if (Vg3) memcpy(Vg3, vg, sizeof(float) * B * 3);
+  if (PVg9) memcpy(PVg9, pvg, sizeof(float) * B * 9);
+  if (Wx36) memcpy(Wx36, wx, sizeof(float) * B * 36);
+  if (X6) memcpy(X6, x, sizeof(float) * B * 6);
+  if (ok) memcpy(ok, okv.data(), sizeof(int) * B);
+  if (V3) memcpy(V3, v, sizeof(float) * B * 3);
+  for (int b = 0; b < B; ++b) {   // rode home with the match counters (k_rotate of the second half)
+    if (n_keylines_new) n_keylines_new[b] = c->h_cnt[b * CNT_STRIDE + CNT_NKEY];
+    if (auto_threshold_new) memcpy(auto_threshold_new + b, c->h_cnt + b * CNT_STRIDE + CNT_ATHR, sizeof(float));
   }
   return RBV_OK;
 }

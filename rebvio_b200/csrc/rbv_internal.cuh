@@ -144,6 +144,7 @@ struct rbv_ctx {
   int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
   void* prof;                       // ProfState* (rbv_api.cu)
   int seq_fused;                    // inside rbv_track_g1/g2: k_rotate zeroes the lane counters, the stages skip k_zero_cnt
+  rbv_map* seq_new;                 // rbv_track_g2: map whose keyline count / auto threshold ride home in lane_cnt slots 4, 5
   int seq_min_matches;              // rbv_track_g2: lanes whose directed-match count is below this skip regularise + Kalman (0 = off)
   void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed
 };
@@ -153,7 +154,7 @@ enum { IN_R = 0, IN_VEL = 9, IN_RVEL = 12, IN_RBACK = 21, IN_SRMIN = 30, IN_MAXR
 // lane_out slots
 enum { OUT_JTJ = 0, OUT_JTF = 9, OUT_SCORE = 12, OUT_WX = 16, OUT_X = 52, OUT_OK = 58, OUT_Q = 59, OUT_STRIDE = 64 };
 // lane_cnt slots
-enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_STRIDE = 8 };
+enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR = 5, CNT_STRIDE = 8 };
 
 // ---- kernel registry: every launch goes through RBV_LAUNCH so that launches are counted per kernel and can be
 // bracketed with CUDA events on the launching stream (rbv_profile_*; bench.py's roofline numbers come from there) ----

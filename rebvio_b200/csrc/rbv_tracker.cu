@@ -268,12 +268,17 @@ int tr_build_field(rbv_ctx* c, rbv_map* map) {
 // rotateKeylines: R * makeVector(float, float, double) is a float x double product accumulated in double
 // (TooN make_vector.hh:26, operators.hh:200-208) and rounded to float on assignment.
 __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in, int* zero_cnt,
-                         unsigned long long* zero_probes, const __grid_constant__ DevParams P) {
+                         unsigned long long* zero_probes, const int* __restrict__ nkey_src, const float* __restrict__ athr_src,
+                         const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (zero_cnt && idx == 0) {   // first kernel of a fused tracker sequence: reset the lane's match counters for the stages behind it
     zero_cnt[b * CNT_STRIDE + CNT_FWD] = 0; zero_cnt[b * CNT_STRIDE + CNT_DIR] = 0;
     zero_cnt[b * CNT_STRIDE + CNT_KF] = 0; zero_cnt[b * CNT_STRIDE + CNT_REG] = 0;
     zero_probes[b] = 0ull;
+    if (nkey_src) {   // the new map's keyline count and auto threshold travel with the counters (one D2H for the frame)
+      zero_cnt[b * CNT_STRIDE + CNT_NKEY] = nkey_src[b];
+      zero_cnt[b * CNT_STRIDE + CNT_ATHR] = __float_as_int(athr_src[b]);
+    }
   }
   if (idx >= count[b]) return;
   const float* R = lane_in + (size_t)b * IN_STRIDE + IN_R;
@@ -313,7 +318,8 @@ __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const floa
 int tr_rotate(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   RBV_LAUNCH(c, k_rotate, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in,
-             c->seq_fused ? c->lane_cnt : nullptr, c->probes, P);
+             c->seq_fused ? c->lane_cnt : nullptr, c->probes, (c->seq_fused && c->seq_new) ? c->seq_new->count : nullptr,
+             (c->seq_fused && c->seq_new) ? c->seq_new->threshold : nullptr, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

@@ -236,6 +236,18 @@ class Context:
         check(self.L.rbv_track_g2(self.h, old.h, new.h, ptr(R0), ptr(V), ptr(PV), ptr(Rg), max_radius, min_matches, ptr(n), ptr(kf)))
         return n, kf
 
+    def track(self, old, new, R, max_radius=40.0, min_matches=0):
+        """one tracker frame in one call (rbv_track: g1, host fusion, g2); R [B,3,3] = rotation since the previous frame"""
+        B = self.lanes
+        R = _f32(np.broadcast_to(np.asarray(R, np.float32).reshape(-1, 9), (B, 9)), (B, 9))
+        Vg = np.zeros((B, 3), np.float32); PVg = np.zeros((B, 3, 3), np.float32)
+        Wx = np.zeros((B, 6, 6), np.float32); X = np.zeros((B, 6), np.float32); ok = np.zeros(B, np.int32)
+        V = np.zeros((B, 3), np.float32); n = np.zeros(B, np.int32); kf = np.zeros(B, np.int32)
+        nk = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+        check(self.L.rbv_track(self.h, old.h, new.h, ptr(R), max_radius, min_matches, ptr(Vg), ptr(PVg), ptr(Wx), ptr(X), ptr(ok),
+                               ptr(V), ptr(n), ptr(kf), ptr(nk), ptr(at)))
+        return dict(Vg=Vg, P_Vg=PVg, Wx=Wx, X=X, ok=ok, V=V, matches=n, kf_matches=kf, keylines=nk, auto_threshold=at)
+
     # debug taps
     def read_image(self, which, lane=0):
         out = np.empty((self.cam.rows, self.cam.cols), np.float32)

@@ -35,7 +35,8 @@ def so3_exp_batch(w):
 
 
 def visual_fusion(R, Vg, Wx, X):
-    """batched host block between the two tracker halves -> float32 (R0 [B,9], V [B,3], P_V [B,9], Rgva [B,9])"""
+    """batched host block between the two tracker halves -> float32 (R0 [B,9], V [B,3], P_V [B,9], Rgva [B,9]).
+    numpy statement of what rbv_visual_fusion (C ABI, used by rbv_track / BatchedPipeline) computes; kept as its CPU test oracle"""
     B = len(X)
     R0 = so3_exp_batch(np.asarray(X, np.float64)[:, 3:6])
     V = np.einsum("bij,bj->bi", R0, np.asarray(Vg, np.float64)) + np.asarray(X, np.float64)[:, 0:3]
@@ -103,25 +104,23 @@ class BatchedPipeline:
         ctx, B = self.ctx, self.lanes
         self._servo()
         new = self.maps[self.cur]
+        # with an old map in hand the detect call takes no outputs (no device synchronisation): the new map's keyline count and
+        # auto threshold come back with the tracker's results
         n = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+        pn, pat = (None, None) if self.have_old else (capi.ptr(n), capi.ptr(at))
         ts = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if ts_us is None else ts_us, np.uint64), (B,)))
         if device_ptr is not None:
-            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), pn, pat))
         else:
             fn = ctx.L.rbv_detect_u8 if frames.dtype == np.uint8 else ctx.L.rbv_detect
-            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), capi.ptr(self.threshold), capi.ptr(n), capi.ptr(at)))
+            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), capi.ptr(self.threshold), pn, pat))
         if next_frames is not None:
             self.prefetch(next_frames)
-        self.count = n
         out = {"keylines": n, "auto_threshold": at}
         if self.have_old:
             old = self.maps[1 - self.cur]
-            R = np.ascontiguousarray(R_rel, np.float32).reshape(B, 3, 3)
-            Rt = np.ascontiguousarray(np.transpose(R, (0, 2, 1))).reshape(B, 9)
-            Vg, P_Vg, Wx, X, ok = ctx.track_g1(old, new, Rt)
-            R0, V, P_V, Rgva = visual_fusion(R, Vg, Wx, X)
-            nm, kf = ctx.track_g2(old, new, R0, V, P_V, Rgva, 40.0, self.min_matches)
-            out.update(Vg=Vg, P_Vg=P_Vg, Wx=Wx, X=X, ok=ok, V=V, matches=nm, kf_matches=kf)
+            out.update(ctx.track(old, new, R_rel, 40.0, self.min_matches))   # g1, host fusion (rbv_visual_fusion), g2
+        self.count = out["keylines"]
         self.have_old = True
         self.cur = 1 - self.cur
         self.frames_done += 1

@@ -111,3 +111,31 @@ def test_cpp_adapter_compiles_and_links(tmp_path):
     assert r.returncode == 0, r.stdout
     out = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
     assert out.returncode == 0 and "adapter linked" in out.stdout
+
+
+def test_visual_fusion_matches_numpy_statement():
+    """rbv_visual_fusion (pure host C, the block between the tracker halves; rebvio.cpp:193-200 visual-only) against the
+    numpy statement in rebvio_b200.pipeline: float32 outputs agree to 1 ulp-level tolerance, singular Wx -> 1e10 I"""
+    from rebvio_b200 import pipeline
+    L = capi.load()
+    rng = np.random.RandomState(3)
+    B = 9
+    w = rng.randn(B, 3) * 0.02
+    R = pipeline.so3_exp_batch(w).astype(np.float32)
+    Vg = (rng.randn(B, 3) * 0.05).astype(np.float32)
+    X = (rng.randn(B, 6) * 0.01).astype(np.float32)
+    X[0, 3:] = 0.0                                       # zero rotation: the small-angle branch
+    M = rng.randn(B, 6, 6)
+    Wx = (M @ np.transpose(M, (0, 2, 1)) * 1e4 + np.eye(6) * 10).astype(np.float32)
+    Wx[1] = 0.0                                          # singular
+    R0, V, PV, Rg = (np.zeros((B, n), np.float32) for n in (9, 3, 9, 9))
+    rc = L.rbv_visual_fusion(B, capi.ptr(np.ascontiguousarray(R).reshape(B, 9)), capi.ptr(Vg), capi.ptr(np.ascontiguousarray(Wx).reshape(B, 36)),
+                             capi.ptr(X), capi.ptr(R0), capi.ptr(V), capi.ptr(PV), capi.ptr(Rg))
+    assert rc == 0
+    eR0, eV, ePV, eRg = pipeline.visual_fusion(R, Vg, Wx, X)
+    for got, exp in ((R0, eR0), (V, eV), (Rg, eRg)):
+        assert np.allclose(got, exp, rtol=1e-6, atol=1e-9)
+    ok = np.ones(B, bool); ok[1] = False
+    assert np.allclose(PV[ok], ePV[ok], rtol=2e-5, atol=1e-12)
+    assert np.array_equal(PV[1].reshape(3, 3), np.eye(3, dtype=np.float32) * np.float32(1e10))
+    assert L.rbv_visual_fusion(0, None, None, None, None, None, None, None, None) != 0

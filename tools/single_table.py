@@ -13,6 +13,9 @@ frames_u8, R_rel = synth.batched_sequences(spec, [1000], 12, device=dev, n_textu
 d = frames_u8.to(torch.float32) * 3.0
 stream = torch.cuda.Stream(device=dev)
 p = BatchedPipeline(cam, det, mapc, core, 1, device=0, cuda_stream=stream.cuda_stream)
+for kv in os.environ.get('RBV_TUNE', '').split(','):
+    if kv:
+        p.ctx.set_tuning(*[int(x) for x in kv.split('=')])
 for k in range(6):
     p.push(device_ptr=d[k, 0:1].data_ptr(), R_rel=R_rel[k, 0:1] if k else None)
 p.ctx.profile_reset(); p.ctx.profile_set(-2)
