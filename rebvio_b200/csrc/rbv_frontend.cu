@@ -417,11 +417,11 @@ __global__ void __launch_bounds__(CB_TPB) k_colbox(const float* __restrict__ row
 #define RL_R 32
 #define RL_TPB 256
 __global__ void __launch_bounds__(RL_TPB) k_rowscan_lat(const float* __restrict__ in, float* __restrict__ out, int rows, int cols,
-                                                        size_t in_plane_stride, size_t out_plane_stride, int spitch) {
-  extern __shared__ __align__(128) float rl_smem[];   // [RL_R][spitch], (spitch / 4) odd: conflict-free 128-bit row walks
+                                                        size_t in_plane_stride, size_t out_plane_stride, int spitch, int rpb) {
+  extern __shared__ __align__(128) float rl_smem[];   // [rpb][spitch] (rpb <= 32 rows per block), (spitch / 4) odd: conflict-free 128-bit row walks
   __shared__ __align__(8) unsigned long long rl_bar;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int r0 = blockIdx.x * RL_R, nr = min(RL_R, rows - r0);
+  const int r0 = blockIdx.x * rpb, nr = min(rpb, rows - r0);
   const float* src = in + (size_t)blockIdx.y * in_plane_stride + (size_t)r0 * cols;
   float* dst = out + (size_t)blockIdx.y * out_plane_stride + (size_t)r0 * cols;
   const int n4 = cols >> 2;
@@ -490,16 +490,16 @@ __device__ __forceinline__ float box_value_lin(const float* __restrict__ tile, i
 #define CL_TPB 256
 __global__ void __launch_bounds__(CL_TPB) k_colbox_lat(const float* __restrict__ rowsum, float* __restrict__ out0, float* __restrict__ out1,
                                                        int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
-                                                       int d1, int dual, int hmax) {
-  extern __shared__ __align__(16) float cl_tile[];   // [rows][tw]: image columns c0 - hmax - 1 .. c0 + CL_W - 1 + hmax
+                                                       int d1, int dual, int hmax, int cw) {
+  extern __shared__ __align__(16) float cl_tile[];   // [rows][tw]: image columns c0 - hmax - 1 .. c0 + cw - 1 + hmax (cw <= 32, even)
   __shared__ float inv_area[16][16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int plane = blockIdx.y;
   const int z = dual ? 0 : plane % nz;
   const int ha = (z ? d1 : d0) / 2;
   const int hb = dual ? d1 / 2 : ha;
-  const int tw = CL_W + 2 * hmax + 1;                 // odd: lane = column accesses are conflict-free
-  const int c0 = blockIdx.x * CL_W, cbase = c0 - hmax - 1;
+  const int tw = cw + 2 * hmax + 1;                   // odd: lane = column accesses are conflict-free
+  const int c0 = blockIdx.x * cw, cbase = c0 - hmax - 1;
   const float* src = rowsum + (size_t)plane * in_plane_stride;
   for (int i = tid; i < 256; i += CL_TPB) {
     const int a = i / 16, b = i % 16;
@@ -537,7 +537,7 @@ __global__ void __launch_bounds__(CL_TPB) k_colbox_lat(const float* __restrict__
   }
   __syncthreads();
   const int col = c0 + lane;
-  if (col >= cols) return;
+  if (lane >= cw || col >= cols) return;
   int jhi[2], jlo[2], ncol[2];
   float inv_mid[2];
   const int hh[2] = {ha, hb};
@@ -791,24 +791,39 @@ static int lat_hmax(const rbv_ctx* c) {
     for (int p = 0; p < 3; ++p) m = c->widths[s2][p] / 2 > m ? c->widths[s2][p] / 2 : m;
   return m;
 }
-static size_t lat_row_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)RL_R * lat_spitch(c->P.cols); }
-static size_t lat_col_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)c->P.rows * (CL_W + 2 * lat_hmax(c) + 1); }
+// rows per block of the row kernel / output columns per block of the column kernel: the largest of 32, 16, 8 whose tile fits
+static int lat_rpb(const rbv_ctx* c) {
+  for (int r = 32; r >= 8; r >>= 1)
+    if (sizeof(float) * (size_t)r * lat_spitch(c->P.cols) <= 200 * 1024) return r;
+  return 0;
+}
+static int lat_cw(const rbv_ctx* c) {
+  for (int w = CL_W; w >= 8; w >>= 1)
+    if (sizeof(float) * (size_t)c->P.rows * (w + 2 * lat_hmax(c) + 1) <= 200 * 1024) return w;
+  return 0;
+}
+static size_t lat_row_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)lat_rpb(c) * lat_spitch(c->P.cols); }
+static size_t lat_col_smem(const rbv_ctx* c) { return sizeof(float) * (size_t)c->P.rows * (lat_cw(c) + 2 * lat_hmax(c) + 1); }
 static bool lat_use(const rbv_ctx* c, const void* src) {
-  const bool fits = (c->P.cols & 3) == 0 && lat_row_smem(c) <= 200 * 1024 && lat_col_smem(c) <= 200 * 1024 && lat_hmax(c) <= 7 &&
-                    ((uintptr_t)src & 15) == 0;
+  const bool fits = (c->P.cols & 3) == 0 && lat_rpb(c) > 0 && lat_cw(c) > 0 && lat_hmax(c) <= 7 && ((uintptr_t)src & 15) == 0;
   if (!fits || c->tune[RBV_TUNE_BOX] == 1 || c->tune[RBV_TUNE_BOX] == 2) return false;
   if (c->tune[RBV_TUNE_BOX] == 3) return true;
-  return true;   // automatic: the fused kernel was already chosen above for many lanes; this beats the split pair otherwise
+  // automatic: one scanning warp per block pays off only while the grid does not fill the GPU (few planes); with many
+  // planes the split kernels hide their load latency behind other blocks and move more bytes per second
+  // (and only with full-size tiles: at 4K the 8-row / 8-column tiles measured no better than the split kernels)
+  return lat_rpb(c) == 32 && lat_cw(c) == CL_W && 2 * c->P.lanes * ((c->P.rows + 31) / 32) <= 2 * 148;
 }
 static void lat_rowscan(rbv_ctx* c, const float* in, float* out, int planes) {
   const size_t N = (size_t)c->P.npix;
-  RBV_LAUNCH(c, k_rowscan_lat, (dim3((c->P.rows + RL_R - 1) / RL_R, planes)), (RL_TPB), lat_row_smem(c), in, out, c->P.rows, c->P.cols, N, N,
-             lat_spitch(c->P.cols));
+  const int rpb = lat_rpb(c);
+  RBV_LAUNCH(c, k_rowscan_lat, (dim3((c->P.rows + rpb - 1) / rpb, planes)), (RL_TPB), lat_row_smem(c), in, out, c->P.rows, c->P.cols, N, N,
+             lat_spitch(c->P.cols), rpb);
 }
 static void lat_colbox(rbv_ctx* c, const float* rowsum, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
                        int d0, int d1, int dual) {
-  RBV_LAUNCH(c, k_colbox_lat, (dim3((c->P.cols + CL_W - 1) / CL_W, planes)), (CL_TPB), lat_col_smem(c), rowsum, out0, out1, c->P.rows,
-             c->P.cols, in_stride, out_stride, nz, d0, d1, dual, lat_hmax(c));
+  const int cw = lat_cw(c);
+  RBV_LAUNCH(c, k_colbox_lat, (dim3((c->P.cols + cw - 1) / cw, planes)), (CL_TPB), lat_col_smem(c), rowsum, out0, out1, c->P.rows,
+             c->P.cols, in_stride, out_stride, nz, d0, d1, dual, lat_hmax(c), cw);
 }
 
 int fe_init(rbv_ctx* c) {

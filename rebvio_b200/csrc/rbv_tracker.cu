@@ -1000,8 +1000,8 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     const size_t half = (size_t)P.lanes * nblk;
     float* agg_cur = c->blkagg + (size_t)c->tv_parity * half;
     const float* agg_prev = c->blkagg + (size_t)(1 - c->tv_parity) * half;
-    // keylines per thread (RBV_TUNE_TRYVEL): 1 = k_tryvel_fast, 2 / 4 = k_tryvel_fast2 / k_tryvel_fast4 (0 = automatic: 4)
-    int kpt = c->tune[RBV_TUNE_TRYVEL] ? c->tune[RBV_TUNE_TRYVEL] : 4;
+    // keylines per thread (RBV_TUNE_TRYVEL): 1 = k_tryvel_fast, 2 / 4 = k_tryvel_fast2 / k_tryvel_fast4 (0 = automatic: 4, or 2 with fewer than 8 lanes)
+    int kpt = c->tune[RBV_TUNE_TRYVEL] ? c->tune[RBV_TUNE_TRYVEL] : (P.lanes >= 8 ? 4 : 2);   // few lanes: more, smaller CTAs
     if (kpt == 3 || kpt > 4) kpt = 4;
     const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
 #define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P

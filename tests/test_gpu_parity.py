@@ -188,7 +188,7 @@ def test_box_pass_kernel_vs_oracle(rows, cols):
     ctx.close(); orc.close()
 
 
-@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (35, 832), (720, 1280)])
+@pytest.mark.parametrize("rows,cols", [(32, 32), (37, 64), (97, 132), (240, 320), (480, 640), (480, 752), (35, 832), (720, 1280), (1080, 1920), (2160, 3840)])
 def test_latency_box_pass_kernels_vs_oracle(rows, cols):
     """k_rowscan_lat + k_colbox_lat (the shared-memory-resident box pass used with few lanes), ragged and full sizes"""
     cfg = common.cfgs(0.6 * cols, cols / 2.0, rows / 2.0, rows, cols, 100, 200)
