@@ -171,8 +171,9 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
       // add pipe: the RZ add of 0.5 is what roundf() itself does, the RZ add of 2^23 leaves trunc() in the mantissa
       // (values >= 2^23, Inf and NaN come out as huge indices and fail the range test). No FRND / F2I conversions.
       const float fr0 = (float)rs;
-      int off[FB_G];
-      unsigned key[FB_G];
+      const unsigned cell_a = (unsigned)__cvta_generic_to_shared(fb_cell);
+      unsigned addr[FB_G], key[FB_G];
+      bool ok[FB_G];
 #pragma unroll
       for (int u = 0; u < FB_G; ++u) {
         const int r = rs + u;
@@ -181,18 +182,25 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
         const float fx = kux * fr + kpx;                                                  // :51
         const int iy = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fy), 0.5f), 8388608.0f)) - 0x4B000000;
         const int ix = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fx), 0.5f), 8388608.0f)) - 0x4B000000;
-        const int row = (fy < 0.0f && iy != 0) ? -1 : iy;
-        const int col = (fx < 0.0f && ix != 0) ? -1 : ix;
-        const bool ok = r < re && (unsigned)(row - r0) < (unsigned)nrows && (unsigned)col < (unsigned)cols;
-        off[u] = ok ? (row - r0) * cols + col : -1;
-        key[u] = ((unsigned)abs(r) << 24) | lowkey;                                      // :54-56 as min over (|r|, -idx)
+        // a negative coordinate rounds to an index >= 0 only for v > -0.5 (round(-0.3) = -0 -> 0, round(-0.5) = -1): one compare
+        // per axis instead of sign test + zero test + select; NaN fails the compare, Inf the range test
+        ok[u] = r < re && fy > -0.5f && fx > -0.5f && (unsigned)(iy - r0) < (unsigned)nrows && (unsigned)ix < (unsigned)cols;
+        addr[u] = cell_a + 4u * (unsigned)((iy - r0) * cols + ix);
+        key[u] = lowkey + ((unsigned)abs(r) << 24);                                      // :54-56 as min over (|r|, -idx)
       }
+      // loads, then compares + atomics: predicated instructions (no branch per candidate), all loads issued before the first use
       unsigned cur[FB_G];
 #pragma unroll
-      for (int u = 0; u < FB_G; ++u) cur[u] = off[u] >= 0 ? *(volatile unsigned*)(fb_cell + off[u]) : 0u;
+      for (int u = 0; u < FB_G; ++u)
+        asm volatile("{ .reg .pred p;\n"
+                     "  setp.ne.u32 p, %2, 0;\n"
+                     "  mov.u32 %0, 0;\n"
+                     "  @p ld.volatile.shared.u32 %0, [%1]; }" : "=r"(cur[u]) : "r"(addr[u]), "r"((unsigned)ok[u]));
 #pragma unroll
       for (int u = 0; u < FB_G; ++u)
-        if (off[u] >= 0 && cur[u] > key[u]) atomicMin(fb_cell + off[u], key[u]);
+        asm volatile("{ .reg .pred q;\n"
+                     "  setp.gt.u32 q, %2, %1;\n"
+                     "  @q red.shared.min.u32 [%0], %1; }" ::"r"(addr[u]), "r"(key[u]), "r"(cur[u]) : "memory");
     }
     __syncthreads();
   }
