@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-single", action="store_true", help="skip the single-stream latency leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--undistort", action="store_true", help="e2e leg: raw camera frames, Camera::undistort (EuRoC cam0 model) on the device")
     ap.add_argument("--tune", default="", help="implementation choices, e.g. '2=4,0=1' (rbv_set_tuning key=value pairs)")
     ap.add_argument("--kernel-table", default="", help="write the per-kernel CUDA-event table (one untimed step) here")
     return ap.parse_args()
@@ -349,6 +350,9 @@ def run_b200(args):
         torch.cuda.synchronize()
         hnp = h_frames.numpy()
         pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
+        if args.undistort:   # rebvio/include/rebvio/camera.hpp:26-40
+            fm = 0.5 * (458.654 + 457.296)
+            pipe.ctx.set_undistort([fm, fm, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0])
         pipe.push(frames=hnp[0], next_frames=hnp[1])
         for k in range(1, 1 + W):
             pipe.push(frames=hnp[k], R_rel=R_rel[k], next_frames=hnp[k + 1])
@@ -367,7 +371,8 @@ def run_b200(args):
         d2h = B * (8 + lm_bytes + 64 * 4 + 8 * 4)
         line["e2e"] = {"value": frames_total / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                        "ms_per_step": 1e3 * e2e_s / K,
-                       "input": "uint8 frames in pinned host memory through rbv_detect_u8; next frame's upload overlapped (rbv_prefetch_frames)"}
+                       "input": "uint8 frames in pinned host memory through rbv_detect_u8; next frame's upload overlapped (rbv_prefetch_frames)"
+                                + ("; Camera::undistort on the device (rbv_set_undistort)" if args.undistort else "")}
         pipe.close()
         del h_frames, hnp
 

@@ -136,6 +136,14 @@ int rbv_profile_reset(rbv_ctx* ctx);
 int rbv_profile_read(rbv_ctx* ctx, int kid, double* total_ms, unsigned long long* timed_launches,
                      unsigned long long* launches);
 
+/* Camera::undistort on the device (camera.hpp:54-58 = cv::undistort(img, K_, D_), called from Rebvio::imageCallback,
+ * rebvio.cpp:45, on the float32 x 3 frame). K4 = (fx, fy, cx, cy) - the reference passes (fm, fm, cx, cy), camera.hpp:39 -
+ * and D5 = (k1, k2, p1, p2, k3), both float32 like the reference's K_ / D_ matrices. Once set, rbv_detect, rbv_detect_u8
+ * and rbv_prefetch_frames take RAW camera frames and the library runs the fixed-point bilinear remap of cv::undistort
+ * (INTER_BITS = 5, BORDER_CONSTANT 0) in front of the scale space; rbv_detect_device is unaffected (device frames are
+ * taken as already undistorted). K4 = NULL switches it off. Bit-exact against cv2.undistort on the golden vectors.      */
+int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
+
 /* implementation choices, for tests and profiling; 0 = automatic (the default) everywhere.
  *   RBV_TUNE_FIELD: distance field — 1 = one thread per keyline with global atomics, 2 = shared-memory row bands
  *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel,
@@ -277,7 +285,8 @@ int rbv_map_upload(rbv_ctx* ctx, rbv_map* map, int lane, const rbv_keyline* keyl
                    const uint32_t* pixel_idx, int n);
 
 /* ---- debug taps used by the parity tests ---------------------------------------------------------------- */
-/* which: 0 = scale0, 1 = scale1, 2 = DoG, 3 = squared gradient magnitude; out: rows*cols float32 */
+/* which: 0 = scale0, 1 = scale1, 2 = DoG, 3 = squared gradient magnitude, 4 = the float frame the front end worked on
+ * (after the x3 conversion / undistortion of the host-frame paths); out: rows*cols float32 */
 int rbv_debug_read_image(rbv_ctx* ctx, int lane, int which, float* out);
 /* id mask of EdgeDetector (keylines_mask_, edge_detector.hpp:86) for the last detect: rows*cols int32 */
 int rbv_debug_read_mask(rbv_ctx* ctx, rbv_map* map, int lane, int* out);

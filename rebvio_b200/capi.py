@@ -91,6 +91,7 @@ _SIG = {
     "rbv_update_inverse_depth": (C.c_int, [vp, vp]),
     "rbv_track_g1": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rbv_track_g2": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]),
+    "rbv_set_undistort": (C.c_int, [vp, vp, vp]),
     "rbv_visual_fusion": (C.c_int, [C.c_int, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rbv_track": (C.c_int, [vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rbv_map_size": (C.c_int, [vp, vp, vp]),

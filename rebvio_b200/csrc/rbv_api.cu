@@ -317,6 +317,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   }
   cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm);
   if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+  if (c->undist_map) cudaFree(c->undist_map);
   for (int i = 0; i < 2; ++i) {
     cudaFree(c->raw[i]);
     if (c->raw_ready[i]) cudaEventDestroy(c->raw_ready[i]);
@@ -543,6 +544,82 @@ __global__ void k_u8_to_f32(const uint4* __restrict__ src16, float4* __restrict_
   for (size_t i = n16 * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dstf[i] = (float)src[i] * 3.0f;
 }
 
+// ---- Camera::undistort on the device ------------------------------------------------------------
+// Rebvio::imageCallback (rebvio.cpp:43-45) converts the camera frame to float32 x 3 and runs cv::undistort(K, D) on it on the
+// host, holding the image mutex. cv::undistort = per-pixel map in double (initUndistortRectifyMap: normalise with inv(K), radial
+// (k1, k2, k3) and tangential (p1, p2) distortion, project with K), quantised to 1/32 pixel (CV_16SC2 + CV_16UC1 maps,
+// INTER_BITS = 5), then remap INTER_LINEAR / BORDER_CONSTANT 0 with the float32 weight table. The map depends on the camera
+// only, so it is built once (k_undistort_map, 8 bytes per pixel: source x, y as int16, the four weights' table index) and every
+// frame is one gather kernel that also does the x 3 conversion. oracle/undistort.py restates the same algorithm and is pinned
+// bit for bit against cv2.undistort (tests/golden/undistort_euroc.npz).
+struct UndistortK {
+  double ifx, ifx_cx, ify, ify_cy, fx, fy, cx, cy, k1, k2, p1, p2, k3;
+};
+__global__ void k_undistort_map(uint2* __restrict__ map, int rows, int cols, const __grid_constant__ UndistortK U) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= cols) return;
+  const double x = (double)j * U.ifx + U.ifx_cx, y = (double)i * U.ify + U.ify_cy;       // inv(K) * (j, i, 1)
+  const double x2 = x * x, y2 = y * y, r2 = x2 + y2, _2xy = 2.0 * x * y;
+  const double kr = 1.0 + ((U.k3 * r2 + U.k2) * r2 + U.k1) * r2;
+  const double xd = x * kr + U.p1 * _2xy + U.p2 * (r2 + 2.0 * x2);
+  const double yd = y * kr + U.p1 * (r2 + 2.0 * y2) + U.p2 * _2xy;
+  const double u = U.fx * xd + U.cx, v = U.fy * yd + U.cy;
+  const long long iu = __double2ll_rn(u * 32.0), iv = __double2ll_rn(v * 32.0);         // cvRound: half to even
+  long long sx = iu >> 5, sy = iv >> 5;
+  // anything that cannot touch the image is parked at one fully-outside position (result 0, as BORDER_CONSTANT gives)
+  if (sx < -1 || sx > cols || sy < -1 || sy > rows) { sx = -2; sy = -2; }
+  const unsigned wx = (unsigned)(iu & 31), wy = (unsigned)(iv & 31);
+  map[(size_t)i * cols + j] = make_uint2(((unsigned)(sx & 0xFFFF)) | ((unsigned)(sy & 0xFFFF) << 16), wy * 32u + wx);
+}
+template <typename T> __device__ __forceinline__ float ud_fetch(const T* __restrict__ src, int rows, int cols, int yy, int xx) {
+  if ((unsigned)yy >= (unsigned)rows || (unsigned)xx >= (unsigned)cols) return 0.0f;    // BORDER_CONSTANT, value 0
+  return (float)src[(size_t)yy * cols + xx] * (sizeof(T) == 1 ? 3.0f : 1.0f);            // convertTo(CV_32F, 3.0) for camera bytes
+}
+__global__ void __launch_bounds__(256) k_undistort(const unsigned char* __restrict__ src8, const float* __restrict__ src32, float* __restrict__ dst,
+                                                   const uint2* __restrict__ map, int rows, int cols) {
+  const size_t N = (size_t)rows * cols;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if ((size_t)p >= N) return;
+  const uint2 m = map[p];
+  const int sx = (int)(short)(m.x & 0xFFFFu), sy = (int)(short)(m.x >> 16);
+  const float fx = (float)(m.y & 31u) * 0.03125f, fy = (float)(m.y >> 5) * 0.03125f;
+  const float cx0 = 1.0f - fx, cy0 = 1.0f - fy;
+  const float w00 = cy0 * cx0, w01 = cy0 * fx, w10 = fy * cx0, w11 = fy * fx;
+  float s00, s01, s10, s11;
+  if (src8) {
+    const unsigned char* s = src8 + (size_t)blockIdx.y * N;
+    s00 = ud_fetch(s, rows, cols, sy, sx); s01 = ud_fetch(s, rows, cols, sy, sx + 1);
+    s10 = ud_fetch(s, rows, cols, sy + 1, sx); s11 = ud_fetch(s, rows, cols, sy + 1, sx + 1);
+  } else {
+    const float* s = src32 + (size_t)blockIdx.y * N;
+    s00 = ud_fetch(s, rows, cols, sy, sx); s01 = ud_fetch(s, rows, cols, sy, sx + 1);
+    s10 = ud_fetch(s, rows, cols, sy + 1, sx); s11 = ud_fetch(s, rows, cols, sy + 1, sx + 1);
+  }
+  dst[(size_t)blockIdx.y * N + p] = ((s00 * w00 + s01 * w01) + s10 * w10) + s11 * w11;
+}
+
+extern "C" int rbv_set_undistort(rbv_ctx* c, const float* K4, const float* D5) {
+  CHECK_CTX(c);
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  rbv_graphs_clear(c, nullptr);
+  if (!K4) {                              // frames arrive undistorted again
+    if (c->undist_map) { cudaFree(c->undist_map); c->undist_map = nullptr; }
+    return RBV_OK;
+  }
+  if (!D5) { rbv_set_error("rbv_set_undistort: distortion coefficients missing"); return RBV_ERR_ARG; }
+  if (c->P.rows > 32000 || c->P.cols > 32000) { rbv_set_error("rbv_set_undistort: image too large for 16-bit map coordinates"); return RBV_ERR_ARG; }
+  if (!(K4[0] > 0.0f) || !(K4[1] > 0.0f)) { rbv_set_error("rbv_set_undistort: focal lengths must be positive"); return RBV_ERR_ARG; }
+  UndistortK U;
+  U.fx = K4[0]; U.fy = K4[1]; U.cx = K4[2]; U.cy = K4[3];                     // float32 K_, D_ widened to double (camera.hpp:39-40)
+  U.ifx = 1.0 / U.fx; U.ify = 1.0 / U.fy; U.ifx_cx = -U.cx * U.ifx; U.ify_cy = -U.cy * U.ify;
+  U.k1 = D5[0]; U.k2 = D5[1]; U.p1 = D5[2]; U.p2 = D5[3]; U.k3 = D5[4];
+  if (!c->undist_map) RBV_CUDA(cudaMalloc(&c->undist_map, sizeof(uint2) * (size_t)c->P.npix));
+  RBV_LAUNCH(c, k_undistort_map, (dim3((c->P.cols + 127) / 128, c->P.rows)), (128), 0, c->undist_map, c->P.rows, c->P.cols, U);
+  RBV_CUDA(cudaGetLastError());
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  return RBV_OK;
+}
+
 // H2D of B frames (element size esz) into a dense [B][N] device buffer on stream st: one copy when the host frames are
 // dense and back to back, else one copy per lane
 static int upload_frames(rbv_ctx* c, void* dst, const void* const* images, size_t pitch_bytes, size_t esz, cudaStream_t st) {
@@ -596,10 +673,22 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
     c->raw_key[slot] = nullptr;
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));   // a stale prefetch into this slot must have landed first
     TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 1, c->stream));
+  } else if (c->undist_map) {            // float frames that still need undistorting: stage them, the remap writes c->img
+    slot = c->raw_next;
+    c->raw_next = 1 - slot;
+    c->raw_key[slot] = nullptr;
+    RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
+    TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 4, c->stream));
   } else {
     TRY(upload_frames(c, c->img, images, pitch_bytes, 4, c->stream));
   }
-  if (is_u8) {
+  if (c->undist_map) {                   // Camera::undistort (+ the x3 conversion for camera bytes) in one gather pass
+    RBV_LAUNCH(c, k_undistort, (dim3((unsigned)((c->P.npix + 255) / 256), c->P.lanes)), (256), 0,
+               is_u8 ? (const unsigned char*)c->raw[slot] : nullptr, is_u8 ? nullptr : (const float*)c->raw[slot], c->img, c->undist_map,
+               c->P.rows, c->P.cols);
+    RBV_CUDA(cudaGetLastError());
+    d_img = c->img;
+  } else if (is_u8) {
     const size_t n = (size_t)c->P.lanes * c->P.npix;
     RBV_LAUNCH(c, k_u8_to_f32, (148 * 8), (256), 0, (const uint4*)c->raw[slot], (float4*)c->img, (const unsigned char*)c->raw[slot], c->img,
                n / 16, n);
@@ -1068,9 +1157,13 @@ extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keylin
 // ---- debug taps ----
 extern "C" int rbv_debug_read_image(rbv_ctx* c, int lane, int which, float* out) {
   CHECK_CTX(c);
-  if (lane < 0 || lane >= c->P.lanes || which < 0 || which > 3 || !out) return RBV_ERR_ARG;
+  if (lane < 0 || lane >= c->P.lanes || which < 0 || which > 4 || !out) return RBV_ERR_ARG;
   const size_t N = c->P.npix;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
+  if (which == 4) {   // the float frame the front end worked on (after the u8 conversion / undistortion of the host-frame paths)
+    RBV_CUDA(copy_sync(c, out, c->img + (size_t)lane * N, sizeof(float) * N, cudaMemcpyDeviceToHost));
+    return RBV_OK;
+  }
   if (which < 2) {
     RBV_CUDA(copy_sync(c, out, c->bufA + ((size_t)lane * 2 + which) * N, sizeof(float) * N, cudaMemcpyDeviceToHost));
     return RBV_OK;

@@ -138,6 +138,7 @@ struct rbv_ctx {
   const void* raw_key[2];     // images[0] of the prefetch that filled slot i (nullptr = empty)
   int raw_u8[2];
   int raw_next;
+  uint2* undist_map;          // [N] fixed-point remap of cv::undistort (rbv_set_undistort), nullptr = frames arrive undistorted
   unsigned long long launches;  // kernels launched since creation
   unsigned long long klaunch[48];   // per kernel id
   int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
@@ -164,7 +165,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
-  X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat)
+  X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)

@@ -97,6 +97,12 @@ class Context:
 
     def set_reduce_mode(self, mode): check(self.L.rbv_set_reduce_mode(self.h, mode))
     def set_tuning(self, key, value): check(self.L.rbv_set_tuning(self.h, int(key), int(value)))
+    def set_undistort(self, K4=None, D5=None):
+        """Camera::undistort on the device: K4 = (fx, fy, cx, cy), D5 = (k1, k2, p1, p2, k3); None switches it off"""
+        k = None if K4 is None else np.ascontiguousarray(K4, np.float32)
+        d = None if D5 is None else np.ascontiguousarray(D5, np.float32)
+        check(self.L.rbv_set_undistort(self.h, ptr(k), ptr(d)))
+
     def set_stream(self, cuda_stream): check(self.L.rbv_set_stream(self.h, C.c_void_p(cuda_stream)))
     def sync(self): check(self.L.rbv_sync(self.h))
     def launch_count(self): return int(self.L.rbv_launch_count(self.h))
