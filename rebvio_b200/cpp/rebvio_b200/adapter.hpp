@@ -66,6 +66,11 @@ class Device {
   Device& operator=(const Device&) = delete;
   rbv_ctx* ctx() const { return ctx_; }
   int keylines_max() const { return kmax_; }
+  // Camera::undistort on the device (camera.hpp:54-58): K_ = [fm 0 cx; 0 fm cy; 0 0 1], D_ = (k1, k2, p1, p2, k3); raw frames from then on
+  void setUndistort(float fm, float cx, float cy, float k1, float k2, float p1, float p2, float k3) {
+    const float K4[4] = {fm, fm, cx, cy}, D5[5] = {k1, k2, p1, p2, k3};
+    check(rbv_set_undistort(ctx_, K4, D5), "rbv_set_undistort");
+  }
 
  private:
   rbv_ctx* ctx_ = nullptr;

@@ -286,6 +286,9 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaMallocHost((void**)&c->h_cnt, sizeof(int) * B * (CNT_STRIDE + 2)));
   RBV_CUDA(cudaMallocHost((void**)&c->h_lm, sizeof(LMState) * B));
   RBV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  RBV_CUDA(cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+  RBV_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  RBV_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   for (int i = 0; i < 2; ++i) {
     RBV_CUDA(cudaMalloc(&c->raw[i], sizeof(float) * B * N));
     RBV_CUDA(cudaEventCreateWithFlags(&c->raw_ready[i], cudaEventDisableTiming));
@@ -317,6 +320,9 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   }
   cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm);
   if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+  if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->undist_map) cudaFree(c->undist_map);
   for (int i = 0; i < 2; ++i) {
     cudaFree(c->raw[i]);
@@ -775,16 +781,20 @@ __global__ void k_lm_init(LMState* lm, const float* lane_in, int lanes) {
 }
 
 // enqueue Core::minimizeVel (core.cpp:150-189) on the stream: quantile, residual reset, (1 + iterations) tryVel + LM steps
-static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map) {
+// part: 0 = everything, 1 = only what precedes the first tryVel (quantile, LM seed), 2 = only the tryVel / LM calls
+static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map, int part = 0) {
   // FAST mode with several keylines per thread: the quantile kernel also seeds the LM state, and call 0 of tryVel takes the
   // residuals as zero and writes every entry, so neither k_lm_init nor the residual fill is launched
   const bool lean = c->reduce_mode == RBV_REDUCE_FAST && c->tune[RBV_TUNE_TRYVEL] != 1;
-  TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, lean ? 2 : 1));
-  if (!lean) {
-    TRY(rbv_fill32(c, old_map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax));
-    RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
+  if (part != 2) {
+    TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, lean ? 2 : 1));
+    if (!lean) {
+      TRY(rbv_fill32(c, old_map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax));
+      RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
+    }
   }
-  for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
+  if (part != 1)
+    for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
   return RBV_OK;
 }
 static int fetch_lm(rbv_ctx* c, float* vel3, float* Rvel9, float* score) {
@@ -904,9 +914,22 @@ extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   TRY(stage_commit(c, slot));
   TRY(run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
     SeqFused fused(c, 0);
+    // two independent branches: the distance field of the NEW map (the longest kernel of the half, instruction bound at ~45 %
+    // occupancy) and rotation + sigma_rho quantile + LM seed of the OLD map; they meet in front of the first tryVel
+    RBV_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+    RBV_CUDA(cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0));
+    {
+      cudaStream_t main_stream = c->stream;
+      c->stream = c->side_stream;
+      int rc = tr_rotate(c, old_map);
+      if (rc == RBV_OK) rc = enqueue_minimize(c, old_map, 1);
+      c->stream = main_stream;
+      TRY(rc);
+    }
+    RBV_CUDA(cudaEventRecord(c->ev_join, c->side_stream));
     TRY(tr_build_field(c, new_map));
-    TRY(tr_rotate(c, old_map));
-    TRY(enqueue_minimize(c, old_map));
+    RBV_CUDA(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    TRY(enqueue_minimize(c, old_map, 2));
     TRY(tr_forward_match(c, old_map, new_map));
     return tr_ext_rot_vel(c, new_map, 1);
   }));

@@ -132,6 +132,8 @@ struct rbv_ctx {
   // frame upload: double-buffered raw staging on a copy stream (rbv_prefetch_frames) so that the H2D of frame k+1 overlaps
   // the tracker of frame k; u8 frames are converted (x 3.0, rebvio.cpp:43) on the device
   cudaStream_t copy_stream;
+  cudaStream_t side_stream;   // second branch of rbv_track_g1: rotate + quantile of the old map next to the field build of the new one
+  cudaEvent_t ev_fork, ev_join;
   void* raw[2];               // [B][N] bytes (u8) or floats (f32) as uploaded
   cudaEvent_t raw_ready[2];   // upload of slot i finished (recorded on copy_stream)
   cudaEvent_t raw_free[2];    // the front end has consumed slot i (recorded on stream)
