@@ -566,7 +566,7 @@ __host__ __device__ inline int bp_ncw(int nwarps) {
 
 __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __restrict__ in, float* __restrict__ out0, float* __restrict__ out1,
                                                      int rows, int cols, size_t in_plane_stride, size_t out_plane_stride, int nz, int d0,
-                                                     int d1, int dual, int spitch) {
+                                                     int d1, int dual, int spitch, int in_div) {
   extern __shared__ __align__(128) float bp_smem[];
   __shared__ float inv_area[16][16];
   __shared__ __align__(8) unsigned long long bars[6];   // full[2], scanned[2], empty[2]
@@ -584,7 +584,7 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
   const int ha = (z ? d1 : d0) / 2;
   const int hb = dual ? d1 / 2 : ha;
   const int hm = max(ha, hb);
-  const float* src = in + (size_t)plane * in_plane_stride;
+  const float* src = in + (size_t)(plane / in_div) * in_plane_stride;   // in_div = 2: both scales of a lane read the same input plane
   for (int i = tid; i < 256; i += blockDim.x) {
     const int a = i / 16, b = i % 16;
     inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171
@@ -775,11 +775,11 @@ static bool bp_use(const rbv_ctx* c, const void* src) {
   return c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
 }
 static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
-                     int d0, int d1, int dual) {
+                     int d0, int d1, int dual, int in_div = 1) {
   const int cols = c->P.cols;
   const int threads = bp_threads(cols);
   RBV_LAUNCH(c, k_boxpass, (planes), (threads), bp_smem_bytes(cols), in, out0, out1, c->P.rows, cols, in_stride, out_stride, nz, d0, d1,
-             dual, bp_spitch(cols));
+             dual, bp_spitch(cols), in_div);
   return RBV_OK;
 }
 
@@ -851,7 +851,10 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
   const int rows = c->P.rows, cols = c->P.cols, B = c->P.lanes;
   const size_t N = (size_t)c->P.npix;
   if (bp_use(c, d_img)) {   // fused passes: 64 N -> 44 N bytes of traffic per frame, 3 launches instead of 6
-    if (part != 2) bp_launch(c, d_img, c->bufA, c->bufA + N, B, N, 2 * N, 1, c->widths[0][0], c->widths[1][0], 1);
+    // pass 0: one CTA per (lane, scale), both reading the lane's frame. The dual form (one CTA per lane filtering both
+    // widths from one scan) moves a third less data but is a 64-CTA launch of 140 us on 148 SMs; two single-width CTAs per
+    // lane fill the GPU like passes 1 and 2 do.
+    if (part != 2) bp_launch(c, d_img, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
     if (part != 1) {
       bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
       bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
