@@ -466,7 +466,7 @@ enum { GK_DETECT = 1, GK_TRACK1 = 2, GK_TRACK2 = 3 };
 struct SeqFused {
   rbv_ctx* c;
   SeqFused(rbv_ctx* ctx, int min_matches, rbv_map* new_map = nullptr) : c(ctx) { c->seq_fused = 1; c->seq_min_matches = min_matches; c->seq_new = new_map; }
-  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; c->seq_new = nullptr; }
+  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; c->seq_new = nullptr; c->seq_reg_pending = 0; }
 };
 template <class Body>
 static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int flag, Body body) {

@@ -1624,7 +1624,8 @@ int tr_regularize(rbv_ctx* c, rbv_map* map) {
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
   if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_REG, nullptr);
   RBV_LAUNCH(c, k_reg_eval, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, c->seq_fused ? c->seq_min_matches : 0, P);
-  RBV_LAUNCH(c, k_reg_apply, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, c->seq_fused ? c->seq_min_matches : 0, P.kmax);
+  if (c->seq_fused && map == c->field_map) c->seq_reg_pending = 1;   // k_kalman (next in rbv_track_g2, same map) applies the result
+  else RBV_LAUNCH(c, k_reg_apply, (g), (256), 0, map->k, map->count, c->reg_r, c->reg_s, c->fwd_next, c->lane_cnt, c->seq_fused ? c->seq_min_matches : 0, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -1632,17 +1633,24 @@ int tr_regularize(rbv_ctx* c, rbv_map* map) {
 // ---------------------------------------------------------------------------------------------------------------
 // updateInverseDepth + updateInverseDepthARLU (core.cpp:417-456): scalar EKF per matched keyline of the field map
 __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ lane_in,
-                                                const int* __restrict__ lane_cnt, int min_matches, const __grid_constant__ DevParams P) {
+                                                const int* __restrict__ lane_cnt, int min_matches, const float* __restrict__ reg_r,
+                                                const float* __restrict__ reg_s, const int* __restrict__ reg_set,
+                                                const __grid_constant__ DevParams P) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count[b]) return;
   if (min_matches > 0 && lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) return;
   const size_t o = (size_t)b * P.kmax + idx;
-  if (K.match_id[o] < 0) return;
+  float rho = K.rho[o], srho = K.srho[o];
+  bool dirty = false;
+  if (reg_set && reg_set[o]) { rho = reg_r[o]; srho = reg_s[o]; dirty = true; }         // second phase of regularize1Iter (edge_map.cpp:252-257)
+  if (K.match_id[o] < 0) {
+    if (dirty) { K.rho[o] = rho; K.srho[o] = srho; }
+    return;
+  }
   const float* vel = lane_in + (size_t)b * IN_STRIDE + IN_VEL;
   const float v0 = vel[0], v1 = vel[1], v2 = vel[2], fm = P.fm;
   const float2 q = K.pos_img[o], q0 = K.match_pos_img[o], mg = K.match_grad[o];
   const float mgn = K.match_gnorm[o];
-  float rho = K.rho[o], srho = K.srho[o];
   float v_rho = srho * srho;                                                             // :429
   const float ux = mg.x / mgn, uy = mg.y / mgn;
   const float Y = ux * (q.x - q0.x) + uy * (q.y - q0.y);                                 // :432
@@ -1673,8 +1681,13 @@ __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restr
 
 int tr_kalman(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
+  // inside rbv_track_g2 the write phase of regularize1Iter rides along (tr_regularize skipped k_reg_apply): every keyline is
+  // touched by exactly one thread here and k_reg_eval has completed, so the reference's two-phase rule holds
+  const bool apply = c->seq_fused && c->seq_reg_pending;
+  c->seq_reg_pending = 0;
   RBV_LAUNCH(c, k_kalman, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, c->lane_in, c->lane_cnt,
-             c->seq_fused ? c->seq_min_matches : 0, P);
+             c->seq_fused ? c->seq_min_matches : 0, apply ? c->reg_r : nullptr, apply ? c->reg_s : nullptr,
+             apply ? (const int*)c->fwd_next : nullptr, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

@@ -392,3 +392,74 @@ def test_cuda_graph_replay_equals_stream_launches(lanes, mode):
             assert np.array_equal(H.bits(np.asarray(o[key], np.float32)), H.bits(np.asarray(o0[key], np.float32))), key
         for a, b in zip(kl, kl0):
             assert a.tobytes() == b.tobytes()
+
+
+def test_long_free_running_sequence_c1():
+    """BASELINE.json configs[0] shape (640x480 textured plane), 12 frames free-running (no teacher forcing): with ordered
+    reductions every stage of every frame stays bit-exact against the oracle; with the FP64 throughput reductions the keyline
+    sets stay identical (the front end does not depend on the tracker), the fused velocity agrees to 1e-3 relative and the
+    directed-match count to 0.5 % after 11 tracked frames."""
+    nf = 12
+    spec, frames, R_rel = common.sequence("C1", nf)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    T = H.run_stages(orc, frames, R_rel)
+    g = _gpu(cfg, lanes=2, lane=1, mode=capi.REDUCE_ORDERED)
+    G = H.run_stages(g, frames, R_rel)
+    assert H.dirty(H.report(T, G)) == []
+    g.close()
+    g = _gpu(cfg, lanes=2, lane=0, mode=capi.REDUCE_FAST)
+    F = H.run_stages(g, frames, R_rel)
+    g.close(); orc.close()
+    for k in range(nf):
+        assert F[k]["detect"]["n"] == T[k]["detect"]["n"]
+    for k in range(1, nf):
+        vt, vf = np.asarray(T[k]["minimize"]["Vg"], np.float64), np.asarray(F[k]["minimize"]["Vg"], np.float64)
+        assert np.linalg.norm(vf - vt) <= 1e-3 * max(np.linalg.norm(vt), 1e-3), (k, vt, vf)
+        nt, nfm = T[k]["directed"]["n"], F[k]["directed"]["n"]
+        assert abs(nt - nfm) <= max(2, 0.005 * nt), (k, nt, nfm)
+
+
+@pytest.mark.parametrize("mode", [capi.REDUCE_ORDERED, capi.REDUCE_FAST])
+def test_fused_tracker_sequences_equal_stage_calls(mode):
+    """rbv_track_g1 / rbv_track_g2 (captured graphs, second branch, counter reset in k_rotate, match-floor gate as kernel
+    argument, regularise write phase inside k_kalman) against the same frame done with one C-ABI call per reference member
+    function: bit-identical outputs and maps."""
+    from rebvio_b200 import pipeline
+    spec, frames, R_rel = common.sequence("C5:320x240", 3)
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+    B = 2
+    imgs = [np.broadcast_to(np.asarray(f, np.float32), (B,) + f.shape) for f in frames]
+    thr = np.full(B, det.threshold, np.float32)
+    R = np.broadcast_to(np.asarray(R_rel[1], np.float32), (B, 3, 3))
+    Rt = np.ascontiguousarray(np.transpose(R, (0, 2, 1)))
+    res = []
+    for fused in (True, False):
+        ctx = host.Context(cam, det, mapc, core, lanes=B, reduce_mode=mode)
+        a, _, _ = ctx.detect(imgs[0], thr)
+        b, _, _ = ctx.detect(imgs[1], thr)
+        if fused:
+            Vg, PVg, Wx, X, ok = ctx.track_g1(a, b, Rt)
+        else:
+            ctx.buildDistanceField(b)
+            ctx.rotateKeylines(a, Rt)
+            score, Vg, PVg = ctx.minimizeVel(a, np.zeros((B, 3), np.float32))
+            ctx.forwardMatch(a, b)
+            ok, Wx, X = ctx.extRotVel(b, Vg)
+        R0, V, PV, Rg = pipeline.visual_fusion(R, Vg, Wx, X)
+        if fused:
+            n, kf = ctx.track_g2(a, b, R0, V, PV, Rg, 40.0, 10)
+        else:
+            ctx.rotateKeylines(a, R0)
+            n, kf = ctx.directedMatch(b, a, V, PV, Rg, 40.0)
+            ctx.regularize1Iter(b)
+            ctx.updateInverseDepth(V)
+        res.append(dict(Vg=np.array(Vg), PVg=np.array(PVg), Wx=np.array(Wx), X=np.array(X), n=np.array(n), kf=np.array(kf),
+                        a=[a.keylines(l)[0].tobytes() for l in range(B)], b=[b.keylines(l)[0].tobytes() for l in range(B)]))
+        ctx.close()
+    for key in ("Vg", "PVg", "Wx", "X", "n", "kf"):
+        assert np.array_equal(H.bits(np.asarray(res[0][key], np.float32)), H.bits(np.asarray(res[1][key], np.float32))), key
+    assert res[0]["a"] == res[1]["a"] and res[0]["b"] == res[1]["b"]
+    assert int(res[0]["n"][0]) > 500
