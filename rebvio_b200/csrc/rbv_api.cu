@@ -269,6 +269,8 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
   RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
+  RBV_CUDA(cudaMemset(c->rowcount, 0, sizeof(int) * B * P.rows));          // kept clean by k_detect_scan
+  RBV_CUDA(cudaMemset(c->fwd_head, 0xFF, sizeof(int) * B * K));            // kept empty (-1) by k_fwd_resolve
   RBV_CUDA(cudaMemset(c->lm, 0, sizeof(LMState) * B));
   RBV_CUDA(cudaMemset(c->lane_in, 0, sizeof(float) * B * IN_STRIDE));
   RBV_CUDA(cudaMemset(c->lane_out, 0, sizeof(float) * B * OUT_STRIDE));
@@ -466,7 +468,7 @@ enum { GK_DETECT = 1, GK_TRACK1 = 2, GK_TRACK2 = 3 };
 struct SeqFused {
   rbv_ctx* c;
   SeqFused(rbv_ctx* ctx, int min_matches, rbv_map* new_map = nullptr) : c(ctx) { c->seq_fused = 1; c->seq_min_matches = min_matches; c->seq_new = new_map; }
-  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; c->seq_new = nullptr; c->seq_reg_pending = 0; }
+  ~SeqFused() { c->seq_fused = 0; c->seq_min_matches = 0; c->seq_new = nullptr; c->seq_reg_pending = 0; c->seq_resolve_agg = nullptr; }
 };
 template <class Body>
 static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int flag, Body body) {

@@ -1112,7 +1112,7 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
 }
 
 // Pass 2: exclusive prefix of the per-row counts -> first keyline id of every row; count = min(total, keylines_max)
-__global__ void __launch_bounds__(1024) k_detect_scan(const int* __restrict__ rowcount, int* __restrict__ rowoffset, int* __restrict__ count,
+__global__ void __launch_bounds__(1024) k_detect_scan(int* __restrict__ rowcount, int* __restrict__ rowoffset, int* __restrict__ count,
                                                       int rows, int kmax) {
   __shared__ int part[1024];
   const int b = blockIdx.x, t = threadIdx.x;
@@ -1133,6 +1133,7 @@ __global__ void __launch_bounds__(1024) k_detect_scan(const int* __restrict__ ro
   for (int r = lo; r < hi; ++r) {
     rowoffset[b * rows + r] = run;
     run += rowcount[b * rows + r];
+    rowcount[b * rows + r] = 0;   // consumed: left clean for the next frame's k_detect_flags (no fill launch per frame)
   }
   if (t == 1023) count[b] = min(part[1023], kmax);
 }
@@ -1305,7 +1306,7 @@ int fe_detect(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   const int B = P.lanes, rows = P.rows, cols = P.cols;
   const int wpr = (cols + 31) / 32;
-  { int rc = rbv_fill32(c, c->rowcount, 0u, (size_t)B * rows); if (rc != RBV_OK) return rc; }
+  // c->rowcount is all zero here: cleared at creation and by every k_detect_scan after it has consumed the counts
   dim3 g1((cols + DT_W - 1) / DT_W, (rows + DT_H - 1) / DT_H, B);
   float4* fit = reinterpret_cast<float4*>(c->rowsum);   // rowsum + bufB are one contiguous 4*B*N float scratch, free after the scale space
   RBV_LAUNCH(c, k_detect_flags, (g1), (256), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, fit, P, wpr);

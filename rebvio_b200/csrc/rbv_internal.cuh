@@ -148,6 +148,8 @@ struct rbv_ctx {
   void* prof;                       // ProfState* (rbv_api.cu)
   int seq_fused;                    // inside rbv_track_g1/g2: k_rotate zeroes the lane counters, the stages skip k_zero_cnt
   rbv_map* seq_new;                 // rbv_track_g2: map whose keyline count / auto threshold ride home in lane_cnt slots 4, 5
+  const float* seq_resolve_agg;     // rbv_track_g1: block aggregates of the last tryVel call, for k_fwd_link to clear the residual markers
+  int seq_resolve_kpb;
   int seq_reg_pending;              // rbv_track_g2: regularize1Iter's write phase is pending and will be done by k_kalman
   int seq_min_matches;              // rbv_track_g2: lanes whose directed-match count is below this skip regularise + Kalman (0 = off)
   void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed

@@ -1017,7 +1017,9 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else { RBV_LAUNCH(c, k_tryvel_fast4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
 #undef RBV_TV_ARGS
-    if (lm_call < 0 || lm_call == P.iterations)
+    if (c->seq_fused && lm_call == P.iterations) {   // rbv_track_g1: k_fwd_link (next over the same keylines) clears the markers
+      c->seq_resolve_agg = agg_cur; c->seq_resolve_kpb = TV_TPB * kpt;
+    } else if (lm_call < 0 || lm_call == P.iterations)
       RBV_LAUNCH(c, k_residual_resolve, (dim3(nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_cur, nblk, P.kmax, TV_TPB * kpt);
     c->tv_parity = 1 - c->tv_parity;
   }
@@ -1030,16 +1032,21 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
 // overwrite the target unless the target already holds a larger rho; the count includes overwrites. Parallel form:
 // (a) every old keyline with a forward match pushes itself on a per-target list (atomicExch), (b) one thread per
 // target replays its (short) list in ascending index order with the reference's rule, so result and count are exact.
-__global__ void k_fwd_link(KeylineSoA Ko, const int* __restrict__ count_o, int* __restrict__ head, int* __restrict__ next, int kmax) {
+__global__ void k_fwd_link(KeylineSoA Ko, const int* __restrict__ count_o, int* __restrict__ head, int* __restrict__ next, int kmax,
+                           const float* __restrict__ agg, int nblk, int kpb) {
   const int b = blockIdx.y, idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= count_o[b]) return;
   const size_t base = (size_t)b * kmax;
+  if (agg) {   // rbv_track_g1: k_residual_resolve's job rides along (same thread-per-old-keyline shape, one launch less)
+    const size_t o = base + idx;
+    if (Ko.residual[o] < 0.0f) Ko.residual[o] = residual_lookback(agg + (size_t)b * nblk, idx / kpb);
+  }
   const int f = Ko.match_fwd[base + idx];
   if (f < 0) return;
   next[base + idx] = atomicExch(&head[base + f], idx);
 }
 
-__global__ void k_fwd_resolve(KeylineSoA Ko, KeylineSoA Kn, const int* __restrict__ count_n, const int* __restrict__ head,
+__global__ void k_fwd_resolve(KeylineSoA Ko, KeylineSoA Kn, const int* __restrict__ count_n, int* __restrict__ head,
                               const int* __restrict__ next, int* __restrict__ lane_cnt, int kmax) {
   const int b = blockIdx.y, f = blockIdx.x * blockDim.x + threadIdx.x;
   int writes = 0;
@@ -1047,6 +1054,7 @@ __global__ void k_fwd_resolve(KeylineSoA Ko, KeylineSoA Kn, const int* __restric
     const size_t base = (size_t)b * kmax;
     const int h = head[base + f];
     if (h >= 0) {
+      head[base + f] = -1;   // consumed: the head table is left empty for the next frame (no fill launch per frame)
       int match_id = Kn.match_id[base + f];
       float rho = Kn.rho[base + f];
       int last = -1, winner = -1;
@@ -1088,10 +1096,12 @@ __global__ void k_zero_cnt(int* lane_cnt, int slot, unsigned long long* probes) 
 
 int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
   const DevParams& P = c->P;
-  { int rc = rbv_fill32(c, c->fwd_head, 0xFFFFFFFFu, (size_t)P.lanes * P.kmax); if (rc != RBV_OK) return rc; }
+  // c->fwd_head is all -1 here: filled at creation, and k_fwd_resolve empties every list it replays
   if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_FWD, nullptr);
   dim3 g((P.keylines_max + 255) / 256, P.lanes);
-  RBV_LAUNCH(c, k_fwd_link, (g), (256), 0, old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax);
+  RBV_LAUNCH(c, k_fwd_link, (g), (256), 0, old_map->k, old_map->count, c->fwd_head, c->fwd_next, P.kmax,
+             c->seq_resolve_agg, c->nblk, c->seq_resolve_kpb);
+  c->seq_resolve_agg = nullptr;
   RBV_LAUNCH(c, k_fwd_resolve, (g), (256), 0, old_map->k, new_map->k, new_map->count, c->fwd_head, c->fwd_next, c->lane_cnt, P.kmax);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;

@@ -457,9 +457,10 @@ def test_fused_tracker_sequences_equal_stage_calls(mode):
             ctx.regularize1Iter(b)
             ctx.updateInverseDepth(V)
         res.append(dict(Vg=np.array(Vg), PVg=np.array(PVg), Wx=np.array(Wx), X=np.array(X), n=np.array(n), kf=np.array(kf),
-                        a=[a.keylines(l)[0].tobytes() for l in range(B)], b=[b.keylines(l)[0].tobytes() for l in range(B)]))
+                        a=[a.keylines(l)[0].tobytes() for l in range(B)], b=[b.keylines(l)[0].tobytes() for l in range(B)],
+                        res=[a.residuals(l).tobytes() for l in range(B)]))
         ctx.close()
     for key in ("Vg", "PVg", "Wx", "X", "n", "kf"):
         assert np.array_equal(H.bits(np.asarray(res[0][key], np.float32)), H.bits(np.asarray(res[1][key], np.float32))), key
-    assert res[0]["a"] == res[1]["a"] and res[0]["b"] == res[1]["b"]
+    assert res[0]["a"] == res[1]["a"] and res[0]["b"] == res[1]["b"] and res[0]["res"] == res[1]["res"]
     assert int(res[0]["n"][0]) > 500
