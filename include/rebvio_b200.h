@@ -14,6 +14,9 @@
  *     B = 1 is the reference's single-stream shape.
  *   - host pointers may be pageable or pinned; calls are asynchronous on the context's CUDA stream unless
  *     they return data to the host, in which case they synchronise that stream before returning.
+ *   - thread safety: every call that takes an rbv_ctx* holds that context's lock while it runs, so the reference's
+ *     acquisition and estimation threads (rebvio.cpp:98-99) may share one context; calls are serialised in arrival
+ *     order. rbv_last_error() is per thread. rbv_destroy must not race with other calls on the same context.
  *   - there is NO CPU fallback: if no sm_100 device / kernel image is usable, rbv_create fails with
  *     RBV_ERR_CUDA and rbv_last_error() says why.
  */

@@ -7,10 +7,12 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 #include "rbv_internal.cuh"
 
+#define LOCK_CTX(c) std::lock_guard<std::recursive_mutex> ctx_lock_(*static_cast<std::recursive_mutex*>((c)->mtx))
 void rbv_graphs_clear(rbv_ctx* c, const void* map);   // drop captured graphs (all, or those that touch `map`)
 
 static thread_local char g_err[512] = "";
@@ -132,6 +134,7 @@ extern "C" int rbv_kernel_count(void) { return KID_COUNT; }
 extern "C" const char* rbv_kernel_name(int kid) { return (kid >= 0 && kid < KID_COUNT) ? g_kernel_names[kid] : ""; }
 extern "C" int rbv_profile_set(rbv_ctx* c, int mode) {
   if (!c || mode < -2 || mode >= KID_COUNT) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   prof_drain(c);
   if (!c->prof) { ProfState* p = new ProfState(); memset(p, 0, sizeof(*p)); c->prof = p; }
   c->prof_mode = mode;
@@ -139,6 +142,7 @@ extern "C" int rbv_profile_set(rbv_ctx* c, int mode) {
 }
 extern "C" int rbv_profile_reset(rbv_ctx* c) {
   if (!c) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   prof_drain(c);
   if (c->prof) { ProfState* p = static_cast<ProfState*>(c->prof); memset(p->ms, 0, sizeof(p->ms)); memset(p->n, 0, sizeof(p->n)); }
   memset(c->klaunch, 0, sizeof(c->klaunch));
@@ -146,6 +150,7 @@ extern "C" int rbv_profile_reset(rbv_ctx* c) {
 }
 extern "C" int rbv_profile_read(rbv_ctx* c, int kid, double* total_ms, unsigned long long* timed_launches, unsigned long long* launches) {
   if (!c || kid < 0 || kid >= KID_COUNT) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   prof_drain(c);
   ProfState* p = static_cast<ProfState*>(c->prof);
   if (total_ms) *total_ms = p ? p->ms[kid] : 0.0;
@@ -210,6 +215,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaSetDevice(device));
   rbv_ctx* c = new rbv_ctx();
   memset(c, 0, sizeof(*c));
+  c->mtx = new std::recursive_mutex();
   c->cam = *cam; c->det = *det; c->mapc = *map; c->core = *core;
   c->device = device;
   c->reduce_mode = RBV_REDUCE_FAST;
@@ -332,6 +338,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
     if (c->raw_free[i]) cudaEventDestroy(c->raw_free[i]);
   }
   if (c->own_stream) cudaStreamDestroy(c->stream);
+  delete static_cast<std::recursive_mutex*>(c->mtx);
   delete c;
 }
 
@@ -342,12 +349,14 @@ extern "C" int rbv_sync(rbv_ctx* c) {
 }
 extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
   if (!c || (mode != RBV_REDUCE_FAST && mode != RBV_REDUCE_ORDERED)) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   rbv_graphs_clear(c, nullptr);
   c->reduce_mode = mode;
   return RBV_OK;
 }
 extern "C" int rbv_set_tuning(rbv_ctx* c, int key, int value) {
   if (!c || key < 0 || key >= RBV_TUNE_COUNT || value < 0 || value > 64) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   rbv_graphs_clear(c, nullptr);
   c->tune[key] = value;
   return RBV_OK;
@@ -355,6 +364,7 @@ extern "C" int rbv_set_tuning(rbv_ctx* c, int key, int value) {
 extern "C" int rbv_lanes(const rbv_ctx* c) { return c ? c->P.lanes : 0; }
 extern "C" int rbv_set_stream(rbv_ctx* c, void* cuda_stream) {
   if (!c) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   rbv_graphs_clear(c, nullptr);
   if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
@@ -366,6 +376,7 @@ extern "C" unsigned long long rbv_launch_count(const rbv_ctx* c) { return c ? c-
 // ---- maps ----
 extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
   if (!c || !out) return RBV_ERR_ARG;
+  LOCK_CTX(c);
   RBV_CUDA(cudaSetDevice(c->device));
   const size_t B = c->P.lanes, K = c->P.kmax, N = c->P.npix;
   rbv_map* m = new rbv_map();
@@ -398,6 +409,8 @@ extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
 
 extern "C" void rbv_map_release(rbv_ctx* c, rbv_map* m) {
   if (!m) return;
+  std::unique_lock<std::recursive_mutex> lk;
+  if (c) lk = std::unique_lock<std::recursive_mutex>(*static_cast<std::recursive_mutex*>(c->mtx));
   if (c) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); if (c->field_map == m) c->field_map = nullptr; rbv_graphs_clear(c, m); }
   cudaFree(m->slab);
   free(m->ts_us);
@@ -432,7 +445,12 @@ static int fetch_cnt(rbv_ctx* c) {
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   return RBV_OK;
 }
-#define CHECK_CTX(c) do { if (!(c)) { rbv_set_error("null context"); return RBV_ERR_ARG; } RBV_CUDA(cudaSetDevice((c)->device)); } while (0)
+// entry guard: null check, per-context lock (held to the end of the calling function; recursive because entry points call each
+// other), device selection
+#define CHECK_CTX(c)                                                        \
+  if (!(c)) { rbv_set_error("null context"); return RBV_ERR_ARG; }          \
+  LOCK_CTX(c);                                                              \
+  RBV_CUDA(cudaSetDevice((c)->device))
 #define TRY(x) do { int rc_ = (x); if (rc_ != RBV_OK) return rc_; } while (0)
 
 

@@ -152,6 +152,8 @@ struct rbv_ctx {
   int seq_resolve_kpb;
   int seq_reg_pending;              // rbv_track_g2: regularize1Iter's write phase is pending and will be done by k_kalman
   int seq_min_matches;              // rbv_track_g2: lanes whose directed-match count is below this skip regularise + Kalman (0 = off)
+  void* mtx;                        // std::recursive_mutex*: every C-ABI entry locks its context (the reference calls detect and the
+                                    // tracker stages from two threads, rebvio.cpp:28-29)
   void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed
 };
 

@@ -464,3 +464,64 @@ def test_fused_tracker_sequences_equal_stage_calls(mode):
         assert np.array_equal(H.bits(np.asarray(res[0][key], np.float32)), H.bits(np.asarray(res[1][key], np.float32))), key
     assert res[0]["a"] == res[1]["a"] and res[0]["b"] == res[1]["b"] and res[0]["res"] == res[1]["res"]
     assert int(res[0]["n"][0]) > 500
+
+
+def test_detector_and_tracker_threads_share_one_context():
+    """The reference runs the edge detector and the tracker on two threads (rebvio.cpp:98-99 start them, the pipeline ring
+    hands maps across).  Two Python threads (ctypes drops the GIL inside each call) drive ONE context the same way - one
+    detects frames ahead into fresh maps, the other tracks consecutive pairs - and every output is bit-identical to the same
+    sequence driven from one thread: calls on a context are serialised by its lock, whatever the interleaving."""
+    import queue, threading
+    nf = 10
+    spec, frames, R_rel = common.sequence("C5:320x240", nf)
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+    B = 2
+    imgs = [np.ascontiguousarray(np.broadcast_to(np.asarray(f, np.float32), (B,) + f.shape)) for f in frames]
+    thr = np.full(B, det.threshold, np.float32)
+    Rs = [np.ascontiguousarray(np.broadcast_to(np.asarray(R_rel[k], np.float32), (B, 3, 3))) for k in range(nf)]
+
+    def pack(out, new):
+        return tuple(np.asarray(out[k]).tobytes() for k in ("Vg", "P_Vg", "Wx", "X", "ok", "V", "matches", "kf_matches",
+                                                            "keylines", "auto_threshold")) + (new.keylines(1)[0].tobytes(),)
+
+    ctx = host.Context(cam, det, mapc, core, lanes=B, reduce_mode=capi.REDUCE_FAST)
+    serial, maps = [], []
+    for k in range(nf):
+        m, _, _ = ctx.detect(imgs[k], thr, want_counts=False)
+        maps.append(m)
+        if k:
+            serial.append(pack(ctx.track(maps[k - 1], m, Rs[k], 40.0, 10), m))
+    for m in maps: m.release()
+    ctx.close()
+
+    for trial in range(3):
+        ctx = host.Context(cam, det, mapc, core, lanes=B, reduce_mode=capi.REDUCE_FAST)
+        q, got, errs = queue.Queue(maxsize=3), [], []
+
+        def detector():
+            try:
+                for k in range(nf):
+                    q.put(ctx.detect(imgs[k], thr, want_counts=False)[0])
+            except Exception as e:  # pragma: no cover
+                errs.append(e)
+            q.put(None)
+
+        def tracker():
+            try:
+                old, k = q.get(), 1
+                while True:
+                    new = q.get()
+                    if new is None: break
+                    got.append(pack(ctx.track(old, new, Rs[k], 40.0, 10), new))
+                    old.release(); old = new; k += 1
+            except Exception as e:  # pragma: no cover
+                errs.append(e)
+
+        ta, tb = threading.Thread(target=detector), threading.Thread(target=tracker)
+        ta.start(); tb.start(); ta.join(120); tb.join(120)
+        assert not ta.is_alive() and not tb.is_alive()
+        ctx.close()
+        assert errs == []
+        assert got == serial, trial
