@@ -273,6 +273,58 @@ int rbv_track(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const float* R9,
               float* Vg3, float* PVg9, float* Wx36, float* X6, int* ok, float* V3, int* n_matches, int* kf_matches,
               int* n_keylines_new, float* auto_threshold_new);
 
+/* ---- IMU fusion block on the device --------------------------------------------------------
+ * The part of Rebvio::stateEstimationProcess between the tracker's two halves, per lane and device-resident:
+ * gyro-bias initialisation and pre-rotation (rebvio.cpp:146-165), Core::gyroBiasCorrection (core.cpp:264-287),
+ * Core::estimateLs4Acceleration / estimateMeanAcceleration (core.cpp:289-352), Core::estimateBias + SABEstimator
+ * (core.cpp:355-414, sab_estimator.cpp:21-165), the composition of R, Rgva and V (rebvio.cpp:183-233) and the
+ * incremental pose (rebvio.cpp:255-268). The IMU sample integrator (types::IntegratedImu, imu.hpp:33-150) stays on
+ * the host: its result is the per-frame input below.                                                              */
+typedef struct rbv_imu_cfg {            /* types::ImuStateConfig, imu.hpp:153-168 */
+  float g_norm, g_uncertainty, g_norm_uncertainty, acc_std_dev, gyro_std_dev, gyro_bias_std_dev, vbias_std_dev;
+  float scale_std_dev_mult, scale_std_dev_max, scale_stdd_dev_init;
+  int init_bias, init_bias_frame_num;
+  float init_bias_guess[3];
+} rbv_imu_cfg;
+void rbv_default_imu_cfg(rbv_imu_cfg* cfg);
+
+typedef struct rbv_imu_in {             /* one lane, one frame: IntegratedImu::get() of the NEW map (rebvio.cpp:145) */
+  float R[9];                           /* R()      integrated gyro rotation, row-major */
+  float gyro[3];                        /* gyro()   mean rate */
+  float cacc[3];                        /* cacc()   compensated mean acceleration */
+  float dt_s;                           /* dt_s()   integration interval */
+  float frame_dt;                       /* (new ts - old ts) / 1e6, rebvio.cpp:182 */
+} rbv_imu_in;
+
+typedef struct rbv_imu_out {            /* one lane, one frame */
+  float Rt[9];                          /* R.T() handed to the first rotateKeylines (rebvio.cpp:163-165) */
+  float R[9], R0[9], Rgva[9];           /* R after the visual correction; the rotation applied by the second
+                                           rotateKeylines (R0 or R0gva); Rgva (rebvio.cpp:192-231) */
+  float V[3], P_V[9];                   /* translation and covariance handed to directedMatch */
+  float Xgv[6], Xgva[6];
+  float Bg[3], Av[3], As[3], X[7];      /* gyro bias, visual / sensed acceleration, filter state after the frame */
+  float orientation[3], position[3];    /* types::Odometry (rebvio.cpp:270-273) */
+  float K;                              /* scale (rebvio.cpp:215) */
+  int initialized, stopped, num_frames; /* stopped: 1 = NaN in V (rebvio.cpp:236-241) */
+} rbv_imu_out;
+
+/* (re)create the per-lane filter state = the state of a freshly constructed Rebvio (rebvio.hpp:92-101,
+ * rebvio.cpp:95-115, sab_estimator.hpp:56-71). Must precede the calls below. */
+int rbv_imu_reset(rbv_ctx* ctx, const rbv_imu_cfg* cfg);
+/* stage call 1 (rebvio.cpp:146-165): bias initialisation, R = imu.R corrected by the bias. Rt9 [B][9] (may be NULL)
+ * receives R.T(), the argument of the first rotateKeylines; it is also left in the device slot rbv_track_imu uses. */
+int rbv_imu_prerotate(rbv_ctx* ctx, const rbv_imu_in* in /*[B]*/, float* Rt9);
+/* stage call 2 (rebvio.cpp:183-233, 255-273): everything between extRotVel and the second rotateKeylines, plus
+ * the pose. Inputs are the tracker's results [B][..]: Vg3 (minimizeVel), Wx36 / X6 (extRotVel). */
+int rbv_imu_fuse(rbv_ctx* ctx, const float* Vg3, const float* Wx36, const float* X6, rbv_imu_out* out /*[B]*/);
+/* One tracker frame with the IMU filters, kernels only: prerotate, first half (rbv_track_g1's sequence), fuse,
+ * second half (rbv_track_g2's sequence), ONE device synchronisation at the end. Outputs as rbv_track (any may be
+ * NULL) plus the fusion record per lane. Lanes whose directed-match count is below min_matches skip regularise and
+ * Kalman update as in rbv_track_g2; the caller stops such a lane (rebvio.cpp:247-252).                            */
+int rbv_track_imu(rbv_ctx* ctx, rbv_map* old_map, rbv_map* new_map, const rbv_imu_in* in, float max_radius,
+                  int min_matches, float* Vg3, float* PVg9, float* Wx36, float* X6, int* ok, rbv_imu_out* out,
+                  int* n_matches, int* kf_matches, int* n_keylines_new, float* auto_threshold_new);
+
 /* ---- host mirror (EdgeMap::keylines(), operator[], mask(), size(), threshold(); edge_map.hpp:40-75) ---- */
 
 int rbv_map_size(rbv_ctx* ctx, rbv_map* map, int* n_keylines /*[B]*/);

@@ -63,7 +63,9 @@ class FrameOut(C.Structure):
                 ("K", C.c_float), ("frame_dt", C.c_float), ("n_new", C.c_int), ("n_old", C.c_int),
                 ("fwd_matches", C.c_int), ("klm_num", C.c_int), ("kf_matches", C.c_int), ("reg_num", C.c_int),
                 ("ok", C.c_int), ("estimated", C.c_int), ("stopped", C.c_int), ("old_map", C.c_int),
-                ("new_map", C.c_int)]
+                ("new_map", C.c_int), ("imu_R", C.c_float * 9), ("imu_gyro", C.c_float * 3), ("imu_cacc", C.c_float * 3),
+                ("imu_dt_s", C.c_float), ("Bg", C.c_float * 3), ("Av", C.c_float * 3), ("As", C.c_float * 3),
+                ("sabX", C.c_float * 7), ("Rt1", C.c_float * 9), ("initialized", C.c_int)]
 
 
 def default_cfgs(cam=None, det=None, core=None, mapc=None):

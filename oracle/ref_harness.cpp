@@ -374,6 +374,10 @@ struct ref_frame_out {
   float score, K, frame_dt;
   int n_new, n_old, fwd_matches, klm_num, kf_matches, reg_num, ok, estimated, stopped;
   int old_map, new_map;
+  // the IMU fusion block's inputs (IntegratedImu::get of the new map) and filter state after the frame
+  float imu_R[9], imu_gyro[3], imu_cacc[3], imu_dt_s;
+  float Bg[3], Av[3], As[3], sabX[7], Rt1[9];
+  int initialized;
 };
 
 // One image: Rebvio::dataAcquisitionProcess body (rebvio.cpp:63-84), then — if two maps are queued — one
@@ -443,8 +447,12 @@ int ref_pipeline_frame(void* h, const float* img, uint64_t ts_us, ref_frame_out*
     }
   }
 
+  from_m3(imu.R(), out->imu_R);
+  for (int i = 0; i < 3; ++i) { out->imu_gyro[i] = imu.gyro()[i]; out->imu_cacc[i] = imu.cacc()[i]; }
+  out->imu_dt_s = imu.dt_s();
   R = imu.R();
   R.T() = TooN::SO3<Float>(imu_state_.Bg) * R.T();
+  { types::Matrix3f Rt1 = R.T(); from_m3(Rt1, out->Rt1); }
   ts0 = now_s();
   old_edge_map->rotateKeylines(R.T());
   c->t_stage[1] += now_s() - ts0;
@@ -545,6 +553,9 @@ int ref_pipeline_frame(void* h, const float* img, uint64_t ts_us, ref_frame_out*
   }
   out->klm_num = klm_num;
   out->kf_matches = num_kf_back_m;
+  for (int i = 0; i < 3; ++i) { out->Bg[i] = imu_state_.Bg[i]; out->Av[i] = imu_state_.Av[i]; out->As[i] = imu_state_.As[i]; }
+  for (int i = 0; i < 7; ++i) out->sabX[i] = sab_state_.X[i];
+  out->initialized = imu_state_.initialized ? 1 : 0;
 
   if (c->num_frames > 4 + (unsigned)icfg.init_bias_frame_num) {
     imu_state_.u_est = Rgva.T() * imu_state_.u_est;

@@ -31,6 +31,24 @@ class MapCfg(C.Structure):
                 ("match_threshold_angle", C.c_float), ("regularization_threshold", C.c_float)]
 
 
+class ImuCfg(C.Structure):
+    """types::ImuStateConfig (reference imu.hpp:153-168)"""
+    _fields_ = [(n, C.c_float) for n in ("g_norm", "g_uncertainty", "g_norm_uncertainty", "acc_std_dev", "gyro_std_dev",
+                                         "gyro_bias_std_dev", "vbias_std_dev", "scale_std_dev_mult", "scale_std_dev_max",
+                                         "scale_stdd_dev_init")] + \
+               [("init_bias", C.c_int), ("init_bias_frame_num", C.c_int), ("init_bias_guess", C.c_float * 3)]
+
+
+# numpy mirrors of rbv_imu_in / rbv_imu_out (include/rebvio_b200.h): one record per lane
+IMU_IN = np.dtype([("R", np.float32, 9), ("gyro", np.float32, 3), ("cacc", np.float32, 3), ("dt_s", np.float32),
+                   ("frame_dt", np.float32)])
+IMU_OUT = np.dtype([("Rt", np.float32, 9), ("R", np.float32, 9), ("R0", np.float32, 9), ("Rgva", np.float32, 9),
+                    ("V", np.float32, 3), ("P_V", np.float32, 9), ("Xgv", np.float32, 6), ("Xgva", np.float32, 6),
+                    ("Bg", np.float32, 3), ("Av", np.float32, 3), ("As", np.float32, 3), ("X", np.float32, 7),
+                    ("orientation", np.float32, 3), ("position", np.float32, 3), ("K", np.float32),
+                    ("initialized", np.int32), ("stopped", np.int32), ("num_frames", np.int32)])
+
+
 class CoreCfg(C.Structure):
     _fields_ = [("search_range", C.c_float), ("reweight_distance", C.c_float), ("match_treshold", C.c_float),
                 ("min_match_threshold", C.c_uint), ("iterations", C.c_uint),
@@ -94,6 +112,11 @@ _SIG = {
     "rbv_set_undistort": (C.c_int, [vp, vp, vp]),
     "rbv_visual_fusion": (C.c_int, [C.c_int, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rbv_track": (C.c_int, [vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "rbv_default_imu_cfg": (None, [vp]),
+    "rbv_imu_reset": (C.c_int, [vp, vp]),
+    "rbv_imu_prerotate": (C.c_int, [vp, vp, vp]),
+    "rbv_imu_fuse": (C.c_int, [vp, vp, vp, vp, vp]),
+    "rbv_track_imu": (C.c_int, [vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rbv_map_size": (C.c_int, [vp, vp, vp]),
     "rbv_map_threshold": (C.c_int, [vp, vp, vp]),
     "rbv_map_set_threshold": (C.c_int, [vp, vp, vp]),

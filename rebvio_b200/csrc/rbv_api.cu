@@ -338,6 +338,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
     if (c->raw_free[i]) cudaEventDestroy(c->raw_free[i]);
   }
   if (c->own_stream) cudaStreamDestroy(c->stream);
+  cudaFree(c->imu_state); cudaFree(c->imu_in); cudaFree(c->imu_out); cudaFree(c->imu_stage); cudaFreeHost(c->imu_host);
   delete static_cast<std::recursive_mutex*>(c->mtx);
   delete c;
 }
@@ -924,15 +925,9 @@ extern "C" int rbv_update_inverse_depth(rbv_ctx* c, const float* vel3) {
 }
 
 // ---- fused per-frame sequences (rebvio.cpp:142-177 and :223-259) ----
-extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R9, float* vel3, float* Rvel9, float* Wx36,
-                            float* X6, int* ok) {
-  CHECK_CTX(c);
-  if (!old_map || !new_map || !R9) return RBV_ERR_ARG;
-  int slot;
-  float* h = stage_begin(c, &slot);
-  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R9, 9);   // IN_VEL stays 0: imu_state_.Vg = Zeros (rebvio.cpp:168)
-  TRY(stage_commit(c, slot));
-  TRY(run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
+// first half of a tracker frame as one (graph-replayed) kernel sequence; R.T() in lane_in[IN_R], lane_in[IN_VEL] = 0
+static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
+  return run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
     SeqFused fused(c, 0);
     // two independent branches: the distance field of the NEW map (the longest kernel of the half, instruction bound at ~45 %
     // occupancy) and rotation + sigma_rho quantile + LM seed of the OLD map; they meet in front of the first tryVel
@@ -952,7 +947,29 @@ extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
     TRY(enqueue_minimize(c, old_map, 2));
     TRY(tr_forward_match(c, old_map, new_map));
     return tr_ext_rot_vel(c, new_map, 1);
-  }));
+  });
+}
+
+// second half; R0, V, P_V, Rgva, max_radius in lane_in
+static int enqueue_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, int min_matches) {
+  return run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
+    SeqFused fused(c, min_matches, new_map);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
+    TRY(tr_rotate(c, old_map));
+    TRY(tr_directed_match(c, new_map, old_map));
+    TRY(tr_regularize(c, new_map));
+    return tr_kalman(c, new_map);
+  });
+}
+
+extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const float* R9, float* vel3, float* Rvel9, float* Wx36,
+                            float* X6, int* ok) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map || !R9) return RBV_ERR_ARG;
+  int slot;
+  float* h = stage_begin(c, &slot);
+  for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R9, 9);   // IN_VEL stays 0: imu_state_.Vg = Zeros (rebvio.cpp:168)
+  TRY(stage_commit(c, slot));
+  TRY(enqueue_g1(c, old_map, new_map));
   c->field_map = new_map;   // tr_build_field's host-side effect, also when the sequence was replayed
   RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * (size_t)c->P.lanes * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
   TRY(fetch_lm(c, vel3, Rvel9, nullptr));
@@ -970,13 +987,7 @@ extern "C" int rbv_track_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   for (int b = 0; b < c->P.lanes; ++b) put(h, b, IN_R, R0_9, 9);
   put_directed(c, h, V3, PV9, Rgva9, max_radius);
   TRY(stage_commit(c, slot));
-  TRY(run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
-    SeqFused fused(c, min_matches, new_map);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
-    TRY(tr_rotate(c, old_map));
-    TRY(tr_directed_match(c, new_map, old_map));
-    TRY(tr_regularize(c, new_map));
-    return tr_kalman(c, new_map);
-  }));
+  TRY(enqueue_g2(c, old_map, new_map, min_matches));
   TRY(fetch_cnt(c));
   for (int b = 0; b < c->P.lanes; ++b) {
     if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
@@ -1081,6 +1092,99 @@ extern "C" int rbv_track(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const f
     if (n_keylines_new) n_keylines_new[b] = c->h_cnt[b * CNT_STRIDE + CNT_NKEY];
     if (auto_threshold_new) memcpy(auto_threshold_new + b, c->h_cnt + b * CNT_STRIDE + CNT_ATHR, sizeof(float));
   }
+  return RBV_OK;
+}
+
+// ---- IMU fusion block (rbv_fusion.cu) ----
+extern "C" void rbv_default_imu_cfg(rbv_imu_cfg* cfg) {   // types::ImuStateConfig, imu.hpp:153-168
+  if (!cfg) return;
+  *cfg = rbv_imu_cfg{9.81f, 2e-3f, 0.2e3f, 2.0e-3f, 1.6968e-04f, 1.9393e-05f, 1e-7f, 1e-2f, 1e-4f, 1.2e-3f, 1, 10, {0.0188f, 0.0037f, 0.0776f}};
+}
+
+extern "C" int rbv_imu_reset(rbv_ctx* c, const rbv_imu_cfg* cfg) {
+  CHECK_CTX(c);
+  if (!cfg) return RBV_ERR_ARG;
+  return fu_reset(c, cfg);
+}
+
+static int imu_ready(rbv_ctx* c) {
+  if (!c->imu_state) { rbv_set_error("IMU fusion call before rbv_imu_reset"); return RBV_ERR_STATE; }
+  return RBV_OK;
+}
+static rbv_imu_in* imu_host_in(rbv_ctx* c) { return static_cast<rbv_imu_in*>(c->imu_host); }
+static rbv_imu_out* imu_host_out(rbv_ctx* c) { return reinterpret_cast<rbv_imu_out*>(imu_host_in(c) + c->P.lanes); }
+static float* imu_host_stage(rbv_ctx* c) { return reinterpret_cast<float*>(imu_host_out(c) + c->P.lanes); }
+
+extern "C" int rbv_imu_prerotate(rbv_ctx* c, const rbv_imu_in* in, float* Rt9) {
+  CHECK_CTX(c);
+  if (!in) return RBV_ERR_ARG;
+  TRY(imu_ready(c));
+  const size_t B = c->P.lanes;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));   // the pinned mirror is reused every call
+  memcpy(imu_host_in(c), in, sizeof(rbv_imu_in) * B);
+  RBV_CUDA(cudaMemcpyAsync(c->imu_in, imu_host_in(c), sizeof(rbv_imu_in) * B, cudaMemcpyHostToDevice, c->stream));
+  TRY(fu_pre(c));
+  if (Rt9) {
+    RBV_CUDA(cudaMemcpyAsync(imu_host_out(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaStreamSynchronize(c->stream));
+    for (size_t b = 0; b < B; ++b) memcpy(Rt9 + b * 9, imu_host_out(c)[b].Rt, 36);
+  }
+  return RBV_OK;
+}
+
+extern "C" int rbv_imu_fuse(rbv_ctx* c, const float* Vg3, const float* Wx36, const float* X6, rbv_imu_out* out) {
+  CHECK_CTX(c);
+  if (!Vg3 || !Wx36 || !X6 || !out) return RBV_ERR_ARG;
+  TRY(imu_ready(c));
+  const size_t B = c->P.lanes;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  float* h = imu_host_stage(c);
+  for (size_t b = 0; b < B; ++b) {
+    memcpy(h + b * 48, Vg3 + b * 3, 12);
+    memcpy(h + b * 48 + 3, Wx36 + b * 36, 144);
+    memcpy(h + b * 48 + 39, X6 + b * 6, 24);
+  }
+  RBV_CUDA(cudaMemcpyAsync(c->imu_stage, h, sizeof(float) * 48 * B, cudaMemcpyHostToDevice, c->stream));
+  float max_radius = 0.0f;   // the stage call leaves lane_in[IN_MAXRADIUS] to rbv_directed_match / rbv_track_g2
+  TRY(fu_fuse(c, c->imu_stage, 48, c->imu_stage + 3, 48, c->imu_stage + 39, 48, max_radius));
+  RBV_CUDA(cudaMemcpyAsync(imu_host_out(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  memcpy(out, imu_host_out(c), sizeof(rbv_imu_out) * B);
+  return RBV_OK;
+}
+
+extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const rbv_imu_in* in, float max_radius,
+                             int min_matches, float* Vg3, float* PVg9, float* Wx36, float* X6, int* ok, rbv_imu_out* out,
+                             int* n_matches, int* kf_matches, int* n_keylines_new, float* auto_threshold_new) {
+  CHECK_CTX(c);
+  if (!old_map || !new_map || !in) return RBV_ERR_ARG;
+  TRY(imu_ready(c));
+  const size_t B = c->P.lanes;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  memcpy(imu_host_in(c), in, sizeof(rbv_imu_in) * B);
+  RBV_CUDA(cudaMemcpyAsync(c->imu_in, imu_host_in(c), sizeof(rbv_imu_in) * B, cudaMemcpyHostToDevice, c->stream));
+  TRY(fu_pre(c));
+  TRY(enqueue_g1(c, old_map, new_map));
+  c->field_map = new_map;
+  TRY(fu_fuse(c, c->lm[0].vel, (int)(sizeof(LMState) / sizeof(float)), c->lane_out + OUT_WX, OUT_STRIDE, c->lane_out + OUT_X,
+              OUT_STRIDE, max_radius));
+  // the tracker's first-half results leave the device before the second half may overwrite them (same stream: ordered)
+  RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * B * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(c->h_lm, c->lm, sizeof(LMState) * B, cudaMemcpyDeviceToHost, c->stream));
+  TRY(enqueue_g2(c, old_map, new_map, min_matches));
+  RBV_CUDA(cudaMemcpyAsync(imu_host_out(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
+  TRY(fetch_cnt(c));   // synchronises
+  const LMState* L = reinterpret_cast<const LMState*>(c->h_lm);
+  for (size_t b = 0; b < B; ++b) {
+    if (Vg3) memcpy(Vg3 + b * 3, L[b].vel, 12);
+    if (PVg9) memcpy(PVg9 + b * 9, L[b].Rvel, 36);
+    if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
+    if (kf_matches) kf_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_KF];
+    if (n_keylines_new) n_keylines_new[b] = c->h_cnt[b * CNT_STRIDE + CNT_NKEY];
+    if (auto_threshold_new) memcpy(auto_threshold_new + b, c->h_cnt + b * CNT_STRIDE + CNT_ATHR, sizeof(float));
+  }
+  copy_extrot_out(c, Wx36, X6, ok);
+  if (out) memcpy(out, imu_host_out(c), sizeof(rbv_imu_out) * B);
   return RBV_OK;
 }
 

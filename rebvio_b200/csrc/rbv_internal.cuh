@@ -154,6 +154,9 @@ struct rbv_ctx {
   int seq_min_matches;              // rbv_track_g2: lanes whose directed-match count is below this skip regularise + Kalman (0 = off)
   void* mtx;                        // std::recursive_mutex*: every C-ABI entry locks its context (the reference calls detect and the
                                     // tracker stages from two threads, rebvio.cpp:28-29)
+  void *imu_state, *imu_in, *imu_out, *imu_host;   // IMU fusion block (rbv_fusion.cu): per-lane ImuLane, per-frame rbv_imu_in / rbv_imu_out, pinned mirror
+  float* imu_stage;                 // [B][48] tracker results handed to the stage call rbv_imu_fuse (Vg 3, Wx 36, X 6)
+  rbv_imu_cfg imu_cfg;
   void* graphs;                     // GraphCache* (rbv_api.cu): captured stage sequences, see run_graphed
 };
 
@@ -172,7 +175,8 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_fwd_link) X(k_fwd_resolve) X(k_extrot_rows) X(k_extrot_reduce) X(k_directed) X(k_reg_eval) X(k_reg_apply)    \
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
-  X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort)
+  X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
+  X(k_imu_pre) X(k_imu_fuse)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
@@ -219,6 +223,12 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm);
 int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map);
 int tr_regularize(rbv_ctx* c, rbv_map* map);
 int tr_kalman(rbv_ctx* c, rbv_map* map);                   // vel in lane_in[IN_VEL]
+
+// IMU fusion block (rbv_fusion.cu)
+int fu_reset(rbv_ctx* c, const rbv_imu_cfg* cfg);
+int fu_pre(rbv_ctx* c);                                    // rbv_imu_in in c->imu_in -> lane_in[IN_R], lane_in[IN_VEL] = 0
+int fu_fuse(rbv_ctx* c, const float* vg, int vg_stride, const float* wx, int wx_stride, const float* x, int x_stride,
+            float max_radius);                             // -> lane_in[IN_R, IN_VEL, IN_RVEL, IN_RBACK, IN_MAXRADIUS], c->imu_out
 
 // ---- device helpers -------------------------------------------------------------------------------------
 // 3x3 determinant by Gaussian elimination with partial pivoting (TooN determinant.h:91-146)

@@ -254,6 +254,48 @@ class Context:
                                ptr(V), ptr(n), ptr(kf), ptr(nk), ptr(at)))
         return dict(Vg=Vg, P_Vg=PVg, Wx=Wx, X=X, ok=ok, V=V, matches=n, kf_matches=kf, keylines=nk, auto_threshold=at)
 
+    # ---- IMU fusion block (rbv_fusion.cu; reference rebvio.cpp:146-165, 183-233, 255-273; core.cpp:264-414) ----
+    def imu_reset(self, cfg=None):
+        """state of a freshly constructed Rebvio for every lane; cfg = capi.ImuCfg (default: imu.hpp:153-168)"""
+        if cfg is None:
+            cfg = capi.ImuCfg(); self.L.rbv_default_imu_cfg(C.byref(cfg))
+        self.imu_cfg = cfg
+        check(self.L.rbv_imu_reset(self.h, C.byref(cfg)))
+
+    def _imu_in(self, imu_in):
+        a = np.ascontiguousarray(np.broadcast_to(np.asarray(imu_in, capi.IMU_IN).reshape(-1), (self.lanes,)))
+        return a
+
+    def imu_prerotate(self, imu_in):
+        """rebvio.cpp:146-165 -> R.T() [B,3,3], the argument of the first rotateKeylines"""
+        a = self._imu_in(imu_in)
+        Rt = np.zeros((self.lanes, 3, 3), np.float32)
+        check(self.L.rbv_imu_prerotate(self.h, a.ctypes.data, ptr(Rt)))
+        return Rt
+
+    def imu_fuse(self, Vg, Wx, X):
+        """rebvio.cpp:183-233 + pose -> record array (capi.IMU_OUT) per lane"""
+        B = self.lanes
+        Vg = _f32(np.broadcast_to(np.asarray(Vg, np.float32).reshape(-1, 3), (B, 3)), (B, 3))
+        Wx = _f32(np.broadcast_to(np.asarray(Wx, np.float32).reshape(-1, 36), (B, 36)), (B, 36))
+        X = _f32(np.broadcast_to(np.asarray(X, np.float32).reshape(-1, 6), (B, 6)), (B, 6))
+        out = np.zeros(B, capi.IMU_OUT)
+        check(self.L.rbv_imu_fuse(self.h, ptr(Vg), ptr(Wx), ptr(X), out.ctypes.data))
+        return out
+
+    def track_imu(self, old, new, imu_in, max_radius=40.0, min_matches=0):
+        """one tracker frame with the IMU filters, kernels only (rbv_track_imu)"""
+        B = self.lanes
+        a = self._imu_in(imu_in)
+        Vg = np.zeros((B, 3), np.float32); PVg = np.zeros((B, 3, 3), np.float32)
+        Wx = np.zeros((B, 6, 6), np.float32); X = np.zeros((B, 6), np.float32); ok = np.zeros(B, np.int32)
+        n = np.zeros(B, np.int32); kf = np.zeros(B, np.int32); nk = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+        out = np.zeros(B, capi.IMU_OUT)
+        check(self.L.rbv_track_imu(self.h, old.h, new.h, a.ctypes.data, max_radius, min_matches, ptr(Vg), ptr(PVg), ptr(Wx),
+                                   ptr(X), ptr(ok), out.ctypes.data, ptr(n), ptr(kf), ptr(nk), ptr(at)))
+        return dict(Vg=Vg, P_Vg=PVg, Wx=Wx, X=X, ok=ok, imu=out, V=out["V"].copy(), matches=n, kf_matches=kf, keylines=nk,
+                    auto_threshold=at)
+
     # debug taps
     def read_image(self, which, lane=0):
         out = np.empty((self.cam.rows, self.cam.cols), np.float32)

@@ -57,8 +57,13 @@ def visual_fusion(R, Vg, Wx, X):
 
 
 class BatchedPipeline:
-    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None):
+    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None, imu_cfg=None):
+        """imu_cfg: None = visual-only fusion (rbv_track); True or a capi.ImuCfg = the reference's IMU filters on the device
+        (rbv_track_imu; push then takes `imu_in`, the integrated IMU of every lane, instead of R_rel)"""
         self.ctx = host.Context(cam, det, mapc, core, lanes=lanes, device=device, reduce_mode=reduce_mode)
+        self.with_imu = imu_cfg is not None
+        if self.with_imu:
+            self.ctx.imu_reset(None if imu_cfg is True else imu_cfg)
         if cuda_stream is not None:
             self.ctx.set_stream(cuda_stream)
         self.lanes = lanes
@@ -95,7 +100,7 @@ class BatchedPipeline:
         tracker of the current frame. Pass the same array to the next push."""
         capi.check(self.ctx.L.rbv_prefetch_frames(self.ctx.h, self._host_ptrs(frames), 0, int(frames.dtype == np.uint8)))
 
-    def push(self, frames=None, R_rel=None, device_ptr=None, ts_us=None, next_frames=None):
+    def push(self, frames=None, R_rel=None, device_ptr=None, ts_us=None, next_frames=None, imu_in=None):
         """One frame per lane. `frames`: host uint8 [B,rows,cols] as the camera delivers them (converted x3 on the device,
         rebvio.cpp:43) or host float32 (0..765; pageable or pinned) — or `device_ptr`: float32 frames already in device
         memory. R_rel [B,3,3]: rotation of the camera since the previous frame. `next_frames`: the frames of the NEXT
@@ -119,7 +124,10 @@ class BatchedPipeline:
         out = {"keylines": n, "auto_threshold": at}
         if self.have_old:
             old = self.maps[1 - self.cur]
-            out.update(ctx.track(old, new, R_rel, 40.0, self.min_matches))   # g1, host fusion (rbv_visual_fusion), g2
+            if self.with_imu:   # prerotate, g1, IMU fusion kernel, g2: kernels only (imu_in: capi.IMU_IN records per lane)
+                out.update(ctx.track_imu(old, new, imu_in, 40.0, self.min_matches))
+            else:
+                out.update(ctx.track(old, new, R_rel, 40.0, self.min_matches))   # g1, host fusion (rbv_visual_fusion), g2
         self.count = out["keylines"]
         self.have_old = True
         self.cur = 1 - self.cur
