@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--undistort", action="store_true", help="e2e leg: raw camera frames, Camera::undistort (EuRoC cam0 model) on the device")
+    ap.add_argument("--imu", action="store_true", help="run the reference's IMU filters on the device between the tracker halves "
+                    "(rbv_track_imu: gyro-bias correction + scale-attitude-bias filter, SURVEY 8(f2)) instead of the visual-only fusion")
     ap.add_argument("--tune", default="", help="implementation choices, e.g. '2=4,0=1' (rbv_set_tuning key=value pairs)")
     ap.add_argument("--kernel-table", default="", help="write the per-kernel CUDA-event table (one untimed step) here")
     return ap.parse_args()
@@ -260,8 +262,20 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    imu_cfg = True if args.imu else None
+
+    def targs(k, lanes=slice(None)):
+        """tracker arguments of frame k: the inter-frame rotation, or (--imu) an integrated-IMU record per lane built from it
+        (R = R_rel, gravity-only compensated acceleration, 50 ms interval)"""
+        R = np.asarray(R_rel[k, lanes], np.float32)
+        if not args.imu:
+            return dict(R_rel=R)
+        a = np.zeros(R.shape[0], capi.IMU_IN)
+        a["R"] = R.reshape(-1, 9); a["cacc"] = (0.0, -9.81, 0.0); a["dt_s"] = 1.0 / spec.fps; a["frame_dt"] = 1.0 / spec.fps
+        return dict(imu_in=a)
+
     # ---- leg 1: device-resident inputs ----------------------------------------------------------------------
-    pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
+    pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg)
     tune = [tuple(int(x) for x in kv.split("=")) for kv in args.tune.split(",") if kv]
     for key, val in tune:
         pipe.ctx.set_tuning(key, val)
@@ -269,11 +283,11 @@ def run_b200(args):
     pipe.push(device_ptr=ptr(0))
     # warm-up; the first warm-up step runs with every kernel bracketed by CUDA events to find the dominant kernel
     pipe.ctx.profile_reset(); pipe.ctx.profile_set(-2)
-    out = pipe.push(device_ptr=ptr(1), R_rel=R_rel[1])
+    out = pipe.push(device_ptr=ptr(1), **targs(1))
     table = pipe.ctx.profile_read()
     pipe.ctx.profile_set(-1)
     for k in range(2, 1 + W):
-        out = pipe.push(device_ptr=ptr(k), R_rel=R_rel[k])
+        out = pipe.push(device_ptr=ptr(k), **targs(k))
     top = max(table, key=lambda n: table[n][0])
     if args.kernel_table and rank == 0:
         tot = sum(v[0] for v in table.values())
@@ -290,7 +304,7 @@ def run_b200(args):
     barrier()
     ev0.record(stream)
     for k in range(1 + W, 1 + W + K):
-        out = pipe.push(device_ptr=ptr(k), R_rel=R_rel[k])
+        out = pipe.push(device_ptr=ptr(k), **targs(k))
         kl_sum += float(out["keylines"].sum()); match_sum += float(out["matches"].sum())
     ev1.record(stream)
     barrier()
@@ -328,7 +342,8 @@ def run_b200(args):
             "config": {"workload": f"batched replay: {B} independent EuRoC-shaped {spec.cam.cols}x{spec.cam.rows} sequences per GPU "
                                    f"(C2 generator, seeds 1000+64*rank+i), step = 1 frame of every sequence through detect + tracker",
                        "lanes_per_gpu": B, "keylines_per_frame": K_mean, "matches_per_frame": match_sum / (B * K),
-                       "reduce_mode": args.reduce, "parallelism": f"replicas x{world} (no collective)",
+                       "reduce_mode": args.reduce, "fusion": "imu filters on device (rbv_track_imu)" if args.imu else "visual-only (rbv_track)",
+                       "parallelism": f"replicas x{world} (no collective)",
                        "l2": f"per-step working set {B} lanes x ~14 MB >> 126 MB L2 (inputs larger than L2, no flush needed)"},
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
@@ -349,17 +364,17 @@ def run_b200(args):
         h_frames[nf].copy_(frames_u8[nf - 1])
         torch.cuda.synchronize()
         hnp = h_frames.numpy()
-        pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
+        pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg)
         if args.undistort:   # rebvio/include/rebvio/camera.hpp:26-40
             fm = 0.5 * (458.654 + 457.296)
             pipe.ctx.set_undistort([fm, fm, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0])
         pipe.push(frames=hnp[0], next_frames=hnp[1])
         for k in range(1, 1 + W):
-            pipe.push(frames=hnp[k], R_rel=R_rel[k], next_frames=hnp[k + 1])
+            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **targs(k))
         barrier()
         t0 = time.perf_counter()
         for k in range(1 + W, 1 + W + K):
-            pipe.push(frames=hnp[k], R_rel=R_rel[k], next_frames=hnp[k + 1])
+            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **targs(k))
         pipe.ctx.sync()
         t1 = time.perf_counter()
         barrier()
@@ -379,14 +394,14 @@ def run_b200(args):
     # ---- leg 3: single-stream latency (configs[1]) on rank 0 -----------------------------------------------------
     if not args.no_single and rank == 0:
         nfs = min(nf, 1 + W + K)
-        p1 = BatchedPipeline(cam, det, mapc, core, 1, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream)
+        p1 = BatchedPipeline(cam, det, mapc, core, 1, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg)
         lat = []
         p1.push(device_ptr=d_frames[0, 0:1].data_ptr())
         for k in range(1, nfs):
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
-            p1.push(device_ptr=d_frames[k, 0:1].data_ptr(), R_rel=R_rel[k, 0:1])
+            p1.push(device_ptr=d_frames[k, 0:1].data_ptr(), **targs(k, slice(0, 1)))
             b.record(stream)
             torch.cuda.synchronize()
             if k > W:

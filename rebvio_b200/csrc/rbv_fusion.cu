@@ -40,13 +40,18 @@ __device__ void mm(float* C, const float* A, int ars, int acs, const float* B, i
   }
   __syncwarp();
 }
-// same with a double accumulator and double output (TooN promotes after a double scalar factor)
-__device__ void mm_d(double* C, const double* A, int ars, int acs, const float* B, int brs, int bcs, int n, int k, int m) {
-  for (int e = lane_id(); e < n * m; e += 32) {
-    const int i = e / m, j = e - i * m;
-    double s = A[i * ars] * (double)B[j * bcs];
-    for (int q = 1; q < k; ++q) s += A[i * ars + q * acs] * (double)B[q * brs + j * bcs];
-    C[e] = s;
+template <int N, int K, int M>   // compile-time shape: constant divisions, unrolled dot products
+__device__ __forceinline__ void mm(float* C, const float* A, int ars, int acs, const float* B, int brs, int bcs) {
+#pragma unroll
+  for (int e0 = 0; e0 < N * M; e0 += 32) {
+    const int e = e0 + lane_id();
+    if (e < N * M) {
+      const int i = e / M, j = e - i * M;
+      float s = A[i * ars] * B[j * bcs];
+#pragma unroll
+      for (int q = 1; q < K; ++q) s += A[i * ars + q * acs] * B[q * brs + j * bcs];
+      C[e] = s;
+    }
   }
   __syncwarp();
 }
@@ -201,7 +206,7 @@ __device__ void so3_ln(float* r, const float* M) {
 // ---- TooN::SVD<7>(JtJ).backsub(rhs) (sab_estimator.cpp:31-32; double precision, LAPACK dgesvd_ un-vendored) ----
 // Same pair as extRotVel's 6x6 solve (rbv_tracker.cu): FP64 LDL^T when the matrix is provably well inside the
 // conditioning rule of SVD::backsub (1/s_i zeroed when s_i * 1e9 <= s_max; s_max <= trace, s_min >= 1/||A^-1||_F), the
-// cyclic Jacobi pseudo-inverse otherwise. S = symmetrised matrix in shared memory (double, N*N), b = right-hand side.
+// Jacobi pseudo-inverse (solve_jacobi8_warp below) otherwise. S = symmetrised matrix in shared memory (double, N*N), b = right-hand side.
 // Returns x[lane] for lane < N. All 32 lanes must call.
 template <int N>
 __device__ bool solve_ldl_warp(const double* S, const double* b, double& xout) {
@@ -253,67 +258,144 @@ __device__ bool solve_ldl_warp(const double* S, const double* b, double& xout) {
   return ok;
 }
 
-template <int N>
-__device__ double solve_jacobi_warp(const double* S, const double* b) {
-  const int lane = lane_id();
-  const bool act = lane < N;
-  double a[N], v[N];
+// The eigen path: symmetric Jacobi pseudo-inverse, 1/lambda_i zeroed when lambda_i * 1e9 <= lambda_max. It runs 20 times
+// per frame on nearly the same matrix and - the filter's prior information spans 1e-2 .. 1e13 - is the path always taken
+// once the accelerometer filter is active. Three differences to the cyclic one-warp Jacobi of extRotVel (rbv_tracker.cu):
+//  * round-robin ordering on the matrix padded to 8x8 (row/column 7 is zero: one more zero eigenvalue, dropped by the
+//    conditioning rule): the 4 rotations of a round touch disjoint index pairs, every lane computes their 4 (c, s)
+//    together (independent FP64 chains), lane r < 8 owns row r, row pairs are exchanged with one shuffle per element;
+//  * warm start: V of the previous Gauss-Newton iteration diagonalises the new matrix almost completely, so it is
+//    transformed first (V^T A V through shared memory) and the sweeps continue from there (1-2 instead of ~8);
+//  * the sweeps stop when the off-diagonal norm is below 1e-13 of the matrix norm (see the loop).
+// v[8] (row `lane` of V) persists in the caller; warm = 0 starts from the identity. sA: 64 doubles = the symmetric matrix
+// padded to 8x8, sV / sT: 64 doubles of workspace each. Returns x[lane] for lane < 7.
+struct RotCS { double c, s; };
+__device__ __forceinline__ RotCS jacobi_cs(double app, double aqq, double apq) {
+  // t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)), theta = (aqq - app) / (2 apq), written as sgn * |b| / (|d| + hypot(d, b)).
+  // The angle only has to be good enough for the sweeps to converge (a float32 t leaves 1e-7 of the annihilated element, the
+  // next sweep takes care of it); what must hold to FP64 accuracy is c^2 + s^2 = 1, and c = rsqrt(1 + t^2), s = t c does
+  // that for any t. So t comes from float32 arithmetic on (d, b) scaled by a power of two (exact) - FP64 divide and square
+  // root are ~30-instruction dependent chains, and there are three of them in the textbook formula.
+  RotCS r;
+  r.c = 1.0; r.s = 0.0;
+  if (apq == 0.0) return r;
+  const double d = aqq - app, b = 2.0 * apq;
+  const int e = (__double2hiint(fmax(fabs(d), fabs(b))) >> 20) & 0x7ff;
+  if (e == 0 || e == 0x7ff) return r;                                   // denormal or not finite: leave the pair alone
+  const double sc = __hiloint2double((2046 - e) << 20, 0);              // 2^(1023 - e): the larger magnitude lands in [1, 2)
+  const double ds = d * sc, bs = b * sc;
+  const float df = (float)ds, bf = (float)bs;
+  const float tf = fabsf(bf) / (fabsf(df) + sqrtf(df * df + bf * bf));
+  double t = ((d >= 0.0) == (b >= 0.0)) ? (double)tf : -(double)tf;     // sign of theta (theta = 0 counts as +)
+  // one Newton step on b t^2 + 2 d t - b = 0 (the small root) in FP64, its divide through a float32 reciprocal refined
+  // once: t goes from 1e-7 to ~1e-13 relative, which keeps the sweeps quadratically convergent
+  const double den = 2.0 * (bs * t + ds);
+  double ri = (double)(1.0f / (float)den);
+  ri = ri + ri * (1.0 - den * ri);
+  t = t - ((bs * t + 2.0 * ds) * t - bs) * ri;
+  r.c = rsqrt(t * t + 1.0);
+  r.s = t * r.c;
+  return r;
+}
+template <int R>
+__device__ __forceinline__ void jacobi_round(double (&a)[8], double (&v)[8], int lane) {
+  // round R of the 8-player round robin: (7, R) and ((R+i) % 7, (R-i+7) % 7), i = 1..3
+  constexpr int P[4] = {R, (R + 1) % 7, (R + 2) % 7, (R + 3) % 7};
+  constexpr int Q[4] = {7, (R + 6) % 7, (R + 5) % 7, (R + 4) % 7};
+  RotCS cs[4];
 #pragma unroll
-  for (int j = 0; j < N; ++j) {
-    a[j] = act ? S[lane * N + j] : 0.0;
-    v[j] = (act && lane == j) ? 1.0 : 0.0;
+  for (int i = 0; i < 4; ++i) {
+    const int p = P[i] < Q[i] ? P[i] : Q[i], q = P[i] < Q[i] ? Q[i] : P[i];
+    cs[i] = jacobi_cs(shfl_dd(a[p], p), shfl_dd(a[q], q), shfl_dd(a[q], p));
   }
-  for (int sweep = 0; sweep < 60; ++sweep) {
+  int partner = lane;
+  double cm = 1.0, sm = 0.0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = P[i] < Q[i] ? P[i] : Q[i], q = P[i] < Q[i] ? Q[i] : P[i];
+    { const double akp = a[p], akq = a[q]; a[p] = cs[i].c * akp - cs[i].s * akq; a[q] = cs[i].s * akp + cs[i].c * akq; }
+    { const double vkp = v[p], vkq = v[q]; v[p] = cs[i].c * vkp - cs[i].s * vkq; v[q] = cs[i].s * vkp + cs[i].c * vkq; }
+    if (lane == p) { partner = q; cm = cs[i].c; sm = -cs[i].s; }
+    if (lane == q) { partner = p; cm = cs[i].c; sm = cs[i].s; }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const double other = shfl_dd(a[k], partner);
+    a[k] = cm * a[k] + sm * other;        // row p: c*row_p - s*row_q; row q: s*row_p + c*row_q
+  }
+}
+__device__ double solve_jacobi8_warp(const double* sA, const double* b7, double (&v)[8], bool warm, double* sV, double* sT) {
+  const int lane = lane_id();
+  const bool act = lane < 8;
+  double a[8];
+  if (warm) {
+    if (act) for (int j = 0; j < 8; ++j) sV[lane * 8 + j] = v[j];
+    __syncwarp();
+    for (int e = lane; e < 64; e += 32) {
+      const int i = e >> 3, j = e & 7;
+      double t = 0.0;
+      for (int k = 0; k < 8; ++k) t += sA[i * 8 + k] * sV[k * 8 + j];
+      sT[e] = t;
+    }
+    __syncwarp();
+    double m[2];
+    for (int r = 0; r < 2; ++r) {
+      const int e = lane + 32 * r, i = e >> 3, j = e & 7;
+      double t = 0.0;
+      for (int k = 0; k < 8; ++k) t += sV[k * 8 + i] * sT[k * 8 + j];
+      m[r] = t;
+    }
+    __syncwarp();
+    sV[lane] = m[0]; sV[lane + 32] = m[1];          // sV now holds V^T A V
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = act ? 0.5 * (sV[lane * 8 + j] + sV[j * 8 + lane]) : 0.0;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { a[j] = act ? sA[lane * 8 + j] : 0.0; v[j] = (act && lane == j) ? 1.0 : 0.0; }
+  }
+  __syncwarp();
+  for (int sweep = 0; sweep < 30; ++sweep) {
+    // converged when the off-diagonal norm is below 1e-13 of the matrix norm (1e-26 on the squared masses). The matrix is
+    // float32 data (J^T J of the reference, relative accuracy 6e-8) and changes by float32 ulps from one Gauss-Newton
+    // iteration to the next, so after the warm start ONE sweep (quadratic: 1e-7 -> 1e-14) lands below the bound, and an
+    // unchanged matrix needs none. Eigenvalues that survive the conditioning rule (>= 1e-9 of the largest) are accurate to
+    // 1e-4 relative in the worst case and ~1e-7 typically - the accuracy of the data; the fixed point the 20 iterations
+    // converge to does not depend on the step accuracy.
     double off = 0.0, dia = 0.0;
 #pragma unroll
-    for (int j = 0; j < N; ++j) {
+    for (int j = 0; j < 8; ++j) {
       if (j > lane) off += a[j] * a[j];
       if (j == lane) dia += a[j] * a[j];
     }
 #pragma unroll
     for (int o2 = 4; o2; o2 >>= 1) { off += __shfl_xor_sync(FULL, off, o2); dia += __shfl_xor_sync(FULL, dia, o2); }
     off = shfl_dd(off, 0); dia = shfl_dd(dia, 0);
-    if (off == 0.0 || off <= 1e-60 * dia) break;
-#pragma unroll
-    for (int p = 0; p < N; ++p) {
-#pragma unroll
-      for (int q = p + 1; q < N; ++q) {
-        const double apq = shfl_dd(a[q], p);
-        if (apq == 0.0) continue;
-        const double app = shfl_dd(a[p], p), aqq = shfl_dd(a[q], q);
-        const double theta = (aqq - app) / (2.0 * apq);
-        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-        const double cs = 1.0 / sqrt(t * t + 1.0), sn = t * cs;
-        { const double akp = a[p], akq = a[q]; a[p] = cs * akp - sn * akq; a[q] = sn * akp + cs * akq; }
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          const double apk = shfl_dd(a[k], p), aqk = shfl_dd(a[k], q);
-          if (lane == p) a[k] = cs * apk - sn * aqk;
-          if (lane == q) a[k] = sn * apk + cs * aqk;
-        }
-        { const double vkp = v[p], vkq = v[q]; v[p] = cs * vkp - sn * vkq; v[q] = sn * vkp + cs * vkq; }
-      }
-    }
+    if (!(off > 1e-26 * dia)) break;                // also leaves on NaN
+    jacobi_round<0>(a, v, lane); jacobi_round<1>(a, v, lane); jacobi_round<2>(a, v, lane); jacobi_round<3>(a, v, lane);
+    jacobi_round<4>(a, v, lane); jacobi_round<5>(a, v, lane); jacobi_round<6>(a, v, lane);
   }
   double d = 0.0;
 #pragma unroll
-  for (int j = 0; j < N; ++j) if (j == lane) d = a[j];
+  for (int j = 0; j < 8; ++j) if (j == lane) d = a[j];
   double smax = act ? fabs(d) : 0.0;
 #pragma unroll
   for (int o2 = 4; o2; o2 >>= 1) smax = fmax(smax, __shfl_xor_sync(FULL, smax, o2));
   smax = shfl_dd(smax, 0);
-  const double bk = act ? b[lane] : 0.0;
-  double x = 0.0;
-#pragma unroll
-  for (int i = 0; i < N; ++i) {
-    const double aii = shfl_dd(d, i);
-    double proj = 0.0;
-#pragma unroll
-    for (int k = 0; k < N; ++k) proj += shfl_dd(v[i] * bk, k);
-    if (fabs(aii) * 1e9 <= smax) continue;
-    proj /= aii;
-    x += v[i] * proj;
+  // x = sum_i v_i (v_i . b) / lambda_i over the kept eigenpairs (SVD::backsub's conditioning rule, SVD.h:266-274), through
+  // shared memory: lane k stores row k of V scaled by b[k], lane i sums column i = v_i . b (k ascending)
+  const double bk = lane < 7 ? b7[lane] : 0.0;
+  if (act) for (int i = 0; i < 8; ++i) sT[lane * 8 + i] = v[i] * bk;
+  __syncwarp();
+  if (act) {
+    double proj = sT[lane];
+    for (int k = 1; k < 8; ++k) proj += sT[k * 8 + lane];
+    sV[lane] = (fabs(d) * 1e9 > smax) ? proj / d : 0.0;
   }
+  __syncwarp();
+  double x = 0.0;
+  if (act) for (int i = 0; i < 8; ++i) x += v[i] * sV[i];
+  __syncwarp();
   return x;
 }
 
@@ -359,17 +441,23 @@ struct FusionSh {
   // estimateBias
   float Xs[7], xp[7], F7[49], Q[49], T7[49], T7b[49], Pp[49], W7[49];
   // SABEstimator::problem
-  float F[11], dFda[11], dFdx1[66], Wm[121], Pm[121], dPda[121], dWda[121], T11[121];
-  float M6a[66], M6b[66], v11[11], v6[6], JtJ[49], JtF[7];
-  double dv0[11], dv1[11], dM0[66], dM1[66], dv6[6];
+  float F[11], dFda[11], dFdx1[66], Wm[121];
+  float M6a[66], M6b[66], JtJ[49], JtF[7];
   double S7[49], rhs[7];
+  double A8[64], V8[64], T8[64];
   float as[3], av[3];
+  float Pz[9], dP3[9], W3[9], T3[9], dW3[9];
   float G, Rg, K;
   int stopped;
 };
 
 // SABEstimator::problem (sab_estimator.cpp:44-163): JtJ (7x7) and JtF (7) at the state s.Xs. s.W7 = inverse of the prior
 // covariance s.Pp (constant over the Gauss-Newton iterations; the reference recomputes the same values every time).
+// The 11x11 matrices of the reference are block diagonal: W = diag(W3, 1/Rg, W7), P = diag(Pz, Rg, Pp), and dPda / dWda are
+// non-zero in the leading 3x3 block only. A dot product that runs over the structural zeros as well adds exact zeros to
+// the same partial sums, so the blocks are multiplied directly (same terms, same order, same roundings); only the
+// products with the dense 11x6 Jacobian stay dense. Constant entries (zeros of dFdx1, Wm outside the 3x3 block) are
+// written once by the caller.
 __device__ void sab_problem(FusionSh& s, const float* Rs) {
   one([&]() {
     const float a = s.Xs[0];
@@ -391,69 +479,94 @@ __device__ void sab_problem(FusionSh& s, const float* Rs) {
     so3_exp(Rb, b);
     mat3_vec(Rbg, Rb, g);
     for (int i = 0; i < 3; ++i) { s.F[5 + i] = Rbg[i] - s.xp[1 + i]; s.F[8 + i] = b[i] - s.xp[4 + i]; }
-    for (int i = 0; i < 66; ++i) s.dFdx1[i] = 0.0f;
     for (int i = 0; i < 3; ++i) {
       s.dFdx1[i * 6 + i] = ca;
       s.dFdx1[3 * 6 + i] = (float)(2.0 * (double)g[i]);
       for (int j = 0; j < 3; ++j) s.dFdx1[(5 + i) * 6 + j] = Rb[i * 3 + j];
-      s.dFdx1[(8 + i) * 6 + 3 + i] = 1.0f;
     }
     s.dFdx1[5 * 6 + 4] = Rbg[2];  s.dFdx1[5 * 6 + 5] = -Rbg[1];
     s.dFdx1[6 * 6 + 3] = -Rbg[2]; s.dFdx1[6 * 6 + 5] = Rbg[0];
     s.dFdx1[7 * 6 + 3] = Rbg[1];  s.dFdx1[7 * 6 + 4] = -Rbg[0];
-    // P, dPda (only the leading 3x3 block depends on a); the 3x3 block of W is filled after the Cholesky inverse below
     const double k2 = 2.0 * (double)sa * (double)ca;
-    for (int i = 0; i < 3; ++i)
-      for (int j = 0; j < 3; ++j) {
-        s.Pm[i * 11 + j] = sa * sa * s.Rv[i * 3 + j] + ca * ca * Rs[i * 3 + j];
-        s.dPda[i * 11 + j] = (float)(k2 * (double)(s.Rv[i * 3 + j] - Rs[i * 3 + j]));
-        s.T7b[i * 3 + j] = s.Pm[i * 11 + j];   // contiguous copy of Pz for the Cholesky
+    for (int e = 0; e < 9; ++e) {
+      s.Pz[e] = sa * sa * s.Rv[e] + ca * ca * Rs[e];
+      s.dP3[e] = (float)(k2 * (double)(s.Rv[e] - Rs[e]));
+    }
+  });
+  chol_inverse(s.W3, s.Pz, s.ch, 3);
+  each(9, [&](int e) {
+    const int i = e / 3, j = e % 3;
+    s.Wm[i * 11 + j] = s.W3[e];
+    s.T3[e] = (-s.W3[i * 3] * s.dP3[j] + -s.W3[i * 3 + 1] * s.dP3[3 + j]) + -s.W3[i * 3 + 2] * s.dP3[6 + j];   // (-W)*dPda
+  });
+  each(9, [&](int e) {
+    const int i = e / 3, j = e % 3;
+    s.dW3[e] = (s.T3[i * 3] * s.W3[j] + s.T3[i * 3 + 1] * s.W3[3 + j]) + s.T3[i * 3 + 2] * s.W3[6 + j];        // ... *W
+  });
+  mm<6, 11, 11>(s.M6a, s.dFdx1, 1, 6, s.Wm, 11, 1);           // dFdx1.T()*W   (6x11)
+  // lanes 0..5: one element of the column 0.5*dFdx1.T()*dWda*F + dFdx1.T()*W*dFda, and of dFdx1.T()*W*F
+  // lane 8: JtJ(0,0) and JtF[0]
+  {
+    const int l = lane_id();
+    if (l < 6) {
+      double r[3];
+      for (int j = 0; j < 3; ++j) {                            // row l of (0.5*dFdx1.T())*dWda: terms q = 0..2 (the rest are zeros)
+        double t = (0.5 * (double)s.dFdx1[l]) * (double)s.dW3[j];
+        t += (0.5 * (double)s.dFdx1[6 + l]) * (double)s.dW3[3 + j];
+        t += (0.5 * (double)s.dFdx1[12 + l]) * (double)s.dW3[6 + j];
+        r[j] = t;
       }
-  });
-  chol_inverse(s.T7, s.T7b, s.ch, 3);
-  each(9, [&](int e) { s.Wm[(e / 3) * 11 + e % 3] = s.T7[e]; });
-  // dWda = -W * dPda * W
-  each(121, [&](int e) { s.T11[e] = -s.Wm[e]; });
-  mm(s.dWda, s.T11, 11, 1, s.dPda, 11, 1, 11, 11, 11);
-  each(121, [&](int e) { s.T11[e] = s.dWda[e]; });
-  mm(s.dWda, s.T11, 11, 1, s.Wm, 11, 1, 11, 11, 11);
-  // JtJ(0,0) = 0.25*F*dWda*P*dWda*F + dFda*dWda*F + dFda*W*dFda   (first chain double after the 0.25 factor)
-  each(11, [&](int e) { s.dv0[e] = 0.25 * (double)s.F[e]; });
-  mm_d(s.dv1, s.dv0, 0, 1, s.dWda, 11, 1, 1, 11, 11);
-  mm_d(s.dv0, s.dv1, 0, 1, s.Pm, 11, 1, 1, 11, 11);
-  mm_d(s.dv1, s.dv0, 0, 1, s.dWda, 11, 1, 1, 11, 11);
-  mm(s.v11, s.dFda, 0, 1, s.dWda, 11, 1, 1, 11, 11);          // dFda*dWda
-  mm(s.M6a, s.dFda, 0, 1, s.Wm, 11, 1, 1, 11, 11);            // dFda*W (M6a[0..10])
-  one([&]() {
-    double t0 = s.dv1[0] * (double)s.F[0];
-    for (int i = 1; i < 11; ++i) t0 += s.dv1[i] * (double)s.F[i];
-    float t1 = s.v11[0] * s.F[0], t2 = s.M6a[0] * s.dFda[0], t3 = s.M6a[0] * s.F[0];
-    for (int i = 1; i < 11; ++i) { t1 += s.v11[i] * s.F[i]; t2 += s.M6a[i] * s.dFda[i]; t3 += s.M6a[i] * s.F[i]; }
-    s.JtJ[0] = (float)((t0 + (double)t1) + (double)t2);
-    s.JtF[0] = t3;                                            // dFda*W*F; the 0.5*F*dWda*F term is added below
-  });
-  // 0.5*F*dWda*F
-  each(11, [&](int e) { s.dv0[e] = 0.5 * (double)s.F[e]; });
-  mm_d(s.dv1, s.dv0, 0, 1, s.dWda, 11, 1, 1, 11, 11);
-  one([&]() {
-    double t0 = s.dv1[0] * (double)s.F[0];
-    for (int i = 1; i < 11; ++i) t0 += s.dv1[i] * (double)s.F[i];
-    s.JtF[0] = (float)(t0 + (double)s.JtF[0]);
-  });
-  // column: 0.5*dFdx1.T()*dWda*F + dFdx1.T()*W*dFda
-  each(66, [&](int e) { const int i = e / 11, j = e % 11; s.dM0[e] = 0.5 * (double)s.dFdx1[j * 6 + i]; });   // 6x11
-  mm_d(s.dM1, s.dM0, 11, 1, s.dWda, 11, 1, 6, 11, 11);
-  mm_d(s.dv6, s.dM1, 11, 1, s.F, 1, 0, 6, 11, 1);
-  mm(s.M6a, s.dFdx1, 1, 6, s.Wm, 11, 1, 6, 11, 11);           // dFdx1.T()*W   (6x11)
-  mm(s.v6, s.M6a, 11, 1, s.dFda, 1, 0, 6, 11, 1);
-  mm(s.M6b, s.M6a, 11, 1, s.dFdx1, 6, 1, 6, 11, 6);           // (dFdx1.T()*W)*dFdx1   (6x6, in M6b[0..35])
-  mm(s.v11, s.M6a, 11, 1, s.F, 1, 0, 6, 11, 1);               // dFdx1.T()*W*F   (v11[0..5])
-  each(6, [&](int e) {
-    const float c = (float)(s.dv6[e] + (double)s.v6[e]);
-    s.JtJ[(1 + e) * 7] = c;
-    s.JtJ[1 + e] = c;
-    s.JtF[1 + e] = s.v11[e];
-  });
+      double cd = r[0] * (double)s.F[0];
+      cd += r[1] * (double)s.F[1];
+      cd += r[2] * (double)s.F[2];
+      float cf = s.M6a[l * 11] * s.dFda[0], jf = s.M6a[l * 11] * s.F[0];
+      for (int q = 1; q < 11; ++q) { cf += s.M6a[l * 11 + q] * s.dFda[q]; jf += s.M6a[l * 11 + q] * s.F[q]; }
+      const float c = (float)(cd + (double)cf);
+      s.JtJ[(1 + l) * 7] = c;
+      s.JtJ[1 + l] = c;
+      s.JtF[1 + l] = jf;
+    } else if (l == 8) {
+      double v0[3], v1[3];
+      // 0.25*F*dWda*P*dWda*F
+      for (int j = 0; j < 3; ++j) {
+        double t = (0.25 * (double)s.F[0]) * (double)s.dW3[j];
+        t += (0.25 * (double)s.F[1]) * (double)s.dW3[3 + j];
+        t += (0.25 * (double)s.F[2]) * (double)s.dW3[6 + j];
+        v0[j] = t;
+      }
+      for (int j = 0; j < 3; ++j) { double t = v0[0] * (double)s.Pz[j]; t += v0[1] * (double)s.Pz[3 + j]; t += v0[2] * (double)s.Pz[6 + j]; v1[j] = t; }
+      for (int j = 0; j < 3; ++j) { double t = v1[0] * (double)s.dW3[j]; t += v1[1] * (double)s.dW3[3 + j]; t += v1[2] * (double)s.dW3[6 + j]; v0[j] = t; }
+      double t0 = v0[0] * (double)s.F[0];
+      t0 += v0[1] * (double)s.F[1];
+      t0 += v0[2] * (double)s.F[2];
+      // dFda*dWda*F
+      float u[3];
+      for (int j = 0; j < 3; ++j) u[j] = (s.dFda[0] * s.dW3[j] + s.dFda[1] * s.dW3[3 + j]) + s.dFda[2] * s.dW3[6 + j];
+      const float t1 = (u[0] * s.F[0] + u[1] * s.F[1]) + u[2] * s.F[2];
+      // dFda*W: entries 0..2 from W3, entry 3 zero, entries 4..10 = row 0 of W7 (dFda[4] = 1)
+      float m[11];
+      for (int j = 0; j < 3; ++j) m[j] = (s.dFda[0] * s.W3[j] + s.dFda[1] * s.W3[3 + j]) + s.dFda[2] * s.W3[6 + j];
+      m[3] = 0.0f;
+      for (int j = 0; j < 7; ++j) m[4 + j] = s.W7[j];
+      const float t2 = ((m[0] * s.dFda[0] + m[1] * s.dFda[1]) + m[2] * s.dFda[2]) + m[4];
+      float t3 = m[0] * s.F[0];
+      for (int j = 1; j < 11; ++j) t3 += m[j] * s.F[j];
+      s.JtJ[0] = (float)((t0 + (double)t1) + (double)t2);
+      // 0.5*F*dWda*F + dFda*W*F
+      for (int j = 0; j < 3; ++j) {
+        double t = (0.5 * (double)s.F[0]) * (double)s.dW3[j];
+        t += (0.5 * (double)s.F[1]) * (double)s.dW3[3 + j];
+        t += (0.5 * (double)s.F[2]) * (double)s.dW3[6 + j];
+        v1[j] = t;
+      }
+      double t4 = v1[0] * (double)s.F[0];
+      t4 += v1[1] * (double)s.F[1];
+      t4 += v1[2] * (double)s.F[2];
+      s.JtF[0] = (float)(t4 + (double)t3);
+    }
+    __syncwarp();
+  }
+  mm<6, 11, 6>(s.M6b, s.M6a, 11, 1, s.dFdx1, 6, 1);           // (dFdx1.T()*W)*dFdx1
   each(36, [&](int e) { s.JtJ[(1 + e / 6) * 7 + 1 + e % 6] = s.M6b[e]; });
 }
 
@@ -597,19 +710,27 @@ __global__ void __launch_bounds__(32) k_imu_fuse(ImuLane* __restrict__ st, const
     chol_inverse(s.W7, s.Pp, s.ch, 7);
     each(121, [&](int e) {
       const int i = e / 11, j = e % 11;
-      float w = 0.0f, p = 0.0f;
-      if (i == 3 && j == 3) { w = (float)(1.0 / (double)s.Rg); p = s.Rg; }
-      if (i >= 4 && j >= 4) { w = s.W7[(i - 4) * 7 + j - 4]; p = s.Pp[(i - 4) * 7 + j - 4]; }
-      s.Wm[e] = w; s.Pm[e] = p; s.dPda[e] = 0.0f;
+      float w = 0.0f;
+      if (i == 3 && j == 3) w = (float)(1.0 / (double)s.Rg);
+      if (i >= 4 && j >= 4) w = s.W7[(i - 4) * 7 + j - 4];
+      s.Wm[e] = w;
     });
+    each(66, [&](int e) { const int i = e / 6, j = e % 6; s.dFdx1[e] = (i >= 8 && j == i - 5) ? 1.0f : 0.0f; });
     // ---- SABEstimator::gaussNewton(_X, 20) with a_tol = r_tol = 0: never leaves early (sab_estimator.cpp:21-42). An
     // iteration that leaves X bit-identical makes every later one a repeat of itself, so stopping there changes nothing.
+    double jv[8];                    // row `lane` of the eigenvector matrix, carried from one iteration to the next
+    bool warm = false, try_ldl = true;   // once the conditioning test has failed the later iterations (nearly the same matrix) go straight to the eigen-solve
     for (int it = 0; it < 20; ++it) {
       sab_problem(s, Rs3);
       each(49, [&](int e) { const int i = e / 7, j = e % 7; s.S7[e] = 0.5 * ((double)s.JtJ[e] + (double)s.JtJ[j * 7 + i]); });
       each(7, [&](int e) { s.rhs[e] = -(double)s.JtF[e]; });
       double h;
-      if (!solve_ldl_warp<7>(s.S7, s.rhs, h)) h = solve_jacobi_warp<7>(s.S7, s.rhs);
+      if (!(try_ldl && solve_ldl_warp<7>(s.S7, s.rhs, h))) {
+        try_ldl = false;
+        each(64, [&](int e) { const int i = e >> 3, j = e & 7; s.A8[e] = (i < 7 && j < 7) ? s.S7[i * 7 + j] : 0.0; });
+        h = solve_jacobi8_warp(s.A8, s.rhs, jv, warm, s.V8, s.T8);
+        warm = true;
+      }
       const int l = lane_id();
       float xn = 0.0f;
       if (l < 7) {
