@@ -135,6 +135,7 @@ class RefLib:
             "ref_pipeline_frame": (C.c_int, [vp, f32p, C.c_uint64, C.POINTER(FrameOut)]),
             "ref_timers": (None, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double * 9)]),
             "ref_timers_reset": (None, [vp]),
+            "ref_camera_extrinsics": (None, [f32p, f32p]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -268,6 +269,12 @@ class RefLib:
         return d.value, t.value, list(st)
 
     def timers_reset(self): self.L.ref_timers_reset(self.h)
+
+    def camera_extrinsics(self):
+        """Camera::getRc2i / getTc2i of a default-constructed reference camera"""
+        R, t = np.zeros(9, np.float32), np.zeros(3, np.float32)
+        self.L.ref_camera_extrinsics(R, t)
+        return R.reshape(3, 3), t
 
 
 class OracleLib:

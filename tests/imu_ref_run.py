@@ -27,6 +27,8 @@ def run(name, n_frames, q=None):
         r = {f: np.array(getattr(o, f), np.float32) for f in FIELDS}
         r.update({f: getattr(o, f) for f in SCALARS})
         recs.append(r)
+    Rc2i, tc2i = ref.camera_extrinsics()
+    recs[0]["Rc2i"], recs[0]["tc2i"] = Rc2i, tc2i
     ref.close()
     if q is not None:
         q.put(recs)

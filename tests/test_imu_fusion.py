@@ -147,3 +147,31 @@ def test_track_imu_equals_stage_calls_and_follows_reference():
     assert abs(nm - r["klm_num"]) <= 0.002 * r["klm_num"]
     assert _rel(o["position"], r["position"]) < 1e-3 and _rel(o["orientation"], r["orientation"], 1e-3) < 1e-3
     assert abs(float(o["K"]) - r["K"]) < 1e-3 * r["K"]
+
+
+def test_replay_odometry_follows_reference(tmp_path):
+    """the headless replay (files in, odometry log out; host IMU integrator + rbv_detect_u8 + rbv_track_imu) on
+    the same camera frames and raw IMU samples as the reference's deterministic pipeline: one log line per estimated frame in
+    the reference's format, every pose within 1e-4 absolute (metres / radians) of the reference's, free running."""
+    import io
+    from rebvio_b200 import replay
+    recs = _ref()
+    spec = synth.config(SEQ, n_frames=NF)
+    seq = synth.generate(spec)
+    ctx, det = _ctx(1)
+    cam, mapc, core = ctx.cam, ctx.mapc, ctx.core
+    ctx.close()
+    out = io.StringIO()
+    res = replay.replay(seq.frames, seq.ts_us, seq.imu_ts_us, seq.gyro, seq.acc, cam, det, mapc, core, out=out)
+    lines = out.getvalue().strip().split("\n")
+    assert len(res) == NF - 1 == len(lines)
+    worst = 0.0
+    for (ts, ori, pos, r, nm), line, ref in zip(res, lines, recs[1:]):
+        assert ts == ref["ts_us"] and ref["estimated"]
+        f = line.split(" ")
+        assert len(f) == 7 and int(f[0]) == ts and all(len(x.split(".")[1]) == 6 for x in f[1:])
+        worst = max(worst, float(np.abs(ori - ref["orientation"]).max()), float(np.abs(pos - ref["position"]).max()))
+        assert abs(nm - ref["klm_num"]) <= max(2, 0.002 * ref["klm_num"])
+    print("replay: worst absolute pose difference over %d frames: %.2e" % (len(res), worst))
+    assert worst < 1e-4
+    assert abs(float(res[-1][3]["K"]) - recs[-1]["K"]) < 1e-3 * recs[-1]["K"]

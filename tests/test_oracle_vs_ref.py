@@ -97,3 +97,33 @@ def test_quantile_and_servo():
         ref.detect(frames[1]); orc.detect(frames[1])
         assert H.bits(np.float32(ref.get_threshold())) == H.bits(np.float32(orc.get_threshold()))
     ref.close(); orc.close()
+
+
+def test_host_imu_integrator_and_odometry_line_vs_reference():
+    """rebvio_b200/imu.py (host side of SURVEY 8(f2)/(f4)): the float32 IMU sample integrator against the reference's
+    types::IntegratedImu as exercised by its own pipeline (R, gyro, cacc, dt per frame), the camera extrinsics against
+    Camera::getRc2i / getTc2i, and the odometry log line format (rebvio.cpp:275-283)."""
+    import imu_ref_run
+    from rebvio_b200 import imu, synth
+    name, nf = "C5:160x120", 14
+    recs = imu_ref_run.run_in_subprocess(name, nf)
+    seq = synth.generate(synth.config(name, n_frames=nf))
+    assert np.array_equal(recs[0]["Rc2i"], imu.R_C2I) and np.array_equal(recs[0]["tc2i"], imu.T_C2I)
+    j = 0
+    worst = 0.0
+    for k in range(nf):
+        integ = imu.IntegratedImu()
+        while j < len(seq.imu_ts_us) and seq.imu_ts_us[j] <= seq.ts_us[k]:
+            integ.add(seq.imu_ts_us[j], seq.gyro[j], seq.acc[j]); j += 1
+        if k == 0:
+            continue
+        rec = integ.get(frame_dt=np.float32(np.float32(int(seq.ts_us[k]) - int(seq.ts_us[k - 1])) / 1000000.0))[0]
+        r = recs[k]
+        assert r["estimated"]
+        for mine, ref in ((rec["R"], r["imu_R"]), (rec["gyro"], r["imu_gyro"]), (rec["cacc"], r["imu_cacc"]),
+                          (rec["dt_s"], r["imu_dt_s"]), (rec["frame_dt"], r["frame_dt"])):
+            a, b = np.asarray(mine, np.float64).ravel(), np.asarray(ref, np.float64).ravel()
+            worst = max(worst, float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-12)))
+    assert worst <= 2e-7, worst       # float32 rounding of sin / cos (numpy vs glibc float overloads); measured 0 .. 6e-8
+    assert imu.odometry_line(1403637145538319104 // 1000, [0.0123456789, -1.5, 2e-7], [1, -0.25, 3.14159265]) == \
+        "1403637145538319 0.012346 -1.500000 0.000000 1.000000 -0.250000 3.141593"
