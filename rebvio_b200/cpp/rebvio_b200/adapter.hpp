@@ -87,6 +87,8 @@ class EdgeMap {
 
   rbv_map* handle() const { return map_; }
   uint64_t ts_us() const { return ts_us_; }
+  // a pooled map is reused for a later frame (the device slab and the captured graphs of its map pairs stay alive)
+  void reset(uint64_t ts_us) { ts_us_ = ts_us; invalidate(); }
   int size() { int n = 0; check(rbv_map_size(dev_->ctx(), map_, &n), "rbv_map_size"); return n; }
   float threshold() { float t = 0; check(rbv_map_threshold(dev_->ctx(), map_, &t), "rbv_map_threshold"); return t; }
   void threshold(const float& t) { check(rbv_map_set_threshold(dev_->ctx(), map_, &t), "rbv_map_set_threshold"); }
@@ -176,6 +178,18 @@ class EdgeDetector {
     auto map = std::make_shared<EdgeMap>(dev_, ts_us);
     float at = 0;
     check(rbv_detect(dev_->ctx(), map->handle(), &image, pitch_bytes, &ts_us, &config_->threshold, &keylines_count_, &at), "rbv_detect");
+    auto_threshold_ = at;
+    return map;
+  }
+  // the same for the 8-bit frame the camera driver delivers: Rebvio::imageCallback's convertTo(x3) (rebvio.cpp:43) and, after
+  // Device::setUndistort, Camera::undistort (rebvio.cpp:45) run on the device in front of the detector. `reuse`: a pooled map to
+  // detect into instead of allocating one (the reference allocates a map per frame, edge_detector.cpp:31).
+  EdgeMap::SharedPtr detect(const uint8_t* image, size_t pitch_bytes, uint64_t ts_us, EdgeMap::SharedPtr reuse = nullptr) {
+    config_->threshold = rbv_servo_threshold(config_.get(), config_->threshold, keylines_count_);
+    EdgeMap::SharedPtr map = reuse ? reuse : std::make_shared<EdgeMap>(dev_, ts_us);
+    if (reuse) map->reset(ts_us);
+    float at = 0;
+    check(rbv_detect_u8(dev_->ctx(), map->handle(), &image, pitch_bytes, &ts_us, &config_->threshold, &keylines_count_, &at), "rbv_detect_u8");
     auto_threshold_ = at;
     return map;
   }

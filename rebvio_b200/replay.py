@@ -55,6 +55,21 @@ def replay(frames_u8, ts_us, imu_ts_us, gyro, acc, cam, det, mapc, core, imu_cfg
     return res
 
 
+def write_sequence(path, frames_u8, ts_us, imu_ts_us, gyro, acc, cam, keylines_ref=0, keylines_max=0):
+    """the sequence file of the C++ replay (rebvio_b200/cpp/rebvio_replay.cpp, which drives the rebvio_b200::Rebvio façade)"""
+    import struct
+    frames_u8 = np.ascontiguousarray(frames_u8, np.uint8)
+    n, rows, cols = frames_u8.shape
+    with open(path, "wb") as f:
+        f.write(b"RBVSEQ1\0")
+        f.write(struct.pack("<6i3f", rows, cols, n, len(imu_ts_us), int(keylines_ref), int(keylines_max), cam.fm, cam.cx, cam.cy))
+        f.write(np.ascontiguousarray(ts_us, "<u8").tobytes())
+        f.write(frames_u8.tobytes())
+        f.write(np.ascontiguousarray(imu_ts_us, "<u8").tobytes())
+        f.write(np.ascontiguousarray(gyro, "<f4").tobytes())
+        f.write(np.ascontiguousarray(acc, "<f4").tobytes())
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--synthetic", default="", help="sequence name of rebvio_b200.synth (e.g. C2, C5:320x240)")
