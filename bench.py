@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--undistort", action="store_true", help="e2e leg: raw camera frames, Camera::undistort (EuRoC cam0 model) on the device")
     ap.add_argument("--imu", action="store_true", help="run the reference's IMU filters on the device between the tracker halves "
                     "(rbv_track_imu: gyro-bias correction + scale-attitude-bias filter, SURVEY 8(f2)) instead of the visual-only fusion")
+    ap.add_argument("--no-overlap", action="store_true", help="in-order schedule on one stream (detect, then the tracker of the same frame) "
+                    "instead of the reference's two-thread schedule on two streams (detect of frame n+1 next to the tracker of n-1, n)")
     ap.add_argument("--tune", default="", help="implementation choices, e.g. '2=4,0=1' (rbv_set_tuning key=value pairs)")
     ap.add_argument("--kernel-table", default="", help="write the per-kernel CUDA-event table (one untimed step) here")
     return ap.parse_args()
@@ -234,7 +236,9 @@ def run_b200(args):
     cam, det, mapc, core = cfg_structs(spec)
     B, K, W = args.lanes, args.steps, args.warmup
     N = spec.cam.rows * spec.cam.cols
-    nf = 1 + W + K
+    lag = 0 if args.no_overlap else 1        # overlapped schedule: push(k) runs detect(k) next to the tracker of the pair (k-2, k-1)
+    first = 1 + lag                          # first push that has a pair to track
+    nf = first + W + K
     seeds = [1000 + LANES_PER_GPU * rank + i for i in range(B)]
     frames_u8, R_rel = synth.batched_sequences(spec, seeds, nf, device=dev, n_textures=2)
     d_frames = frames_u8.to(torch.float32) * 3.0                     # rebvio.cpp:43 conversion, resident in HBM
@@ -275,19 +279,22 @@ def run_b200(args):
         return dict(imu_in=a)
 
     # ---- leg 1: device-resident inputs ----------------------------------------------------------------------
-    pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg)
+    pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg,
+                           overlap=bool(lag))
     tune = [tuple(int(x) for x in kv.split("=")) for kv in args.tune.split(",") if kv]
     for key, val in tune:
         pipe.ctx.set_tuning(key, val)
     ptr = lambda k: d_frames[k].data_ptr()
-    pipe.push(device_ptr=ptr(0))
-    # warm-up; the first warm-up step runs with every kernel bracketed by CUDA events to find the dominant kernel
+    pargs = lambda k: targs(k - lag) if k >= first else {}     # arguments of the pair push(k) tracks
+    for k in range(first):
+        pipe.push(device_ptr=ptr(k))
+    # warm-up; the first warm-up step runs with every kernel bracketed by CUDA events (in order, on one stream) to find the dominant kernel
     pipe.ctx.profile_reset(); pipe.ctx.profile_set(-2)
-    out = pipe.push(device_ptr=ptr(1), **targs(1))
+    out = pipe.push(device_ptr=ptr(first), **pargs(first))
     table = pipe.ctx.profile_read()
     pipe.ctx.profile_set(-1)
-    for k in range(2, 1 + W):
-        out = pipe.push(device_ptr=ptr(k), **targs(k))
+    for k in range(first + 1, first + W):
+        out = pipe.push(device_ptr=ptr(k), **pargs(k))
     top = max(table, key=lambda n: table[n][0])
     if args.kernel_table and rank == 0:
         tot = sum(v[0] for v in table.values())
@@ -303,8 +310,8 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record(stream)
-    for k in range(1 + W, 1 + W + K):
-        out = pipe.push(device_ptr=ptr(k), **targs(k))
+    for k in range(first + W, first + W + K):
+        out = pipe.push(device_ptr=ptr(k), **pargs(k))
         kl_sum += float(out["keylines"].sum()); match_sum += float(out["matches"].sum())
     ev1.record(stream)
     barrier()
@@ -342,6 +349,9 @@ def run_b200(args):
             "config": {"workload": f"batched replay: {B} independent EuRoC-shaped {spec.cam.cols}x{spec.cam.rows} sequences per GPU "
                                    f"(C2 generator, seeds 1000+64*rank+i), step = 1 frame of every sequence through detect + tracker",
                        "lanes_per_gpu": B, "keylines_per_frame": K_mean, "matches_per_frame": match_sum / (B * K),
+                       "schedule": ("detect(n+1) on the front-end stream next to the tracker of (n-1, n) on the tracker stream, as the reference's "
+                                    "two threads (rebvio.cpp:56-90 / 92-293); every step = one detect + one tracker pass of all lanes") if lag
+                                   else "in order on one stream",
                        "reduce_mode": args.reduce, "fusion": "imu filters on device (rbv_track_imu)" if args.imu else "visual-only (rbv_track)",
                        "parallelism": f"replicas x{world} (no collective)",
                        "l2": f"per-step working set {B} lanes x ~14 MB >> 126 MB L2 (inputs larger than L2, no flush needed)"},
@@ -349,6 +359,15 @@ def run_b200(args):
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
                          "avg_launch_ms": top_ms / max(1, top_n), "launches_timed": top_n,
                          "kernel_share_of_step": (top_ms / max(1, top_n)) * (top_launches / K) / (ms / K),
+                         # with the two-stream schedule the events around a front-end kernel also see the tracker kernels that share
+                         # the SMs with it; `alone` = the same kernel bracketed the same way in the in-order warm-up step (one stream,
+                         # every kernel serialised) - the figure that compares with the ncu launch list
+                         "concurrent": bool(lag),
+                         "alone": {"avg_launch_ms": table[top][0] / max(1, table[top][1]),
+                                   "achieved": abytes / (table[top][0] / max(1, table[top][1]) * 1e-3) / 1e9,
+                                   "frac": abytes / (table[top][0] / max(1, table[top][1]) * 1e-3) / 1e9 / peak,
+                                   "share_of_in_order_step": table[top][0] / sum(v[0] for v in table.values()),
+                                   "in_order_step_kernel_sum_ms": sum(v[0] for v in table.values())},
                          "frame_level": {"achieved": frame_gbs, "frac": frame_gbs / peak,
                                          "bytes_per_frame": roofline.frame_bytes(N, K_mean, probes)}},
             "clocks": clocks, "gpu_launches": int(gpu_launches)}
@@ -364,17 +383,19 @@ def run_b200(args):
         h_frames[nf].copy_(frames_u8[nf - 1])
         torch.cuda.synchronize()
         hnp = h_frames.numpy()
-        pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg)
+        pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg,
+                               overlap=bool(lag))
         if args.undistort:   # rebvio/include/rebvio/camera.hpp:26-40
             fm = 0.5 * (458.654 + 457.296)
             pipe.ctx.set_undistort([fm, fm, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0])
-        pipe.push(frames=hnp[0], next_frames=hnp[1])
-        for k in range(1, 1 + W):
-            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **targs(k))
+        for k in range(first):
+            pipe.push(frames=hnp[k], next_frames=hnp[k + 1])
+        for k in range(first, first + W):
+            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **pargs(k))
         barrier()
         t0 = time.perf_counter()
-        for k in range(1 + W, 1 + W + K):
-            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **targs(k))
+        for k in range(first + W, first + W + K):
+            pipe.push(frames=hnp[k], next_frames=hnp[k + 1], **pargs(k))
         pipe.ctx.sync()
         t1 = time.perf_counter()
         barrier()

@@ -155,12 +155,17 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
  *   RBV_TUNE_FIELD_ROWS: image rows per band of the shared-memory distance field (0 = automatic)
  *   RBV_TUNE_GRAPH: 1 = every kernel launched on the stream, 2 (default) = the kernel sequences of rbv_detect*, rbv_track_g1 and
  *                   rbv_track_g2 are captured once per (map pair) as CUDA graphs and replayed with one launch each
- *                   (one block per image plane, TMA-staged row chunks; needs cols % 4 == 0 and cols <= 832)        */
+ *                   (one block per image plane, TMA-staged row chunks; needs cols % 4 == 0 and cols <= 832)
+ *   RBV_TUNE_FE_STREAM: 1 = rbv_detect* enqueue on the context's own front-end stream (SURVEY.md 8(b) "Threading": the
+ *                   reference detects frame n+1 on one thread while the other tracks frames n-1, n, rebvio.cpp:56-90 /
+ *                   92-293). A detect without outputs returns at once, rbv_detect_wait collects its counts; tracker and
+ *                   mirror calls wait on the device for the detects of the maps they are given. Results are identical.    */
 #define RBV_TUNE_FIELD 0
 #define RBV_TUNE_BOX 1
 #define RBV_TUNE_TRYVEL 2
 #define RBV_TUNE_GRAPH 3
 #define RBV_TUNE_FIELD_ROWS 4
+#define RBV_TUNE_FE_STREAM 5
 #define RBV_TUNE_COUNT 8
 int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
 
@@ -196,6 +201,10 @@ int rbv_prefetch_frames(rbv_ctx* ctx, const void* const* images, size_t pitch_by
 /* same, frames already resident in device memory (lane-major contiguous [B][rows][cols] float32). */
 int rbv_detect_device(rbv_ctx* ctx, rbv_map* map, const float* d_images, const uint64_t* ts_us,
                       const float* threshold, int* n_keylines, float* auto_threshold);
+
+/* keyline counts and auto thresholds (both optional, length B) of the most recent detect into `map`: after a detect on the
+ * front-end stream (RBV_TUNE_FE_STREAM) this waits for that detect only; otherwise it reads the map's counters. */
+int rbv_detect_wait(rbv_ctx* ctx, rbv_map* map, int* n_keylines, float* auto_threshold);
 
 /* host scalar servo of edge_detector.cpp:33-36: returns the new config_->threshold. */
 float rbv_servo_threshold(const rbv_detector_cfg* cfg, float threshold, int last_keyline_count);

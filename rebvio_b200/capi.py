@@ -66,7 +66,7 @@ assert KEYLINE_DTYPE.itemsize == 84
 
 RBV_OK, RBV_ERR_ARG, RBV_ERR_CUDA, RBV_ERR_STATE = 0, 1, 2, 3
 REDUCE_FAST, REDUCE_ORDERED = 0, 1
-TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH, TUNE_FIELD_ROWS = 0, 1, 2, 3, 4   # rbv_set_tuning keys (0 = automatic; see the header for the values)
+TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH, TUNE_FIELD_ROWS, TUNE_FE_STREAM = 0, 1, 2, 3, 4, 5   # rbv_set_tuning keys (0 = automatic; see the header for the values)
 
 vp = C.c_void_p
 _SIG = {
@@ -94,6 +94,7 @@ _SIG = {
     "rbv_detect": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),
     "rbv_detect_u8": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),
     "rbv_prefetch_frames": (C.c_int, [vp, C.POINTER(vp), C.c_size_t, C.c_int]),
+    "rbv_detect_wait": (C.c_int, [vp, vp, vp, vp]),
     "rbv_detect_device": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "rbv_servo_threshold": (C.c_float, [C.POINTER(DetectorCfg), C.c_float, C.c_int]),
     "rbv_build_distance_field": (C.c_int, [vp, vp]),

@@ -295,6 +295,8 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaMallocHost((void**)&c->h_lm, sizeof(LMState) * B));
   RBV_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
   RBV_CUDA(cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+  RBV_CUDA(cudaStreamCreateWithFlags(&c->fe_stream, cudaStreamNonBlocking));
+  RBV_CUDA(cudaEventCreateWithFlags(&c->ev_tracker, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   for (int i = 0; i < 2; ++i) {
@@ -329,6 +331,8 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm);
   if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
   if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
+  if (c->fe_stream) { cudaStreamSynchronize(c->fe_stream); cudaStreamDestroy(c->fe_stream); }
+  if (c->ev_tracker) cudaEventDestroy(c->ev_tracker);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->undist_map) cudaFree(c->undist_map);
@@ -346,6 +350,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
 extern "C" int rbv_sync(rbv_ctx* c) {
   if (!c) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
+  if (c->fe_stream) RBV_CUDA(cudaStreamSynchronize(c->fe_stream));
   return RBV_OK;
 }
 extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
@@ -404,6 +409,8 @@ extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
   RBV_CUDA(cudaMemcpyAsync(m->threshold, thr.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   m->ts_us = (uint64_t*)calloc(B, sizeof(uint64_t));
+  RBV_CUDA(cudaEventCreateWithFlags(&m->ready, cudaEventDisableTiming));
+  RBV_CUDA(cudaMallocHost((void**)&m->h_fe, B * 8));
   *out = m;
   return RBV_OK;
 }
@@ -412,7 +419,14 @@ extern "C" void rbv_map_release(rbv_ctx* c, rbv_map* m) {
   if (!m) return;
   std::unique_lock<std::recursive_mutex> lk;
   if (c) lk = std::unique_lock<std::recursive_mutex>(*static_cast<std::recursive_mutex*>(c->mtx));
-  if (c) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); if (c->field_map == m) c->field_map = nullptr; rbv_graphs_clear(c, m); }
+  if (c) {
+    cudaSetDevice(c->device); cudaStreamSynchronize(c->stream);
+    if (c->fe_stream) cudaStreamSynchronize(c->fe_stream);
+    if (c->field_map == m) c->field_map = nullptr;
+    rbv_graphs_clear(c, m);
+  }
+  if (m->ready) cudaEventDestroy(m->ready);
+  if (m->h_fe) cudaFreeHost(m->h_fe);
   cudaFree(m->slab);
   free(m->ts_us);
   delete m;
@@ -453,6 +467,31 @@ static int fetch_cnt(rbv_ctx* c) {
   LOCK_CTX(c);                                                              \
   RBV_CUDA(cudaSetDevice((c)->device))
 #define TRY(x) do { int rc_ = (x); if (rc_ != RBV_OK) return rc_; } while (0)
+
+// ---- front-end stream (SURVEY.md 8(b) "Threading": detect of frame n+1 next to the tracker of frames n-1, n) ---------------
+// With RBV_TUNE_FE_STREAM = 1 the rbv_detect* calls enqueue on the context's own front-end stream instead of the tracker
+// stream: the detector's buffers (img, rowsum, bufA/B, flags, row counts, thr_dev) are disjoint from the tracker's, a map
+// carries an event recorded behind its detect, and every tracker / mirror entry waits for the events of the maps it is given.
+// A detect without outputs then returns at once; rbv_detect_wait hands the keyline counts back later.
+#define MAP_READY(c, m)                                                                                   \
+  do {                                                                                                    \
+    if ((m) && (m)->fe_pending) { RBV_CUDA(cudaStreamWaitEvent((c)->stream, (m)->ready, 0)); (m)->fe_pending = 0; } \
+  } while (0)
+struct FeScope {
+  rbv_ctx* c;
+  cudaStream_t saved;
+  bool active;
+  explicit FeScope(rbv_ctx* ctx) : c(ctx), saved(ctx->stream), active(false) {
+    if (c->tune[RBV_TUNE_FE_STREAM] == 1 && c->fe_stream && c->stream != c->fe_stream && c->prof_mode != -2) {
+      // whatever the tracker stream has been given so far may still read the map this detect overwrites: it comes first
+      cudaEventRecord(c->ev_tracker, c->stream);
+      cudaStreamWaitEvent(c->fe_stream, c->ev_tracker, 0);
+      c->stream = c->fe_stream;
+      active = true;
+    }
+  }
+  ~FeScope() { if (active) c->stream = saved; }
+};
 
 
 // ---- CUDA-graph cache ------------------------------------------------------------------------------------------------
@@ -529,6 +568,8 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
                                  int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
   if (!map || !d_images || !threshold) { rbv_set_error("rbv_detect: null argument"); return RBV_ERR_ARG; }
+  FeScope fe(c);
+  const bool on_fe = c->stream == c->fe_stream;
   const int B = c->P.lanes;
   int slot;
   float* h = stage_begin(c, &slot);   // reuse a staging slot for the B thresholds
@@ -544,6 +585,14 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
     TRY(fe_scale_space(c, d_images, 2));
     return fe_detect(c, map);
   }));
+  map->fe_valid = 0;
+  if (on_fe) {   // counts and auto thresholds leave on the front-end stream (rbv_detect_wait), the map's event follows them
+    RBV_CUDA(cudaMemcpyAsync(map->h_fe, map->count, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaMemcpyAsync(map->h_fe + B, map->threshold, sizeof(float) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaEventRecord(map->ready, c->stream));
+    map->fe_pending = 1;
+    map->fe_valid = 1;
+  }
   if (n_keylines || auto_threshold) {
     int* hc = c->h_cnt;
     float* ht = reinterpret_cast<float*>(c->h_cnt + B);
@@ -732,24 +781,45 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
 extern "C" int rbv_detect(rbv_ctx* c, rbv_map* map, const float* const* images, size_t pitch_bytes, const uint64_t* ts_us,
                           const float* threshold, int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
+  FeScope fe(c);
   return detect_host(c, map, (const void* const*)images, pitch_bytes, 0, ts_us, threshold, n_keylines, auto_threshold);
 }
 
 extern "C" int rbv_detect_u8(rbv_ctx* c, rbv_map* map, const uint8_t* const* images, size_t pitch_bytes, const uint64_t* ts_us,
                              const float* threshold, int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
+  FeScope fe(c);
   return detect_host(c, map, (const void* const*)images, pitch_bytes, 1, ts_us, threshold, n_keylines, auto_threshold);
+}
+
+// keyline counts and auto thresholds of the most recent detect into `map` (both optional, length B). After a detect on the
+// front-end stream this waits for that detect alone (the tracker stream keeps running); otherwise it reads the map.
+extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float* auto_threshold) {
+  CHECK_CTX(c);
+  if (!map) return RBV_ERR_ARG;
+  const size_t B = c->P.lanes;
+  if (map->fe_valid) {
+    RBV_CUDA(cudaEventSynchronize(map->ready));
+    if (n_keylines) memcpy(n_keylines, map->h_fe, sizeof(int) * B);
+    if (auto_threshold) memcpy(auto_threshold, map->h_fe + B, sizeof(float) * B);
+    return RBV_OK;
+  }
+  if (n_keylines) TRY(rbv_map_size(c, map, n_keylines));
+  if (auto_threshold) TRY(rbv_map_threshold(c, map, auto_threshold));
+  return RBV_OK;
 }
 
 // ---- tracker stages ----
 extern "C" int rbv_build_distance_field(rbv_ctx* c, rbv_map* map) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map) return RBV_ERR_ARG;
   return tr_build_field(c, map);
 }
 
 extern "C" int rbv_rotate_keylines(rbv_ctx* c, rbv_map* map, const float* R9) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map || !R9) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -760,6 +830,7 @@ extern "C" int rbv_rotate_keylines(rbv_ctx* c, rbv_map* map, const float* R9) {
 
 extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile, int num_bins, float* out) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map) return RBV_ERR_ARG;
   TRY(tr_quantile(c, map, percentile, num_bins, 0));
   if (out) {
@@ -771,12 +842,14 @@ extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile,
 
 extern "C" int rbv_reset_residuals(rbv_ctx* c, rbv_map* map) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map) return RBV_ERR_ARG;
   return rbv_fill32(c, map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax);   // core.cpp:158
 }
 
 extern "C" int rbv_try_vel(rbv_ctx* c, rbv_map* map, const float* vel3, const float* sigma_rho_min, float* JtJ9, float* JtF3, float* score) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map || !vel3 || !sigma_rho_min) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -832,6 +905,7 @@ static int fetch_lm(rbv_ctx* c, float* vel3, float* Rvel9, float* score) {
 
 extern "C" int rbv_minimize_vel(rbv_ctx* c, rbv_map* old_map, float* vel3, float* Rvel9, float* score) {
   CHECK_CTX(c);
+  MAP_READY(c, old_map);
   if (!old_map || !vel3) return RBV_ERR_ARG;
   if (!c->field_map) { rbv_set_error("minimizeVel before buildDistanceField"); return RBV_ERR_STATE; }
   int slot;
@@ -844,6 +918,8 @@ extern "C" int rbv_minimize_vel(rbv_ctx* c, rbv_map* old_map, float* vel3, float
 
 extern "C" int rbv_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, int* n_matches) {
   CHECK_CTX(c);
+  MAP_READY(c, old_map);
+  MAP_READY(c, new_map);
   if (!old_map || !new_map) return RBV_ERR_ARG;
   TRY(tr_forward_match(c, old_map, new_map));
   if (n_matches) {
@@ -864,6 +940,7 @@ static void copy_extrot_out(rbv_ctx* c, float* Wx36, float* X6, int* ok) {
 
 extern "C" int rbv_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, const float* vel3, float* Wx36, float* X6, int* ok) {
   CHECK_CTX(c);
+  MAP_READY(c, new_map);
   if (!new_map || !vel3) return RBV_ERR_ARG;
   if (c->field_map != new_map) { rbv_set_error("extRotVel: map is not the distance-field map (core.cpp:195)"); return RBV_ERR_STATE; }
   int slot;
@@ -886,6 +963,8 @@ static void put_directed(rbv_ctx* c, float* h, const float* vel3, const float* R
 extern "C" int rbv_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map, const float* vel3, const float* Rvel9,
                                   const float* Rback9, float max_radius, int* kf_matches, int* n_matches) {
   CHECK_CTX(c);
+  MAP_READY(c, new_map);
+  MAP_READY(c, old_map);
   if (!new_map || !old_map || !vel3 || !Rvel9 || !Rback9) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -904,6 +983,7 @@ extern "C" int rbv_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map
 
 extern "C" int rbv_regularize(rbv_ctx* c, rbv_map* map, int* n_regularized) {
   CHECK_CTX(c);
+  MAP_READY(c, map);
   if (!map) return RBV_ERR_ARG;
   TRY(tr_regularize(c, map));
   if (n_regularized) {
@@ -927,6 +1007,8 @@ extern "C" int rbv_update_inverse_depth(rbv_ctx* c, const float* vel3) {
 // ---- fused per-frame sequences (rebvio.cpp:142-177 and :223-259) ----
 // first half of a tracker frame as one (graph-replayed) kernel sequence; R.T() in lane_in[IN_R], lane_in[IN_VEL] = 0
 static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
+  MAP_READY(c, old_map);
+  MAP_READY(c, new_map);
   return run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
     SeqFused fused(c, 0);
     // two independent branches: the distance field of the NEW map (the longest kernel of the half, instruction bound at ~45 %
@@ -952,6 +1034,8 @@ static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
 
 // second half; R0, V, P_V, Rgva, max_radius in lane_in
 static int enqueue_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, int min_matches) {
+  MAP_READY(c, old_map);
+  MAP_READY(c, new_map);
   return run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
     SeqFused fused(c, min_matches, new_map);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
     TRY(tr_rotate(c, old_map));
@@ -1191,6 +1275,7 @@ extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, con
 // ---- host mirror (EdgeMap::keylines(), mask(), size(), threshold(); edge_map.hpp:40-75) ----
 extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || !n) return RBV_ERR_ARG;
   RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->count, sizeof(int) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
@@ -1199,6 +1284,7 @@ extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
 }
 extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || !t) return RBV_ERR_ARG;
   RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->threshold, sizeof(float) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
@@ -1207,6 +1293,7 @@ extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
 }
 extern "C" int rbv_map_set_threshold(rbv_ctx* c, rbv_map* m, const float* t) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || !t) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   RBV_CUDA(copy_sync(c, m->threshold, t, sizeof(float) * c->P.lanes, cudaMemcpyHostToDevice));
@@ -1225,6 +1312,7 @@ static cudaError_t push(rbv_ctx* c, const std::vector<T>& h, T* d, size_t lane, 
 
 extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* kl, uint32_t* pixel_idx, int cap, int* n_out) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !n_out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;
@@ -1262,6 +1350,7 @@ extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* k
 
 extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keyline* kl, const uint32_t* pixel_idx, int n) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || n < 0 || n > c->P.keylines_max || (n && !kl)) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   const size_t K = c->P.kmax, L = lane, N = c->P.npix;
@@ -1324,6 +1413,7 @@ extern "C" int rbv_debug_read_image(rbv_ctx* c, int lane, int which, float* out)
 
 extern "C" int rbv_debug_read_mask(rbv_ctx* c, rbv_map* m, int lane, int* out) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   RBV_CUDA(copy_sync(c, out, m->mask + (size_t)lane * c->P.npix, sizeof(int) * (size_t)c->P.npix, cudaMemcpyDeviceToHost));
@@ -1347,6 +1437,7 @@ extern "C" int rbv_debug_read_field(rbv_ctx* c, int lane, int* id, int* distance
 
 extern "C" int rbv_debug_read_residuals(rbv_ctx* c, rbv_map* m, int lane, float* out, int cap) {
   CHECK_CTX(c);
+  MAP_READY(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;

@@ -50,6 +50,9 @@ struct rbv_map {
   uint64_t* ts_us;   // host copy only
   void* slab;        // one allocation backing everything above
   size_t slab_bytes;
+  cudaEvent_t ready; // recorded behind a detect on the front-end stream; tracker entries wait for it (fe_pending)
+  int fe_pending, fe_valid;
+  int* h_fe;         // pinned [B] keyline counts + [B] auto thresholds of that detect (rbv_detect_wait)
 };
 
 // Levenberg-Marquardt state of Core::minimizeVel, one per lane, device resident
@@ -132,6 +135,8 @@ struct rbv_ctx {
   // frame upload: double-buffered raw staging on a copy stream (rbv_prefetch_frames) so that the H2D of frame k+1 overlaps
   // the tracker of frame k; u8 frames are converted (x 3.0, rebvio.cpp:43) on the device
   cudaStream_t copy_stream;
+  cudaStream_t fe_stream;     // front-end stream (RBV_TUNE_FE_STREAM): rbv_detect* next to the tracker of the previous frame pair
+  cudaEvent_t ev_tracker;
   cudaStream_t side_stream;   // second branch of rbv_track_g1: rotate + quantile of the old map next to the field build of the new one
   cudaEvent_t ev_fork, ev_join;
   void* raw[2];               // [B][N] bytes (u8) or floats (f32) as uploaded

@@ -57,9 +57,15 @@ def visual_fusion(R, Vg, Wx, X):
 
 
 class BatchedPipeline:
-    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None, imu_cfg=None):
+    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None, imu_cfg=None,
+                 overlap=False):
         """imu_cfg: None = visual-only fusion (rbv_track); True or a capi.ImuCfg = the reference's IMU filters on the device
-        (rbv_track_imu; push then takes `imu_in`, the integrated IMU of every lane, instead of R_rel)"""
+        (rbv_track_imu; push then takes `imu_in`, the integrated IMU of every lane, instead of R_rel).
+        overlap: the reference's two-thread schedule (rebvio.cpp:56-90 next to :92-293) on two CUDA streams: push(frame n+1)
+        enqueues the front end of frame n+1 on the context's front-end stream and, next to it, the tracker of the pair
+        (n-1, n); the tracker outputs a push returns are therefore those of the PREVIOUS frame (R_rel / imu_in passed to a push
+        belong to that pair too, i.e. to the frame pushed one call earlier). Three maps rotate. Results are bit-identical to
+        the in-order schedule, one call later."""
         self.ctx = host.Context(cam, det, mapc, core, lanes=lanes, device=device, reduce_mode=reduce_mode)
         self.with_imu = imu_cfg is not None
         if self.with_imu:
@@ -67,7 +73,11 @@ class BatchedPipeline:
         if cuda_stream is not None:
             self.ctx.set_stream(cuda_stream)
         self.lanes = lanes
-        self.maps = [self.ctx.new_map(), self.ctx.new_map()]
+        self.overlap = bool(overlap)
+        self.maps = [self.ctx.new_map() for _ in range(3 if self.overlap else 2)]
+        self.n_detected = 0
+        if self.overlap:
+            self.ctx.set_tuning(capi.TUNE_FE_STREAM, 1)
         self.cur = 0            # index of the map the next detect writes
         self.have_old = False
         self.threshold = np.full(lanes, np.float32(det.threshold), np.float32)   # config_->threshold per lane
@@ -106,6 +116,8 @@ class BatchedPipeline:
         memory. R_rel [B,3,3]: rotation of the camera since the previous frame. `next_frames`: the frames of the NEXT
         push; their upload is started right after this frame's front end so that it overlaps the tracker.
         Returns a dict of per-lane outputs (keyline counts always; velocities/matches once two frames are in)."""
+        if self.overlap:
+            return self._push_overlapped(frames, R_rel, device_ptr, ts_us, next_frames, imu_in)
         ctx, B = self.ctx, self.lanes
         self._servo()
         new = self.maps[self.cur]
@@ -134,5 +146,47 @@ class BatchedPipeline:
         self.frames_done += 1
         return out
 
+    def _push_overlapped(self, frames, R_rel, device_ptr, ts_us, next_frames, imu_in):
+        ctx, B = self.ctx, self.lanes
+        self._servo()                                   # with the keyline counts of the previous detect (edge_detector.cpp:33-36)
+        k = self.n_detected
+        new = self.maps[k % 3]
+        ts = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if ts_us is None else ts_us, np.uint64), (B,)))
+        # front end of frame k on the front-end stream: no outputs, no synchronisation
+        if device_ptr is not None:
+            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), None, None))
+        else:
+            fn = ctx.L.rbv_detect_u8 if frames.dtype == np.uint8 else ctx.L.rbv_detect
+            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), capi.ptr(self.threshold), None, None))
+        if next_frames is not None:
+            self.prefetch(next_frames)
+        out = {}
+        if k >= 2:                                      # tracker of the pair (k-2, k-1) on the tracker stream, next to that detect
+            old, mid = self.maps[(k - 2) % 3], self.maps[(k - 1) % 3]
+            if self.with_imu:
+                out.update(ctx.track_imu(old, mid, imu_in, 40.0, self.min_matches))
+            else:
+                out.update(ctx.track(old, mid, R_rel, 40.0, self.min_matches))
+            out["tracked_keylines"] = out.pop("keylines"); out.pop("auto_threshold", None)
+        n = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+        capi.check(ctx.L.rbv_detect_wait(ctx.h, new.h, capi.ptr(n), capi.ptr(at)))
+        out["keylines"], out["auto_threshold"] = n, at
+        self.count = n
+        self.n_detected += 1
+        self.frames_done += 1
+        return out
+
+    def flush(self, R_rel=None, imu_in=None):
+        """overlap mode: run the tracker of the last pair (the one a further push would have run) -> its outputs"""
+        k = self.n_detected
+        if not self.overlap or k < 2:
+            return {}
+        old, mid = self.maps[(k - 2) % 3], self.maps[(k - 1) % 3]
+        if self.with_imu:
+            return self.ctx.track_imu(old, mid, imu_in, 40.0, self.min_matches)
+        return self.ctx.track(old, mid, R_rel, 40.0, self.min_matches)
+
     def newest_map(self):
+        if self.overlap:
+            return self.maps[(self.n_detected - 1) % 3]
         return self.maps[1 - self.cur]

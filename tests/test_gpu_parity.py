@@ -525,3 +525,55 @@ def test_detector_and_tracker_threads_share_one_context():
         ctx.close()
         assert errs == []
         assert got == serial, trial
+
+
+@pytest.mark.parametrize("lanes,mode,imu", [(1, capi.REDUCE_FAST, False), (3, capi.REDUCE_ORDERED, False), (20, capi.REDUCE_FAST, True)])
+def test_front_end_stream_schedule_equals_in_order(lanes, mode, imu):
+    """SURVEY 8(b) threading: detect of frame n+1 on the front-end stream next to the tracker of (n-1, n) on the tracker stream
+    (RBV_TUNE_FE_STREAM, BatchedPipeline(overlap=True): the reference's two-thread schedule) gives bit-identical keylines,
+    tracker outputs and maps to the in-order single-stream schedule, one push later; host frames with prefetch included."""
+    from rebvio_b200.pipeline import BatchedPipeline
+    nfr = 8
+    spec = synth.config("C5:320x240", n_frames=nfr)
+    seq = synth.generate(spec)
+    B = lanes
+    u8 = np.stack([np.stack([np.ascontiguousarray(seq.frames[(k + b) % nfr]) for b in range(B)]) for k in range(nfr)]).astype(np.uint8)
+    R = np.stack([np.stack([seq.R_rel[k] for b in range(B)]) for k in range(nfr)]).astype(np.float32)
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+
+    def targs(k):
+        if not imu:
+            return dict(R_rel=R[k])
+        a = np.zeros(B, capi.IMU_IN)
+        a["R"] = R[k].reshape(B, 9); a["cacc"] = (0.0, -9.81, 0.0); a["dt_s"] = 0.05; a["frame_dt"] = 0.05
+        return dict(imu_in=a)
+
+    keys = ("Vg", "X", "Wx", "matches", "kf_matches", "ok") + (("imu",) if imu else ("V",))
+    # in order
+    pipe = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=mode, imu_cfg=True if imu else None)
+    ref = []
+    for k in range(nfr):
+        o = pipe.push(frames=u8[k], **(targs(k) if k else {}))
+        ref.append((o, [pipe.newest_map().keylines(b)[0].tobytes() for b in range(B)]))
+    pipe.close()
+    # two streams, with and without the prefetched upload
+    for prefetch in (False, True):
+        pipe = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=mode, imu_cfg=True if imu else None, overlap=True)
+        got = []
+        for k in range(nfr):
+            nxt = u8[k + 1] if (prefetch and k + 1 < nfr) else None
+            o = pipe.push(frames=u8[k], next_frames=nxt, **(targs(k - 1) if k >= 2 else {}))
+            assert np.array_equal(o["keylines"], ref[k][0]["keylines"]), k               # the detect of THIS push
+            assert np.array_equal(H.bits(o["auto_threshold"]), H.bits(ref[k][0]["auto_threshold"])), k
+            got.append(o)
+        got.append(pipe.flush(**targs(nfr - 1)))
+        for k in range(1, nfr):                                                      # tracker outputs of pair (k-1, k) arrive one push later
+            o, o0 = got[k + 1], ref[k][0]
+            for key in keys:
+                a, b = np.asarray(o[key]), np.asarray(o0[key])
+                assert a.tobytes() == b.tobytes(), (prefetch, k, key)
+        last = [pipe.newest_map().keylines(b)[0].tobytes() for b in range(B)]
+        assert last == ref[-1][1]                                                    # the newest map after its Kalman update
+        pipe.close()
