@@ -34,8 +34,8 @@ LANES_PER_GPU = 64
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=60)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--lanes", type=int, default=LANES_PER_GPU)
     ap.add_argument("--config", default="C2", help="sequence shape of every lane (C2 = 752x480 EuRoC-shaped)")
@@ -244,7 +244,7 @@ def run_b200(args):
     d_frames = frames_u8.to(torch.float32) * 3.0                     # rebvio.cpp:43 conversion, resident in HBM
     torch.cuda.synchronize()
     mode = capi.REDUCE_FAST if args.reduce == "fast" else capi.REDUCE_ORDERED
-    stream = torch.cuda.Stream(device=dev)
+    stream = torch.cuda.Stream(device=dev, priority=int(os.environ.get("BENCH_STREAM_PRIORITY", "-1")))   # tracker stream above the library's front-end stream (see rbv_create)
 
     def barrier():
         torch.cuda.synchronize()
