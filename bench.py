@@ -48,6 +48,8 @@ def parse():
                     "(rbv_track_imu: gyro-bias correction + scale-attitude-bias filter, SURVEY 8(f2)) instead of the visual-only fusion")
     ap.add_argument("--no-overlap", action="store_true", help="in-order schedule on one stream (detect, then the tracker of the same frame) "
                     "instead of the reference's two-thread schedule on two streams (detect of frame n+1 next to the tracker of n-1, n)")
+    ap.add_argument("--overlap", type=int, default=2, choices=[1, 2], help="1 = host threshold servo, front end of frame n+1 next to the tracker "
+                    "of (n-1, n); 2 = servo on the device, the front end runs one more frame ahead (BatchedPipeline overlap modes)")
     ap.add_argument("--tune", default="", help="implementation choices, e.g. '2=4,0=1' (rbv_set_tuning key=value pairs)")
     ap.add_argument("--kernel-table", default="", help="write the per-kernel CUDA-event table (one untimed step) here")
     return ap.parse_args()
@@ -236,7 +238,7 @@ def run_b200(args):
     cam, det, mapc, core = cfg_structs(spec)
     B, K, W = args.lanes, args.steps, args.warmup
     N = spec.cam.rows * spec.cam.cols
-    lag = 0 if args.no_overlap else 1        # overlapped schedule: push(k) runs detect(k) next to the tracker of the pair (k-2, k-1)
+    lag = 0 if args.no_overlap else args.overlap   # overlapped schedule: push(k) enqueues detect(k) next to the tracker of the pair (k-lag-1, k-lag)
     first = 1 + lag                          # first push that has a pair to track
     nf = first + W + K
     seeds = [1000 + LANES_PER_GPU * rank + i for i in range(B)]
@@ -280,7 +282,7 @@ def run_b200(args):
 
     # ---- leg 1: device-resident inputs ----------------------------------------------------------------------
     pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg,
-                           overlap=bool(lag))
+                           overlap=lag)
     tune = [tuple(int(x) for x in kv.split("=")) for kv in args.tune.split(",") if kv]
     for key, val in tune:
         pipe.ctx.set_tuning(key, val)
@@ -349,8 +351,9 @@ def run_b200(args):
             "config": {"workload": f"batched replay: {B} independent EuRoC-shaped {spec.cam.cols}x{spec.cam.rows} sequences per GPU "
                                    f"(C2 generator, seeds 1000+64*rank+i), step = 1 frame of every sequence through detect + tracker",
                        "lanes_per_gpu": B, "keylines_per_frame": K_mean, "matches_per_frame": match_sum / (B * K),
-                       "schedule": ("detect(n+1) on the front-end stream next to the tracker of (n-1, n) on the tracker stream, as the reference's "
-                                    "two threads (rebvio.cpp:56-90 / 92-293); every step = one detect + one tracker pass of all lanes") if lag
+                       "schedule": (f"front end on its own stream up to {lag} frame(s) ahead of the tracker of the pair (n-1, n) on the tracker stream, as the "
+                                    "reference's two threads (rebvio.cpp:56-90 / 92-293); every step = one detect + one tracker pass of all lanes"
+                                    + ("; threshold servo on the device" if lag == 2 else "")) if lag
                                    else "in order on one stream",
                        "reduce_mode": args.reduce, "fusion": "imu filters on device (rbv_track_imu)" if args.imu else "visual-only (rbv_track)",
                        "parallelism": f"replicas x{world} (no collective)",
@@ -384,7 +387,7 @@ def run_b200(args):
         torch.cuda.synchronize()
         hnp = h_frames.numpy()
         pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg,
-                               overlap=bool(lag))
+                               overlap=lag)
         if args.undistort:   # rebvio/include/rebvio/camera.hpp:26-40
             fm = 0.5 * (458.654 + 457.296)
             pipe.ctx.set_undistort([fm, fm, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0])

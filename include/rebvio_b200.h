@@ -202,9 +202,15 @@ int rbv_prefetch_frames(rbv_ctx* ctx, const void* const* images, size_t pitch_by
 int rbv_detect_device(rbv_ctx* ctx, rbv_map* map, const float* d_images, const uint64_t* ts_us,
                       const float* threshold, int* n_keylines, float* auto_threshold);
 
-/* keyline counts and auto thresholds (both optional, length B) of the most recent detect into `map`: after a detect on the
+/* Threshold servo on the device: every rbv_detect* call accepts threshold = NULL, meaning "servo config_->threshold of every lane
+ * from the keyline counts of this context's previous detect" (edge_detector.cpp:33-36, the same float32 statement as
+ * rbv_servo_threshold; the state starts at rbv_detector_cfg::threshold with a count of 0, and an explicit threshold array
+ * overwrites it). Such a detect needs nothing read back from the previous one, so front ends can be enqueued frames ahead of
+ * the tracker (RBV_TUNE_FE_STREAM); rbv_detect_wait's threshold_used returns what the servo chose.
+ *
+ * keyline counts, auto thresholds and thresholds used (all optional, length B) of the most recent detect into `map`: after a detect on the
  * front-end stream (RBV_TUNE_FE_STREAM) this waits for that detect only; otherwise it reads the map's counters. */
-int rbv_detect_wait(rbv_ctx* ctx, rbv_map* map, int* n_keylines, float* auto_threshold);
+int rbv_detect_wait(rbv_ctx* ctx, rbv_map* map, int* n_keylines, float* auto_threshold, float* threshold_used);
 
 /* host scalar servo of edge_detector.cpp:33-36: returns the new config_->threshold. */
 float rbv_servo_threshold(const rbv_detector_cfg* cfg, float threshold, int last_keyline_count);

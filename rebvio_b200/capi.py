@@ -94,7 +94,7 @@ _SIG = {
     "rbv_detect": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),
     "rbv_detect_u8": (C.c_int, [vp, vp, C.POINTER(vp), C.c_size_t, vp, vp, vp, vp]),
     "rbv_prefetch_frames": (C.c_int, [vp, C.POINTER(vp), C.c_size_t, C.c_int]),
-    "rbv_detect_wait": (C.c_int, [vp, vp, vp, vp]),
+    "rbv_detect_wait": (C.c_int, [vp, vp, vp, vp, vp]),
     "rbv_detect_device": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "rbv_servo_threshold": (C.c_float, [C.POINTER(DetectorCfg), C.c_float, C.c_int]),
     "rbv_build_distance_field": (C.c_int, [vp, vp]),

@@ -263,6 +263,12 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(dalloc(&c->rowcount, B * P.rows));
   RBV_CUDA(dalloc(&c->rowoffset, B * P.rows));
   RBV_CUDA(dalloc(&c->thr_dev, B));
+  RBV_CUDA(dalloc(&c->last_count, B));
+  {
+    std::vector<float> t0(B, det->threshold);
+    RBV_CUDA(cudaMemcpy(c->thr_dev, t0.data(), sizeof(float) * B, cudaMemcpyHostToDevice));
+    RBV_CUDA(cudaMemset(c->last_count, 0, sizeof(int) * B));
+  }
   RBV_CUDA(dalloc(&c->field, B * N));
   RBV_CUDA(dalloc(&c->tgt, 2 * B * K));
   RBV_CUDA(dalloc(&c->prod, 10 * B * K));
@@ -326,7 +332,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->field, c->prod, c->fiabs,
+  void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->last_count, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
                  c->partials, c->ticket, c->blkagg, c->tgt};
   for (void* p : dev) cudaFree(p);
@@ -376,6 +382,8 @@ extern "C" int rbv_set_reduce_mode(rbv_ctx* c, int mode) {
 extern "C" int rbv_set_tuning(rbv_ctx* c, int key, int value) {
   if (!c || key < 0 || key >= RBV_TUNE_COUNT || value < 0 || value > 64) return RBV_ERR_ARG;
   LOCK_CTX(c);
+  cudaStreamSynchronize(c->stream);
+  if (c->fe_stream) cudaStreamSynchronize(c->fe_stream);
   rbv_graphs_clear(c, nullptr);
   c->tune[key] = value;
   return RBV_OK;
@@ -423,7 +431,7 @@ extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   m->ts_us = (uint64_t*)calloc(B, sizeof(uint64_t));
   RBV_CUDA(cudaEventCreateWithFlags(&m->ready, cudaEventDisableTiming));
-  RBV_CUDA(cudaMallocHost((void**)&m->h_fe, B * 8));
+  RBV_CUDA(cudaMallocHost((void**)&m->h_fe, B * 12));
   *out = m;
   return RBV_OK;
 }
@@ -576,20 +584,40 @@ static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int f
   return RBV_OK;
 }
 
+// edge_detector.cpp:33-36 on the device, for callers that pass threshold = NULL: config_->threshold of every lane lives in thr_dev,
+// keylines_count_ in last_count (left there by the previous detect). Same float32 statement as rbv_servo_threshold (-fmad=false).
+// With the servo on the device a detect depends on nothing the host has to read back, so the front end can be enqueued frames ahead.
+__global__ void k_servo(float* __restrict__ thr, const int* __restrict__ last_count, int B, float gain, int keylines_ref, float tmin, float tmax) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float t = thr[b];
+  if (gain > 0) {
+    t -= gain * (float)(keylines_ref - last_count[b]);
+    t = (t > tmax) ? tmax : ((t < tmin) ? tmin : t);
+  }
+  thr[b] = t;
+}
+
 // ---- front end ----
 extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images, const uint64_t* ts_us, const float* threshold,
                                  int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
-  if (!map || !d_images || !threshold) { rbv_set_error("rbv_detect: null argument"); return RBV_ERR_ARG; }
+  if (!map || !d_images) { rbv_set_error("rbv_detect: null argument"); return RBV_ERR_ARG; }
   FeScope fe(c);
   const bool on_fe = c->stream == c->fe_stream;
   const int B = c->P.lanes;
-  int slot;
-  float* h = stage_begin(c, &slot);   // reuse a staging slot for the B thresholds
-  memcpy(h, threshold, sizeof(float) * B);
-  Stage* s = stage_of(c);
-  RBV_CUDA(cudaMemcpyAsync(c->thr_dev, h, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
-  RBV_CUDA(cudaEventRecord(s->ev[slot], c->stream));
+  if (threshold) {
+    int slot;
+    float* h = stage_begin(c, &slot);   // reuse a staging slot for the B thresholds
+    memcpy(h, threshold, sizeof(float) * B);
+    Stage* s = stage_of(c);
+    RBV_CUDA(cudaMemcpyAsync(c->thr_dev, h, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
+    RBV_CUDA(cudaEventRecord(s->ev[slot], c->stream));
+  } else {                              // threshold servo on the device from the previous detect's keyline counts
+    RBV_LAUNCH(c, k_servo, ((unsigned)((B + 127) / 128)), (128), 0, c->thr_dev, c->last_count, B, c->det.gain, c->det.keylines_ref,
+               c->det.min_threshold, c->det.max_threshold);
+    RBV_CUDA(cudaGetLastError());
+  }
   if (ts_us) memcpy(map->ts_us, ts_us, sizeof(uint64_t) * B);
   // the one kernel that reads the caller's frame buffer is launched directly; everything behind it works on the
   // context's own buffers and is replayed from a graph
@@ -599,9 +627,11 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
     return fe_detect(c, map);
   }));
   map->fe_valid = 0;
-  if (on_fe) {   // counts and auto thresholds leave on the front-end stream (rbv_detect_wait), the map's event follows them
+  RBV_CUDA(cudaMemcpyAsync(c->last_count, map->count, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));   // keylines_count_ for k_servo
+  if (on_fe) {   // counts, auto thresholds and the thresholds used leave on the front-end stream (rbv_detect_wait), the map's event follows them
     RBV_CUDA(cudaMemcpyAsync(map->h_fe, map->count, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     RBV_CUDA(cudaMemcpyAsync(map->h_fe + B, map->threshold, sizeof(float) * B, cudaMemcpyDeviceToHost, c->stream));
+    RBV_CUDA(cudaMemcpyAsync(map->h_fe + 2 * B, c->thr_dev, sizeof(float) * B, cudaMemcpyDeviceToHost, c->stream));
     RBV_CUDA(cudaEventRecord(map->ready, c->stream));
     map->fe_pending = 1;
     map->fe_valid = 1;
@@ -807,7 +837,7 @@ extern "C" int rbv_detect_u8(rbv_ctx* c, rbv_map* map, const uint8_t* const* ima
 
 // keyline counts and auto thresholds of the most recent detect into `map` (both optional, length B). After a detect on the
 // front-end stream this waits for that detect alone (the tracker stream keeps running); otherwise it reads the map.
-extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float* auto_threshold) {
+extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float* auto_threshold, float* threshold_used) {
   CHECK_CTX(c);
   if (!map) return RBV_ERR_ARG;
   const size_t B = c->P.lanes;
@@ -815,10 +845,12 @@ extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float*
     RBV_CUDA(cudaEventSynchronize(map->ready));
     if (n_keylines) memcpy(n_keylines, map->h_fe, sizeof(int) * B);
     if (auto_threshold) memcpy(auto_threshold, map->h_fe + B, sizeof(float) * B);
+    if (threshold_used) memcpy(threshold_used, map->h_fe + 2 * B, sizeof(float) * B);
     return RBV_OK;
   }
   if (n_keylines) TRY(rbv_map_size(c, map, n_keylines));
   if (auto_threshold) TRY(rbv_map_threshold(c, map, auto_threshold));
+  if (threshold_used) RBV_CUDA(copy_sync(c, threshold_used, c->thr_dev, sizeof(float) * B, cudaMemcpyDeviceToHost));   // of the context's latest detect
   return RBV_OK;
 }
 

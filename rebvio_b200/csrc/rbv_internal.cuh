@@ -105,7 +105,8 @@ struct rbv_ctx {
   unsigned* flags;  // [B][rows][wpr] bit flags
   int* rowcount;    // [B][rows]
   int* rowoffset;   // [B][rows]
-  float* thr_dev;   // [B] servoed thresholds of this detect
+  float* thr_dev;   // [B] servoed thresholds of this detect = config_->threshold of every lane (persistent: k_servo advances it)
+  int* last_count;  // [B] keyline counts of the most recent detect (EdgeDetector::keylines_count_), input of k_servo
   // tracker scratch
   unsigned* field;  // [B][N]
   float4* tgt;      // [B][kmax][2] packed target keylines of the distance-field map (k_pack_targets)
@@ -181,7 +182,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
-  X(k_imu_pre) X(k_imu_fuse)
+  X(k_imu_pre) X(k_imu_fuse) X(k_servo)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)

@@ -65,7 +65,11 @@ class BatchedPipeline:
         enqueues the front end of frame n+1 on the context's front-end stream and, next to it, the tracker of the pair
         (n-1, n); the tracker outputs a push returns are therefore those of the PREVIOUS frame (R_rel / imu_in passed to a push
         belong to that pair too, i.e. to the frame pushed one call earlier). Three maps rotate. Results are bit-identical to
-        the in-order schedule, one call later."""
+        the in-order schedule, one call later.
+        overlap=2: the same with the threshold servo on the device (rbv_detect* with threshold = NULL), so that a front end
+        needs nothing read back from the previous one: push(frame n+2) enqueues its front end behind the one of frame n+1
+        (possibly still running) and tracks the pair (n-1, n); the front-end stream always has work queued next to the
+        tracker. Four maps rotate, outputs arrive two calls later, `keylines` are those of the tracked pair's new map."""
         self.ctx = host.Context(cam, det, mapc, core, lanes=lanes, device=device, reduce_mode=reduce_mode)
         self.with_imu = imu_cfg is not None
         if self.with_imu:
@@ -74,7 +78,9 @@ class BatchedPipeline:
             self.ctx.set_stream(cuda_stream)
         self.lanes = lanes
         self.overlap = bool(overlap)
-        self.maps = [self.ctx.new_map() for _ in range(3 if self.overlap else 2)]
+        self.lag = int(overlap)                       # 0 in order, 1 detect next to the previous pair's tracker, 2 front end one more frame ahead
+        self.nmaps = 2 + self.lag
+        self.maps = [self.ctx.new_map() for _ in range(self.nmaps)]
         self.n_detected = 0
         if self.overlap:
             self.ctx.set_tuning(capi.TUNE_FE_STREAM, 1)
@@ -147,46 +153,63 @@ class BatchedPipeline:
         return out
 
     def _push_overlapped(self, frames, R_rel, device_ptr, ts_us, next_frames, imu_in):
-        ctx, B = self.ctx, self.lanes
-        self._servo()                                   # with the keyline counts of the previous detect (edge_detector.cpp:33-36)
+        ctx, B, lag, M = self.ctx, self.lanes, self.lag, self.nmaps
         k = self.n_detected
-        new = self.maps[k % 3]
+        new = self.maps[k % M]
+        if lag == 1:
+            self._servo()                               # with the keyline counts of the previous detect (edge_detector.cpp:33-36)
+            thr = capi.ptr(self.threshold)
+        else:
+            thr = None                                  # servo on the device: nothing of the previous detect is read back
         ts = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if ts_us is None else ts_us, np.uint64), (B,)))
         # front end of frame k on the front-end stream: no outputs, no synchronisation
         if device_ptr is not None:
-            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), capi.ptr(self.threshold), None, None))
+            capi.check(ctx.L.rbv_detect_device(ctx.h, new.h, C.c_void_p(device_ptr), capi.ptr(ts), thr, None, None))
         else:
             fn = ctx.L.rbv_detect_u8 if frames.dtype == np.uint8 else ctx.L.rbv_detect
-            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), capi.ptr(self.threshold), None, None))
+            capi.check(fn(ctx.h, new.h, self._host_ptrs(frames), 0, capi.ptr(ts), thr, None, None))
         if next_frames is not None:
             self.prefetch(next_frames)
         out = {}
-        if k >= 2:                                      # tracker of the pair (k-2, k-1) on the tracker stream, next to that detect
-            old, mid = self.maps[(k - 2) % 3], self.maps[(k - 1) % 3]
+        if k >= lag + 1:                                # tracker of the pair (k-lag-1, k-lag) on the tracker stream, next to the front end(s)
+            old, mid = self.maps[(k - lag - 1) % M], self.maps[(k - lag) % M]
             if self.with_imu:
                 out.update(ctx.track_imu(old, mid, imu_in, 40.0, self.min_matches))
             else:
                 out.update(ctx.track(old, mid, R_rel, 40.0, self.min_matches))
-            out["tracked_keylines"] = out.pop("keylines"); out.pop("auto_threshold", None)
-        n = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
-        capi.check(ctx.L.rbv_detect_wait(ctx.h, new.h, capi.ptr(n), capi.ptr(at)))
-        out["keylines"], out["auto_threshold"] = n, at
-        self.count = n
+            out["tracked_keylines"] = out["keylines"]
+        if lag == 1:
+            n = np.zeros(B, np.int32); at = np.zeros(B, np.float32)
+            capi.check(ctx.L.rbv_detect_wait(ctx.h, new.h, capi.ptr(n), capi.ptr(at), None))
+            out["keylines"], out["auto_threshold"] = n, at
+            self.count = n
         self.n_detected += 1
         self.frames_done += 1
         return out
 
-    def flush(self, R_rel=None, imu_in=None):
-        """overlap mode: run the tracker of the last pair (the one a further push would have run) -> its outputs"""
-        k = self.n_detected
-        if not self.overlap or k < 2:
-            return {}
-        old, mid = self.maps[(k - 2) % 3], self.maps[(k - 1) % 3]
-        if self.with_imu:
-            return self.ctx.track_imu(old, mid, imu_in, 40.0, self.min_matches)
-        return self.ctx.track(old, mid, R_rel, 40.0, self.min_matches)
+    def detect_results(self, back=0):
+        """overlap modes: (keyline counts, auto thresholds, thresholds used) of the detect `back` pushes ago; waits for that detect only"""
+        m = self.maps[(self.n_detected - 1 - back) % self.nmaps]
+        B = self.lanes
+        n = np.zeros(B, np.int32); at = np.zeros(B, np.float32); th = np.zeros(B, np.float32)
+        capi.check(self.ctx.L.rbv_detect_wait(self.ctx.h, m.h, capi.ptr(n), capi.ptr(at), capi.ptr(th)))
+        return n, at, th
+
+    def flush(self, args=()):
+        """overlap modes: run the trackers of the pairs still in flight; `args` = one dict(R_rel=... | imu_in=...) per pair, oldest
+        first -> list of their outputs"""
+        k, lag, M = self.n_detected, self.lag, self.nmaps
+        outs = []
+        for i, a in zip(range(lag), args):
+            j = k + i                                   # the push that would have tracked this pair
+            if j < lag + 1:
+                continue
+            old, mid = self.maps[(j - lag - 1) % M], self.maps[(j - lag) % M]
+            outs.append(self.ctx.track_imu(old, mid, a["imu_in"], 40.0, self.min_matches) if self.with_imu
+                        else self.ctx.track(old, mid, a["R_rel"], 40.0, self.min_matches))
+        return outs
 
     def newest_map(self):
         if self.overlap:
-            return self.maps[(self.n_detected - 1) % 3]
+            return self.maps[(self.n_detected - 1) % self.nmaps]
         return self.maps[1 - self.cur]

@@ -558,22 +558,26 @@ def test_front_end_stream_schedule_equals_in_order(lanes, mode, imu):
         o = pipe.push(frames=u8[k], **(targs(k) if k else {}))
         ref.append((o, [pipe.newest_map().keylines(b)[0].tobytes() for b in range(B)]))
     pipe.close()
-    # two streams, with and without the prefetched upload
-    for prefetch in (False, True):
-        pipe = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=mode, imu_cfg=True if imu else None, overlap=True)
+    # two streams (lag 1: host servo; lag 2: servo on the device, front end one more frame ahead), with and without the prefetched upload
+    for lag, prefetch in ((1, False), (1, True), (2, False), (2, True)):
+        pipe = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=mode, imu_cfg=True if imu else None, overlap=lag)
         got = []
         for k in range(nfr):
             nxt = u8[k + 1] if (prefetch and k + 1 < nfr) else None
-            o = pipe.push(frames=u8[k], next_frames=nxt, **(targs(k - 1) if k >= 2 else {}))
-            assert np.array_equal(o["keylines"], ref[k][0]["keylines"]), k               # the detect of THIS push
-            assert np.array_equal(H.bits(o["auto_threshold"]), H.bits(ref[k][0]["auto_threshold"])), k
+            o = pipe.push(frames=u8[k], next_frames=nxt, **(targs(k - lag) if k >= lag + 1 else {}))
+            if lag == 1:                                                              # the detect of THIS push
+                assert np.array_equal(o["keylines"], ref[k][0]["keylines"]), k
+                assert np.array_equal(H.bits(o["auto_threshold"]), H.bits(ref[k][0]["auto_threshold"])), k
             got.append(o)
-        got.append(pipe.flush(**targs(nfr - 1)))
-        for k in range(1, nfr):                                                      # tracker outputs of pair (k-1, k) arrive one push later
-            o, o0 = got[k + 1], ref[k][0]
+        n, at, th = pipe.detect_results()
+        assert np.array_equal(n, ref[-1][0]["keylines"]) and np.array_equal(H.bits(at), H.bits(ref[-1][0]["auto_threshold"]))
+        got.extend(pipe.flush([targs(nfr - lag + i) for i in range(lag)]))
+        for k in range(1, nfr):                                                      # tracker outputs of pair (k-1, k) arrive `lag` pushes later
+            o, o0 = got[k + lag], ref[k][0]
+            assert np.array_equal(o["tracked_keylines"] if "tracked_keylines" in o else o["keylines"], o0["keylines"]), (lag, k)
             for key in keys:
                 a, b = np.asarray(o[key]), np.asarray(o0[key])
-                assert a.tobytes() == b.tobytes(), (prefetch, k, key)
+                assert a.tobytes() == b.tobytes(), (lag, prefetch, k, key)
         last = [pipe.newest_map().keylines(b)[0].tobytes() for b in range(B)]
         assert last == ref[-1][1]                                                    # the newest map after its Kalman update
         pipe.close()
