@@ -66,6 +66,8 @@ class Device {
   Device& operator=(const Device&) = delete;
   rbv_ctx* ctx() const { return ctx_; }
   int keylines_max() const { return kmax_; }
+  // the two worker loops of Rebvio get a CUDA stream each (RBV_TUNE_FE_STREAM): detect of frame n+1 runs next to the tracker of n-1, n
+  void useFrontEndStream(bool on = true) { check(rbv_set_tuning(ctx_, RBV_TUNE_FE_STREAM, on ? 1 : 0), "rbv_set_tuning"); }
   // Camera::undistort on the device (camera.hpp:54-58): K_ = [fm 0 cx; 0 fm cy; 0 0 1], D_ = (k1, k2, p1, p2, k3); raw frames from then on
   void setUndistort(float fm, float cx, float cy, float k1, float k2, float p1, float p2, float k3) {
     const float K4[4] = {fm, fm, cx, cy}, D5[5] = {k1, k2, p1, p2, k3};
@@ -189,7 +191,9 @@ class EdgeDetector {
     EdgeMap::SharedPtr map = reuse ? reuse : std::make_shared<EdgeMap>(dev_, ts_us);
     if (reuse) map->reset(ts_us);
     float at = 0;
-    check(rbv_detect_u8(dev_->ctx(), map->handle(), &image, pitch_bytes, &ts_us, &config_->threshold, &keylines_count_, &at), "rbv_detect_u8");
+    // enqueue without outputs, then wait for this detect alone: with Device::useFrontEndStream() the tracker stream keeps running
+    check(rbv_detect_u8(dev_->ctx(), map->handle(), &image, pitch_bytes, &ts_us, &config_->threshold, nullptr, nullptr), "rbv_detect_u8");
+    check(rbv_detect_wait(dev_->ctx(), map->handle(), &keylines_count_, &at, nullptr), "rbv_detect_wait");
     auto_threshold_ = at;
     return map;
   }

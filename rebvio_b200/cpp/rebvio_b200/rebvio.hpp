@@ -18,6 +18,8 @@
 //    edge-image callback is valid until the estimation thread has used it as the OLD map of the next pair.
 //  * all filter state lives in the device context (no function-local statics, core.cpp:292-298,340-343), so any number of
 //    Rebvio objects can share a process.
+//  * the two loops have a CUDA stream each (RBV_TUNE_FE_STREAM) and rbv_track_imu drops the context lock while it waits for the device,
+//    so detect of frame n+1 really runs next to the tracker of frames n-1, n, as on the reference's two CPU threads.
 //  * waitIdle() lets a replay driver drain the queues deterministically; the reference has no such call (its test sleeps).
 // Stop conditions are the reference's: NaN in the fused velocity or fewer directed matches than
 // CoreConfig::global_min_matches_threshold end the run (rebvio.cpp:236-252); running() then returns false.
@@ -178,6 +180,7 @@ struct RebvioConfig {                 // rebvio::RebvioConfig (rebvio.hpp:29-33)
   float distortion[5] = {-0.28340811f, 0.07395907f, 0.00019359f, 1.76187114e-05f, 0.0f};   // camera.hpp:35 (k1 k2 p1 p2 k3)
   int device = 0;
   int map_pool = 3;                   // >= 3: old + new on the tracker, one in the detector
+  bool two_streams = true;            // the acquisition loop's detect on the front-end stream, next to the estimation loop's tracker call
 };
 
 class Rebvio {
@@ -190,6 +193,7 @@ class Rebvio {
     if (config_.undistort)
       dev_->setUndistort(config_.camera.fm_, config_.camera.cx_, config_.camera.cy_, config_.distortion[0], config_.distortion[1],
                          config_.distortion[2], config_.distortion[3], config_.distortion[4]);
+    dev_->useFrontEndStream(config_.two_streams);
     check(rbv_imu_reset(dev_->ctx(), &config_.imu_state), "rbv_imu_reset");
     edge_detector_.reset(new EdgeDetector(dev_, det_cfg_));
     for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) Rt_c2i_[i * 3 + j] = config_.R_c2i[j * 3 + i];

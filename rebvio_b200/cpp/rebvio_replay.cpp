@@ -94,6 +94,7 @@ int main(int argc, char** argv) {
     rebvio.registerOdometryCallback([&](types::Odometry& o) { std::fprintf(out, "%s\n", types::odometry_line(o).c_str()); ++lines; });
     rebvio.registerEdgeImageCallback([&](const types::Image&, EdgeMap::SharedPtr& m) { if (m->ts_us() || edge_images == 0) ++edge_images; });
     int j = 0;
+    const auto t0 = std::chrono::steady_clock::now();
     for (int k = 0; k < s.n_frames && rebvio.running(); ++k) {
       while (j < s.n_imu && s.imu_ts[j] <= s.ts[k]) { rebvio.imuCallback(sample(s, j)); ++j; }
       types::Image img;
@@ -104,8 +105,9 @@ int main(int argc, char** argv) {
       if (wait) rebvio.waitIdle();
     }
     rebvio.waitIdle();
-    std::fprintf(stderr, "rebvio_replay: %d frames in, %d edge images, %d odometry lines, scale K %.6f, last matches %d, running %d\n", s.n_frames,
-                 edge_images, lines, rebvio.lastState().K, rebvio.lastMatches(), (int)rebvio.running());
+    const double wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::fprintf(stderr, "rebvio_replay: %d frames in, %d edge images, %d odometry lines, scale K %.6f, last matches %d, running %d, %.1f frames/s wall\n",
+                 s.n_frames, edge_images, lines, rebvio.lastState().K, rebvio.lastMatches(), (int)rebvio.running(), s.n_frames / wall_s);
   } catch (const std::exception& e) {
     std::fprintf(stderr, "rebvio_replay: %s\n", e.what());
     std::fclose(out);

@@ -431,6 +431,7 @@ extern "C" int rbv_map_create(rbv_ctx* c, rbv_map** out) {
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   m->ts_us = (uint64_t*)calloc(B, sizeof(uint64_t));
   RBV_CUDA(cudaEventCreateWithFlags(&m->ready, cudaEventDisableTiming));
+  RBV_CUDA(cudaEventCreateWithFlags(&m->used, cudaEventDisableTiming));
   RBV_CUDA(cudaMallocHost((void**)&m->h_fe, B * 12));
   *out = m;
   return RBV_OK;
@@ -447,6 +448,7 @@ extern "C" void rbv_map_release(rbv_ctx* c, rbv_map* m) {
     rbv_graphs_clear(c, m);
   }
   if (m->ready) cudaEventDestroy(m->ready);
+  if (m->used) cudaEventDestroy(m->used);
   if (m->h_fe) cudaFreeHost(m->h_fe);
   cudaFree(m->slab);
   free(m->ts_us);
@@ -498,15 +500,27 @@ static int fetch_cnt(rbv_ctx* c) {
   do {                                                                                                    \
     if ((m) && (m)->fe_pending) { RBV_CUDA(cudaStreamWaitEvent((c)->stream, (m)->ready, 0)); (m)->fe_pending = 0; } \
   } while (0)
+// every tracker / mirror entry leaves an event on the tracker stream behind its work for the maps it was given (declared right
+// behind MAP_READY, so it fires on every return path while the context lock is still held)
+struct MapUse {
+  rbv_ctx* c;
+  rbv_map *a, *b;
+  MapUse(rbv_ctx* ctx, rbv_map* m1, rbv_map* m2 = nullptr) : c(ctx), a(m1), b(m2) {}
+  ~MapUse() {
+    if (c->tune[RBV_TUNE_FE_STREAM] != 1) return;   // one stream: program order is enough
+    if (a && a->used) { cudaEventRecord(a->used, c->stream); a->used_valid = 1; }
+    if (b && b->used) { cudaEventRecord(b->used, c->stream); b->used_valid = 1; }
+  }
+};
 struct FeScope {
   rbv_ctx* c;
   cudaStream_t saved;
   bool active;
-  explicit FeScope(rbv_ctx* ctx) : c(ctx), saved(ctx->stream), active(false) {
+  FeScope(rbv_ctx* ctx, rbv_map* target) : c(ctx), saved(ctx->stream), active(false) {
     if (c->tune[RBV_TUNE_FE_STREAM] == 1 && c->fe_stream && c->stream != c->fe_stream && c->prof_mode != -2) {
-      // whatever the tracker stream has been given so far may still read the map this detect overwrites: it comes first
-      cudaEventRecord(c->ev_tracker, c->stream);
-      cudaStreamWaitEvent(c->fe_stream, c->ev_tracker, 0);
+      // tracker work that was given the map this detect overwrites comes first (other tracker work may still be running: the
+      // reference's estimation thread works on maps n-1, n while its acquisition thread fills map n+1)
+      if (target && target->used_valid) cudaStreamWaitEvent(c->fe_stream, target->used, 0);
       c->stream = c->fe_stream;
       active = true;
     }
@@ -603,7 +617,7 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
                                  int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
   if (!map || !d_images) { rbv_set_error("rbv_detect: null argument"); return RBV_ERR_ARG; }
-  FeScope fe(c);
+  FeScope fe(c, map);
   const bool on_fe = c->stream == c->fe_stream;
   const int B = c->P.lanes;
   if (threshold) {
@@ -824,14 +838,14 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
 extern "C" int rbv_detect(rbv_ctx* c, rbv_map* map, const float* const* images, size_t pitch_bytes, const uint64_t* ts_us,
                           const float* threshold, int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
-  FeScope fe(c);
+  FeScope fe(c, map);
   return detect_host(c, map, (const void* const*)images, pitch_bytes, 0, ts_us, threshold, n_keylines, auto_threshold);
 }
 
 extern "C" int rbv_detect_u8(rbv_ctx* c, rbv_map* map, const uint8_t* const* images, size_t pitch_bytes, const uint64_t* ts_us,
                              const float* threshold, int* n_keylines, float* auto_threshold) {
   CHECK_CTX(c);
-  FeScope fe(c);
+  FeScope fe(c, map);
   return detect_host(c, map, (const void* const*)images, pitch_bytes, 1, ts_us, threshold, n_keylines, auto_threshold);
 }
 
@@ -858,6 +872,7 @@ extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float*
 extern "C" int rbv_build_distance_field(rbv_ctx* c, rbv_map* map) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map) return RBV_ERR_ARG;
   return tr_build_field(c, map);
 }
@@ -865,6 +880,7 @@ extern "C" int rbv_build_distance_field(rbv_ctx* c, rbv_map* map) {
 extern "C" int rbv_rotate_keylines(rbv_ctx* c, rbv_map* map, const float* R9) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map || !R9) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -876,6 +892,7 @@ extern "C" int rbv_rotate_keylines(rbv_ctx* c, rbv_map* map, const float* R9) {
 extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile, int num_bins, float* out) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map) return RBV_ERR_ARG;
   TRY(tr_quantile(c, map, percentile, num_bins, 0));
   if (out) {
@@ -888,6 +905,7 @@ extern "C" int rbv_estimate_quantile(rbv_ctx* c, rbv_map* map, float percentile,
 extern "C" int rbv_reset_residuals(rbv_ctx* c, rbv_map* map) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map) return RBV_ERR_ARG;
   return rbv_fill32(c, map->k.residual, 0u, (size_t)c->P.lanes * c->P.kmax);   // core.cpp:158
 }
@@ -895,6 +913,7 @@ extern "C" int rbv_reset_residuals(rbv_ctx* c, rbv_map* map) {
 extern "C" int rbv_try_vel(rbv_ctx* c, rbv_map* map, const float* vel3, const float* sigma_rho_min, float* JtJ9, float* JtF3, float* score) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map || !vel3 || !sigma_rho_min) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -951,6 +970,7 @@ static int fetch_lm(rbv_ctx* c, float* vel3, float* Rvel9, float* score) {
 extern "C" int rbv_minimize_vel(rbv_ctx* c, rbv_map* old_map, float* vel3, float* Rvel9, float* score) {
   CHECK_CTX(c);
   MAP_READY(c, old_map);
+  MapUse map_use_(c, old_map);
   if (!old_map || !vel3) return RBV_ERR_ARG;
   if (!c->field_map) { rbv_set_error("minimizeVel before buildDistanceField"); return RBV_ERR_STATE; }
   int slot;
@@ -965,6 +985,7 @@ extern "C" int rbv_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map,
   CHECK_CTX(c);
   MAP_READY(c, old_map);
   MAP_READY(c, new_map);
+  MapUse map_use_(c, old_map, new_map);
   if (!old_map || !new_map) return RBV_ERR_ARG;
   TRY(tr_forward_match(c, old_map, new_map));
   if (n_matches) {
@@ -986,6 +1007,7 @@ static void copy_extrot_out(rbv_ctx* c, float* Wx36, float* X6, int* ok) {
 extern "C" int rbv_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, const float* vel3, float* Wx36, float* X6, int* ok) {
   CHECK_CTX(c);
   MAP_READY(c, new_map);
+  MapUse map_use_(c, new_map);
   if (!new_map || !vel3) return RBV_ERR_ARG;
   if (c->field_map != new_map) { rbv_set_error("extRotVel: map is not the distance-field map (core.cpp:195)"); return RBV_ERR_STATE; }
   int slot;
@@ -1010,6 +1032,7 @@ extern "C" int rbv_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map
   CHECK_CTX(c);
   MAP_READY(c, new_map);
   MAP_READY(c, old_map);
+  MapUse map_use_(c, new_map, old_map);
   if (!new_map || !old_map || !vel3 || !Rvel9 || !Rback9) return RBV_ERR_ARG;
   int slot;
   float* h = stage_begin(c, &slot);
@@ -1029,6 +1052,7 @@ extern "C" int rbv_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map
 extern "C" int rbv_regularize(rbv_ctx* c, rbv_map* map, int* n_regularized) {
   CHECK_CTX(c);
   MAP_READY(c, map);
+  MapUse map_use_(c, map);
   if (!map) return RBV_ERR_ARG;
   TRY(tr_regularize(c, map));
   if (n_regularized) {
@@ -1040,6 +1064,8 @@ extern "C" int rbv_regularize(rbv_ctx* c, rbv_map* map, int* n_regularized) {
 
 extern "C" int rbv_update_inverse_depth(rbv_ctx* c, const float* vel3) {
   CHECK_CTX(c);
+  MAP_READY(c, c->field_map);
+  MapUse map_use_(c, c->field_map);
   if (!vel3) return RBV_ERR_ARG;
   if (!c->field_map) { rbv_set_error("updateInverseDepth before buildDistanceField"); return RBV_ERR_STATE; }
   int slot;
@@ -1054,6 +1080,7 @@ extern "C" int rbv_update_inverse_depth(rbv_ctx* c, const float* vel3) {
 static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
   MAP_READY(c, old_map);
   MAP_READY(c, new_map);
+  MapUse map_use_(c, old_map, new_map);
   return run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
     SeqFused fused(c, 0);
     // two independent branches: the distance field of the NEW map (the longest kernel of the half, instruction bound at ~45 %
@@ -1081,6 +1108,7 @@ static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
 static int enqueue_g2(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, int min_matches) {
   MAP_READY(c, old_map);
   MAP_READY(c, new_map);
+  MapUse map_use_(c, old_map, new_map);
   return run_graphed(c, GK_TRACK2, old_map, new_map, min_matches, [&]() -> int {
     SeqFused fused(c, min_matches, new_map);   // lanes below the match floor skip regularise + Kalman (rebvio.cpp:247-252)
     TRY(tr_rotate(c, old_map));
@@ -1285,7 +1313,11 @@ extern "C" int rbv_imu_fuse(rbv_ctx* c, const float* Vg3, const float* Wx36, con
 extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, const rbv_imu_in* in, float max_radius,
                              int min_matches, float* Vg3, float* PVg9, float* Wx36, float* X6, int* ok, rbv_imu_out* out,
                              int* n_matches, int* kf_matches, int* n_keylines_new, float* auto_threshold_new) {
-  CHECK_CTX(c);
+  if (!c) { rbv_set_error("null context"); return RBV_ERR_ARG; }
+  // outermost entry (never called with the lock held): the lock is dropped while the call waits for the device at its end, so that the
+  // reference's acquisition thread can enqueue the next detect on the front-end stream meanwhile (RBV_TUNE_FE_STREAM)
+  std::unique_lock<std::recursive_mutex> ctx_lock_(*static_cast<std::recursive_mutex*>(c->mtx));
+  RBV_CUDA(cudaSetDevice(c->device));
   if (!old_map || !new_map || !in) return RBV_ERR_ARG;
   TRY(imu_ready(c));
   const size_t B = c->P.lanes;
@@ -1302,7 +1334,19 @@ extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, con
   RBV_CUDA(cudaMemcpyAsync(c->h_lm, c->lm, sizeof(LMState) * B, cudaMemcpyDeviceToHost, c->stream));
   TRY(enqueue_g2(c, old_map, new_map, min_matches));
   RBV_CUDA(cudaMemcpyAsync(imu_host_out(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
-  TRY(fetch_cnt(c));   // synchronises
+  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, c->lane_cnt, sizeof(int) * B * CNT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  if (c->tune[RBV_TUNE_FE_STREAM] == 1) {
+    RBV_CUDA(cudaEventRecord(old_map->used, c->stream)); old_map->used_valid = 1;
+    RBV_CUDA(cudaEventRecord(new_map->used, c->stream)); new_map->used_valid = 1;
+  }
+  {
+    cudaStream_t st = c->stream;
+    const bool drop = c->tune[RBV_TUNE_FE_STREAM] == 1;   // h_cnt, h_out, h_lm and the IMU mirror are this call's own until it returns
+    if (drop) ctx_lock_.unlock();
+    const cudaError_t se = cudaStreamSynchronize(st);
+    if (drop) { ctx_lock_.lock(); cudaSetDevice(c->device); }
+    RBV_CUDA(se);
+  }
   const LMState* L = reinterpret_cast<const LMState*>(c->h_lm);
   for (size_t b = 0; b < B; ++b) {
     if (Vg3) memcpy(Vg3 + b * 3, L[b].vel, 12);
@@ -1321,6 +1365,7 @@ extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, con
 extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || !n) return RBV_ERR_ARG;
   RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->count, sizeof(int) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
@@ -1330,6 +1375,7 @@ extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
 extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || !t) return RBV_ERR_ARG;
   RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->threshold, sizeof(float) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
@@ -1339,6 +1385,7 @@ extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
 extern "C" int rbv_map_set_threshold(rbv_ctx* c, rbv_map* m, const float* t) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || !t) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   RBV_CUDA(copy_sync(c, m->threshold, t, sizeof(float) * c->P.lanes, cudaMemcpyHostToDevice));
@@ -1358,6 +1405,7 @@ static cudaError_t push(rbv_ctx* c, const std::vector<T>& h, T* d, size_t lane, 
 extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* kl, uint32_t* pixel_idx, int cap, int* n_out) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !n_out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;
@@ -1396,6 +1444,7 @@ extern "C" int rbv_map_download(rbv_ctx* c, rbv_map* m, int lane, rbv_keyline* k
 extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keyline* kl, const uint32_t* pixel_idx, int n) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || n < 0 || n > c->P.keylines_max || (n && !kl)) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   const size_t K = c->P.kmax, L = lane, N = c->P.npix;
@@ -1459,6 +1508,7 @@ extern "C" int rbv_debug_read_image(rbv_ctx* c, int lane, int which, float* out)
 extern "C" int rbv_debug_read_mask(rbv_ctx* c, rbv_map* m, int lane, int* out) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   RBV_CUDA(copy_sync(c, out, m->mask + (size_t)lane * c->P.npix, sizeof(int) * (size_t)c->P.npix, cudaMemcpyDeviceToHost));
@@ -1483,6 +1533,7 @@ extern "C" int rbv_debug_read_field(rbv_ctx* c, int lane, int* id, int* distance
 extern "C" int rbv_debug_read_residuals(rbv_ctx* c, rbv_map* m, int lane, float* out, int cap) {
   CHECK_CTX(c);
   MAP_READY(c, m);
+  MapUse map_use_(c, m);
   if (!m || lane < 0 || lane >= c->P.lanes || !out) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
   int n = 0;

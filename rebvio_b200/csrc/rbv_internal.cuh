@@ -52,6 +52,8 @@ struct rbv_map {
   size_t slab_bytes;
   cudaEvent_t ready; // recorded behind a detect on the front-end stream; tracker entries wait for it (fe_pending)
   int fe_pending, fe_valid;
+  cudaEvent_t used;  // recorded on the tracker stream behind every tracker / mirror entry that was given this map; a detect INTO the map waits for it
+  int used_valid;
   int* h_fe;         // pinned [B] keyline counts + [B] auto thresholds of that detect (rbv_detect_wait)
 };
 
