@@ -172,7 +172,7 @@ def run_reference(args):
                              "sample": f"{args.steps} frames on each of {cores} processes (reference -O3 build)"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -446,12 +446,25 @@ def run_b200(args):
                                 "sample": f"{ns} frames of lane 0's sequence, single thread, "
                                           + ("unmodified reference sources (-O3 -march=x86-64-v3)" if kind == "reference" else "plain-C oracle port")}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_OUT = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's real stdout"""
+    (_OUT or sys.stdout).write(json.dumps(line) + "\n")
+    (_OUT or sys.stdout).flush()
+
+
 if __name__ == "__main__":
+    # libraries print to stdout as well (NCCL's "NCCL version ..." banner at the first collective): everything but the JSON line goes to stderr
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     a = parse()
     sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))
