@@ -854,10 +854,20 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
     // pass 0: one CTA per (lane, scale), both reading the lane's frame. The dual form (one CTA per lane filtering both
     // widths from one scan) moves a third less data but is a 64-CTA launch of 140 us on 148 SMs; two single-width CTAs per
     // lane fill the GPU like passes 1 and 2 do.
-    if (part != 2) bp_launch(c, d_img, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
-    if (part != 1) {
-      bp_launch(c, c->bufA, c->bufB, c->bufB, 2 * B, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
-      bp_launch(c, c->bufB, c->bufA, c->bufA, 2 * B, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+    // RBV_TUNE_BOX_SPLIT = G: every pass as G launches over 2B/G planes each. One launch of 2B = 128 blocks owns 128 of the 148 SMs for
+    // its whole duration (544 threads x 96 registers leave no room for a tracker block next to it); with the front end on its own stream
+    // G > 1 leaves SMs to the tracker stream at all times, at the price of a longer front end.
+    int G = c->tune[RBV_TUNE_BOX_SPLIT] > 1 ? c->tune[RBV_TUNE_BOX_SPLIT] : 1;
+    while (G > 1 && (B % G) != 0) --G;
+    const int pl = 2 * B / G;                                  // planes per launch (even: both scales of a lane stay together)
+    for (int g = 0; g < G; ++g) {
+      const size_t po = (size_t)g * pl * N;                    // plane offset in bufA / bufB
+      const float* img_g = d_img + (size_t)g * (pl / 2) * N;   // pass 0 reads one input plane per lane
+      if (part != 2) bp_launch(c, img_g, c->bufA + po, c->bufA + po, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
+      if (part != 1) {
+        bp_launch(c, c->bufA + po, c->bufB + po, c->bufB + po, pl, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
+        bp_launch(c, c->bufB + po, c->bufA + po, c->bufA + po, pl, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+      }
     }
     RBV_CUDA(cudaGetLastError());
     return RBV_OK;
