@@ -581,3 +581,37 @@ def test_front_end_stream_schedule_equals_in_order(lanes, mode, imu):
         last = [pipe.newest_map().keylines(b)[0].tobytes() for b in range(B)]
         assert last == ref[-1][1]                                                    # the newest map after its Kalman update
         pipe.close()
+
+
+def test_device_threshold_servo_equals_host_servo_on_one_stream():
+    """rbv_detect* with threshold = NULL (k_servo: edge_detector.cpp:33-36 on the device from the previous detect's keyline counts)
+    on the context's single stream, read back through rbv_detect_wait's one-stream path: counts, auto thresholds and the servoed
+    thresholds equal the host servo's (rbv_servo_threshold via BatchedPipeline._servo) bit for bit over a sequence."""
+    import ctypes as C
+    from rebvio_b200.pipeline import BatchedPipeline
+    nfr, B = 6, 3
+    spec = synth.config("C5:320x240", n_frames=nfr)
+    seq = synth.generate(spec)
+    u8 = np.stack([np.stack([np.ascontiguousarray(seq.frames[(k + 2 * b) % nfr]) for b in range(B)]) for k in range(nfr)]).astype(np.uint8)
+    cam, det, mapc, core = capi.defaults()
+    cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
+    det.keylines_ref, det.keylines_max = spec.keylines_ref, spec.keylines_max
+    det.gain = 5e-7 * 40                                    # a servo that visibly moves the threshold at this image size
+    ref = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=capi.REDUCE_ORDERED)
+    dev = BatchedPipeline(cam, det, mapc, core, B, reduce_mode=capi.REDUCE_ORDERED)
+    moved = False
+    for k in range(nfr):
+        ref.have_old = False                                # detect only, with outputs
+        o = ref.push(frames=u8[k])
+        m = dev.maps[k % 2]
+        ts = np.zeros(B, np.uint64)
+        capi.check(dev.ctx.L.rbv_detect_u8(dev.ctx.h, m.h, dev._host_ptrs(u8[k]), 0, capi.ptr(ts), None, None, None))
+        n = np.zeros(B, np.int32); at = np.zeros(B, np.float32); th = np.zeros(B, np.float32)
+        capi.check(dev.ctx.L.rbv_detect_wait(dev.ctx.h, m.h, capi.ptr(n), capi.ptr(at), capi.ptr(th)))
+        assert np.array_equal(n, o["keylines"]), k
+        assert np.array_equal(H.bits(at), H.bits(o["auto_threshold"])), k
+        assert np.array_equal(H.bits(th), H.bits(ref.threshold)), (k, th, ref.threshold)
+        moved = moved or bool(np.any(th != np.float32(det.threshold)))
+        assert m.keylines(1)[0].tobytes() == ref.maps[ref.cur ^ 1].keylines(1)[0].tobytes()
+    assert moved
+    ref.close(); dev.close()
