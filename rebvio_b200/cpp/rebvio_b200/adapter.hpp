@@ -67,7 +67,12 @@ class Device {
   rbv_ctx* ctx() const { return ctx_; }
   int keylines_max() const { return kmax_; }
   // the two worker loops of Rebvio get a CUDA stream each (RBV_TUNE_FE_STREAM): detect of frame n+1 runs next to the tracker of n-1, n
-  void useFrontEndStream(bool on = true) { check(rbv_set_tuning(ctx_, RBV_TUNE_FE_STREAM, on ? 1 : 0), "rbv_set_tuning"); }
+  // field_in_front_end: the distance field of a map is built behind its detect on that stream as well (RBV_TUNE_FIELD_IN_FE; pays with
+  // many lanes, where the tracker is the longer chain - with one lane the two loops are balanced without it)
+  void useFrontEndStream(bool on = true, bool field_in_front_end = false) {
+    check(rbv_set_tuning(ctx_, RBV_TUNE_FE_STREAM, on ? 1 : 0), "rbv_set_tuning");
+    check(rbv_set_tuning(ctx_, RBV_TUNE_FIELD_IN_FE, (on && field_in_front_end) ? 1 : 0), "rbv_set_tuning");
+  }
   // Camera::undistort on the device (camera.hpp:54-58): K_ = [fm 0 cx; 0 fm cy; 0 0 1], D_ = (k1, k2, p1, p2, k3); raw frames from then on
   void setUndistort(float fm, float cx, float cy, float k1, float k2, float p1, float p2, float k3) {
     const float K4[4] = {fm, fm, cx, cy}, D5[5] = {k1, k2, p1, p2, k3};

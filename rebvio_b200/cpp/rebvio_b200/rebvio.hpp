@@ -14,7 +14,7 @@
 // Differences from the reference, on purpose:
 //  * the reference pushes the new edge map to the estimation queue BEFORE integrating its IMU samples (rebvio.cpp:72-80), so
 //    the estimation thread can read a half-integrated record; here the map is handed over after the integration.
-//  * edge maps come from a small pool (3 device slabs by default) instead of one allocation per frame; a map handed to an
+//  * edge maps come from a small pool (4 device slabs by default) instead of one allocation per frame; a map handed to an
 //    edge-image callback is valid until the estimation thread has used it as the OLD map of the next pair.
 //  * all filter state lives in the device context (no function-local statics, core.cpp:292-298,340-343), so any number of
 //    Rebvio objects can share a process.
@@ -179,7 +179,7 @@ struct RebvioConfig {                 // rebvio::RebvioConfig (rebvio.hpp:29-33)
   bool undistort = false;             // Camera::undistort on the device (rbv_set_undistort) with the coefficients below
   float distortion[5] = {-0.28340811f, 0.07395907f, 0.00019359f, 1.76187114e-05f, 0.0f};   // camera.hpp:35 (k1 k2 p1 p2 k3)
   int device = 0;
-  int map_pool = 3;                   // >= 3: old + new on the tracker, one in the detector
+  int map_pool = 4;                   // >= 3: old + new on the tracker, one in the detector; a fourth lets the detector run a frame ahead
   bool two_streams = true;            // the acquisition loop's detect on the front-end stream, next to the estimation loop's tracker call
 };
 

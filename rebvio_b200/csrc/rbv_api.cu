@@ -447,6 +447,8 @@ extern "C" void rbv_map_release(rbv_ctx* c, rbv_map* m) {
     if (c->field_map == m) c->field_map = nullptr;
     rbv_graphs_clear(c, m);
   }
+  if (m->field) cudaFree(m->field);
+  if (m->tgt) cudaFree(m->tgt);
   if (m->ready) cudaEventDestroy(m->ready);
   if (m->used) cudaEventDestroy(m->used);
   if (m->h_fe) cudaFreeHost(m->h_fe);
@@ -598,6 +600,26 @@ static int run_graphed(rbv_ctx* c, int kind, const void* a, const void* b, int f
   return RBV_OK;
 }
 
+// ---- distance field in the front end (RBV_TUNE_FIELD_IN_FE) --------------------------------------------------------------------
+// DistanceField::build (core.hpp:37-59) reads only what the detector wrote (pos, gradient, gradient_norm, the auto threshold): none of
+// it changes before the tracker's first half uses the field, so the build can follow the detect on the front-end stream instead of
+// heading the tracker chain - the longest tracker kernel leaves the critical path. The field then belongs to the map (the front end
+// may be frames ahead of the tracker); the tracker's kernels are pointed at it for the duration of the enqueue.
+static int map_field_alloc(rbv_ctx* c, rbv_map* m) {
+  if (m->field && m->tgt) return RBV_OK;
+  const size_t B = c->P.lanes, K = c->P.kmax, N = c->P.npix;
+  if (!m->field) { RBV_CUDA(cudaMalloc((void**)&m->field, sizeof(unsigned) * B * N)); RBV_CUDA(cudaMemset(m->field, 0xFF, sizeof(unsigned) * B * N)); }
+  if (!m->tgt) RBV_CUDA(cudaMalloc((void**)&m->tgt, sizeof(float4) * 2 * B * K));
+  return RBV_OK;
+}
+struct FieldScope {   // point the context's field / target slots at a map's own buffers
+  rbv_ctx* c;
+  unsigned* f0;
+  float4* t0;
+  FieldScope(rbv_ctx* ctx, rbv_map* m, bool on) : c(ctx), f0(ctx->field), t0(ctx->tgt) { if (on) { c->field = m->field; c->tgt = m->tgt; } }
+  ~FieldScope() { c->field = f0; c->tgt = t0; }
+};
+
 // edge_detector.cpp:33-36 on the device, for callers that pass threshold = NULL: config_->threshold of every lane lives in thr_dev,
 // keylines_count_ in last_count (left there by the previous detect). Same float32 statement as rbv_servo_threshold (-fmad=false).
 // With the servo on the device a detect depends on nothing the host has to read back, so the front end can be enqueued frames ahead.
@@ -641,6 +663,16 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
     return fe_detect(c, map);
   }));
   map->fe_valid = 0;
+  map->field_built = 0;
+  if (on_fe && c->tune[RBV_TUNE_FIELD_IN_FE] == 1) {
+    TRY(map_field_alloc(c, map));
+    rbv_map* fm0 = c->field_map;
+    int rc;
+    { FieldScope fs(c, map, true); rc = tr_build_field(c, map); }
+    c->field_map = fm0;   // host-side notion of the tracker's current field map: unchanged by a front end running ahead
+    TRY(rc);
+    map->field_built = 1;
+  }
   RBV_CUDA(cudaMemcpyAsync(c->last_count, map->count, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));   // keylines_count_ for k_servo
   if (on_fe) {   // counts, auto thresholds and the thresholds used leave on the front-end stream (rbv_detect_wait), the map's event follows them
     RBV_CUDA(cudaMemcpyAsync(map->h_fe, map->count, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
@@ -852,11 +884,20 @@ extern "C" int rbv_detect_u8(rbv_ctx* c, rbv_map* map, const uint8_t* const* ima
 // keyline counts and auto thresholds of the most recent detect into `map` (both optional, length B). After a detect on the
 // front-end stream this waits for that detect alone (the tracker stream keeps running); otherwise it reads the map.
 extern "C" int rbv_detect_wait(rbv_ctx* c, rbv_map* map, int* n_keylines, float* auto_threshold, float* threshold_used) {
-  CHECK_CTX(c);
+  if (!c) { rbv_set_error("null context"); return RBV_ERR_ARG; }
+  std::unique_lock<std::recursive_mutex> ctx_lock_(*static_cast<std::recursive_mutex*>(c->mtx));   // outermost entry, see rbv_track_imu
+  RBV_CUDA(cudaSetDevice(c->device));
   if (!map) return RBV_ERR_ARG;
   const size_t B = c->P.lanes;
   if (map->fe_valid) {
-    RBV_CUDA(cudaEventSynchronize(map->ready));
+    {   // the wait itself needs nothing of the context: the estimation thread may enqueue its tracker call meanwhile
+      cudaEvent_t ev = map->ready;
+      ctx_lock_.unlock();
+      const cudaError_t se = cudaEventSynchronize(ev);
+      ctx_lock_.lock();
+      cudaSetDevice(c->device);
+      RBV_CUDA(se);
+    }
     if (n_keylines) memcpy(n_keylines, map->h_fe, sizeof(int) * B);
     if (auto_threshold) memcpy(auto_threshold, map->h_fe + B, sizeof(float) * B);
     if (threshold_used) memcpy(threshold_used, map->h_fe + 2 * B, sizeof(float) * B);
@@ -1081,7 +1122,10 @@ static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
   MAP_READY(c, old_map);
   MAP_READY(c, new_map);
   MapUse map_use_(c, old_map, new_map);
-  return run_graphed(c, GK_TRACK1, old_map, new_map, 0, [&]() -> int {
+  const bool pre = new_map->field_built != 0;   // the field was built behind the map's detect: the kernels below read the map's own field
+  FieldScope fs(c, new_map, pre);
+  if (pre) c->field_map = new_map;              // what tr_build_field would have left (the stages below check it)
+  return run_graphed(c, GK_TRACK1, old_map, new_map, pre ? 1 : 0, [&]() -> int {
     SeqFused fused(c, 0);
     // two independent branches: the distance field of the NEW map (the longest kernel of the half, instruction bound at ~45 %
     // occupancy) and rotation + sigma_rho quantile + LM seed of the OLD map; they meet in front of the first tryVel
@@ -1096,7 +1140,7 @@ static int enqueue_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map) {
       TRY(rc);
     }
     RBV_CUDA(cudaEventRecord(c->ev_join, c->side_stream));
-    TRY(tr_build_field(c, new_map));
+    if (!pre) TRY(tr_build_field(c, new_map));
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     TRY(enqueue_minimize(c, old_map, 2));
     TRY(tr_forward_match(c, old_map, new_map));
@@ -1480,7 +1524,7 @@ extern "C" int rbv_map_upload(rbv_ctx* c, rbv_map* m, int lane, const rbv_keylin
     RBV_CUDA(copy_sync(c, m->mask + L * N, mask.data(), sizeof(int) * N, cudaMemcpyHostToDevice));
     if (n) RBV_CUDA(push(c, px, m->k.pixel, L, K, n));
   }
-  if (c->field_map == m) TRY(tr_pack_targets(c, m));   // tryVel reads a packed copy of the field map's keylines
+  if (c->field_map == m) { FieldScope fs(c, m, m->field_built != 0); TRY(tr_pack_targets(c, m)); }   // tryVel reads a packed copy of the field map's keylines
   return RBV_OK;
 }
 

@@ -52,6 +52,9 @@ struct rbv_map {
   size_t slab_bytes;
   cudaEvent_t ready; // recorded behind a detect on the front-end stream; tracker entries wait for it (fe_pending)
   int fe_pending, fe_valid;
+  unsigned* field;   // [B][N] this map's own distance field and [B][kmax][2] packed targets, built behind its detect on the front-end
+  float4* tgt;       // stream (RBV_TUNE_FIELD_IN_FE); nullptr until first needed. field_built: valid for the keylines now in the map
+  int field_built;
   cudaEvent_t used;  // recorded on the tracker stream behind every tracker / mirror entry that was given this map; a detect INTO the map waits for it
   int used_valid;
   int* h_fe;         // pinned [B] keyline counts + [B] auto thresholds of that detect (rbv_detect_wait)

@@ -84,6 +84,7 @@ class BatchedPipeline:
         self.n_detected = 0
         if self.overlap:
             self.ctx.set_tuning(capi.TUNE_FE_STREAM, 1)
+            self.ctx.set_tuning(capi.TUNE_FIELD_IN_FE, 1)   # the new map's distance field follows its detect on the front-end stream
         self.cur = 0            # index of the map the next detect writes
         self.have_old = False
         self.threshold = np.full(lanes, np.float32(det.threshold), np.float32)   # config_->threshold per lane

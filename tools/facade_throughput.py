@@ -8,5 +8,5 @@ spec = synth.config("C2", n_frames=120); seq = synth.generate(spec)
 replay.write_sequence("/tmp/c2.rbvseq", seq.frames, seq.ts_us, seq.imu_ts_us, seq.gyro, seq.acc, spec.cam, spec.keylines_ref, spec.keylines_max)
 exe="/tmp/rebvio_replay_gpu"
 r=subprocess.run(["g++","-std=c++14","-O2","-ffp-contract=off","-Iinclude","-Irebvio_b200/cpp","rebvio_b200/cpp/rebvio_replay.cpp","-o",exe,"-Lrebvio_b200","-lrebvio_b200","-Wl,-rpath,"+os.path.join(os.getcwd(),"rebvio_b200"),"-lpthread"],capture_output=True,text=True); print(r.stderr)
-for extra in ([],["--no-wait"],["--no-wait"]):
+for extra in ([], ["--no-wait"], ["--no-wait"], ["--no-wait"], ["--no-wait"]):
     r=subprocess.run([exe,"/tmp/c2.rbvseq","/tmp/odo.txt"]+extra,capture_output=True,text=True); print(extra, r.stderr.strip())
