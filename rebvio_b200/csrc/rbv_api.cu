@@ -318,7 +318,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_tracker, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < RBV_RAW_SLOTS; ++i) {
     RBV_CUDA(cudaMalloc(&c->raw[i], sizeof(float) * B * N));
     RBV_CUDA(cudaEventCreateWithFlags(&c->raw_ready[i], cudaEventDisableTiming));
     RBV_CUDA(cudaEventCreateWithFlags(&c->raw_free[i], cudaEventDisableTiming));
@@ -355,7 +355,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->undist_map) cudaFree(c->undist_map);
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < RBV_RAW_SLOTS; ++i) {
     cudaFree(c->raw[i]);
     if (c->raw_ready[i]) cudaEventDestroy(c->raw_ready[i]);
     if (c->raw_free[i]) cudaEventDestroy(c->raw_free[i]);
@@ -818,7 +818,7 @@ extern "C" int rbv_prefetch_frames(rbv_ctx* c, const void* const* images, size_t
   RBV_CUDA(cudaEventRecord(c->raw_ready[slot], c->copy_stream));
   c->raw_key[slot] = images[0];
   c->raw_u8[slot] = is_u8 ? 1 : 0;
-  c->raw_next = 1 - slot;
+  c->raw_next = (slot + 1) % RBV_RAW_SLOTS;
   return RBV_OK;
 }
 
@@ -826,7 +826,7 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
                        const float* threshold, int* n_keylines, float* auto_threshold) {
   if (!images || !images[0]) { rbv_set_error("rbv_detect: null images"); return RBV_ERR_ARG; }
   int slot = -1;
-  for (int i = 0; i < 2; ++i)
+  for (int i = 0; i < RBV_RAW_SLOTS; ++i)
     if (c->raw_key[i] == images[0] && c->raw_u8[i] == (is_u8 ? 1 : 0)) slot = i;
   const float* d_img;
   if (slot >= 0) {                       // staged by rbv_prefetch_frames: wait for the copy stream, no second copy
@@ -834,13 +834,13 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
     c->raw_key[slot] = nullptr;
   } else if (is_u8) {                    // upload now, in stream order
     slot = c->raw_next;
-    c->raw_next = 1 - slot;
+    c->raw_next = (slot + 1) % RBV_RAW_SLOTS;
     c->raw_key[slot] = nullptr;
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));   // a stale prefetch into this slot must have landed first
     TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 1, c->stream));
   } else if (c->undist_map) {            // float frames that still need undistorting: stage them, the remap writes c->img
     slot = c->raw_next;
-    c->raw_next = 1 - slot;
+    c->raw_next = (slot + 1) % RBV_RAW_SLOTS;
     c->raw_key[slot] = nullptr;
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
     TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 4, c->stream));

@@ -90,6 +90,9 @@ struct DevParams {  // constant per context
   float pinv[75];
 };
 
+// staging slots for uploaded frames: the one the front end reads, the one being uploaded, and one more because the front end may lag
+// a frame behind the host when it runs ahead of the tracker (RBV_TUNE_FE_STREAM)
+#define RBV_RAW_SLOTS 3
 struct rbv_ctx {
   DevParams P;
   rbv_camera cam;
@@ -145,11 +148,11 @@ struct rbv_ctx {
   cudaEvent_t ev_tracker;
   cudaStream_t side_stream;   // second branch of rbv_track_g1: rotate + quantile of the old map next to the field build of the new one
   cudaEvent_t ev_fork, ev_join;
-  void* raw[2];               // [B][N] bytes (u8) or floats (f32) as uploaded
-  cudaEvent_t raw_ready[2];   // upload of slot i finished (recorded on copy_stream)
-  cudaEvent_t raw_free[2];    // the front end has consumed slot i (recorded on stream)
-  const void* raw_key[2];     // images[0] of the prefetch that filled slot i (nullptr = empty)
-  int raw_u8[2];
+  void* raw[RBV_RAW_SLOTS];               // [B][N] bytes (u8) or floats (f32) as uploaded
+  cudaEvent_t raw_ready[RBV_RAW_SLOTS];   // upload of slot i finished (recorded on copy_stream)
+  cudaEvent_t raw_free[RBV_RAW_SLOTS];    // the front end has consumed slot i (recorded on stream)
+  const void* raw_key[RBV_RAW_SLOTS];     // images[0] of the prefetch that filled slot i (nullptr = empty)
+  int raw_u8[RBV_RAW_SLOTS];
   int raw_next;
   uint2* undist_map;          // [N] fixed-point remap of cv::undistort (rbv_set_undistort), nullptr = frames arrive undistorted
   unsigned long long launches;  // kernels launched since creation
