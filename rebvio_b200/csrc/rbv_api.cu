@@ -357,6 +357,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   if (c->undist_map) cudaFree(c->undist_map);
   for (int i = 0; i < RBV_RAW_SLOTS; ++i) {
     cudaFree(c->raw[i]);
+    if (c->rawf[i]) cudaFree(c->rawf[i]);
     if (c->raw_ready[i]) cudaEventDestroy(c->raw_ready[i]);
     if (c->raw_free[i]) cudaEventDestroy(c->raw_free[i]);
   }
@@ -815,6 +816,18 @@ extern "C" int rbv_prefetch_frames(rbv_ctx* c, const void* const* images, size_t
   const int slot = c->raw_next;
   RBV_CUDA(cudaStreamWaitEvent(c->copy_stream, c->raw_free[slot], 0));   // the front end is done with what was in this slot
   TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, is_u8 ? 1 : 4, c->copy_stream));
+  c->raw_conv[slot] = 0;
+  if (is_u8 && !c->undist_map) {   // convertTo(CV_32FC1, 3.0) (rebvio.cpp:43) behind the upload, on the copy stream: one kernel less on the front-end chain
+    const size_t n = (size_t)c->P.lanes * c->P.npix;
+    if (!c->rawf[slot]) RBV_CUDA(cudaMalloc((void**)&c->rawf[slot], sizeof(float) * n));
+    cudaStream_t s0 = c->stream;
+    c->stream = c->copy_stream;
+    RBV_LAUNCH(c, k_u8_to_f32, (148 * 8), (256), 0, (const uint4*)c->raw[slot], (float4*)c->rawf[slot], (const unsigned char*)c->raw[slot],
+               c->rawf[slot], n / 16, n);
+    c->stream = s0;
+    RBV_CUDA(cudaGetLastError());
+    c->raw_conv[slot] = 1;
+  }
   RBV_CUDA(cudaEventRecord(c->raw_ready[slot], c->copy_stream));
   c->raw_key[slot] = images[0];
   c->raw_u8[slot] = is_u8 ? 1 : 0;
@@ -829,6 +842,7 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
   for (int i = 0; i < RBV_RAW_SLOTS; ++i)
     if (c->raw_key[i] == images[0] && c->raw_u8[i] == (is_u8 ? 1 : 0)) slot = i;
   const float* d_img;
+  const bool converted = slot >= 0 && is_u8 && c->raw_conv[slot] && !c->undist_map;   // prefetched and already float32 x 3
   if (slot >= 0) {                       // staged by rbv_prefetch_frames: wait for the copy stream, no second copy
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
     c->raw_key[slot] = nullptr;
@@ -853,6 +867,8 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
                c->P.rows, c->P.cols);
     RBV_CUDA(cudaGetLastError());
     d_img = c->img;
+  } else if (converted) {
+    d_img = c->rawf[slot];
   } else if (is_u8) {
     const size_t n = (size_t)c->P.lanes * c->P.npix;
     RBV_LAUNCH(c, k_u8_to_f32, (148 * 8), (256), 0, (const uint4*)c->raw[slot], (float4*)c->img, (const unsigned char*)c->raw[slot], c->img,

@@ -153,6 +153,8 @@ struct rbv_ctx {
   cudaEvent_t raw_free[RBV_RAW_SLOTS];    // the front end has consumed slot i (recorded on stream)
   const void* raw_key[RBV_RAW_SLOTS];     // images[0] of the prefetch that filled slot i (nullptr = empty)
   int raw_u8[RBV_RAW_SLOTS];
+  float* rawf[RBV_RAW_SLOTS];  // [B][N] float32 x 3 of a prefetched u8 slot, converted on the copy stream (off the front-end chain); lazily allocated
+  int raw_conv[RBV_RAW_SLOTS]; // rawf[i] holds the converted frames of slot i
   int raw_next;
   uint2* undist_map;          // [N] fixed-point remap of cv::undistort (rbv_set_undistort), nullptr = frames arrive undistorted
   unsigned long long launches;  // kernels launched since creation
