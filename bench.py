@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--lanes", type=int, default=LANES_PER_GPU)
     ap.add_argument("--config", default="C2", help="sequence shape of every lane (C2 = 752x480 EuRoC-shaped)")
-    ap.add_argument("--reduce", default="fast", choices=["fast", "ordered"])
+    ap.add_argument("--reduce", default="ordered", choices=["fast", "ordered"])
     ap.add_argument("--no-single", action="store_true", help="skip the single-stream latency leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")

@@ -55,7 +55,7 @@ class Device {
  public:
   using SharedPtr = std::shared_ptr<Device>;
   Device(const Camera& cam, const rbv_detector_cfg& det, const rbv_map_cfg& map, const rbv_core_cfg& core, int device = 0,
-         int reduce_mode = RBV_REDUCE_FAST) {
+         int reduce_mode = RBV_REDUCE_ORDERED) {
     rbv_camera c{cam.fm_, cam.cx_, cam.cy_, cam.rows_, cam.cols_};
     check(rbv_create(&c, &det, &map, &core, device, 1, &ctx_), "rbv_create");
     check(rbv_set_reduce_mode(ctx_, reduce_mode), "rbv_set_reduce_mode");

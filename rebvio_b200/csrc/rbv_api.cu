@@ -218,7 +218,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   c->mtx = new std::recursive_mutex();
   c->cam = *cam; c->det = *det; c->mapc = *map; c->core = *core;
   c->device = device;
-  c->reduce_mode = RBV_REDUCE_FAST;
+  c->reduce_mode = RBV_REDUCE_ORDERED;
   c->prof_mode = -1;
   float st[2];
   kovesi_widths(3.56359f, 3, c->widths[0], &st[0]);                       // scale_space.cpp:186
@@ -271,7 +271,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   }
   RBV_CUDA(dalloc(&c->field, B * N));
   RBV_CUDA(dalloc(&c->tgt, 2 * B * K));
-  RBV_CUDA(dalloc(&c->prod, 10 * B * K));
+  RBV_CUDA(dalloc(&c->prod, 10 * B * K + 256));
   RBV_CUDA(dalloc(&c->fiabs, B * K));
   RBV_CUDA(dalloc(&c->fwd_head, B * K));
   RBV_CUDA(dalloc(&c->fwd_next, B * K));
@@ -285,6 +285,8 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   c->nblk = (P.kmax + 255) / 256;
   RBV_CUDA(dalloc(&c->partials, B * c->nblk * 27));
   RBV_CUDA(dalloc(&c->ticket, B));
+  RBV_CUDA(dalloc(&c->ord_flags, 2 * B * c->nblk));
+  RBV_CUDA(cudaMemset(c->ord_flags, 0, sizeof(unsigned) * 2 * B * c->nblk));
   RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
   RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
@@ -334,7 +336,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaStreamSynchronize(c->stream);
   void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->last_count, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
-                 c->partials, c->ticket, c->blkagg, c->tgt};
+                 c->partials, c->ticket, c->blkagg, c->tgt, c->ord_flags};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {
@@ -1000,7 +1002,7 @@ __global__ void k_lm_init(LMState* lm, const float* lane_in, int lanes) {
 static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map, int part = 0) {
   // FAST mode with several keylines per thread: the quantile kernel also seeds the LM state, and call 0 of tryVel takes the
   // residuals as zero and writes every entry, so neither k_lm_init nor the residual fill is launched
-  const bool lean = c->reduce_mode == RBV_REDUCE_FAST && c->tune[RBV_TUNE_TRYVEL] != 1;
+  const bool lean = !tr_ordered_legacy(c) && (c->reduce_mode == RBV_REDUCE_ORDERED || c->tune[RBV_TUNE_TRYVEL] != 1);
   if (part != 2) {
     TRY(tr_quantile(c, old_map, c->P.quantile_cutoff, c->P.quantile_num_bins, lean ? 2 : 1));
     if (!lean) {

@@ -119,7 +119,8 @@ struct rbv_ctx {
   unsigned* field;  // [B][N]
   float4* tgt;      // [B][kmax][2] packed target keylines of the distance-field map (k_pack_targets)
   rbv_map* field_map;
-  float* prod;      // [10][B][kmax] tryVel per-keyline addends / [7][B][kmax] extRotVel rows (shared)
+  float* prod;      // [10][B][kmax] (+ a chunk of slack) ORDERED mode: tryVel factor rows (jx, jy, jz, f) / the 7 extRotVel rows per keyline
+  unsigned* ord_flags;  // [2][B][nblk] "block's rows are written" flags of the ORDERED chain warps (tryVel | extRotVel), cleared by the consumer
   float* fiabs;     // [B][kmax]
   int* fwd_head;    // [B][kmax]
   int* fwd_next;    // [B][kmax]
@@ -192,7 +193,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
-  X(k_imu_pre) X(k_imu_fuse) X(k_servo)
+  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
@@ -233,6 +234,7 @@ int tr_build_field(rbv_ctx* c, rbv_map* map);
 int tr_pack_targets(rbv_ctx* c, rbv_map* map);   // refresh the packed copy after the field map's keylines were replaced
 int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);
+int tr_ordered_legacy(const rbv_ctx* c);
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call);     // lm_call: -1 = single evaluation (vel, srmin in lane_in), t >= 0 = LM call t
 int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map);
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm);

@@ -249,10 +249,11 @@ int tr_pack_targets(rbv_ctx* c, rbv_map* map) {
   return RBV_OK;
 }
 
+int tr_init_ordered(void);
 int tr_init(rbv_ctx* c) {
   (void)c;   // the current device is the context's
   RBV_CUDA(cudaFuncSetAttribute(k_field_band, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  return RBV_OK;
+  return tr_init_ordered();
 }
 
 int tr_build_field(rbv_ctx* c, rbv_map* map) {
@@ -781,23 +782,27 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
   }
 }
 
-template <int KPT>
-__device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
+// ORD = RBV_REDUCE_ORDERED: instead of FP64 partial sums the block leaves (jx, jy, jz, f) of every keyline in four planes
+// (`rows`, zeros for skipped keylines: x + 0 == x exactly) and raises its flag; the lane's chain warp (ordered_chain, below)
+// forms the ten products and adds them in keyline order.
+template <int KPT, bool ORD>
+__device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
                                                          const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
                                                          int vel_stride, const float* __restrict__ sr_ptr, int sr_stride,
                                                          double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                          const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
-                                                         LMState* lm, float* lane_out, int lm_call, const DevParams& P) {
+                                                         LMState* lm, float* lane_out, int lm_call, const DevParams& P,
+                                                         float* __restrict__ rows, unsigned* __restrict__ flags) {
   __shared__ double sm[(TV_TPB / 32) * 10];
   __shared__ double result[10];
   __shared__ float warp_val[TV_TPB / 32];
   __shared__ int warp_has[TV_TPB / 32];
   __shared__ int s_last;
   constexpr int KPB = TV_TPB * KPT;
-  const int b = blockIdx.y, n = count_o[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int n = count_o[b], t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int nact = max(1, (n + KPB - 1) / KPB);
-  if ((int)blockIdx.x >= nact) return;
-  const int idx0 = (blockIdx.x * TV_TPB + t) * KPT;
+  if (blk >= nact) return;
+  const int idx0 = (blk * TV_TPB + t) * KPT;
   const size_t base = (size_t)b * P.kmax, o = base + idx0;
   const int nvalid = min(KPT, n - idx0);          // <= 0: nothing of this thread is a keyline
   double acc[10];
@@ -822,7 +827,7 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
     unsigned cell[KPT];
 #pragma unroll
     for (int k = 0; k < KPT; ++k) {
-      if (res[k] < 0.0f) res[k] = residual_lookback(agg_prev + (size_t)b * nblk, blockIdx.x);
+      if (res[k] < 0.0f) res[k] = residual_lookback(agg_prev + (size_t)b * nblk, blk);
       skip[k] = (k >= nvalid) || (thr > 0.0f && gn[k] < thr) || (srho[k] > srmin) || (mt[k] < P.min_matches);   // core.cpp:88,91
       w[k] = 1.0f;
       if (res[k] > P.reweight_distance) w[k] = P.reweight_distance / res[k];           // :94
@@ -852,14 +857,17 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
       else { t0[k] = make_float4(0.f, 0.f, 0.f, 0.f); t1[k] = t0[k]; }
     }
     int fwd[KPT];
+    float ojx[KPT], ojy[KPT], ojz[KPT], of[KPT];   // ORD: what the chain warp multiplies
 #pragma unroll
     for (int k = 0; k < KPT; ++k) {
       fwd[k] = -1;
+      ojx[k] = ojy[k] = ojz[k] = of[k] = 0.0f;
       if (skip[k]) continue;
       float add[10];
       if (penalty[k]) {
         const float f = (float)((1.0 / (double)srho[k]) * (double)P.search_range * (double)w[k]);   // :99 / :115
-        acc[0] += (double)(f * f);
+        if constexpr (ORD) of[k] = f;
+        else acc[0] += (double)(f * f);
         continue;
       }
       float dfx = 0.0f, dfy = 0.0f, f;
@@ -880,17 +888,26 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
       }
       if (!matched) { f = P.search_range / srho[k]; code[k] = -1.0f; }                 // :52 / :59
       f *= w[k];
-      add[0] = f * f;
       const float jx = rho_p[k] * P.fm * dfx * w[k];                                   // :126-128
       const float jy = rho_p[k] * P.fm * dfy * w[k];
       const float jz = -rho_p[k] * (px[k] * dfx + py[k] * dfy) * w[k];
-      add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
-      add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
-      add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
+      if constexpr (ORD) {
+        ojx[k] = jx; ojy[k] = jy; ojz[k] = jz; of[k] = f;
+      } else {
+        add[0] = f * f;
+        add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
+        add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
+        add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
 #pragma unroll
-      for (int a = 0; a < 10; ++a) acc[a] += (double)add[a];
+        for (int a = 0; a < 10; ++a) acc[a] += (double)add[a];
+      }
     }
     tv_st<KPT, int>(Ko.match_fwd + o, fwd, nvalid);                                    // core.cpp:87
+    if constexpr (ORD) {
+      const size_t ps = (size_t)P.lanes * P.kmax;
+      tv_st<KPT, float>(rows + o, ojx, nvalid); tv_st<KPT, float>(rows + ps + o, ojy, nvalid);
+      tv_st<KPT, float>(rows + 2 * ps + o, ojz, nvalid); tv_st<KPT, float>(rows + 3 * ps + o, of, nvalid);
+    }
   }
   // carried |fi| in keyline order: thread aggregate = its last matched keyline, inclusive scan over the threads of the warp
   int has = 0; float val = 0.0f;
@@ -906,12 +923,14 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
   int ehas = __shfl_up_sync(0xFFFFFFFFu, has, 1);                                      // exclusive: what enters this thread
   float eval = __shfl_up_sync(0xFFFFFFFFu, val, 1);
   if (lane == 0) { ehas = 0; eval = 0.0f; }
+  if constexpr (!ORD) {
 #pragma unroll
-  for (int a = 0; a < 10; ++a) {
-    double v = acc[a];
+    for (int a = 0; a < 10; ++a) {
+      double v = acc[a];
 #pragma unroll
-    for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
-    if (lane == 0) sm[warp * 10 + a] = v;
+      for (int off = 16; off; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+      if (lane == 0) sm[warp * 10 + a] = v;
+    }
   }
   __syncthreads();
   if (!ehas || !has) {
@@ -928,16 +947,22 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
     for (int k = 0; k < KPT; ++k) {
       if (code[k] >= 0.0f) { ehas = 1; eval = code[k]; }
       // core.cpp:141 (-1 = look back next time); no write this call = keep the (resolved) value that was read
-      out[k] = code[k] >= -1.5f ? (ehas ? eval : (blockIdx.x == 0 ? 0.0f : -1.0f)) : res[k];
+      out[k] = code[k] >= -1.5f ? (ehas ? eval : (blk == 0 ? 0.0f : -1.0f)) : res[k];
     }
     tv_st<KPT, float>(Ko.residual + o, out, nvalid);
   }
-  if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blockIdx.x] = has ? val : -1.0f;
+  if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blk] = has ? val : -1.0f;
+  if constexpr (ORD) {   // release the block's rows to the lane's chain warp
+    __threadfence();
+    __syncthreads();
+    if (t == 0 && n > 0) { __threadfence(); *reinterpret_cast<volatile unsigned*>(flags + (size_t)b * nblk + blk) = 1u; }
+    return;
+  }
   if (t < 10) {
     double s2 = 0.0;
 #pragma unroll
     for (int w2 = 0; w2 < TV_TPB / 32; ++w2) s2 += sm[w2 * 10 + t];
-    partials[((size_t)b * nblk + blockIdx.x) * 10 + t] = s2;
+    partials[((size_t)b * nblk + blk) * 10 + t] = s2;
   }
   __threadfence();
   __syncthreads();
@@ -974,8 +999,139 @@ __device__ __forceinline__ void tryvel_fastn_body(KeylineSoA Ko, const int* __re
                       int sr_stride, double* __restrict__ partials, unsigned* __restrict__ ticket, const float* __restrict__ agg_prev,            \
                       float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const __grid_constant__ DevParams P
 #define RBV_TV_PASS Ko, count_o, thr_o, tgt, field, vel_ptr, vel_stride, sr_ptr, sr_stride, partials, ticket, agg_prev, agg_cur, nblk, lm, lane_out, lm_call, P
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2>(RBV_TV_PASS); }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4>(RBV_TV_PASS); }
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr, nullptr); }
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr, nullptr); }
+
+// ---- RBV_REDUCE_ORDERED: the reference's float32 sums, in keyline order, next to the evaluation -------------------------------
+// The reference adds its ten tryVel accumulators (and the 27 of extRotVel) sequentially in float32 over the keylines
+// (core.cpp:130-139,244-245); match indices downstream depend on those bits. A sequential float32 sum cannot be re-associated,
+// so the chain itself stays serial: ONE warp per lane, thread a = accumulator a, 4 cycles per dependent FADD (~2 ns per keyline).
+// What can be done is to take everything else off that chain and to run it NEXT TO the evaluation instead of behind it:
+//   * producers (the evaluation blocks, all lanes' block 0 first, then all block 1, ...) leave per-keyline factor rows in
+//     global memory (L2) and raise one flag per block (fence + flag store);
+//   * the chain warp of a lane (reducer CTAs are the first CTAs of the same launch; each hosts several lanes' warps) waits for
+//     the flags in block order, stages 128-keyline chunks of the rows into a 4-deep shared-memory ring with cp.async.cg, forms
+//     the products (one FMUL, off the chain) and adds them in order; all 32 lanes fetch, accumulator threads add.
+// Producers never wait for anything, so the launch cannot deadlock whatever the CTA scheduling order; the flags are cleared
+// by the chain warp as it consumes them. The chain (13 k keylines ~ 27 us) hides behind the evaluation of the other lanes.
+#define ORD_CH 128
+#define ORD_RS (ORD_CH + 4)   // shared-memory row stride in floats: row r starts at bank 4 r, so LDS.128 of different rows never collide
+#define ORD_NST 4
+#define TV_RW (TV_TPB / 32)   // lanes (chain warps) per reducer CTA of tryVel
+#define ER_RW 4               // ... of extRotVel (7 rows per chunk instead of 4)
+__device__ __forceinline__ unsigned ord_ld_acquire(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+template <int NROWS>
+__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, int kpb,
+                                               unsigned* flags_lane, int pa, int pb, float* ring) {
+  const int lane = threadIdx.x & 31;
+  const int nch = (n + ORD_CH - 1) / ORD_CH;
+  int issued = 0, nflag = 0;
+  float s = 0.0f;
+  for (int c = 0; c < nch; ++c) {
+    // keep up to ORD_NST chunks in flight, as far as the producers' flags allow; block only for the chunk needed now
+    while (issued < nch && issued < c + ORD_NST) {
+      const int need = (min((issued + 1) * ORD_CH, n) - 1) / kpb;   // producer block that holds the chunk's last keyline
+      bool ok = true;
+      while (nflag <= need) {
+        unsigned f = 0u;
+        if (lane == 0) f = ord_ld_acquire(flags_lane + nflag);
+        f = __shfl_sync(0xFFFFFFFFu, f, 0);
+        if (f) { if (lane == 0) flags_lane[nflag] = 0u; ++nflag; }
+        else if (issued > c) { ok = false; break; }
+      }
+      if (!ok) break;
+      __syncwarp();
+      float* st = ring + (size_t)(issued % ORD_NST) * NROWS * ORD_RS + 4 * lane;
+      const float* src = rows + base + (size_t)issued * ORD_CH + 4 * lane;
+#pragma unroll
+      for (int r = 0; r < NROWS; ++r) ord_cp16(st + r * ORD_RS, src + (size_t)r * ps);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      ++issued;
+    }
+    const int pend = issued - c - 1;   // groups committed behind chunk c's
+    if (pend >= 3) asm volatile("cp.async.wait_group 3;" ::: "memory");
+    else if (pend == 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
+    else if (pend == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    const float* st = ring + (size_t)(c % ORD_NST) * NROWS * ORD_RS;
+    const float4* ra = reinterpret_cast<const float4*>(st + pa * ORD_RS);
+    const float4* rb = reinterpret_cast<const float4*>(st + pb * ORD_RS);
+    const int cnt = min(ORD_CH, n - c * ORD_CH), c4 = cnt >> 2;
+    // two groups of four keylines are fetched ahead of the one being added (LDS latency ~ 7 dependent adds); the row stride leaves one
+    // float4 of slack behind the chunk for the look-ahead of its last groups
+    float4 x0 = ra[0], y0 = rb[0], x1 = ra[1], y1 = rb[1];
+#pragma unroll 4
+    for (int i = 0; i < c4; ++i) {
+      const int in = min(i + 2, ORD_CH / 4);
+      const float4 xn = ra[in], yn = rb[in];
+      const float p0 = x0.x * y0.x, p1 = x0.y * y0.y, p2 = x0.z * y0.z, p3 = x0.w * y0.w;   // float products, off the chain
+      s += p0; s += p1; s += p2; s += p3;                                                  // float adds in keyline order
+      x0 = x1; y0 = y1; x1 = xn; y1 = yn;
+    }
+    for (int i = c4 * 4; i < cnt; ++i) s += st[pa * ORD_RS + i] * st[pb * ORD_RS + i];
+    __syncwarp();   // every lane is done with the slot before a later cp.async refills it
+  }
+  return s;
+}
+
+// tryVel accumulators 0..9 (score | JtJ 00 11 22 01 02 12 | JtF 0 1 2) as products of rows (jx, jy, jz, f) = (0, 1, 2, 3)
+__constant__ signed char c_tv_pa[10] = {3, 0, 1, 2, 0, 0, 1, 0, 1, 2};
+__constant__ signed char c_tv_pb[10] = {3, 0, 1, 2, 1, 2, 2, 3, 3, 3};
+
+template <int KPT>
+__device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,
+                                                  const unsigned* __restrict__ field, const float* __restrict__ vel_ptr, int vel_stride,
+                                                  const float* __restrict__ sr_ptr, int sr_stride, double* __restrict__ partials,
+                                                  unsigned* __restrict__ ticket, const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
+                                                  LMState* lm, float* lane_out, int lm_call, const DevParams& P, float* __restrict__ rows,
+                                                  unsigned* __restrict__ flags, int nred) {
+  extern __shared__ __align__(16) float ord_ring[];
+  if ((int)blockIdx.x < nred) {   // chain warps: lane b = TV_RW * block + warp
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x * TV_RW + warp;
+    if (b >= P.lanes) return;
+    const int n = count_o[b];
+    const int pa = lane < 10 ? c_tv_pa[lane] : 0, pb = lane < 10 ? c_tv_pb[lane] : 0;
+    const float s = ordered_chain<4>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk, pa, pb,
+                                     ord_ring + (size_t)warp * ORD_NST * 4 * ORD_RS);
+    float r[10];
+#pragma unroll
+    for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
+    if (lane == 0) {
+      float JtJ[9], JtF[3];
+      const float score = r[0];
+      JtJ[0] = r[1]; JtJ[4] = r[2]; JtJ[8] = r[3];
+      JtJ[1] = JtJ[3] = r[4]; JtJ[2] = JtJ[6] = r[5]; JtJ[5] = JtJ[7] = r[6];
+      JtF[0] = r[7]; JtF[1] = r[8]; JtF[2] = r[9];
+      if (lm_call >= 0) {
+        float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
+        lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
+      }
+      float* outp = lane_out + (size_t)b * OUT_STRIDE;
+      for (int i = 0; i < 9; ++i) outp[OUT_JTJ + i] = JtJ[i];
+      for (int i = 0; i < 3; ++i) outp[OUT_JTF + i] = JtF[i];
+      outp[OUT_SCORE] = score;
+    }
+    return;
+  }
+  const int pbk = blockIdx.x - nred;   // producers: every lane's block 0, then every lane's block 1, ... (the order the chains consume)
+  tryvel_fastn_body<KPT, true>(pbk % P.lanes, pbk / P.lanes, RBV_TV_PASS, rows, flags);
+}
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred) {
+  tryvel_ord_kernel<2>(RBV_TV_PASS, rows, flags, nred);
+}
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred) {
+  tryvel_ord_kernel<4>(RBV_TV_PASS, rows, flags, nred);
+}
 
 __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
                                                              int nblk, int kmax, int kpb) {
@@ -984,6 +1140,10 @@ __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, cons
   const size_t o = (size_t)b * kmax + idx;
   if (Ko.residual[o] < 0.0f) Ko.residual[o] = residual_lookback(agg + (size_t)b * nblk, idx / kpb);
 }
+
+// RBV_REDUCE_ORDERED through the first implementation (k_tryvel_eval + k_tryvel_reduce, k_extrot_rows + k_extrot_reduce: evaluation, then
+// one block per lane adding behind it) instead of the chain warps next to the evaluation; kept as a cross-check (RBV_TUNE_ORDERED = 1)
+int tr_ordered_legacy(const rbv_ctx* c) { return c->reduce_mode == RBV_REDUCE_ORDERED && c->tune[RBV_TUNE_ORDERED] == 1; }
 
 // lm_call = -1: single evaluation at lane_in vel / sigma_rho_min; 0: first LM call at lm.vel; >= 1: at lm.vnew
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
@@ -1000,20 +1160,28 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     sr_ptr = lmf + offsetof(LMState, sigma_rho_min) / sizeof(float);
     sr_stride = lm_floats;
   }
-  if (c->reduce_mode == RBV_REDUCE_ORDERED) {
+  if (tr_ordered_legacy(c)) {
     RBV_LAUNCH(c, k_tryvel_eval, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->prod, c->fiabs, P);
     RBV_LAUNCH(c, k_tryvel_reduce, (P.lanes), (1024), 0, map->k, map->count, c->prod, c->fiabs, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, 1, P);
   } else {
+    const bool ord = c->reduce_mode == RBV_REDUCE_ORDERED;
     const int nblk = c->nblk;
     const size_t half = (size_t)P.lanes * nblk;
     float* agg_cur = c->blkagg + (size_t)c->tv_parity * half;
     const float* agg_prev = c->blkagg + (size_t)(1 - c->tv_parity) * half;
-    // keylines per thread (RBV_TUNE_TRYVEL): 1 = k_tryvel_fast, 2 / 4 = k_tryvel_fast2 / k_tryvel_fast4 (0 = automatic: 4, or 2 with fewer than 8 lanes)
+    // keylines per thread (RBV_TUNE_TRYVEL): 1 = k_tryvel_fast (FAST only), 2 / 4 = k_tryvel_{fast,ord}2 / 4 (0 = automatic: 4, or 2 with fewer than 8 lanes)
     int kpt = c->tune[RBV_TUNE_TRYVEL] ? c->tune[RBV_TUNE_TRYVEL] : (P.lanes >= 8 ? 4 : 2);   // few lanes: more, smaller CTAs
     if (kpt == 3 || kpt > 4) kpt = 4;
+    if (ord && kpt == 1) kpt = 2;
     const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
 #define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P
-    if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
+    if (ord) {   // chain-warp CTAs first, then the evaluation blocks of every lane in block-major order
+      const int nred = (P.lanes + TV_RW - 1) / TV_RW;
+      const size_t smem = sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS;
+      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred); }
+      else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred); }
+    }
+    else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else { RBV_LAUNCH(c, k_tryvel_fast4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
 #undef RBV_TV_ARGS
@@ -1442,13 +1610,66 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
   if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
+// RBV_REDUCE_ORDERED: rows Phi_j (6) and Y_j of every keyline to seven planes (zeros for unmatched keylines), one flag per block;
+// the lane's chain warp adds the 27 products Phi^T Phi / Phi^T Y in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
+__global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
+                                                       float* __restrict__ rows, unsigned* __restrict__ flags, int nblk, int nred, float* lane_out,
+                                                       const __grid_constant__ DevParams P) {
+  extern __shared__ __align__(16) float ord_ring[];
+  __shared__ double s_res[ER_RW][27];
+  __shared__ float s_sys[ER_RW][42];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const size_t ps = (size_t)P.lanes * P.kmax;
+  if ((int)blockIdx.x < nred) {
+    const int b = blockIdx.x * ER_RW + warp;
+    if (warp >= ER_RW || b >= P.lanes) return;
+    const int pa = lane < 27 ? c_pair_a[lane] : 0, pb = lane < 27 ? c_pair_b[lane] : 0;
+    const float s = ordered_chain<7>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk, pa, pb,
+                                     ord_ring + (size_t)warp * ORD_NST * 7 * ORD_RS);
+    if (lane < 27) s_res[warp][lane] = (double)s;
+    __syncwarp();
+    extrot_finish_warp(s_res[warp], lane_out + (size_t)b * OUT_STRIDE, s_sys[warp]);
+    return;
+  }
+  const int pbk = blockIdx.x - nred;
+  const int b = pbk % P.lanes, blk = pbk / P.lanes, n = count[b];
+  if (blk * TV_TPB * ER_KPT >= n) return;
+  const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+  ExtRotIn in[ER_KPT];
+#pragma unroll
+  for (int j = 0; j < ER_KPT; ++j) {                // every load of the thread's ER_KPT keylines first (one round trip)
+    const int idx = (blk * ER_KPT + j) * TV_TPB + t;
+    in[j].mid = -1;
+    if (idx < n) in[j] = extrot_load(K, (size_t)b * P.kmax + idx);
+  }
+#pragma unroll
+  for (int j = 0; j < ER_KPT; ++j) {
+    const int idx = (blk * ER_KPT + j) * TV_TPB + t;
+    if (idx >= n) continue;
+    float r[7];
+    extrot_row_in(in[j], v0, v1, v2, P, r);         // zeros for an unmatched keyline: x + 0 * 0 == x
+    const size_t o = (size_t)b * P.kmax + idx;
+#pragma unroll
+    for (int a = 0; a < 7; ++a) rows[a * ps + o] = r[a];
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) { __threadfence(); *reinterpret_cast<volatile unsigned*>(flags + (size_t)b * nblk + blk) = 1u; }
+}
+
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
   const DevParams& P = c->P;
   const float* vel_ptr = vel_from_lm ? reinterpret_cast<const float*>(c->lm) + offsetof(LMState, vel) / sizeof(float) : c->lane_in + IN_VEL;
   const int vel_stride = vel_from_lm ? (int)(sizeof(LMState) / sizeof(float)) : IN_STRIDE;
-  if (c->reduce_mode == RBV_REDUCE_ORDERED) {
+  if (tr_ordered_legacy(c)) {
     RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
     RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
+  } else if (c->reduce_mode == RBV_REDUCE_ORDERED) {
+    const int nred = (P.lanes + ER_RW - 1) / ER_RW;
+    const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
+    const size_t smem = sizeof(float) * ER_RW * ORD_NST * 7 * ORD_RS;
+    RBV_LAUNCH(c, k_extrot_ord, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod,
+               c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, c->lane_out, P);
   } else {
     RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
@@ -1699,5 +1920,12 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
              c->seq_fused ? c->seq_min_matches : 0, apply ? c->reg_r : nullptr, apply ? c->reg_s : nullptr,
              apply ? (const int*)c->fwd_next : nullptr, P);
   RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
+
+int tr_init_ordered(void) {
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW * ORD_NST * 7 * ORD_RS)));
   return RBV_OK;
 }

@@ -74,7 +74,7 @@ class Map:
 
 
 class Context:
-    def __init__(self, cam=None, det=None, mapc=None, core=None, lanes=1, device=0, reduce_mode=capi.REDUCE_FAST):
+    def __init__(self, cam=None, det=None, mapc=None, core=None, lanes=1, device=0, reduce_mode=capi.REDUCE_ORDERED):
         self.L = capi.load()
         dc, dd, dm, dk = capi.defaults()
         self.cam, self.det, self.mapc, self.core = cam or dc, det or dd, mapc or dm, core or dk

@@ -57,7 +57,7 @@ def visual_fusion(R, Vg, Wx, X):
 
 
 class BatchedPipeline:
-    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_FAST, cuda_stream=None, imu_cfg=None,
+    def __init__(self, cam, det, mapc, core, lanes, device=0, reduce_mode=capi.REDUCE_ORDERED, cuda_stream=None, imu_cfg=None,
                  overlap=False):
         """imu_cfg: None = visual-only fusion (rbv_track); True or a capi.ImuCfg = the reference's IMU filters on the device
         (rbv_track_imu; push then takes `imu_in`, the integrated IMU of every lane, instead of R_rel).

@@ -45,18 +45,27 @@ def test_cuda_vs_reference_golden_teacher_forced(name):
     g.close()
 
 
-@pytest.mark.parametrize("name,nf", [("C5:320x240", 4), ("C1", 3), ("C2", 4), ("C3", 3)])
-def test_cuda_vs_oracle_free_running_ordered(name, nf):
-    """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits."""
+@pytest.mark.parametrize("name,nf,legacy,lanes", [("C5:320x240", 4, 0, 2), ("C1", 3, 0, 2), ("C2", 4, 0, 2), ("C3", 3, 0, 2), ("C2", 3, 1, 2),
+                                                  ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9)])
+def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
+    """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits.
+    legacy = RBV_TUNE_ORDERED 1: the ordered sums by one adding block per lane behind the evaluation (the first implementation)
+    instead of the chain warps next to it (k_tryvel_ord*, k_extrot_ord)."""
     spec, frames, R_rel = common.sequence(name, nf)
     cfg = common.cfgs_from_spec(spec)
     orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
     T = H.run_stages(orc, frames, R_rel)
-    g = _gpu(cfg)
+    g = _gpu(cfg, lanes=lanes, lane=lanes - 1, tune={capi.TUNE_ORDERED: legacy})   # 9 / 21 lanes: several chain-warp CTAs, a partly filled one
     G = H.run_stages(g, frames, R_rel)
     rep = H.report(T, G)
     assert H.dirty(rep) == []
     assert common.x_rel_max(rep) <= common.X_RTOL_FLOOR
+    names = g.ctx.profile_launches()
+    if legacy:
+        assert names.get("k_tryvel_reduce", 0) > 0 and names.get("k_extrot_reduce", 0) > 0 and names.get("k_extrot_ord", 0) == 0
+    else:
+        assert names.get("k_tryvel_ord2", 0) + names.get("k_tryvel_ord4", 0) > 0 and names.get("k_extrot_ord", 0) > 0
+        assert names.get("k_tryvel_reduce", 0) == 0
     g.close(); orc.close()
 
 
@@ -95,15 +104,16 @@ def test_cuda_fast_reduction_teacher_forced(name, nf):
 
 @pytest.mark.parametrize("kpt", [1, 2, 4])
 def test_try_vel_fast_vs_ordered_indices_and_sums(kpt):
-    """kpt = keylines per thread of the FAST-mode tryVel kernel (k_tryvel_fast / k_tryvel_fast2 / k_tryvel_fast4)"""
+    """kpt = keylines per thread of the tryVel kernel (FAST: k_tryvel_fast / k_tryvel_fast2 / k_tryvel_fast4; ORDERED: see below)"""
     spec, frames, R_rel = common.sequence("C2", 3)
     cfg = common.cfgs_from_spec(spec)
-    for mode in ((capi.REDUCE_ORDERED, capi.REDUCE_FAST) if kpt == 1 else (capi.REDUCE_FAST,)):
+    for mode in (capi.REDUCE_ORDERED, capi.REDUCE_FAST):
         orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
         a, b = orc.detect(frames[0]), orc.detect(frames[1])
         orc.build_distance_field(b)
         n = orc.map_size(a)
-        g = _gpu(cfg, mode=mode, tune={capi.TUNE_TRYVEL: kpt})
+        # ORDERED: 2 / 4 keylines per thread = the chain-warp kernels k_tryvel_ord2 / k_tryvel_ord4; 1 = evaluation + adding block per lane
+        g = _gpu(cfg, mode=mode, lanes=3 if kpt == 4 else 2, tune={capi.TUNE_TRYVEL: kpt, capi.TUNE_ORDERED: 1 if kpt == 1 else 0})
         ga, gb = g.detect(frames[0]), g.detect(frames[1])
         g.build_distance_field(gb)
         res = np.zeros(n, np.float32)
@@ -122,6 +132,8 @@ def test_try_vel_fast_vs_ordered_indices_and_sums(kpt):
                 assert H.rel_err(JJg, JJo) <= 1e-5 and H.rel_err(JFg, JFo) <= 1e-5
         if mode == capi.REDUCE_FAST:
             assert g.ctx.profile_launches().get({1: "k_tryvel_fast", 2: "k_tryvel_fast2", 4: "k_tryvel_fast4"}[kpt], 0) > 0
+        else:
+            assert g.ctx.profile_launches().get({1: "k_tryvel_reduce", 2: "k_tryvel_ord2", 4: "k_tryvel_ord4"}[kpt], 0) > 0
         g.close(); orc.close()
 
 
@@ -362,7 +374,7 @@ def test_u8_upload_and_prefetch_match_float_path():
                 assert a.tobytes() == b.tobytes()
 
 
-@pytest.mark.parametrize("lanes,mode", [(1, capi.REDUCE_FAST), (3, capi.REDUCE_ORDERED), (20, capi.REDUCE_FAST)])
+@pytest.mark.parametrize("lanes,mode", [(1, capi.REDUCE_FAST), (3, capi.REDUCE_ORDERED), (20, capi.REDUCE_ORDERED)])
 def test_cuda_graph_replay_equals_stream_launches(lanes, mode):
     """RBV_TUNE_GRAPH: the captured kernel sequences of detect / track_g1 / track_g2 (replayed from frame 3 on, when both
     map pairings have been captured) give bit-identical outputs, keylines and launch counts to plain stream launches.
@@ -527,7 +539,7 @@ def test_detector_and_tracker_threads_share_one_context():
         assert got == serial, trial
 
 
-@pytest.mark.parametrize("lanes,mode,imu", [(1, capi.REDUCE_FAST, False), (3, capi.REDUCE_ORDERED, False), (20, capi.REDUCE_FAST, True)])
+@pytest.mark.parametrize("lanes,mode,imu", [(1, capi.REDUCE_FAST, False), (3, capi.REDUCE_ORDERED, False), (20, capi.REDUCE_ORDERED, True)])
 def test_front_end_stream_schedule_equals_in_order(lanes, mode, imu):
     """SURVEY 8(b) threading: detect of frame n+1 on the front-end stream next to the tracker of (n-1, n) on the tracker stream
     (RBV_TUNE_FE_STREAM, BatchedPipeline(overlap=True): the reference's two-thread schedule) gives bit-identical keylines,
