@@ -36,8 +36,9 @@ extern "C" {
 #define RBV_ERR_STATE 3    /* call order violated (e.g. tracker stage before a distance field)   */
 
 /* reduction mode for the tracker's J^T J / J^T F sums (core.cpp:130-139,244-245)                     */
-#define RBV_REDUCE_FAST 0     /* warp-shuffle tree, FP64 accumulate, fixed order (deterministic)        */
-#define RBV_REDUCE_ORDERED 1  /* per-accumulator serial float32 adds in keyline order == CPU bits        */
+#define RBV_REDUCE_FAST 0     /* warp-shuffle tree, FP64 accumulate, fixed order (deterministic; NOT the reference's bits) */
+#define RBV_REDUCE_ORDERED 1  /* DEFAULT: per-accumulator serial float32 adds in keyline order == CPU bits; the adding   */
+                              /* warps run next to the evaluation blocks of the same launch (rbv_tracker.cu)             */
 
 /* ---- POD mirrors of the reference's structs ------------------------------------------------------- */
 
@@ -119,7 +120,7 @@ int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map
 void rbv_destroy(rbv_ctx* ctx);
 const char* rbv_last_error(void);
 int rbv_sync(rbv_ctx* ctx);
-int rbv_set_reduce_mode(rbv_ctx* ctx, int mode); /* RBV_REDUCE_FAST (default) | RBV_REDUCE_ORDERED */
+int rbv_set_reduce_mode(rbv_ctx* ctx, int mode); /* RBV_REDUCE_ORDERED (default, bit-exact) | RBV_REDUCE_FAST */
 int rbv_lanes(const rbv_ctx* ctx);
 /* run every subsequent call on the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)
  * instead of the context's own; lets a host framework time the work with its own events. */
@@ -151,7 +152,7 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
  *   RBV_TUNE_FIELD: distance field — 1 = one thread per keyline with global atomics, 2 = shared-memory row bands
  *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel,
  *                   3 = the shared-memory-resident pair for few planes (k_rowscan_lat + k_colbox_lat)
- *   RBV_TUNE_TRYVEL: keylines per thread of the FAST-mode tryVel kernel — 1, 2 or 4
+ *   RBV_TUNE_TRYVEL: keylines per thread of the tryVel kernel — 1 (FAST mode only), 2 or 4
  *   RBV_TUNE_FIELD_ROWS: image rows per band of the shared-memory distance field (0 = automatic)
  *   RBV_TUNE_GRAPH: 1 = every kernel launched on the stream, 2 (default) = the kernel sequences of rbv_detect*, rbv_track_g1 and
  *                   rbv_track_g2 are captured once per (map pair) as CUDA graphs and replayed with one launch each
@@ -182,8 +183,10 @@ void rbv_map_release(rbv_ctx* ctx, rbv_map* map);
  * frames. `images`: B pointers to host float32 frames (row pitch `pitch_bytes`), values 0..765 as produced by
  * Rebvio::imageCallback (rebvio.cpp:43-45). `threshold[B]` is the (already servoed) config_->threshold of each
  * lane (edge_detector.cpp:33-36 stays on the host: rbv_servo_threshold). Outputs (host, length B, optional):
- * keyline counts and the auto threshold written to map->threshold(). The call copies H2D, launches, and
- * returns after the counts are back on the host. */
+ * keyline counts and the auto threshold written to map->threshold(). The call copies H2D, launches, and - when an output
+ * pointer is given - returns after the counts are back on the host; with both outputs NULL (or on the front-end stream,
+ * RBV_TUNE_FE_STREAM) it returns once the frames have been UPLOADED: the caller's buffers (pageable or pinned) may be reused as
+ * soon as the call returns, the kernels may still be running (rbv_detect_wait / rbv_sync wait for those). */
 int rbv_detect(rbv_ctx* ctx, rbv_map* map, const float* const* images, size_t pitch_bytes,
                const uint64_t* ts_us, const float* threshold, int* n_keylines, float* auto_threshold);
 
@@ -197,8 +200,9 @@ int rbv_detect_u8(rbv_ctx* ctx, rbv_map* map, const uint8_t* const* images, size
 /* start uploading the NEXT frames (B host pointers, u8 if is_u8 else float32) on the context's copy stream and return
  * at once; the upload overlaps whatever runs on the compute stream (the tracker of the current frame — the reference
  * overlaps acquisition and estimation with two threads, rebvio.cpp:56-117). The next rbv_detect / rbv_detect_u8 call
- * whose images[0] equals this call's images[0] consumes the staged frames instead of copying again. Two slots. The
- * host buffers must stay valid and unchanged until that detect call returns. */
+ * whose images[0] equals this call's images[0] consumes the staged frames instead of copying again. Three slots. The
+ * host buffers must stay valid and unchanged until that detect call returns (it waits for the staged upload to have finished
+ * reading them before it returns). */
 int rbv_prefetch_frames(rbv_ctx* ctx, const void* const* images, size_t pitch_bytes, int is_u8);
 
 /* same, frames already resident in device memory (lane-major contiguous [B][rows][cols] float32). */

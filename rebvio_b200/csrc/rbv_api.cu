@@ -198,10 +198,23 @@ static cudaError_t copy_sync(rbv_ctx* c, void* dst, const void* src, size_t byte
 template <typename T>
 static cudaError_t dalloc(T** p, size_t n) { return cudaMalloc((void**)p, n * sizeof(T)); }
 
+// rbv_track_imu's own pinned result block (it drops the context lock while it waits for the device, so it must not share the
+// staging buffers of the entry points another thread may call meanwhile): [B] LMState | [B][OUT_STRIDE] float | [B][CNT_STRIDE] int | [B] rbv_imu_out
+static size_t trk_block_bytes(size_t B) { return B * (sizeof(LMState) + sizeof(float) * OUT_STRIDE + sizeof(int) * CNT_STRIDE + sizeof(rbv_imu_out)); }
+static LMState* trk_lm(rbv_ctx* c) { return reinterpret_cast<LMState*>(c->h_trk); }
+static float* trk_out(rbv_ctx* c) { return reinterpret_cast<float*>(trk_lm(c) + c->P.lanes); }
+static int* trk_cnt(rbv_ctx* c) { return reinterpret_cast<int*>(trk_out(c) + (size_t)c->P.lanes * OUT_STRIDE); }
+static rbv_imu_out* trk_imu(rbv_ctx* c) { return reinterpret_cast<rbv_imu_out*>(trk_cnt(c) + (size_t)c->P.lanes * CNT_STRIDE); }
+
+static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map_cfg* map, const rbv_core_cfg* core,
+                       int device, int lanes);
 extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map_cfg* map, const rbv_core_cfg* core,
                           int device, int lanes, rbv_ctx** out) {
   if (!cam || !det || !map || !core || !out || lanes < 1 || lanes > 1024) { rbv_set_error("rbv_create: bad argument"); return RBV_ERR_ARG; }
-  if (cam->rows < 32 || cam->cols < 32 || cam->rows > 65535 || det->keylines_max < 1 || det->keylines_max >= (1 << 24)) {
+  *out = nullptr;
+  // pixel indices are int32 (rows * cols must fit with every lane offset held in size_t), rows / cols ride in 16-bit fields of the packed masks
+  if (cam->rows < 32 || cam->cols < 32 || cam->rows > 32767 || cam->cols > 32767 || (long long)cam->rows * cam->cols > 0x7FFFFFFFll ||
+      det->keylines_max < 1 || det->keylines_max >= (1 << 24)) {
     rbv_set_error("rbv_create: image size / keylines_max out of range"); return RBV_ERR_ARG;
   }
   if (core->iterations > RBV_MAX_LM_ITERS || core->search_range < 1 || core->search_range > 127 || core->quantile_num_bins < 1 ||
@@ -216,6 +229,15 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   rbv_ctx* c = new rbv_ctx();
   memset(c, 0, sizeof(*c));
   c->mtx = new std::recursive_mutex();
+  c->device = device;
+  const int rc = create_body(c, cam, det, map, core, device, lanes);
+  if (rc != RBV_OK) { rbv_destroy(c); return rc; }   // a context is GBs of device and pinned memory: nothing of a failed one is left behind
+  *out = c;
+  return RBV_OK;
+}
+
+static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg* det, const rbv_map_cfg* map, const rbv_core_cfg* core,
+                       int device, int lanes) {
   c->cam = *cam; c->det = *det; c->mapc = *map; c->core = *core;
   c->device = device;
   c->reduce_mode = RBV_REDUCE_ORDERED;
@@ -223,7 +245,7 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   float st[2];
   kovesi_widths(3.56359f, 3, c->widths[0], &st[0]);                       // scale_space.cpp:186
   kovesi_widths((float)(st[0] * 1.2599), 3, c->widths[1], &st[1]);
-  for (int s = 0; s < 2; ++s) for (int p = 0; p < 3; ++p) if (c->widths[s][p] > 15) { rbv_set_error("box width > 15"); delete c; return RBV_ERR_ARG; }
+  for (int s = 0; s < 2; ++s) for (int p = 0; p < 3; ++p) if (c->widths[s][p] > 15) { rbv_set_error("box width > 15"); return RBV_ERR_ARG; }
   DevParams& P = c->P;
   P.fm = cam->fm; P.cx = cam->cx; P.cy = cam->cy; P.rows = cam->rows; P.cols = cam->cols; P.npix = cam->rows * cam->cols;
   P.keylines_max = det->keylines_max;
@@ -320,13 +342,15 @@ extern "C" int rbv_create(const rbv_camera* cam, const rbv_detector_cfg* det, co
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_tracker, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   RBV_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  RBV_CUDA(cudaEventCreateWithFlags(&c->ev_upload, cudaEventDisableTiming));
   for (int i = 0; i < RBV_RAW_SLOTS; ++i) {
     RBV_CUDA(cudaMalloc(&c->raw[i], sizeof(float) * B * N));
     RBV_CUDA(cudaEventCreateWithFlags(&c->raw_ready[i], cudaEventDisableTiming));
     RBV_CUDA(cudaEventCreateWithFlags(&c->raw_free[i], cudaEventDisableTiming));
   }
+  RBV_CUDA(cudaMallocHost((void**)&c->h_misc, sizeof(int) * B * 2));
+  RBV_CUDA(cudaMallocHost((void**)&c->h_trk, trk_block_bytes(B)));
   RBV_CUDA(cudaDeviceSynchronize());   // the memsets above ran on the legacy stream; the context's stream is non-blocking
-  *out = c;
   return RBV_OK;
 }
 
@@ -343,19 +367,20 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
     for (int i = 0; i < STAGE_SLOTS; ++i) { cudaFreeHost(stg->host[i]); cudaEventDestroy(stg->ev[i]); }
     delete stg;
   }
-  rbv_graphs_clear(c, nullptr);
+  if (c->graphs) rbv_graphs_clear(c, nullptr);
   if (c->prof) {
     ProfState* p = static_cast<ProfState*>(c->prof);
     for (int i = 0; i < p->created; ++i) { cudaEventDestroy(p->ev[i][0]); cudaEventDestroy(p->ev[i][1]); }
     delete p;
   }
-  cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm);
+  cudaFreeHost(c->h_out); cudaFreeHost(c->h_cnt); cudaFreeHost(c->h_lm); cudaFreeHost(c->h_misc); cudaFreeHost(c->h_trk);
   if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
   if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
   if (c->fe_stream) { cudaStreamSynchronize(c->fe_stream); cudaStreamDestroy(c->fe_stream); }
   if (c->ev_tracker) cudaEventDestroy(c->ev_tracker);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->ev_upload) cudaEventDestroy(c->ev_upload);
   if (c->undist_map) cudaFree(c->undist_map);
   for (int i = 0; i < RBV_RAW_SLOTS; ++i) {
     cudaFree(c->raw[i]);
@@ -686,8 +711,8 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
     map->fe_valid = 1;
   }
   if (n_keylines || auto_threshold) {
-    int* hc = c->h_cnt;
-    float* ht = reinterpret_cast<float*>(c->h_cnt + B);
+    int* hc = c->h_misc;     // not h_cnt: rbv_track_imu on another thread may be waiting for its counters (it drops the lock meanwhile)
+    float* ht = reinterpret_cast<float*>(c->h_misc + B);
     RBV_CUDA(cudaMemcpyAsync(hc, map->count, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     RBV_CUDA(cudaMemcpyAsync(ht, map->threshold, sizeof(float) * B, cudaMemcpyDeviceToHost, c->stream));
     RBV_CUDA(cudaStreamSynchronize(c->stream));
@@ -845,23 +870,28 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
     if (c->raw_key[i] == images[0] && c->raw_u8[i] == (is_u8 ? 1 : 0)) slot = i;
   const float* d_img;
   const bool converted = slot >= 0 && is_u8 && c->raw_conv[slot] && !c->undist_map;   // prefetched and already float32 x 3
+  cudaEvent_t upload_ev = nullptr;       // fires when the caller's host frames have been read
   if (slot >= 0) {                       // staged by rbv_prefetch_frames: wait for the copy stream, no second copy
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
     c->raw_key[slot] = nullptr;
+    upload_ev = c->raw_ready[slot];
   } else if (is_u8) {                    // upload now, in stream order
     slot = c->raw_next;
     c->raw_next = (slot + 1) % RBV_RAW_SLOTS;
     c->raw_key[slot] = nullptr;
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));   // a stale prefetch into this slot must have landed first
     TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 1, c->stream));
+    RBV_CUDA(cudaEventRecord(c->ev_upload, c->stream)); upload_ev = c->ev_upload;
   } else if (c->undist_map) {            // float frames that still need undistorting: stage them, the remap writes c->img
     slot = c->raw_next;
     c->raw_next = (slot + 1) % RBV_RAW_SLOTS;
     c->raw_key[slot] = nullptr;
     RBV_CUDA(cudaStreamWaitEvent(c->stream, c->raw_ready[slot], 0));
     TRY(upload_frames(c, c->raw[slot], images, pitch_bytes, 4, c->stream));
+    RBV_CUDA(cudaEventRecord(c->ev_upload, c->stream)); upload_ev = c->ev_upload;
   } else {
     TRY(upload_frames(c, c->img, images, pitch_bytes, 4, c->stream));
+    RBV_CUDA(cudaEventRecord(c->ev_upload, c->stream)); upload_ev = c->ev_upload;
   }
   if (c->undist_map) {                   // Camera::undistort (+ the x3 conversion for camera bytes) in one gather pass
     RBV_LAUNCH(c, k_undistort, (dim3((unsigned)((c->P.npix + 255) / 256), c->P.lanes)), (256), 0,
@@ -882,6 +912,9 @@ static int detect_host(rbv_ctx* c, rbv_map* map, const void* const* images, size
   }
   const int rc = rbv_detect_device(c, map, d_img, ts_us, threshold, n_keylines, auto_threshold);
   if (slot >= 0) RBV_CUDA(cudaEventRecord(c->raw_free[slot], c->stream));
+  // the header's promise: the caller's frames may be reused once this call returns. A copy from pinned memory is a real DMA that may still
+  // be reading them, so the call waits for the upload (not for the kernels behind it); a prefetched upload was started a frame ago
+  if (upload_ev) RBV_CUDA(cudaEventSynchronize(upload_ev));
   return rc;
 }
 
@@ -1054,9 +1087,9 @@ extern "C" int rbv_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map,
   return RBV_OK;
 }
 
-static void copy_extrot_out(rbv_ctx* c, float* Wx36, float* X6, int* ok) {
+static void copy_extrot_out(rbv_ctx* c, const float* h_out, float* Wx36, float* X6, int* ok) {
   for (int b = 0; b < c->P.lanes; ++b) {
-    const float* o = c->h_out + (size_t)b * OUT_STRIDE;
+    const float* o = h_out + (size_t)b * OUT_STRIDE;
     if (Wx36) memcpy(Wx36 + b * 36, o + OUT_WX, 144);
     if (X6) memcpy(X6 + b * 6, o + OUT_X, 24);
     if (ok) ok[b] = o[OUT_OK] != 0.0f;
@@ -1075,7 +1108,7 @@ extern "C" int rbv_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, const float* vel3, 
   TRY(stage_commit(c, slot));
   TRY(tr_ext_rot_vel(c, new_map, 0));
   TRY(fetch_out(c));
-  copy_extrot_out(c, Wx36, X6, ok);
+  copy_extrot_out(c, c->h_out, Wx36, X6, ok);
   return RBV_OK;
 }
 
@@ -1192,7 +1225,7 @@ extern "C" int rbv_track_g1(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, cons
   c->field_map = new_map;   // tr_build_field's host-side effect, also when the sequence was replayed
   RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * (size_t)c->P.lanes * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
   TRY(fetch_lm(c, vel3, Rvel9, nullptr));
-  copy_extrot_out(c, Wx36, X6, ok);
+  copy_extrot_out(c, c->h_out, Wx36, X6, ok);
   return RBV_OK;
 }
 
@@ -1392,34 +1425,37 @@ extern "C" int rbv_track_imu(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map, con
   TRY(fu_fuse(c, c->lm[0].vel, (int)(sizeof(LMState) / sizeof(float)), c->lane_out + OUT_WX, OUT_STRIDE, c->lane_out + OUT_X,
               OUT_STRIDE, max_radius));
   // the tracker's first-half results leave the device before the second half may overwrite them (same stream: ordered)
-  RBV_CUDA(cudaMemcpyAsync(c->h_out, c->lane_out, sizeof(float) * B * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
-  RBV_CUDA(cudaMemcpyAsync(c->h_lm, c->lm, sizeof(LMState) * B, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(trk_out(c), c->lane_out, sizeof(float) * B * OUT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(trk_lm(c), c->lm, sizeof(LMState) * B, cudaMemcpyDeviceToHost, c->stream));
   TRY(enqueue_g2(c, old_map, new_map, min_matches));
-  RBV_CUDA(cudaMemcpyAsync(imu_host_out(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
-  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, c->lane_cnt, sizeof(int) * B * CNT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(trk_imu(c), c->imu_out, sizeof(rbv_imu_out) * B, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(trk_cnt(c), c->lane_cnt, sizeof(int) * B * CNT_STRIDE, cudaMemcpyDeviceToHost, c->stream));
   if (c->tune[RBV_TUNE_FE_STREAM] == 1) {
     RBV_CUDA(cudaEventRecord(old_map->used, c->stream)); old_map->used_valid = 1;
     RBV_CUDA(cudaEventRecord(new_map->used, c->stream)); new_map->used_valid = 1;
   }
   {
     cudaStream_t st = c->stream;
-    const bool drop = c->tune[RBV_TUNE_FE_STREAM] == 1;   // h_cnt, h_out, h_lm and the IMU mirror are this call's own until it returns
+    // the results land in h_trk, which no other entry point touches (one estimation thread per context, like the reference's): the acquisition
+    // thread's detect / map_size / threshold calls use h_misc and the map's own h_fe while the lock is dropped
+    const bool drop = c->tune[RBV_TUNE_FE_STREAM] == 1;
     if (drop) ctx_lock_.unlock();
     const cudaError_t se = cudaStreamSynchronize(st);
     if (drop) { ctx_lock_.lock(); cudaSetDevice(c->device); }
     RBV_CUDA(se);
   }
-  const LMState* L = reinterpret_cast<const LMState*>(c->h_lm);
+  const LMState* L = trk_lm(c);
+  const int* hc = trk_cnt(c);
   for (size_t b = 0; b < B; ++b) {
     if (Vg3) memcpy(Vg3 + b * 3, L[b].vel, 12);
     if (PVg9) memcpy(PVg9 + b * 9, L[b].Rvel, 36);
-    if (n_matches) n_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_DIR];
-    if (kf_matches) kf_matches[b] = c->h_cnt[b * CNT_STRIDE + CNT_KF];
-    if (n_keylines_new) n_keylines_new[b] = c->h_cnt[b * CNT_STRIDE + CNT_NKEY];
-    if (auto_threshold_new) memcpy(auto_threshold_new + b, c->h_cnt + b * CNT_STRIDE + CNT_ATHR, sizeof(float));
+    if (n_matches) n_matches[b] = hc[b * CNT_STRIDE + CNT_DIR];
+    if (kf_matches) kf_matches[b] = hc[b * CNT_STRIDE + CNT_KF];
+    if (n_keylines_new) n_keylines_new[b] = hc[b * CNT_STRIDE + CNT_NKEY];
+    if (auto_threshold_new) memcpy(auto_threshold_new + b, hc + b * CNT_STRIDE + CNT_ATHR, sizeof(float));
   }
-  copy_extrot_out(c, Wx36, X6, ok);
-  if (out) memcpy(out, imu_host_out(c), sizeof(rbv_imu_out) * B);
+  copy_extrot_out(c, trk_out(c), Wx36, X6, ok);
+  if (out) memcpy(out, trk_imu(c), sizeof(rbv_imu_out) * B);
   return RBV_OK;
 }
 
@@ -1429,9 +1465,9 @@ extern "C" int rbv_map_size(rbv_ctx* c, rbv_map* m, int* n) {
   MAP_READY(c, m);
   MapUse map_use_(c, m);
   if (!m || !n) return RBV_ERR_ARG;
-  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->count, sizeof(int) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(c->h_misc, m->count, sizeof(int) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  memcpy(n, c->h_cnt, sizeof(int) * c->P.lanes);
+  memcpy(n, c->h_misc, sizeof(int) * c->P.lanes);
   return RBV_OK;
 }
 extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
@@ -1439,9 +1475,9 @@ extern "C" int rbv_map_threshold(rbv_ctx* c, rbv_map* m, float* t) {
   MAP_READY(c, m);
   MapUse map_use_(c, m);
   if (!m || !t) return RBV_ERR_ARG;
-  RBV_CUDA(cudaMemcpyAsync(c->h_cnt, m->threshold, sizeof(float) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
+  RBV_CUDA(cudaMemcpyAsync(c->h_misc, m->threshold, sizeof(float) * c->P.lanes, cudaMemcpyDeviceToHost, c->stream));
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  memcpy(t, c->h_cnt, sizeof(float) * c->P.lanes);
+  memcpy(t, c->h_misc, sizeof(float) * c->P.lanes);
   return RBV_OK;
 }
 extern "C" int rbv_map_set_threshold(rbv_ctx* c, rbv_map* m, const float* t) {

@@ -909,7 +909,9 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
-int fe_uses_fused_box(rbv_ctx* c, const float* d_img) { return bp_use(c, d_img) ? 1 : 0; }
+// which of the three scale-space paths fe_scale_space takes for this input pointer (its alignment decides): 2 = fused box pass, 1 = latency
+// pair, 0 = split kernels. Part of the detect graph's key: part 1 (launched directly) and the captured part 2 must be the same path.
+int fe_uses_fused_box(rbv_ctx* c, const float* d_img) { return bp_use(c, d_img) ? 2 : (lat_use(c, d_img) ? 1 : 0); }
 
 // debug: one box pass (createIntegralImage + average) on lane 0, plane 0 of the scratch buffers
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {

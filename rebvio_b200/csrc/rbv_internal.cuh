@@ -142,6 +142,9 @@ struct rbv_ctx {
   float* h_out;
   int* h_cnt;
   float* h_lm;
+  int* h_misc;        // [2][B] counts / thresholds of the small synchronous reads (rbv_map_size, rbv_map_threshold, detect outputs)
+  void* h_trk;        // rbv_track_imu's own result block (see trk_block_bytes, rbv_api.cu)
+  cudaEvent_t ev_upload;   // behind the H2D of a detect call's host frames
   // frame upload: double-buffered raw staging on a copy stream (rbv_prefetch_frames) so that the H2D of frame k+1 overlaps
   // the tracker of frame k; u8 frames are converted (x 3.0, rebvio.cpp:43) on the device
   cudaStream_t copy_stream;

@@ -69,6 +69,26 @@ def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     g.close(); orc.close()
 
 
+@pytest.mark.parametrize("name,nf", [("C1", 3), ("C2", 4), ("C3", 2)])
+def test_cuda_vs_compiled_reference_teacher_forced(name, nf):
+    """benchmark sizes against the UNMODIFIED reference itself (oracle/_ref/librebvio_ref.so travels to the GPU box), not its
+    C restatement: the reference runs free, the CUDA path is given its state before every stage; every stage bit-exact, X within
+    the accuracy of the reference's float32 LAPACK solve. (Free-running against the reference cannot be bit-exact past the first
+    extRotVel: its X comes out of sgesvd_, an un-vendored dependency - SURVEY.md 8(c).)"""
+    if not pyref.available():
+        pytest.skip("oracle/_ref/librebvio_ref.so not present")
+    spec, frames, R_rel = common.sequence(name, nf)
+    cfg = common.cfgs_from_spec(spec)
+    ref = pyref.RefLib(cfg[0], cfg[1], cfg[3])
+    T = H.run_stages(ref, frames, R_rel)
+    g = _gpu(cfg)
+    G = H.run_stages(g, frames, R_rel, teacher=T)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    common.assert_x_vs_ref(T, rep)
+    g.close(); ref.close()
+
+
 @pytest.mark.parametrize("name,nf", [("C2", 3), ("C3", 2)])
 def test_cuda_fast_reduction_teacher_forced(name, nf):
     """Throughput mode (FP64 shuffle-tree sums): per-stage inputs from the oracle; indices and every per-keyline output

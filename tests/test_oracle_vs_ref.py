@@ -54,6 +54,23 @@ def test_full_chain_teacher_forced_320x240():
     ref.close(); orc.close()
 
 
+@pytest.mark.parametrize("name,nf", [("C1", 3), ("C2", 4), ("C3", 2)])
+def test_full_chain_teacher_forced_benchmark_sizes(name, nf):
+    """the same pin at the sizes the GPU parity tests and the bench run on (BASELINE.json configs[0..3]: 640x480, 752x480,
+    1280x720 with 20 k / 32 k keylines): unmodified reference free-running, oracle teacher-forced from its state, every
+    stage bit-exact; X within the accuracy of the reference's own float32 LAPACK solve (tests/common.py)"""
+    spec, frames, R_rel = common.sequence(name, nf)
+    cam, det, mapc, core = common.cfgs_from_spec(spec)
+    ref, orc = pyref.RefLib(cam, det, core), pyref.OracleLib(cam, det, core, mapc)
+    T = H.run_stages(ref, frames, R_rel)
+    G = H.run_stages(orc, frames, R_rel, teacher=T)
+    rep = H.report(T, G)
+    assert H.dirty(rep) == []
+    common.assert_x_vs_ref(T, rep)
+    assert T[1]["detect"]["n"] > 5000
+    ref.close(); orc.close()
+
+
 def test_try_vel_nonzero_velocity_and_residual_carry():
     """tryVel at a few velocities (incl. one that pushes keylines behind the camera / out of the image) with the
     residual vector carried from call to call as minimizeVel does (core.cpp:158,141)."""
