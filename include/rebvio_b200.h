@@ -170,7 +170,8 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
 #define RBV_TUNE_FIELD_IN_FE 7 /* with RBV_TUNE_FE_STREAM: Core::buildDistanceField of a map runs behind its detect on the front-end stream, into the map's own field */
 #define RBV_TUNE_BOX_SPLIT 6 /* fused box pass as G launches over 2B/G planes each (0, 1 = one launch) */
 #define RBV_TUNE_ORDERED 8 /* RBV_REDUCE_ORDERED: 0 = chain warps next to the evaluation (one launch), 1 = evaluation, then one adding block per lane */
-#define RBV_TUNE_COUNT 9
+#define RBV_TUNE_ORD_RW 9 /* RBV_REDUCE_ORDERED: chain warps per reducer CTA (0 = automatic: 2 for tryVel, 1 for extRotVel) */
+#define RBV_TUNE_COUNT 10
 int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
 
 /* allocate / free a B-lane map (replaces std::make_shared<EdgeMap>, edge_detector.cpp:50). */

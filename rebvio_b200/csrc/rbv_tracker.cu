@@ -1017,8 +1017,14 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 #define ORD_CH 128
 #define ORD_RS (ORD_CH + 4)   // shared-memory row stride in floats: row r starts at bank 4 r, so LDS.128 of different rows never collide
 #define ORD_NST 4
-#define TV_RW (TV_TPB / 32)   // lanes (chain warps) per reducer CTA of tryVel
-#define ER_RW 4               // ... of extRotVel (7 rows per chunk instead of 4)
+// Chain warps per reducer CTA (rw, a launch parameter; RBV_TUNE_ORD_RW). A chain warp pulls two factors per accumulator and keyline out of
+// shared memory: with 8 of them on one SM the shared-memory pipe, not the 4-cycle FADD, set the pace (measured: tryVel 167 us instead
+// of 44 us in FAST mode). So the chains are spread over many SMs - few warps per reducer CTA, the CTA's other warps exit at once - and only
+// the accumulator lanes issue the loads. Default: 2 chain warps per CTA for tryVel (10 accumulators), 1 for extRotVel (27).
+#define TV_RW_MAX (TV_TPB / 32)
+#define TV_RW_DEFAULT 2
+#define ER_RW_MAX 4
+#define ER_RW_DEFAULT 1
 __device__ __forceinline__ unsigned ord_ld_acquire(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -1030,7 +1036,7 @@ __device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
 }
 template <int NROWS>
 __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, int kpb,
-                                               unsigned* flags_lane, int pa, int pb, float* ring) {
+                                               unsigned* flags_lane, int pa, int pb, float* ring, int nacc) {
   const int lane = threadIdx.x & 31;
   const int nch = (n + ORD_CH - 1) / ORD_CH;
   int issued = 0, nflag = 0;
@@ -1066,18 +1072,20 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
     const float4* ra = reinterpret_cast<const float4*>(st + pa * ORD_RS);
     const float4* rb = reinterpret_cast<const float4*>(st + pb * ORD_RS);
     const int cnt = min(ORD_CH, n - c * ORD_CH), c4 = cnt >> 2;
-    // two groups of four keylines are fetched ahead of the one being added (LDS latency ~ 7 dependent adds); the row stride leaves one
-    // float4 of slack behind the chunk for the look-ahead of its last groups
-    float4 x0 = ra[0], y0 = rb[0], x1 = ra[1], y1 = rb[1];
+    if (lane < nacc) {   // only the accumulator lanes touch shared memory: a warp-wide LDS.128 costs a wavefront per quarter warp that has an active lane
+      // two groups of four keylines are fetched ahead of the one being added (LDS latency ~ 7 dependent adds); the row stride leaves one
+      // float4 of slack behind the chunk for the look-ahead of its last groups
+      float4 x0 = ra[0], y0 = rb[0], x1 = ra[1], y1 = rb[1];
 #pragma unroll 4
-    for (int i = 0; i < c4; ++i) {
-      const int in = min(i + 2, ORD_CH / 4);
-      const float4 xn = ra[in], yn = rb[in];
-      const float p0 = x0.x * y0.x, p1 = x0.y * y0.y, p2 = x0.z * y0.z, p3 = x0.w * y0.w;   // float products, off the chain
-      s += p0; s += p1; s += p2; s += p3;                                                  // float adds in keyline order
-      x0 = x1; y0 = y1; x1 = xn; y1 = yn;
+      for (int i = 0; i < c4; ++i) {
+        const int in = min(i + 2, ORD_CH / 4);
+        const float4 xn = ra[in], yn = rb[in];
+        const float p0 = x0.x * y0.x, p1 = x0.y * y0.y, p2 = x0.z * y0.z, p3 = x0.w * y0.w;   // float products, off the chain
+        s += p0; s += p1; s += p2; s += p3;                                                  // float adds in keyline order
+        x0 = x1; y0 = y1; x1 = xn; y1 = yn;
+      }
+      for (int i = c4 * 4; i < cnt; ++i) s += st[pa * ORD_RS + i] * st[pb * ORD_RS + i];
     }
-    for (int i = c4 * 4; i < cnt; ++i) s += st[pa * ORD_RS + i] * st[pb * ORD_RS + i];
     __syncwarp();   // every lane is done with the slot before a later cp.async refills it
   }
   return s;
@@ -1093,16 +1101,16 @@ __device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __re
                                                   const float* __restrict__ sr_ptr, int sr_stride, double* __restrict__ partials,
                                                   unsigned* __restrict__ ticket, const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
                                                   LMState* lm, float* lane_out, int lm_call, const DevParams& P, float* __restrict__ rows,
-                                                  unsigned* __restrict__ flags, int nred) {
+                                                  unsigned* __restrict__ flags, int nred, int rw) {
   extern __shared__ __align__(16) float ord_ring[];
-  if ((int)blockIdx.x < nred) {   // chain warps: lane b = TV_RW * block + warp
+  if ((int)blockIdx.x < nred) {   // chain warps: lane b = rw * block + warp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int b = blockIdx.x * TV_RW + warp;
-    if (b >= P.lanes) return;
+    const int b = blockIdx.x * rw + warp;
+    if (warp >= rw || b >= P.lanes) return;
     const int n = count_o[b];
     const int pa = lane < 10 ? c_tv_pa[lane] : 0, pb = lane < 10 ? c_tv_pb[lane] : 0;
     const float s = ordered_chain<4>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk, pa, pb,
-                                     ord_ring + (size_t)warp * ORD_NST * 4 * ORD_RS);
+                                     ord_ring + (size_t)warp * ORD_NST * 4 * ORD_RS, 10);
     float r[10];
 #pragma unroll
     for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1126,11 +1134,11 @@ __device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __re
   const int pbk = blockIdx.x - nred;   // producers: every lane's block 0, then every lane's block 1, ... (the order the chains consume)
   tryvel_fastn_body<KPT, true>(pbk % P.lanes, pbk / P.lanes, RBV_TV_PASS, rows, flags);
 }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred) {
-  tryvel_ord_kernel<2>(RBV_TV_PASS, rows, flags, nred);
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred, int rw) {
+  tryvel_ord_kernel<2>(RBV_TV_PASS, rows, flags, nred, rw);
 }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred) {
-  tryvel_ord_kernel<4>(RBV_TV_PASS, rows, flags, nred);
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred, int rw) {
+  tryvel_ord_kernel<4>(RBV_TV_PASS, rows, flags, nred, rw);
 }
 
 __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
@@ -1176,10 +1184,12 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
 #define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P
     if (ord) {   // chain-warp CTAs first, then the evaluation blocks of every lane in block-major order
-      const int nred = (P.lanes + TV_RW - 1) / TV_RW;
-      const size_t smem = sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS;
-      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred); }
-      else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred); }
+      int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : TV_RW_DEFAULT;
+      rw = rw > TV_RW_MAX ? TV_RW_MAX : rw;
+      const int nred = (P.lanes + rw - 1) / rw;
+      const size_t smem = sizeof(float) * rw * ORD_NST * 4 * ORD_RS;
+      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
+      else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
     }
     else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
@@ -1613,19 +1623,19 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
 // RBV_REDUCE_ORDERED: rows Phi_j (6) and Y_j of every keyline to seven planes (zeros for unmatched keylines), one flag per block;
 // the lane's chain warp adds the 27 products Phi^T Phi / Phi^T Y in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
 __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
-                                                       float* __restrict__ rows, unsigned* __restrict__ flags, int nblk, int nred, float* lane_out,
-                                                       const __grid_constant__ DevParams P) {
+                                                       float* __restrict__ rows, unsigned* __restrict__ flags, int nblk, int nred, int rw,
+                                                       float* lane_out, const __grid_constant__ DevParams P) {
   extern __shared__ __align__(16) float ord_ring[];
-  __shared__ double s_res[ER_RW][27];
-  __shared__ float s_sys[ER_RW][42];
+  __shared__ double s_res[ER_RW_MAX][27];
+  __shared__ float s_sys[ER_RW_MAX][42];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const size_t ps = (size_t)P.lanes * P.kmax;
   if ((int)blockIdx.x < nred) {
-    const int b = blockIdx.x * ER_RW + warp;
-    if (warp >= ER_RW || b >= P.lanes) return;
+    const int b = blockIdx.x * rw + warp;
+    if (warp >= rw || b >= P.lanes) return;
     const int pa = lane < 27 ? c_pair_a[lane] : 0, pb = lane < 27 ? c_pair_b[lane] : 0;
     const float s = ordered_chain<7>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk, pa, pb,
-                                     ord_ring + (size_t)warp * ORD_NST * 7 * ORD_RS);
+                                     ord_ring + (size_t)warp * ORD_NST * 7 * ORD_RS, 27);
     if (lane < 27) s_res[warp][lane] = (double)s;
     __syncwarp();
     extrot_finish_warp(s_res[warp], lane_out + (size_t)b * OUT_STRIDE, s_sys[warp]);
@@ -1665,11 +1675,13 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
     RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
   } else if (c->reduce_mode == RBV_REDUCE_ORDERED) {
-    const int nred = (P.lanes + ER_RW - 1) / ER_RW;
+    int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : ER_RW_DEFAULT;
+    rw = rw > ER_RW_MAX ? ER_RW_MAX : rw;
+    const int nred = (P.lanes + rw - 1) / rw;
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
-    const size_t smem = sizeof(float) * ER_RW * ORD_NST * 7 * ORD_RS;
+    const size_t smem = sizeof(float) * rw * ORD_NST * 7 * ORD_RS;
     RBV_LAUNCH(c, k_extrot_ord, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod,
-               c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, c->lane_out, P);
+               c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, rw, c->lane_out, P);
   } else {
     RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
@@ -1924,8 +1936,8 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 }
 
 int tr_init_ordered(void) {
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS)));
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW * ORD_NST * 4 * ORD_RS)));
-  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW * ORD_NST * 7 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 7 * ORD_RS)));
   return RBV_OK;
 }

@@ -45,7 +45,7 @@ def _imu_in(r):
     return a
 
 
-def _ctx(lanes=2, mode=capi.REDUCE_FAST):
+def _ctx(lanes=2, mode=capi.REDUCE_ORDERED):
     spec = synth.config(SEQ, n_frames=NF)
     cam, det, mapc, core = capi.defaults()
     cam.fm, cam.cx, cam.cy, cam.rows, cam.cols = spec.cam.fm, spec.cam.cx, spec.cam.cy, spec.cam.rows, spec.cam.cols
