@@ -150,8 +150,9 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
 
 /* implementation choices, for tests and profiling; 0 = automatic (the default) everywhere.
  *   RBV_TUNE_FIELD: distance field — 1 = one thread per keyline with global atomics, 2 = shared-memory row bands
- *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel,
- *                   3 = the shared-memory-resident pair for few planes (k_rowscan_lat + k_colbox_lat)
+ *   RBV_TUNE_BOX:   box passes of the scale space — 1 = row-prefix kernel + column/box kernel, 2 = fused kernel, first form (k_boxpass),
+ *                   3 = the shared-memory-resident pair for few planes (k_rowscan_lat + k_colbox_lat), 4 = fused kernel, second form
+ *                   (k_boxpass2: register delay lines, three TMA chunk buffers; box widths 7 / 9, cols <= 832, cols % 4 == 0)
  *   RBV_TUNE_TRYVEL: keylines per thread of the tryVel kernel — 1 (FAST mode only), 2 or 4
  *   RBV_TUNE_FIELD_ROWS: image rows per band of the shared-memory distance field (0 = automatic)
  *   RBV_TUNE_GRAPH: 1 = every kernel launched on the stream, 2 (default) = the kernel sequences of rbv_detect*, rbv_track_g1 and

@@ -752,6 +752,295 @@ __global__ void __launch_bounds__(BP_MAX_THREADS, 1) k_boxpass(const float* __re
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused box pass, second form (k_boxpass2). Same roles as k_boxpass (TMA producer, row pass, column pass + box; one CTA per
+// plane, neither the row prefix nor the integral image reaches HBM) and the same arithmetic statement by statement, but the
+// box no longer reads its four taps from a 40-row shared ring (k_boxpass: 6 shared-memory accesses per pixel, `mio_throttle`
+// its top stall). The thread that scans integral-image column j now produces output column j - h:
+//   A = ii[r+h][j]      is the running column sum it has just formed,
+//   C = ii[r-h-1][j]    is the sum it formed W = 2h+1 rows earlier: a W-deep delay line in registers,
+//   B = ii[r+h][j-W]    is read from the ring (the one tap load left), and kept in a second delay line, because
+//   D = ii[r-h-1][j-W]  is the B of W rows earlier.
+// Rows are walked in sub-chunks of W rows, so both delay lines are register arrays with compile-time indices (two sets that
+// swap roles every sub-chunk: no copies). Per pixel: 1 load of the row prefix, 1 store + 1 load of the ring = 3 shared accesses, and
+// the ring shrinks to 2 x W rows, which pays for a THIRD TMA chunk buffer (fill / row pass / column pass of three chunks overlap)
+// and for a two-stage row pass (warp RA scans the left half of a chunk's rows and hands the 16 carries to warp RB, which scans
+// the right half while RA starts the next chunk: the 752-add dependent chain per chunk becomes two pipelined chains of 376).
+// The last h output columns (right tap clamped to cols-1), the top rows (no upper taps) and the bottom h rows (lower taps clamped,
+// other association order, scale_space.cpp:114-124) take generic paths that read all their taps from the ring.
+// Box widths 7 and 9 (the reference's sigma: {7,7,7} / {9,9,9}); other widths fall back to k_boxpass.
+#define B2_R 16
+#define B2_NB 3
+#define B2_SROWS (B2_R * B2_NB)
+#define B2_MAX_THREADS 512
+
+template <int W> struct B2Cols { float v0[W], v1[W], b0[W], b1[W]; };   // column sums and left-tap values of one sub-chunk, columns c0 and c0 + 32
+
+__device__ __forceinline__ void b2_scan_range(float4* row, int b4, int e4, float& carry) {   // scale_space.cpp:50-57 over float4 [b4, e4)
+  float4 a[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a[i] = (b4 + i < e4) ? row[b4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c4 = b4; c4 < e4; c4 += 4) {
+    float4 nx[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) nx[i] = (c4 + 4 + i < e4) ? row[c4 + 4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    bp_scan4(a[0], carry, c4 == 0);
+    bp_scan4(a[1], carry, false);
+    bp_scan4(a[2], carry, false);
+    bp_scan4(a[3], carry, false);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (c4 + i < e4) row[c4 + i] = a[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = nx[i];
+  }
+}
+
+// what a column thread keeps across sub-chunks
+struct B2State {
+  unsigned S_a, ring_a, spb, rpb;     // shared addresses of S[0][c0] and ring[0][0][c0]; byte pitches of an S row and a ring row
+  unsigned nbar;
+  int rows, cols, nchunks, c0, h, q, lane;
+  float run0, run1, inv0, inv1;
+  bool st0, st1;
+  int ci_ready, ci_rel;
+  float* dst;                         // output plane + (c0 - h)
+  unsigned long long *scanned, *empty;
+  const float (*inv_area)[16];
+};
+
+// one sub-chunk: rows k0 .. k0+nr-1 are scanned into `cur` (and the ring), then the box rows k0-h .. k0+nr-1-h are written from
+// `cur` (A, B) and `prev` (C, D). TOP = first sub-chunk (no upper taps, scale_space.cpp:78-84). MIXED = warp 0 (columns without a left tap, :94).
+template <int W, bool MIXED, bool TOP>
+__device__ __forceinline__ void b2_sub(B2State& st, B2Cols<W>& cur, const B2Cols<W>& prev, int s) {
+  constexpr int h = W / 2;
+  const int k0 = s * W, nr = min(W, st.rows - k0), k1 = k0 + nr;
+  const int need = (k1 - 1) / B2_R;
+  if (st.q == 0)
+    for (; st.ci_ready <= need; ++st.ci_ready) mbar_wait(st.scanned + st.ci_ready % B2_NB, (unsigned)((st.ci_ready / B2_NB) & 1));
+  asm volatile("bar.sync 1, %0;" ::"r"(st.nbar) : "memory");   // chunk rows visible to every column warp; the box reads of sub-chunk s-1 are done
+  const unsigned rb = st.ring_a + (unsigned)((s & 1) * W) * st.rpb;
+  {
+    int srow = k0 % B2_SROWS;
+    float x0[W], x1[W];
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      const unsigned sa = st.S_a + (unsigned)srow * st.spb;
+      x0[i] = lds_f32(sa); x1[i] = lds_f32(sa + 128u);
+      srow = (srow + 1 == B2_SROWS) ? 0 : srow + 1;
+    }
+#pragma unroll
+    for (int i = 0; i < W; ++i) {                                                       // column pass, scale_space.cpp:59-65
+      if (i < nr) {
+        if (TOP && i == 0) { st.run0 = x0[0]; st.run1 = x1[0]; }
+        else { st.run0 = st.run0 + x0[i]; st.run1 = st.run1 + x1[i]; }
+        cur.v0[i] = st.run0; cur.v1[i] = st.run1;
+        sts_f32(rb + (unsigned)i * st.rpb, st.run0);
+        sts_f32(rb + (unsigned)i * st.rpb + 128u, st.run1);
+      }
+    }
+  }
+  // chunk buffers whose last row has now been read go back to the producer
+  while (st.ci_rel < st.nchunks && ((st.ci_rel + 1) * B2_R <= k1 || k1 == st.rows)) {
+    __syncwarp();
+    if (st.lane == 0) { fence_proxy_async(); mbar_arrive(st.empty + st.ci_rel % B2_NB); }
+    ++st.ci_rel;
+  }
+  asm volatile("bar.sync 1, %0;" ::"r"(st.nbar) : "memory");   // ring rows of this sub-chunk complete
+  const bool left0 = !MIXED || st.c0 >= W;
+  {
+    const unsigned lb = rb - 4u * (unsigned)(left0 ? W : 0);   // column c0 - W (clamped to c0 where there is no left tap: never used)
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      if (i < nr) { cur.b0[i] = lds_f32(lb + (unsigned)i * st.rpb); cur.b1[i] = lds_f32(rb - 4u * W + (unsigned)i * st.rpb + 128u); }
+    }
+  }
+  float* d = st.dst + (ptrdiff_t)(k0 - h) * st.cols;
+#pragma unroll
+  for (int i = 0; i < W; ++i) {
+    if (i < nr && (!TOP || i >= h)) {
+      float o0, o1;
+      if (TOP) {                                                                        // :78-84: rows without upper taps
+        o0 = left0 ? cur.v0[i] - cur.b0[i] : cur.v0[i];
+        o1 = cur.v1[i] - cur.b1[i];
+        const int nc0 = min(W, st.c0 + 1);
+        o0 *= st.inv_area[i + 1][nc0];
+        o1 *= st.inv_area[i + 1][W];
+      } else {                                                                          // :99 ((A - B) - C) + D, :94 A - C
+        o0 = ((cur.v0[i] - cur.b0[i]) - prev.v0[i]) + prev.b0[i];
+        if (MIXED && !left0) o0 = cur.v0[i] - prev.v0[i];
+        o1 = ((cur.v1[i] - cur.b1[i]) - prev.v1[i]) + prev.b1[i];
+        o0 *= st.inv0; o1 *= st.inv1;
+      }
+      if (st.st0) d[(size_t)i * st.cols] = o0;
+      if (st.st1) d[(size_t)i * st.cols + 32] = o1;
+    }
+  }
+  // the h output columns whose right tap is clamped to the last column: every tap from the ring (this sub-chunk and the previous one)
+  if (MIXED && st.lane < h) {
+    const int oc = st.cols - h + st.lane, jlo = oc - h - 1, ncol = (st.cols - 1) - jlo;
+    const unsigned ring0 = st.ring_a - 4u * (unsigned)st.c0;   // column 0 of ring row 0
+    const unsigned ca = ring0 + (unsigned)((s & 1) * W) * st.rpb, pa = ring0 + (unsigned)(((s & 1) ^ 1) * W) * st.rpb;
+    const float invm = (float)(1.0 / (double)((float)W * (float)ncol));
+    float* dt = st.dst - (st.c0 - h) + oc + (ptrdiff_t)(k0 - h) * st.cols;
+    for (int i = TOP ? h : 0; i < nr; ++i) {
+      const float A = lds_f32(ca + (unsigned)i * st.rpb + 4u * (unsigned)(st.cols - 1)), Bv = lds_f32(ca + (unsigned)i * st.rpb + 4u * (unsigned)jlo);
+      float o;
+      if (TOP) o = (A - Bv) * st.inv_area[i + 1][ncol];
+      else {
+        const float C = lds_f32(pa + (unsigned)i * st.rpb + 4u * (unsigned)(st.cols - 1)), D = lds_f32(pa + (unsigned)i * st.rpb + 4u * (unsigned)jlo);
+        o = (((A - Bv) - C) + D) * invm;
+      }
+      dt[(size_t)i * st.cols] = o;
+    }
+  }
+}
+
+template <int W>
+__device__ __forceinline__ void boxpass2_body(const float* __restrict__ src, float* __restrict__ outp, int rows, int cols, int spitch, int ncw, int rcols,
+                                              float* bp_smem, float (*inv_area)[16], unsigned long long* bars, float (*carry_s)[B2_R]) {
+  constexpr int h = W / 2;
+  float* S = bp_smem;                                   // [B2_SROWS][spitch]: image row r in S row r % 48
+  float* ring = bp_smem + B2_SROWS * spitch;            // [2][W][rcols]: integral-image rows of the current / previous sub-chunk
+  unsigned long long* full = bars;                      // [3] TMA landed
+  unsigned long long* scanned = bars + 3;               // [3] row pass done
+  unsigned long long* empty = bars + 6;                 // [3] column warps are done with the chunk
+  unsigned long long* half = bars + 9;                  // [2] RA has left its carries for RB
+  unsigned long long* cfree = bars + 11;                // [2] RB has taken them
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 256; i += blockDim.x) {
+    const int a = i / 16, b = i % 16;
+    inv_area[a][b] = (a && b) ? (float)(1.0 / (double)((float)a * (float)b)) : 0.0f;   // precomputeDivisors :130-171
+  }
+  if (tid == 0) {
+    for (int i = 0; i < B2_NB; ++i) { mbar_init(full + i, 1u); mbar_init(scanned + i, 32u); mbar_init(empty + i, (unsigned)ncw); }
+    for (int i = 0; i < 2; ++i) { mbar_init(half + i, 32u); mbar_init(cfree + i, 32u); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int nchunks = (rows + B2_R - 1) / B2_R;
+  const int n4 = cols >> 2;
+  const int n4a = min(n4, ((n4 / 2 + 3) / 4) * 4);      // RA scans float4 [0, n4a), RB [n4a, n4)
+  if (warp == 0) {
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci % B2_NB;
+      const int nr = min(B2_R, rows - ci * B2_R);
+      if (lane == 0) {
+        if (ci >= B2_NB) mbar_wait(empty + buf, (unsigned)(((ci / B2_NB) - 1) & 1));
+        mbar_arrive_expect_tx(full + buf, (unsigned)(nr * cols * 4));
+      }
+      __syncwarp();
+      if (lane < nr)
+        bulk_g2s(S + (size_t)(buf * B2_R + lane) * spitch, src + (size_t)(ci * B2_R + lane) * cols, (unsigned)(cols * 4), full + buf);
+    }
+  } else if (warp == 1) {                               // RA: left half of every row of the chunk, carries to RB
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci % B2_NB;
+      const int nr = min(B2_R, rows - ci * B2_R);
+      mbar_wait(full + buf, (unsigned)((ci / B2_NB) & 1));
+      float carry = 0.0f;
+      if (lane < nr) b2_scan_range(reinterpret_cast<float4*>(S + (size_t)(buf * B2_R + lane) * spitch), 0, n4a, carry);
+      if (ci >= 2) mbar_wait(cfree + (ci & 1), (unsigned)(((ci >> 1) - 1) & 1));
+      if (lane < B2_R) carry_s[ci & 1][lane] = carry;
+      mbar_arrive(half + (ci & 1));
+    }
+  } else if (warp == 2) {                               // RB: right half, starting from RA's carries
+    for (int ci = 0; ci < nchunks; ++ci) {
+      const int buf = ci % B2_NB;
+      const int nr = min(B2_R, rows - ci * B2_R);
+      mbar_wait(full + buf, (unsigned)((ci / B2_NB) & 1));
+      mbar_wait(half + (ci & 1), (unsigned)((ci >> 1) & 1));
+      float carry = (lane < B2_R) ? carry_s[ci & 1][lane] : 0.0f;
+      __syncwarp();
+      mbar_arrive(cfree + (ci & 1));
+      if (lane < nr && n4a < n4) b2_scan_range(reinterpret_cast<float4*>(S + (size_t)(buf * B2_R + lane) * spitch), n4a, n4, carry);
+      mbar_arrive(scanned + buf);
+    }
+  } else if (warp - 3 < ncw) {
+    B2State st;
+    st.q = warp - 3; st.lane = lane;
+    st.c0 = st.q * 64 + lane;
+    const int c1 = st.c0 + 32;
+    st.rows = rows; st.cols = cols; st.nchunks = nchunks; st.h = h;
+    st.spb = 4u * (unsigned)spitch; st.rpb = 4u * (unsigned)rcols;
+    st.S_a = smem_u32(S) + 4u * (unsigned)st.c0;
+    st.ring_a = smem_u32(ring) + 4u * (unsigned)st.c0;
+    st.nbar = (unsigned)(ncw * 32);
+    st.run0 = st.run1 = 0.0f;
+    st.inv0 = (float)(1.0 / (double)((float)W * (float)min(W, st.c0 + 1)));              // interior-row divisor (:72 / :168)
+    st.inv1 = (float)(1.0 / (double)((float)W * (float)W));
+    st.st0 = st.c0 >= h && st.c0 < cols; st.st1 = c1 < cols;
+    st.ci_ready = 0; st.ci_rel = 0;
+    st.dst = outp + (st.c0 - h);
+    st.scanned = scanned; st.empty = empty; st.inv_area = inv_area;
+    B2Cols<W> X, Y;
+    const int nsub = (rows + W - 1) / W;
+    if (st.q == 0) {
+      b2_sub<W, true, true>(st, X, Y, 0);
+      int s2 = 1;
+      for (; s2 + 1 < nsub; s2 += 2) { b2_sub<W, true, false>(st, Y, X, s2); b2_sub<W, true, false>(st, X, Y, s2 + 1); }
+      if (s2 < nsub) b2_sub<W, true, false>(st, Y, X, s2);
+    } else {
+      b2_sub<W, false, true>(st, X, Y, 0);
+      int s2 = 1;
+      for (; s2 + 1 < nsub; s2 += 2) { b2_sub<W, false, false>(st, Y, X, s2); b2_sub<W, false, false>(st, X, Y, s2 + 1); }
+      if (s2 < nsub) b2_sub<W, false, false>(st, Y, X, s2);
+    }
+    // bottom h rows (:104-124): lower taps clamped to the last row, ((A - C) - B) + D; every tap from the ring, which holds the last two
+    // sub-chunks (row r in buffer (r / W) & 1, slot r % W). No barrier needed: the ring is not written any more.
+    const unsigned ring0 = st.ring_a - 4u * (unsigned)st.c0;
+    auto ring_at = [&](int r, int c) -> float { return lds_f32(ring0 + (unsigned)(((r / W) & 1) * W + r % W) * st.rpb + 4u * (unsigned)c); };
+    for (int ro = rows - h; ro < rows; ++ro) {
+      const int rlo = ro - h - 1, rhi = rows - 1, nrow = rhi - rlo;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        int oc;
+        if (j == 0) { if (!st.st0) continue; oc = st.c0 - h; }
+        else if (j == 1) { if (!st.st1) continue; oc = c1 - h; }
+        else { if (!(st.q == 0 && lane < h)) continue; oc = cols - h + lane; }
+        const int jhi = min(oc + h, cols - 1), jlo = oc - h - 1, ncol = jhi - max(jlo, -1);
+        const float A = ring_at(rhi, jhi), C = ring_at(rlo, jhi);
+        float v;
+        if (jlo >= 0) { const float Bv = ring_at(rhi, jlo), D = ring_at(rlo, jlo); v = ((A - C) - Bv) + D; }   // :119, :124
+        else v = A - C;                                                                                       // :114
+        outp[(size_t)ro * cols + oc] = v * inv_area[nrow][ncol];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(B2_MAX_THREADS, 1) k_boxpass2(const float* __restrict__ in, float* __restrict__ out, int rows, int cols,
+                                                                 size_t in_plane_stride, size_t out_plane_stride, int nz, int d0, int d1, int spitch,
+                                                                 int in_div, int ncw, int rcols) {
+  extern __shared__ __align__(128) float bp_smem[];
+  __shared__ float inv_area[16][16];
+  __shared__ __align__(8) unsigned long long bars[13];
+  __shared__ float carry_s[2][B2_R];
+  const int plane = blockIdx.x;
+  const int d = (plane % nz) ? d1 : d0;
+  const float* src = in + (size_t)(plane / in_div) * in_plane_stride;   // in_div = 2: both scales of a lane read the same input plane
+  float* outp = out + (size_t)plane * out_plane_stride;
+  if (d == 7) boxpass2_body<7>(src, outp, rows, cols, spitch, ncw, rcols, bp_smem, inv_area, bars, carry_s);
+  else boxpass2_body<9>(src, outp, rows, cols, spitch, ncw, rcols, bp_smem, inv_area, bars, carry_s);
+}
+
+static int b2_ncw(int cols) { return (cols + 63) / 64; }
+static int b2_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }
+static size_t b2_smem_bytes(int cols) {
+  return sizeof(float) * ((size_t)B2_SROWS * b2_spitch(cols) + (size_t)2 * 9 * (b2_ncw(cols) * 64) + 64);
+}
+static bool b2_supported(const rbv_ctx* c) {
+  const int cols = c->P.cols;
+  for (int s2 = 0; s2 < 2; ++s2)
+    for (int p = 0; p < 3; ++p) if (c->widths[s2][p] != 7 && c->widths[s2][p] != 9) return false;
+  return (cols & 3) == 0 && (3 + b2_ncw(cols)) * 32 <= B2_MAX_THREADS && b2_smem_bytes(cols) <= 225 * 1024 && c->P.rows >= 32 && cols >= 64;
+}
+static int b2_launch(rbv_ctx* c, const float* in, float* out, int planes, size_t in_stride, size_t out_stride, int nz, int d0, int d1, int in_div = 1) {
+  const int cols = c->P.cols, ncw = b2_ncw(cols);
+  RBV_LAUNCH(c, k_boxpass2, (planes), ((3 + ncw) * 32), b2_smem_bytes(cols), in, out, c->P.rows, cols, in_stride, out_stride, nz, d0, d1,
+             b2_spitch(cols), in_div, ncw, ncw * 64);
+  return RBV_OK;
+}
+
 static int bp_spitch(int cols) { return cols + (((cols >> 2) & 1) ? 8 : 4); }   // (pitch / 4) odd: conflict-free 128-bit row accesses
 static int bp_threads(int cols) {   // smallest block whose column warps cover cols at two columns per thread
   const int need = (cols + 63) / 64;
@@ -768,11 +1057,14 @@ static bool bp_supported(const rbv_ctx* c) {
   const int cols = c->P.cols;
   return (cols & 3) == 0 && bp_threads(cols) <= BP_MAX_THREADS && bp_smem_bytes(cols) <= 225 * 1024;
 }
-static bool bp_use(const rbv_ctx* c, const void* src) {
-  if (!bp_supported(c) || ((uintptr_t)src & 15) != 0) return false;
+// which fused kernel: k_boxpass2 (register delay lines) where it applies, unless RBV_TUNE_BOX = 2 asks for the first form
+static bool b2_use(const rbv_ctx* c) { return b2_supported(c) && c->tune[RBV_TUNE_BOX] != 2; }
+static bool bp_use(const rbv_ctx* c, const void* src) {   // a fused (one block per plane) box pass at all?
+  if (((uintptr_t)src & 15) != 0) return false;
   if (c->tune[RBV_TUNE_BOX] == 1 || c->tune[RBV_TUNE_BOX] == 3) return false;
-  if (c->tune[RBV_TUNE_BOX] == 2) return true;
-  return c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
+  if (c->tune[RBV_TUNE_BOX] == 2) return bp_supported(c);
+  if (c->tune[RBV_TUNE_BOX] == 4) return b2_supported(c);
+  return (b2_supported(c) || bp_supported(c)) && c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
 }
 static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
                      int d0, int d1, int dual, int in_div = 1) {
@@ -829,6 +1121,7 @@ static void lat_colbox(rbv_ctx* c, const float* rowsum, float* out0, float* out1
 int fe_init(rbv_ctx* c) {
   (void)c;   // the current device is the context's; the limit is per device and shared by every context on it
   RBV_CUDA(cudaFuncSetAttribute(k_boxpass, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+  RBV_CUDA(cudaFuncSetAttribute(k_boxpass2, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
   RBV_CUDA(cudaFuncSetAttribute(k_rowscan_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   RBV_CUDA(cudaFuncSetAttribute(k_colbox_lat, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   return RBV_OK;
@@ -863,6 +1156,14 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
     for (int g = 0; g < G; ++g) {
       const size_t po = (size_t)g * pl * N;                    // plane offset in bufA / bufB
       const float* img_g = d_img + (size_t)g * (pl / 2) * N;   // pass 0 reads one input plane per lane
+      if (b2_use(c)) {
+        if (part != 2) b2_launch(c, img_g, c->bufA + po, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 2);
+        if (part != 1) {
+          b2_launch(c, c->bufA + po, c->bufB + po, pl, N, N, 2, c->widths[0][1], c->widths[1][1]);
+          b2_launch(c, c->bufB + po, c->bufA + po, pl, N, N, 2, c->widths[0][2], c->widths[1][2]);
+        }
+        continue;
+      }
       if (part != 2) bp_launch(c, img_g, c->bufA + po, c->bufA + po, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
       if (part != 1) {
         bp_launch(c, c->bufA + po, c->bufB + po, c->bufB + po, pl, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
@@ -911,13 +1212,18 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
 }
 // which of the three scale-space paths fe_scale_space takes for this input pointer (its alignment decides): 2 = fused box pass, 1 = latency
 // pair, 0 = split kernels. Part of the detect graph's key: part 1 (launched directly) and the captured part 2 must be the same path.
-int fe_uses_fused_box(rbv_ctx* c, const float* d_img) { return bp_use(c, d_img) ? 2 : (lat_use(c, d_img) ? 1 : 0); }
+int fe_uses_fused_box(rbv_ctx* c, const float* d_img) { return bp_use(c, d_img) ? (b2_use(c) ? 3 : 2) : (lat_use(c, d_img) ? 1 : 0); }
 
 // debug: one box pass (createIntegralImage + average) on lane 0, plane 0 of the scratch buffers
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out) {
   const int rows = c->P.rows, cols = c->P.cols;
   const size_t N = (size_t)c->P.npix;
   const int d = c->widths[scale][pass];
+  if (c->tune[RBV_TUNE_BOX] == 4 && bp_use(c, d_in) && b2_use(c)) {
+    b2_launch(c, d_in, d_out, 1, N, N, 1, d, d);
+    RBV_CUDA(cudaGetLastError());
+    return RBV_OK;
+  }
   if (c->tune[RBV_TUNE_BOX] == 2 && bp_use(c, d_in)) {
     bp_launch(c, d_in, d_out, d_out, 1, N, N, 1, d, d, 0);
     RBV_CUDA(cudaGetLastError());

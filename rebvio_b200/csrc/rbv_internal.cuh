@@ -196,13 +196,14 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
-  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord)
+  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord) X(k_boxpass2)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
 #undef X
   KID_COUNT
 };
+static_assert(KID_COUNT <= 48, "rbv_ctx::klaunch holds 48 kernel ids");
 void rbv_prof_begin(rbv_ctx* c, int kid);
 void rbv_prof_end(rbv_ctx* c, int kid);
 #define RBV_LAUNCH(c, kern, grid, block, smem, ...)                     \

@@ -1014,16 +1014,17 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 //     the products (one FMUL, off the chain) and adds them in order; all 32 lanes fetch, accumulator threads add.
 // Producers never wait for anything, so the launch cannot deadlock whatever the CTA scheduling order; the flags are cleared
 // by the chain warp as it consumes them. The chain (13 k keylines ~ 27 us) hides behind the evaluation of the other lanes.
-#define ORD_CH 128
-#define ORD_RS (ORD_CH + 4)   // shared-memory row stride in floats: row r starts at bank 4 r, so LDS.128 of different rows never collide
 #define ORD_NST 4
+#define ORD_PAD 4             // floats behind a staged row: row r of a chunk starts at bank 4 r, so LDS.128 of different rows never collide
+#define TV_CH 512             // keylines per staged chunk: tryVel (4 rows) / extRotVel (7 rows). The per-chunk work (flag test, cp.async issue,
+#define ER_CH 256             // wait, two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
 // Chain warps per reducer CTA (rw, a launch parameter; RBV_TUNE_ORD_RW). A chain warp pulls two factors per accumulator and keyline out of
-// shared memory: with 8 of them on one SM the shared-memory pipe, not the 4-cycle FADD, set the pace (measured: tryVel 167 us instead
-// of 44 us in FAST mode). So the chains are spread over many SMs - few warps per reducer CTA, the CTA's other warps exit at once - and only
-// the accumulator lanes issue the loads. Default: 2 chain warps per CTA for tryVel (10 accumulators), 1 for extRotVel (27).
-#define TV_RW_MAX (TV_TPB / 32)
+// shared memory: with 8 of them on one SM the shared-memory pipe, not the 4-cycle FADD, set the pace (measured: tryVel 167 us per call
+// against 108 us with 1 or 2). So the chains are spread over many SMs - few warps per reducer CTA, the CTA's other warps exit at once -
+// and only the accumulator lanes issue the loads. Default: 2 chain warps per CTA for tryVel (10 accumulators), 1 for extRotVel (27).
+#define TV_RW_MAX 4
 #define TV_RW_DEFAULT 2
-#define ER_RW_MAX 4
+#define ER_RW_MAX 2
 #define ER_RW_DEFAULT 1
 __device__ __forceinline__ unsigned ord_ld_acquire(const unsigned* p) {
   unsigned v;
@@ -1034,17 +1035,26 @@ __device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
-template <int NROWS>
+// 16 keylines: float products (off the chain), then the float adds in keyline order
+__device__ __forceinline__ void ord_add16(float& s, const float4* x, const float4* y) {
+  float p[16];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) { p[4 * g] = x[g].x * y[g].x; p[4 * g + 1] = x[g].y * y[g].y; p[4 * g + 2] = x[g].z * y[g].z; p[4 * g + 3] = x[g].w * y[g].w; }
+#pragma unroll
+  for (int k = 0; k < 16; ++k) s += p[k];
+}
+template <int NROWS, int CH>
 __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, int kpb,
                                                unsigned* flags_lane, int pa, int pb, float* ring, int nacc) {
+  constexpr int RS = CH + ORD_PAD;
   const int lane = threadIdx.x & 31;
-  const int nch = (n + ORD_CH - 1) / ORD_CH;
+  const int nch = (n + CH - 1) / CH;
   int issued = 0, nflag = 0;
   float s = 0.0f;
   for (int c = 0; c < nch; ++c) {
     // keep up to ORD_NST chunks in flight, as far as the producers' flags allow; block only for the chunk needed now
     while (issued < nch && issued < c + ORD_NST) {
-      const int need = (min((issued + 1) * ORD_CH, n) - 1) / kpb;   // producer block that holds the chunk's last keyline
+      const int need = (min((issued + 1) * CH, n) - 1) / kpb;   // producer block that holds the chunk's last keyline
       bool ok = true;
       while (nflag <= need) {
         unsigned f = 0u;
@@ -1055,10 +1065,12 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
       }
       if (!ok) break;
       __syncwarp();
-      float* st = ring + (size_t)(issued % ORD_NST) * NROWS * ORD_RS + 4 * lane;
-      const float* src = rows + base + (size_t)issued * ORD_CH + 4 * lane;
+      float* st = ring + (size_t)(issued % ORD_NST) * NROWS * RS + 4 * lane;
+      const float* src = rows + base + (size_t)issued * CH + 4 * lane;
 #pragma unroll
-      for (int r = 0; r < NROWS; ++r) ord_cp16(st + r * ORD_RS, src + (size_t)r * ps);
+      for (int r = 0; r < NROWS; ++r)
+#pragma unroll
+        for (int q = 0; q < CH / 128; ++q) ord_cp16(st + r * RS + 128 * q, src + (size_t)r * ps + 128 * q);
       asm volatile("cp.async.commit_group;" ::: "memory");
       ++issued;
     }
@@ -1068,23 +1080,31 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
     else if (pend == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
-    const float* st = ring + (size_t)(c % ORD_NST) * NROWS * ORD_RS;
-    const float4* ra = reinterpret_cast<const float4*>(st + pa * ORD_RS);
-    const float4* rb = reinterpret_cast<const float4*>(st + pb * ORD_RS);
-    const int cnt = min(ORD_CH, n - c * ORD_CH), c4 = cnt >> 2;
+    const int cnt = min(CH, n - c * CH);
     if (lane < nacc) {   // only the accumulator lanes touch shared memory: a warp-wide LDS.128 costs a wavefront per quarter warp that has an active lane
-      // two groups of four keylines are fetched ahead of the one being added (LDS latency ~ 7 dependent adds); the row stride leaves one
-      // float4 of slack behind the chunk for the look-ahead of its last groups
-      float4 x0 = ra[0], y0 = rb[0], x1 = ra[1], y1 = rb[1];
-#pragma unroll 4
-      for (int i = 0; i < c4; ++i) {
-        const int in = min(i + 2, ORD_CH / 4);
-        const float4 xn = ra[in], yn = rb[in];
-        const float p0 = x0.x * y0.x, p1 = x0.y * y0.y, p2 = x0.z * y0.z, p3 = x0.w * y0.w;   // float products, off the chain
-        s += p0; s += p1; s += p2; s += p3;                                                  // float adds in keyline order
-        x0 = x1; y0 = y1; x1 = xn; y1 = yn;
+      const float* st = ring + (size_t)(c % ORD_NST) * NROWS * RS;
+      const float4* ra = reinterpret_cast<const float4*>(st + pa * RS);
+      const float4* rb = reinterpret_cast<const float4*>(st + pb * RS);
+      // blocks of 16 keylines, the next block's factors fetched while the current one is added (two register sets, swapped by unrolling)
+      const int nb16 = cnt >> 4;
+      float4 xa[4], ya[4], xb[4], yb[4];
+      if (nb16 > 0) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) { xa[g] = ra[g]; ya[g] = rb[g]; }
       }
-      for (int i = c4 * 4; i < cnt; ++i) s += st[pa * ORD_RS + i] * st[pb * ORD_RS + i];
+      int b16 = 0;
+      for (; b16 + 2 <= nb16; b16 += 2) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) { xb[g] = ra[4 * (b16 + 1) + g]; yb[g] = rb[4 * (b16 + 1) + g]; }
+        ord_add16(s, xa, ya);
+        if (b16 + 2 < nb16) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) { xa[g] = ra[4 * (b16 + 2) + g]; ya[g] = rb[4 * (b16 + 2) + g]; }
+        }
+        ord_add16(s, xb, yb);
+      }
+      if (b16 < nb16) { ord_add16(s, xa, ya); ++b16; }
+      for (int i = b16 * 16; i < cnt; ++i) s += st[pa * RS + i] * st[pb * RS + i];
     }
     __syncwarp();   // every lane is done with the slot before a later cp.async refills it
   }
@@ -1109,8 +1129,8 @@ __device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __re
     if (warp >= rw || b >= P.lanes) return;
     const int n = count_o[b];
     const int pa = lane < 10 ? c_tv_pa[lane] : 0, pb = lane < 10 ? c_tv_pb[lane] : 0;
-    const float s = ordered_chain<4>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk, pa, pb,
-                                     ord_ring + (size_t)warp * ORD_NST * 4 * ORD_RS, 10);
+    const float s = ordered_chain<4, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk, pa, pb,
+                                            ord_ring + (size_t)warp * ORD_NST * 4 * (TV_CH + ORD_PAD), 10);
     float r[10];
 #pragma unroll
     for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1187,7 +1207,7 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
       int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : TV_RW_DEFAULT;
       rw = rw > TV_RW_MAX ? TV_RW_MAX : rw;
       const int nred = (P.lanes + rw - 1) / rw;
-      const size_t smem = sizeof(float) * rw * ORD_NST * 4 * ORD_RS;
+      const size_t smem = sizeof(float) * rw * ORD_NST * 4 * (TV_CH + ORD_PAD);
       if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
       else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
     }
@@ -1634,8 +1654,8 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
     const int b = blockIdx.x * rw + warp;
     if (warp >= rw || b >= P.lanes) return;
     const int pa = lane < 27 ? c_pair_a[lane] : 0, pb = lane < 27 ? c_pair_b[lane] : 0;
-    const float s = ordered_chain<7>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk, pa, pb,
-                                     ord_ring + (size_t)warp * ORD_NST * 7 * ORD_RS, 27);
+    const float s = ordered_chain<7, ER_CH>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk, pa, pb,
+                                            ord_ring + (size_t)warp * ORD_NST * 7 * (ER_CH + ORD_PAD), 27);
     if (lane < 27) s_res[warp][lane] = (double)s;
     __syncwarp();
     extrot_finish_warp(s_res[warp], lane_out + (size_t)b * OUT_STRIDE, s_sys[warp]);
@@ -1679,7 +1699,7 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     rw = rw > ER_RW_MAX ? ER_RW_MAX : rw;
     const int nred = (P.lanes + rw - 1) / rw;
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
-    const size_t smem = sizeof(float) * rw * ORD_NST * 7 * ORD_RS;
+    const size_t smem = sizeof(float) * rw * ORD_NST * 7 * (ER_CH + ORD_PAD);
     RBV_LAUNCH(c, k_extrot_ord, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod,
                c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, rw, c->lane_out, P);
   } else {
@@ -1936,8 +1956,8 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 }
 
 int tr_init_ordered(void) {
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * ORD_RS)));
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * ORD_RS)));
-  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 7 * ORD_RS)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * (TV_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * (TV_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 7 * (ER_CH + ORD_PAD))));
   return RBV_OK;
 }
