@@ -417,7 +417,7 @@ def run_b200(args):
     K_mean, probes = main["K_mean"], main["probes"]
     top_ms, top_n, top_launches = main["prof"]
     # planes per launch of the box-pass kernels: pass 0 = 1 (rowscan) / 1+1 (colbox x2 launches), passes 1,2 = 2
-    planes = {"k_rowscan": 5.0 / 3.0, "k_rowscan4": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0}.get(top, 1.0)
+    planes = {"k_rowscan": 5.0 / 3.0, "k_rowscan4": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0, "k_boxpass2": 11.0 / 6.0}.get(top, 1.0)
     words = B * N if top == "k_fill" else 0
     abytes = roofline.kernel_bytes(top, N, K_mean, B, planes=planes, P=probes, words=words)
     achieved = abytes / (top_ms / max(1, top_n) * 1e-3) / 1e9
@@ -572,7 +572,7 @@ def run_b200(args):
     return 0
 
 
-SCALE_K = ("k_boxpass", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
+SCALE_K = ("k_boxpass", "k_boxpass2", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
 DETECT_K = ("k_detect_flags", "k_detect_scan", "k_detect_emit", "k_detect_emit_wide", "k_join", "k_tune")
 TRYVEL_K = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_tryvel_eval", "k_tryvel_reduce")
 

@@ -293,7 +293,7 @@ static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg
   }
   RBV_CUDA(dalloc(&c->field, B * N));
   RBV_CUDA(dalloc(&c->tgt, 2 * B * K));
-  RBV_CUDA(dalloc(&c->prod, 10 * B * K + 1024));   // + a staged chunk of slack: the chain warps copy whole chunks
+  RBV_CUDA(dalloc(&c->prod, 27 * B * K + 1024));   // + a staged chunk of slack: the chain warps copy whole chunks
   RBV_CUDA(dalloc(&c->fiabs, B * K));
   RBV_CUDA(dalloc(&c->fwd_head, B * K));
   RBV_CUDA(dalloc(&c->fwd_next, B * K));

@@ -170,18 +170,21 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-// wait on a phase: try_wait with a suspend-time hint parks the warp in hardware instead of spinning (a spinning warp
-// takes issue slots from the warps it is waiting for); the loop only re-arms after the hint expires.
+// wait on a phase by POLLING (mbarrier.test_wait). The first version parked the warp with try_wait + a suspend-time hint (SASS:
+// SYNCS.PHASECHK.TRYWAIT + NANOSLEEP.SYNCS); a parked warp comes back some hundred nanoseconds after the phase completes, and the
+// box-pass pipeline hands a chunk over four to five times (TMA -> row pass -> column pass -> producer) with only two or three chunks
+// in flight, so those wake-ups were the kernel: every stage of k_boxpass2 idle most of the time (ncu: 70 % of all samples in
+// barrier / sleep). The polling warps are few (producer lane, row warps, one column warp) and issue a test every ~20 cycles.
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
   const unsigned a = smem_u32(bar);
   long long t0 = 0;
   for (int spin = 0;; ++spin) {
     unsigned ok;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"(a), "r"(parity), "r"(0x989680u) : "memory");
+    asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
     if (ok) return;
-    if ((spin & 255) == 0) {
-      if (spin == 0) t0 = clock64();
+    if ((spin & 4095) == 4095) {
+      if (t0 == 0) t0 = clock64();
       else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
     }
   }
@@ -1247,11 +1250,14 @@ int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float*
 struct FitResult {
   float th0, th1, xs, ys;
 };
+template <bool PN_DONE = false>
 __device__ __forceinline__ bool rbv_fit_plane(const float* y, const DevParams& P, float gradient_threshold_squared, FitResult& o) {
-  int pn = 0;
+  if (!PN_DONE) {
+    int pn = 0;
 #pragma unroll
-  for (int k = 0; k < 25; ++k) pn = (y[k] > 0.0f) ? pn + 1 : pn - 1;                   // :92
-  if (fabs((double)pn) > (double)P.pn_threshold) return false;                         // :96
+    for (int k = 0; k < 25; ++k) pn = (y[k] > 0.0f) ? pn + 1 : pn - 1;                 // :92
+    if (fabs((double)pn) > (double)P.pn_threshold) return false;                       // :96
+  }
   float th[3];
 #pragma unroll
   for (int a = 0; a < 3; ++a) {                                                        // :98 sequential dot from 0
@@ -1271,20 +1277,18 @@ __device__ __forceinline__ bool rbv_fit_plane(const float* y, const DevParams& P
 
 // Pass 1: flags. Block = 256 threads, tile = 16 rows x 64 columns (+2 halo). DoG = s1 - s0 is formed in shared memory (never
 // written to HBM), the squared gradient magnitude comes from the s0 tile.
-// Phase A: every pixel takes the magnitude test (:83) and a CHEAP CERTAIN-REJECT test of the plane fit: theta is estimated
-// from separable 5-tap column sums shared between neighbouring pixels (about 20 flops instead of 150) together with a
-// rigorous bound e on |theta_estimate - theta_reference|, and the pixel is dropped only if the sub-pixel test (:103) or the
-// gradient test (:107) fails for EVERY theta within that bound. Roughly half of all pixels pass the magnitude test but
-// only ~5 % survive this; the survivors are compacted into a shared-memory list.
-// Phase B: the threads work through the list densely and run the reference's own arithmetic (25-tap sign count :85-96,
-// sequential dot products :98, tests :99-107), so what is accepted, and every accepted value, is bit-exact.
+// Phase A: every pixel takes the two CHEAP tests of the reference exactly: the magnitude test (:83) and the 25-tap sign count
+// (:85-96, |pos - neg| <= 10), the latter from per-column counts of positive DoG values over the window's 5 rows (one small
+// integer per tile position, shared by the 5 windows that contain the column). Both are exact, so there is no error bound to
+// argue about; the sign count alone rejects ~80 % of all pixels (a window passes only where the zero crossing runs through it),
+// the two together ~83 %. The survivors are compacted into a shared-memory list.
+// Phase B: the threads work through the list densely and run the reference's own arithmetic (sequential dot products :98,
+// tests :99-107), so what is accepted, and every accepted value, is bit-exact.
+// (Round 1 filtered with a float estimate of the plane fit and a rigorous error bound: ~150 instructions per pixel in
+// phase A because a warp runs the estimate when any of its lanes needs it, and three more shared planes to build. ncu, 64
+// lanes x 752x480: 273 thread instructions per pixel, issue-bound at 82 %.)
 // Accepted pixels set their bit in the per-row flag words and park (theta0, theta1, xs, ys) in the fit buffer for the emit
 // pass. Also resets the id mask.
-//
-// Error bound: theta_a = sum_k pinv[a][k] * y[k], |pinv| <= 0.04 (2/50 resp. 1/25), 25 terms. Sequential float32 evaluation
-// errs by at most (25 + 1) * 2^-24 * sum|pinv_k y_k| <= 6.2e-8 * S with S = sum_k |y[k]|; the separable estimate obeys the
-// same bound, so the two differ by <= 1.3e-7 * S. The kernel uses e = 4e-7 * S and a further 1e-4 relative slack on the
-// compared products, which also covers the roundings of tmp = theta2 / n2 and xs = -theta0 * tmp in the reference.
 #define DT_W 64
 #define DT_H 16
 #define DT_PITCH (DT_W + 5)
@@ -1293,9 +1297,7 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
                                                       float4* __restrict__ fit, const __grid_constant__ DevParams P, int wpr) {
   __shared__ float s0t[DT_H + 4][DT_PITCH];
   __shared__ float dogt[DT_H + 4][DT_PITCH];
-  __shared__ float colV[DT_H][DT_PITCH];   // sum_dr y            (column sums over the 5 window rows)
-  __shared__ float colM[DT_H][DT_PITCH];   // sum_dr dr * y
-  __shared__ float colW[DT_H][DT_PITCH];   // sum_dr |y|
+  __shared__ unsigned char colP[DT_H][DT_PITCH + 3];   // positives among the 5 window rows of a column (0..5)
   __shared__ unsigned short cand[DT_W * DT_H];
   __shared__ unsigned sflags[DT_H][2];
   __shared__ int ncand;
@@ -1356,9 +1358,7 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
   for (int i = tid; i < DT_H * (DT_W + 4); i += 256) {
     const int vr = i / (DT_W + 4), vc = i % (DT_W + 4);
     const float y0 = dogt[vr][vc], y1 = dogt[vr + 1][vc], y2 = dogt[vr + 2][vc], y3 = dogt[vr + 3][vc], y4 = dogt[vr + 4][vc];
-    colV[vr][vc] = (y0 + y1) + (y2 + (y3 + y4));
-    colM[vr][vc] = 2.0f * (y4 - y0) + (y3 - y1);
-    colW[vr][vc] = (fabsf(y0) + fabsf(y1)) + (fabsf(y2) + (fabsf(y3) + fabsf(y4)));
+    colP[vr][vc] = (unsigned char)((y0 > 0.0f) + (y1 > 0.0f) + (y2 > 0.0f) + (y3 > 0.0f) + (y4 > 0.0f));   // :92, NaN counts as negative
   }
   __syncthreads();
   const float thr = thr_dev[b];
@@ -1380,18 +1380,9 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
         const float dy = s0t[tr + 1][tc] - s0t[tr - 1][tc];
         const float mag = dx * dx + dy * dy;                                           // scale_space.cpp:228-230
         c = !(mag < mag_threshold);                                                    // :83
-        if (c) {   // certain-reject test on the estimated plane
-          const float v0 = colV[pr][pc], v1 = colV[pr][pc + 1], v2 = colV[pr][pc + 2], v3 = colV[pr][pc + 3], v4 = colV[pr][pc + 4];
-          const float ea = fabsf(0.02f * (2.0f * (v4 - v0) + (v3 - v1)));              // |theta0| estimate
-          const float ec = fabsf(0.04f * ((v0 + v1) + (v2 + (v3 + v4))));              // |theta2|
-          const float eb = fabsf(0.02f * ((colM[pr][pc] + colM[pr][pc + 1]) + (colM[pr][pc + 2] + (colM[pr][pc + 3] + colM[pr][pc + 4]))));
-          const float e = 4e-7f * ((colW[pr][pc] + colW[pr][pc + 1]) + (colW[pr][pc + 2] + (colW[pr][pc + 3] + colW[pr][pc + 4])));
-          const float ua = ea + e, ub = eb + e;
-          const float la = fmaxf(ea - e, 0.0f), lb = fmaxf(eb - e, 0.0f), lc = fmaxf(ec - e, 0.0f);
-          const float n2_ub = (ua * ua + ub * ub) * 1.0001f;
-          // every comparison below is false for NaN / Inf input, which then goes to the exact path
-          if (n2_ub < gts) c = false;                                                  // :107 certainly fails
-          else if (la * lc > 0.5f * n2_ub || lb * lc > 0.5f * n2_ub) c = false;        // :103 certainly fails
+        if (c) {   // sign count of the 5x5 DoG window, edge_detector.cpp:85-96: pn = positives - negatives
+          const int pos = (int)colP[pr][pc] + (int)colP[pr][pc + 1] + (int)colP[pr][pc + 2] + (int)colP[pr][pc + 3] + (int)colP[pr][pc + 4];
+          c = !((float)abs(2 * pos - 25) > P.pn_threshold);                            // :96 (small integers: exact in float32 as in double)
         }
       }
     }
@@ -1412,7 +1403,7 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
 #pragma unroll
       for (int dc = 0; dc < 5; ++dc) y[dr * 5 + dc] = dogt[pr + dr][pc + dc];
     FitResult fr;
-    if (rbv_fit_plane(y, P, gts, fr)) {
+    if (rbv_fit_plane<true>(y, P, gts, fr)) {
       atomicOr(&sflags[pr][pc >> 5], 1u << (pc & 31));
       fit[(size_t)b * N + (size_t)(r0 + pr) * cols + (c0 + pc)] = make_float4(fr.th0, fr.th1, fr.xs, fr.ys);
     }

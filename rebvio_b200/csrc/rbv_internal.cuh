@@ -119,7 +119,7 @@ struct rbv_ctx {
   unsigned* field;  // [B][N]
   float4* tgt;      // [B][kmax][2] packed target keylines of the distance-field map (k_pack_targets)
   rbv_map* field_map;
-  float* prod;      // [10][B][kmax] (+ a chunk of slack) ORDERED mode: tryVel factor rows (jx, jy, jz, f) / the 7 extRotVel rows per keyline
+  float* prod;      // [27][B][kmax] (+ a chunk of slack) ORDERED mode: the 10 float32 addends of tryVel / the 27 of extRotVel per keyline
   unsigned* ord_flags;  // [2][B][nblk] "block's rows are written" flags of the ORDERED chain warps (tryVel | extRotVel), cleared by the consumer
   float* fiabs;     // [B][kmax]
   int* fwd_head;    // [B][kmax]

@@ -54,14 +54,15 @@ __global__ void __launch_bounds__(128) k_field_build(KeylineSoA K, const int* __
 #define FB_TPB 512
 #define FB_G 8        // candidates per work item
 #define FB_MAXI 12    // work items per keyline at most (search range <= 46)
-__global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ threshold,
-                                                       unsigned* __restrict__ field, const __grid_constant__ DevParams P, int band_rows) {
+__global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict__ tgt, const float2* __restrict__ pos, const int* __restrict__ count,
+                                                       const float* __restrict__ threshold, unsigned* __restrict__ field,
+                                                       const __grid_constant__ DevParams P, int band_rows) {
   extern __shared__ __align__(16) unsigned fb_cell[];
   __shared__ int s_lo, s_hi;
+  // per warp: the 32 keylines of its current round (unit normal, position, r-interval) and their work items
   __shared__ float s_ux[FB_TPB], s_uy[FB_TPB], s_px[FB_TPB], s_py[FB_TPB];
   __shared__ int s_ral[FB_TPB];                         // r-interval of the keyline: start (low 16 bits, signed) | length << 16
-  __shared__ unsigned short s_item[FB_TPB * FB_MAXI];   // work item -> keyline of the round (low 9 bits) | item of that keyline << 9
-  __shared__ int s_wsum[FB_TPB / 32];
+  __shared__ unsigned short s_item[FB_TPB * FB_MAXI];   // work item -> keyline of the warp's round (low 5 bits) | item of that keyline << 5
   const int b = blockIdx.y, t = threadIdx.x;
   const int rows = P.rows, cols = P.cols;
   const int r0 = blockIdx.x * band_rows, r1 = min(r0 + band_rows, rows);
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
     for (int i0 = t; i0 < n; i0 += 4 * FB_TPB) {
       float y[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) y[u] = (i0 + u * FB_TPB < n) ? K.pos[base + i0 + u * FB_TPB].y : -1e30f;
+      for (int u = 0; u < 4; ++u) y[u] = (i0 + u * FB_TPB < n) ? pos[base + i0 + u * FB_TPB].y : -1e30f;
 #pragma unroll
       for (int u = 0; u < 4; ++u)
         if (y[u] >= ylo && y[u] <= yhi) { lo = min(lo, i0 + u * FB_TPB); hi = max(hi, i0 + u * FB_TPB + 1); }
@@ -102,36 +103,39 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
   const int lo = s_lo, hi = s_hi;
   const float thr = threshold[b];
   const float r0f = (float)r0, r1f = (float)r1;
-  // Rounds of FB_TPB keylines. Phase 1 (thread = keyline): unit normal and the r-interval that can land in the band.
-  // Phase 2 (thread = work item of FB_G consecutive r of one keyline): the intervals differ a lot in length (1 .. 80,
-  // by slope and by distance to the band), so they are cut into equal items and dealt out densely instead of leaving
-  // a warp waiting for its longest line.
-  const int lane = t & 31, warp = t >> 5;
-  for (int k0 = lo; k0 < hi; k0 += FB_TPB) {
-    const int idx = k0 + t;
+  // Every WARP works through rounds of 32 keylines on its own (no block barrier inside the loop: a warp that waits for its
+  // keyline loads or its divisions does not hold the other 15 up - the block-wide rounds of the first version spent a third of
+  // the kernel in barriers and load stalls). Phase 1 (lane = keyline): the unit normal - divided once per keyline by
+  // k_pack_targets, the same float32 division - and the r-interval that can land in the band. Phase 2 (lane = work item of FB_G
+  // consecutive r of one keyline): the intervals differ a lot in length (1 .. 80, by slope and by distance to the band), so they
+  // are cut into equal items and dealt out densely over the warp's lanes.
+  const int lane = t & 31, warp = t >> 5, wb = warp * 32;
+  unsigned short* w_item = s_item + wb * FB_MAXI;
+  for (int k0 = lo + wb; k0 < hi; k0 += FB_TPB) {
+    const int idx = k0 + lane;
     int ra = 0, len = 0;
     float ux = 0.0f, uy = 0.0f;
     float2 p = make_float2(0.0f, 0.0f);
     if (idx < hi) {
-      const size_t o = base + idx;
-      p = K.pos[o];
-      const float gn = K.gnorm[o];                                                       // (the three loads go out together)
-      const float2 g = K.grad[o];
+      const float4 t0 = tgt[2 * (base + idx)], t1 = tgt[2 * (base + idx) + 1];           // (g.x, g.y, pos.x, pos.y), (g.x / |g|, g.y / |g|, |g|, -)
+      p = make_float2(t0.z, t0.w);
+      const float gn = t1.z;
       if (p.y >= ylo && p.y <= yhi && !(thr > 0.0f && gn < thr)) {                     // core.hpp:47
-        ux = g.x / gn; uy = g.y / gn;
+        ux = t1.x; uy = t1.y;
         int rb = rb0;
         ra = ra0;
-        if (fabsf(uy) > 1e-2f) {   // rows hit are monotone in r: clip to the r-interval that can land in [r0, r1) (+-1 margin, re-tested below)
-          const float t0 = (r0f - 0.5f - p.y) / uy, t1 = (r1f - 0.5f - p.y) / uy;
-          ra = max(ra, __float2int_rd(fminf(t0, t1)) - 1);
-          rb = min(rb, __float2int_ru(fmaxf(t0, t1)) + 1);
+        if (fabsf(uy) > 1e-2f) {   // rows hit are monotone in r: clip to the r-interval that can land in [r0, r1) (+-1 margin, re-tested below;
+          const float iuy = __fdividef(1.0f, uy);   // an approximate reciprocal moves the bounds by < 1e-2, far inside the margin)
+          const float t0c = (r0f - 0.5f - p.y) * iuy, t1c = (r1f - 0.5f - p.y) * iuy;
+          ra = max(ra, __float2int_rd(fminf(t0c, t1c)) - 1);
+          rb = min(rb, __float2int_ru(fmaxf(t0c, t1c)) + 1);
         }
         len = max(rb - ra + 1, 0);
         if (!(fabsf(ux) <= 2.0f && fabsf(uy) <= 2.0f)) len = 0;   // non-finite normal: the reference's getIndex yields -1 for every r
       }
     }
     s_ux[t] = ux; s_uy[t] = uy; s_px[t] = p.x; s_py[t] = p.y; s_ral[t] = (ra & 0xFFFF) | (len << 16);
-    // exclusive scan of the item counts, then every keyline lists its items in the item table
+    // exclusive scan of the item counts over the warp, then every keyline lists its items in the warp's item table
     const int items = min((len + FB_G - 1) / FB_G, FB_MAXI);
     int inc = items;
 #pragma unroll
@@ -139,31 +143,19 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
       const int v = __shfl_up_sync(0xFFFFFFFFu, inc, off);
       if (lane >= off) inc += v;
     }
-    if (lane == 31) s_wsum[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      int w = (lane < FB_TPB / 32) ? s_wsum[lane] : 0;
-#pragma unroll
-      for (int off = 1; off < 32; off <<= 1) {
-        const int v = __shfl_up_sync(0xFFFFFFFFu, w, off);
-        if (lane >= off) w += v;
-      }
-      if (lane < FB_TPB / 32) s_wsum[lane] = w;   // inclusive warp totals
-    }
-    __syncthreads();
-    const int first = inc - items + (warp ? s_wsum[warp - 1] : 0);
-    const int total = s_wsum[FB_TPB / 32 - 1];
-    for (int i = 0; i < items; ++i) s_item[first + i] = (unsigned short)(t | (i << 9));
-    __syncthreads();
-    for (int j = t; j < total; j += FB_TPB) {
-      const int it = s_item[j];
-      const int ks = it & 511;
+    const int first = inc - items;
+    const int total = __shfl_sync(0xFFFFFFFFu, inc, 31);
+    for (int i = 0; i < items; ++i) w_item[first + i] = (unsigned short)(lane | (i << 5));
+    __syncwarp();
+    for (int j = lane; j < total; j += 32) {
+      const int it = w_item[j];
+      const int ks = wb + (it & 31);
       const int ral = s_ral[ks];
       const int kra = (int)(short)(ral & 0xFFFF);
-      const int rs = kra + (it >> 9) * FB_G;
+      const int rs = kra + (it >> 5) * FB_G;
       const int re = kra + (ral >> 16);
       const float kux = s_ux[ks], kuy = s_uy[ks], kpx = s_px[ks], kpy = s_py[ks];
-      const unsigned lowkey = 0xFFFFFFu - (unsigned)(k0 + ks);
+      const unsigned lowkey = 0xFFFFFFu - (unsigned)(k0 + (it & 31));
       // The FB_G candidates of the item as straight-line predicated code: FB_G independent address chains, then FB_G
       // loads, then the (few) atomics. A loop with early `continue`s made every warp crawl through one dependent chain
       // with a branch bubble every few instructions (measured ~12 cycles per issued instruction).
@@ -202,8 +194,9 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(KeylineSoA K, const int* 
                      "  setp.gt.u32 q, %2, %1;\n"
                      "  @q red.shared.min.u32 [%0], %1; }" ::"r"(addr[u]), "r"(key[u]), "r"(cur[u]) : "memory");
     }
-    __syncthreads();
+    __syncwarp();   // the warp's tables are rewritten by its next round
   }
+  __syncthreads();
   unsigned* dst = field + (size_t)b * P.npix + (size_t)r0 * cols;
   if ((cols & 3) == 0) {
     const uint4* s4 = reinterpret_cast<const uint4*>(fb_cell);
@@ -239,7 +232,7 @@ __global__ void k_pack_targets(KeylineSoA K, const int* __restrict__ count, floa
   const float2 g = K.grad[o], p = K.pos[o];
   const float gn = K.gnorm[o];
   tgt[2 * o] = make_float4(g.x, g.y, p.x, p.y);
-  tgt[2 * o + 1] = make_float4(g.x / gn, g.y / gn, 0.0f, 0.0f);                          // core.cpp:64-65
+  tgt[2 * o + 1] = make_float4(g.x / gn, g.y / gn, gn, 0.0f);                            // core.cpp:64-65 (and |g| for k_field_band)
 }
 
 int tr_pack_targets(rbv_ctx* c, rbv_map* map) {
@@ -260,14 +253,14 @@ int tr_build_field(rbv_ctx* c, rbv_map* map) {
   const DevParams& P = c->P;
   const int H = field_band_rows(c);
   const bool band = (c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 8)) && P.field_nr <= FB_G * FB_MAXI;
+  { int rc = tr_pack_targets(c, map); if (rc != RBV_OK) return rc; }   // first: the band kernel reads the packed records (unit normals divided once)
   if (band && H >= 1) {
     const size_t smem = (size_t)H * P.cols * 4;
-    RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, map->k, map->count, map->threshold, c->field, P, H);
+    RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, c->tgt, map->k.pos, map->count, map->threshold, c->field, P, H);
   } else {
     { int rc = rbv_fill32(c, c->field, RBV_FIELD_EMPTY, (size_t)P.lanes * P.npix); if (rc != RBV_OK) return rc; }
     RBV_LAUNCH(c, k_field_build, (dim3((P.keylines_max + 127) / 128, P.lanes)), (128), 0, map->k, map->count, map->threshold, c->field, P);
   }
-  { int rc = tr_pack_targets(c, map); if (rc != RBV_OK) return rc; }
   c->field_map = map;
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
@@ -782,9 +775,9 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
   }
 }
 
-// ORD = RBV_REDUCE_ORDERED: instead of FP64 partial sums the block leaves (jx, jy, jz, f) of every keyline in four planes
-// (`rows`, zeros for skipped keylines: x + 0 == x exactly) and raises its flag; the lane's chain warp (ordered_chain, below)
-// forms the ten products and adds them in keyline order.
+// ORD = RBV_REDUCE_ORDERED: instead of FP64 partial sums the block leaves the ten float32 addends of every keyline in ten planes
+// (`rows`, zeros where the reference adds nothing: x + 0 == x exactly) and raises its flag; the lane's chain warp (ordered_chain,
+// below) adds them in keyline order.
 template <int KPT, bool ORD>
 __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
                                                          const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
@@ -857,16 +850,19 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
       else { t0[k] = make_float4(0.f, 0.f, 0.f, 0.f); t1[k] = t0[k]; }
     }
     int fwd[KPT];
-    float ojx[KPT], ojy[KPT], ojz[KPT], of[KPT];   // ORD: what the chain warp multiplies
+    float oadd[ORD ? 10 : 1][KPT];   // ORD: the ten float32 addends of every keyline (zeros where the reference adds nothing: x + 0 == x)
 #pragma unroll
     for (int k = 0; k < KPT; ++k) {
       fwd[k] = -1;
-      ojx[k] = ojy[k] = ojz[k] = of[k] = 0.0f;
+      if constexpr (ORD) {
+#pragma unroll
+        for (int a = 0; a < 10; ++a) oadd[a][k] = 0.0f;
+      }
       if (skip[k]) continue;
       float add[10];
       if (penalty[k]) {
         const float f = (float)((1.0 / (double)srho[k]) * (double)P.search_range * (double)w[k]);   // :99 / :115
-        if constexpr (ORD) of[k] = f;
+        if constexpr (ORD) oadd[0][k] = f * f;
         else acc[0] += (double)(f * f);
         continue;
       }
@@ -891,22 +887,21 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
       const float jx = rho_p[k] * P.fm * dfx * w[k];                                   // :126-128
       const float jy = rho_p[k] * P.fm * dfy * w[k];
       const float jz = -rho_p[k] * (px[k] * dfx + py[k] * dfy) * w[k];
-      if constexpr (ORD) {
-        ojx[k] = jx; ojy[k] = jy; ojz[k] = jz; of[k] = f;
-      } else {
-        add[0] = f * f;
-        add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
-        add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
-        add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
+      add[0] = f * f;
+      add[1] = jx * jx; add[2] = jy * jy; add[3] = jz * jz;
+      add[4] = jx * jy; add[5] = jx * jz; add[6] = jy * jz;
+      add[7] = jx * f; add[8] = jy * f; add[9] = jz * f;
 #pragma unroll
-        for (int a = 0; a < 10; ++a) acc[a] += (double)add[a];
+      for (int a = 0; a < 10; ++a) {
+        if constexpr (ORD) oadd[a][k] = add[a];
+        else acc[a] += (double)add[a];
       }
     }
     tv_st<KPT, int>(Ko.match_fwd + o, fwd, nvalid);                                    // core.cpp:87
     if constexpr (ORD) {
       const size_t ps = (size_t)P.lanes * P.kmax;
-      tv_st<KPT, float>(rows + o, ojx, nvalid); tv_st<KPT, float>(rows + ps + o, ojy, nvalid);
-      tv_st<KPT, float>(rows + 2 * ps + o, ojz, nvalid); tv_st<KPT, float>(rows + 3 * ps + o, of, nvalid);
+#pragma unroll
+      for (int a = 0; a < 10; ++a) tv_st<KPT, float>(rows + a * ps + o, oadd[a], nvalid);
     }
   }
   // carried |fi| in keyline order: thread aggregate = its last matched keyline, inclusive scan over the threads of the warp
@@ -1016,8 +1011,8 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 // by the chain warp as it consumes them. The chain (13 k keylines ~ 27 us) hides behind the evaluation of the other lanes.
 #define ORD_NST 4
 #define ORD_PAD 4             // floats behind a staged row: row r of a chunk starts at bank 4 r, so LDS.128 of different rows never collide
-#define TV_CH 512             // keylines per staged chunk: tryVel (4 rows) / extRotVel (7 rows). The per-chunk work (flag test, cp.async issue,
-#define ER_CH 256             // wait, two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
+#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (flag test, cp.async issue,
+#define ER_CH 128             // wait, two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
 // Chain warps per reducer CTA (rw, a launch parameter; RBV_TUNE_ORD_RW). A chain warp pulls two factors per accumulator and keyline out of
 // shared memory: with 8 of them on one SM the shared-memory pipe, not the 4-cycle FADD, set the pace (measured: tryVel 167 us per call
 // against 108 us with 1 or 2). So the chains are spread over many SMs - few warps per reducer CTA, the CTA's other warps exit at once -
@@ -1035,17 +1030,9 @@ __device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
-// 16 keylines: float products (off the chain), then the float adds in keyline order
-__device__ __forceinline__ void ord_add16(float& s, const float4* x, const float4* y) {
-  float p[16];
-#pragma unroll
-  for (int g = 0; g < 4; ++g) { p[4 * g] = x[g].x * y[g].x; p[4 * g + 1] = x[g].y * y[g].y; p[4 * g + 2] = x[g].z * y[g].z; p[4 * g + 3] = x[g].w * y[g].w; }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) s += p[k];
-}
 template <int NROWS, int CH>
 __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, int kpb,
-                                               unsigned* flags_lane, int pa, int pb, float* ring, int nacc) {
+                                               unsigned* flags_lane, float* ring) {
   constexpr int RS = CH + ORD_PAD;
   const int lane = threadIdx.x & 31;
   const int nch = (n + CH - 1) / CH;
@@ -1081,39 +1068,26 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     const int cnt = min(CH, n - c * CH);
-    if (lane < nacc) {   // only the accumulator lanes touch shared memory: a warp-wide LDS.128 costs a wavefront per quarter warp that has an active lane
-      const float* st = ring + (size_t)(c % ORD_NST) * NROWS * RS;
-      const float4* ra = reinterpret_cast<const float4*>(st + pa * RS);
-      const float4* rb = reinterpret_cast<const float4*>(st + pb * RS);
-      // blocks of 16 keylines, the next block's factors fetched while the current one is added (two register sets, swapped by unrolling)
-      const int nb16 = cnt >> 4;
-      float4 xa[4], ya[4], xb[4], yb[4];
-      if (nb16 > 0) {
-#pragma unroll
-        for (int g = 0; g < 4; ++g) { xa[g] = ra[g]; ya[g] = rb[g]; }
+    if (lane < NROWS) {   // lane a adds accumulator a: nothing but the load and the dependent FADD on this warp (the FP32 pipe takes a
+      // 3-register instruction every 2 cycles per scheduler, so one FMUL per keyline next to the FADD already makes the 4-cycle chain slip:
+      // measured 8 cycles per keyline with the products formed here)
+      const float4* ra = reinterpret_cast<const float4*>(ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS);
+      const int n16 = cnt >> 4;
+      float4 a0, a1, a2, a3;
+      if (n16 > 0) { a0 = ra[0]; a1 = ra[1]; a2 = ra[2]; a3 = ra[3]; }
+      for (int b16 = 0; b16 < n16; ++b16) {
+        float4 b0 = a0, b1 = a1, b2 = a2, b3 = a3;
+        if (b16 + 1 < n16) { a0 = ra[4 * b16 + 4]; a1 = ra[4 * b16 + 5]; a2 = ra[4 * b16 + 6]; a3 = ra[4 * b16 + 7]; }   // next block's addends first
+        s += b0.x; s += b0.y; s += b0.z; s += b0.w; s += b1.x; s += b1.y; s += b1.z; s += b1.w;                       // float32 adds in keyline order
+        s += b2.x; s += b2.y; s += b2.z; s += b2.w; s += b3.x; s += b3.y; s += b3.z; s += b3.w;
       }
-      int b16 = 0;
-      for (; b16 + 2 <= nb16; b16 += 2) {
-#pragma unroll
-        for (int g = 0; g < 4; ++g) { xb[g] = ra[4 * (b16 + 1) + g]; yb[g] = rb[4 * (b16 + 1) + g]; }
-        ord_add16(s, xa, ya);
-        if (b16 + 2 < nb16) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) { xa[g] = ra[4 * (b16 + 2) + g]; ya[g] = rb[4 * (b16 + 2) + g]; }
-        }
-        ord_add16(s, xb, yb);
-      }
-      if (b16 < nb16) { ord_add16(s, xa, ya); ++b16; }
-      for (int i = b16 * 16; i < cnt; ++i) s += st[pa * RS + i] * st[pb * RS + i];
+      const float* rt = reinterpret_cast<const float*>(ra);
+      for (int i = n16 * 16; i < cnt; ++i) s += rt[i];
     }
     __syncwarp();   // every lane is done with the slot before a later cp.async refills it
   }
   return s;
 }
-
-// tryVel accumulators 0..9 (score | JtJ 00 11 22 01 02 12 | JtF 0 1 2) as products of rows (jx, jy, jz, f) = (0, 1, 2, 3)
-__constant__ signed char c_tv_pa[10] = {3, 0, 1, 2, 0, 0, 1, 0, 1, 2};
-__constant__ signed char c_tv_pb[10] = {3, 0, 1, 2, 1, 2, 2, 3, 3, 3};
 
 template <int KPT>
 __device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,
@@ -1128,9 +1102,8 @@ __device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __re
     const int b = blockIdx.x * rw + warp;
     if (warp >= rw || b >= P.lanes) return;
     const int n = count_o[b];
-    const int pa = lane < 10 ? c_tv_pa[lane] : 0, pb = lane < 10 ? c_tv_pb[lane] : 0;
-    const float s = ordered_chain<4, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk, pa, pb,
-                                            ord_ring + (size_t)warp * ORD_NST * 4 * (TV_CH + ORD_PAD), 10);
+    const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk,
+                                             ord_ring + (size_t)warp * ORD_NST * 10 * (TV_CH + ORD_PAD));
     float r[10];
 #pragma unroll
     for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1207,7 +1180,7 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
       int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : TV_RW_DEFAULT;
       rw = rw > TV_RW_MAX ? TV_RW_MAX : rw;
       const int nred = (P.lanes + rw - 1) / rw;
-      const size_t smem = sizeof(float) * rw * ORD_NST * 4 * (TV_CH + ORD_PAD);
+      const size_t smem = sizeof(float) * rw * ORD_NST * 10 * (TV_CH + ORD_PAD);
       if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
       else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
     }
@@ -1640,8 +1613,8 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
   if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
-// RBV_REDUCE_ORDERED: rows Phi_j (6) and Y_j of every keyline to seven planes (zeros for unmatched keylines), one flag per block;
-// the lane's chain warp adds the 27 products Phi^T Phi / Phi^T Y in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
+// RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline to 27 planes (zeros for unmatched keylines), one
+// flag per block; the lane's chain warp adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
 __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
                                                        float* __restrict__ rows, unsigned* __restrict__ flags, int nblk, int nred, int rw,
                                                        float* lane_out, const __grid_constant__ DevParams P) {
@@ -1653,9 +1626,8 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
   if ((int)blockIdx.x < nred) {
     const int b = blockIdx.x * rw + warp;
     if (warp >= rw || b >= P.lanes) return;
-    const int pa = lane < 27 ? c_pair_a[lane] : 0, pb = lane < 27 ? c_pair_b[lane] : 0;
-    const float s = ordered_chain<7, ER_CH>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk, pa, pb,
-                                            ord_ring + (size_t)warp * ORD_NST * 7 * (ER_CH + ORD_PAD), 27);
+    const float s = ordered_chain<27, ER_CH>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk,
+                                             ord_ring + (size_t)warp * ORD_NST * 27 * (ER_CH + ORD_PAD));
     if (lane < 27) s_res[warp][lane] = (double)s;
     __syncwarp();
     extrot_finish_warp(s_res[warp], lane_out + (size_t)b * OUT_STRIDE, s_sys[warp]);
@@ -1677,10 +1649,15 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
     const int idx = (blk * ER_KPT + j) * TV_TPB + t;
     if (idx >= n) continue;
     float r[7];
-    extrot_row_in(in[j], v0, v1, v2, P, r);         // zeros for an unmatched keyline: x + 0 * 0 == x
+    extrot_row_in(in[j], v0, v1, v2, P, r);         // zeros for an unmatched keyline: x + 0 == x
     const size_t o = (size_t)b * P.kmax + idx;
+    int k = 0;                                      // the 27 float32 products of Phi^T Phi (upper triangle, row-major) and Phi^T Y, operators.hh:200-208
 #pragma unroll
-    for (int a = 0; a < 7; ++a) rows[a * ps + o] = r[a];
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+      for (int q = a; q < 6; ++q) rows[(size_t)(k++) * ps + o] = r[a] * r[q];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) rows[(size_t)(21 + a) * ps + o] = r[a] * r[6];
   }
   __threadfence();
   __syncthreads();
@@ -1699,7 +1676,7 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     rw = rw > ER_RW_MAX ? ER_RW_MAX : rw;
     const int nred = (P.lanes + rw - 1) / rw;
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
-    const size_t smem = sizeof(float) * rw * ORD_NST * 7 * (ER_CH + ORD_PAD);
+    const size_t smem = sizeof(float) * rw * ORD_NST * 27 * (ER_CH + ORD_PAD);
     RBV_LAUNCH(c, k_extrot_ord, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod,
                c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, rw, c->lane_out, P);
   } else {
@@ -1956,8 +1933,8 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 }
 
 int tr_init_ordered(void) {
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * (TV_CH + ORD_PAD))));
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 4 * (TV_CH + ORD_PAD))));
-  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 7 * (ER_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 10 * (TV_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 10 * (TV_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 27 * (ER_CH + ORD_PAD))));
   return RBV_OK;
 }

@@ -30,6 +30,7 @@ def kernel_bytes(name, N, K, B, planes=1, P=20.0, words=0):
         "k_field_build": 340.0 * K,          # 20 B keyline read + 80 candidates x 4 B
         "k_field_band": 4.0 * N + 340.0 * K,  # same + the field reset/write it absorbs (4 N)
         "k_boxpass": 8.0 * N * planes,       # one whole box pass: read N + write N per plane
+        "k_boxpass2": 8.0 * N * planes,
         "k_pack_targets": 52.0 * K,          # 20 B read + 32 B packed write
         "k_rotate": 48.0 * K,
         "k_quantile": 4.0 * K,
