@@ -68,6 +68,13 @@ def parse():
     return ap.parse_args()
 
 
+def trace(msg):
+    """progress on stderr with BENCH_TRACE=1 (a hung GPU call otherwise leaves nothing behind)"""
+    if os.environ.get("BENCH_TRACE"):
+        sys.stderr.write(f"[bench {time.strftime('%H:%M:%S')}] {msg}\n")
+        sys.stderr.flush()
+
+
 def cfg_structs(spec):
     from rebvio_b200 import capi
     cam, det, mapc, core = capi.defaults()
@@ -360,6 +367,7 @@ def run_b200(args):
             pipe.push(device_ptr=ptr(t))
         t = first
         table = None
+        trace(f"device leg reduce={reduce_mode}: {first} detect-only pushes done")
         if profile:   # one step with every kernel bracketed by CUDA events, in order on one stream: finds the dominant kernel (`alone`)
             pipe.ctx.sync()
             pipe.ctx.profile_reset(); pipe.ctx.profile_set(-2)
@@ -367,8 +375,11 @@ def run_b200(args):
             pipe.ctx.sync()
             table = pipe.ctx.profile_read()
             pipe.ctx.profile_set(-1)
+        trace("profiled step done")
         for _ in range(W):
             out = pipe.push(device_ptr=ptr(t), **pargs(t)); t += 1
+        pipe.ctx.sync()
+        trace("warm-up done")
         kl_sum = match_sum = 0.0
         win_ms, launches = [], 0
         sampler = ClockSampler(local, sampler_core); sampler.start()
@@ -385,6 +396,7 @@ def run_b200(args):
             barrier()
             win_ms.append(max_over_ranks(ev0.elapsed_time(ev1)))
             launches = pipe.ctx.launch_count() - l0
+            trace(f"window {w}: {win_ms[-1]:.2f} ms")
         clocks = sampler.result()
         res = {"win_ms": win_ms, "ms": float(np.median(win_ms)), "clocks": clocks, "launches": int(launches),
                "K_mean": kl_sum / (B * K * windows), "matches": match_sum / (B * K * windows),
@@ -485,6 +497,7 @@ def run_b200(args):
     # uint8 camera frames in pinned host memory -> rbv_detect_u8 (upload + x3 conversion on the device, rebvio.cpp:43)
     # -> tracker; the upload of frame k+1 is started after the front end of frame k (rbv_prefetch_frames) so that it
     # overlaps the tracker, like the reference's acquisition thread overlaps its estimation thread.
+    trace("device legs done")
     if not args.no_e2e:
         h_frames = torch.empty((nf, B, spec.cam.rows, spec.cam.cols), dtype=torch.uint8, pin_memory=True)
         h_frames.copy_(frames_u8)
@@ -574,7 +587,7 @@ def run_b200(args):
 
 SCALE_K = ("k_boxpass", "k_boxpass2", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
 DETECT_K = ("k_detect_flags", "k_detect_scan", "k_detect_emit", "k_detect_emit_wide", "k_join", "k_tune")
-TRYVEL_K = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_tryvel_eval", "k_tryvel_reduce")
+TRYVEL_K = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_tryvel_eval", "k_tryvel_reduce")
 
 
 def run_sweep(torch, dev, local, stream, mode, peak):

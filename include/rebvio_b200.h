@@ -37,8 +37,8 @@ extern "C" {
 
 /* reduction mode for the tracker's J^T J / J^T F sums (core.cpp:130-139,244-245)                     */
 #define RBV_REDUCE_FAST 0     /* warp-shuffle tree, FP64 accumulate, fixed order (deterministic; NOT the reference's bits) */
-#define RBV_REDUCE_ORDERED 1  /* DEFAULT: per-accumulator serial float32 adds in keyline order == CPU bits; the adding   */
-                              /* warps run next to the evaluation blocks of the same launch (rbv_tracker.cu)             */
+#define RBV_REDUCE_ORDERED 1  /* DEFAULT: per-accumulator serial float32 adds in keyline order == CPU bits (one chain warp  */
+                              /* per lane behind the evaluation kernel, rbv_tracker.cu)                                  */
 
 /* ---- POD mirrors of the reference's structs ------------------------------------------------------- */
 
@@ -169,10 +169,9 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
 #define RBV_TUNE_FIELD_ROWS 4
 #define RBV_TUNE_FE_STREAM 5
 #define RBV_TUNE_FIELD_IN_FE 7 /* with RBV_TUNE_FE_STREAM: Core::buildDistanceField of a map runs behind its detect on the front-end stream, into the map's own field */
-#define RBV_TUNE_BOX_SPLIT 6 /* fused box pass as G launches over 2B/G planes each (0, 1 = one launch) */
-#define RBV_TUNE_ORDERED 8 /* RBV_REDUCE_ORDERED: 0 = chain warps next to the evaluation (one launch), 1 = evaluation, then one adding block per lane */
-#define RBV_TUNE_ORD_RW 9 /* RBV_REDUCE_ORDERED: chain warps per reducer CTA (0 = automatic: 2 for tryVel, 1 for extRotVel) */
-#define RBV_TUNE_COUNT 10
+/* key 6 is unused (was RBV_TUNE_BOX_SPLIT, measured and rejected in round 1) */
+#define RBV_TUNE_ORDERED 8 /* RBV_REDUCE_ORDERED: 0 = evaluation kernel + chain kernel (one warp per lane, addends staged through shared memory), 1 = the first form (adding block per lane reading global memory) */
+#define RBV_TUNE_COUNT 9
 int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
 
 /* allocate / free a B-lane map (replaces std::make_shared<EdgeMap>, edge_detector.cpp:50). */

@@ -66,7 +66,7 @@ assert KEYLINE_DTYPE.itemsize == 84
 
 RBV_OK, RBV_ERR_ARG, RBV_ERR_CUDA, RBV_ERR_STATE = 0, 1, 2, 3
 REDUCE_FAST, REDUCE_ORDERED = 0, 1
-TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH, TUNE_FIELD_ROWS, TUNE_FE_STREAM, TUNE_BOX_SPLIT, TUNE_FIELD_IN_FE, TUNE_ORDERED, TUNE_ORD_RW = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9   # rbv_set_tuning keys (0 = automatic; see the header for the values)
+TUNE_FIELD, TUNE_BOX, TUNE_TRYVEL, TUNE_GRAPH, TUNE_FIELD_ROWS, TUNE_FE_STREAM, TUNE_FIELD_IN_FE, TUNE_ORDERED = 0, 1, 2, 3, 4, 5, 7, 8   # rbv_set_tuning keys (0 = automatic; see the header for the values)
 
 vp = C.c_void_p
 _SIG = {

@@ -12,6 +12,9 @@
 // The device keeps the keylines as SoA; `keylines()` / `operator[]` / `mask()` materialise the 84-byte AoS mirror lazily
 // and `commit()` pushes host-side edits back (SURVEY.md 7 "Host<->device coherence at an AoS API").
 // One context = one lane here (the reference's single stream); the batched multi-lane form is the C ABI itself.
+// Reference signatures carried as they are: EdgeDetector(Camera::SharedPtr, cfg), Core(Camera::SharedPtr, cfg), detect(types::Image&)
+// for a cv::Mat-shaped image, EdgeMap::imu(). tests/cpp/ref_signature_test.cpp compiles the tracker half of Rebvio's estimation loop
+// (rebvio.cpp:142-259) against them with the reference's own TooN vector / matrix types.
 // Errors: the reference's hot path throws nothing and reports through return values; C-ABI failures (no device, CUDA
 // error) surface as std::runtime_error carrying rbv_last_error() — there is no CPU fallback to fall through to.
 #pragma once
@@ -22,7 +25,10 @@
 #include <unordered_map>
 #include <vector>
 
+#include <mutex>
+
 #include "rebvio_b200.h"
+#include "types.hpp"
 
 namespace rebvio_b200 {
 
@@ -55,17 +61,63 @@ class Device {
  public:
   using SharedPtr = std::shared_ptr<Device>;
   Device(const Camera& cam, const rbv_detector_cfg& det, const rbv_map_cfg& map, const rbv_core_cfg& core, int device = 0,
-         int reduce_mode = RBV_REDUCE_ORDERED) {
-    rbv_camera c{cam.fm_, cam.cx_, cam.cy_, cam.rows_, cam.cols_};
-    check(rbv_create(&c, &det, &map, &core, device, 1, &ctx_), "rbv_create");
-    check(rbv_set_reduce_mode(ctx_, reduce_mode), "rbv_set_reduce_mode");
-    kmax_ = det.keylines_max;
-  }
-  ~Device() { rbv_destroy(ctx_); }
+         int reduce_mode = RBV_REDUCE_ORDERED)
+      : cam_(cam), det_(det), map_(map), core_(core), device_(device), reduce_mode_(reduce_mode) { create(); }
+  ~Device() { if (ctx_) rbv_destroy(ctx_); }
   Device(const Device&) = delete;
   Device& operator=(const Device&) = delete;
-  rbv_ctx* ctx() const { return ctx_; }
-  int keylines_max() const { return kmax_; }
+  rbv_ctx* ctx() { if (!ctx_) create(); return ctx_; }
+  int keylines_max() const { return det_.keylines_max; }
+
+  // ---- the reference's own constructor shapes: EdgeDetector(Camera::SharedPtr, cfg), Core(Camera::SharedPtr, cfg) (edge_detector.hpp:41,
+  // core.hpp:99). The reference builds the two independently (rebvio.cpp:23-26: each from its own COPY of the camera); here both must
+  // end up on one device context, created once both configurations are known. A detector constructed from a camera opens a pending
+  // Device; the next Core constructed from a camera with the same intrinsics joins it (and vice versa); the context itself is created
+  // at the first device call. Explicit sharing (the Device::SharedPtr constructors) is the unambiguous form when several pipelines
+  // of one camera model live in a process.
+  static SharedPtr forDetector(const Camera& cam, const rbv_detector_cfg& det) { return join(cam, &det, nullptr); }
+  static SharedPtr forCore(const Camera& cam, const rbv_core_cfg& core) { return join(cam, nullptr, &core); }
+  void setMapConfig(const rbv_map_cfg& m) { if (!ctx_) map_ = m; }
+
+ private:
+  Device(const Camera& cam) : cam_(cam), device_(0), reduce_mode_(RBV_REDUCE_ORDERED) {
+    rbv_default_detector_cfg(&det_); rbv_default_map_cfg(&map_); rbv_default_core_cfg(&core_);
+  }
+  void create() {
+    rbv_camera c{cam_.fm_, cam_.cx_, cam_.cy_, cam_.rows_, cam_.cols_};
+    check(rbv_create(&c, &det_, &map_, &core_, device_, 1, &ctx_), "rbv_create");
+    check(rbv_set_reduce_mode(ctx_, reduce_mode_), "rbv_set_reduce_mode");
+  }
+  static bool same(const Camera& a, const Camera& b) {
+    return a.fm_ == b.fm_ && a.cx_ == b.cx_ && a.cy_ == b.cy_ && a.rows_ == b.rows_ && a.cols_ == b.cols_;
+  }
+  static SharedPtr join(const Camera& cam, const rbv_detector_cfg* det, const rbv_core_cfg* core) {
+    static std::mutex mtx;
+    static std::vector<std::weak_ptr<Device>> pending;
+    std::lock_guard<std::mutex> lk(mtx);
+    for (auto it = pending.begin(); it != pending.end();) {
+      SharedPtr d = it->lock();
+      if (!d || d->ctx_) { it = pending.erase(it); continue; }
+      if (same(d->cam_, cam) && ((det && !d->has_det_) || (core && !d->has_core_))) {
+        if (det) { d->det_ = *det; d->has_det_ = true; } else { d->core_ = *core; d->has_core_ = true; }
+        if (d->has_det_ && d->has_core_) pending.erase(it);
+        return d;
+      }
+      ++it;
+    }
+    SharedPtr d(new Device(cam));
+    if (det) { d->det_ = *det; d->has_det_ = true; } else { d->core_ = *core; d->has_core_ = true; }
+    pending.push_back(d);
+    return d;
+  }
+  Camera cam_;
+  rbv_detector_cfg det_;
+  rbv_map_cfg map_;
+  rbv_core_cfg core_;
+  int device_, reduce_mode_;
+  bool has_det_ = false, has_core_ = false;
+
+ public:
   // the two worker loops of Rebvio get a CUDA stream each (RBV_TUNE_FE_STREAM): detect of frame n+1 runs next to the tracker of n-1, n
   // field_in_front_end: the distance field of a map is built behind its detect on that stream as well (RBV_TUNE_FIELD_IN_FE; pays with
   // many lanes, where the tracker is the longer chain - with one lane the two loops are balanced without it)
@@ -81,7 +133,6 @@ class Device {
 
  private:
   rbv_ctx* ctx_ = nullptr;
-  int kmax_ = 0;
 };
 
 class EdgeMap {
@@ -94,6 +145,8 @@ class EdgeMap {
 
   rbv_map* handle() const { return map_; }
   uint64_t ts_us() const { return ts_us_; }
+  // EdgeMap::imu() (edge_map.hpp:70): the IMU samples integrated up to this map's frame (rebvio.cpp:77-84 adds them, :145 reads them)
+  types::IntegratedImu& imu() { return imu_; }
   // a pooled map is reused for a later frame (the device slab and the captured graphs of its map pairs stay alive)
   void reset(uint64_t ts_us) { ts_us_ = ts_us; invalidate(); }
   int size() { int n = 0; check(rbv_map_size(dev_->ctx(), map_, &n), "rbv_map_size"); return n; }
@@ -167,6 +220,7 @@ class EdgeMap {
   Device::SharedPtr dev_;
   rbv_map* map_ = nullptr;
   uint64_t ts_us_;
+  types::IntegratedImu imu_;
   bool fresh_ = false;
   std::vector<KeyLine> keylines_;
   std::vector<uint32_t> pixels_;
@@ -177,7 +231,18 @@ class EdgeDetector {
  public:
   EdgeDetector(Device::SharedPtr dev, EdgeDetectorConfig::SharedPtr config = std::make_shared<EdgeDetectorConfig>())
       : dev_(dev), config_(config) {}
+  // the reference's constructor (edge_detector.hpp:41); see Device::forDetector for how detector and core meet on one context
+  EdgeDetector(Camera::SharedPtr camera, EdgeDetectorConfig::SharedPtr config = std::make_shared<EdgeDetectorConfig>())
+      : dev_(Device::forDetector(*camera, *config)), config_(config) {}
   EdgeDetectorConfig::SharedPtr config() { return config_; }
+  Device::SharedPtr device() { return dev_; }
+  // EdgeDetector::detect(types::Image&) (edge_detector.hpp:50): any image type shaped like the reference's types::Image, i.e. with
+  // `ts_us` and a `data` member that looks like a CV_32FC1 cv::Mat (`ptr<float>(row)`, `step`): a real cv::Mat where OpenCV is
+  // present, types::FloatMat otherwise. The frame is float32 0..765, already undistorted (rebvio.cpp:43-45).
+  template <class ImageT>
+  auto detect(ImageT& image) -> decltype((void)image.data.template ptr<float>(0), EdgeMap::SharedPtr()) {
+    return detect(image.data.template ptr<float>(0), (size_t)image.data.step, (uint64_t)image.ts_us);
+  }
   // EdgeDetector::detect (edge_detector.cpp:30-43). `image`: float32 rows x cols, values 0..765 (types::Image::data after
   // rebvio.cpp:43-45), row pitch in bytes (0 = dense). The servo mutates config_->threshold exactly as the reference does.
   EdgeMap::SharedPtr detect(const float* image, size_t pitch_bytes, uint64_t ts_us) {
@@ -214,7 +279,11 @@ class EdgeDetector {
 class Core {
  public:
   Core(Device::SharedPtr dev, CoreConfig::SharedPtr config = std::make_shared<CoreConfig>()) : dev_(dev), config_(config) {}
+  // the reference's constructor (core.hpp:99)
+  Core(Camera::SharedPtr camera, CoreConfig::SharedPtr config = std::make_shared<CoreConfig>())
+      : dev_(Device::forCore(*camera, *config)), config_(config) {}
   CoreConfig::SharedPtr config() { return config_; }
+  Device::SharedPtr device() { return dev_; }
   // Core::buildDistanceField (core.cpp:33-37); keeps the map like DistanceField::map_ (core.hpp:39,63,78)
   void buildDistanceField(EdgeMap::SharedPtr map) {
     check(rbv_build_distance_field(dev_->ctx(), map->handle()), "rbv_build_distance_field");

@@ -307,8 +307,6 @@ static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg
   c->nblk = (P.kmax + 255) / 256;
   RBV_CUDA(dalloc(&c->partials, B * c->nblk * 27));
   RBV_CUDA(dalloc(&c->ticket, B));
-  RBV_CUDA(dalloc(&c->ord_flags, 2 * B * c->nblk));
-  RBV_CUDA(cudaMemset(c->ord_flags, 0, sizeof(unsigned) * 2 * B * c->nblk));
   RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
   RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
@@ -360,7 +358,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaStreamSynchronize(c->stream);
   void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->last_count, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
-                 c->partials, c->ticket, c->blkagg, c->tgt, c->ord_flags};
+                 c->partials, c->ticket, c->blkagg, c->tgt};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {

@@ -170,21 +170,19 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-// wait on a phase by POLLING (mbarrier.test_wait). The first version parked the warp with try_wait + a suspend-time hint (SASS:
-// SYNCS.PHASECHK.TRYWAIT + NANOSLEEP.SYNCS); a parked warp comes back some hundred nanoseconds after the phase completes, and the
-// box-pass pipeline hands a chunk over four to five times (TMA -> row pass -> column pass -> producer) with only two or three chunks
-// in flight, so those wake-ups were the kernel: every stage of k_boxpass2 idle most of the time (ncu: 70 % of all samples in
-// barrier / sleep). The polling warps are few (producer lane, row warps, one column warp) and issue a test every ~20 cycles.
+// wait on a phase: try_wait with a suspend-time hint parks the warp in hardware instead of spinning (a spinning warp
+// takes issue slots from the warps it is waiting for); the loop only re-arms after the hint expires. (Polling with test_wait was
+// measured in round 2: no faster - k_boxpass2 230 us either way.)
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
   const unsigned a = smem_u32(bar);
   long long t0 = 0;
   for (int spin = 0;; ++spin) {
     unsigned ok;
-    asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(a), "r"(parity), "r"(0x989680u) : "memory");
     if (ok) return;
-    if ((spin & 4095) == 4095) {
-      if (t0 == 0) t0 = clock64();
+    if ((spin & 255) == 0) {
+      if (spin == 0) t0 = clock64();
       else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
     }
   }
@@ -1060,14 +1058,14 @@ static bool bp_supported(const rbv_ctx* c) {
   const int cols = c->P.cols;
   return (cols & 3) == 0 && bp_threads(cols) <= BP_MAX_THREADS && bp_smem_bytes(cols) <= 225 * 1024;
 }
-// which fused kernel: k_boxpass2 (register delay lines) where it applies, unless RBV_TUNE_BOX = 2 asks for the first form
-static bool b2_use(const rbv_ctx* c) { return b2_supported(c) && c->tune[RBV_TUNE_BOX] != 2; }
+// which fused kernel: k_boxpass (automatic) or k_boxpass2 (register delay lines) with RBV_TUNE_BOX = 4
+static bool b2_use(const rbv_ctx* c) { return b2_supported(c) && c->tune[RBV_TUNE_BOX] == 4; }   // opt-in: measured slower than k_boxpass so far (230 us vs 105 us)
 static bool bp_use(const rbv_ctx* c, const void* src) {   // a fused (one block per plane) box pass at all?
   if (((uintptr_t)src & 15) != 0) return false;
   if (c->tune[RBV_TUNE_BOX] == 1 || c->tune[RBV_TUNE_BOX] == 3) return false;
   if (c->tune[RBV_TUNE_BOX] == 2) return bp_supported(c);
   if (c->tune[RBV_TUNE_BOX] == 4) return b2_supported(c);
-  return (b2_supported(c) || bp_supported(c)) && c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
+  return bp_supported(c) && c->P.lanes >= 16;   // one block per plane: with few planes the split kernels have far more parallelism
 }
 static int bp_launch(rbv_ctx* c, const float* in, float* out0, float* out1, int planes, size_t in_stride, size_t out_stride, int nz,
                      int d0, int d1, int dual, int in_div = 1) {
@@ -1150,27 +1148,18 @@ int fe_scale_space(rbv_ctx* c, const float* d_img, int part) {
     // pass 0: one CTA per (lane, scale), both reading the lane's frame. The dual form (one CTA per lane filtering both
     // widths from one scan) moves a third less data but is a 64-CTA launch of 140 us on 148 SMs; two single-width CTAs per
     // lane fill the GPU like passes 1 and 2 do.
-    // RBV_TUNE_BOX_SPLIT = G: every pass as G launches over 2B/G planes each. One launch of 2B = 128 blocks owns 128 of the 148 SMs for
-    // its whole duration (544 threads x 96 registers leave no room for a tracker block next to it); with the front end on its own stream
-    // G > 1 leaves SMs to the tracker stream at all times, at the price of a longer front end.
-    int G = c->tune[RBV_TUNE_BOX_SPLIT] > 1 ? c->tune[RBV_TUNE_BOX_SPLIT] : 1;
-    while (G > 1 && (B % G) != 0) --G;
-    const int pl = 2 * B / G;                                  // planes per launch (even: both scales of a lane stay together)
-    for (int g = 0; g < G; ++g) {
-      const size_t po = (size_t)g * pl * N;                    // plane offset in bufA / bufB
-      const float* img_g = d_img + (size_t)g * (pl / 2) * N;   // pass 0 reads one input plane per lane
-      if (b2_use(c)) {
-        if (part != 2) b2_launch(c, img_g, c->bufA + po, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 2);
-        if (part != 1) {
-          b2_launch(c, c->bufA + po, c->bufB + po, pl, N, N, 2, c->widths[0][1], c->widths[1][1]);
-          b2_launch(c, c->bufB + po, c->bufA + po, pl, N, N, 2, c->widths[0][2], c->widths[1][2]);
-        }
-        continue;
-      }
-      if (part != 2) bp_launch(c, img_g, c->bufA + po, c->bufA + po, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
+    const int pl = 2 * B;
+    if (b2_use(c)) {
+      if (part != 2) b2_launch(c, d_img, c->bufA, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 2);
       if (part != 1) {
-        bp_launch(c, c->bufA + po, c->bufB + po, c->bufB + po, pl, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
-        bp_launch(c, c->bufB + po, c->bufA + po, c->bufA + po, pl, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
+        b2_launch(c, c->bufA, c->bufB, pl, N, N, 2, c->widths[0][1], c->widths[1][1]);
+        b2_launch(c, c->bufB, c->bufA, pl, N, N, 2, c->widths[0][2], c->widths[1][2]);
+      }
+    } else {
+      if (part != 2) bp_launch(c, d_img, c->bufA, c->bufA, pl, N, N, 2, c->widths[0][0], c->widths[1][0], 0, 2);
+      if (part != 1) {
+        bp_launch(c, c->bufA, c->bufB, c->bufB, pl, N, N, 2, c->widths[0][1], c->widths[1][1], 0);
+        bp_launch(c, c->bufB, c->bufA, c->bufA, pl, N, N, 2, c->widths[0][2], c->widths[1][2], 0);
       }
     }
     RBV_CUDA(cudaGetLastError());

@@ -120,7 +120,6 @@ struct rbv_ctx {
   float4* tgt;      // [B][kmax][2] packed target keylines of the distance-field map (k_pack_targets)
   rbv_map* field_map;
   float* prod;      // [27][B][kmax] (+ a chunk of slack) ORDERED mode: the 10 float32 addends of tryVel / the 27 of extRotVel per keyline
-  unsigned* ord_flags;  // [2][B][nblk] "block's rows are written" flags of the ORDERED chain warps (tryVel | extRotVel), cleared by the consumer
   float* fiabs;     // [B][kmax]
   int* fwd_head;    // [B][kmax]
   int* fwd_next;    // [B][kmax]
@@ -196,7 +195,7 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
-  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord) X(k_boxpass2)
+  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord) X(k_boxpass2) X(k_chain_tryvel) X(k_chain_extrot)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)

@@ -776,8 +776,7 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
 }
 
 // ORD = RBV_REDUCE_ORDERED: instead of FP64 partial sums the block leaves the ten float32 addends of every keyline in ten planes
-// (`rows`, zeros where the reference adds nothing: x + 0 == x exactly) and raises its flag; the lane's chain warp (ordered_chain,
-// below) adds them in keyline order.
+// (`rows`, zeros where the reference adds nothing: x + 0 == x exactly); k_chain_tryvel, launched behind it, adds them in keyline order.
 template <int KPT, bool ORD>
 __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
                                                          const float4* __restrict__ tgt, const unsigned* __restrict__ field, const float* __restrict__ vel_ptr,
@@ -785,7 +784,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                                                          double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                          const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
                                                          LMState* lm, float* lane_out, int lm_call, const DevParams& P,
-                                                         float* __restrict__ rows, unsigned* __restrict__ flags) {
+                                                         float* __restrict__ rows) {
   __shared__ double sm[(TV_TPB / 32) * 10];
   __shared__ double result[10];
   __shared__ float warp_val[TV_TPB / 32];
@@ -947,12 +946,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
     tv_st<KPT, float>(Ko.residual + o, out, nvalid);
   }
   if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blk] = has ? val : -1.0f;
-  if constexpr (ORD) {   // release the block's rows to the lane's chain warp
-    __threadfence();
-    __syncthreads();
-    if (t == 0 && n > 0) { __threadfence(); *reinterpret_cast<volatile unsigned*>(flags + (size_t)b * nblk + blk) = 1u; }
-    return;
-  }
+  if constexpr (ORD) return;   // the addends are in `rows`: the chain kernel behind this one adds them in keyline order
   if (t < 10) {
     double s2 = 0.0;
 #pragma unroll
@@ -994,64 +988,41 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                       int sr_stride, double* __restrict__ partials, unsigned* __restrict__ ticket, const float* __restrict__ agg_prev,            \
                       float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const __grid_constant__ DevParams P
 #define RBV_TV_PASS Ko, count_o, thr_o, tgt, field, vel_ptr, vel_stride, sr_ptr, sr_stride, partials, ticket, agg_prev, agg_cur, nblk, lm, lane_out, lm_call, P
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr, nullptr); }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr, nullptr); }
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
 
-// ---- RBV_REDUCE_ORDERED: the reference's float32 sums, in keyline order, next to the evaluation -------------------------------
+// ---- RBV_REDUCE_ORDERED: the reference's float32 sums in keyline order --------------------------------------------------------
 // The reference adds its ten tryVel accumulators (and the 27 of extRotVel) sequentially in float32 over the keylines
 // (core.cpp:130-139,244-245); match indices downstream depend on those bits. A sequential float32 sum cannot be re-associated,
-// so the chain itself stays serial: ONE warp per lane, thread a = accumulator a, 4 cycles per dependent FADD (~2 ns per keyline).
-// What can be done is to take everything else off that chain and to run it NEXT TO the evaluation instead of behind it:
-//   * producers (the evaluation blocks, all lanes' block 0 first, then all block 1, ...) leave per-keyline factor rows in
-//     global memory (L2) and raise one flag per block (fence + flag store);
-//   * the chain warp of a lane (reducer CTAs are the first CTAs of the same launch; each hosts several lanes' warps) waits for
-//     the flags in block order, stages 128-keyline chunks of the rows into a 4-deep shared-memory ring with cp.async.cg, forms
-//     the products (one FMUL, off the chain) and adds them in order; all 32 lanes fetch, accumulator threads add.
-// Producers never wait for anything, so the launch cannot deadlock whatever the CTA scheduling order; the flags are cleared
-// by the chain warp as it consumes them. The chain (13 k keylines ~ 27 us) hides behind the evaluation of the other lanes.
+// so the chain itself stays serial: ONE warp per lane, thread a = accumulator a, one dependent FADD (4 cycles, ~2 ns) per keyline.
+// What can be done is to take everything else off that chain:
+//   * the evaluation kernel (k_tryvel_ord2/4, k_extrot_ord: the FAST kernels' per-keyline arithmetic) leaves the float32 ADDENDS
+//     of every keyline in planes [accumulator][lane][keyline] (zeros where the reference adds nothing: x + 0 == x exactly);
+//   * the chain kernel (k_chain_tryvel / k_chain_extrot: one 32-thread CTA per lane, so 64 lanes spread over 64 SMs and the rest
+//     of the GPU stays free for the front-end stream) stages 256 / 128-keyline chunks of the planes into a 4-deep shared-memory
+//     ring with cp.async.cg - all 32 lanes fetch - and lane a adds row a: nothing but an LDS.128 per four keylines and the FADDs
+//     on that warp. (Forming the products on the chain warp costs an FMUL per keyline next to the FADD; the FP32 pipe takes a
+//     3-register instruction every 2 cycles per scheduler, and the chain ran at 8 cycles per keyline instead of 4.)
+// Round 2 first ran the chain warps INSIDE the evaluation launch, fed block by block through release/acquire flags, to hide the
+// chain behind the evaluation; that version produced lane-dependent sums under load on the B200 (no cause found by inspection) and
+// was dropped for this two-kernel form: evaluation, then chain - nothing to synchronise but the kernel boundary.
 #define ORD_NST 4
 #define ORD_PAD 4             // floats behind a staged row: row r of a chunk starts at bank 4 r, so LDS.128 of different rows never collide
-#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (flag test, cp.async issue,
-#define ER_CH 128             // wait, two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
-// Chain warps per reducer CTA (rw, a launch parameter; RBV_TUNE_ORD_RW). A chain warp pulls two factors per accumulator and keyline out of
-// shared memory: with 8 of them on one SM the shared-memory pipe, not the 4-cycle FADD, set the pace (measured: tryVel 167 us per call
-// against 108 us with 1 or 2). So the chains are spread over many SMs - few warps per reducer CTA, the CTA's other warps exit at once -
-// and only the accumulator lanes issue the loads. Default: 2 chain warps per CTA for tryVel (10 accumulators), 1 for extRotVel (27).
-#define TV_RW_MAX 4
-#define TV_RW_DEFAULT 2
-#define ER_RW_MAX 2
-#define ER_RW_DEFAULT 1
-__device__ __forceinline__ unsigned ord_ld_acquire(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
+#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (cp.async issue, wait,
+#define ER_CH 128             // two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
 __device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
 template <int NROWS, int CH>
-__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, int kpb,
-                                               unsigned* flags_lane, float* ring) {
+__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, float* ring) {
   constexpr int RS = CH + ORD_PAD;
   const int lane = threadIdx.x & 31;
   const int nch = (n + CH - 1) / CH;
-  int issued = 0, nflag = 0;
+  int issued = 0;
   float s = 0.0f;
   for (int c = 0; c < nch; ++c) {
-    // keep up to ORD_NST chunks in flight, as far as the producers' flags allow; block only for the chunk needed now
-    while (issued < nch && issued < c + ORD_NST) {
-      const int need = (min((issued + 1) * CH, n) - 1) / kpb;   // producer block that holds the chunk's last keyline
-      bool ok = true;
-      while (nflag <= need) {
-        unsigned f = 0u;
-        if (lane == 0) f = ord_ld_acquire(flags_lane + nflag);
-        f = __shfl_sync(0xFFFFFFFFu, f, 0);
-        if (f) { if (lane == 0) flags_lane[nflag] = 0u; ++nflag; }
-        else if (issued > c) { ok = false; break; }
-      }
-      if (!ok) break;
-      __syncwarp();
+    for (; issued < nch && issued < c + ORD_NST; ++issued) {   // up to ORD_NST chunks in flight
       float* st = ring + (size_t)(issued % ORD_NST) * NROWS * RS + 4 * lane;
       const float* src = rows + base + (size_t)issued * CH + 4 * lane;
 #pragma unroll
@@ -1059,7 +1030,6 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
 #pragma unroll
         for (int q = 0; q < CH / 128; ++q) ord_cp16(st + r * RS + 128 * q, src + (size_t)r * ps + 128 * q);
       asm volatile("cp.async.commit_group;" ::: "memory");
-      ++issued;
     }
     const int pend = issued - c - 1;   // groups committed behind chunk c's
     if (pend >= 3) asm volatile("cp.async.wait_group 3;" ::: "memory");
@@ -1068,9 +1038,7 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     const int cnt = min(CH, n - c * CH);
-    if (lane < NROWS) {   // lane a adds accumulator a: nothing but the load and the dependent FADD on this warp (the FP32 pipe takes a
-      // 3-register instruction every 2 cycles per scheduler, so one FMUL per keyline next to the FADD already makes the 4-cycle chain slip:
-      // measured 8 cycles per keyline with the products formed here)
+    if (lane < NROWS) {   // lane a adds accumulator a
       const float4* ra = reinterpret_cast<const float4*>(ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS);
       const int n16 = cnt >> 4;
       float4 a0, a1, a2, a3;
@@ -1089,49 +1057,37 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
   return s;
 }
 
-template <int KPT>
-__device__ __forceinline__ void tryvel_ord_kernel(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,
-                                                  const unsigned* __restrict__ field, const float* __restrict__ vel_ptr, int vel_stride,
-                                                  const float* __restrict__ sr_ptr, int sr_stride, double* __restrict__ partials,
-                                                  unsigned* __restrict__ ticket, const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
-                                                  LMState* lm, float* lane_out, int lm_call, const DevParams& P, float* __restrict__ rows,
-                                                  unsigned* __restrict__ flags, int nred, int rw) {
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows) {
+  tryvel_fastn_body<2, true>(blockIdx.y, blockIdx.x, RBV_TV_PASS, rows);
+}
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows) {
+  tryvel_fastn_body<4, true>(blockIdx.y, blockIdx.x, RBV_TV_PASS, rows);
+}
+// the ten sums of one tryVel call in keyline order + the LM step (core.cpp:130-139,159-185); one warp = one lane
+__global__ void __launch_bounds__(32) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
+                                                     const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
+                                                     const __grid_constant__ DevParams P) {
   extern __shared__ __align__(16) float ord_ring[];
-  if ((int)blockIdx.x < nred) {   // chain warps: lane b = rw * block + warp
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int b = blockIdx.x * rw + warp;
-    if (warp >= rw || b >= P.lanes) return;
-    const int n = count_o[b];
-    const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, n, TV_TPB * KPT, flags + (size_t)b * nblk,
-                                             ord_ring + (size_t)warp * ORD_NST * 10 * (TV_CH + ORD_PAD));
-    float r[10];
+  const int b = blockIdx.x, lane = threadIdx.x;
+  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring);
+  float r[10];
 #pragma unroll
-    for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
-    if (lane == 0) {
-      float JtJ[9], JtF[3];
-      const float score = r[0];
-      JtJ[0] = r[1]; JtJ[4] = r[2]; JtJ[8] = r[3];
-      JtJ[1] = JtJ[3] = r[4]; JtJ[2] = JtJ[6] = r[5]; JtJ[5] = JtJ[7] = r[6];
-      JtF[0] = r[7]; JtF[1] = r[8]; JtF[2] = r[9];
-      if (lm_call >= 0) {
-        float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
-        lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
-      }
-      float* outp = lane_out + (size_t)b * OUT_STRIDE;
-      for (int i = 0; i < 9; ++i) outp[OUT_JTJ + i] = JtJ[i];
-      for (int i = 0; i < 3; ++i) outp[OUT_JTF + i] = JtF[i];
-      outp[OUT_SCORE] = score;
+  for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
+  if (lane == 0) {
+    float JtJ[9], JtF[3];
+    const float score = r[0];
+    JtJ[0] = r[1]; JtJ[4] = r[2]; JtJ[8] = r[3];
+    JtJ[1] = JtJ[3] = r[4]; JtJ[2] = JtJ[6] = r[5]; JtJ[5] = JtJ[7] = r[6];
+    JtF[0] = r[7]; JtF[1] = r[8]; JtF[2] = r[9];
+    if (lm_call >= 0) {
+      float vu[3] = {vel_ptr[(size_t)b * vel_stride], vel_ptr[(size_t)b * vel_stride + 1], vel_ptr[(size_t)b * vel_stride + 2]};
+      lm_update(lm[b], lm_call, P.iterations, score, JtJ, JtF, vu);
     }
-    return;
+    float* outp = lane_out + (size_t)b * OUT_STRIDE;
+    for (int i = 0; i < 9; ++i) outp[OUT_JTJ + i] = JtJ[i];
+    for (int i = 0; i < 3; ++i) outp[OUT_JTF + i] = JtF[i];
+    outp[OUT_SCORE] = score;
   }
-  const int pbk = blockIdx.x - nred;   // producers: every lane's block 0, then every lane's block 1, ... (the order the chains consume)
-  tryvel_fastn_body<KPT, true>(pbk % P.lanes, pbk / P.lanes, RBV_TV_PASS, rows, flags);
-}
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred, int rw) {
-  tryvel_ord_kernel<2>(RBV_TV_PASS, rows, flags, nred, rw);
-}
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, unsigned* __restrict__ flags, int nred, int rw) {
-  tryvel_ord_kernel<4>(RBV_TV_PASS, rows, flags, nred, rw);
 }
 
 __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
@@ -1176,13 +1132,11 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     if (ord && kpt == 1) kpt = 2;
     const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
 #define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P
-    if (ord) {   // chain-warp CTAs first, then the evaluation blocks of every lane in block-major order
-      int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : TV_RW_DEFAULT;
-      rw = rw > TV_RW_MAX ? TV_RW_MAX : rw;
-      const int nred = (P.lanes + rw - 1) / rw;
-      const size_t smem = sizeof(float) * rw * ORD_NST * 10 * (TV_CH + ORD_PAD);
-      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
-      else { RBV_LAUNCH(c, k_tryvel_ord4, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, RBV_TV_ARGS, c->prod, c->ord_flags, nred, rw); }
+    if (ord) {   // evaluation (addends to c->prod), then the chain kernel: one warp per lane
+      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
+      else { RBV_LAUNCH(c, k_tryvel_ord4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
+      RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (32), sizeof(float) * ORD_NST * 10 * (TV_CH + ORD_PAD), map->count, c->prod, c->lm, c->lane_out,
+                 vel_ptr, vel_stride, lm_call, P);
     }
     else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
@@ -1613,28 +1567,13 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
   if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
-// RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline to 27 planes (zeros for unmatched keylines), one
-// flag per block; the lane's chain warp adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
+// RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline to 27 planes (zeros for unmatched keylines);
+// k_chain_extrot behind it adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
 __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
-                                                       float* __restrict__ rows, unsigned* __restrict__ flags, int nblk, int nred, int rw,
-                                                       float* lane_out, const __grid_constant__ DevParams P) {
-  extern __shared__ __align__(16) float ord_ring[];
-  __shared__ double s_res[ER_RW_MAX][27];
-  __shared__ float s_sys[ER_RW_MAX][42];
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+                                                       float* __restrict__ rows, const __grid_constant__ DevParams P) {
+  const int t = threadIdx.x;
   const size_t ps = (size_t)P.lanes * P.kmax;
-  if ((int)blockIdx.x < nred) {
-    const int b = blockIdx.x * rw + warp;
-    if (warp >= rw || b >= P.lanes) return;
-    const float s = ordered_chain<27, ER_CH>(rows, ps, (size_t)b * P.kmax, count[b], TV_TPB * ER_KPT, flags + (size_t)b * nblk,
-                                             ord_ring + (size_t)warp * ORD_NST * 27 * (ER_CH + ORD_PAD));
-    if (lane < 27) s_res[warp][lane] = (double)s;
-    __syncwarp();
-    extrot_finish_warp(s_res[warp], lane_out + (size_t)b * OUT_STRIDE, s_sys[warp]);
-    return;
-  }
-  const int pbk = blockIdx.x - nred;
-  const int b = pbk % P.lanes, blk = pbk / P.lanes, n = count[b];
+  const int b = blockIdx.y, blk = blockIdx.x, n = count[b];
   if (blk * TV_TPB * ER_KPT >= n) return;
   const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
   ExtRotIn in[ER_KPT];
@@ -1659,9 +1598,17 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
 #pragma unroll
     for (int a = 0; a < 6; ++a) rows[(size_t)(21 + a) * ps + o] = r[a] * r[6];
   }
-  __threadfence();
-  __syncthreads();
-  if (t == 0) { __threadfence(); *reinterpret_cast<volatile unsigned*>(flags + (size_t)b * nblk + blk) = 1u; }
+}
+__global__ void __launch_bounds__(32) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,
+                                                     const __grid_constant__ DevParams P) {
+  extern __shared__ __align__(16) float ord_ring[];
+  __shared__ double s_res[27];
+  __shared__ float s_sys[42];
+  const int b = blockIdx.x, lane = threadIdx.x;
+  const float s = ordered_chain<27, ER_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count[b], ord_ring);
+  if (lane < 27) s_res[lane] = (double)s;
+  __syncwarp();
+  extrot_finish_warp(s_res, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
@@ -1672,13 +1619,9 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     RBV_LAUNCH(c, k_extrot_rows, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
     RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
   } else if (c->reduce_mode == RBV_REDUCE_ORDERED) {
-    int rw = c->tune[RBV_TUNE_ORD_RW] ? c->tune[RBV_TUNE_ORD_RW] : ER_RW_DEFAULT;
-    rw = rw > ER_RW_MAX ? ER_RW_MAX : rw;
-    const int nred = (P.lanes + rw - 1) / rw;
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
-    const size_t smem = sizeof(float) * rw * ORD_NST * 27 * (ER_CH + ORD_PAD);
-    RBV_LAUNCH(c, k_extrot_ord, ((unsigned)(nred + nb * P.lanes)), (TV_TPB), smem, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod,
-               c->ord_flags + (size_t)P.lanes * c->nblk, c->nblk, nred, rw, c->lane_out, P);
+    RBV_LAUNCH(c, k_extrot_ord, (dim3(nb, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
+    RBV_LAUNCH(c, k_chain_extrot, (P.lanes), (32), sizeof(float) * ORD_NST * 27 * (ER_CH + ORD_PAD), new_map->count, c->prod, c->lane_out, P);
   } else {
     RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
@@ -1933,8 +1876,7 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 }
 
 int tr_init_ordered(void) {
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 10 * (TV_CH + ORD_PAD))));
-  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * TV_RW_MAX * ORD_NST * 10 * (TV_CH + ORD_PAD))));
-  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ER_RW_MAX * ORD_NST * 27 * (ER_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_chain_tryvel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ORD_NST * 10 * (TV_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_chain_extrot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ORD_NST * 27 * (ER_CH + ORD_PAD))));
   return RBV_OK;
 }

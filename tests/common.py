@@ -70,3 +70,18 @@ def assert_x_vs_ref(ref_recs, rep):
     for k in range(1, len(rep)):
         tol = x_tol_vs_ref(ref_recs[k]["extrot"]["Wx"])
         assert rep[k]["extrot"]["X_rel"] <= tol, (k, rep[k]["extrot"]["X_rel"], tol)
+
+
+def sequence_long(name, n_frames):
+    """long sequences (hundreds of frames) for the GPU tests: the same scene generator, rendered by synth.render_batch_torch on the
+    device when there is one (the numpy renderer takes ~0.3 s per frame) -> (spec, float frames, R_rel). Both sides of a comparison
+    are fed these same frames, so the +-1 grey level between the two renderers does not matter."""
+    key = ("long", name, n_frames)
+    if key not in _SEQ_CACHE:
+        import torch
+        spec = synth.config(name, n_frames=n_frames)
+        dev = "cuda" if torch.cuda.is_available() else "cpu"
+        frames_u8, R_rel = synth.batched_sequences(spec, [spec.seed], n_frames, device=dev, n_textures=1)
+        f = frames_u8[:, 0].cpu().numpy()
+        _SEQ_CACHE[key] = (spec, [synth.to_float3(f[k]) for k in range(n_frames)], R_rel[:, 0])
+    return _SEQ_CACHE[key]

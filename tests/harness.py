@@ -256,3 +256,45 @@ def dirty(rep, ignore=("X_rel",)):
             if dd:
                 bad.append((k, stage, dd))
     return bad
+
+
+def run_lean(impl, frames, R_rel, snap_every=0, want_ids=False):
+    """Free-running replay of the same loop as run_stages for LONG sequences: no per-stage map snapshots. Per frame it keeps
+    the scalars every stage hands back (counts, Vg, P_Vg, score, Wx, X, V, R0), optionally the two match-index arrays the
+    tracker decides (old map's match_id_forward after minimizeVel, new map's match_id after directedMatch), and the whole new map
+    every `snap_every` frames and at the end. The pose is integrated like Rebvio::stateEstimationProcess does for its odometry
+    (rebvio.cpp:263-273): R_k = R_{k-1} R0_k^T ... kept simple here as position += R_acc V, R_acc = R_acc R0^T (float64)."""
+    recs, old = [], None
+    Racc, pos = np.eye(3), np.zeros(3)
+    for k in range(len(frames)):
+        new = impl.detect(frames[k], 1000000 + 50000 * k)
+        rec = {"n": impl.map_size(new)}
+        if k == 0:
+            recs.append(rec); old = new
+            continue
+        R = np.asarray(R_rel[k], np.float32)
+        impl.build_distance_field(new)
+        impl.rotate(old, R.T)
+        score, Vg, P_Vg, trace, _ = impl.minimize_vel_trace(old, [0, 0, 0], 5)
+        if want_ids:
+            rec["fwd_ids"] = impl.map_get(old)["match_id_forward"].copy()
+        rec.update(score=score, Vg=np.array(Vg), P_Vg=np.array(P_Vg), trace=np.array(trace))
+        rec["nf"] = impl.forward_match(old, new)
+        ok, Wx, X = impl.ext_rot_vel(new, Vg)
+        R0, V, P_V, Rgva = fusion(R, Vg, Wx, X)
+        rec.update(ok=ok, Wx=np.array(Wx), X=np.array(X), V=V, R0=R0)
+        impl.rotate(old, R0)
+        n, kf = impl.directed_match(new, old, V, P_V, Rgva, 40.0)
+        if want_ids:
+            rec["match_ids"] = impl.map_get(new)["match_id"].copy()
+        rec.update(nm=n, kf=kf, nr=impl.regularize(new))
+        impl.update_inverse_depth(V)
+        pos = pos + Racc @ np.asarray(V, np.float64)
+        Racc = Racc @ np.asarray(R0, np.float64).T
+        rec.update(pos=pos.copy(), Racc=Racc.copy())
+        if snap_every and (k % snap_every == 0 or k == len(frames) - 1):
+            rec["new"] = snapshot(impl, new)
+        recs.append(rec)
+        impl.map_free(old)
+        old = new
+    return recs

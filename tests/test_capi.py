@@ -139,3 +139,23 @@ def test_visual_fusion_matches_numpy_statement():
     assert np.allclose(PV[ok], ePV[ok], rtol=2e-5, atol=1e-12)
     assert np.array_equal(PV[1].reshape(3, 3), np.eye(3, dtype=np.float32) * np.float32(1e10))
     assert L.rbv_visual_fusion(0, None, None, None, None, None, None, None, None) != 0
+
+
+def test_reference_signatures_compile_with_toon_types(tmp_path):
+    """tests/cpp/ref_signature_test.cpp: the reference's constructor shapes (EdgeDetector / Core from Camera::SharedPtr copies,
+    rebvio.cpp:23-26), detect(types::Image&)-shaped call, EdgeMap::imu(), and the tracker half of Rebvio::stateEstimationProcess
+    (rebvio.cpp:142-259) with the reference's own TooN types compile and link against the adapter; detector and core meet on one
+    device context. Needs /root/reference/TooN (the build container); the GPU test runs the binary __graft_entry__.build() leaves."""
+    import shutil
+    import subprocess
+    toon = "/root/reference/TooN"
+    if not os.path.isdir(toon) or not shutil.which("g++"):
+        pytest.skip("TooN headers of the reference not present")
+    exe = str(tmp_path / "ref_signature_test")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    cmd = ["g++", "-std=c++14", "-I" + os.path.join(common.ROOT, "include"), "-I" + os.path.join(common.ROOT, "rebvio_b200", "cpp"), "-I" + toon,
+           os.path.join(common.ROOT, "tests", "cpp", "ref_signature_test.cpp"), "-o", exe, "-L" + libdir, "-lrebvio_b200", "-Wl,-rpath," + libdir]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    out = subprocess.run([exe], stdout=subprocess.PIPE, text=True)
+    assert out.returncode == 0 and "compiled and linked" in out.stdout, out.stdout

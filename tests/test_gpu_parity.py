@@ -50,13 +50,13 @@ def test_cuda_vs_reference_golden_teacher_forced(name):
                                                   ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9)])
 def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits.
-    legacy = RBV_TUNE_ORDERED 1: the ordered sums by one adding block per lane behind the evaluation (the first implementation)
-    instead of the chain warps next to it (k_tryvel_ord*, k_extrot_ord)."""
+    legacy = RBV_TUNE_ORDERED 1: the ordered sums by one adding block per lane reading global memory (the first implementation)
+    instead of the chain kernels (k_chain_tryvel / k_chain_extrot: one warp per lane, addends staged through shared memory)."""
     spec, frames, R_rel = common.sequence(name, nf)
     cfg = common.cfgs_from_spec(spec)
     orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
     T = H.run_stages(orc, frames, R_rel)
-    g = _gpu(cfg, lanes=lanes, lane=lanes - 1, tune={capi.TUNE_ORDERED: legacy})   # 9 / 21 lanes: several chain-warp CTAs, a partly filled one
+    g = _gpu(cfg, lanes=lanes, lane=lanes - 1, tune={capi.TUNE_ORDERED: legacy})
     G = H.run_stages(g, frames, R_rel)
     rep = H.report(T, G)
     assert H.dirty(rep) == []
@@ -66,7 +66,7 @@ def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
         assert names.get("k_tryvel_reduce", 0) > 0 and names.get("k_extrot_reduce", 0) > 0 and names.get("k_extrot_ord", 0) == 0
     else:
         assert names.get("k_tryvel_ord2", 0) + names.get("k_tryvel_ord4", 0) > 0 and names.get("k_extrot_ord", 0) > 0
-        assert names.get("k_tryvel_reduce", 0) == 0
+        assert names.get("k_chain_tryvel", 0) > 0 and names.get("k_chain_extrot", 0) > 0 and names.get("k_tryvel_reduce", 0) == 0
     g.close(); orc.close()
 
 
@@ -133,7 +133,7 @@ def test_try_vel_fast_vs_ordered_indices_and_sums(kpt):
         a, b = orc.detect(frames[0]), orc.detect(frames[1])
         orc.build_distance_field(b)
         n = orc.map_size(a)
-        # ORDERED: 2 / 4 keylines per thread = the chain-warp kernels k_tryvel_ord2 / k_tryvel_ord4; 1 = evaluation + adding block per lane
+        # ORDERED: 2 / 4 keylines per thread = k_tryvel_ord2 / k_tryvel_ord4 + k_chain_tryvel; 1 = the first form (k_tryvel_eval + k_tryvel_reduce)
         g = _gpu(cfg, mode=mode, lanes=3 if kpt == 4 else 2, tune={capi.TUNE_TRYVEL: kpt, capi.TUNE_ORDERED: 1 if kpt == 1 else 0})
         ga, gb = g.detect(frames[0]), g.detect(frames[1])
         g.build_distance_field(gb)
@@ -363,6 +363,19 @@ def test_cpp_adapter_runs_the_chain(tmp_path):
     assert out.returncode == 0, out.stdout
     fields = out.stdout.split()
     assert int(fields[1]) > 1000 and int(fields[fields.index("directed") + 1]) > 500, out.stdout
+
+
+def test_reference_signature_loop_runs_on_device():
+    """the binary of tests/cpp/ref_signature_test.cpp (built in the build container against the reference's TooN headers): the
+    reference's constructor shapes and the tracker half of its estimation loop drive the device through the adapter"""
+    import os
+    import subprocess
+    exe = os.path.join(common.ROOT, "tests", "cpp", "_build", "ref_signature_test")
+    if not os.path.exists(exe):
+        pytest.skip("tests/cpp/_build/ref_signature_test not built (needs /root/reference/TooN at build time)")
+    out = subprocess.run([exe, "run"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout
+    assert "keylines" in out.stdout and "imu_samples 1" in out.stdout, out.stdout
 
 
 def test_u8_upload_and_prefetch_match_float_path():
@@ -658,3 +671,35 @@ def test_device_threshold_servo_equals_host_servo_on_one_stream():
         assert m.keylines(1)[0].tobytes() == ref.maps[ref.cur ^ 1].keylines(1)[0].tobytes()
     assert moved
     ref.close(); dev.close()
+
+
+@pytest.mark.parametrize("name", ["C1", "C2"])
+def test_200_frames_free_running_bit_exact(name):
+    """BASELINE.json configs[0] / configs[1] at length: 200 frames free-running (no teacher forcing) in the default reduce mode
+    (RBV_REDUCE_ORDERED: float32 sums in keyline order). Every frame's counts, minimiser trace, Vg, P_Vg, score and 6x6 system are
+    bit-identical to the oracle's, X within the solve tolerance, the integrated pose identical, and the whole map (every keyline
+    field) bit-identical every 25 frames and after the last one."""
+    nf = 200
+    spec, frames, R_rel = common.sequence_long(name, nf)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    T = H.run_lean(orc, frames, R_rel, snap_every=25)
+    orc.close()
+    g = _gpu(cfg, lanes=2, lane=1)
+    G = H.run_lean(g, frames, R_rel, snap_every=25)
+    g.close()
+    for k in range(nf):
+        assert T[k]["n"] == G[k]["n"], k
+        if k == 0:
+            continue
+        for key in ("nf", "nm", "kf", "nr", "ok"):
+            assert T[k][key] == G[k][key], (k, key, T[k][key], G[k][key])
+        for key in ("Vg", "P_Vg", "Wx", "trace"):
+            assert np.array_equal(H.bits(T[k][key]), H.bits(G[k][key])), (k, key)
+        assert H.bits(np.float32(T[k]["score"])) == H.bits(np.float32(G[k]["score"])), k
+        assert H.rel_err(G[k]["X"], T[k]["X"]) <= common.X_RTOL_VS_ORACLE, (k, G[k]["X"], T[k]["X"])
+        assert np.array_equal(T[k]["V"], G[k]["V"]) and np.array_equal(T[k]["R0"], G[k]["R0"]), k   # same float32 inputs of the second half
+        if "new" in T[k]:
+            assert H.clean(H.compare_keylines(T[k]["new"]["kl"], G[k]["new"]["kl"])) == {}, k
+    assert np.array_equal(T[-1]["pos"], G[-1]["pos"]) and np.array_equal(T[-1]["Racc"], G[-1]["Racc"])
+    assert T[-1]["nm"] > 500

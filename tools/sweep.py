@@ -18,7 +18,7 @@ peaks = os.path.join(ROOT, "MEASURED_PEAKS.json")
 PEAK = float(json.load(open(peaks))["hbm_gbs"]) if os.path.exists(peaks) else 6650.0
 SCALE = ("k_boxpass", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
 DETECT = ("k_detect_flags", "k_detect_scan", "k_detect_emit", "k_detect_emit_wide", "k_join", "k_tune")
-TRYVEL = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4")
+TRYVEL = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel")
 dev = torch.device("cuda", 0)
 print(f"# kernel sweep on {torch.cuda.get_device_name(0)}; HBM peak {PEAK:.0f} GB/s (MEASURED_PEAKS.json); algorithmic bytes: scale space 48 N, "
       "detect 12 N + 104 K (flags, emit, join), one tryVel iteration 68 K, frame 64 N + (1260 + 4 P) K; times = CUDA events of one step, "
