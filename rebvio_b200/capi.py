@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librebvio_b200.so")
+LIB_PATH = os.environ.get("RBV_LIB") or os.path.join(HERE, "librebvio_b200.so")   # RBV_LIB: another build of the same library (bisecting on the GPU box)
 
 f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")

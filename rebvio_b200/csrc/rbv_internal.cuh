@@ -296,6 +296,41 @@ __host__ __device__ inline void rbv_inv3(const float* m, float* out) {
 }
 
 #ifdef __CUDACC__
+// ---- mbarrier + TMA bulk-copy helpers (cp.async.bulk global -> shared, completion on an mbarrier) ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// wait on a phase: try_wait with a suspend-time hint parks the warp in hardware instead of spinning (a spinning warp
+// takes issue slots from the warps it is waiting for); the loop only re-arms after the hint expires. (Polling with test_wait was
+// measured in round 2: no faster - k_boxpass2 230 us either way.)
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  const unsigned a = smem_u32(bar);
+  long long t0 = 0;
+  for (int spin = 0;; ++spin) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(a), "r"(parity), "r"(0x989680u) : "memory");
+    if (ok) return;
+    if ((spin & 255) == 0) {
+      if (spin == 0) t0 = clock64();
+      else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
+    }
+  }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+
 // x86 cvttsd2si / cvttss2si semantics (out of range or NaN -> INT_MIN), which the reference's static_cast<int> compiles to
 __device__ __forceinline__ int rbv_d2i(double d) {
   return (d != d || d >= 2147483648.0 || d <= -2147483649.0) ? (-2147483647 - 1) : __double2int_rz(d);

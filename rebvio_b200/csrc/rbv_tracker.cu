@@ -1000,45 +1000,46 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 //     of every keyline in planes [accumulator][lane][keyline] (zeros where the reference adds nothing: x + 0 == x exactly);
 //   * the chain kernel (k_chain_tryvel / k_chain_extrot: one 32-thread CTA per lane, so 64 lanes spread over 64 SMs and the rest
 //     of the GPU stays free for the front-end stream) stages 256 / 128-keyline chunks of the planes into a 4-deep shared-memory
-//     ring with cp.async.cg - all 32 lanes fetch - and lane a adds row a: nothing but an LDS.128 per four keylines and the FADDs
-//     on that warp. (Forming the products on the chain warp costs an FMUL per keyline next to the FADD; the FP32 pipe takes a
+//     ring with TMA bulk copies (one per row and chunk, mbarrier completion) and lane a adds row a: nothing but an LDS.128 per
+//     four keylines and the FADDs on that warp. (Forming the products on the chain warp costs an FMUL per keyline next to the FADD; the FP32 pipe takes a
 //     3-register instruction every 2 cycles per scheduler, and the chain ran at 8 cycles per keyline instead of 4.)
 // Round 2 first ran the chain warps INSIDE the evaluation launch, fed block by block through release/acquire flags, to hide the
 // chain behind the evaluation; that version produced lane-dependent sums under load on the B200 (no cause found by inspection) and
 // was dropped for this two-kernel form: evaluation, then chain - nothing to synchronise but the kernel boundary.
 #define ORD_NST 4
 #define ORD_PAD 4             // floats behind a staged row: row r of a chunk starts at bank 4 r, so LDS.128 of different rows never collide
-#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (cp.async issue, wait,
-#define ER_CH 128             // two warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
-__device__ __forceinline__ void ord_cp16(float* smem_dst, const float* gsrc) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
-}
+#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (bulk-copy issue, wait,
+#define ER_CH 128             // warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
+// Staging: one TMA bulk copy (cp.async.bulk, CH x 4 bytes) per row and chunk, issued by lane r for row r, completion counted in bytes on
+// the stage's mbarrier. (The first form staged with 16-byte cp.async: 80 - 108 LDGSTS in flight per thread; that version added a wrong
+// chunk now and then - deterministically on 200 k-keyline chains - while the same chain over 4 or 7 rows, at most 64 in flight, was
+// bit-exact on every test. One bulk copy per lane and stage has nothing of that kind to overflow.)
 template <int NROWS, int CH>
-__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, float* ring) {
+__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, float* ring,
+                                               unsigned long long* bars /* [ORD_NST], shared */) {
   constexpr int RS = CH + ORD_PAD;
   const int lane = threadIdx.x & 31;
   const int nch = (n + CH - 1) / CH;
+  if (lane == 0) {
+    for (int i = 0; i < ORD_NST; ++i) mbar_init(bars + i, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
   int issued = 0;
   float s = 0.0f;
   for (int c = 0; c < nch; ++c) {
     for (; issued < nch && issued < c + ORD_NST; ++issued) {   // up to ORD_NST chunks in flight
-      float* st = ring + (size_t)(issued % ORD_NST) * NROWS * RS + 4 * lane;
-      const float* src = rows + base + (size_t)issued * CH + 4 * lane;
-#pragma unroll
-      for (int r = 0; r < NROWS; ++r)
-#pragma unroll
-        for (int q = 0; q < CH / 128; ++q) ord_cp16(st + r * RS + 128 * q, src + (size_t)r * ps + 128 * q);
-      asm volatile("cp.async.commit_group;" ::: "memory");
+      const int stage = issued % ORD_NST;
+      if (lane == 0) mbar_arrive_expect_tx(bars + stage, (unsigned)(NROWS * CH * 4));
+      __syncwarp();
+      if (lane < NROWS)
+        bulk_g2s(ring + (size_t)stage * NROWS * RS + lane * RS, rows + (size_t)lane * ps + base + (size_t)issued * CH, (unsigned)(CH * 4), bars + stage);
     }
-    const int pend = issued - c - 1;   // groups committed behind chunk c's
-    if (pend >= 3) asm volatile("cp.async.wait_group 3;" ::: "memory");
-    else if (pend == 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
-    else if (pend == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
-    else asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
+    mbar_wait(bars + c % ORD_NST, (unsigned)((c / ORD_NST) & 1));
     const int cnt = min(CH, n - c * CH);
-    if (lane < NROWS) {   // lane a adds accumulator a
+    if (lane < NROWS) {   // lane a adds accumulator a: nothing but the load and the dependent FADD on this warp (the FP32 pipe takes a
+      // 3-register instruction every 2 cycles per scheduler, so one FMUL per keyline next to the FADD already makes the 4-cycle chain slip:
+      // measured 8 cycles per keyline with the products formed here)
       const float4* ra = reinterpret_cast<const float4*>(ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS);
       const int n16 = cnt >> 4;
       float4 a0, a1, a2, a3;
@@ -1052,7 +1053,8 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
       const float* rt = reinterpret_cast<const float*>(ra);
       for (int i = n16 * 16; i < cnt; ++i) s += rt[i];
     }
-    __syncwarp();   // every lane is done with the slot before a later cp.async refills it
+    fence_proxy_async();   // this thread's reads of the slot are ordered before the bulk copy that refills it (generic -> async proxy)
+    __syncwarp();
   }
   return s;
 }
@@ -1067,9 +1069,10 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __
 __global__ void __launch_bounds__(32) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
                                                      const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
                                                      const __grid_constant__ DevParams P) {
-  extern __shared__ __align__(16) float ord_ring[];
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[ORD_NST];
   const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring);
+  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring, bars);
   float r[10];
 #pragma unroll
   for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1601,11 +1604,12 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
 }
 __global__ void __launch_bounds__(32) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,
                                                      const __grid_constant__ DevParams P) {
-  extern __shared__ __align__(16) float ord_ring[];
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[ORD_NST];
   __shared__ double s_res[27];
   __shared__ float s_sys[42];
   const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<27, ER_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count[b], ord_ring);
+  const float s = ordered_chain<27, ER_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count[b], ord_ring, bars);
   if (lane < 27) s_res[lane] = (double)s;
   __syncwarp();
   extrot_finish_warp(s_res, lane_out + (size_t)b * OUT_STRIDE, s_sys);

@@ -89,6 +89,9 @@ class Context:
         for key, name in ((capi.TUNE_FIELD, "RBV_TUNE_FIELD"), (capi.TUNE_BOX, "RBV_TUNE_BOX")):
             if os.environ.get(name):
                 self.set_tuning(key, int(os.environ[name]))
+        for kv in os.environ.get("RBV_TUNE_ENV", "").split(","):   # "key=value,..." (rbv_set_tuning keys), e.g. "8=1"
+            if kv:
+                self.set_tuning(int(kv.split("=")[0]), int(kv.split("=")[1]))
 
     def close(self):
         if self.h:
