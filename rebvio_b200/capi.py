@@ -131,6 +131,7 @@ _SIG = {
     "rbv_debug_read_setup": (C.c_int, [vp, vp, vp]),
     "rbv_debug_read_lm_trace": (C.c_int, [vp, C.c_int, vp, C.c_int]),
     "rbv_debug_read_probe_count": (C.c_int, [vp, C.c_int, vp]),
+    "rbv_debug_read_addends": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_int]),
 }
 
 EXPORTS = sorted(_SIG)

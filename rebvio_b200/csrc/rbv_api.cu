@@ -1677,3 +1677,13 @@ extern "C" int rbv_debug_read_probe_count(rbv_ctx* c, int lane, unsigned long lo
   RBV_CUDA(copy_sync(c, probes, c->probes + lane, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return RBV_OK;
 }
+
+// debug tap: one plane of the ORDERED-mode addend buffer (tryVel: planes 0..9, extRotVel: 0..26) of one lane, as left by the last evaluation kernel
+extern "C" int rbv_debug_read_addends(rbv_ctx* c, int plane, int lane, float* out, int n) {
+  CHECK_CTX(c);
+  if (plane < -1 || plane >= 27 || lane < 0 || lane >= c->P.lanes || !out || n < 0 || n > c->P.kmax) return RBV_ERR_ARG;
+  RBV_CUDA(cudaStreamSynchronize(c->stream));
+  const float* src = plane < 0 ? c->fiabs + (size_t)lane * c->P.kmax : c->prod + ((size_t)plane * c->P.lanes + lane) * c->P.kmax;   // plane -1: chain debug trace
+  if (n) RBV_CUDA(copy_sync(c, out, src, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  return RBV_OK;
+}

@@ -779,8 +779,11 @@ struct B2State {
 };
 
 // one sub-chunk: rows k0 .. k0+nr-1 are scanned into `cur` (and the ring), then the box rows k0-h .. k0+nr-1-h are written from
-// `cur` (A, B) and `prev` (C, D). TOP = first sub-chunk (no upper taps, scale_space.cpp:78-84). MIXED = warp 0 (columns without a left tap, :94).
-template <int W, bool MIXED, bool TOP>
+// `cur` (A, B) and `prev` (C, D). TOP = first sub-chunk (no upper taps, scale_space.cpp:78-84). Column warp 0 also holds the columns
+// without a left tap (:94) and computes the right-border columns; that is a run-time test so that all column warps share one copy of the
+// code (the first version of this kernel had eight copies of this body - two W x warp 0 / others x ping-pong - 11 k instructions,
+// and spent a quarter of its samples waiting for instruction fetch).
+template <int W, bool TOP>
 __device__ __forceinline__ void b2_sub(B2State& st, B2Cols<W>& cur, const B2Cols<W>& prev, int s) {
   constexpr int h = W / 2;
   const int k0 = s * W, nr = min(W, st.rows - k0), k1 = k0 + nr;
@@ -816,7 +819,7 @@ __device__ __forceinline__ void b2_sub(B2State& st, B2Cols<W>& cur, const B2Cols
     ++st.ci_rel;
   }
   asm volatile("bar.sync 1, %0;" ::"r"(st.nbar) : "memory");   // ring rows of this sub-chunk complete
-  const bool left0 = !MIXED || st.c0 >= W;
+  const bool left0 = st.c0 >= W;
   {
     const unsigned lb = rb - 4u * (unsigned)(left0 ? W : 0);   // column c0 - W (clamped to c0 where there is no left tap: never used)
 #pragma unroll
@@ -837,7 +840,7 @@ __device__ __forceinline__ void b2_sub(B2State& st, B2Cols<W>& cur, const B2Cols
         o1 *= st.inv_area[i + 1][W];
       } else {                                                                          // :99 ((A - B) - C) + D, :94 A - C
         o0 = ((cur.v0[i] - cur.b0[i]) - prev.v0[i]) + prev.b0[i];
-        if (MIXED && !left0) o0 = cur.v0[i] - prev.v0[i];
+        if (!left0) o0 = cur.v0[i] - prev.v0[i];
         o1 = ((cur.v1[i] - cur.b1[i]) - prev.v1[i]) + prev.b1[i];
         o0 *= st.inv0; o1 *= st.inv1;
       }
@@ -845,22 +848,23 @@ __device__ __forceinline__ void b2_sub(B2State& st, B2Cols<W>& cur, const B2Cols
       if (st.st1) d[(size_t)i * st.cols + 32] = o1;
     }
   }
-  // the h output columns whose right tap is clamped to the last column: every tap from the ring (this sub-chunk and the previous one)
-  if (MIXED && st.lane < h) {
-    const int oc = st.cols - h + st.lane, jlo = oc - h - 1, ncol = (st.cols - 1) - jlo;
+  // the h output columns whose right tap is clamped to the last column: every tap from the ring (this sub-chunk and the previous one);
+  // the (row, column) pairs are dealt out over the lanes of column warp 0
+  if (st.q == 0) {
     const unsigned ring0 = st.ring_a - 4u * (unsigned)st.c0;   // column 0 of ring row 0
     const unsigned ca = ring0 + (unsigned)((s & 1) * W) * st.rpb, pa = ring0 + (unsigned)(((s & 1) ^ 1) * W) * st.rpb;
-    const float invm = (float)(1.0 / (double)((float)W * (float)ncol));
-    float* dt = st.dst - (st.c0 - h) + oc + (ptrdiff_t)(k0 - h) * st.cols;
-    for (int i = TOP ? h : 0; i < nr; ++i) {
+    for (int idx = st.lane; idx < h * nr; idx += 32) {
+      const int i = idx / h, j = idx - i * h;
+      if (TOP && i < h) continue;
+      const int oc = st.cols - h + j, jlo = oc - h - 1, ncol = (st.cols - 1) - jlo;
       const float A = lds_f32(ca + (unsigned)i * st.rpb + 4u * (unsigned)(st.cols - 1)), Bv = lds_f32(ca + (unsigned)i * st.rpb + 4u * (unsigned)jlo);
       float o;
       if (TOP) o = (A - Bv) * st.inv_area[i + 1][ncol];
       else {
         const float C = lds_f32(pa + (unsigned)i * st.rpb + 4u * (unsigned)(st.cols - 1)), D = lds_f32(pa + (unsigned)i * st.rpb + 4u * (unsigned)jlo);
-        o = (((A - Bv) - C) + D) * invm;
+        o = (((A - Bv) - C) + D) * (float)(1.0 / (double)((float)W * (float)ncol));
       }
-      dt[(size_t)i * st.cols] = o;
+      st.dst[(ptrdiff_t)(k0 - h + i) * st.cols - (st.c0 - h) + oc] = o;
     }
   }
 }
@@ -942,18 +946,13 @@ __device__ __forceinline__ void boxpass2_body(const float* __restrict__ src, flo
     st.ci_ready = 0; st.ci_rel = 0;
     st.dst = outp + (st.c0 - h);
     st.scanned = scanned; st.empty = empty; st.inv_area = inv_area;
-    B2Cols<W> X, Y;
+    B2Cols<W> cur, prev;
     const int nsub = (rows + W - 1) / W;
-    if (st.q == 0) {
-      b2_sub<W, true, true>(st, X, Y, 0);
-      int s2 = 1;
-      for (; s2 + 1 < nsub; s2 += 2) { b2_sub<W, true, false>(st, Y, X, s2); b2_sub<W, true, false>(st, X, Y, s2 + 1); }
-      if (s2 < nsub) b2_sub<W, true, false>(st, Y, X, s2);
-    } else {
-      b2_sub<W, false, true>(st, X, Y, 0);
-      int s2 = 1;
-      for (; s2 + 1 < nsub; s2 += 2) { b2_sub<W, false, false>(st, Y, X, s2); b2_sub<W, false, false>(st, X, Y, s2 + 1); }
-      if (s2 < nsub) b2_sub<W, false, false>(st, Y, X, s2);
+    b2_sub<W, true>(st, cur, prev, 0);
+#pragma unroll 1
+    for (int s2 = 1; s2 < nsub; ++s2) {
+      prev = cur;                                       // 4 W register moves against ~500 instructions of body: one copy of the code
+      b2_sub<W, false>(st, cur, prev, s2);
     }
     // bottom h rows (:104-124): lower taps clamped to the last row, ((A - C) - B) + D; every tap from the ring, which holds the last two
     // sub-chunks (row r in buffer (r / W) & 1, slot r % W). No barrier needed: the ring is not written any more.

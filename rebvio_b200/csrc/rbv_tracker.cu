@@ -16,6 +16,8 @@
 //
 // Reductions (J^T J, J^T F, score): RBV_REDUCE_FAST = per-thread FP64 partials + warp-shuffle tree in a fixed order;
 // RBV_REDUCE_ORDERED = one lane per accumulator adds the float32 addends in keyline order, reproducing the CPU bits.
+#include <stdlib.h>
+
 #include "rbv_internal.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1016,7 +1018,7 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 // bit-exact on every test. One bulk copy per lane and stage has nothing of that kind to overflow.)
 template <int NROWS, int CH>
 __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, float* ring,
-                                               unsigned long long* bars /* [ORD_NST], shared */) {
+                                               unsigned long long* bars /* [ORD_NST], shared */, float* dbg = nullptr) {
   constexpr int RS = CH + ORD_PAD;
   const int lane = threadIdx.x & 31;
   const int nch = (n + CH - 1) / CH;
@@ -1044,6 +1046,11 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
       const int n16 = cnt >> 4;
       float4 a0, a1, a2, a3;
       if (n16 > 0) { a0 = ra[0]; a1 = ra[1]; a2 = ra[2]; a3 = ra[3]; }
+      // unroll 1: nvcc 12.9 unrolls this loop by 8 with 4 / 2 / 1-block remainder sections, and in the remainder sections the prefetch
+      // for the NEXT section is addressed from the already advanced block counter plus the old offset (block b + 8 instead of b + 4):
+      // chunks with (n16 & 7) in {3, 5, 6, 7} added a block from beyond the chunk. One block per trip has no remainder to get wrong, and the
+      // FADD chain (64 cycles per block) hides the loop overhead.
+#pragma unroll 1
       for (int b16 = 0; b16 < n16; ++b16) {
         float4 b0 = a0, b1 = a1, b2 = a2, b3 = a3;
         if (b16 + 1 < n16) { a0 = ra[4 * b16 + 4]; a1 = ra[4 * b16 + 5]; a2 = ra[4 * b16 + 6]; a3 = ra[4 * b16 + 7]; }   // next block's addends first
@@ -1051,7 +1058,16 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, s
         s += b2.x; s += b2.y; s += b2.z; s += b2.w; s += b3.x; s += b3.y; s += b3.z; s += b3.w;
       }
       const float* rt = reinterpret_cast<const float*>(ra);
+#pragma unroll 1
       for (int i = n16 * 16; i < cnt; ++i) s += rt[i];
+    }
+    if (dbg && lane == 0) dbg[c] = s;   // debug: running sum of accumulator 0 after every chunk
+    if (dbg && c == nch - 1) {          // debug: the last chunk as this warp sees it in shared memory, every row
+      if (lane == 0) { dbg[nch] = (float)cnt; dbg[nch + 1] = (float)n; }
+      if (lane < NROWS) {
+        const float* rr = ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS;
+        for (int i = 0; i < RS; ++i) dbg[64 + lane * RS + i] = rr[i];
+      }
     }
     fence_proxy_async();   // this thread's reads of the slot are ordered before the bulk copy that refills it (generic -> async proxy)
     __syncwarp();
@@ -1068,11 +1084,12 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __
 // the ten sums of one tryVel call in keyline order + the LM step (core.cpp:130-139,159-185); one warp = one lane
 __global__ void __launch_bounds__(32) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
                                                      const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
-                                                     const __grid_constant__ DevParams P) {
+                                                     const __grid_constant__ DevParams P, float* dbg) {
   extern __shared__ __align__(128) float ord_ring[];
   __shared__ __align__(8) unsigned long long bars[ORD_NST];
   const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring, bars);
+  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring, bars,
+                                           dbg ? dbg + (size_t)b * P.kmax : nullptr);
   float r[10];
 #pragma unroll
   for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1139,7 +1156,7 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
       if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
       else { RBV_LAUNCH(c, k_tryvel_ord4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
       RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (32), sizeof(float) * ORD_NST * 10 * (TV_CH + ORD_PAD), map->count, c->prod, c->lm, c->lane_out,
-                 vel_ptr, vel_stride, lm_call, P);
+                 vel_ptr, vel_stride, lm_call, P, getenv("RBV_DEBUG_CHAIN") ? c->fiabs : nullptr);
     }
     else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
