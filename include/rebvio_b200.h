@@ -381,7 +381,8 @@ int rbv_debug_read_setup(rbv_ctx* ctx, float* pinv75, int* widths6);
 int rbv_debug_read_lm_trace(rbv_ctx* ctx, int lane, float* out, int cap_floats);
 /* mean number of mask probes per keyline in the last directed match (P-bar of the byte model) */
 int rbv_debug_read_probe_count(rbv_ctx* ctx, int lane, unsigned long long* probes);
-/* one plane of the ORDERED-mode addend buffer (tryVel: 10 planes in accumulator order, extRotVel: 27) of one lane, after the last evaluation */
+/* debug: one accumulator's ORDERED-mode addends of one lane, keylines [0, n), after the last evaluation kernel (plane 0..9: tryVel in accumulator
+   order, 100..126: extRotVel); plane -1: the chain kernel's running sum of accumulator 0 after every 256-keyline chunk (RBV_DEBUG_CHAIN=1) */
 int rbv_debug_read_addends(rbv_ctx* ctx, int plane, int lane, float* out, int n);
 
 #ifdef __cplusplus

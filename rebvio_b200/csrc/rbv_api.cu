@@ -293,7 +293,10 @@ static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg
   }
   RBV_CUDA(dalloc(&c->field, B * N));
   RBV_CUDA(dalloc(&c->tgt, 2 * B * K));
-  RBV_CUDA(dalloc(&c->prod, 27 * B * K + 1024));   // + a staged chunk of slack: the chain warps copy whole chunks
+  {   // ORDERED addends: chunked layout of the chain kernels (rbv_tracker.cu, OrdLayout) or the 27 planes of the first form (RBV_TUNE_ORDERED = 1)
+    const size_t chunked = tr_ordered_floats(lanes, P.kmax), planes = 27 * B * K;
+    RBV_CUDA(dalloc(&c->prod, chunked > planes ? chunked : planes));
+  }
   RBV_CUDA(dalloc(&c->fiabs, B * K));
   RBV_CUDA(dalloc(&c->fwd_head, B * K));
   RBV_CUDA(dalloc(&c->fwd_next, B * K));
@@ -1678,12 +1681,14 @@ extern "C" int rbv_debug_read_probe_count(rbv_ctx* c, int lane, unsigned long lo
   return RBV_OK;
 }
 
-// debug tap: one plane of the ORDERED-mode addend buffer (tryVel: planes 0..9, extRotVel: 0..26) of one lane, as left by the last evaluation kernel
+// debug tap: one row of the ORDERED-mode addends (tryVel: planes 0..9, extRotVel: 100..126) of one lane, as left by the last evaluation kernel;
+// plane -1: the chain kernel's per-chunk running sums of accumulator 0 (written when RBV_DEBUG_CHAIN is set in the environment)
 extern "C" int rbv_debug_read_addends(rbv_ctx* c, int plane, int lane, float* out, int n) {
   CHECK_CTX(c);
-  if (plane < -1 || plane >= 27 || lane < 0 || lane >= c->P.lanes || !out || n < 0 || n > c->P.kmax) return RBV_ERR_ARG;
+  const bool ok_plane = plane == -1 || (plane >= 0 && plane < 10) || (plane >= 100 && plane < 127);
+  if (!ok_plane || lane < 0 || lane >= c->P.lanes || !out || n < 0 || n > c->P.kmax) return RBV_ERR_ARG;
   RBV_CUDA(cudaStreamSynchronize(c->stream));
-  const float* src = plane < 0 ? c->fiabs + (size_t)lane * c->P.kmax : c->prod + ((size_t)plane * c->P.lanes + lane) * c->P.kmax;   // plane -1: chain debug trace
-  if (n) RBV_CUDA(copy_sync(c, out, src, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+  if (plane >= 0) return tr_debug_addends(c, plane, lane, out, n);
+  if (n) RBV_CUDA(copy_sync(c, out, c->fiabs + (size_t)lane * c->P.kmax, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
   return RBV_OK;
 }

@@ -238,6 +238,8 @@ int tr_pack_targets(rbv_ctx* c, rbv_map* map);   // refresh the packed copy afte
 int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);
 int tr_ordered_legacy(const rbv_ctx* c);
+size_t tr_ordered_floats(int lanes, int kmax);   // floats of c->prod the chain kernels' addend layout needs
+int tr_debug_addends(rbv_ctx* c, int plane, int lane, float* out, int n);
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call);     // lm_call: -1 = single evaluation (vel, srmin in lane_in), t >= 0 = LM call t
 int tr_forward_match(rbv_ctx* c, rbv_map* old_map, rbv_map* new_map);
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm);

@@ -777,6 +777,28 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
   }
 }
 
+// ---- RBV_REDUCE_ORDERED addend layout (the chain kernels are further down, behind the FAST kernels) ----
+#define ORD_NST 4
+#define ORD_PAD 4             // floats behind a row of a chunk: row r starts at bank 4 r, so the LDS.128 of different rows never collide
+#define TV_CH 256             // keylines per chunk: tryVel (10 rows) / extRotVel (27 rows)
+#define ER_CH 128
+// Addend layout in HBM (c->prod): per lane, chunk after chunk; a chunk = NROWS rows of CH + ORD_PAD floats, i.e. exactly the image of one
+// shared-memory stage, so ONE bulk copy (cp.async.bulk, 10.4 / 14.3 KB) per chunk stages it - issued by one thread of a loader warp, the chain
+// warp never spends an issue slot on it. (Round 2 first kept [row][lane][keyline] planes and one copy per row and chunk from the chain warp
+// itself: 10 - 27 serialised UBLKCP per chunk plus a proxy fence, 14 cycles per keyline instead of 4.)
+template <int NROWS, int CH> struct OrdLayout {
+  static constexpr int RS = CH + ORD_PAD, CHUNK = NROWS * RS;
+  __host__ __device__ static size_t lane_stride(int kmax) { return (size_t)((kmax + CH - 1) / CH) * CHUNK; }
+  __host__ __device__ static size_t at(int idx) { return (size_t)(idx / CH) * CHUNK + (size_t)(idx % CH); }   // + a * RS: accumulator a of keyline idx
+};
+typedef OrdLayout<10, TV_CH> OrdTV;
+typedef OrdLayout<27, ER_CH> OrdER;
+size_t tr_ordered_floats(int lanes, int kmax) {   // c->prod: the larger of the two layouts
+  const size_t a = OrdTV::lane_stride(kmax), b = OrdER::lane_stride(kmax);
+  return (size_t)lanes * (a > b ? a : b);
+}
+#define ORD_SMEM(L) (sizeof(float) * ORD_NST * L::CHUNK)
+
 // ORD = RBV_REDUCE_ORDERED: instead of FP64 partial sums the block leaves the ten float32 addends of every keyline in ten planes
 // (`rows`, zeros where the reference adds nothing: x + 0 == x exactly); k_chain_tryvel, launched behind it, adds them in keyline order.
 template <int KPT, bool ORD>
@@ -900,9 +922,9 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
     }
     tv_st<KPT, int>(Ko.match_fwd + o, fwd, nvalid);                                    // core.cpp:87
     if constexpr (ORD) {
-      const size_t ps = (size_t)P.lanes * P.kmax;
+      float* dst = rows + (size_t)b * OrdTV::lane_stride(P.kmax) + OrdTV::at(idx0);   // KPT divides TV_CH: the KPT keylines share a chunk row
 #pragma unroll
-      for (int a = 0; a < 10; ++a) tv_st<KPT, float>(rows + a * ps + o, oadd[a], nvalid);
+      for (int a = 0; a < 10; ++a) tv_st<KPT, float>(dst + a * OrdTV::RS, oadd[a], nvalid);
     }
   }
   // carried |fi| in keyline order: thread aggregate = its last matched keyline, inclusive scan over the threads of the warp
@@ -1008,69 +1030,73 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel
 // Round 2 first ran the chain warps INSIDE the evaluation launch, fed block by block through release/acquire flags, to hide the
 // chain behind the evaluation; that version produced lane-dependent sums under load on the B200 (no cause found by inspection) and
 // was dropped for this two-kernel form: evaluation, then chain - nothing to synchronise but the kernel boundary.
-#define ORD_NST 4
-#define ORD_PAD 4             // floats behind a staged row: row r of a chunk starts at bank 4 r, so LDS.128 of different rows never collide
-#define TV_CH 256             // keylines per staged chunk: tryVel (10 rows) / extRotVel (27 rows). The per-chunk work (bulk-copy issue, wait,
-#define ER_CH 128             // warp syncs) is some hundreds of cycles: it has to be small against CH x 4 cycles of chain
-// Staging: one TMA bulk copy (cp.async.bulk, CH x 4 bytes) per row and chunk, issued by lane r for row r, completion counted in bytes on
-// the stage's mbarrier. (The first form staged with 16-byte cp.async: 80 - 108 LDGSTS in flight per thread; that version added a wrong
-// chunk now and then - deterministically on 200 k-keyline chains - while the same chain over 4 or 7 rows, at most 64 in flight, was
-// bit-exact on every test. One bulk copy per lane and stage has nothing of that kind to overflow.)
-template <int NROWS, int CH>
-__device__ __forceinline__ float ordered_chain(const float* __restrict__ rows, size_t ps, size_t base, int n, float* ring,
-                                               unsigned long long* bars /* [ORD_NST], shared */, float* dbg = nullptr) {
-  constexpr int RS = CH + ORD_PAD;
-  const int lane = threadIdx.x & 31;
+
+// sixteen float32 adds in keyline order
+__device__ __forceinline__ void ord_add16(float& s, const float4& a, const float4& b, const float4& c, const float4& d) {
+  s += a.x; s += a.y; s += a.z; s += a.w; s += b.x; s += b.y; s += b.z; s += b.w;
+  s += c.x; s += c.y; s += c.z; s += c.w; s += d.x; s += d.y; s += d.z; s += d.w;
+}
+// CTA = 2 warps. Warp 1 (one thread) is the loader: waits for a free stage, arms its `full` barrier with the chunk's bytes and issues the
+// bulk copy. Warp 0 is the chain: lane a adds row a of every staged chunk in keyline order, then releases the stage (`empty`).
+// Returns the sum in lanes < NROWS of warp 0; warp 1 returns 0 and has nothing left to do.
+template <typename L>
+__device__ __forceinline__ float ordered_chain(const float* __restrict__ lane_rows, int n, float* ring,
+                                               unsigned long long* bars /* [2 * ORD_NST], shared: full, empty */, float* dbg = nullptr) {
+  constexpr int NROWS = L::CHUNK / L::RS, CH = L::RS - ORD_PAD, RS = L::RS, CHUNK = L::CHUNK;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nch = (n + CH - 1) / CH;
-  if (lane == 0) {
-    for (int i = 0; i < ORD_NST; ++i) mbar_init(bars + i, 1u);
+  unsigned long long* full = bars;
+  unsigned long long* empty = bars + ORD_NST;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2 * ORD_NST; ++i) mbar_init(bars + i, 1u);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncwarp();
-  int issued = 0;
+  __syncthreads();
   float s = 0.0f;
-  for (int c = 0; c < nch; ++c) {
-    for (; issued < nch && issued < c + ORD_NST; ++issued) {   // up to ORD_NST chunks in flight
-      const int stage = issued % ORD_NST;
-      if (lane == 0) mbar_arrive_expect_tx(bars + stage, (unsigned)(NROWS * CH * 4));
-      __syncwarp();
-      if (lane < NROWS)
-        bulk_g2s(ring + (size_t)stage * NROWS * RS + lane * RS, rows + (size_t)lane * ps + base + (size_t)issued * CH, (unsigned)(CH * 4), bars + stage);
-    }
-    mbar_wait(bars + c % ORD_NST, (unsigned)((c / ORD_NST) & 1));
-    const int cnt = min(CH, n - c * CH);
-    if (lane < NROWS) {   // lane a adds accumulator a: nothing but the load and the dependent FADD on this warp (the FP32 pipe takes a
-      // 3-register instruction every 2 cycles per scheduler, so one FMUL per keyline next to the FADD already makes the 4-cycle chain slip:
-      // measured 8 cycles per keyline with the products formed here)
-      const float4* ra = reinterpret_cast<const float4*>(ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS);
-      const int n16 = cnt >> 4;
-      float4 a0, a1, a2, a3;
-      if (n16 > 0) { a0 = ra[0]; a1 = ra[1]; a2 = ra[2]; a3 = ra[3]; }
-      // unroll 1: nvcc 12.9 unrolls this loop by 8 with 4 / 2 / 1-block remainder sections, and in the remainder sections the prefetch
-      // for the NEXT section is addressed from the already advanced block counter plus the old offset (block b + 8 instead of b + 4):
-      // chunks with (n16 & 7) in {3, 5, 6, 7} added a block from beyond the chunk. One block per trip has no remainder to get wrong, and the
-      // FADD chain (64 cycles per block) hides the loop overhead.
+  if (warp == 1) {
+    if (lane == 0) {
 #pragma unroll 1
-      for (int b16 = 0; b16 < n16; ++b16) {
-        float4 b0 = a0, b1 = a1, b2 = a2, b3 = a3;
-        if (b16 + 1 < n16) { a0 = ra[4 * b16 + 4]; a1 = ra[4 * b16 + 5]; a2 = ra[4 * b16 + 6]; a3 = ra[4 * b16 + 7]; }   // next block's addends first
-        s += b0.x; s += b0.y; s += b0.z; s += b0.w; s += b1.x; s += b1.y; s += b1.z; s += b1.w;                       // float32 adds in keyline order
-        s += b2.x; s += b2.y; s += b2.z; s += b2.w; s += b3.x; s += b3.y; s += b3.z; s += b3.w;
+      for (int c = 0; c < nch; ++c) {
+        const int stage = c % ORD_NST;
+        if (c >= ORD_NST) mbar_wait(empty + stage, (unsigned)((c / ORD_NST - 1) & 1));   // the chain has released this stage's previous chunk
+        mbar_arrive_expect_tx(full + stage, (unsigned)(CHUNK * 4));
+        bulk_g2s(ring + (size_t)stage * CHUNK, lane_rows + (size_t)c * CHUNK, (unsigned)(CHUNK * 4), full + stage);
       }
+    }
+    return 0.0f;
+  }
+#pragma unroll 1
+  for (int c = 0; c < nch; ++c) {
+    const int stage = c % ORD_NST;
+    mbar_wait(full + stage, (unsigned)((c / ORD_NST) & 1));
+    const int cnt = min(CH, n - c * CH);
+    if (lane < NROWS) {   // lane a adds accumulator a: nothing but LDS.128 and the dependent FADDs on this warp (the FP32 pipe takes a 3-register
+      // instruction every 2 cycles per scheduler: one FMUL per keyline next to the FADD made the 4-cycle chain run at 8)
+      const float4* ra = reinterpret_cast<const float4*>(ring + (size_t)stage * CHUNK + lane * RS);
+      const int n16 = cnt >> 4;
+      // two 16-keyline blocks per trip, register sets A and B, next block loaded while the current one is added.
+      // unroll 1 on purpose: nvcc 12.9 unrolled the one-block form of this loop by 8 with 4 / 2 / 1-block remainder sections, and in those the
+      // prefetch for the NEXT section was addressed from the already advanced block counter plus the old offset (block b + 8 instead of b + 4):
+      // chunks with (n16 & 7) in {3, 5, 6, 7} added a block from beyond the chunk (found with RBV_DEBUG_CHAIN, tools/debug_ordered.py).
+      float4 A0, A1, A2, A3, B0, B1, B2, B3;
+      if (n16 > 0) { A0 = ra[0]; A1 = ra[1]; A2 = ra[2]; A3 = ra[3]; }
+      int b16 = 0;
+#pragma unroll 1
+      for (; b16 + 2 <= n16; b16 += 2) {
+        const float4* rb = ra + 4 * b16;
+        B0 = rb[4]; B1 = rb[5]; B2 = rb[6]; B3 = rb[7];
+        ord_add16(s, A0, A1, A2, A3);
+        if (b16 + 2 < n16) { A0 = rb[8]; A1 = rb[9]; A2 = rb[10]; A3 = rb[11]; }
+        ord_add16(s, B0, B1, B2, B3);
+      }
+      if (b16 < n16) ord_add16(s, A0, A1, A2, A3);
       const float* rt = reinterpret_cast<const float*>(ra);
 #pragma unroll 1
       for (int i = n16 * 16; i < cnt; ++i) s += rt[i];
     }
-    if (dbg && lane == 0) dbg[c] = s;   // debug: running sum of accumulator 0 after every chunk
-    if (dbg && c == nch - 1) {          // debug: the last chunk as this warp sees it in shared memory, every row
-      if (lane == 0) { dbg[nch] = (float)cnt; dbg[nch + 1] = (float)n; }
-      if (lane < NROWS) {
-        const float* rr = ring + (size_t)(c % ORD_NST) * NROWS * RS + lane * RS;
-        for (int i = 0; i < RS; ++i) dbg[64 + lane * RS + i] = rr[i];
-      }
-    }
-    fence_proxy_async();   // this thread's reads of the slot are ordered before the bulk copy that refills it (generic -> async proxy)
+    if (dbg && lane == 0) dbg[c] = s;   // debug (RBV_DEBUG_CHAIN): running sum of accumulator 0 after every chunk
     __syncwarp();
+    if (lane == 0) mbar_arrive(empty + stage);
   }
   return s;
 }
@@ -1082,14 +1108,14 @@ __global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __
   tryvel_fastn_body<4, true>(blockIdx.y, blockIdx.x, RBV_TV_PASS, rows);
 }
 // the ten sums of one tryVel call in keyline order + the LM step (core.cpp:130-139,159-185); one warp = one lane
-__global__ void __launch_bounds__(32) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
+__global__ void __launch_bounds__(64) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
                                                      const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
                                                      const __grid_constant__ DevParams P, float* dbg) {
   extern __shared__ __align__(128) float ord_ring[];
-  __shared__ __align__(8) unsigned long long bars[ORD_NST];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
   const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<10, TV_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count_o[b], ord_ring, bars,
-                                           dbg ? dbg + (size_t)b * P.kmax : nullptr);
+  const float s = ordered_chain<OrdTV>(rows + (size_t)b * OrdTV::lane_stride(P.kmax), count_o[b], ord_ring, bars, dbg ? dbg + (size_t)b * P.kmax : nullptr);
+  if (threadIdx.x >= 32) return;   // the loader warp
   float r[10];
 #pragma unroll
   for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
@@ -1155,7 +1181,7 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     if (ord) {   // evaluation (addends to c->prod), then the chain kernel: one warp per lane
       if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
       else { RBV_LAUNCH(c, k_tryvel_ord4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
-      RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (32), sizeof(float) * ORD_NST * 10 * (TV_CH + ORD_PAD), map->count, c->prod, c->lm, c->lane_out,
+      RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (64), ORD_SMEM(OrdTV), map->count, c->prod, c->lm, c->lane_out,
                  vel_ptr, vel_stride, lm_call, P, getenv("RBV_DEBUG_CHAIN") ? c->fiabs : nullptr);
     }
     else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
@@ -1587,15 +1613,15 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
   if (warp == 0) extrot_finish_warp(result, lane_out + (size_t)b * OUT_STRIDE, s_sys);
 }
 
-// RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline to 27 planes (zeros for unmatched keylines);
-// k_chain_extrot behind it adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
+// RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline into the chunked addend layout (OrdER; zeros for
+// unmatched keylines); k_chain_extrot behind it adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
 __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
                                                        float* __restrict__ rows, const __grid_constant__ DevParams P) {
   const int t = threadIdx.x;
-  const size_t ps = (size_t)P.lanes * P.kmax;
   const int b = blockIdx.y, blk = blockIdx.x, n = count[b];
   if (blk * TV_TPB * ER_KPT >= n) return;
   const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
+  float* lane_rows = rows + (size_t)b * OrdER::lane_stride(P.kmax);
   ExtRotIn in[ER_KPT];
 #pragma unroll
   for (int j = 0; j < ER_KPT; ++j) {                // every load of the thread's ER_KPT keylines first (one round trip)
@@ -1609,27 +1635,47 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
     if (idx >= n) continue;
     float r[7];
     extrot_row_in(in[j], v0, v1, v2, P, r);         // zeros for an unmatched keyline: x + 0 == x
-    const size_t o = (size_t)b * P.kmax + idx;
+    float* dst = lane_rows + OrdER::at(idx);
     int k = 0;                                      // the 27 float32 products of Phi^T Phi (upper triangle, row-major) and Phi^T Y, operators.hh:200-208
 #pragma unroll
     for (int a = 0; a < 6; ++a)
 #pragma unroll
-      for (int q = a; q < 6; ++q) rows[(size_t)(k++) * ps + o] = r[a] * r[q];
+      for (int q = a; q < 6; ++q) dst[(k++) * OrdER::RS] = r[a] * r[q];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) rows[(size_t)(21 + a) * ps + o] = r[a] * r[6];
+    for (int a = 0; a < 6; ++a) dst[(21 + a) * OrdER::RS] = r[a] * r[6];
   }
 }
-__global__ void __launch_bounds__(32) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,
+__global__ void __launch_bounds__(64) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,
                                                      const __grid_constant__ DevParams P) {
   extern __shared__ __align__(128) float ord_ring[];
-  __shared__ __align__(8) unsigned long long bars[ORD_NST];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
   __shared__ double s_res[27];
   __shared__ float s_sys[42];
   const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<27, ER_CH>(rows, (size_t)P.lanes * P.kmax, (size_t)b * P.kmax, count[b], ord_ring, bars);
+  const float s = ordered_chain<OrdER>(rows + (size_t)b * OrdER::lane_stride(P.kmax), count[b], ord_ring, bars);
+  if (threadIdx.x >= 32) return;   // the loader warp
   if (lane < 27) s_res[lane] = (double)s;
   __syncwarp();
   extrot_finish_warp(s_res, lane_out + (size_t)b * OUT_STRIDE, s_sys);
+}
+
+// debug tap behind rbv_debug_read_addends: row `plane` (0..9 tryVel, 100..126 extRotVel) of one lane's addends, keylines [0, n), as the last
+// evaluation kernel left them. The caller has synchronised the stream.
+int tr_debug_addends(rbv_ctx* c, int plane, int lane, float* out, int n) {
+  const int K = c->P.kmax;
+  if (tr_ordered_legacy(c)) {
+    const int a = plane >= 100 ? plane - 100 : plane;
+    RBV_CUDA(cudaMemcpy(out, c->prod + ((size_t)a * c->P.lanes + lane) * K, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    return RBV_OK;
+  }
+  const bool er = plane >= 100;
+  const int a = er ? plane - 100 : plane, CH = er ? ER_CH : TV_CH;
+  const size_t chunk = er ? OrdER::CHUNK : OrdTV::CHUNK, rs = er ? OrdER::RS : OrdTV::RS;
+  const float* src = c->prod + (size_t)lane * (er ? OrdER::lane_stride(K) : OrdTV::lane_stride(K)) + a * rs;
+  const int nch = (n + CH - 1) / CH;
+  if (nch) RBV_CUDA(cudaMemcpy2D(out, sizeof(float) * CH, src, sizeof(float) * chunk, sizeof(float) * CH, (size_t)(nch - 1), cudaMemcpyDeviceToHost));
+  if (nch) RBV_CUDA(cudaMemcpy(out + (size_t)(nch - 1) * CH, src + (size_t)(nch - 1) * chunk, sizeof(float) * (size_t)(n - (nch - 1) * CH), cudaMemcpyDeviceToHost));
+  return RBV_OK;
 }
 
 int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
@@ -1642,7 +1688,7 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
   } else if (c->reduce_mode == RBV_REDUCE_ORDERED) {
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
     RBV_LAUNCH(c, k_extrot_ord, (dim3(nb, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
-    RBV_LAUNCH(c, k_chain_extrot, (P.lanes), (32), sizeof(float) * ORD_NST * 27 * (ER_CH + ORD_PAD), new_map->count, c->prod, c->lane_out, P);
+    RBV_LAUNCH(c, k_chain_extrot, (P.lanes), (64), ORD_SMEM(OrdER), new_map->count, c->prod, c->lane_out, P);
   } else {
     RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
@@ -1897,7 +1943,7 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 }
 
 int tr_init_ordered(void) {
-  RBV_CUDA(cudaFuncSetAttribute(k_chain_tryvel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ORD_NST * 10 * (TV_CH + ORD_PAD))));
-  RBV_CUDA(cudaFuncSetAttribute(k_chain_extrot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * ORD_NST * 27 * (ER_CH + ORD_PAD))));
+  RBV_CUDA(cudaFuncSetAttribute(k_chain_tryvel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
+  RBV_CUDA(cudaFuncSetAttribute(k_chain_extrot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdER)));
   return RBV_OK;
 }

@@ -72,18 +72,4 @@ for lane in range(2):
         flag = "" if H.bits(dbg[c]) == H.bits(want[c]) else "  <-- differs"
         print("  ", c, dbg[c], want[c], dbg[c] - prevk, want[c] - prevw, flag)
         prevk, prevw = dbg[c], want[c]
-RS = CH + 4
-for lane in range(2):
-    dump = np.zeros(64 + 10 * RS, np.float32)
-    capi.check(g.ctx.L.rbv_debug_read_addends(g.ctx.h, -1, lane, capi.ptr(dump), dump.size))
-    cnt, nn = int(dump[nch]), int(dump[nch + 1])
-    print("lane", lane, "kernel cnt", cnt, "n", nn)
-    for pl in range(10):
-        buf = np.zeros(n, np.float32)
-        capi.check(g.ctx.L.rbv_debug_read_addends(g.ctx.h, pl, lane, capi.ptr(buf), n))
-        seen = dump[64 + pl * RS: 64 + pl * RS + RS]
-        want = buf[(nch - 1) * CH:]
-        bad = np.flatnonzero(H.bits(seen[:len(want)]) != H.bits(want))
-        print("   row", pl, "staged vs plane over", len(want), "elements: mismatches", len(bad), bad[:12].tolist(),
-              "seen", seen[bad[:4]].tolist(), "want", want[bad[:4]].tolist(), " beyond cnt (16):", seen[len(want):len(want) + 16].tolist()[:6])
 g.close()
