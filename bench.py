@@ -381,6 +381,7 @@ def run_b200(args):
         pipe.ctx.sync()
         trace("warm-up done")
         kl_sum = match_sum = 0.0
+        kl_max = 0.0
         win_ms, launches = [], 0
         sampler = ClockSampler(local, sampler_core); sampler.start()
         for w in range(windows):
@@ -391,6 +392,7 @@ def run_b200(args):
             for _ in range(K):
                 out = pipe.push(device_ptr=ptr(t), **pargs(t)); t += 1
                 kl_sum += float(out["keylines"].sum()); match_sum += float(out["matches"].sum())
+                kl_max = max(kl_max, float(out["keylines"].max()))
             pipe.ctx.sync()                      # the front end enqueued ahead belongs to the window too: K detects + K tracker passes between the events
             ev1.record(stream)
             barrier()
@@ -399,16 +401,21 @@ def run_b200(args):
             trace(f"window {w}: {win_ms[-1]:.2f} ms")
         clocks = sampler.result()
         res = {"win_ms": win_ms, "ms": float(np.median(win_ms)), "clocks": clocks, "launches": int(launches),
-               "K_mean": kl_sum / (B * K * windows), "matches": match_sum / (B * K * windows),
+               "K_mean": kl_sum / (B * K * windows), "K_max": kl_max, "matches": match_sum / (B * K * windows),
                "probes": pipe.ctx.probe_count(0) / max(1.0, float(out["keylines"][0])), "table": table}
-        if profile:   # the dominant kernel's events in the shipped two-stream schedule, outside the timed windows
+        if profile:   # the dominant kernel's events in the shipped two-stream schedule, outside the timed windows; then the same for the
+            # dominant kernel that only streams (an ORDERED evaluation launch carries its lanes' serial float32 add chains: a latency floor)
             top = max(table, key=lambda n: table[n][0])
-            pipe.ctx.profile_reset(); pipe.ctx.profile_set(top)
+            stream_only = [n for n in table if n not in CHAIN_K]
+            top_hbm = max(stream_only, key=lambda n: table[n][0]) if stream_only else top
             nprof = min(K, 10)
-            for _ in range(nprof):
-                pipe.push(device_ptr=ptr(t), **pargs(t)); t += 1
-            pipe.ctx.sync()
-            res["top"], res["prof"], res["prof_steps"] = top, pipe.ctx.profile_read()[top], nprof
+            res["top"], res["top_hbm"], res["prof_steps"], res["prof"] = top, top_hbm, nprof, {}
+            for name in dict.fromkeys((top, top_hbm)):
+                pipe.ctx.profile_reset(); pipe.ctx.profile_set(name)
+                for _ in range(nprof):
+                    pipe.push(device_ptr=ptr(t), **pargs(t)); t += 1
+                pipe.ctx.sync()
+                res["prof"][name] = pipe.ctx.profile_read()[name]
             pipe.ctx.profile_set(-1)
         pipe.close()
         return res
@@ -427,27 +434,53 @@ def run_b200(args):
     frames_total = sum_over_ranks(B * K)
     value = frames_total / (ms * 1e-3)
     K_mean, probes = main["K_mean"], main["probes"]
-    top_ms, top_n, top_launches = main["prof"]
-    # planes per launch of the box-pass kernels: pass 0 = 1 (rowscan) / 1+1 (colbox x2 launches), passes 1,2 = 2
-    planes = {"k_rowscan": 5.0 / 3.0, "k_rowscan4": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0, "k_boxpass2": 11.0 / 6.0}.get(top, 1.0)
-    words = B * N if top == "k_fill" else 0
-    abytes = roofline.kernel_bytes(top, N, K_mean, B, planes=planes, P=probes, words=words)
-    achieved = abytes / (top_ms / max(1, top_n) * 1e-3) / 1e9
-    # DRAM traffic of the same kernel from the committed `ncu --set full` capture of this command (64 lanes, 752x480);
-    # only quoted when the run has the capture's shape
-    traffic, traffic_src = None, None
-    for tname in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"):
-        tpath = os.path.join(ROOT, "profiles", tname)
-        if traffic is None and os.path.exists(tpath) and B == LANES_PER_GPU and args.config == "C2":
-            tj = json.load(open(tpath))
-            if top in tj.get("bytes_per_launch", {}):
-                traffic, traffic_src = float(tj["bytes_per_launch"][top]), f"profiles/{tname} (" + tj.get("source", "") + ")"
+    def roof(name):
+        """roofline object of one kernel: algorithmic bytes of a launch / its CUDA-event time, in the shipped schedule and alone"""
+        k_ms, k_n, k_launches = main["prof"][name]
+        # planes per launch of the box-pass kernels: pass 0 = 1 (rowscan) / 1+1 (colbox x2 launches), passes 1,2 = 2
+        planes = {"k_rowscan": 5.0 / 3.0, "k_rowscan4": 5.0 / 3.0, "k_colbox": 6.0 / 4.0, "k_boxpass": 11.0 / 6.0, "k_boxpass2": 11.0 / 6.0}.get(name, 1.0)
+        words = B * N if name == "k_fill" else 0
+        abytes = roofline.kernel_bytes(name, N, K_mean, B, planes=planes, P=probes, words=words)
+        achieved = abytes / (k_ms / max(1, k_n) * 1e-3) / 1e9
+        # DRAM traffic of the same kernel from the committed `ncu --set full` capture of this command (64 lanes, 752x480);
+        # only quoted when the run has the capture's shape
+        traffic, traffic_src = None, None
+        for tname in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"):
+            tpath = os.path.join(ROOT, "profiles", tname)
+            if traffic is None and os.path.exists(tpath) and B == LANES_PER_GPU and args.config == "C2":
+                tj = json.load(open(tpath))
+                if name in tj.get("bytes_per_launch", {}):
+                    traffic, traffic_src = float(tj["bytes_per_launch"][name]), f"profiles/{tname} (" + tj.get("source", "") + ")"
+        alone_ms = table[name][0] / max(1, table[name][1])
+        r = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+             "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
+             "avg_launch_ms": k_ms / max(1, k_n), "launches_timed": k_n,
+             "measured_in": f"{main['prof_steps']} steps of the same schedule right behind the timed windows (plain stream launches: "
+                            "events cannot bracket a kernel inside a replayed graph)",
+             "kernel_share_of_step": (k_ms / max(1, k_n)) * (k_launches / main["prof_steps"]) / (ms / K),
+             # with the two-stream schedule the events around a kernel also see the other stream's kernels that share the SMs with it;
+             # `alone` = the same kernel bracketed the same way in the in-order warm-up step (one stream, every kernel serialised) -
+             # the figure that compares with the ncu launch list
+             "concurrent": bool(lag),
+             "alone": {"avg_launch_ms": alone_ms, "achieved": abytes / (alone_ms * 1e-3) / 1e9, "frac": abytes / (alone_ms * 1e-3) / 1e9 / peak,
+                       "share_of_in_order_step": table[name][0] / sum(v[0] for v in table.values()),
+                       "in_order_step_kernel_sum_ms": sum(v[0] for v in table.values())}}
+        if name in CHAIN_K:
+            # the launch carries one serial float32 add chain per lane (the reference's summation order): its floor is the longest lane's
+            # keylines x one dependent FADD (4 cycles) at the SM clock, whatever the bandwidth
+            kmax_lane = float(main["K_max"])
+            floor_ms = kmax_lane * 4.0 / (main["clocks"]["sm_mhz"] * 1e3) if main["clocks"].get("sm_mhz") else None
+            r["latency_floor"] = {"what": "one dependent float32 add per keyline and accumulator, in keyline order, one warp per lane (bit-exact sums)",
+                                  "longest_lane_keylines": kmax_lane, "cycles_per_keyline": 4, "floor_ms": floor_ms,
+                                  "floor_over_alone": (floor_ms / alone_ms) if floor_ms else None}
+        return r
+
+    top_hbm = main["top_hbm"]
     frame_gbs = roofline.frame_bytes(N, K_mean, probes) * value / max(1, world) / 1e9
     fast_parity = None
     fpath = os.path.join(ROOT, "profiles", "r02_fast_mode_report.json")
     if os.path.exists(fpath):
         fast_parity = json.load(open(fpath)).get("summary")
-    alone_ms = table[top][0] / max(1, table[top][1])
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"batched replay: {B} independent EuRoC-shaped {spec.cam.cols}x{spec.cam.rows} sequences per GPU "
@@ -466,22 +499,11 @@ def run_b200(args):
                        "parallelism": f"replicas x{world} (no collective)",
                        "host_threads": {"launch_core": launch_core, "sampler_core": sampler_core, "slice": core_slice},
                        "l2": f"per-step working set {B} lanes x ~14 MB >> 126 MB L2 (inputs larger than L2, no flush needed)"},
-            "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": abytes,
-                         "avg_launch_ms": top_ms / max(1, top_n), "launches_timed": top_n,
-                         "measured_in": f"{main['prof_steps']} steps of the same schedule right behind the timed windows (plain stream launches: "
-                                        "events cannot bracket a kernel inside a replayed graph)",
-                         "kernel_share_of_step": (top_ms / max(1, top_n)) * (top_launches / main["prof_steps"]) / (ms / K),
-                         # with the two-stream schedule the events around a front-end kernel also see the tracker kernels that share
-                         # the SMs with it; `alone` = the same kernel bracketed the same way in the in-order warm-up step (one stream,
-                         # every kernel serialised) - the figure that compares with the ncu launch list
-                         "concurrent": bool(lag),
-                         "alone": {"avg_launch_ms": alone_ms, "achieved": abytes / (alone_ms * 1e-3) / 1e9, "frac": abytes / (alone_ms * 1e-3) / 1e9 / peak,
-                                   "share_of_in_order_step": table[top][0] / sum(v[0] for v in table.values()),
-                                   "in_order_step_kernel_sum_ms": sum(v[0] for v in table.values())},
-                         "frame_level": {"achieved": frame_gbs, "frac": frame_gbs / peak,
-                                         "bytes_per_frame": roofline.frame_bytes(N, K_mean, probes)}},
+            "roofline": dict(roof(top), frame_level={"achieved": frame_gbs, "frac": frame_gbs / peak,
+                                                     "bytes_per_frame": roofline.frame_bytes(N, K_mean, probes)}),
             "clocks": main["clocks"], "gpu_launches": main["launches"]}
+    if top_hbm != top:   # the dominant kernel that only streams, measured the same way
+        line["roofline_streaming_kernel"] = roof(top_hbm)
 
     # ---- leg 1b: the other reduce mode ---------------------------------------------------------------------------------
     if not args.no_fast:
@@ -587,6 +609,7 @@ def run_b200(args):
 
 SCALE_K = ("k_boxpass", "k_boxpass2", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
 DETECT_K = ("k_detect_flags", "k_detect_scan", "k_detect_emit", "k_detect_emit_wide", "k_join", "k_tune")
+CHAIN_K = ("k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_extrot_ord", "k_chain_extrot", "k_tryvel_reduce", "k_extrot_reduce")   # launches that carry a serial add chain
 TRYVEL_K = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_tryvel_eval", "k_tryvel_reduce")
 
 

@@ -312,6 +312,8 @@ static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg
   RBV_CUDA(dalloc(&c->ticket, B));
   RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
+  RBV_CUDA(dalloc(&c->ord_flags, B * c->nblk));
+  RBV_CUDA(cudaMemset(c->ord_flags, 0, sizeof(int) * B * c->nblk));
   RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->rowcount, 0, sizeof(int) * B * P.rows));          // kept clean by k_detect_scan
   RBV_CUDA(cudaMemset(c->fwd_head, 0xFF, sizeof(int) * B * K));            // kept empty (-1) by k_fwd_resolve
@@ -361,7 +363,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaStreamSynchronize(c->stream);
   void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->last_count, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
-                 c->partials, c->ticket, c->blkagg, c->tgt};
+                 c->partials, c->ticket, c->blkagg, c->tgt, c->ord_flags};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {

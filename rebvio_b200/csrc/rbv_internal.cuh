@@ -133,6 +133,7 @@ struct rbv_ctx {
   // FAST-mode reductions: per-block FP64 partials, per-lane tickets, per-block "last matched |fi|" (ping-pong)
   double* partials;  // [B][nblk][27]
   unsigned* ticket;  // [B]
+  int* ord_flags;    // [B][nblk] ORDERED: evaluation block j of the running k_tryvel_ord* launch has left its addends (set by the block, cleared by the chain's loader)
   float* blkagg;     // [2][B][nblk]
   int nblk;          // blocks of 256 keylines per lane
   int tv_parity;
@@ -325,6 +326,13 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
       else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
     }
   }
+}
+// one non-blocking probe of a phase
+__device__ __forceinline__ bool mbar_test(unsigned long long* bar, unsigned parity) {
+  unsigned ok;
+  asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+               : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
 }
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"

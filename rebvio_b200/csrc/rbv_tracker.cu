@@ -778,10 +778,10 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
 }
 
 // ---- RBV_REDUCE_ORDERED addend layout (the chain kernels are further down, behind the FAST kernels) ----
-#define ORD_NST 4
+#define ORD_NST 4             // stages per lane: 83 / 112 KB of shared memory, one chain CTA per SM anyway
 #define ORD_PAD 4             // floats behind a row of a chunk: row r starts at bank 4 r, so the LDS.128 of different rows never collide
-#define TV_CH 256             // keylines per chunk: tryVel (10 rows) / extRotVel (27 rows)
-#define ER_CH 128
+#define TV_CH 512             // keylines per chunk: tryVel (10 rows) / extRotVel (27 rows). Per chunk the chain warp spends ~100 cycles on barriers
+#define ER_CH 256             // and addressing (measured 400 with 256 / 128-keyline chunks and the wait in line): small against CH x 4 cycles of adds
 // Addend layout in HBM (c->prod): per lane, chunk after chunk; a chunk = NROWS rows of CH + ORD_PAD floats, i.e. exactly the image of one
 // shared-memory stage, so ONE bulk copy (cp.async.bulk, 10.4 / 14.3 KB) per chunk stages it - issued by one thread of a loader warp, the chain
 // warp never spends an issue slot on it. (Round 2 first kept [row][lane][keyline] planes and one copy per row and chunk from the chain warp
@@ -808,7 +808,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                                                          double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                          const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
                                                          LMState* lm, float* lane_out, int lm_call, const DevParams& P,
-                                                         float* __restrict__ rows) {
+                                                         float* __restrict__ rows, int* __restrict__ ord_flags = nullptr) {
   __shared__ double sm[(TV_TPB / 32) * 10];
   __shared__ double result[10];
   __shared__ float warp_val[TV_TPB / 32];
@@ -950,7 +950,11 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
       if (lane == 0) sm[warp * 10 + a] = v;
     }
   }
+  if constexpr (ORD) { if (ord_flags) __threadfence(); }   // this thread's addends are visible device-wide before the block's flag goes up
   __syncthreads();
+  if constexpr (ORD) {   // chain role of the same launch (k_tryvel_ord*, blockIdx.y == 0): its loader polls this flag before it stages the block's chunks
+    if (ord_flags && t == 0) asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+  }
   if (!ehas || !has) {
     for (int w2 = warp - 1; w2 >= 0; --w2)
       if (warp_has[w2]) {
@@ -1011,6 +1015,10 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                       const unsigned* __restrict__ field, const float* __restrict__ vel_ptr, int vel_stride, const float* __restrict__ sr_ptr,    \
                       int sr_stride, double* __restrict__ partials, unsigned* __restrict__ ticket, const float* __restrict__ agg_prev,            \
                       float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const __grid_constant__ DevParams P
+#define RBV_TV_PARAMS_DEV KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,         \
+                          const unsigned* __restrict__ field, const float* __restrict__ vel_ptr, int vel_stride, const float* __restrict__ sr_ptr, \
+                          int sr_stride, double* __restrict__ partials, unsigned* __restrict__ ticket, const float* __restrict__ agg_prev,         \
+                          float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const DevParams& P
 #define RBV_TV_PASS Ko, count_o, thr_o, tgt, field, vel_ptr, vel_stride, sr_ptr, sr_stride, partials, ticket, agg_prev, agg_cur, nblk, lm, lane_out, lm_call, P
 __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
 __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
@@ -1039,9 +1047,12 @@ __device__ __forceinline__ void ord_add16(float& s, const float4& a, const float
 // CTA = 2 warps. Warp 1 (one thread) is the loader: waits for a free stage, arms its `full` barrier with the chunk's bytes and issues the
 // bulk copy. Warp 0 is the chain: lane a adds row a of every staged chunk in keyline order, then releases the stage (`empty`).
 // Returns the sum in lanes < NROWS of warp 0; warp 1 returns 0 and has nothing left to do.
+// `flags` (chain role inside the evaluation launch): flags[j] goes to 1 when evaluation block j (kpb keylines) has left its addends; the
+// loader takes (and clears) the flags of the blocks a chunk covers before it copies the chunk. nullptr: the addends are complete (kernel boundary).
 template <typename L>
 __device__ __forceinline__ float ordered_chain(const float* __restrict__ lane_rows, int n, float* ring,
-                                               unsigned long long* bars /* [2 * ORD_NST], shared: full, empty */, float* dbg = nullptr) {
+                                               unsigned long long* bars /* [2 * ORD_NST], shared: full, empty */, float* dbg = nullptr,
+                                               int* flags = nullptr, int kpb = 1) {
   constexpr int NROWS = L::CHUNK / L::RS, CH = L::RS - ORD_PAD, RS = L::RS, CHUNK = L::CHUNK;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nch = (n + CH - 1) / CH;
@@ -1051,13 +1062,31 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ lane_ro
     for (int i = 0; i < 2 * ORD_NST; ++i) mbar_init(bars + i, 1u);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
+  asm volatile("bar.sync 1, 64;" ::: "memory");   // the two warps of the chain (the CTA may have more threads: they have left)
   float s = 0.0f;
   if (warp == 1) {
     if (lane == 0) {
+      int have = 0;
 #pragma unroll 1
       for (int c = 0; c < nch; ++c) {
         const int stage = c % ORD_NST;
+        if (flags) {
+          const int need = (min(n, (c + 1) * CH) - 1) / kpb + 1;   // evaluation blocks up to the last keyline of this chunk
+          for (; have < need; ++have) {
+            int v;
+            long long t0 = 0;
+            for (int spin = 0;; ++spin) {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + have) : "memory");
+              if (v) break;
+              if ((spin & 1023) == 1023) {
+                if (t0 == 0) t0 = clock64();
+                else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
+              }
+            }
+            flags[have] = 0;   // for the next launch (stream order)
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");   // the blocks' generic-proxy stores before this thread's async-proxy (bulk copy) reads
+        }
         if (c >= ORD_NST) mbar_wait(empty + stage, (unsigned)((c / ORD_NST - 1) & 1));   // the chain has released this stage's previous chunk
         mbar_arrive_expect_tx(full + stage, (unsigned)(CHUNK * 4));
         bulk_g2s(ring + (size_t)stage * CHUNK, lane_rows + (size_t)c * CHUNK, (unsigned)(CHUNK * 4), full + stage);
@@ -1065,10 +1094,14 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ lane_ro
     }
     return 0.0f;
   }
+  bool ready = false;
 #pragma unroll 1
   for (int c = 0; c < nch; ++c) {
     const int stage = c % ORD_NST;
-    mbar_wait(full + stage, (unsigned)((c / ORD_NST) & 1));
+    if (!ready) mbar_wait(full + stage, (unsigned)((c / ORD_NST) & 1));
+    // the next chunk's barrier is probed now and the answer used after this chunk's adds: the loader runs stages ahead, so the probe
+    // nearly always says yes and its ~150-cycle latency never sits in the chain (a no falls back to the blocking wait above)
+    ready = (c + 1 < nch) && mbar_test(full + (c + 1) % ORD_NST, (unsigned)(((c + 1) / ORD_NST) & 1));
     const int cnt = min(CH, n - c * CH);
     if (lane < NROWS) {   // lane a adds accumulator a: nothing but LDS.128 and the dependent FADDs on this warp (the FP32 pipe takes a 3-register
       // instruction every 2 cycles per scheduler: one FMUL per keyline next to the FADD made the 4-cycle chain run at 8)
@@ -1101,25 +1134,13 @@ __device__ __forceinline__ float ordered_chain(const float* __restrict__ lane_ro
   return s;
 }
 
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows) {
-  tryvel_fastn_body<2, true>(blockIdx.y, blockIdx.x, RBV_TV_PASS, rows);
-}
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows) {
-  tryvel_fastn_body<4, true>(blockIdx.y, blockIdx.x, RBV_TV_PASS, rows);
-}
-// the ten sums of one tryVel call in keyline order + the LM step (core.cpp:130-139,159-185); one warp = one lane
-__global__ void __launch_bounds__(64) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
-                                                     const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
-                                                     const __grid_constant__ DevParams P, float* dbg) {
-  extern __shared__ __align__(128) float ord_ring[];
-  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
-  const int b = blockIdx.x, lane = threadIdx.x;
-  const float s = ordered_chain<OrdTV>(rows + (size_t)b * OrdTV::lane_stride(P.kmax), count_o[b], ord_ring, bars, dbg ? dbg + (size_t)b * P.kmax : nullptr);
-  if (threadIdx.x >= 32) return;   // the loader warp
+// warp 0 of a chain: the ten sums -> LM step (core.cpp:159-185) and the lane's outputs
+__device__ __forceinline__ void tryvel_chain_finish(float s, int b, LMState* lm, float* lane_out, const float* __restrict__ vel_ptr, int vel_stride,
+                                                    int lm_call, const DevParams& P) {
   float r[10];
 #pragma unroll
   for (int a = 0; a < 10; ++a) r[a] = __shfl_sync(0xFFFFFFFFu, s, a);
-  if (lane == 0) {
+  if ((threadIdx.x & 31) == 0) {
     float JtJ[9], JtF[3];
     const float score = r[0];
     JtJ[0] = r[1]; JtJ[4] = r[2]; JtJ[8] = r[3];
@@ -1134,6 +1155,40 @@ __global__ void __launch_bounds__(64) k_chain_tryvel(const int* __restrict__ cou
     for (int i = 0; i < 3; ++i) outp[OUT_JTF + i] = JtF[i];
     outp[OUT_SCORE] = score;
   }
+}
+// Evaluation + chain in ONE launch (ord_flags != nullptr): grid (lanes, 1 + blocks). Row y = 0 of the grid is dispatched first: one chain CTA
+// per lane (2 of its warps stay: chain + loader); rows y >= 1 are the evaluation blocks, block index fastest over the lanes, so every lane's
+// chain finds its first chunks after the first wave and the adds run behind the evaluation instead of after it. The evaluation never waits
+// for a chain, so any dispatch order terminates. ord_flags == nullptr: evaluation only, grid (lanes, blocks), k_chain_tryvel behind it.
+template <int KPT>
+__device__ __forceinline__ void tryvel_ord_entry(RBV_TV_PARAMS_DEV, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
+  const int b = blockIdx.x;
+  if (ord_flags && blockIdx.y == 0) {
+    if (threadIdx.x >= 64) return;
+    const float s = ordered_chain<OrdTV>(rows + (size_t)b * OrdTV::lane_stride(P.kmax), count_o[b], ord_ring, bars,
+                                         dbg ? dbg + (size_t)b * P.kmax : nullptr, ord_flags + (size_t)b * nblk, TV_TPB * KPT);
+    if (threadIdx.x < 32) tryvel_chain_finish(s, b, lm, lane_out, vel_ptr, vel_stride, lm_call, P);
+    return;
+  }
+  tryvel_fastn_body<KPT, true>(b, (int)blockIdx.y - (ord_flags ? 1 : 0), RBV_TV_PASS, rows, ord_flags);
+}
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
+  tryvel_ord_entry<2>(RBV_TV_PASS, rows, ord_flags, dbg);
+}
+__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
+  tryvel_ord_entry<4>(RBV_TV_PASS, rows, ord_flags, dbg);
+}
+// the two-kernel form (RBV_TUNE_ORDERED = 2): the ten sums of one tryVel call in keyline order + the LM step, behind the evaluation kernel
+__global__ void __launch_bounds__(64) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
+                                                     const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
+                                                     const __grid_constant__ DevParams P, float* dbg) {
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
+  const int b = blockIdx.x;
+  const float s = ordered_chain<OrdTV>(rows + (size_t)b * OrdTV::lane_stride(P.kmax), count_o[b], ord_ring, bars, dbg ? dbg + (size_t)b * P.kmax : nullptr);
+  if (threadIdx.x < 32) tryvel_chain_finish(s, b, lm, lane_out, vel_ptr, vel_stride, lm_call, P);
 }
 
 __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ agg,
@@ -1178,11 +1233,15 @@ int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
     if (ord && kpt == 1) kpt = 2;
     const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt);
 #define RBV_TV_ARGS map->k, map->count, map->threshold, c->tgt, c->field, vel_ptr, vel_stride, sr_ptr, sr_stride, c->partials, c->ticket, agg_prev, agg_cur, nblk, c->lm, c->lane_out, lm_call, P
-    if (ord) {   // evaluation (addends to c->prod), then the chain kernel: one warp per lane
-      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
-      else { RBV_LAUNCH(c, k_tryvel_ord4, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS, c->prod); }
-      RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (64), ORD_SMEM(OrdTV), map->count, c->prod, c->lm, c->lane_out,
-                 vel_ptr, vel_stride, lm_call, P, getenv("RBV_DEBUG_CHAIN") ? c->fiabs : nullptr);
+    if (ord) {   // evaluation (addends to c->prod) with the chain CTAs in the same launch, or (RBV_TUNE_ORDERED = 2) the chain kernel behind it
+      const bool two = c->tune[RBV_TUNE_ORDERED] == 2;
+      float* dbg = getenv("RBV_DEBUG_CHAIN") ? c->fiabs : nullptr;
+      int* flags = two ? nullptr : c->ord_flags;
+      const dim3 grid(P.lanes, nb + (two ? 0 : 1));
+      const size_t smem = two ? 0 : ORD_SMEM(OrdTV);
+      if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_ord2, (grid), (TV_TPB), smem, RBV_TV_ARGS, c->prod, flags, dbg); }
+      else { RBV_LAUNCH(c, k_tryvel_ord4, (grid), (TV_TPB), smem, RBV_TV_ARGS, c->prod, flags, dbg); }
+      if (two) RBV_LAUNCH(c, k_chain_tryvel, (P.lanes), (64), ORD_SMEM(OrdTV), map->count, c->prod, c->lm, c->lane_out, vel_ptr, vel_stride, lm_call, P, dbg);
     }
     else if (kpt == 1) { RBV_LAUNCH(c, k_tryvel_fast, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
     else if (kpt == 2) { RBV_LAUNCH(c, k_tryvel_fast2, (dim3(nb, P.lanes)), (TV_TPB), 0, RBV_TV_ARGS); }
@@ -1615,10 +1674,27 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_fast(KeylineSoA K, const int*
 
 // RBV_REDUCE_ORDERED: the 27 float32 products of Phi^T Phi / Phi^T Y of every keyline into the chunked addend layout (OrdER; zeros for
 // unmatched keylines); k_chain_extrot behind it adds them in keyline order (TooN operators.hh:200-208) and runs the 6x6 solve.
+// ord_flags != nullptr: grid (lanes, 1 + blocks), row y = 0 = one chain CTA per lane adding behind the evaluation blocks (as k_tryvel_ord*);
+// nullptr: evaluation only, grid (lanes, blocks), k_chain_extrot behind it.
 __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* __restrict__ count, const float* __restrict__ vel_ptr, int vel_stride,
-                                                       float* __restrict__ rows, const __grid_constant__ DevParams P) {
+                                                       float* __restrict__ rows, int* __restrict__ ord_flags, int nblk, float* lane_out,
+                                                       const __grid_constant__ DevParams P) {
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
+  __shared__ double s_res[27];
+  __shared__ float s_sys[42];
   const int t = threadIdx.x;
-  const int b = blockIdx.y, blk = blockIdx.x, n = count[b];
+  const int b = blockIdx.x, n = count[b];
+  if (ord_flags && blockIdx.y == 0) {
+    if (t >= 64) return;
+    const float s = ordered_chain<OrdER>(rows + (size_t)b * OrdER::lane_stride(P.kmax), n, ord_ring, bars, nullptr, ord_flags + (size_t)b * nblk, TV_TPB * ER_KPT);
+    if (t >= 32) return;
+    if (t < 27) s_res[t] = (double)s;
+    __syncwarp();
+    extrot_finish_warp(s_res, lane_out + (size_t)b * OUT_STRIDE, s_sys);
+    return;
+  }
+  const int blk = (int)blockIdx.y - (ord_flags ? 1 : 0);
   if (blk * TV_TPB * ER_KPT >= n) return;
   const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
   float* lane_rows = rows + (size_t)b * OrdER::lane_stride(P.kmax);
@@ -1643,6 +1719,11 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
       for (int q = a; q < 6; ++q) dst[(k++) * OrdER::RS] = r[a] * r[q];
 #pragma unroll
     for (int a = 0; a < 6; ++a) dst[(21 + a) * OrdER::RS] = r[a] * r[6];
+  }
+  if (ord_flags) {   // the block's addends are out: flag for the chain CTA's loader
+    __threadfence();
+    __syncthreads();
+    if (t == 0) asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
   }
 }
 __global__ void __launch_bounds__(64) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,
@@ -1687,8 +1768,10 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
     RBV_LAUNCH(c, k_extrot_reduce, (P.lanes), (512), 0, new_map->count, c->prod, c->lane_out, 1, P);
   } else if (c->reduce_mode == RBV_REDUCE_ORDERED) {
     const int nb = (c->nblk + ER_KPT - 1) / ER_KPT;
-    RBV_LAUNCH(c, k_extrot_ord, (dim3(nb, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->prod, P);
-    RBV_LAUNCH(c, k_chain_extrot, (P.lanes), (64), ORD_SMEM(OrdER), new_map->count, c->prod, c->lane_out, P);
+    const bool two = c->tune[RBV_TUNE_ORDERED] == 2 || c->tune[RBV_TUNE_ORDERED] == 3;
+    RBV_LAUNCH(c, k_extrot_ord, (dim3(P.lanes, nb + (two ? 0 : 1))), (TV_TPB), (two ? 0 : ORD_SMEM(OrdER)), new_map->k, new_map->count, vel_ptr, vel_stride,
+               c->prod, two ? nullptr : c->ord_flags, c->nblk, c->lane_out, P);
+    if (two) RBV_LAUNCH(c, k_chain_extrot, (P.lanes), (64), ORD_SMEM(OrdER), new_map->count, c->prod, c->lane_out, P);
   } else {
     RBV_LAUNCH(c, k_extrot_fast, (dim3((c->nblk + ER_KPT - 1) / ER_KPT, P.lanes)), (TV_TPB), 0, new_map->k, new_map->count, vel_ptr, vel_stride, c->partials, c->ticket, c->nblk, c->lane_out, P);
   }
@@ -1944,6 +2027,9 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 
 int tr_init_ordered(void) {
   RBV_CUDA(cudaFuncSetAttribute(k_chain_tryvel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
+  RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
   RBV_CUDA(cudaFuncSetAttribute(k_chain_extrot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdER)));
+  RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdER)));
   return RBV_OK;
 }

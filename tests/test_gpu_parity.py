@@ -47,11 +47,12 @@ def test_cuda_vs_reference_golden_teacher_forced(name):
 
 
 @pytest.mark.parametrize("name,nf,legacy,lanes", [("C5:320x240", 4, 0, 2), ("C1", 3, 0, 2), ("C2", 4, 0, 2), ("C3", 3, 0, 2), ("C2", 3, 1, 2),
-                                                  ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9)])
+                                                  ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9), ("C2", 3, 2, 2), ("C5:320x240", 4, 2, 5)])
 def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits.
-    legacy = RBV_TUNE_ORDERED 1: the ordered sums by one adding block per lane reading global memory (the first implementation)
-    instead of the chain kernels (k_chain_tryvel / k_chain_extrot: one warp per lane, addends staged through shared memory)."""
+    legacy = RBV_TUNE_ORDERED: 0 = the default (tryVel: evaluation blocks and one chain CTA per lane in ONE launch, the chain adding behind the
+    evaluation; k_extrot_ord likewise), 2 = the same chains as kernels of their own (k_chain_tryvel, k_chain_extrot) behind the evaluation,
+    1 = the first implementation (one adding block per lane reading global memory)."""
     spec, frames, R_rel = common.sequence(name, nf)
     cfg = common.cfgs_from_spec(spec)
     orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
@@ -62,11 +63,11 @@ def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     assert H.dirty(rep) == []
     assert common.x_rel_max(rep) <= common.X_RTOL_FLOOR
     names = g.ctx.profile_launches()
-    if legacy:
+    if legacy == 1:
         assert names.get("k_tryvel_reduce", 0) > 0 and names.get("k_extrot_reduce", 0) > 0 and names.get("k_extrot_ord", 0) == 0
     else:
         assert names.get("k_tryvel_ord2", 0) + names.get("k_tryvel_ord4", 0) > 0 and names.get("k_extrot_ord", 0) > 0
-        assert names.get("k_chain_tryvel", 0) > 0 and names.get("k_chain_extrot", 0) > 0 and names.get("k_tryvel_reduce", 0) == 0
+        assert (names.get("k_chain_tryvel", 0) > 0) == (legacy == 2) and (names.get("k_chain_extrot", 0) > 0) == (legacy == 2) and names.get("k_tryvel_reduce", 0) == 0
     g.close(); orc.close()
 
 

@@ -58,7 +58,7 @@ g.build_distance_field(gb)
 g.ctx.resetResiduals(ga)
 sc, JtJ, JtF = g.ctx.tryVel(ga, [0, 0, 0], 1e3)
 print("chain4 again: score lanes", sc)
-CH = 256
+CH = 512
 nch = (n + CH - 1) // CH
 for lane in range(2):
     buf = np.zeros(n, np.float32); dbg = np.zeros(nch, np.float32)
