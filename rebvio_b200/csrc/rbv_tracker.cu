@@ -635,6 +635,9 @@ __global__ void __launch_bounds__(1024) k_tryvel_reduce(KeylineSoA Ko, const int
 // matched |fi|" (blkagg, ping-pong per call) when the next call reads it. k_residual_resolve clears the markers after
 // the last call so the map never leaves the library with one.
 #define TV_TPB 256
+#ifndef TV_MINB
+#define TV_MINB 1   // minimum resident blocks per SM asked of ptxas for the tryVel evaluation kernels (A/B knob)
+#endif
 __device__ __forceinline__ float residual_lookback(const float* __restrict__ agg_lane, int blk) {
   for (int j = blk - 1; j >= 0; --j) {
     const float a = __ldcg(agg_lane + j);
@@ -778,10 +781,16 @@ template <int KPT, typename T> __device__ __forceinline__ void tv_st(T* p, const
 }
 
 // ---- RBV_REDUCE_ORDERED addend layout (the chain kernels are further down, behind the FAST kernels) ----
+#ifndef ORD_NST
 #define ORD_NST 4             // stages per lane: 83 / 112 KB of shared memory, one chain CTA per SM anyway
+#endif
 #define ORD_PAD 4             // floats behind a row of a chunk: row r starts at bank 4 r, so the LDS.128 of different rows never collide
+#ifndef TV_CH
 #define TV_CH 512             // keylines per chunk: tryVel (10 rows) / extRotVel (27 rows). Per chunk the chain warp spends ~100 cycles on barriers
+#endif
+#ifndef ER_CH
 #define ER_CH 256             // and addressing (measured 400 with 256 / 128-keyline chunks and the wait in line): small against CH x 4 cycles of adds
+#endif
 // Addend layout in HBM (c->prod): per lane, chunk after chunk; a chunk = NROWS rows of CH + ORD_PAD floats, i.e. exactly the image of one
 // shared-memory stage, so ONE bulk copy (cp.async.bulk, 10.4 / 14.3 KB) per chunk stages it - issued by one thread of a loader warp, the chain
 // warp never spends an issue slot on it. (Round 2 first kept [row][lane][keyline] planes and one copy per row and chunk from the chain warp
@@ -1021,7 +1030,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                           float* __restrict__ agg_cur, int nblk, LMState* lm, float* lane_out, int lm_call, const DevParams& P
 #define RBV_TV_PASS Ko, count_o, thr_o, tgt, field, vel_ptr, vel_stride, sr_ptr, sr_stride, partials, ticket, agg_prev, agg_cur, nblk, lm, lane_out, lm_call, P
 __global__ void __launch_bounds__(TV_TPB) k_tryvel_fast2(RBV_TV_PARAMS) { tryvel_fastn_body<2, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
+__global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_fast4(RBV_TV_PARAMS) { tryvel_fastn_body<4, false>(blockIdx.y, blockIdx.x, RBV_TV_PASS, nullptr); }
 
 // ---- RBV_REDUCE_ORDERED: the reference's float32 sums in keyline order --------------------------------------------------------
 // The reference adds its ten tryVel accumulators (and the 27 of extRotVel) sequentially in float32 over the keylines
@@ -1174,10 +1183,10 @@ __device__ __forceinline__ void tryvel_ord_entry(RBV_TV_PARAMS_DEV, float* __res
   }
   tryvel_fastn_body<KPT, true>(b, (int)blockIdx.y - (ord_flags ? 1 : 0), RBV_TV_PASS, rows, ord_flags);
 }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
+__global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_ord2(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
   tryvel_ord_entry<2>(RBV_TV_PASS, rows, ord_flags, dbg);
 }
-__global__ void __launch_bounds__(TV_TPB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
+__global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
   tryvel_ord_entry<4>(RBV_TV_PASS, rows, ord_flags, dbg);
 }
 // the two-kernel form (RBV_TUNE_ORDERED = 2): the ten sums of one tryVel call in keyline order + the LM step, behind the evaluation kernel
