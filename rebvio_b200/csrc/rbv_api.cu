@@ -688,18 +688,21 @@ extern "C" int rbv_detect_device(rbv_ctx* c, rbv_map* map, const float* d_images
   if (ts_us) memcpy(map->ts_us, ts_us, sizeof(uint64_t) * B);
   // the one kernel that reads the caller's frame buffer is launched directly; everything behind it works on the
   // context's own buffers and is replayed from a graph
+  // the distance field of this map follows its detect on the front-end stream: k_detect_emit then also writes the packed target records
+  // (one launch less; same values as k_pack_targets computes from what emit stores)
+  const bool fe_field = on_fe && c->tune[RBV_TUNE_FIELD_IN_FE] == 1;
+  if (fe_field) TRY(map_field_alloc(c, map));
   TRY(fe_scale_space(c, d_images, 1));
-  TRY(run_graphed(c, GK_DETECT, map, nullptr, fe_uses_fused_box(c, d_images), [&]() -> int {
+  TRY(run_graphed(c, GK_DETECT, map, nullptr, fe_uses_fused_box(c, d_images) + (fe_field ? 8 : 0), [&]() -> int {
     TRY(fe_scale_space(c, d_images, 2));
-    return fe_detect(c, map);
+    return fe_detect(c, map, fe_field ? map->tgt : nullptr);
   }));
   map->fe_valid = 0;
   map->field_built = 0;
-  if (on_fe && c->tune[RBV_TUNE_FIELD_IN_FE] == 1) {
-    TRY(map_field_alloc(c, map));
+  if (fe_field) {
     rbv_map* fm0 = c->field_map;
     int rc;
-    { FieldScope fs(c, map, true); rc = tr_build_field(c, map); }
+    { FieldScope fs(c, map, true); rc = tr_build_field(c, map, true); }
     c->field_map = fm0;   // host-side notion of the tracker's current field map: unchanged by a front end running ahead
     TRY(rc);
     map->field_built = 1;

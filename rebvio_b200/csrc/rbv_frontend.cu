@@ -1413,7 +1413,7 @@ __global__ void __launch_bounds__(1024) k_detect_scan(int* __restrict__ rowcount
 #define EM_MAXW 1024   // columns per row the shared list can hold (wider images take the direct path below)
 __global__ void __launch_bounds__(32 * EM_ROWS) k_detect_emit(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
                                                               const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
-                                                              const __grid_constant__ DevParams P, int wpr) {
+                                                              const __grid_constant__ DevParams P, int wpr, float4* __restrict__ tgt) {
   __shared__ unsigned short list[EM_ROWS][EM_MAXW];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.y, r = blockIdx.x * EM_ROWS + warp + 2;
@@ -1456,7 +1456,12 @@ __global__ void __launch_bounds__(32 * EM_ROWS) k_detect_emit(const float4* __re
     K.match_pos_img[o] = pi;
     K.grad[o] = make_float2(fr.x, fr.y);
     K.match_grad[o] = make_float2(0.0f, 0.0f);
-    K.gnorm[o] = sqrtf(fr.x * fr.x + fr.y * fr.y);
+    const float gn = sqrtf(fr.x * fr.x + fr.y * fr.y);
+    K.gnorm[o] = gn;
+    if (tgt) {   // the packed target record of k_pack_targets (rbv_tracker.cu), written here when the map's distance field follows its detect
+      tgt[2 * o] = make_float4(fr.x, fr.y, px, py);
+      tgt[2 * o + 1] = make_float4(fr.x / gn, fr.y / gn, gn, 0.0f);                       // core.cpp:64-65
+    }
     K.match_gnorm[o] = 0.0f;
     K.rho[o] = RBV_RHO_INIT;
     K.srho[o] = RBV_RHO_MAX;
@@ -1471,7 +1476,7 @@ __global__ void __launch_bounds__(32 * EM_ROWS) k_detect_emit(const float4* __re
 // the same for rows wider than the shared list: lane l walks the bits of its own flag words
 __global__ void __launch_bounds__(32) k_detect_emit_wide(const float4* __restrict__ fit, const unsigned* __restrict__ flags,
                                                          const int* __restrict__ rowoffset, KeylineSoA K, int* __restrict__ mask,
-                                                         const __grid_constant__ DevParams P, int wpr) {
+                                                         const __grid_constant__ DevParams P, int wpr, float4* __restrict__ tgt) {
   const int b = blockIdx.y, r = blockIdx.x + 2, lane = threadIdx.x;
   const int rows = P.rows, cols = P.cols, kmax = P.kmax;
   const size_t N = (size_t)P.npix;
@@ -1504,7 +1509,12 @@ __global__ void __launch_bounds__(32) k_detect_emit_wide(const float4* __restric
         K.match_pos_img[o] = pi;
         K.grad[o] = make_float2(fr.x, fr.y);
         K.match_grad[o] = make_float2(0.0f, 0.0f);
-        K.gnorm[o] = sqrtf(fr.x * fr.x + fr.y * fr.y);
+        const float gn = sqrtf(fr.x * fr.x + fr.y * fr.y);
+        K.gnorm[o] = gn;
+        if (tgt) {   // packed target record, as in k_detect_emit
+          tgt[2 * o] = make_float4(fr.x, fr.y, px, py);
+          tgt[2 * o + 1] = make_float4(fr.x / gn, fr.y / gn, gn, 0.0f);
+        }
         K.match_gnorm[o] = 0.0f;
         K.rho[o] = RBV_RHO_INIT;
         K.srho[o] = RBV_RHO_MAX;
@@ -1568,7 +1578,7 @@ __global__ void __launch_bounds__(1024) k_tune(KeylineSoA K, const int* __restri
 }
 
 // EdgeDetector::buildEdgeMap + joinEdges + tuneThreshold on the scale space already in bufA
-int fe_detect(rbv_ctx* c, rbv_map* map) {
+int fe_detect(rbv_ctx* c, rbv_map* map, float4* tgt) {
   const DevParams& P = c->P;
   const int B = P.lanes, rows = P.rows, cols = P.cols;
   const int wpr = (cols + 31) / 32;
@@ -1578,9 +1588,9 @@ int fe_detect(rbv_ctx* c, rbv_map* map) {
   RBV_LAUNCH(c, k_detect_flags, (g1), (256), 0, c->bufA, c->thr_dev, c->flags, c->rowcount, map->mask, fit, P, wpr);
   RBV_LAUNCH(c, k_detect_scan, (B), (1024), 0, c->rowcount, c->rowoffset, map->count, rows, P.keylines_max);
   if (cols <= EM_MAXW)
-    RBV_LAUNCH(c, k_detect_emit, (dim3((rows - 4 + EM_ROWS - 1) / EM_ROWS, B)), (32 * EM_ROWS), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+    RBV_LAUNCH(c, k_detect_emit, (dim3((rows - 4 + EM_ROWS - 1) / EM_ROWS, B)), (32 * EM_ROWS), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr, tgt);
   else
-    RBV_LAUNCH(c, k_detect_emit_wide, (dim3(rows - 4, B)), (32), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr);
+    RBV_LAUNCH(c, k_detect_emit_wide, (dim3(rows - 4, B)), (32), 0, fit, c->flags, c->rowoffset, map->k, map->mask, P, wpr, tgt);
   RBV_LAUNCH(c, k_join, (dim3((P.kmax + 255) / 256, B)), (256), 0, map->k, map->count, map->mask, P);
   RBV_LAUNCH(c, k_tune, (B), (1024), 0, map->k, map->count, map->threshold, P.kmax);
   RBV_CUDA(cudaGetLastError());

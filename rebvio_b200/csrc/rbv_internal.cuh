@@ -230,11 +230,11 @@ int fe_init(rbv_ctx* c);   // per-device kernel attributes (dynamic shared memor
 int tr_init(rbv_ctx* c);
 int fe_scale_space(rbv_ctx* c, const float* d_img, int part);
 int fe_uses_fused_box(rbv_ctx* c, const float* d_img);
-int fe_detect(rbv_ctx* c, rbv_map* map);
+int fe_detect(rbv_ctx* c, rbv_map* map, float4* tgt = nullptr);   // tgt: also write the packed target records (k_pack_targets' output) of the new keylines
 int fe_box_pass_debug(rbv_ctx* c, int scale, int pass, const float* d_in, float* d_out);
 int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out);
 
-int tr_build_field(rbv_ctx* c, rbv_map* map);
+int tr_build_field(rbv_ctx* c, rbv_map* map, bool packed = false);   // packed: the map's target records are already in c->tgt (written by k_detect_emit)
 int tr_pack_targets(rbv_ctx* c, rbv_map* map);   // refresh the packed copy after the field map's keylines were replaced
 int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);

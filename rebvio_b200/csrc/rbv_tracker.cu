@@ -251,11 +251,11 @@ int tr_init(rbv_ctx* c) {
   return tr_init_ordered();
 }
 
-int tr_build_field(rbv_ctx* c, rbv_map* map) {
+int tr_build_field(rbv_ctx* c, rbv_map* map, bool packed) {
   const DevParams& P = c->P;
   const int H = field_band_rows(c);
   const bool band = (c->tune[RBV_TUNE_FIELD] == 2 || (c->tune[RBV_TUNE_FIELD] == 0 && H >= 8)) && P.field_nr <= FB_G * FB_MAXI;
-  { int rc = tr_pack_targets(c, map); if (rc != RBV_OK) return rc; }   // first: the band kernel reads the packed records (unit normals divided once)
+  if (!packed) { int rc = tr_pack_targets(c, map); if (rc != RBV_OK) return rc; }   // first: the band kernel reads the packed records (unit normals divided once); packed: k_detect_emit has written them
   if (band && H >= 1) {
     const size_t smem = (size_t)H * P.cols * 4;
     RBV_LAUNCH(c, k_field_band, (dim3((P.rows + H - 1) / H, P.lanes)), (FB_TPB), smem, c->tgt, map->k.pos, map->count, map->threshold, c->field, P, H);

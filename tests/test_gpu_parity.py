@@ -704,3 +704,57 @@ def test_200_frames_free_running_bit_exact(name):
             assert H.clean(H.compare_keylines(T[k]["new"]["kl"], G[k]["new"]["kl"])) == {}, k
     assert np.array_equal(T[-1]["pos"], G[-1]["pos"]) and np.array_equal(T[-1]["Racc"], G[-1]["Racc"])
     assert T[-1]["nm"] > 500
+
+
+@pytest.mark.parametrize("form,kmax", [(0, 6000), (2, 6000), (0, 3491), (0, 1389), (0, 700)])
+def test_ordered_addends_sum_to_outputs(form, kmax):
+    """RBV_REDUCE_ORDERED contract, stage by stage: the evaluation blocks leave the float32 addends of every keyline (debug tap
+    rbv_debug_read_addends: rows 0..9 tryVel, 100..126 extRotVel) and the chain adds them in keyline order - so numpy's sequential
+    float32 sum of every row must equal, bit for bit, the score / JtJ / JtF the call returns and the Wx the solve was fed with; and both
+    must equal the oracle's. Keyline counts chosen so that the last chunk has every kind of block count (the nvcc 12.9 unroller bug the
+    chain loop works around showed on (blocks & 7) in {3, 5, 6, 7}). form = RBV_TUNE_ORDERED (0: chain CTAs inside the evaluation
+    launch, 2: chain kernels behind it)."""
+    rows, cols = 240, 320
+    spec, frames, R_rel = common.sequence("C5:320x240", 3)
+    cfg = common.cfgs(spec.cam.fm, spec.cam.cx, spec.cam.cy, rows, cols, int(0.75 * kmax), kmax)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    a, b = orc.detect(frames[0]), orc.detect(frames[1])
+    orc.build_distance_field(b)
+    n = orc.map_size(a)
+    vel = np.float32([0.01, -0.02, 0.005])
+    so, JJo, JFo = orc.try_vel(a, vel, 1e3, np.zeros(n, np.float32))
+    g = _gpu(cfg, lanes=3, lane=2, tune={capi.TUNE_ORDERED: form})
+    ga, gb = g.detect(frames[0]), g.detect(frames[1])
+    assert g.map_size(ga) == n
+    g.build_distance_field(gb)
+    g.ctx.resetResiduals(ga)
+    sc, JtJ, JtF = g.ctx.tryVel(ga, vel, 1e3)
+    seq = lambda v: np.add.accumulate(v, dtype=np.float32)[-1] if len(v) else np.float32(0)
+
+    def row(plane, lane, count):
+        buf = np.zeros(count, np.float32)
+        capi.check(g.ctx.L.rbv_debug_read_addends(g.ctx.h, plane, lane, capi.ptr(buf), count))
+        return buf
+
+    for lane in range(3):
+        s = [seq(row(p, lane, n)) for p in range(10)]
+        want = np.float32([s[0], s[1], s[2], s[3], s[4], s[5], s[6], s[7], s[8], s[9]])
+        got = np.float32([sc[lane], JtJ[lane, 0, 0], JtJ[lane, 1, 1], JtJ[lane, 2, 2], JtJ[lane, 0, 1], JtJ[lane, 0, 2], JtJ[lane, 1, 2],
+                          JtF[lane, 0], JtF[lane, 1], JtF[lane, 2]])
+        assert np.array_equal(H.bits(want), H.bits(got)), ("tryVel", lane)
+    assert H.bits(np.float32(sc[2])) == H.bits(np.float32(so)) and np.array_equal(H.bits(JtJ[2]), H.bits(JJo)) and np.array_equal(H.bits(JtF[2]), H.bits(JFo))
+    # extRotVel: 21 upper-triangle products of Phi^T Phi (row-major) + 6 of Phi^T Y
+    orc.forward_match(a, b)
+    g.ctx.forwardMatch(ga, gb)
+    nn = orc.map_size(b)
+    oko, Wxo, Xo = orc.ext_rot_vel(b, np.zeros(3, np.float32))
+    ok, Wx, X = g.ctx.extRotVel(gb, np.zeros(3, np.float32))
+    for lane in range(3):
+        s = [seq(row(100 + p, lane, nn)) for p in range(27)]
+        k = 0
+        for i in range(6):
+            for j in range(i, 6):
+                assert H.bits(np.float32(Wx[lane, i, j])) == H.bits(np.float32(s[k])) == H.bits(np.float32(Wx[lane, j, i])), ("extRotVel", lane, i, j)
+                k += 1
+    assert np.array_equal(H.bits(Wx[2]), H.bits(np.asarray(Wxo, np.float32).reshape(6, 6)))
+    g.close(); orc.close()

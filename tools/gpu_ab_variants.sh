@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B of library variants on the two-stream schedule: tools/gpu_run_q.sh <lib names...> ("main" = the shipped library)
+# A/B of library variants on the two-stream schedule: tools/gpu_ab_variants.sh <lib names...> ("main" = the shipped library)
 mkdir -p gpurun_out
 Q="--no-cpu --no-e2e --no-single --no-sweep --no-fast --windows 3 --steps 40"
 for rep in 1 2; do

@@ -1,5 +1,6 @@
 #!/bin/bash
-# round-2 GPU pass K: chunked addend layout + loader warp for the ORDERED chain kernels
+# quick GPU check (under gpurun): ORDERED debug probe, the GPU suite (or a subset with `quick`), in-order and two-stream quick benches, kernel table
+# usage: bash tools/gpu_check.sh <tag> [quick]
 mkdir -p gpurun_out
 export BENCH_TRACE=1
 P=${1:-k}
