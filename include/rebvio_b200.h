@@ -374,6 +374,17 @@ int rbv_debug_read_residuals(rbv_ctx* ctx, rbv_map* map, int lane, float* out, i
 /* one box pass (createIntegralImage + average, scale_space.cpp:48-128) of width index `pass` of scale
  * `scale` applied to a host image; for the first-kernel parity test. */
 int rbv_debug_box_pass(rbv_ctx* ctx, int scale, int pass, const float* in, float* out);
+/* One box pass (createIntegralImage + average, scale_space.cpp:48-128: the arithmetic of rbv_debug_box_pass) of ONE image plane
+ * that allocates nothing. NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it). d_in / d_out: DEVICE pointers to rows*cols
+ * float32 (may not alias), on the CURRENT device; width: odd box width 3..15; cuda_stream: cudaStream_t (NULL = default stream).
+ * Asynchronous: returns after the two kernel launches. No context is needed and no cudaMalloc / cudaFree / allocating routine is
+ * called: the row-prefix scratch between the two kernels is a static device array of RBV_NOALLOC_MAX_PIXELS floats (4 MiB, held by
+ * every device that loads the library until exit); rows*cols beyond that is rejected with RBV_ERR_ARG and a message. All calls
+ * share that array (it keeps the last call's contents; nothing in it has to start at zero): calls that overlap on the GPU - two
+ * streams without ordering between them - race. Calls on one stream are safe. */
+#define RBV_NOALLOC_MAX_PIXELS (1024 * 1024)
+int rbv_box_pass_noalloc(const float* d_in, float* d_out, int rows, int cols, int width, void* cuda_stream);
 /* the 3x25 plane-fit pseudo inverse and box widths the context computed */
 int rbv_debug_read_setup(rbv_ctx* ctx, float* pinv75, int* widths6);
 /* LM trace of the last rbv_minimize_vel: per tryVel call t=0..iterations: vel[3], JtJ[9], JtF[3], score

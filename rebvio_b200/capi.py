@@ -86,6 +86,7 @@ _SIG = {
     "rbv_launch_count": (C.c_ulonglong, [vp]),
     "rbv_kernel_count": (C.c_int, []),
     "rbv_kernel_name": (C.c_char_p, [C.c_int]),
+    "rbv_box_pass_noalloc": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "rbv_profile_set": (C.c_int, [vp, C.c_int]),
     "rbv_profile_reset": (C.c_int, [vp]),
     "rbv_profile_read": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),

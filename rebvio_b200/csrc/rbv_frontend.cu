@@ -1617,3 +1617,58 @@ int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out) {
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// rbv_box_pass_noalloc: one box pass (createIntegralImage + average) of a device image without any allocation.
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+// CUDA-graph capture, tight serving loops, harnesses that forbid it). It is the split path's k_rowscan(4) + k_colbox pair - the same
+// kernels, unchanged, that rbv_debug_box_pass runs by default - with the row-prefix image, the scratch between the two, in a
+// file-scope device array instead of the context's cudaMalloc'd `rowsum`. Every device that loads the library holds the array
+// (RBV_NOALLOC_MAX_PIXELS floats = 4 MiB) until exit.
+// The array's NAME is a host-side stand-in in host code, not a device address: the address is taken once per device, with that
+// device current, by cudaGetSymbolAddress, and that pointer is what the kernels get.
+// All calls share the array and it keeps the last call's contents; nothing has to start at zero (k_rowscan writes every word of
+// rows x cols before k_colbox reads it). Two calls that overlap on the GPU (different streams, no ordering between them) race on it.
+static __device__ __align__(256) float rbv_noalloc_rowsum[RBV_NOALLOC_MAX_PIXELS];
+
+#include <mutex>
+static std::mutex noalloc_mu;
+static float* noalloc_ptr[64];   // device address of rbv_noalloc_rowsum, per device ordinal
+
+static int noalloc_scratch(float** out) {
+  int dev = -1;
+  RBV_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { rbv_set_error("rbv_box_pass_noalloc: device ordinal %d out of range", dev); return RBV_ERR_ARG; }
+  std::lock_guard<std::mutex> lk(noalloc_mu);
+  if (!noalloc_ptr[dev]) {   // set-up, once per device, that device current
+    float* p = nullptr;
+    RBV_CUDA(cudaGetSymbolAddress((void**)&p, rbv_noalloc_rowsum));
+    if (!p) { rbv_set_error("rbv_box_pass_noalloc: cudaGetSymbolAddress returned a null address"); return RBV_ERR_CUDA; }
+    noalloc_ptr[dev] = p;
+  }
+  *out = noalloc_ptr[dev];
+  return RBV_OK;
+}
+
+extern "C" int rbv_box_pass_noalloc(const float* d_in, float* d_out, int rows, int cols, int width, void* cuda_stream) {
+  if (!d_in || !d_out) { rbv_set_error("rbv_box_pass_noalloc: null device pointer"); return RBV_ERR_ARG; }
+  if (rows < 1 || cols < 1 || rows > 32767 || cols > 32767) { rbv_set_error("rbv_box_pass_noalloc: bad image size %d x %d", rows, cols); return RBV_ERR_ARG; }
+  if ((long long)rows * cols > (long long)RBV_NOALLOC_MAX_PIXELS) {
+    rbv_set_error("rbv_box_pass_noalloc: %d x %d = %lld pixels exceed the static scratch of RBV_NOALLOC_MAX_PIXELS = %d pixels", rows, cols,
+                  (long long)rows * cols, (int)RBV_NOALLOC_MAX_PIXELS);
+    return RBV_ERR_ARG;
+  }
+  if (width < 3 || width > 15 || (width & 1) == 0) { rbv_set_error("rbv_box_pass_noalloc: box width %d not an odd number in 3..15", width); return RBV_ERR_ARG; }
+  float* scratch = nullptr;
+  { const int rc = noalloc_scratch(&scratch); if (rc != RBV_OK) return rc; }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const size_t N = (size_t)rows * cols;
+  if ((cols & 3) == 0 && ((uintptr_t)d_in & 15) == 0)
+    k_rowscan4<<<dim3((rows + 31) / 32, 1), 32, 0, st>>>(d_in, scratch, rows, cols, N, N);
+  else
+    k_rowscan<<<dim3((rows + 31) / 32, 1), 32, 0, st>>>(d_in, scratch, rows, cols, N, N);
+  const int W = CB_TPB - (2 * (width / 2) + 1);
+  k_colbox<<<dim3((cols + W - 1) / W, 1), CB_TPB, 0, st>>>(scratch, d_out, d_out, rows, cols, N, N, 1, width, width, 0);
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
