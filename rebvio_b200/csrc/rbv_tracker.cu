@@ -164,32 +164,41 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict_
       // getIndex (core.hpp:66-71): (int)std::round(v), half away from zero = sign(v) * trunc(|v| + 0.5). All on the FP32
       // add pipe: the RZ add of 0.5 is what roundf() itself does, the RZ add of 2^23 leaves trunc() in the mantissa
       // (values >= 2^23, Inf and NaN come out as huge indices and fail the range test). No FRND / F2I conversions.
-      const float fr0 = (float)rs;
+      // The range tests are made on the float coordinate, not on the rounded index (round-half-away(v) in [a, b) <=> v in [a - 0.5, b - 0.5),
+      // and v > -0.5 for a = 0): four chained float compares per candidate and no integer index at all - the cell address comes straight
+      // from the bit patterns (bits = 0x4B000000 + index): addr = bits_y * 4 cols + bits_x * 4 + A0 with the constants folded into A0
+      // (unsigned wrap-around arithmetic). |r| of the key the same way: bits(|fr| + 2^23) << 24 drops the 0x4B.
+      const float fr0 = (float)rs, fre = (float)re;
       const unsigned cell_a = (unsigned)__cvta_generic_to_shared(fb_cell);
-      unsigned addr[FB_G], key[FB_G];
-      bool ok[FB_G];
+      const unsigned cols4 = 4u * (unsigned)cols;
+      const unsigned A0 = cell_a - cols4 * (0x4B000000u + (unsigned)r0) - 4u * 0x4B000000u;
+      const float ylo = r0 > 0 ? __int_as_float(__float_as_int(r0f - 0.5f) - 1) : -0.5f;   // fy > ylo  <=>  round(fy) >= r0 (r0 - 0.5 itself rounds to r0)
+      const float yhi = r1f - 0.5f, xhi = (float)cols - 0.5f;                                // fy < yhi  <=>  round(fy) < r1
+      unsigned addr[FB_G], key[FB_G], cur[FB_G];
 #pragma unroll
       for (int u = 0; u < FB_G; ++u) {
-        const int r = rs + u;
-        const float fr = fr0 + (float)u;
+        float fr;   // (float)(rs + u), exact; as one FADD (left to itself nvcc converts rs + u again for every candidate: IADD + I2F)
+        asm("add.rn.f32 %0, %1, %2;" : "=f"(fr) : "f"(fr0), "f"((float)u));
         const float fy = kuy * fr + kpy;                                                  // :50
         const float fx = kux * fr + kpx;                                                  // :51
-        const int iy = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fy), 0.5f), 8388608.0f)) - 0x4B000000;
-        const int ix = __float_as_int(__fadd_rz(__fadd_rz(fabsf(fx), 0.5f), 8388608.0f)) - 0x4B000000;
-        // a negative coordinate rounds to an index >= 0 only for v > -0.5 (round(-0.3) = -0 -> 0, round(-0.5) = -1): one compare
-        // per axis instead of sign test + zero test + select; NaN fails the compare, Inf the range test
-        ok[u] = r < re && fy > -0.5f && fx > -0.5f && (unsigned)(iy - r0) < (unsigned)nrows && (unsigned)ix < (unsigned)cols;
-        addr[u] = cell_a + 4u * (unsigned)((iy - r0) * cols + ix);
-        key[u] = lowkey + ((unsigned)abs(r) << 24);                                      // :54-56 as min over (|r|, -idx)
-      }
-      // loads, then compares + atomics: predicated instructions (no branch per candidate), all loads issued before the first use
-      unsigned cur[FB_G];
-#pragma unroll
-      for (int u = 0; u < FB_G; ++u)
+        const unsigned by = (unsigned)__float_as_int(__fadd_rz(__fadd_rz(fabsf(fy), 0.5f), 8388608.0f));
+        const unsigned bx = (unsigned)__float_as_int(__fadd_rz(__fadd_rz(fabsf(fx), 0.5f), 8388608.0f));
+        addr[u] = by * cols4 + (bx * 4u + A0);
+        key[u] = lowkey + ((unsigned)__float_as_int(fabsf(fr) + 8388608.0f) << 24);        // :54-56 as min over (|r|, -idx)
+        // in range: r < re, round(fy) in [r0, r1), round(fx) in [0, cols) - a negative coordinate rounds to an index >= 0 only for
+        // v > -0.5 (round(-0.3) = -0 -> 0, round(-0.5) = -1); NaN fails every compare. The five compares chain into ONE predicate that
+        // guards the load (a predicated instruction, no branch per candidate); out of range reads as 0 = "nothing to improve" below.
         asm volatile("{ .reg .pred p;\n"
-                     "  setp.ne.u32 p, %2, 0;\n"
+                     "  setp.lt.f32 p, %2, %3;\n"
+                     "  setp.gt.and.f32 p, %4, %5, p;\n"
+                     "  setp.lt.and.f32 p, %4, %6, p;\n"
+                     "  setp.gt.and.f32 p, %7, 0fBF000000, p;\n"
+                     "  setp.lt.and.f32 p, %7, %8, p;\n"
                      "  mov.u32 %0, 0;\n"
-                     "  @p ld.volatile.shared.u32 %0, [%1]; }" : "=r"(cur[u]) : "r"(addr[u]), "r"((unsigned)ok[u]));
+                     "  @p ld.volatile.shared.u32 %0, [%1]; }"
+                     : "=r"(cur[u]) : "r"(addr[u]), "f"(fr), "f"(fre), "f"(fy), "f"(ylo), "f"(yhi), "f"(fx), "f"(xhi));
+      }
+      // compares + atomics, all loads issued before the first use
 #pragma unroll
       for (int u = 0; u < FB_G; ++u)
         asm volatile("{ .reg .pred q;\n"
