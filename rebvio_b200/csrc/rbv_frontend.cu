@@ -1312,10 +1312,21 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
   if (tid < DT_H * 2) sflags[tid >> 1][tid & 1] = 0u;
   if (tid == 0) ncand = 0;
   __syncthreads();
-  for (int i = tid; i < DT_H * (DT_W + 4); i += 256) {
-    const int vr = i / (DT_W + 4), vc = i % (DT_W + 4);
-    const float y0 = dogt[vr][vc], y1 = dogt[vr + 1][vc], y2 = dogt[vr + 2][vc], y3 = dogt[vr + 3][vc], y4 = dogt[vr + 4][vc];
-    colP[vr][vc] = (unsigned char)((y0 > 0.0f) + (y1 > 0.0f) + (y2 > 0.0f) + (y3 > 0.0f) + (y4 > 0.0f));   // :92, NaN counts as negative
+  {
+    // colP[vr][vc] = positives among dogt[vr .. vr + 4][vc] (:92, NaN counts as negative). A thread takes four consecutive rows of one
+    // column: eight loads and a sliding count instead of twenty loads (and no division of a flat index by the 68-column pitch)
+    static_assert(DT_H == 16 && DT_W == 64, "colP mapping: 4 row groups x 64 columns per 256 threads, the 4 halo columns by 16 threads");
+    auto col4 = [&](int vc, int g) {
+      int pz[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) pz[k] = dogt[4 * g + k][vc] > 0.0f;
+      int sct = pz[0] + pz[1] + pz[2] + pz[3] + pz[4];
+      colP[4 * g][vc] = (unsigned char)sct;
+#pragma unroll
+      for (int k = 1; k < 4; ++k) { sct += pz[k + 4] - pz[k - 1]; colP[4 * g + k][vc] = (unsigned char)sct; }
+    };
+    col4(tid & 63, tid >> 6);
+    if (tid < 16) col4(DT_W + (tid & 3), tid >> 2);
   }
   __syncthreads();
   const float thr = thr_dev[b];
@@ -1323,6 +1334,7 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
   const float mag_threshold = tm * tm;                                                 // edge_detector.cpp:71
   const float tg = tm * P.dog_threshold;
   const float gts = tg * tg;                                                           // :70
+  unsigned cm[(DT_W * DT_H) / 256];   // ballots of the thread's four pixels
 #pragma unroll
   for (int i = 0; i < (DT_W * DT_H) / 256; ++i) {
     const int p = tid + i * 256;
@@ -1343,11 +1355,20 @@ __global__ void __launch_bounds__(256) k_detect_flags(const float* __restrict__ 
         }
       }
     }
-    const unsigned m = __ballot_sync(0xFFFFFFFFu, c);
+    cm[i] = __ballot_sync(0xFFFFFFFFu, c);
+  }
+  {   // one slot reservation per warp for its (up to 128) candidates; their order in the list does not matter (the fit below is per candidate)
+    int tot = 0;
+#pragma unroll
+    for (int i = 0; i < (DT_W * DT_H) / 256; ++i) tot += __popc(cm[i]);
     int base = 0;
-    if (lane == 0 && m) base = atomicAdd(&ncand, __popc(m));
+    if (lane == 0 && tot) base = atomicAdd(&ncand, tot);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (c) cand[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)p;
+#pragma unroll
+    for (int i = 0; i < (DT_W * DT_H) / 256; ++i) {
+      if ((cm[i] >> lane) & 1u) cand[base + __popc(cm[i] & ((1u << lane) - 1u))] = (unsigned short)(tid + i * 256);
+      base += __popc(cm[i]);
+    }
   }
   __syncthreads();
   const int nc = ncand;

@@ -968,10 +968,14 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
       if (lane == 0) sm[warp * 10 + a] = v;
     }
   }
-  if constexpr (ORD) { if (ord_flags) __threadfence(); }   // this thread's addends are visible device-wide before the block's flag goes up
   __syncthreads();
-  if constexpr (ORD) {   // chain role of the same launch (k_tryvel_ord*, blockIdx.y == 0): its loader polls this flag before it stages the block's chunks
-    if (ord_flags && t == 0) asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+  if constexpr (ORD) {   // chain role of the same launch (k_tryvel_ord*, blockIdx.y == 0): its loader polls this flag before it stages the block's chunks.
+    // The block's addends are ordered before the flag by the barrier above plus ONE cumulative gpu-scope fence + release store in thread 0
+    // (the grid-sync pattern); a fence in every thread made all 256 of them wait for their stores to be acknowledged (`membar` stalls)
+    if (ord_flags && t == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+    }
   }
   if (!ehas || !has) {
     for (int w2 = warp - 1; w2 >= 0; --w2)
@@ -1739,9 +1743,11 @@ __global__ void __launch_bounds__(TV_TPB) k_extrot_ord(KeylineSoA K, const int* 
     for (int a = 0; a < 6; ++a) dst[(21 + a) * OrdER::RS] = r[a] * r[6];
   }
   if (ord_flags) {   // the block's addends are out: flag for the chain CTA's loader
-    __threadfence();
     __syncthreads();
-    if (t == 0) asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+    if (t == 0) {   // barrier + one cumulative fence + release store, as in tryvel_fastn_body
+      __threadfence();
+      asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+    }
   }
 }
 __global__ void __launch_bounds__(64) k_chain_extrot(const int* __restrict__ count, const float* __restrict__ rows, float* lane_out,

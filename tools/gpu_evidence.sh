@@ -1,8 +1,9 @@
 #!/bin/bash
-# round-2 evidence pass: suite, full bench, reference arm, ncu launch list + full captures, FAST-mode report
+# evidence pass (under gpurun): suite, full bench, reference arm, ncu launch list + full captures, FAST-mode report
+# usage: bash tools/gpu_evidence.sh <tag> [lean]   (lean: without the suite and the FAST-mode report)
 mkdir -p gpurun_out
 P=${1:-p}
-timeout 1500 python -m pytest tests -m gpu -q --timeout 400 > gpurun_out/${P}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${P}_pytest.log; tail -3 gpurun_out/${P}_pytest.log
+[ "$2" = lean ] || timeout 1500 python -m pytest tests -m gpu -q --timeout 400 > gpurun_out/${P}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${P}_pytest.log; tail -3 gpurun_out/${P}_pytest.log
 timeout 900 python bench.py --kernel-table gpurun_out/${P}_ktable.csv > gpurun_out/${P}_bench.json 2> gpurun_out/${P}_bench.err; echo "bench rc=$?"
 python - <<PY
 import json
@@ -19,4 +20,4 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 CMD="python bench.py --steps 2 --warmup 3 --windows 1 --no-cpu --no-single --no-e2e --no-sweep --no-fast"
 timeout 200 $CMD > gpurun_out/${P}_plain.log 2>&1 && timeout 500 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -c 600 --csv --log-file gpurun_out/${P}_launches.csv $CMD > gpurun_out/${P}_ncu_list.log 2>&1; echo "launch list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_boxpass|k_tryvel_ord4|k_field_band|k_detect_flags|k_directed|k_extrot_ord" -s 24 -c 14 -o gpurun_out/${P}_prof $CMD > gpurun_out/${P}_ncu_full.log 2>&1; echo "full capture rc=$?"
-timeout 600 python tools/fast_mode_report.py 200 > gpurun_out/${P}_fast_mode_report.json 2> gpurun_out/${P}_fast_mode_report.err; echo "fast report rc=$?"; tail -2 gpurun_out/${P}_fast_mode_report.err
+[ "$2" = lean ] || timeout 600 python tools/fast_mode_report.py 200 > gpurun_out/${P}_fast_mode_report.json 2> gpurun_out/${P}_fast_mode_report.err; echo "fast report rc=$?"; tail -2 gpurun_out/${P}_fast_mode_report.err
