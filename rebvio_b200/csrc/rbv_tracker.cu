@@ -972,7 +972,9 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
   if constexpr (ORD) {   // chain role of the same launch (k_tryvel_ord*, blockIdx.y == 0): its loader polls this flag before it stages the block's chunks.
     // The block's addends are ordered before the flag by the barrier above plus ONE cumulative gpu-scope fence + release store in thread 0
     // (the grid-sync pattern); a fence in every thread made all 256 of them wait for their stores to be acknowledged (`membar` stalls)
-    if (ord_flags && t == 0) {
+    // (blk * KPB < n: block 0 of a lane WITHOUT keylines also runs - it owns the lane's bookkeeping - but the chain has no chunk to
+    // wait for then and would leave the flag standing for the next launch)
+    if (ord_flags && t == 0 && blk * KPB < n) {
       __threadfence();
       asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
     }

@@ -335,6 +335,47 @@ def test_empty_and_flat_frames():
     g.close()
 
 
+@pytest.mark.parametrize("form", [0, 2])
+def test_ordered_sums_after_an_empty_map(form):
+    """A lane whose map has no keylines (flat frame) and then a real map on the same context, RBV_REDUCE_ORDERED: the evaluation block
+    that runs for the empty lane must not leave its "addends ready" flag standing (nothing consumes it: the chain has no chunk), or the
+    next call's chain would stage chunk 0 before it is written. tryVel and extRotVel after the empty calls equal the oracle bit for bit."""
+    rows, cols = 240, 320
+    spec, frames, R_rel = common.sequence("C5:320x240", 3)
+    cfg = common.cfgs_from_spec(spec)
+    orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+    a, b = orc.detect(frames[0]), orc.detect(frames[1])
+    orc.build_distance_field(b)
+    n = orc.map_size(a)
+    vel = np.float32([0.01, -0.02, 0.005])
+    so, JJo, JFo = orc.try_vel(a, vel, 1e3, np.zeros(n, np.float32))
+    orc.forward_match(a, b)
+    oko, Wxo, Xo = orc.ext_rot_vel(b, np.zeros(3, np.float32))
+    g = _gpu(cfg, lanes=2, lane=1, tune={capi.TUNE_ORDERED: form})
+    flat = np.full((rows, cols), 300.0, np.float32)
+    ga, gb = g.detect(frames[0]), g.detect(frames[1])          # (first, as in the oracle: the threshold servo follows the keyline counts)
+    e0, e1 = g.detect(flat), g.detect(flat)
+    assert g.map_size(e0) == 0 and g.map_size(ga) == n
+    for rep in range(3):
+        g.build_distance_field(e1)
+        g.ctx.resetResiduals(e0)
+        sc, _, _ = g.ctx.tryVel(e0, vel, 1e3)                  # empty lanes: block 0 runs, the chain has nothing to add
+        assert (sc == 0.0).all()
+        g.ctx.forwardMatch(e0, e1)
+        g.ctx.extRotVel(e1, np.zeros(3, np.float32))
+        g.build_distance_field(gb)
+        g.ctx.resetResiduals(ga)
+        sc, JtJ, JtF = g.ctx.tryVel(ga, vel, 1e3)
+        for lane in range(2):
+            assert H.bits(np.float32(sc[lane])) == H.bits(np.float32(so)), (rep, lane)
+            assert np.array_equal(H.bits(JtJ[lane]), H.bits(JJo)) and np.array_equal(H.bits(JtF[lane]), H.bits(JFo)), (rep, lane)
+        g.ctx.forwardMatch(ga, gb)
+        ok, Wx, X = g.ctx.extRotVel(gb, np.zeros(3, np.float32))
+        for lane in range(2):
+            assert np.array_equal(H.bits(Wx[lane]), H.bits(np.asarray(Wxo, np.float32).reshape(6, 6))), (rep, lane)
+    g.close(); orc.close()
+
+
 def test_fast_mode_is_deterministic():
     spec, frames, R_rel = common.sequence("C5:320x240", 4)
     cfg = common.cfgs_from_spec(spec)
