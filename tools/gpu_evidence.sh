@@ -20,4 +20,4 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 CMD="python bench.py --steps 2 --warmup 3 --windows 1 --no-cpu --no-single --no-e2e --no-sweep --no-fast"
 timeout 200 $CMD > gpurun_out/${P}_plain.log 2>&1 && timeout 500 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -c 600 --csv --log-file gpurun_out/${P}_launches.csv $CMD > gpurun_out/${P}_ncu_list.log 2>&1; echo "launch list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_boxpass|k_tryvel_ord4|k_field_band|k_detect_flags|k_directed|k_extrot_ord" -s 24 -c 14 -o gpurun_out/${P}_prof $CMD > gpurun_out/${P}_ncu_full.log 2>&1; echo "full capture rc=$?"
-[ "$2" = lean ] || timeout 600 python tools/fast_mode_report.py 200 > gpurun_out/${P}_fast_mode_report.json 2> gpurun_out/${P}_fast_mode_report.err; echo "fast report rc=$?"; tail -2 gpurun_out/${P}_fast_mode_report.err
+[ "$2" = lean ] || timeout 600 python tools/fast_mode_report.py 200 > gpurun_out/${P}_fast_mode_report.json 2> gpurun_out/${P}_fast_mode_report.err; echo "fast report rc=$?"; tail -2 gpurun_out/${P}_fast_mode_report.err 2>/dev/null; true
