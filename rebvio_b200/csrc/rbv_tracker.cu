@@ -1808,7 +1808,10 @@ int tr_ext_rot_vel(rbv_ctx* c, rbv_map* new_map, int vel_from_lm) {
 // ---------------------------------------------------------------------------------------------------------------
 // directedMatch + searchMatch (edge_map.cpp:101-218): every new keyline walks its epipolar segment in the OLD map's
 // pixel->id mask. Independent per keyline (the loop only mutates the querying keyline), so one thread each.
-__global__ void __launch_bounds__(256) k_directed(KeylineSoA Kn, const int* __restrict__ count_n, KeylineSoA Ko, const int* __restrict__ mask_o,
+#ifndef DIR_TPB
+#define DIR_TPB 128   // walks differ a lot in length: smaller blocks balance the SMs better (measured 120 -> 114 us; 64 threads: the same)
+#endif
+__global__ void __launch_bounds__(DIR_TPB) k_directed(KeylineSoA Kn, const int* __restrict__ count_n, KeylineSoA Ko, const int* __restrict__ mask_o,
                                                   const float* __restrict__ lane_in, int* __restrict__ lane_cnt,
                                                   unsigned long long* __restrict__ probes, const __grid_constant__ DevParams P) {
   __shared__ float s_vel[3], s_Rvel[9];
@@ -1927,7 +1930,7 @@ __global__ void __launch_bounds__(256) k_directed(KeylineSoA Kn, const int* __re
 int tr_directed_match(rbv_ctx* c, rbv_map* new_map, rbv_map* old_map) {
   const DevParams& P = c->P;
   if (!c->seq_fused) RBV_LAUNCH(c, k_zero_cnt, (1), (P.lanes), 0, c->lane_cnt, CNT_DIR, c->probes);
-  RBV_LAUNCH(c, k_directed, (dim3((P.keylines_max + 255) / 256, P.lanes)), (256), 0, new_map->k, new_map->count, old_map->k, old_map->mask, c->lane_in, c->lane_cnt, c->probes, P);
+  RBV_LAUNCH(c, k_directed, (dim3((P.keylines_max + DIR_TPB - 1) / DIR_TPB, P.lanes)), (DIR_TPB), 0, new_map->k, new_map->count, old_map->k, old_map->mask, c->lane_in, c->lane_cnt, c->probes, P);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }

@@ -311,6 +311,61 @@ def test_lanes_are_independent():
     ctx.close()
 
 
+@pytest.mark.parametrize("form", [0, 2])
+def test_ragged_lanes_ordered(form):
+    """Lanes with very different keyline counts in one context, RBV_REDUCE_ORDERED: a full frame, a frame with half its texture, a flat
+    frame (no keylines), a frame with one small textured patch (less than one chunk of the add chain); then the lanes swap their inputs
+    on the SAME context, so every lane's chain length, block count and flags change from call to call. Every non-empty lane equals the
+    oracle run alone on its pair, bit for bit (X within the solve's tolerance); the empty lane returns zeros."""
+    spec, frames, R_rel = common.sequence("C5:320x240", 4)
+    rows, cols = frames[0].shape
+    cfg = common.cfgs_from_spec(spec)
+    conv = lambda cls, src: cls(*[getattr(src, f[0]) for f in cls._fields_])
+    B = 4
+    ctx = host.Context(conv(capi.Camera, cfg[0]), conv(capi.DetectorCfg, cfg[1]), conv(capi.MapCfg, cfg[2]), conv(capi.CoreCfg, cfg[3]),
+                       lanes=B, reduce_mode=capi.REDUCE_ORDERED)
+    ctx.set_tuning(capi.TUNE_ORDERED, form)
+
+    def variant(img, kind):
+        img = np.array(img, np.float32)
+        if kind == 1: img[:, cols // 2:] = 300.0
+        if kind == 2: img[:] = 300.0
+        if kind == 3:
+            patch = img[100:140, 120:180].copy(); img[:] = 300.0; img[100:140, 120:180] = patch
+        return img
+
+    counts = []
+    for rnd, kinds in enumerate([(0, 1, 2, 3), (3, 2, 1, 0), (1, 0, 3, 2)]):
+        old_imgs = np.stack([variant(frames[rnd], k) for k in kinds])
+        new_imgs = np.stack([variant(frames[rnd + 1], k) for k in kinds])
+        Rs = np.stack([np.asarray(R_rel[rnd + 1], np.float32).T for _ in range(B)])
+        old, n_old, _ = ctx.detect(old_imgs, 0.01)
+        new, n_new, _ = ctx.detect(new_imgs, 0.01)
+        counts.append([int(v) for v in n_old])
+        vel, Rv, Wx, X, ok = ctx.track_g1(old, new, Rs)
+        for b, k in enumerate(kinds):
+            if k == 2:
+                assert n_old[b] == 0 and n_new[b] == 0 and not np.any(vel[b]) and not np.any(Wx[b])
+                continue
+            orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
+            orc.set_threshold(0.01); orc.det.gain = 0.0
+            o = orc.map_new(); nn = orc.L.orc_detect(orc.h, np.ascontiguousarray(old_imgs[b]), 0.01, o)
+            m = orc.map_new(); orc.L.orc_detect(orc.h, np.ascontiguousarray(new_imgs[b]), 0.01, m)
+            assert nn == n_old[b] and nn > 0
+            orc.build_distance_field(m)
+            orc.rotate(o, Rs[b])
+            s_, v, P = orc.minimize_vel(o, [0, 0, 0])
+            orc.forward_match(o, m)
+            oko, Wxo, Xo = orc.ext_rot_vel(m, v)
+            assert np.array_equal(H.bits(v), H.bits(vel[b])) and np.array_equal(H.bits(P), H.bits(Rv[b])), (rnd, b, k)
+            assert np.array_equal(H.bits(Wxo), H.bits(Wx[b])), (rnd, b, k)
+            assert H.dirty([{"d": H.clean(H.compare_keylines(orc.map_get(o), old.keylines(b)[0]))}]) == [], (rnd, b, k)
+            orc.close()
+        old.release(); new.release()
+    assert len({c for cs in counts for c in cs}) >= 4, counts     # the lanes really had different keyline counts
+    ctx.close()
+
+
 def test_empty_and_flat_frames():
     """a constant frame yields no keylines (the reference would hit undefined behaviour in tuneThreshold on an empty
     map, edge_detector.cpp:168,177; here the map keeps threshold -1) and every tracker stage is a no-op that returns."""
