@@ -298,6 +298,8 @@ __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const floa
   const size_t o = (size_t)b * P.kmax + idx;
   const float fm = P.fm;
   float2 pi = K.pos_img[o];
+  const float rho = K.rho[o], srho = K.srho[o];   // every load of the keyline first: one memory round trip (the stores below may alias for all the compiler knows)
+  const float2 g = K.grad[o];
   const double v0 = (double)(pi.x / fm), v1 = (double)(pi.y / fm), v2 = 1.0;
   float q[3];
 #pragma unroll
@@ -312,10 +314,9 @@ __global__ void k_rotate(KeylineSoA K, const int* __restrict__ count, const floa
     pi.x = q[0] / q[2] * fm;
     pi.y = q[1] / q[2] * fm;
     K.pos_img[o] = pi;
-    K.rho[o] = K.rho[o] / q[2];
-    K.srho[o] = K.srho[o] / q[2];
+    K.rho[o] = rho / q[2];
+    K.srho[o] = srho / q[2];
   }
-  const float2 g = K.grad[o];
   float2 go;
   {
     double acc = 0.0;
@@ -2002,17 +2003,21 @@ __global__ void __launch_bounds__(256) k_kalman(KeylineSoA K, const int* __restr
   if (idx >= count[b]) return;
   if (min_matches > 0 && lane_cnt[b * CNT_STRIDE + CNT_DIR] < min_matches) return;
   const size_t o = (size_t)b * P.kmax + idx;
+  // every load of the keyline up front, unconditionally (all in range; unused values cost a few bytes, a dependent round trip costs a microsecond)
   float rho = K.rho[o], srho = K.srho[o];
+  const int mid = K.match_id[o];
+  const int rset = reg_set ? reg_set[o] : 0;
+  const float rr = reg_set ? reg_r[o] : 0.0f, rs = reg_set ? reg_s[o] : 0.0f;
+  const float2 q = K.pos_img[o], q0 = K.match_pos_img[o], mg = K.match_grad[o];
+  const float mgn = K.match_gnorm[o];
   bool dirty = false;
-  if (reg_set && reg_set[o]) { rho = reg_r[o]; srho = reg_s[o]; dirty = true; }         // second phase of regularize1Iter (edge_map.cpp:252-257)
-  if (K.match_id[o] < 0) {
+  if (rset) { rho = rr; srho = rs; dirty = true; }                                       // second phase of regularize1Iter (edge_map.cpp:252-257)
+  if (mid < 0) {
     if (dirty) { K.rho[o] = rho; K.srho[o] = srho; }
     return;
   }
   const float* vel = lane_in + (size_t)b * IN_STRIDE + IN_VEL;
   const float v0 = vel[0], v1 = vel[1], v2 = vel[2], fm = P.fm;
-  const float2 q = K.pos_img[o], q0 = K.match_pos_img[o], mg = K.match_grad[o];
-  const float mgn = K.match_gnorm[o];
   float v_rho = srho * srho;                                                             // :429
   const float ux = mg.x / mgn, uy = mg.y / mgn;
   const float Y = ux * (q.x - q0.x) + uy * (q.y - q0.y);                                 // :432
