@@ -12,6 +12,7 @@
 // rounds differently, so every row / column chain is walked in order by one thread and parallelism comes from the
 // (lanes x rows) resp. (lanes x columns) independent chains. Compiled with -fmad=false.
 #include "rbv_internal.cuh"
+#include <mutex>
 
 // ---------------------------------------------------------------------------------------------------------------
 // Row pass: out[r][c] = out[r][c-1] + in[r][c]   (scale_space.cpp:50-57)
@@ -1652,7 +1653,6 @@ int fe_dog_mag_debug(rbv_ctx* c, int lane, int which, float* d_out) {
 // rows x cols before k_colbox reads it). Two calls that overlap on the GPU (different streams, no ordering between them) race on it.
 static __device__ __align__(256) float rbv_noalloc_rowsum[RBV_NOALLOC_MAX_PIXELS];
 
-#include <mutex>
 static std::mutex noalloc_mu;
 static float* noalloc_ptr[64];   // device address of rbv_noalloc_rowsum, per device ordinal
 
