@@ -609,7 +609,7 @@ def run_b200(args):
 
 SCALE_K = ("k_boxpass", "k_boxpass2", "k_rowscan", "k_rowscan4", "k_colbox", "k_rowscan_lat", "k_colbox_lat")
 DETECT_K = ("k_detect_flags", "k_detect_scan", "k_detect_emit", "k_detect_emit_wide", "k_join", "k_tune")
-CHAIN_K = ("k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_extrot_ord", "k_chain_extrot", "k_tryvel_reduce", "k_extrot_reduce")   # launches that carry a serial add chain
+CHAIN_K = ("k_minimize_ord2", "k_minimize_ord4", "k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_extrot_ord", "k_chain_extrot", "k_tryvel_reduce", "k_extrot_reduce")   # launches that carry a serial add chain
 TRYVEL_K = ("k_tryvel_fast", "k_tryvel_fast2", "k_tryvel_fast4", "k_tryvel_ord2", "k_tryvel_ord4", "k_chain_tryvel", "k_tryvel_eval", "k_tryvel_reduce")
 
 

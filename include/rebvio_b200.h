@@ -170,7 +170,7 @@ int rbv_set_undistort(rbv_ctx* ctx, const float* K4, const float* D5);
 #define RBV_TUNE_FE_STREAM 5
 #define RBV_TUNE_FIELD_IN_FE 7 /* with RBV_TUNE_FE_STREAM: Core::buildDistanceField of a map runs behind its detect on the front-end stream, into the map's own field */
 /* key 6 is unused (was RBV_TUNE_BOX_SPLIT, measured and rejected in round 1) */
-#define RBV_TUNE_ORDERED 8 /* RBV_REDUCE_ORDERED tryVel and extRotVel: 0 = one launch each: evaluation blocks + one chain CTA per lane adding behind them (addends staged through shared memory by bulk copies), 2 = the same chains as kernels of their own behind the evaluation, 3 = tryVel as 0, extRotVel as 2, 1 = the first form (adding block per lane reading global memory) */
+#define RBV_TUNE_ORDERED 8 /* RBV_REDUCE_ORDERED tryVel and extRotVel: 0 = one launch each: evaluation blocks + one chain CTA per lane adding behind them (addends staged through shared memory by bulk copies), 2 = the same chains as kernels of their own behind the evaluation, 3 = tryVel as 0, extRotVel as 2, 4 = as 0 with all iterations + 1 tryVel calls of Core::minimizeVel in ONE launch (k_minimize_ord*: the chain CTAs stay, every lane advances on its own; measured no faster: the slowest lane's chain is the floor either way), 1 = the first form (adding block per lane reading global memory) */
 #define RBV_TUNE_COUNT 9
 int rbv_set_tuning(rbv_ctx* ctx, int key, int value);
 

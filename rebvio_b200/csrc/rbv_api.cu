@@ -312,6 +312,8 @@ static int create_body(rbv_ctx* c, const rbv_camera* cam, const rbv_detector_cfg
   RBV_CUDA(dalloc(&c->ticket, B));
   RBV_CUDA(dalloc(&c->blkagg, 2 * B * c->nblk));
   RBV_CUDA(cudaMemset(c->ticket, 0, sizeof(unsigned) * B));
+  RBV_CUDA(dalloc(&c->lm_done, B));
+  RBV_CUDA(cudaMemset(c->lm_done, 0, sizeof(int) * B));
   RBV_CUDA(dalloc(&c->ord_flags, B * c->nblk));
   RBV_CUDA(cudaMemset(c->ord_flags, 0, sizeof(int) * B * c->nblk));
   RBV_CUDA(cudaMemset(c->blkagg, 0, sizeof(float) * 2 * B * c->nblk));
@@ -363,7 +365,7 @@ extern "C" void rbv_destroy(rbv_ctx* c) {
   cudaStreamSynchronize(c->stream);
   void* dev[] = {c->img, c->rowsum, c->bufA, c->flags, c->rowcount, c->rowoffset, c->thr_dev, c->last_count, c->field, c->prod, c->fiabs,
                  c->fwd_head, c->fwd_next, c->reg_r, c->reg_s, c->lm, c->lane_in, c->lane_out, c->lane_cnt, c->probes,
-                 c->partials, c->ticket, c->blkagg, c->tgt, c->ord_flags};
+                 c->partials, c->ticket, c->blkagg, c->tgt, c->ord_flags, c->lm_done};
   for (void* p : dev) cudaFree(p);
   Stage* stg = stage_of(c);
   if (stg) {
@@ -1049,8 +1051,10 @@ static int enqueue_minimize(rbv_ctx* c, rbv_map* old_map, int part = 0) {
       RBV_LAUNCH(c, k_lm_init, ((c->P.lanes + 63) / 64), (64), 0, c->lm, c->lane_in, c->P.lanes);
     }
   }
-  if (part != 1)
-    for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
+  if (part != 1) {
+    if (lean && tr_minimize_persist_wanted(c)) TRY(tr_minimize_persist(c, old_map));   // RBV_TUNE_ORDERED = 4: all calls in one launch
+    else for (int t = 0; t <= c->P.iterations; ++t) TRY(tr_try_vel(c, old_map, t));
+  }
   return RBV_OK;
 }
 static int fetch_lm(rbv_ctx* c, float* vel3, float* Rvel9, float* score) {

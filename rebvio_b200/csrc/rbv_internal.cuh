@@ -133,6 +133,7 @@ struct rbv_ctx {
   // FAST-mode reductions: per-block FP64 partials, per-lane tickets, per-block "last matched |fi|" (ping-pong)
   double* partials;  // [B][nblk][27]
   unsigned* ticket;  // [B]
+  int* lm_done;      // [B] k_minimize_ord*: finished LM calls of the lane in the running launch (reset by k_quantile)
   int* ord_flags;    // [B][nblk] ORDERED: evaluation block j of the running k_tryvel_ord* launch has left its addends (set by the block, cleared by the chain's loader)
   float* blkagg;     // [2][B][nblk]
   int nblk;          // blocks of 256 keylines per lane
@@ -162,7 +163,7 @@ struct rbv_ctx {
   int raw_next;
   uint2* undist_map;          // [N] fixed-point remap of cv::undistort (rbv_set_undistort), nullptr = frames arrive undistorted
   unsigned long long launches;  // kernels launched since creation
-  unsigned long long klaunch[48];   // per kernel id
+  unsigned long long klaunch[64];   // per kernel id
   int tune[RBV_TUNE_COUNT];         // rbv_set_tuning: implementation choices (0 = automatic)
   int prof_mode;                    // -1 off, -2 every kernel, >= 0 that kernel id only
   void* prof;                       // ProfState* (rbv_api.cu)
@@ -196,14 +197,14 @@ enum { CNT_FWD = 0, CNT_DIR = 1, CNT_KF = 2, CNT_REG = 3, CNT_NKEY = 4, CNT_ATHR
   X(k_kalman) X(k_lm_init) X(k_tryvel_fast) X(k_residual_resolve) X(k_extrot_fast)        \
   X(k_field_band) X(k_boxpass) X(k_u8_to_f32) X(k_detect_emit_wide) X(k_pack_targets) X(k_rowscan4) \
   X(k_tryvel_fast2) X(k_tryvel_fast4) X(k_rowscan_lat) X(k_colbox_lat) X(k_undistort_map) X(k_undistort) \
-  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord) X(k_boxpass2) X(k_chain_tryvel) X(k_chain_extrot)
+  X(k_imu_pre) X(k_imu_fuse) X(k_servo) X(k_tryvel_ord2) X(k_tryvel_ord4) X(k_extrot_ord) X(k_boxpass2) X(k_chain_tryvel) X(k_chain_extrot) X(k_minimize_ord2) X(k_minimize_ord4)
 enum {
 #define X(n) KID_##n,
   RBV_KERNEL_LIST(X)
 #undef X
   KID_COUNT
 };
-static_assert(KID_COUNT <= 48, "rbv_ctx::klaunch holds 48 kernel ids");
+static_assert(KID_COUNT <= 64, "rbv_ctx::klaunch holds 64 kernel ids");
 void rbv_prof_begin(rbv_ctx* c, int kid);
 void rbv_prof_end(rbv_ctx* c, int kid);
 #define RBV_LAUNCH(c, kern, grid, block, smem, ...)                     \
@@ -239,6 +240,8 @@ int tr_pack_targets(rbv_ctx* c, rbv_map* map);   // refresh the packed copy afte
 int tr_rotate(rbv_ctx* c, rbv_map* map);                   // R in lane_in[IN_R]
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm);
 int tr_ordered_legacy(const rbv_ctx* c);
+int tr_minimize_persist_wanted(const rbv_ctx* c);
+int tr_minimize_persist(rbv_ctx* c, rbv_map* map);
 size_t tr_ordered_floats(int lanes, int kmax);   // floats of c->prod the chain kernels' addend layout needs
 int tr_debug_addends(rbv_ctx* c, int plane, int lane, float* out, int n);
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call);     // lm_call: -1 = single evaluation (vel, srmin in lane_in), t >= 0 = LM call t

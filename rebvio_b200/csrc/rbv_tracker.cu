@@ -340,7 +340,7 @@ int tr_rotate(rbv_ctx* c, rbv_map* map) {
 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) k_quantile(KeylineSoA K, const int* __restrict__ count, float percentile, int bins, int kmax,
-                                                  LMState* lm, float* lane_out, int to_lm, const float* __restrict__ lane_in) {
+                                                  LMState* lm, float* lane_out, int to_lm, const float* __restrict__ lane_in, int* lm_done) {
   __shared__ int hist[RBV_MAX_QBINS];
   const int b = blockIdx.x, n = count[b];
   for (int i = threadIdx.x; i < bins; i += blockDim.x) hist[i] = 0;
@@ -362,6 +362,7 @@ __global__ void __launch_bounds__(1024) k_quantile(KeylineSoA K, const int* __re
     }
     if (to_lm) {
       lm[b].sigma_rho_min = out;
+      lm_done[b] = 0;   // k_minimize_ord*: number of finished LM calls of this lane (the minimisation always follows its quantile)
       if (to_lm == 2)   // also the start velocity of Core::minimizeVel (what k_lm_init does for the stand-alone call)
         for (int i = 0; i < 3; ++i) lm[b].vel[i] = lane_in[(size_t)b * IN_STRIDE + IN_VEL + i];
     }
@@ -371,7 +372,7 @@ __global__ void __launch_bounds__(1024) k_quantile(KeylineSoA K, const int* __re
 
 int tr_quantile(rbv_ctx* c, rbv_map* map, float pct, int bins, int to_lm) {
   if (bins < 1 || bins > RBV_MAX_QBINS) { rbv_set_error("quantile bins out of range"); return RBV_ERR_ARG; }
-  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (1024), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm, c->lane_in);
+  RBV_LAUNCH(c, k_quantile, (c->P.lanes), (1024), 0, map->k, map->count, pct, bins, c->P.kmax, c->lm, c->lane_out, to_lm, c->lane_in, c->lm_done);
   RBV_CUDA(cudaGetLastError());
   return RBV_OK;
 }
@@ -827,7 +828,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
                                                          double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                          const float* __restrict__ agg_prev, float* __restrict__ agg_cur, int nblk,
                                                          LMState* lm, float* lane_out, int lm_call, const DevParams& P,
-                                                         float* __restrict__ rows, int* __restrict__ ord_flags = nullptr) {
+                                                         float* __restrict__ rows, int* __restrict__ ord_flags = nullptr, bool persist = false) {
   __shared__ double sm[(TV_TPB / 32) * 10];
   __shared__ double result[10];
   __shared__ float warp_val[TV_TPB / 32];
@@ -847,15 +848,21 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
 #pragma unroll
   for (int k = 0; k < KPT; ++k) { code[k] = -2.0f; res[k] = 0.0f; }
   if (nvalid > 0) {
-    const float v0 = vel_ptr[(size_t)b * vel_stride], v1 = vel_ptr[(size_t)b * vel_stride + 1], v2 = vel_ptr[(size_t)b * vel_stride + 2];
-    const float srmin = sr_ptr[(size_t)b * sr_stride], thr = thr_o[b];
+    // (__ldcg: in k_minimize_ord* the velocity was written by the lane's chain CTA earlier in the SAME launch - no stale L1 / read-only path)
+    const float v0 = __ldcg(vel_ptr + (size_t)b * vel_stride), v1 = __ldcg(vel_ptr + (size_t)b * vel_stride + 1), v2 = __ldcg(vel_ptr + (size_t)b * vel_stride + 2);
+    const float srmin = __ldcg(sr_ptr + (size_t)b * sr_stride), thr = thr_o[b];
     const unsigned* __restrict__ field_b = field + (size_t)b * P.npix;
     // ---- round trip 1: every field of the KPT keylines, no test in between
     float gn[KPT], srho[KPT], rho[KPT];
     unsigned mt[KPT];
     float2 pi[KPT], g[KPT];
     tv_ld<KPT>(Ko.gnorm + o, gn); tv_ld<KPT>(Ko.srho + o, srho); tv_ld<KPT>(Ko.rho + o, rho);
-    if (lm_call != 0) tv_ld<KPT>(Ko.residual + o, res);   // call 0 of minimizeVel starts from residuals = 0 (core.cpp:158): no fill pass, no read
+    if (lm_call != 0) {   // call 0 of minimizeVel starts from residuals = 0 (core.cpp:158): no fill pass, no read
+      if (persist) {      // written by the previous call's block earlier in the same launch: read past L1
+#pragma unroll
+        for (int k = 0; k < KPT; ++k) res[k] = (k < nvalid) ? __ldcg(Ko.residual + o + k) : 0.0f;
+      } else tv_ld<KPT>(Ko.residual + o, res);
+    }
     tv_ld<KPT>(Ko.matches + o, mt); tv_ld2<KPT>(Ko.pos_img + o, pi); tv_ld2<KPT>(Ko.grad + o, g);
     float w[KPT], rho_p[KPT], px[KPT], py[KPT], pxc[KPT], pyc[KPT];
     bool skip[KPT], penalty[KPT];
@@ -975,7 +982,7 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
     // (the grid-sync pattern); a fence in every thread made all 256 of them wait for their stores to be acknowledged (`membar` stalls)
     // (blk * KPB < n: block 0 of a lane WITHOUT keylines also runs - it owns the lane's bookkeeping - but the chain has no chunk to
     // wait for then and would leave the flag standing for the next launch)
-    if (ord_flags && t == 0 && blk * KPB < n) {
+    if (ord_flags && !persist && t == 0 && blk * KPB < n) {
       __threadfence();
       asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
     }
@@ -999,7 +1006,17 @@ __device__ __forceinline__ void tryvel_fastn_body(const int b, const int blk, Ke
     tv_st<KPT, float>(Ko.residual + o, out, nvalid);
   }
   if (t == TV_TPB - 1) agg_cur[(size_t)b * nblk + blk] = has ? val : -1.0f;
-  if constexpr (ORD) return;   // the addends are in `rows`: the chain kernel behind this one adds them in keyline order
+  if constexpr (ORD) {
+    if (persist) {   // k_minimize_ord*: the next call's block of these keylines reads the residuals and the block aggregate written above, so the
+      // flag goes up behind them (barrier + one cumulative fence + release; the chain's release of the lane's call counter carries it on)
+      __syncthreads();
+      if (ord_flags && t == 0 && blk * KPB < n) {
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], 1;" ::"l"(ord_flags + (size_t)b * nblk + blk) : "memory");
+      }
+    }
+    return;   // the addends are in `rows`: the chain adds them in keyline order
+  }
   if (t < 10) {
     double s2 = 0.0;
 #pragma unroll
@@ -1205,6 +1222,72 @@ __global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_ord2(RBV_TV_PARAMS, 
 __global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_ord4(RBV_TV_PARAMS, float* __restrict__ rows, int* __restrict__ ord_flags, float* dbg) {
   tryvel_ord_entry<4>(RBV_TV_PASS, rows, ord_flags, dbg);
 }
+// Core::minimizeVel in ONE launch (RBV_TUNE_ORDERED = 4): grid (lanes, 1 + calls x blocks). Row 0: one chain CTA per lane, which stays for all
+// iterations + 1 tryVel calls: chain, LM step, then it publishes the lane's call counter (lm_done, reset by k_quantile in front of every
+// minimisation). Rows 1..: the evaluation blocks of call 0, then of call 1, ...; a block of call t waits for lm_done[lane] >= t, i.e. for the
+// velocity its call evaluates. Lanes never wait for each other: a lane with few keylines runs ahead, and no call pays for the slowest
+// lane's chain as the per-call launches do. Progress: blocks are dispatched in linear order, so every block another block can wait for
+// (the lane's chain CTA, the blocks of earlier calls) is resident or finished by then; a waiting block only holds its slot.
+template <int KPT>
+__device__ __forceinline__ void minimize_ord_entry(KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o,
+                                                   const float4* __restrict__ tgt, const unsigned* __restrict__ field, float* blkagg, int parity0,
+                                                   int nblk, LMState* lm, float* lane_out, int ncall, const DevParams& P, float* __restrict__ rows,
+                                                   int* __restrict__ ord_flags, int* lm_done, int nb) {
+  extern __shared__ __align__(128) float ord_ring[];
+  __shared__ __align__(8) unsigned long long bars[2 * ORD_NST];
+  const int b = blockIdx.x;
+  const float* lmf = reinterpret_cast<const float*>(lm);
+  constexpr int LMF = (int)(sizeof(LMState) / sizeof(float));
+  const float* vel0 = lmf + offsetof(LMState, vel) / sizeof(float);
+  const float* vel1 = lmf + offsetof(LMState, vnew) / sizeof(float);
+  if (blockIdx.y == 0) {
+    if (threadIdx.x >= 64) return;
+    for (int t = 0; t < ncall; ++t) {
+      const float s = ordered_chain<OrdTV>(rows + (size_t)b * OrdTV::lane_stride(P.kmax), count_o[b], ord_ring, bars, nullptr,
+                                           ord_flags + (size_t)b * nblk, TV_TPB * KPT);
+      if (threadIdx.x < 32) {
+        tryvel_chain_finish(s, b, lm, lane_out, t == 0 ? vel0 : vel1, LMF, t, P);
+        if (threadIdx.x == 0) {   // the LM state of call t is out: the lane's blocks of call t + 1 may go
+          __threadfence();
+          asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(lm_done + b), "r"(t + 1) : "memory");
+        }
+      }
+    }
+    return;
+  }
+  const int t = ((int)blockIdx.y - 1) / nb, blk = ((int)blockIdx.y - 1) % nb;
+  {
+    const int n = count_o[b];
+    if (blk >= max(1, (n + TV_TPB * KPT - 1) / (TV_TPB * KPT))) return;   // before any waiting: nothing of this block is a keyline
+  }
+  if (t > 0) {
+    if (threadIdx.x == 0) {
+      long long t0 = 0;
+      for (int spin = 0;; ++spin) {
+        int v;
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(lm_done + b) : "memory");
+        if (v >= t) break;
+        __nanosleep(200);
+        if ((spin & 1023) == 1023) {
+          if (t0 == 0) t0 = clock64();
+          else if (clock64() - t0 > 8000000000ll) __trap();   // seconds: a protocol bug must fault, never hang the device
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const size_t half = (size_t)P.lanes * nblk;
+  const int par = (parity0 + t) & 1;
+  tryvel_fastn_body<KPT, true>(b, blk, Ko, count_o, thr_o, tgt, field, t == 0 ? vel0 : vel1, LMF, lmf + offsetof(LMState, sigma_rho_min) / sizeof(float), LMF,
+                               nullptr, nullptr, blkagg + (size_t)(1 - par) * half, blkagg + (size_t)par * half, nblk, lm, lane_out, t, P, rows, ord_flags, true);
+}
+#define RBV_MIN_PARAMS KeylineSoA Ko, const int* __restrict__ count_o, const float* __restrict__ thr_o, const float4* __restrict__ tgt,          \
+                       const unsigned* __restrict__ field, float* blkagg, int parity0, int nblk, LMState* lm, float* lane_out, int ncall,        \
+                       const __grid_constant__ DevParams P, float* __restrict__ rows, int* __restrict__ ord_flags, int* lm_done, int nb
+#define RBV_MIN_PASS Ko, count_o, thr_o, tgt, field, blkagg, parity0, nblk, lm, lane_out, ncall, P, rows, ord_flags, lm_done, nb
+__global__ void __launch_bounds__(TV_TPB) k_minimize_ord2(RBV_MIN_PARAMS) { minimize_ord_entry<2>(RBV_MIN_PASS); }
+__global__ void __launch_bounds__(TV_TPB) k_minimize_ord4(RBV_MIN_PARAMS) { minimize_ord_entry<4>(RBV_MIN_PASS); }
+
 // the two-kernel form (RBV_TUNE_ORDERED = 2): the ten sums of one tryVel call in keyline order + the LM step, behind the evaluation kernel
 __global__ void __launch_bounds__(64) k_chain_tryvel(const int* __restrict__ count_o, const float* __restrict__ rows, LMState* lm, float* lane_out,
                                                      const float* __restrict__ vel_ptr, int vel_stride, int lm_call,
@@ -1227,6 +1310,29 @@ __global__ void __launch_bounds__(TV_TPB) k_residual_resolve(KeylineSoA Ko, cons
 // RBV_REDUCE_ORDERED through the first implementation (k_tryvel_eval + k_tryvel_reduce, k_extrot_rows + k_extrot_reduce: evaluation, then
 // one block per lane adding behind it) instead of the chain warps next to the evaluation; kept as a cross-check (RBV_TUNE_ORDERED = 1)
 int tr_ordered_legacy(const rbv_ctx* c) { return c->reduce_mode == RBV_REDUCE_ORDERED && c->tune[RBV_TUNE_ORDERED] == 1; }
+
+// all iterations + 1 tryVel calls of Core::minimizeVel in one launch (k_minimize_ord*); 0 = not this configuration, the caller launches call by call
+int tr_minimize_persist_wanted(const rbv_ctx* c) {
+  return c->reduce_mode == RBV_REDUCE_ORDERED && c->tune[RBV_TUNE_ORDERED] == 4 && c->prof_mode == -1 ? 1 : 0;
+}
+int tr_minimize_persist(rbv_ctx* c, rbv_map* map) {
+  const DevParams& P = c->P;
+  if (!c->field_map) { rbv_set_error("minimizeVel before buildDistanceField"); return RBV_ERR_STATE; }
+  int kpt = c->tune[RBV_TUNE_TRYVEL] ? c->tune[RBV_TUNE_TRYVEL] : (P.lanes >= 8 ? 4 : 2);
+  if (kpt != 2) kpt = 4;
+  const int nb = (P.kmax + TV_TPB * kpt - 1) / (TV_TPB * kpt), ncall = P.iterations + 1;
+  const dim3 grid(P.lanes, 1 + ncall * nb);
+  if (grid.y > 65535u) { rbv_set_error("minimizeVel: too many blocks for one launch"); return RBV_ERR_ARG; }
+  if (kpt == 2) { RBV_LAUNCH(c, k_minimize_ord2, (grid), (TV_TPB), ORD_SMEM(OrdTV), map->k, map->count, map->threshold, c->tgt, c->field, c->blkagg, c->tv_parity, c->nblk, c->lm, c->lane_out, ncall, P, c->prod, c->ord_flags, c->lm_done, nb); }
+  else { RBV_LAUNCH(c, k_minimize_ord4, (grid), (TV_TPB), ORD_SMEM(OrdTV), map->k, map->count, map->threshold, c->tgt, c->field, c->blkagg, c->tv_parity, c->nblk, c->lm, c->lane_out, ncall, P, c->prod, c->ord_flags, c->lm_done, nb); }
+  const size_t half = (size_t)P.lanes * c->nblk;
+  float* agg_last = c->blkagg + (size_t)((c->tv_parity + ncall - 1) & 1) * half;   // the aggregates of the last call (residual look-back of pending keylines)
+  if (c->seq_fused) { c->seq_resolve_agg = agg_last; c->seq_resolve_kpb = TV_TPB * kpt; }
+  else RBV_LAUNCH(c, k_residual_resolve, (dim3(c->nblk, P.lanes)), (TV_TPB), 0, map->k, map->count, agg_last, c->nblk, P.kmax, TV_TPB * kpt);
+  c->tv_parity = (c->tv_parity + ncall) & 1;
+  RBV_CUDA(cudaGetLastError());
+  return RBV_OK;
+}
 
 // lm_call = -1: single evaluation at lane_in vel / sigma_rho_min; 0: first LM call at lm.vel; >= 1: at lm.vnew
 int tr_try_vel(rbv_ctx* c, rbv_map* map, int lm_call) {
@@ -2062,6 +2168,8 @@ int tr_kalman(rbv_ctx* c, rbv_map* map) {
 int tr_init_ordered(void) {
   RBV_CUDA(cudaFuncSetAttribute(k_chain_tryvel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
   RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
+  RBV_CUDA(cudaFuncSetAttribute(k_minimize_ord2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
+  RBV_CUDA(cudaFuncSetAttribute(k_minimize_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
   RBV_CUDA(cudaFuncSetAttribute(k_tryvel_ord4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdTV)));
   RBV_CUDA(cudaFuncSetAttribute(k_chain_extrot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdER)));
   RBV_CUDA(cudaFuncSetAttribute(k_extrot_ord, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ORD_SMEM(OrdER)));

@@ -35,7 +35,7 @@ def kernel_bytes(name, N, K, B, planes=1, P=20.0, words=0):
         "k_rotate": 48.0 * K,
         "k_quantile": 4.0 * K,
         "k_tryvel_fast": 68.0 * K, "k_tryvel_fast2": 68.0 * K, "k_tryvel_fast4": 68.0 * K,
-        "k_tryvel_ord2": 68.0 * K, "k_tryvel_ord4": 68.0 * K,   # the addend planes the chain kernel reads back (40 B written + 40 B read per keyline) are not algorithmic
+        "k_tryvel_ord2": 68.0 * K, "k_tryvel_ord4": 68.0 * K, "k_minimize_ord2": 6 * 68.0 * K, "k_minimize_ord4": 6 * 68.0 * K,   # the addend planes the chain kernel reads back (40 B written + 40 B read per keyline) are not algorithmic
         "k_chain_tryvel": 0.0, "k_chain_extrot": 0.0,           # serial float32 add chains: latency, not bytes
         "k_extrot_fast": 40.0 * K, "k_extrot_ord": 40.0 * K,
         "k_tryvel_eval": 68.0 * K,           # 36 B keyline + 4 B field + 20 B target + 8 B write

@@ -47,12 +47,14 @@ def test_cuda_vs_reference_golden_teacher_forced(name):
 
 
 @pytest.mark.parametrize("name,nf,legacy,lanes", [("C5:320x240", 4, 0, 2), ("C1", 3, 0, 2), ("C2", 4, 0, 2), ("C3", 3, 0, 2), ("C2", 3, 1, 2),
-                                                  ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9), ("C2", 3, 2, 2), ("C5:320x240", 4, 2, 5)])
+                                                  ("C5:320x240", 4, 0, 21), ("C2", 3, 0, 9), ("C2", 3, 2, 2), ("C5:320x240", 4, 2, 5),
+                                                  ("C5:320x240", 4, 4, 2), ("C2", 3, 4, 9)])
 def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     """No teacher forcing: the whole chain runs on its own state for nf frames and still reproduces the CPU bits.
     legacy = RBV_TUNE_ORDERED: 0 = the default (tryVel: evaluation blocks and one chain CTA per lane in ONE launch, the chain adding behind the
     evaluation; k_extrot_ord likewise), 2 = the same chains as kernels of their own (k_chain_tryvel, k_chain_extrot) behind the evaluation,
-    1 = the first implementation (one adding block per lane reading global memory)."""
+    1 = the first implementation (one adding block per lane reading global memory), 4 = Core::minimizeVel as ONE launch (k_minimize_ord*:
+    the chain CTAs stay for all six tryVel calls, every lane advances on its own)."""
     spec, frames, R_rel = common.sequence(name, nf)
     cfg = common.cfgs_from_spec(spec)
     orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
@@ -65,6 +67,9 @@ def test_cuda_vs_oracle_free_running_ordered(name, nf, legacy, lanes):
     names = g.ctx.profile_launches()
     if legacy == 1:
         assert names.get("k_tryvel_reduce", 0) > 0 and names.get("k_extrot_reduce", 0) > 0 and names.get("k_extrot_ord", 0) == 0
+    elif legacy == 4:
+        assert names.get("k_minimize_ord2", 0) + names.get("k_minimize_ord4", 0) > 0 and names.get("k_extrot_ord", 0) > 0
+        assert names.get("k_tryvel_reduce", 0) == 0
     else:
         assert names.get("k_tryvel_ord2", 0) + names.get("k_tryvel_ord4", 0) > 0 and names.get("k_extrot_ord", 0) > 0
         assert (names.get("k_chain_tryvel", 0) > 0) == (legacy == 2) and (names.get("k_chain_extrot", 0) > 0) == (legacy == 2) and names.get("k_tryvel_reduce", 0) == 0
@@ -311,7 +316,7 @@ def test_lanes_are_independent():
     ctx.close()
 
 
-@pytest.mark.parametrize("form", [0, 2])
+@pytest.mark.parametrize("form", [0, 2, 4])
 def test_ragged_lanes_ordered(form):
     """Lanes with very different keyline counts in one context, RBV_REDUCE_ORDERED: a full frame, a frame with half its texture, a flat
     frame (no keylines), a frame with one small textured patch (less than one chunk of the add chain); then the lanes swap their inputs
@@ -770,8 +775,8 @@ def test_device_threshold_servo_equals_host_servo_on_one_stream():
     ref.close(); dev.close()
 
 
-@pytest.mark.parametrize("name", ["C1", "C2"])
-def test_200_frames_free_running_bit_exact(name):
+@pytest.mark.parametrize("name,form", [("C1", 0), ("C2", 0)])
+def test_200_frames_free_running_bit_exact(name, form):
     """BASELINE.json configs[0] / configs[1] at length: 200 frames free-running (no teacher forcing) in the default reduce mode
     (RBV_REDUCE_ORDERED: float32 sums in keyline order). Every frame's counts, minimiser trace, Vg, P_Vg, score and 6x6 system are
     bit-identical to the oracle's, X within the solve tolerance, the integrated pose identical, and the whole map (every keyline
@@ -782,7 +787,7 @@ def test_200_frames_free_running_bit_exact(name):
     orc = pyref.OracleLib(cfg[0], cfg[1], cfg[3], cfg[2])
     T = H.run_lean(orc, frames, R_rel, snap_every=25)
     orc.close()
-    g = _gpu(cfg, lanes=2, lane=1)
+    g = _gpu(cfg, lanes=2, lane=1, tune={capi.TUNE_ORDERED: form})   # form 4: Core::minimizeVel as one launch (k_minimize_ord*)
     G = H.run_lean(g, frames, R_rel, snap_every=25)
     g.close()
     for k in range(nf):
