@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fast", action="store_true", help="skip the RBV_REDUCE_FAST leg")
     ap.add_argument("--no-sweep", action="store_true", help="skip the configs[2] / configs[4] size sweep")
+    ap.add_argument("--check-schedule", type=int, default=24, metavar="N", help="parity self-check of the benchmarked configuration: N frames of all lanes through the in-order schedule and through the timed two-stream schedule, every tracker output and the last map compared bit for bit (config.schedule_check; 0 = skip)")
     ap.add_argument("--undistort", action="store_true", help="e2e leg: raw camera frames, Camera::undistort (EuRoC cam0 model) on the device")
     ap.add_argument("--imu", action="store_true", help="run the reference's IMU filters on the device between the tracker halves "
                     "(rbv_track_imu: gyro-bias correction + scale-attitude-bias filter, SURVEY 8(f2)) instead of the visual-only fusion")
@@ -420,6 +421,33 @@ def run_b200(args):
         pipe.close()
         return res
 
+    def schedule_check(n):
+        """the timed configuration against the in-order schedule on the same resident frames: outputs of every tracked pair and the
+        newest map, byte for byte (in order vs the oracle / the compiled reference is what tests/ cover)"""
+        n = min(n, nf)
+        keys = ("Vg", "X", "Wx", "matches", "kf_matches", "ok") + (("imu",) if args.imu else ("V",))
+        runs = []
+        for lg in (0, lag):
+            pipe = BatchedPipeline(cam, det, mapc, core, B, device=local, reduce_mode=mode, cuda_stream=stream.cuda_stream, imu_cfg=imu_cfg, overlap=lg)
+            for key, val in tune:
+                pipe.ctx.set_tuning(key, val)
+            outs = []
+            for t in range(n):
+                o = pipe.push(device_ptr=d_frames[t].data_ptr(), **(targs(t - lg) if t >= 1 + lg else {}))
+                if t >= 1 + lg:
+                    outs.append(o)
+            if lg:
+                outs.extend(pipe.flush([targs(n - lg + i) for i in range(lg)]))
+            pipe.ctx.sync()
+            last = [pipe.newest_map().keylines(b)[0].tobytes() for b in range(0, B, max(1, B // 8))]
+            runs.append(([{k: np.asarray(o[k]).tobytes() for k in keys} for o in outs], last))
+            pipe.close()
+        (a, la), (b, lb) = runs
+        bad = [(i, k) for i, (x, y) in enumerate(zip(a, b)) for k in keys if x[k] != y[k]]
+        return {"frames": n, "lanes": B, "pairs_compared": min(len(a), len(b)), "pairs_expected": n - 1, "mismatches": len(bad), "first_mismatch": bad[:1],
+                "last_map_identical": la == lb and len(a) == len(b) == n - 1,
+                "what": f"two-stream schedule (overlap {lag}) against in order on one stream, same frames: {', '.join(keys)} of every pair and the newest map of every 8th lane, byte for byte"}
+
     # ---- leg 1: device-resident inputs, default (bit-exact) reduce mode ---------------------------------------------
     main = device_leg(mode, RW, True)
     table, top = main["table"], main["top"]
@@ -502,6 +530,8 @@ def run_b200(args):
             "roofline": dict(roof(top), frame_level={"achieved": frame_gbs, "frac": frame_gbs / peak,
                                                      "bytes_per_frame": roofline.frame_bytes(N, K_mean, probes)}),
             "clocks": main["clocks"], "gpu_launches": main["launches"]}
+    if args.check_schedule and lag:
+        line["config"]["schedule_check"] = schedule_check(args.check_schedule)
     if top_hbm != top:   # the dominant kernel that only streams, measured the same way
         line["roofline_streaming_kernel"] = roof(top_hbm)
 
