@@ -13,6 +13,10 @@ Workload (BASELINE.json `metric`: "frames/sec @752x480 (1 GPU p50 latency; batch
     copies that step's frames from pinned host memory to the device and reads counts / velocities / 6x6 systems back.
   * `roofline` — the dominant kernel by CUDA-event time; its events are taken in windows of their own (never inside the timed
     one: events cannot bracket a kernel inside a replayed graph).
+  * `roofline_streaming_kernel` — the same object for the dominant kernel that only streams (in ORDERED mode the dominant launch carries the
+    lanes' serial float32 add chains, so its `roofline` also states that latency floor).
+  * `config.schedule_check` — parity self-check of the timed configuration: --check-schedule N frames of all lanes through the in-order
+    schedule and through the timed two-stream schedule, every tracker output of every pair and the newest maps compared byte for byte.
   * `single_stream`, `single_stream_imu` (N = 1) — configs[1]: one 752x480 stream, lanes = 1, p50 per-frame latency.
   * `sweep` (N = 1) — configs[2] and configs[4]: the 1280x720 dense scene and 320x240 ... 3840x2160, 3 timed steps each.
 Multi-GPU: replicas only (one frame does not shard); ranks share nothing on the data path, the barrier and the
