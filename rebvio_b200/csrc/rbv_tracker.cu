@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict_
   extern __shared__ __align__(16) unsigned fb_cell[];
   __shared__ int s_lo, s_hi;
   // per warp: the 32 keylines of its current round (unit normal, position, r-interval) and their work items
-  __shared__ float s_ux[FB_TPB], s_uy[FB_TPB], s_px[FB_TPB], s_py[FB_TPB];
+  __shared__ __align__(16) float4 s_kl[FB_TPB];       // (unit normal x, y, position x, y): one 16-byte load per work item
   __shared__ int s_ral[FB_TPB];                         // r-interval of the keyline: start (low 16 bits, signed) | length << 16
   __shared__ unsigned short s_item[FB_TPB * FB_MAXI];   // work item -> keyline of the warp's round (low 5 bits) | item of that keyline << 5
   const int b = blockIdx.y, t = threadIdx.x;
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict_
         if (!(fabsf(ux) <= 2.0f && fabsf(uy) <= 2.0f)) len = 0;   // non-finite normal: the reference's getIndex yields -1 for every r
       }
     }
-    s_ux[t] = ux; s_uy[t] = uy; s_px[t] = p.x; s_py[t] = p.y; s_ral[t] = (ra & 0xFFFF) | (len << 16);
+    s_kl[t] = make_float4(ux, uy, p.x, p.y); s_ral[t] = (ra & 0xFFFF) | (len << 16);
     // exclusive scan of the item counts over the warp, then every keyline lists its items in the warp's item table
     const int items = min((len + FB_G - 1) / FB_G, FB_MAXI);
     int inc = items;
@@ -156,7 +156,8 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict_
       const int kra = (int)(short)(ral & 0xFFFF);
       const int rs = kra + (it >> 5) * FB_G;
       const int re = kra + (ral >> 16);
-      const float kux = s_ux[ks], kuy = s_uy[ks], kpx = s_px[ks], kpy = s_py[ks];
+      const float4 kl = s_kl[ks];
+      const float kux = kl.x, kuy = kl.y, kpx = kl.z, kpy = kl.w;
       const unsigned lowkey = 0xFFFFFFu - (unsigned)(k0 + (it & 31));
       // The FB_G candidates of the item as straight-line predicated code: FB_G independent address chains, then FB_G
       // loads, then the (few) atomics. A loop with early `continue`s made every warp crawl through one dependent chain
@@ -183,8 +184,14 @@ __global__ void __launch_bounds__(FB_TPB) k_field_band(const float4* __restrict_
         const float fx = kux * fr + kpx;                                                  // :51
         const unsigned by = (unsigned)__float_as_int(__fadd_rz(__fadd_rz(fabsf(fy), 0.5f), 8388608.0f));
         const unsigned bx = (unsigned)__float_as_int(__fadd_rz(__fadd_rz(fabsf(fx), 0.5f), 8388608.0f));
-        addr[u] = by * cols4 + (bx * 4u + A0);
-        key[u] = lowkey + ((unsigned)__float_as_int(fabsf(fr) + 8388608.0f) << 24);        // :54-56 as min over (|r|, -idx)
+        const unsigned kb = (unsigned)__float_as_int(fabsf(fr) + 8388608.0f);
+        // address and key as explicit multiply-adds (left to the compiler the folded constants come apart again: 7 integer instructions
+        // per candidate instead of 3): addr = by * 4 cols + (bx * 4 + A0); key = |r| << 24 | (0xFFFFFF - keyline), :54-56 as min over (|r|, -idx)
+        asm("{ .reg .u32 t;\n"
+            "  mad.lo.u32 t, %3, 4, %5;\n"
+            "  mad.lo.u32 %0, %2, %4, t;\n"
+            "  mad.lo.u32 %1, %6, 16777216, %7; }"
+            : "=r"(addr[u]), "=r"(key[u]) : "r"(by), "r"(bx), "r"(cols4), "r"(A0), "r"(kb), "r"(lowkey));
         // in range: r < re, round(fy) in [r0, r1), round(fx) in [0, cols) - a negative coordinate rounds to an index >= 0 only for
         // v > -0.5 (round(-0.3) = -0 -> 0, round(-0.5) = -1); NaN fails every compare. The five compares chain into ONE predicate that
         // guards the load (a predicated instruction, no branch per candidate); out of range reads as 0 = "nothing to improve" below.
