@@ -1077,16 +1077,16 @@ __global__ void __launch_bounds__(TV_TPB, TV_MINB) k_tryvel_fast4(RBV_TV_PARAMS)
 // (core.cpp:130-139,244-245); match indices downstream depend on those bits. A sequential float32 sum cannot be re-associated,
 // so the chain itself stays serial: ONE warp per lane, thread a = accumulator a, one dependent FADD (4 cycles, ~2 ns) per keyline.
 // What can be done is to take everything else off that chain:
-//   * the evaluation kernel (k_tryvel_ord2/4, k_extrot_ord: the FAST kernels' per-keyline arithmetic) leaves the float32 ADDENDS
-//     of every keyline in planes [accumulator][lane][keyline] (zeros where the reference adds nothing: x + 0 == x exactly);
-//   * the chain kernel (k_chain_tryvel / k_chain_extrot: one 32-thread CTA per lane, so 64 lanes spread over 64 SMs and the rest
-//     of the GPU stays free for the front-end stream) stages 256 / 128-keyline chunks of the planes into a 4-deep shared-memory
-//     ring with TMA bulk copies (one per row and chunk, mbarrier completion) and lane a adds row a: nothing but an LDS.128 per
-//     four keylines and the FADDs on that warp. (Forming the products on the chain warp costs an FMUL per keyline next to the FADD; the FP32 pipe takes a
-//     3-register instruction every 2 cycles per scheduler, and the chain ran at 8 cycles per keyline instead of 4.)
-// Round 2 first ran the chain warps INSIDE the evaluation launch, fed block by block through release/acquire flags, to hide the
-// chain behind the evaluation; that version produced lane-dependent sums under load on the B200 (no cause found by inspection) and
-// was dropped for this two-kernel form: evaluation, then chain - nothing to synchronise but the kernel boundary.
+//   * the evaluation blocks (k_tryvel_ord2/4, k_extrot_ord: the FAST kernels' per-keyline arithmetic) leave the float32 ADDENDS of every
+//     keyline in the chunked layout above (OrdLayout; zeros where the reference adds nothing: x + 0 == x exactly) and raise a flag per block;
+//   * one chain CTA per lane rides in the SAME launch (grid row 0, dispatched first; 64 lanes = 64 SMs, the rest of the GPU stays free):
+//     its loader warp takes the flags of the blocks a chunk covers and stages the chunk with ONE TMA bulk copy into a 4-deep shared-memory
+//     ring (mbarrier completion), its chain warp adds row a in lane a: nothing but an LDS.128 per four keylines and the FADDs on that
+//     warp. (Forming the products on the chain warp costs an FMUL per keyline next to the FADD; the FP32 pipe takes a 3-register
+//     instruction every 2 cycles per scheduler, and the chain ran at 8 cycles per keyline instead of 4.)
+// RBV_TUNE_ORDERED = 2 runs the same chain as a kernel of its own behind the evaluation (k_chain_tryvel / k_chain_extrot); = 4 keeps the
+// chain CTAs for all tryVel calls of a minimisation (k_minimize_ord*). History of the round (wrong sums that turned out to be an nvcc
+// unroller bug in the block loop, the staging forms tried): DESIGN.md "ORDERED reductions".
 
 // sixteen float32 adds in keyline order
 __device__ __forceinline__ void ord_add16(float& s, const float4& a, const float4& b, const float4& c, const float4& d) {
